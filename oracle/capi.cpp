@@ -1,0 +1,134 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see cv_prims.hpp).  Plain-C entry points so that pytest
+// (ctypes) and bench.py's CPU-baseline leg can drive the restatement in orb_oracle.hpp.
+#include <chrono>
+#include <thread>
+
+#include "orb_oracle.hpp"
+
+using namespace orbo;
+
+extern "C" {
+
+void* orbo_create(int nf, float sf, int nl, int ini, int mn) { return new Extractor(nf, sf, nl, ini, mn); }
+void orbo_destroy(void* e) { delete (Extractor*)e; }
+
+void orbo_tables(void* e, float* scale, float* inv, float* s2, float* is2, int* quota, int* umax) {
+  Extractor* E = (Extractor*)e;
+  for (int i = 0; i < E->nlevels; ++i) {
+    scale[i] = E->scale[i]; inv[i] = E->invScale[i]; s2[i] = E->sigma2[i]; is2[i] = E->invSigma2[i];
+    quota[i] = E->quota[i];
+  }
+  for (int i = 0; i <= kHalfPatch; ++i) umax[i] = E->umax[i];
+}
+
+// returns the keypoint count, <0 on degenerate geometry, -100 if cap is too small
+int orbo_extract(void* e, const uint8_t* img, int w, int h, int pitch, KeyPt* kps, uint8_t* desc, int cap) {
+  Extractor* E = (Extractor*)e;
+  std::vector<KeyPt> k; std::vector<uint8_t> d;
+  int n = E->extract(img, w, h, pitch, k, d);
+  if (n < 0) return n;
+  if (n > cap) return -100;
+  if (n) { std::memcpy(kps, k.data(), sizeof(KeyPt) * n); std::memcpy(desc, d.data(), 32 * (size_t)n); }
+  return n;
+}
+
+void orbo_level_size(void* e, int l, int* w, int* h) { Extractor* E = (Extractor*)e; *w = E->pyr[l].w; *h = E->pyr[l].h; }
+// copies the bordered plane, (w+38) x (h+38), tightly packed
+void orbo_level_copy(void* e, int l, uint8_t* dst) {
+  Extractor* E = (Extractor*)e;
+  std::memcpy(dst, E->pyr[l].buf.data(), E->pyr[l].buf.size());
+}
+int orbo_level_candidates(void* e, int l, KeyPt* out, int cap) {
+  Extractor* E = (Extractor*)e;
+  int n = (int)E->candidates[l].size();
+  for (int i = 0; i < n && i < cap; ++i) out[i] = E->candidates[l][i];
+  return n;
+}
+int orbo_level_keys(void* e, int l, KeyPt* out, int cap) {
+  Extractor* E = (Extractor*)e;
+  int n = (int)E->levelKeys[l].size();
+  for (int i = 0; i < n && i < cap; ++i) out[i] = E->levelKeys[l][i];
+  return n;
+}
+
+int orbo_stereo(void* eL, void* eR, const KeyPt* kL, const uint8_t* dL, int nL, const KeyPt* kR,
+                const uint8_t* dR, int nR, float bf, float fx, float* uRight, float* depth, int* sad) {
+  std::vector<KeyPt> a(kL, kL + nL), b(kR, kR + nR);
+  return stereo_match(*(Extractor*)eL, *(Extractor*)eR, a, dL, b, dR, bf, fx, uRight, depth, sad);
+}
+
+int orbo_search_init(const KeyPt* k1, const uint8_t* d1, int n1, const KeyPt* k2, const uint8_t* d2,
+                     int n2, int cols, int rows, float* prev, float ratio, int window, int checkOri,
+                     int* m12) {
+  return search_for_init(k1, d1, n1, k2, d2, n2, cols, rows, prev, ratio, window, checkOri != 0, m12);
+}
+
+int orbo_knn_ratio(const uint8_t* dA, const float* angA, int nA, const uint8_t* dB, const float* angB,
+                   int nB, int th, float ratio, int checkOri, int strict, int* m12) {
+  return knn_ratio_bucket(dA, angA, nA, dB, angB, nB, th, ratio, checkOri != 0, strict != 0, m12);
+}
+
+int orbo_hamming256(const uint8_t* a, const uint8_t* b) { return hamming256(a, b); }
+
+// --- primitives, exported so tests can pin them against cv2 -------------------------------
+void orbo_resize(const uint8_t* s, int sw, int sh, int sp, uint8_t* d, int dw, int dh, int dp) {
+  resize_linear_u8(s, sw, sh, sp, d, dw, dh, dp);
+}
+void orbo_border(const uint8_t* s, int w, int h, int sp, uint8_t* d, int dp, int b) { border_reflect101(s, w, h, sp, d, dp, b); }
+void orbo_blur(const uint8_t* s, int w, int h, int sp, uint8_t* d, int dp) { gauss7_sigma2(s, w, h, sp, d, dp); }
+int orbo_fast(const uint8_t* s, int w, int h, int sp, int t, int* xys, int cap) {
+  std::vector<FastPt> v;
+  fast9_16(s, w, h, sp, t, v);
+  for (int i = 0; i < (int)v.size() && i < cap; ++i) { xys[3 * i] = v[i].x; xys[3 * i + 1] = v[i].y; xys[3 * i + 2] = v[i].score; }
+  return (int)v.size();
+}
+float orbo_atan2(float y, float x) { return fast_atan2_deg(y, x); }
+void orbo_atan2_array(const float* y, const float* x, float* out, int n) { for (int i = 0; i < n; ++i) out[i] = fast_atan2_deg(y[i], x[i]); }
+void orbo_sincos_array(const float* a, float* s, float* c, int n) { for (int i = 0; i < n; ++i) { s[i] = libm_sinf(a[i]); c[i] = libm_cosf(a[i]); } }
+void orbo_libm_sincos_array(const float* a, float* s, float* c, int n) { for (int i = 0; i < n; ++i) { s[i] = sinf(a[i]); c[i] = cosf(a[i]); } }
+int orbo_quadtree(const KeyPt* cand, int n, int minX, int maxX, int minY, int maxY, int N, KeyPt* out, int cap) {
+  std::vector<KeyPt> c(cand, cand + n), o;
+  if (!distribute_quadtree(c, minX, maxX, minY, maxY, N, o)) return -1;
+  for (int i = 0; i < (int)o.size() && i < cap; ++i) out[i] = o[i];
+  return (int)o.size();
+}
+
+// --- CPU baseline: the reference's structure (one extractor per eye, per-frame serial
+// pipeline), one stereo frame per std::thread as Examples/Stereo/stereo_kitti.cc times it.
+// imgsL/imgsR: nframes tightly packed w*h images.  Each thread owns its extractors and walks
+// frames t, t+T, ...  `reps` passes over the set.  Returns wall seconds; totals via out params.
+double orbo_bench_stereo(const uint8_t* imgsL, const uint8_t* imgsR, int nframes, int w, int h,
+                         int nf, float sf, int nl, int ini, int mn, float bf, float fx, int threads,
+                         int reps, long long* totalKeys, long long* totalMatches) {
+  std::vector<long long> keys(threads, 0), matches(threads, 0);
+  auto t0 = std::chrono::steady_clock::now();
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      Extractor L(nf, sf, nl, ini, mn), R(nf, sf, nl, ini, mn);
+      std::vector<KeyPt> kl, kr; std::vector<uint8_t> dl, dr; std::vector<float> ur, dp;
+      for (int r = 0; r < reps; ++r)
+        for (int f = t; f < nframes; f += threads) {
+          int a = L.extract(imgsL + (size_t)f * w * h, w, h, w, kl, dl);
+          if (imgsR) {
+            int b = R.extract(imgsR + (size_t)f * w * h, w, h, w, kr, dr);
+            if (a > 0 && b > 0) {
+              ur.resize(a); dp.resize(a);
+              matches[t] += stereo_match(L, R, kl, dl.data(), kr, dr.data(), bf, fx, ur.data(), dp.data());
+            }
+            keys[t] += (b > 0 ? b : 0);
+          }
+          keys[t] += (a > 0 ? a : 0);
+        }
+    });
+  for (auto& th : pool) th.join();
+  double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  long long k = 0, m = 0;
+  for (int t = 0; t < threads; ++t) { k += keys[t]; m += matches[t]; }
+  if (totalKeys) *totalKeys = k;
+  if (totalMatches) *totalMatches = m;
+  return s;
+}
+int orbo_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
+
+}  // extern "C"

@@ -1,0 +1,588 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see cv_prims.hpp for the rule on who may use oracle/).
+//
+// CPU restatement of the reference's per-frame feature front end:
+//   Extractor            <- ORB_SLAM2::ORBextractor            src/ORBextractor.cc:410-470, 1043-1132
+//   Extractor::pyramid   <- ORBextractor::ComputePyramid       src/ORBextractor.cc:1107-1132
+//   Extractor::detect    <- ComputeKeyPointsOctTree            src/ORBextractor.cc:765-853
+//   distribute_quadtree  <- DistributeOctTree / DivideNode     src/ORBextractor.cc:539-763, 481-537
+//   patch_angle          <- IC_Angle                           src/ORBextractor.cc:77-104
+//   steered_brief        <- computeOrbDescriptor               src/ORBextractor.cc:108-147
+//   stereo_match         <- Frame::ComputeStereoMatches        src/Frame.cc:466-640
+//   search_for_init      <- ORBmatcher::SearchForInitialization src/ORBmatcher.cc:405-520
+//                           (+ Frame::GetFeaturesInArea / PosInGrid, src/Frame.cc:327-392)
+//   knn_ratio_bucket     <- ORBmatcher::SearchByBoW(KF,KF), one bucket, src/ORBmatcher.cc:522-655
+//   three_maxima         <- ORBmatcher::ComputeThreeMaxima     src/ORBmatcher.cc:1601-1642
+//   hamming256           <- ORBmatcher::DescriptorDistance     src/ORBmatcher.cc:1647-1663
+//
+// Deliberate normalisations (DESIGN.md "hazards"):
+//   H1 quad-tree ties in the careful phase are broken by node creation order (the reference
+//      sorts on heap addresses, src/ORBextractor.cc:684) = the reference under a bump allocator.
+//   H2 sinf/cosf are the restated glibc 2.39 routines (cv_prims.hpp), proven equal to the host's.
+//   H3 compiled with -ffp-contract=off.
+//   H4 Frame::mb is read before it is set (src/Frame.cc:90 vs :114); defined as mb = bf/fx.
+//   H7 degenerate geometry (a level narrower than 62 px, portrait levels with round(W/H)==0, an
+//      empty stereo match list) returns an error / leaves outputs untouched instead of UB.
+#pragma once
+#include <algorithm>
+#include <climits>
+#include <cstdint>
+#include <list>
+#include <utility>
+#include <vector>
+
+#include "cv_prims.hpp"
+
+namespace orbo {
+
+constexpr int kPatch = 31, kHalfPatch = 15, kEdge = 19;
+
+struct KeyPt {  // same 28-byte layout as cv::KeyPoint
+  float x, y, size, angle, response;
+  int octave, class_id;
+};
+
+struct Plane {  // one bordered pyramid level; roi() is what mvImagePyramid[l] points at
+  int w = 0, h = 0, pitch = 0;
+  std::vector<uint8_t> buf;
+  uint8_t* roi() { return buf.data() + (size_t)kEdge * pitch + kEdge; }
+  const uint8_t* roi() const { return buf.data() + (size_t)kEdge * pitch + kEdge; }
+};
+
+static const int8_t kBrief[1024] = {
+#include "brief_pattern.inc"
+};
+
+static inline int hamming256(const uint8_t* a, const uint8_t* b) {
+  int d = 0;
+  for (int i = 0; i < 8; ++i) {
+    uint32_t u, v;
+    std::memcpy(&u, a + 4 * i, 4);
+    std::memcpy(&v, b + 4 * i, 4);
+    d += __builtin_popcount(u ^ v);
+  }
+  return d;
+}
+
+// ----------------------------------------------------------------------------------------
+struct QNode {
+  int x0, y0, x1, y1;  // UL = (x0,y0), BR = (x1,y1)
+  std::vector<KeyPt> keys;
+  bool leaf = false;
+  int seq = 0;  // creation counter: the H1 stand-in for the heap address
+  std::list<QNode>::iterator self;
+};
+
+inline void split4(const QNode& n, QNode c[4]) {
+  const int hx = (int)std::ceil((float)(n.x1 - n.x0) / 2);
+  const int hy = (int)std::ceil((float)(n.y1 - n.y0) / 2);
+  const int mx = n.x0 + hx, my = n.y0 + hy;
+  c[0].x0 = n.x0; c[0].y0 = n.y0; c[0].x1 = mx;   c[0].y1 = my;
+  c[1].x0 = mx;   c[1].y0 = n.y0; c[1].x1 = n.x1; c[1].y1 = my;
+  c[2].x0 = n.x0; c[2].y0 = my;   c[2].x1 = mx;   c[2].y1 = n.y1;
+  c[3].x0 = mx;   c[3].y0 = my;   c[3].x1 = n.x1; c[3].y1 = n.y1;
+  for (const KeyPt& k : n.keys) {
+    int q = (k.x < (float)mx) ? ((k.y < (float)my) ? 0 : 2) : ((k.y < (float)my) ? 1 : 3);
+    c[q].keys.push_back(k);
+  }
+  for (int q = 0; q < 4; ++q) c[q].leaf = c[q].keys.size() == 1;
+}
+
+// Returns false on degenerate geometry (H7).
+inline bool distribute_quadtree(const std::vector<KeyPt>& cand, int minX, int maxX, int minY,
+                                int maxY, int N, std::vector<KeyPt>& out) {
+  out.clear();
+  const int nIni = (int)std::round((float)(maxX - minX) / (maxY - minY));
+  if (nIni < 1) return false;
+  const float hX = (float)(maxX - minX) / nIni;
+  std::list<QNode> L;
+  std::vector<QNode*> roots(nIni);
+  int seq = 0;
+  for (int i = 0; i < nIni; ++i) {
+    QNode r;
+    r.x0 = (int)(hX * (float)i);
+    r.x1 = (int)(hX * (float)(i + 1));
+    r.y0 = 0;
+    r.y1 = maxY - minY;
+    r.seq = seq++;
+    L.push_back(r);
+    roots[i] = &L.back();
+  }
+  for (const KeyPt& k : cand) {
+    int r = (int)(k.x / hX);
+    if (r < 0 || r >= nIni) return false;
+    roots[r]->keys.push_back(k);
+  }
+  for (auto it = L.begin(); it != L.end();) {
+    if (it->keys.empty()) it = L.erase(it);
+    else { it->leaf = it->keys.size() == 1; ++it; }
+  }
+  typedef std::pair<int, int> SizeSeq;           // (key count, creation seq)
+  std::vector<std::pair<SizeSeq, QNode*>> open;  // children that can still be split
+  auto push_children = [&](QNode c[4]) {
+    for (int q = 0; q < 4; ++q) {
+      if (c[q].keys.empty()) continue;
+      c[q].seq = seq++;
+      L.push_front(c[q]);
+      L.front().self = L.begin();
+      if (c[q].keys.size() > 1) open.push_back({{(int)c[q].keys.size(), c[q].seq}, &L.front()});
+    }
+  };
+  bool done = false;
+  while (!done) {
+    const int before = (int)L.size();
+    open.clear();
+    int expandable = 0;
+    for (auto it = L.begin(); it != L.end();) {
+      if (it->leaf) { ++it; continue; }
+      QNode c[4];
+      split4(*it, c);
+      size_t o0 = open.size();
+      push_children(c);
+      expandable += (int)(open.size() - o0);
+      it = L.erase(it);
+    }
+    if ((int)L.size() >= N || (int)L.size() == before) {
+      done = true;
+    } else if ((int)L.size() + 3 * expandable > N) {
+      while (!done) {
+        const int before2 = (int)L.size();
+        auto todo = open;
+        open.clear();
+        std::sort(todo.begin(), todo.end(),
+                  [](const std::pair<SizeSeq, QNode*>& a, const std::pair<SizeSeq, QNode*>& b) {
+                    return a.first < b.first;
+                  });
+        for (int j = (int)todo.size() - 1; j >= 0; --j) {
+          QNode c[4];
+          split4(*todo[j].second, c);
+          push_children(c);
+          L.erase(todo[j].second->self);
+          if ((int)L.size() >= N) break;
+        }
+        if ((int)L.size() >= N || (int)L.size() == before2) done = true;
+      }
+    }
+  }
+  out.reserve(L.size());
+  for (const QNode& n : L) {
+    const KeyPt* best = &n.keys[0];
+    for (size_t k = 1; k < n.keys.size(); ++k)
+      if (n.keys[k].response > best->response) best = &n.keys[k];
+    out.push_back(*best);
+  }
+  return true;
+}
+
+// ----------------------------------------------------------------------------------------
+static inline float patch_angle(const uint8_t* roi, int pitch, float px, float py, const int* umax) {
+  const uint8_t* c = roi + (size_t)cv_round(py) * pitch + cv_round(px);
+  int m01 = 0, m10 = 0;
+  for (int u = -kHalfPatch; u <= kHalfPatch; ++u) m10 += u * c[u];
+  for (int v = 1; v <= kHalfPatch; ++v) {
+    int vs = 0, d = umax[v];
+    for (int u = -d; u <= d; ++u) {
+      int a = c[u + v * pitch], b = c[u - v * pitch];
+      vs += a - b;
+      m10 += u * (a + b);
+    }
+    m01 += v * vs;
+  }
+  return fast_atan2_deg((float)m01, (float)m10);
+}
+
+static inline void steered_brief(const uint8_t* img, int pitch, const KeyPt& kp, uint8_t* desc) {
+  const float deg2rad = (float)(3.1415926535897932384626433832795 / 180.f);
+  float ang = kp.angle * deg2rad;
+  float a = libm_cosf(ang), b = libm_sinf(ang);
+  const uint8_t* c = img + (size_t)cv_round(kp.y) * pitch + cv_round(kp.x);
+  for (int i = 0; i < 32; ++i) {
+    int byte = 0;
+    for (int j = 0; j < 8; ++j) {
+      const int8_t* t = kBrief + (i * 8 + j) * 4;
+      float x0 = t[0], y0 = t[1], x1 = t[2], y1 = t[3];
+      int v0 = c[cv_round(x0 * b + y0 * a) * pitch + cv_round(x0 * a - y0 * b)];
+      int v1 = c[cv_round(x1 * b + y1 * a) * pitch + cv_round(x1 * a - y1 * b)];
+      byte |= (v0 < v1) << j;
+    }
+    desc[i] = (uint8_t)byte;
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+class Extractor {
+ public:
+  int nfeatures, nlevels, iniTh, minTh;
+  double scaleFactor;
+  std::vector<float> scale, invScale, sigma2, invSigma2;
+  std::vector<int> quota;
+  int umax[kHalfPatch + 1];
+  std::vector<Plane> pyr;
+  std::vector<std::vector<KeyPt>> candidates;  // per level, before the quad-tree (window coords)
+  std::vector<std::vector<KeyPt>> levelKeys;   // per level, after the quad-tree (level coords)
+
+  Extractor(int nf, float sf, int nl, int ini, int mn)
+      : nfeatures(nf), nlevels(nl), iniTh(ini), minTh(mn), scaleFactor(sf) {
+    scale.assign(nl, 1.f); sigma2.assign(nl, 1.f); invScale.resize(nl); invSigma2.resize(nl);
+    for (int i = 1; i < nl; ++i) {
+      scale[i] = (float)(scale[i - 1] * scaleFactor);
+      sigma2[i] = scale[i] * scale[i];
+    }
+    for (int i = 0; i < nl; ++i) { invScale[i] = 1.0f / scale[i]; invSigma2[i] = 1.0f / sigma2[i]; }
+    pyr.resize(nl);
+    quota.resize(nl);
+    float factor = (float)(1.0f / scaleFactor);
+    float want = nf * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+      quota[l] = cv_round(want);
+      sum += quota[l];
+      want *= factor;
+    }
+    quota[nl - 1] = std::max(nf - sum, 0);
+    // disc half-widths for the orientation moments
+    int vmax = (int)std::floor(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+    int vmin = (int)std::ceil(kHalfPatch * std::sqrt(2.f) / 2);
+    const double r2 = kHalfPatch * kHalfPatch;
+    for (int v = 0; v <= vmax; ++v) umax[v] = cv_round(std::sqrt(r2 - v * v));
+    for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+      while (umax[v0] == umax[v0 + 1]) ++v0;
+      umax[v] = v0;
+      ++v0;
+    }
+  }
+
+  // 0 ok, <0 degenerate geometry
+  int pyramid(const uint8_t* img, int w, int h, int pitch) {
+    for (int l = 0; l < nlevels; ++l) {
+      Plane& p = pyr[l];
+      p.w = cv_round((float)w * invScale[l]);
+      p.h = cv_round((float)h * invScale[l]);
+      if (p.w < 2 * (kEdge - 3) + 30 || p.h < 2 * (kEdge - 3) + 30) return -1;
+      p.pitch = p.w + 2 * kEdge;
+      p.buf.assign((size_t)p.pitch * (p.h + 2 * kEdge), 0);
+      if (l == 0) {
+        border_reflect101(img, w, h, pitch, p.buf.data(), p.pitch, kEdge);
+      } else {
+        const Plane& q = pyr[l - 1];
+        resize_linear_u8(q.roi(), q.w, q.h, q.pitch, p.roi(), p.w, p.h, p.pitch);
+        std::vector<uint8_t> tmp((size_t)p.w * p.h);
+        for (int y = 0; y < p.h; ++y) std::memcpy(&tmp[(size_t)y * p.w], p.roi() + (size_t)y * p.pitch, p.w);
+        border_reflect101(tmp.data(), p.w, p.h, p.w, p.buf.data(), p.pitch, kEdge);
+      }
+    }
+    return 0;
+  }
+
+  int detect() {
+    candidates.assign(nlevels, {});
+    levelKeys.assign(nlevels, {});
+    const float W = 30;
+    std::vector<FastPt> cell;
+    for (int l = 0; l < nlevels; ++l) {
+      const Plane& p = pyr[l];
+      const int minBX = kEdge - 3, minBY = minBX, maxBX = p.w - kEdge + 3, maxBY = p.h - kEdge + 3;
+      const float width = (float)(maxBX - minBX), height = (float)(maxBY - minBY);
+      const int nCols = (int)(width / W), nRows = (int)(height / W);
+      if (nCols < 1 || nRows < 1) return -1;
+      const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
+      std::vector<KeyPt>& cand = candidates[l];
+      for (int i = 0; i < nRows; ++i) {
+        const float iniY = (float)(minBY + i * hCell);
+        float maxY = iniY + hCell + 6;
+        if (iniY >= maxBY - 3) continue;
+        if (maxY > maxBY) maxY = (float)maxBY;
+        for (int j = 0; j < nCols; ++j) {
+          const float iniX = (float)(minBX + j * wCell);
+          float maxX = iniX + wCell + 6;
+          if (iniX >= maxBX - 6) continue;
+          if (maxX > maxBX) maxX = (float)maxBX;
+          const int x0 = (int)iniX, y0 = (int)iniY, ww = (int)maxX - x0, hh = (int)maxY - y0;
+          const uint8_t* win = p.roi() + (size_t)y0 * p.pitch + x0;
+          fast9_16(win, ww, hh, p.pitch, iniTh, cell);
+          if (cell.empty()) fast9_16(win, ww, hh, p.pitch, minTh, cell);
+          for (const FastPt& f : cell) {
+            KeyPt k;
+            k.x = (float)f.x + j * wCell;
+            k.y = (float)f.y + i * hCell;
+            k.size = 7.f; k.angle = -1.f; k.response = (float)f.score; k.octave = 0; k.class_id = -1;
+            cand.push_back(k);
+          }
+        }
+      }
+      if (!distribute_quadtree(cand, minBX, maxBX, minBY, maxBY, quota[l], levelKeys[l])) return -2;
+      const int patch = (int)(kPatch * scale[l]);
+      for (KeyPt& k : levelKeys[l]) {
+        k.x += minBX; k.y += minBY; k.octave = l; k.size = (float)patch;
+      }
+    }
+    for (int l = 0; l < nlevels; ++l)
+      for (KeyPt& k : levelKeys[l]) k.angle = patch_angle(pyr[l].roi(), pyr[l].pitch, k.x, k.y, umax);
+    return 0;
+  }
+
+  // Full operator(): returns keypoint count (>=0) or a negative error.
+  int extract(const uint8_t* img, int w, int h, int pitch, std::vector<KeyPt>& kps,
+              std::vector<uint8_t>& desc) {
+    kps.clear(); desc.clear();
+    if (!img || w <= 0 || h <= 0) return 0;  // empty image: silent return (src/ORBextractor.cc:1046)
+    int rc = pyramid(img, w, h, pitch);
+    if (rc < 0) return rc;
+    rc = detect();
+    if (rc < 0) return rc * 10;
+    size_t total = 0;
+    for (auto& v : levelKeys) total += v.size();
+    kps.reserve(total); desc.resize(total * 32);
+    size_t off = 0;
+    std::vector<uint8_t> blurred;
+    for (int l = 0; l < nlevels; ++l) {
+      std::vector<KeyPt>& ks = levelKeys[l];
+      if (ks.empty()) continue;
+      const Plane& p = pyr[l];
+      blurred.resize((size_t)p.w * p.h);
+      gauss7_sigma2(p.roi(), p.w, p.h, p.pitch, blurred.data(), p.w);
+      for (size_t i = 0; i < ks.size(); ++i) steered_brief(blurred.data(), p.w, ks[i], &desc[(off + i) * 32]);
+      off += ks.size();
+      for (const KeyPt& k0 : ks) {
+        KeyPt k = k0;
+        if (l != 0) { k.x *= scale[l]; k.y *= scale[l]; }
+        kps.push_back(k);
+      }
+    }
+    return (int)total;
+  }
+};
+
+// ----------------------------------------------------------------------------------------
+// Frame::ComputeStereoMatches.  EL/ER hold the left/right pyramids of the preceding extract().
+// uRight/depth get -1 where there is no match.  Returns the number of surviving matches.
+inline int stereo_match(const Extractor& EL, const Extractor& ER, const std::vector<KeyPt>& kL,
+                        const uint8_t* dL, const std::vector<KeyPt>& kR, const uint8_t* dR, float bf,
+                        float fx, float* uRight, float* depth, int* sadOut = nullptr) {
+  const int N = (int)kL.size();
+  for (int i = 0; i < N; ++i) { uRight[i] = -1.f; depth[i] = -1.f; if (sadOut) sadOut[i] = -1; }
+  const int thOrb = (100 + 50) / 2;
+  const int nRows = EL.pyr[0].h;
+  std::vector<std::vector<int>> rows(nRows);
+  for (int iR = 0; iR < (int)kR.size(); ++iR) {
+    const float y = kR[iR].y, r = 2.0f * EL.scale[kR[iR].octave];
+    const int hi = (int)std::ceil(y + r), lo = (int)std::floor(y - r);
+    for (int yi = lo; yi <= hi; ++yi)
+      if (yi >= 0 && yi < nRows) rows[yi].push_back(iR);
+  }
+  const float mb = bf / fx;  // H4
+  const float minD = 0, maxD = bf / mb;
+  std::vector<std::pair<int, int>> sadIdx;
+  for (int iL = 0; iL < N; ++iL) {
+    const KeyPt& kl = kL[iL];
+    const int lvl = kl.octave;
+    const float vL = kl.y, uL = kl.x;
+    const int row = (int)vL;
+    if (row < 0 || row >= nRows) continue;
+    const std::vector<int>& cands = rows[row];
+    if (cands.empty()) continue;
+    const float minU = uL - maxD, maxU = uL - minD;
+    if (maxU < 0) continue;
+    int best = 100, bestR = 0;
+    for (int iR : cands) {
+      const KeyPt& kr = kR[iR];
+      if (kr.octave < lvl - 1 || kr.octave > lvl + 1) continue;
+      if (kr.x >= minU && kr.x <= maxU) {
+        int d = hamming256(dL + 32 * (size_t)iL, dR + 32 * (size_t)iR);
+        if (d < best) { best = d; bestR = iR; }
+      }
+    }
+    if (best >= thOrb) continue;
+    const float uR0 = kR[bestR].x, inv = EL.invScale[lvl];
+    const float su = std::round(kl.x * inv), sv = std::round(kl.y * inv), sr = std::round(uR0 * inv);
+    const int w = 5, Ls = 5;
+    const Plane& PL = EL.pyr[lvl];
+    const Plane& PR = ER.pyr[lvl];
+    const float iniu = sr + Ls - w, endu = sr + Ls + w + 1;
+    if (iniu < 0 || endu >= PR.w) continue;
+    const int cy = (int)sv, cxl = (int)su, cxr = (int)sr;
+    const uint8_t* pl = PL.roi();
+    const uint8_t* pr = PR.roi();
+    const float cl = (float)pl[(size_t)cy * PL.pitch + cxl];
+    int bestSad = INT_MAX, bestInc = 0;
+    float dist[11];
+    for (int inc = -Ls; inc <= Ls; ++inc) {
+      const float cr = (float)pr[(size_t)cy * PR.pitch + cxr + inc];
+      double acc = 0;
+      for (int dy = -w; dy <= w; ++dy)
+        for (int dx = -w; dx <= w; ++dx) {
+          float a = (float)pl[(size_t)(cy + dy) * PL.pitch + cxl + dx] - cl;
+          float b = (float)pr[(size_t)(cy + dy) * PR.pitch + cxr + inc + dx] - cr;
+          acc += std::fabs(a - b);
+        }
+      float d = (float)acc;
+      if (d < (float)bestSad) { bestSad = (int)d; bestInc = inc; }
+      dist[Ls + inc] = d;
+    }
+    if (bestInc == -Ls || bestInc == Ls) continue;
+    const float d1 = dist[Ls + bestInc - 1], d2 = dist[Ls + bestInc], d3 = dist[Ls + bestInc + 1];
+    const float delta = (d1 - d3) / (2.0f * (d1 + d3 - 2.0f * d2));
+    if (delta < -1 || delta > 1) continue;
+    float bestu = EL.scale[lvl] * ((float)sr + (float)bestInc + delta);
+    float disp = uL - bestu;
+    if (disp >= minD && disp < maxD) {
+      if (disp <= 0) { disp = 0.01; bestu = uL - 0.01; }
+      depth[iL] = bf / disp;
+      uRight[iL] = bestu;
+      if (sadOut) sadOut[iL] = bestSad;
+      sadIdx.push_back({bestSad, iL});
+    }
+  }
+  if (sadIdx.empty()) return 0;  // H7: the reference indexes an empty vector here
+  std::sort(sadIdx.begin(), sadIdx.end());
+  const float median = (float)sadIdx[sadIdx.size() / 2].first;
+  const float th = 1.5f * 1.4f * median;
+  int kept = (int)sadIdx.size();
+  for (int i = (int)sadIdx.size() - 1; i >= 0; --i) {
+    if ((float)sadIdx[i].first < th) break;
+    uRight[sadIdx[i].second] = -1;
+    depth[sadIdx[i].second] = -1;
+    --kept;
+  }
+  return kept;
+}
+
+// ----------------------------------------------------------------------------------------
+inline void three_maxima(const std::vector<int>* histo, int L, int& i1, int& i2, int& i3) {
+  int m1 = 0, m2 = 0, m3 = 0;
+  for (int i = 0; i < L; ++i) {
+    const int s = (int)histo[i].size();
+    if (s > m1) { m3 = m2; m2 = m1; m1 = s; i3 = i2; i2 = i1; i1 = i; }
+    else if (s > m2) { m3 = m2; m2 = s; i3 = i2; i2 = i; }
+    else if (s > m3) { m3 = s; i3 = i; }
+  }
+  if (m2 < 0.1f * (float)m1) { i2 = -1; i3 = -1; }
+  else if (m3 < 0.1f * (float)m1) { i3 = -1; }
+}
+
+constexpr int kGridCols = 64, kGridRows = 48, kHisto = 30;
+
+// The 64x48 bucket grid of a frame (Frame::AssignFeaturesToGrid, src/Frame.cc:230-245) for an
+// undistorted camera (k1 == 0): bounds are [0,cols) x [0,rows).
+struct FrameGrid {
+  float invW, invH;
+  std::vector<int> cell[kGridCols][kGridRows];
+  FrameGrid(const KeyPt* k, int n, int cols, int rows) {
+    invW = (float)kGridCols / (float)cols;
+    invH = (float)kGridRows / (float)rows;
+    for (int i = 0; i < n; ++i) {
+      int gx = (int)std::round((k[i].x - 0.f) * invW), gy = (int)std::round((k[i].y - 0.f) * invH);
+      if (gx < 0 || gx >= kGridCols || gy < 0 || gy >= kGridRows) continue;
+      cell[gx][gy].push_back(i);
+    }
+  }
+  void in_area(const KeyPt* k, float x, float y, float r, int minLevel, int maxLevel,
+               std::vector<int>& out) const {
+    out.clear();
+    const int cx0 = std::max(0, (int)std::floor((x - 0.f - r) * invW));
+    if (cx0 >= kGridCols) return;
+    const int cx1 = std::min(kGridCols - 1, (int)std::ceil((x - 0.f + r) * invW));
+    if (cx1 < 0) return;
+    const int cy0 = std::max(0, (int)std::floor((y - 0.f - r) * invH));
+    if (cy0 >= kGridRows) return;
+    const int cy1 = std::min(kGridRows - 1, (int)std::ceil((y - 0.f + r) * invH));
+    if (cy1 < 0) return;
+    const bool chk = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = cx0; ix <= cx1; ++ix)
+      for (int iy = cy0; iy <= cy1; ++iy)
+        for (int idx : cell[ix][iy]) {
+          if (chk) {
+            if (k[idx].octave < minLevel) continue;
+            if (maxLevel >= 0 && k[idx].octave > maxLevel) continue;
+          }
+          if (std::fabs(k[idx].x - x) < r && std::fabs(k[idx].y - y) < r) out.push_back(idx);
+        }
+  }
+};
+
+static inline int rot_bin(float a1, float a2) {
+  const float factor = 1.0f / kHisto;
+  float rot = a1 - a2;
+  if (rot < 0.0) rot += 360.0f;
+  int bin = (int)std::round(rot * factor);
+  if (bin == kHisto) bin = 0;
+  return bin;
+}
+
+// ORBmatcher::SearchForInitialization.  prev is vbPrevMatched (in/out, xy pairs).
+inline int search_for_init(const KeyPt* k1, const uint8_t* d1, int n1, const KeyPt* k2,
+                           const uint8_t* d2, int n2, int cols, int rows, float* prev, float ratio,
+                           int window, bool checkOri, int* m12) {
+  int nm = 0;
+  for (int i = 0; i < n1; ++i) m12[i] = -1;
+  std::vector<int> hist[kHisto];
+  std::vector<int> dist2(n2, INT_MAX), m21(n2, -1);
+  FrameGrid grid(k2, n2, cols, rows);
+  std::vector<int> cand;
+  for (int i1 = 0; i1 < n1; ++i1) {
+    if (k1[i1].octave > 0) continue;
+    grid.in_area(k2, prev[2 * i1], prev[2 * i1 + 1], (float)window, 0, 0, cand);
+    if (cand.empty()) continue;
+    int b1 = INT_MAX, b2 = INT_MAX, bi = -1;
+    for (int i2 : cand) {
+      int d = hamming256(d1 + 32 * (size_t)i1, d2 + 32 * (size_t)i2);
+      if (dist2[i2] <= d) continue;
+      if (d < b1) { b2 = b1; b1 = d; bi = i2; }
+      else if (d < b2) b2 = d;
+    }
+    if (b1 <= 50 && (float)b1 < (float)b2 * ratio) {
+      if (m21[bi] >= 0) { m12[m21[bi]] = -1; --nm; }
+      m12[i1] = bi; m21[bi] = i1; dist2[bi] = b1; ++nm;
+      if (checkOri) hist[rot_bin(k1[i1].angle, k2[bi].angle)].push_back(i1);
+    }
+  }
+  if (checkOri) {
+    int a = -1, b = -1, c = -1;
+    three_maxima(hist, kHisto, a, b, c);
+    for (int i = 0; i < kHisto; ++i) {
+      if (i == a || i == b || i == c) continue;
+      for (int idx : hist[i])
+        if (m12[idx] >= 0) { m12[idx] = -1; --nm; }
+    }
+  }
+  for (int i1 = 0; i1 < n1; ++i1)
+    if (m12[i1] >= 0) { prev[2 * i1] = k2[m12[i1]].x; prev[2 * i1 + 1] = k2[m12[i1]].y; }
+  return nm;
+}
+
+// ORBmatcher::SearchByBoW(KF,KF) with every feature valid and a single vocabulary bucket holding
+// all features of each side in index order (BASELINE config 5).  strict: best < th (KF,KF form,
+// src/ORBmatcher.cc:598) vs best <= th (KF,Frame form, :228).
+inline int knn_ratio_bucket(const uint8_t* dA, const float* angA, int nA, const uint8_t* dB,
+                            const float* angB, int nB, int th, float ratio, bool checkOri,
+                            bool strict, int* m12) {
+  for (int i = 0; i < nA; ++i) m12[i] = -1;
+  std::vector<char> used(nB, 0);
+  std::vector<int> hist[kHisto];
+  int nm = 0;
+  for (int i = 0; i < nA; ++i) {
+    int b1 = 256, b2 = 256, bi = -1;
+    for (int j = 0; j < nB; ++j) {
+      if (used[j]) continue;
+      int d = hamming256(dA + 32 * (size_t)i, dB + 32 * (size_t)j);
+      if (d < b1) { b2 = b1; b1 = d; bi = j; }
+      else if (d < b2) b2 = d;
+    }
+    bool pass = strict ? (b1 < th) : (b1 <= th);
+    if (pass && (float)b1 < ratio * (float)b2) {
+      m12[i] = bi; used[bi] = 1;
+      if (checkOri) hist[rot_bin(angA[i], angB[bi])].push_back(i);
+      ++nm;
+    }
+  }
+  if (checkOri) {
+    int a = -1, b = -1, c = -1;
+    three_maxima(hist, kHisto, a, b, c);
+    for (int i = 0; i < kHisto; ++i) {
+      if (i == a || i == b || i == c) continue;
+      for (int idx : hist[i]) { m12[idx] = -1; --nm; }
+    }
+  }
+  return nm;
+}
+
+}  // namespace orbo

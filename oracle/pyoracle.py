@@ -1,0 +1,221 @@
+"""ctypes binding of oracle/liborb_oracle.so — TEST INFRASTRUCTURE ONLY.
+
+Imported by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs, never by the
+orb_slam2_b200 package."""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", _HERE], check=True)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "liborb_oracle.so")
+        if not os.path.exists(path):
+            build()
+        _LIB = C.CDLL(path)
+        _LIB.orbo_create.restype = C.c_void_p
+        _LIB.orbo_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        _LIB.orbo_destroy.argtypes = [C.c_void_p]
+        _LIB.orbo_atan2.restype = C.c_float
+        _LIB.orbo_atan2.argtypes = [C.c_float, C.c_float]
+        _LIB.orbo_bench_stereo.restype = C.c_double
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Extractor:
+    def __init__(self, nfeatures, scale=1.2, nlevels=8, ini=20, mn=7):
+        self.nlevels, self.nfeatures = nlevels, nfeatures
+        self.args = (nfeatures, scale, nlevels, ini, mn)
+        self.h = C.c_void_p(lib().orbo_create(nfeatures, C.c_float(scale), nlevels, ini, mn))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orbo_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        n = self.nlevels
+        f = [np.zeros(n, np.float32) for _ in range(4)]
+        q = np.zeros(n, np.int32); u = np.zeros(16, np.int32)
+        lib().orbo_tables(self.h, *[_p(a) for a in f], _p(q), _p(u))
+        return dict(scale=f[0], inv=f[1], sigma2=f[2], invsigma2=f[3], quota=q, umax=u)
+
+    def extract(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        cap = self.nfeatures + 3 * self.nlevels + 64
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+        n = lib().orbo_extract(self.h, _p(img), img.shape[1], img.shape[0], img.strides[0], _p(kps), _p(desc), cap)
+        if n < 0:
+            raise RuntimeError(f"oracle extract failed: {n}")
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l):
+        w, h = C.c_int(), C.c_int()
+        lib().orbo_level_size(self.h, l, C.byref(w), C.byref(h))
+        buf = np.zeros((h.value + 38, w.value + 38), np.uint8)
+        lib().orbo_level_copy(self.h, l, _p(buf))
+        return buf
+
+    def candidates(self, l, cap=200000):
+        out = np.zeros(cap, KP_DTYPE)
+        n = lib().orbo_level_candidates(self.h, l, _p(out), cap)
+        return out[:n].copy()
+
+    def level_keys(self, l, cap=20000):
+        out = np.zeros(cap, KP_DTYPE)
+        n = lib().orbo_level_keys(self.h, l, _p(out), cap)
+        return out[:n].copy()
+
+
+def stereo(eL, eR, kL, dL, kR, dR, bf, fx):
+    n = len(kL)
+    ur = np.zeros(n, np.float32); dp = np.zeros(n, np.float32); sad = np.zeros(n, np.int32)
+    kL = np.ascontiguousarray(kL); kR = np.ascontiguousarray(kR)
+    dL = np.ascontiguousarray(dL); dR = np.ascontiguousarray(dR)
+    m = lib().orbo_stereo(eL.h, eR.h, _p(kL), _p(dL), n, _p(kR), _p(dR), len(kR), C.c_float(bf), C.c_float(fx),
+                          _p(ur), _p(dp), _p(sad))
+    return ur, dp, sad, m
+
+
+def search_init(k1, d1, k2, d2, cols, rows, prev, ratio=0.9, window=100, check_ori=True):
+    k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+    d1 = np.ascontiguousarray(d1); d2 = np.ascontiguousarray(d2)
+    prev = np.ascontiguousarray(prev, np.float32).copy()
+    m12 = np.zeros(len(k1), np.int32)
+    n = lib().orbo_search_init(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), cols, rows, _p(prev),
+                               C.c_float(ratio), window, int(check_ori), _p(m12))
+    return m12, n, prev
+
+
+def knn_ratio(dA, angA, dB, angB, th=50, ratio=0.75, check_ori=True, strict=True):
+    dA = np.ascontiguousarray(dA); dB = np.ascontiguousarray(dB)
+    angA = np.ascontiguousarray(angA, np.float32); angB = np.ascontiguousarray(angB, np.float32)
+    m12 = np.zeros(len(dA), np.int32)
+    n = lib().orbo_knn_ratio(_p(dA), _p(angA), len(dA), _p(dB), _p(angB), len(dB), th, C.c_float(ratio),
+                             int(check_ori), int(strict), _p(m12))
+    return m12, n
+
+
+def resize(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orbo_resize(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dw, dh, dw)
+    return dst
+
+
+def border(src, b=19):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((src.shape[0] + 2 * b, src.shape[1] + 2 * b), np.uint8)
+    lib().orbo_border(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dst.shape[1], b)
+    return dst
+
+
+def blur(src):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros_like(src)
+    lib().orbo_blur(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dst.strides[0])
+    return dst
+
+
+def fast(src, t, cap=100000):
+    src = np.ascontiguousarray(src, np.uint8)
+    out = np.zeros((cap, 3), np.int32)
+    n = lib().orbo_fast(_p(src), src.shape[1], src.shape[0], src.strides[0], t, _p(out), cap)
+    return out[:n].copy()
+
+
+def atan2_array(y, x):
+    y = np.ascontiguousarray(y, np.float32); x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros_like(y)
+    lib().orbo_atan2_array(_p(y), _p(x), _p(out), len(y))
+    return out
+
+
+def sincos_array(a, libm=False):
+    a = np.ascontiguousarray(a, np.float32)
+    s = np.zeros_like(a); c = np.zeros_like(a)
+    (lib().orbo_libm_sincos_array if libm else lib().orbo_sincos_array)(_p(a), _p(s), _p(c), len(a))
+    return s, c
+
+
+def quadtree(cand, minX, maxX, minY, maxY, N, cap=20000):
+    cand = np.ascontiguousarray(cand)
+    out = np.zeros(cap, KP_DTYPE)
+    n = lib().orbo_quadtree(_p(cand), len(cand), minX, maxX, minY, maxY, N, _p(out), cap)
+    if n < 0:
+        raise RuntimeError("degenerate quadtree geometry")
+    return out[:n].copy()
+
+
+def hamming256(a, b):
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    return lib().orbo_hamming256(_p(a), _p(b))
+
+
+def bench_stereo(imgsL, imgsR, params, bf, fx, threads, reps=1):
+    """Times extraction (+ stereo matching when imgsR is given) on the host; returns
+    (seconds, total keypoints, total stereo matches)."""
+    imgsL = np.ascontiguousarray(imgsL, np.uint8)
+    n, h, w = imgsL.shape
+    if imgsR is not None:
+        imgsR = np.ascontiguousarray(imgsR, np.uint8)
+    k = C.c_longlong(); m = C.c_longlong()
+    nf, sf, nl, ini, mn = params
+    s = lib().orbo_bench_stereo(_p(imgsL), _p(imgsR), n, w, h, nf, C.c_float(sf), nl, ini, mn, C.c_float(bf),
+                                C.c_float(fx), threads, reps, C.byref(k), C.byref(m))
+    return s, k.value, m.value
+
+
+def hardware_threads():
+    return lib().orbo_hardware_threads()
+
+
+# --- oracle/_ref: the reference's own ORBextractor.cc (built by `make -C oracle ref`) -----------
+REF_BIN = os.path.join(_HERE, "_ref", "orbref")
+
+
+def ref_available():
+    return os.path.exists(REF_BIN)
+
+
+def ref_extract(imgs, nfeatures, scale=1.2, nlevels=8, ini=20, mn=7, reps=1, use_malloc=False):
+    """Runs the reference's ORBextractor::operator() (separate process) on a stack of equally
+    sized images; returns ([(kps, desc), ...], seconds inside operator())."""
+    import tempfile
+    imgs = np.ascontiguousarray(imgs, np.uint8)
+    if imgs.ndim == 2:
+        imgs = imgs[None]
+    n, h, w = imgs.shape
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        with open(fin, "wb") as f:
+            f.write(np.array([w, h, n], np.int32).tobytes())
+            f.write(imgs.tobytes())
+        cmd = [REF_BIN, "extract", fin, fout, str(nfeatures), repr(float(scale)), str(nlevels), str(ini), str(mn),
+               str(reps)] + (["malloc"] if use_malloc else [])
+        res = subprocess.run(cmd, check=True, capture_output=True, text=True)
+        raw = open(fout, "rb").read()
+    out, off = [], 0
+    for _ in range(n):
+        cnt = int(np.frombuffer(raw, np.int32, 1, off)[0]); off += 4
+        kps = np.frombuffer(raw, KP_DTYPE, cnt, off).copy(); off += 28 * cnt
+        desc = np.frombuffer(raw, np.uint8, 32 * cnt, off).reshape(cnt, 32).copy(); off += 32 * cnt
+        out.append((kps, desc))
+    return out, float(res.stdout.strip().splitlines()[-1])

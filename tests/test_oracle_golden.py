@@ -1,0 +1,116 @@
+"""Oracle vs (a) golden vectors produced by the reference's own ORBextractor.cc
+(tests/golden/ref_extract.json, made by tools/gen_golden.py from oracle/_ref/orbref), (b) the
+oracle/_ref binary itself when it travelled with the snapshot, and (c) known-answer tests for
+the constants SURVEY.md §8c lists."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from orb_slam2_b200 import synth
+
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "ref_extract.json")))
+
+
+@pytest.mark.parametrize("case", GOLD["cases"], ids=lambda c: f"{c['name']}-{c['frame']}")
+def test_oracle_matches_reference_golden(oracle, case):
+    img = synth.mono_frame(case["frame"], case["w"], case["h"])
+    assert hashlib.sha256(img.tobytes()).hexdigest() == case["img_sha256"], "synthetic generator drifted"
+    k, d = oracle.Extractor(case["nfeatures"]).extract(img)
+    assert len(k) == case["count"]
+    assert [int((k["octave"] == l).sum()) for l in range(8)] == case["per_level"]
+    assert hashlib.sha256(k.tobytes()).hexdigest() == case["kps_sha256"]
+    assert hashlib.sha256(d.tobytes()).hexdigest() == case["desc_sha256"]
+    assert d[0].tolist() == case["first_desc"]
+
+
+def test_oracle_matches_reference_binary(oracle):
+    if not oracle.ref_available():
+        pytest.skip("oracle/_ref/orbref not built (needs /root/reference: make -C oracle ref)")
+    for w, h, nf in [(1241, 376, 2000), (640, 480, 1000)]:
+        imgs = np.stack([synth.synth_image(900 + i, w, h) for i in range(2)])
+        ref, _ = oracle.ref_extract(imgs, nf)
+        E = oracle.Extractor(nf)
+        for i in range(2):
+            k, d = E.extract(imgs[i])
+            assert k.tobytes() == ref[i][0].tobytes()
+            assert np.array_equal(d, ref[i][1])
+
+
+def test_constants_kat(oracle):
+    t = oracle.Extractor(2000).tables()
+    assert t["umax"].tolist() == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+    assert t["quota"].tolist() == [434, 362, 302, 251, 209, 175, 145, 122]
+    assert oracle.Extractor(1200).tables()["quota"].tolist() == [261, 217, 181, 151, 126, 105, 87, 72]
+    assert oracle.Extractor(1000).tables()["quota"].tolist() == [217, 181, 151, 126, 105, 87, 73, 60]
+    assert [int(31 * s) for s in t["scale"]] == [31, 37, 44, 53, 64, 77, 92, 111]
+    assert t["scale"][1] == np.float32(1.2) and t["inv"][0] == 1.0
+
+
+def test_keypoint_fields(oracle):
+    k, d = oracle.Extractor(1000).extract(synth.mono_frame(3, 640, 480))
+    sizes = {0: 31, 1: 37, 2: 44, 3: 53, 4: 64, 5: 77, 6: 92, 7: 111}
+    assert all(k["size"][i] == sizes[int(k["octave"][i])] for i in range(len(k)))
+    assert (k["class_id"] == -1).all() and (k["angle"] >= 0).all() and (k["angle"] < 360).all()
+    assert np.all(np.diff(k["octave"]) >= 0)                      # level-major output
+    assert 1000 <= len(k) <= 1000 + 3 * 8 and d.shape == (len(k), 32)
+
+
+def test_hamming_kat(oracle):
+    z = np.zeros(32, np.uint8); o = np.full(32, 255, np.uint8)
+    assert oracle.hamming256(z, z) == 0 and oracle.hamming256(z, o) == 256
+    one = z.copy(); one[17] = 0x10
+    assert oracle.hamming256(z, one) == 1 and oracle.hamming256(o, one) == 255
+    rng = np.random.default_rng(0)
+    a, b = rng.integers(0, 256, 32, dtype=np.uint8), rng.integers(0, 256, 32, dtype=np.uint8)
+    assert oracle.hamming256(a, b) == int(np.unpackbits(a ^ b).sum())
+
+
+
+
+def test_quadtree_tie_rule_h1(oracle):
+    """Two equally sized open nodes, room for only one more split: the node created LAST is the
+    one split (reference under a bump allocator: sort by (size, address), walk from the back)."""
+    KP = oracle.KP_DTYPE
+    pts = [(10, 10, 5), (30, 30, 6),        # child n1 of the root: 2 keys
+           (90, 10, 7), (110, 30, 8),       # child n2: 2 keys
+           (10, 90, 9)]                     # child n3: singleton
+    cand = np.zeros(len(pts), KP)
+    for i, (x, y, r) in enumerate(pts):
+        cand[i]["x"], cand[i]["y"], cand[i]["response"] = x, y, r
+    # root 128x128 -> 3 children (2 open, sizes equal).  N=4: 3 + 3*2 > 4 -> careful phase; the
+    # first careful split already reaches 4 nodes, so exactly one of the two open nodes is split.
+    out = oracle.quadtree(cand, 0, 128, 0, 128, 4)
+    got = sorted((float(k["x"]), float(k["y"])) for k in out)
+    # n2 (created after n1) is split: both of its keys survive; n1 keeps only its best (30,30).
+    assert got == sorted([(30.0, 30.0), (90.0, 10.0), (110.0, 30.0), (10.0, 90.0)])
+    # list order: newest children first
+    assert [(float(k["x"]), float(k["y"])) for k in out] == [(110.0, 30.0), (90.0, 10.0), (10.0, 90.0), (30.0, 30.0)]
+
+
+def test_stereo_and_matchers_behave(oracle):
+    cfg = synth.KITTI
+    L, R, rowd = synth.stereo_pair(5, cfg["w"], cfg["h"])
+    EL, ER = oracle.Extractor(cfg["nfeatures"]), oracle.Extractor(cfg["nfeatures"])
+    kl, dl = EL.extract(L); kr, dr = ER.extract(R)
+    ur, dp, sad, m = oracle.stereo(EL, ER, kl, dl, kr, dr, cfg["bf"], cfg["fx"])
+    ok = ur >= 0
+    assert m == ok.sum() and m > 300
+    assert np.all(dp[ok] > 0) and np.all(dp[~ok] == -1)
+    err = np.abs((kl["x"] - ur)[ok] - rowd[kl["y"].astype(int)][ok])
+    assert np.median(err) < 1.0                                   # planted disparity recovered
+    a, b, (dx, dy) = synth.mono_pair(1, 640, 480)
+    E = oracle.Extractor(1000)
+    k1, d1 = E.extract(a); k2, d2 = E.extract(b)
+    prev = np.stack([k1["x"], k1["y"]], 1)
+    m12, n, prev2 = oracle.search_init(k1, d1, k2, d2, 640, 480, prev)
+    assert n == (m12 >= 0).sum() and n > 30
+    hit = [abs(k2["x"][j] - k1["x"][i] - dx) < 2 and abs(k2["y"][j] - k1["y"][i] - dy) < 2 for i, j in enumerate(m12) if j >= 0]
+    assert np.mean(hit) > 0.8
+    assert np.all(k1["octave"][m12 >= 0] == 0)
+    mm, nn = oracle.knn_ratio(d1, k1["angle"], d2, k2["angle"])
+    assert nn == (mm >= 0).sum() and nn > 100
+    used = mm[mm >= 0]
+    assert len(set(used.tolist())) == len(used)                   # greedy exclusion: B side unique
