@@ -1,0 +1,168 @@
+/*
+ * orbx — C ABI of the B200 (sm_100a) ORB feature front end.
+ *
+ * This is the drop-in boundary for ONE path of ORB-SLAM2: ORBextractor::operator(),
+ * Frame::ComputeStereoMatches and the ORBmatcher Hamming searches.  The reference has no FFI
+ * layer; its boundary is the C++ class surface that Frame / Tracking call, so every entry point
+ * below names the reference member it stands in for (paths relative to the reference tree).
+ * include/orbx_cxx.hpp re-creates those C++ classes on top of this ABI; INTEGRATION.md shows
+ * the binding a maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ or torch types cross this boundary
+ *   - every call returns an orbx_status; nothing throws, asserts or exits
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream)
+ *   - an extractor handle owns all device memory it needs (allocated once in create);
+ *     extract/match calls allocate nothing
+ *   - a handle is a single-stream object: calls on one handle must not overlap; distinct
+ *     handles may be used from different host threads (the reference runs its left and right
+ *     extractor on two threads, src/Frame.cc:78-81)
+ *   - there is no CPU fallback: without a CUDA device create() fails with ORBX_ERR_CUDA
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum orbx_status {
+  ORBX_OK = 0,
+  ORBX_ERR_BAD_ARG = 1,   /* null pointer, non-positive size, threshold outside [1,254], ... */
+  ORBX_ERR_GEOMETRY = 2,  /* a pyramid level would be narrower than 62 px or round(W/H) == 0 or > 16
+                             (the reference divides by zero there, src/ORBextractor.cc:543,784) */
+  ORBX_ERR_CAPACITY = 3,  /* batch larger than max_batch, image larger than max_w x max_h,
+                             or a caller buffer too small */
+  ORBX_ERR_CUDA = 4,      /* CUDA runtime error, see orbx_last_error_string() */
+  ORBX_ERR_STATE = 5      /* e.g. stereo matching before any extract on that slot */
+} orbx_status;
+
+/* ORBextractor constructor arguments, include/ORBextractor.h:51-52 / src/ORBextractor.cc:410 */
+typedef struct orbx_params {
+  int nfeatures;
+  float scale_factor;
+  int nlevels; /* 1..8 */
+  int ini_th_fast;
+  int min_th_fast;
+} orbx_params;
+
+/* Same 28-byte layout as cv::KeyPoint: pt.x, pt.y, size, angle, response, octave, class_id. */
+typedef struct orbx_keypoint {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} orbx_keypoint;
+
+typedef struct orbx_extractor orbx_extractor;
+
+/* ---- extractor life cycle -------------------------------------------------------------- */
+
+/* ORBextractor::ORBextractor (src/ORBextractor.cc:410-470).  Scale tables, per-level quotas and
+ * the orientation disc are computed on the host with the reference's float/double arithmetic.
+ * max_w/max_h bound the image size, max_batch the number of image slots held on the device
+ * (a stereo batch of F frames uses 2F slots of one handle, or F slots of two handles). */
+orbx_status orbx_extractor_create(const orbx_params* params, int max_w, int max_h, int max_batch,
+                                  int device, orbx_extractor** out);
+void orbx_extractor_destroy(orbx_extractor* ext);
+
+/* GetLevels / GetScaleFactor(s) / GetInverseScaleFactors / GetScaleSigmaSquares /
+ * GetInverseScaleSigmaSquares (include/ORBextractor.h:63-83); any pointer may be NULL.
+ * quota = mnFeaturesPerLevel (src/ORBextractor.cc:436-446). */
+orbx_status orbx_get_tables(const orbx_extractor* ext, int* nlevels, float* scale, float* inv_scale,
+                            float* sigma2, float* inv_sigma2, int* quota);
+
+/* Upper bound on keypoints one image can return (nfeatures plus up to 3 per level, because the
+ * quad-tree's last split may overshoot, src/ORBextractor.cc:730). Size caller buffers with it. */
+int orbx_max_keypoints(const orbx_extractor* ext);
+
+/* ---- extraction ------------------------------------------------------------------------ */
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors), src/ORBextractor.cc:1043-1105,
+ * for ONE host image, synchronous.  mask is ignored by the reference (include/ORBextractor.h:58)
+ * and has no parameter here.  A NULL/empty image returns ORBX_OK with *n = 0 (silent return,
+ * src/ORBextractor.cc:1046).  kps/desc are host buffers of `cap` entries (desc: cap x 32 bytes).
+ * Results stay resident in slot 0 for orbx_stereo_match / orbx_download_level. */
+orbx_status orbx_extract(orbx_extractor* ext, const uint8_t* img, int w, int h, int stride,
+                         orbx_keypoint* kps, uint8_t* desc, int cap, int* n, void* stream);
+
+/* The same path for `n` equally sized images in one go (slots first_slot .. first_slot+n-1),
+ * asynchronous on `stream`.  imgs points at image 0; image i starts image_stride bytes after
+ * image i-1, rows are `stride` bytes apart.  src_on_device: 0 = host memory (pinned for true
+ * async; copied with cudaMemcpy2DAsync), 1 = device memory (read in place). */
+orbx_status orbx_extract_batch(orbx_extractor* ext, const uint8_t* imgs, int n, int w, int h,
+                               int stride, size_t image_stride, int src_on_device, int first_slot,
+                               void* stream);
+
+/* Copies results of slots [first_slot, first_slot+n) to caller memory (host or device, per
+ * dst_on_device), asynchronous on `stream`: counts[i], kps[i*cap .. ], desc[(i*cap .. )*32].
+ * Any of kps/desc/counts may be NULL.  cap must be >= orbx_max_keypoints(). */
+orbx_status orbx_fetch_results(orbx_extractor* ext, int first_slot, int n, orbx_keypoint* kps,
+                               uint8_t* desc, int* counts, int cap, int dst_on_device, void* stream);
+
+/* ORBextractor::mvImagePyramid[level] (public member, include/ORBextractor.h:85; read by
+ * src/Frame.cc:473,563,575,580): device pointer to the level's inner ROI (w x h, rows `stride`
+ * bytes apart; the 19-px reflect-101 border lies around it). */
+orbx_status orbx_pyramid_level(const orbx_extractor* ext, int slot, int level,
+                               const uint8_t** dev_ptr, int* w, int* h, int* stride);
+/* Host copy of the bordered plane, tightly packed (w+38) x (h+38); synchronous. */
+orbx_status orbx_download_level(orbx_extractor* ext, int slot, int level, uint8_t* dst);
+
+/* Introspection for parity tests: the FAST candidates of one level in the order the reference
+ * hands them to DistributeOctTree (src/ORBextractor.cc:820-825), packed x | y<<12 | response<<24
+ * with x,y relative to the 16-px FAST border; and the post-quad-tree keypoints of one level in
+ * list order (level coordinates).  Synchronous.  Returns the count in *n (may exceed cap). */
+orbx_status orbx_debug_candidates(orbx_extractor* ext, int slot, int level, uint32_t* out, int cap, int* n);
+orbx_status orbx_debug_level_keys(orbx_extractor* ext, int slot, int level, uint32_t* out, int cap, int* n);
+
+/* ---- stereo ---------------------------------------------------------------------------- */
+
+/* Frame::ComputeStereoMatches (src/Frame.cc:466-640) for n stereo pairs whose left images were
+ * extracted into slots slotL0.. of extL and right images into slotR0.. of extR (extL may equal
+ * extR).  bf and fx are Frame::mbf and Frame::fx; the search range is maxD = bf/(bf/fx)
+ * (Frame::mb is read before it is assigned in the reference, src/Frame.cc:90 vs :114; it is
+ * defined here as bf/fx).  Outputs per pair i, at [i*cap ..): mvuRight and mvDepth (-1 = no
+ * match), n_matches[i] = surviving matches.  Asynchronous on `stream`. */
+orbx_status orbx_stereo_match_batch(orbx_extractor* extL, int slotL0, orbx_extractor* extR, int slotR0,
+                                    int n, float bf, float fx, float* u_right, float* depth,
+                                    int* n_matches, int cap, int dst_on_device, void* stream);
+
+/* ---- ORBmatcher -------------------------------------------------------------------------- */
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1647-1663), host-side helper. */
+int orbx_hamming256(const uint8_t* a, const uint8_t* b);
+
+/* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520) for n_pairs independent frame
+ * pairs.  Pair p: frame 1 has n1[p] keypoints at kps1 + p*cap (desc1 likewise), frame 2 n2[p].
+ * prev_xy (in/out) is vbPrevMatched as x,y pairs; matches12 receives vnMatches12 (-1 = none),
+ * n_matches the return value.  cols/rows are the image bounds used by the 64x48 feature grid
+ * (src/Frame.cc:230-245, undistorted camera).  All pointers host or all device per on_device. */
+orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const int* n1,
+                                   const orbx_keypoint* kps2, const uint8_t* desc2, const int* n2,
+                                   int n_pairs, int cap, int cols, int rows, float* prev_xy,
+                                   float nnratio, int window, int check_orientation,
+                                   int* matches12, int* n_matches, int on_device, void* stream);
+
+/* ORBmatcher::SearchByBoW(KeyFrame*,KeyFrame*,...) (src/ORBmatcher.cc:522-655) restricted to one
+ * vocabulary bucket holding all features of each side in index order: brute-force best/second
+ * best 256-bit Hamming, threshold (strict_lt: best < th as in the KF/KF form :598, else best <= th
+ * as in the KF/Frame form :228), ratio test, greedy exclusion of matched B features, rotation
+ * histogram.  Batched over n_pairs like orbx_search_init_batch; ang = keypoint angles. */
+orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const int* nA,
+                                 const uint8_t* descB, const float* angB, const int* nB, int n_pairs,
+                                 int cap, int th, float nnratio, int check_orientation, int strict_lt,
+                                 int* matches12, int* n_matches, int on_device, void* stream);
+
+/* ---- misc -------------------------------------------------------------------------------- */
+
+/* Message of the last failing call on the calling thread ("" if none). */
+const char* orbx_last_error_string(void);
+/* Number of kernels launched by this library in the calling process so far (for bench.py). */
+unsigned long long orbx_kernel_launch_count(void);
+const char* orbx_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */

@@ -1,0 +1,330 @@
+"""Host-side mirror of the reference's front-end classes over the orbx C ABI (include/orbx.h).
+
+The product's host language is C++ (include/orbx_cxx.hpp re-creates ORB_SLAM2::ORBextractor /
+ORBmatcher for a C++ caller); this module is the same surface for Python so that tests and
+bench.py read like calls into the reference:
+
+    ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)   include/ORBextractor.h:51
+    extractor(image, mask) -> keypoints, descriptors                      src/ORBextractor.cc:1043
+    extractor.GetScaleFactors() ... , extractor.mvImagePyramid            include/ORBextractor.h:63-85
+    ComputeStereoMatches(extL, extR, bf, fx)                              src/Frame.cc:466
+    ORBmatcher(nnratio, checkOri).SearchForInitialization / SearchByBoW   src/ORBmatcher.cc:405,522
+
+Everything here goes through liborbx.so (CUDA, sm_100a).  There is no CPU path: if the library
+is missing or no GPU is present the calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+
+OK, ERR_BAD_ARG, ERR_GEOMETRY, ERR_CAPACITY, ERR_CUDA, ERR_STATE = range(6)
+
+
+class OrbxError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"orbx status {status}: {msg}")
+        self.status = status
+
+
+class _Params(C.Structure):
+    _fields_ = [("nfeatures", C.c_int), ("scale_factor", C.c_float), ("nlevels", C.c_int),
+                ("ini_th_fast", C.c_int), ("min_th_fast", C.c_int)]
+
+
+EXPORTS = ["orbx_extractor_create", "orbx_extractor_destroy", "orbx_get_tables", "orbx_max_keypoints",
+           "orbx_extract", "orbx_extract_batch", "orbx_fetch_results", "orbx_pyramid_level",
+           "orbx_download_level", "orbx_debug_candidates", "orbx_debug_level_keys",
+           "orbx_stereo_match_batch", "orbx_hamming256", "orbx_search_init_batch", "orbx_knn_ratio_batch",
+           "orbx_last_error_string", "orbx_kernel_launch_count", "orbx_version"]
+
+
+def library_path():
+    return os.path.join(_HERE, "liborbx.so")
+
+
+def lib():
+    """Loads liborbx.so (building it in-tree with nvcc if it is not there).  Raises if it cannot."""
+    global _LIB
+    if _LIB is None:
+        path = library_path()
+        if not os.path.exists(path):
+            from . import build as _build
+            _build.build()
+        L = C.CDLL(path)
+        L.orbx_last_error_string.restype = C.c_char_p
+        L.orbx_version.restype = C.c_char_p
+        L.orbx_kernel_launch_count.restype = C.c_ulonglong
+        L.orbx_extractor_destroy.restype = None
+        L.orbx_extractor_destroy.argtypes = [C.c_void_p]
+        L.orbx_max_keypoints.argtypes = [C.c_void_p]
+        L.orbx_extract_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t,
+                                         C.c_int, C.c_int, C.c_void_p]
+        L.orbx_fetch_results.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                         C.c_int, C.c_void_p]
+        L.orbx_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                   C.c_void_p, C.c_void_p]
+        L.orbx_stereo_match_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orbx_search_init_batch.argtypes = [C.c_void_p] * 6 + [C.c_int] * 4 + [C.c_void_p, C.c_float, C.c_int, C.c_int,
+                                                                             C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_knn_ratio_batch.argtypes = [C.c_void_p] * 6 + [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
+                                                              C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_download_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orbx_debug_candidates.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_debug_level_keys.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_pyramid_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orbx_get_tables.argtypes = [C.c_void_p] * 7
+        L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def _check(status):
+    if status != OK:
+        raise OrbxError(status, lib().orbx_last_error_string().decode())
+
+
+def _ptr(a):
+    """Raw address of a numpy array or a torch tensor (None -> NULL)."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()          # torch.Tensor
+
+
+def _on_device(a):
+    return 0 if isinstance(a, np.ndarray) else int(a.is_cuda)
+
+
+def kernel_launch_count():
+    return int(lib().orbx_kernel_launch_count())
+
+
+class ORBextractor:
+    """ORB_SLAM2::ORBextractor.  The device handle is created on first use (the reference's
+    constructor does not know the image size); pass max_w/max_h/max_batch to size it up front."""
+
+    HARRIS_SCORE, FAST_SCORE = 0, 1
+
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, max_w=0, max_h=0, max_batch=1, device=0):
+        self.params = _Params(int(nfeatures), float(scaleFactor), int(nlevels), int(iniThFAST), int(minThFAST))
+        self.max_w, self.max_h, self.max_batch, self.device = max_w, max_h, max_batch, device
+        self._h = None
+        self.shape = None
+        if max_w and max_h:
+            self._create(max_w, max_h)
+
+    def _create(self, w, h):
+        h_ = C.c_void_p()
+        _check(lib().orbx_extractor_create(C.byref(self.params), int(w), int(h), int(self.max_batch), int(self.device), C.byref(h_)))
+        self._h = h_
+        self.max_w, self.max_h = w, h
+        self.kp_cap = lib().orbx_max_keypoints(self._h)
+
+    def close(self):
+        if self._h is not None:
+            lib().orbx_extractor_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- the reference's getters (include/ORBextractor.h:63-83) ---
+    def _tables(self):
+        if self._h is None:
+            raise OrbxError(ERR_STATE, "extractor handle not created yet (pass max_w/max_h or extract once)")
+        n = C.c_int()
+        arr = [np.zeros(8, np.float32) for _ in range(4)]
+        q = np.zeros(8, np.int32)
+        _check(lib().orbx_get_tables(self._h, C.byref(n), *[a.ctypes.data for a in arr], q.ctypes.data))
+        return n.value, arr, q
+
+    def GetLevels(self):
+        return self.params.nlevels
+
+    def GetScaleFactor(self):
+        return self.params.scale_factor
+
+    def GetScaleFactors(self):
+        n, a, _ = self._tables(); return a[0][:n].copy()
+
+    def GetInverseScaleFactors(self):
+        n, a, _ = self._tables(); return a[1][:n].copy()
+
+    def GetScaleSigmaSquares(self):
+        n, a, _ = self._tables(); return a[2][:n].copy()
+
+    def GetInverseScaleSigmaSquares(self):
+        n, a, _ = self._tables(); return a[3][:n].copy()
+
+    def features_per_level(self):
+        n, _, q = self._tables(); return q[:n].copy()
+
+    # --- operator() ---
+    def __call__(self, image, mask=None):
+        """(keypoints, descriptors) for one host image; mask is ignored as in the reference."""
+        if image is None or image.size == 0:
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        if image.dtype != np.uint8 or image.ndim != 2:
+            raise OrbxError(ERR_BAD_ARG, "image must be a 2-D uint8 array (CV_8UC1)")   # assert at src/ORBextractor.cc:1050
+        h, w = image.shape
+        if self._h is None:
+            self._create(w, h)
+        cap = self.kp_cap
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8); n = C.c_int()
+        _check(lib().orbx_extract(self._h, image.ctypes.data, w, h, image.strides[0], kps.ctypes.data, desc.ctypes.data,
+                                  cap, C.byref(n), None))
+        self.shape = (h, w)
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    # --- batched path (many frames per launch) ---
+    def extract_batch(self, images, first_slot=0, stream=None):
+        """images: (n, h, w) uint8, numpy (host) or torch (host pinned / cuda).  Asynchronous."""
+        n, h, w = images.shape
+        if self._h is None:
+            self._create(w, h)
+        if isinstance(images, np.ndarray):
+            stride, istride = images.strides[1], images.strides[0]
+        else:
+            stride, istride = images.stride(1), images.stride(0)
+        _check(lib().orbx_extract_batch(self._h, _ptr(images), n, w, h, stride, istride, _on_device(images), first_slot, stream))
+        self.shape = (h, w)
+
+    def fetch_into(self, first_slot, n, kps, desc, counts, stream=None):
+        """Copies results into caller arrays/tensors laid out [n][cap]; cap is read from `counts`' siblings."""
+        ref = kps if kps is not None else desc
+        cap = ref.shape[1] if ref is not None else self.kp_cap
+        dev = _on_device(ref if ref is not None else counts)
+        _check(lib().orbx_fetch_results(self._h, first_slot, n, _ptr(kps), _ptr(desc), _ptr(counts), cap, dev, stream))
+
+    def fetch(self, first_slot=0, n=1):
+        """Synchronous convenience: list of (keypoints, descriptors) per slot."""
+        cap = self.kp_cap
+        kps = np.zeros((n, cap), KP_DTYPE); desc = np.zeros((n, cap, 32), np.uint8); cnt = np.zeros(n, np.int32)
+        self.fetch_into(first_slot, n, kps, desc, cnt)
+        _sync(self.device)
+        return [(kps[i, :cnt[i]].copy(), desc[i, :cnt[i]].copy()) for i in range(n)]
+
+    def level(self, slot, level):
+        """Bordered pyramid plane (h+38, w+38) of one slot, as the reference's mvImagePyramid backing store."""
+        ww, hh = C.c_int(), C.c_int()
+        _check(lib().orbx_pyramid_level(self._h, slot, level, None, C.byref(ww), C.byref(hh), None))
+        out = np.zeros((hh.value + 38, ww.value + 38), np.uint8)
+        _check(lib().orbx_download_level(self._h, slot, level, out.ctypes.data))
+        return out
+
+    @property
+    def mvImagePyramid(self):
+        """Host copies of slot 0's level ROIs (the reference's public member, include/ORBextractor.h:85)."""
+        return [self.level(0, l)[19:-19, 19:-19] for l in range(self.params.nlevels)]
+
+    def debug_candidates(self, slot, level, cap=1 << 20):
+        out = np.zeros(cap, np.uint32); n = C.c_int()
+        _check(lib().orbx_debug_candidates(self._h, slot, level, out.ctypes.data, cap, C.byref(n)))
+        p = out[:n.value]
+        return np.stack([p & 0xFFF, (p >> 12) & 0xFFF, p >> 24], 1).astype(np.int32)
+
+    def debug_level_keys(self, slot, level, cap=1 << 16):
+        out = np.zeros(cap, np.uint32); n = C.c_int()
+        _check(lib().orbx_debug_level_keys(self._h, slot, level, out.ctypes.data, cap, C.byref(n)))
+        p = out[:n.value]
+        return np.stack([p & 0xFFF, (p >> 12) & 0xFFF, p >> 24], 1).astype(np.int32)
+
+
+def _sync(device=0):
+    import torch
+    torch.cuda.synchronize(device)
+
+
+def ComputeStereoMatches(extL, extR, bf, fx, n=1, slotL0=0, slotR0=0, out=None, stream=None):
+    """Frame::ComputeStereoMatches for n pairs already extracted into the given slots.
+    Returns (mvuRight [n][cap], mvDepth [n][cap], n_matches [n]).  With `out` = (uRight, depth,
+    n_matches) torch/numpy buffers the call is asynchronous and returns them."""
+    cap = extL.kp_cap
+    if out is None:
+        ur = np.zeros((n, cap), np.float32); dp = np.zeros((n, cap), np.float32); nm = np.zeros(n, np.int32)
+        _check(lib().orbx_stereo_match_batch(extL._h, slotL0, extR._h, slotR0, n, bf, fx, ur.ctypes.data, dp.ctypes.data,
+                                             nm.ctypes.data, cap, 0, stream))
+        _sync(extL.device)
+        return ur, dp, nm
+    ur, dp, nm = out
+    _check(lib().orbx_stereo_match_batch(extL._h, slotL0, extR._h, slotR0, n, bf, fx, _ptr(ur), _ptr(dp), _ptr(nm),
+                                         ur.shape[1], _on_device(ur), stream))
+    return out
+
+
+class Frame:
+    """The slice of ORB_SLAM2::Frame the matchers read: undistorted keypoints, descriptors, image bounds."""
+
+    def __init__(self, keypoints, descriptors, cols, rows):
+        self.mvKeysUn, self.mDescriptors, self.cols, self.rows = keypoints, descriptors, cols, rows
+
+
+class ORBmatcher:
+    """ORB_SLAM2::ORBmatcher (include/ORBmatcher.h:41-89): the two searches on the hot path."""
+    TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        self.mfNNratio, self.mbCheckOrientation = float(nnratio), bool(checkOri)
+
+    @staticmethod
+    def DescriptorDistance(a, b):
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return int(lib().orbx_hamming256(a.ctypes.data, b.ctypes.data))
+
+    def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
+        """Returns (nmatches, vnMatches12); vbPrevMatched (N1 x 2 float32) is updated in place."""
+        r = self.SearchForInitializationBatch([F1], [F2], [vbPrevMatched], windowSize)
+        return r[0][0], r[1][0]
+
+    def SearchForInitializationBatch(self, F1s, F2s, prevs, windowSize=10):
+        npairs = len(F1s)
+        cap = max(max(len(f.mvKeysUn) for f in F1s), max(len(f.mvKeysUn) for f in F2s), 1)
+        k1 = np.zeros((npairs, cap), KP_DTYPE); k2 = np.zeros((npairs, cap), KP_DTYPE)
+        d1 = np.zeros((npairs, cap, 32), np.uint8); d2 = np.zeros((npairs, cap, 32), np.uint8)
+        n1 = np.zeros(npairs, np.int32); n2 = np.zeros(npairs, np.int32)
+        pv = np.zeros((npairs, cap, 2), np.float32)
+        for p, (a, b, pr) in enumerate(zip(F1s, F2s, prevs)):
+            n1[p], n2[p] = len(a.mvKeysUn), len(b.mvKeysUn)
+            k1[p, :n1[p]] = a.mvKeysUn; d1[p, :n1[p]] = a.mDescriptors
+            k2[p, :n2[p]] = b.mvKeysUn; d2[p, :n2[p]] = b.mDescriptors
+            pv[p, :n1[p]] = pr
+        m12 = np.zeros((npairs, cap), np.int32); nm = np.zeros(npairs, np.int32)
+        _check(lib().orbx_search_init_batch(k1.ctypes.data, d1.ctypes.data, n1.ctypes.data, k2.ctypes.data, d2.ctypes.data,
+                                            n2.ctypes.data, npairs, cap, F2s[0].cols, F2s[0].rows, pv.ctypes.data,
+                                            self.mfNNratio, int(windowSize), int(self.mbCheckOrientation),
+                                            m12.ctypes.data, nm.ctypes.data, 0, None))
+        for p, pr in enumerate(prevs):
+            pr[:] = pv[p, :n1[p]]
+        return [int(v) for v in nm], [m12[p, :n1[p]].copy() for p in range(npairs)]
+
+    def SearchByBoW(self, descA, angA, descB, angB, strict=True):
+        """SearchByBoW(KF,KF) with one bucket holding all features (brute-force kNN + ratio)."""
+        r = self.SearchByBoWBatch([(descA, angA)], [(descB, angB)], strict)
+        return r[0][0], r[1][0]
+
+    def SearchByBoWBatch(self, As, Bs, strict=True):
+        npairs = len(As)
+        cap = max(max(len(a[0]) for a in As), max(len(b[0]) for b in Bs), 1)
+        dA = np.zeros((npairs, cap, 32), np.uint8); dB = np.zeros((npairs, cap, 32), np.uint8)
+        aA = np.zeros((npairs, cap), np.float32); aB = np.zeros((npairs, cap), np.float32)
+        nA = np.zeros(npairs, np.int32); nB = np.zeros(npairs, np.int32)
+        for p, ((da, aa), (db, ab)) in enumerate(zip(As, Bs)):
+            nA[p], nB[p] = len(da), len(db)
+            dA[p, :nA[p]] = da; aA[p, :nA[p]] = aa; dB[p, :nB[p]] = db; aB[p, :nB[p]] = ab
+        m12 = np.zeros((npairs, cap), np.int32); nm = np.zeros(npairs, np.int32)
+        _check(lib().orbx_knn_ratio_batch(dA.ctypes.data, aA.ctypes.data, nA.ctypes.data, dB.ctypes.data, aB.ctypes.data,
+                                          nB.ctypes.data, npairs, cap, self.TH_LOW, self.mfNNratio,
+                                          int(self.mbCheckOrientation), int(strict), m12.ctypes.data, nm.ctypes.data, 0, None))
+        return [int(v) for v in nm], [m12[p, :nA[p]].copy() for p in range(npairs)]

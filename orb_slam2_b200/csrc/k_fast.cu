@@ -1,0 +1,169 @@
+// K2 — FAST-9/16 corner detection per 30-px cell with the reference's threshold fallback.
+//
+// Replaces the per-cell cv::FAST calls of ORBextractor::ComputeKeyPointsOctTree
+// (src/ORBextractor.cc:789-829): FAST(window, iniThFAST, nms=true) and, iff that returns no
+// keypoint, FAST(window, minThFAST, nms=true).
+//
+// Formulation (DESIGN.md "K2"): for every tested pixel the arc score
+//     S(p) = max over the 16 arcs of 9 contiguous ring pixels of max(min d_k, min -d_k),
+//     d_k = I(p) - I(ring_k)
+// is threshold independent: p is a corner at t  <=>  S > t, and cv::FAST's response is S-1.
+// OpenCV's 3x3 non-max suppression (neighbours that are not corners count as 0, pixels in the
+// 3-px window rim are never corners) reduces to "S(p) > t and S(p) > S(q) for the 8 neighbours
+// q inside the cell", also threshold independent.  So one S map per cell serves both thresholds.
+//
+// One warp per cell.  The window is staged in shared memory, each lane owns a column.  S is
+// evaluated branch-free with the DPX 3-input packed min/max (VIMNMX3.S16x2): the bright and the
+// dark polarity ride in the two 16-bit halves of one register, built by a single IMAD per ring
+// pixel: P_k = r_k*0xFFFF + ((256-v)<<16 | (v+256))  ->  lo = d_k+256, hi = -d_k+256.
+// Kept corners are appended to the level's candidate pool in pixel row-major order (ballot +
+// popc); the cell table records {pool offset, count} so K3 can restore the reference's
+// cell-row-major candidate order.
+#include "orbx_internal.h"
+
+namespace orbx {
+
+constexpr int kFastWarps = 4;
+
+__device__ __forceinline__ uint32_t vmin3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_s16x2(a, b, c); }
+__device__ __forceinline__ uint32_t vmax3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
+
+// Arc score of the pixel at c (shared-memory window, row pitch wp).  Returns S in [-255, 255].
+__device__ __forceinline__ int arc_score(const uint8_t* c, int wp) {
+  const int v = c[0];
+  const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
+  uint32_t P[16];
+  const uint8_t* r3 = c + 3 * wp;
+  const uint8_t* r2 = c + 2 * wp;
+  const uint8_t* r1 = c + wp;
+  const uint8_t* q1 = c - wp;
+  const uint8_t* q2 = c - 2 * wp;
+  const uint8_t* q3 = c - 3 * wp;
+  P[0] = r3[0] * 0xFFFFu + base;   P[1] = r3[1] * 0xFFFFu + base;   P[2] = r2[2] * 0xFFFFu + base;
+  P[3] = r1[3] * 0xFFFFu + base;   P[4] = c[3] * 0xFFFFu + base;    P[5] = q1[3] * 0xFFFFu + base;
+  P[6] = q2[2] * 0xFFFFu + base;   P[7] = q3[1] * 0xFFFFu + base;   P[8] = q3[0] * 0xFFFFu + base;
+  P[9] = q3[-1] * 0xFFFFu + base;  P[10] = q2[-2] * 0xFFFFu + base; P[11] = q1[-3] * 0xFFFFu + base;
+  P[12] = c[-3] * 0xFFFFu + base;  P[13] = r1[-3] * 0xFFFFu + base; P[14] = r2[-2] * 0xFFFFu + base;
+  P[15] = r3[-1] * 0xFFFFu + base;
+  uint32_t m3[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) m3[k] = vmin3(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
+  uint32_t m9[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) m9[k] = vmin3(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+  uint32_t a = vmax3(m9[0], m9[1], m9[2]), b = vmax3(m9[3], m9[4], m9[5]), d = vmax3(m9[6], m9[7], m9[8]);
+  uint32_t e = vmax3(m9[9], m9[10], m9[11]), f = vmax3(m9[12], m9[13], m9[14]);
+  uint32_t g = vmax3(a, b, d), h = vmax3(e, f, m9[15]);
+  uint32_t s = vmax3(g, h, h);
+  return max((int)(s & 0xFFFF), (int)(s >> 16)) - 256;
+}
+
+// smem per warp: window [win_rows][win_pitch] (reused as the code map) + S map [(ih+2)][s_pitch]
+__global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, int first_slot, int n, int win_pitch,
+                                                                int win_rows, int s_pitch, int s_rows) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int win_bytes = win_pitch * win_rows, s_bytes = s_pitch * s_rows;
+  uint8_t* win = smem + (size_t)warp * (win_bytes + s_bytes);
+  uint8_t* smap = win + win_bytes;
+
+  const long long gcell = (long long)blockIdx.x * kFastWarps + warp;
+  if (gcell >= (long long)n * L.cells_per_slot) return;
+  const int img = (int)(gcell / L.cells_per_slot);
+  const int c = (int)(gcell - (long long)img * L.cells_per_slot);
+  const int slot = first_slot + img;
+  int level = 0;
+  for (int l = 1; l < L.nlevels; ++l)
+    if (c >= L.geom[l].cell_base) level = l;
+  const LevelGeom& g = L.geom[level];
+  const int ci = c - g.cell_base, ci_row = ci / g.nCols, ci_col = ci - ci_row * g.nCols;
+  const int x0 = kFastBorder + ci_col * g.wCell, y0 = kFastBorder + ci_row * g.hCell;
+  const int ww = min(x0 + g.wCell + 6, g.maxBX) - x0, hh = min(y0 + g.hCell + 6, g.maxBY) - y0;
+  uint2* cell_out = L.celltab + (size_t)slot * L.cells_per_slot + c;
+  if (y0 >= g.maxBY - 3 || x0 >= g.maxBX - 6 || ww < 7 || hh < 7) {  // src/ORBextractor.cc:794,802
+    if (lane == 0) *cell_out = make_uint2(0u, 0u);
+    return;
+  }
+  const int iw = ww - 6, ih = hh - 6;
+
+  // stage the window; clear the S map (its 1-px rim stays 0 = "not a corner")
+  const uint8_t* roi = L.pyr + g.plane_off + (size_t)slot * g.plane_stride + (size_t)kEdge * g.pitch + kEdge;
+  for (int r = 0; r < hh; ++r) {
+    const uint8_t* srow = roi + (size_t)(y0 + r) * g.pitch + x0;
+    for (int x = lane; x < ww; x += 32) win[r * win_pitch + x] = __ldg(srow + x);
+  }
+  for (int i = lane; i < (s_bytes >> 2); i += 32) reinterpret_cast<uint32_t*>(smap)[i] = 0u;
+  __syncwarp();
+
+  // pass 1: S for every tested pixel
+  for (int cb = 0; cb < iw; cb += 32) {
+    const int xx = cb + lane;
+    if (xx < iw) {
+      for (int yy = 0; yy < ih; ++yy) {
+        const int s = arc_score(win + (yy + 3) * win_pitch + xx + 3, win_pitch);
+        smap[(yy + 1) * s_pitch + xx + 1] = (uint8_t)max(s, 0);
+      }
+    }
+  }
+  __syncwarp();
+
+  // pass 2: strict 3x3 maxima -> code 2 (corner at iniTh), 1 (corner at minTh only), 0
+  uint8_t* code = win;  // the window is dead from here on
+  int cnt_ini = 0, cnt_min = 0;
+  for (int yy = 0; yy < ih; ++yy)
+    for (int cb = 0; cb < iw; cb += 32) {
+      const int xx = cb + lane;
+      int cd = 0;
+      if (xx < iw) {
+        const uint8_t* p = smap + (yy + 1) * s_pitch + xx + 1;
+        const int s = p[0];
+        if (s > L.min_th) {
+          const bool mx = p[-1] < s && p[1] < s && p[-s_pitch - 1] < s && p[-s_pitch] < s && p[-s_pitch + 1] < s &&
+                          p[s_pitch - 1] < s && p[s_pitch] < s && p[s_pitch + 1] < s;
+          if (mx) cd = s > L.ini_th ? 2 : 1;
+        }
+        code[yy * iw + xx] = (uint8_t)cd;
+      }
+      cnt_ini += __popc(__ballot_sync(0xffffffffu, cd == 2));
+      cnt_min += __popc(__ballot_sync(0xffffffffu, cd >= 1));
+    }
+  const int need = cnt_ini > 0 ? 2 : 1;              // src/ORBextractor.cc:812: retry iff empty
+  const int total = cnt_ini > 0 ? cnt_ini : cnt_min;
+  int base = 0;
+  if (lane == 0) {
+    if (total > 0) base = atomicAdd(L.poolcnt + slot * kMaxLevels + level, total);
+    *cell_out = make_uint2((uint32_t)base, (uint32_t)total);
+  }
+  if (total == 0) return;
+  base = __shfl_sync(0xffffffffu, base, 0);
+  __syncwarp();
+
+  // pass 3: emit in pixel row-major order
+  uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
+  int run = 0;
+  for (int yy = 0; yy < ih; ++yy)
+    for (int cb = 0; cb < iw; cb += 32) {
+      const int xx = cb + lane;
+      const bool keep = xx < iw && code[yy * iw + xx] >= need;
+      const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+      if (keep) {
+        const int pos = base + run + __popc(bal & ((1u << lane) - 1u));
+        const int resp = (int)smap[(yy + 1) * s_pitch + xx + 1] - 1;
+        if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
+      }
+      run += __popc(bal);
+    }
+}
+
+int launch_fast(const DeviceLayout& L, const LevelGeom* hg, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
+  (void)hg;
+  const int win_pitch = (win_w + 3) & ~3, win_rows = win_h;
+  const int s_pitch = ((win_w - 6 + 2) + 3) & ~3, s_rows = win_h - 6 + 2;
+  const size_t smem = (size_t)kFastWarps * (win_pitch * win_rows + s_pitch * s_rows);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const long long cells = (long long)n * L.cells_per_slot;
+  k_fast_cells<<<(unsigned)((cells + kFastWarps - 1) / kFastWarps), kFastWarps * 32, smem, st>>>(L, first_slot, n, win_pitch, win_rows, s_pitch, s_rows);
+  return 1;
+}
+
+}  // namespace orbx

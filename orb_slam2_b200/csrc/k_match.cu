@@ -1,0 +1,241 @@
+// K6 / K7 — ORBmatcher Hamming searches, batched over independent frame pairs.
+//
+// K6  k_search_init  <- ORBmatcher::SearchForInitialization   src/ORBmatcher.cc:405-520
+//                       (+ Frame::GetFeaturesInArea / PosInGrid, src/Frame.cc:327-392)
+// K7  k_knn_ratio    <- ORBmatcher::SearchByBoW(KF,KF), one bucket  src/ORBmatcher.cc:522-655
+//     three_maxima   <- ORBmatcher::ComputeThreeMaxima        src/ORBmatcher.cc:1601-1642
+//
+// Both reference routines carry a sequential dependency (hazard H6): a query's candidate set
+// depends on what earlier queries matched (vMatchedDistance / vbMatched2).  Queries are
+// therefore resolved in index order by one warp (K6) or one CTA (K7) per pair, with the
+// per-query candidate scan spread over the lanes/threads; pairs are independent and fill the GPU.
+//
+// K6 needs no bucket grid: a keypoint of frame 2 is returned by GetFeaturesInArea iff it is on
+// level 0, PosInGrid accepted it, and |dx| < r, |dy| < r (the cell range computed with
+// floor/ceil always covers the round()-assigned cell of such a keypoint).  The grid only fixes
+// the enumeration order (cell x, cell y, index), which matters for ties on the best distance;
+// it is carried as a 64-bit key  distance<<32 | cell<<16 | index  reduced with min.
+#include <climits>
+
+#include "orbx_internal.h"
+
+namespace orbx {
+
+constexpr int kHisto = 30;
+
+__device__ __forceinline__ int ham8(const uint32_t* a, const uint32_t* b) {
+  int d = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i += 2)
+    d += __popcll(((unsigned long long)(a[i + 1] ^ b[i + 1]) << 32) | (a[i] ^ b[i]));
+  return d;
+}
+
+__device__ __forceinline__ int rot_bin(float a1, float a2) {
+  float rot = __fsub_rn(a1, a2);
+  if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+  int bin = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
+  if (bin == kHisto) bin = 0;
+  return bin;
+}
+
+// hist[0..29] -> the up-to-three bins to keep
+__device__ __forceinline__ void three_maxima(const int* hist, int& i1, int& i2, int& i3) {
+  int m1 = 0, m2 = 0, m3 = 0;
+  i1 = i2 = i3 = -1;
+  for (int i = 0; i < kHisto; ++i) {
+    const int s = hist[i];
+    if (s > m1) { m3 = m2; m2 = m1; m1 = s; i3 = i2; i2 = i1; i1 = i; }
+    else if (s > m2) { m3 = m2; m2 = s; i3 = i2; i2 = i; }
+    else if (s > m3) { m3 = s; i3 = i; }
+  }
+  if ((float)m2 < __fmul_rn(0.1f, (float)m1)) { i2 = -1; i3 = -1; }
+  else if ((float)m3 < __fmul_rn(0.1f, (float)m1)) { i3 = -1; }
+}
+
+// ------------------------------------------------------------------------------------------
+// K6: one warp per frame pair.  scratch per pair: 4*cap ints
+//   [0,cap)      compact list of frame-2 level-0 keypoints: cell<<16 | index
+//   [cap,2cap)   vMatchedDistance per frame-2 keypoint
+//   [2cap,3cap)  vnMatches21
+//   [3cap,4cap)  rotation bin per frame-1 keypoint (-1 = none)
+__global__ void __launch_bounds__(32) k_search_init(InitMatchArgs a) {
+  __shared__ int s_hist[kHisto];
+  const int p = blockIdx.x, lane = threadIdx.x;
+  const int n1 = a.n1[p], n2 = a.n2[p];
+  const orbx_keypoint* k1 = a.k1 + (size_t)p * a.cap;
+  const orbx_keypoint* k2 = a.k2 + (size_t)p * a.cap;
+  const uint32_t* d1 = reinterpret_cast<const uint32_t*>(a.d1 + (size_t)p * a.cap * 32);
+  const uint32_t* d2 = reinterpret_cast<const uint32_t*>(a.d2 + (size_t)p * a.cap * 32);
+  float* prev = a.prev + (size_t)p * a.cap * 2;
+  int* m12 = a.m12 + (size_t)p * a.cap;
+  int* clist = a.scratch + (size_t)p * a.cap * 4;
+  int* mdist = clist + a.cap;
+  int* m21 = mdist + a.cap;
+  int* binof = m21 + a.cap;
+
+  for (int i = lane; i < n1; i += 32) { m12[i] = -1; binof[i] = -1; }
+  for (int i = lane; i < n2; i += 32) { mdist[i] = INT_MAX; m21[i] = -1; }
+  if (lane < kHisto) s_hist[lane] = 0;
+  int nc = 0;
+  for (int base = 0; base < n2; base += 32) {
+    const int i = base + lane;
+    bool ok = false;
+    int cell = 0;
+    if (i < n2) {
+      const orbx_keypoint kp = k2[i];
+      const int gx = (int)roundf(__fmul_rn(kp.x, a.invW)), gy = (int)roundf(__fmul_rn(kp.y, a.invH));   // PosInGrid
+      ok = kp.octave == 0 && gx >= 0 && gx < 64 && gy >= 0 && gy < 48;
+      cell = gx * 48 + gy;
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if (ok) clist[nc + __popc(bal & ((1u << lane) - 1u))] = (cell << 16) | i;
+    nc += __popc(bal);
+  }
+  __syncwarp();
+
+  int nm = 0;
+  const float r = a.window;
+  for (int i1 = 0; i1 < n1; ++i1) {
+    if (k1[i1].octave > 0) continue;
+    const float qx = prev[2 * i1], qy = prev[2 * i1 + 1];
+    uint32_t q[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) q[w] = __ldg(d1 + (size_t)i1 * 8 + w);
+    unsigned long long b1 = ~0ull;
+    int b2 = INT_MAX;
+    for (int j = lane; j < nc; j += 32) {
+      const int ck = clist[j], i2 = ck & 0xFFFF;
+      const orbx_keypoint kp = k2[i2];
+      if (!(fabsf(__fsub_rn(kp.x, qx)) < r && fabsf(__fsub_rn(kp.y, qy)) < r)) continue;
+      const int d = ham8(q, d2 + (size_t)i2 * 8);
+      if (mdist[i2] <= d) continue;
+      const unsigned long long key = ((unsigned long long)d << 32) | (unsigned)ck;
+      if (key < b1) { if (b1 != ~0ull) b2 = (int)(b1 >> 32); b1 = key; }
+      else if (d < b2) b2 = d;
+    }
+    // warp merge: global best key; second best = min(owner's second, everybody else's best)
+    unsigned hi = (unsigned)(b1 >> 32), lo = (unsigned)b1;
+    const unsigned ghi = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned glo = __reduce_min_sync(0xffffffffu, hi == ghi ? lo : 0xffffffffu);
+    if (ghi == 0xffffffffu) continue;
+    const bool owner = hi == ghi && lo == glo;
+    const int contrib = owner ? b2 : (b1 == ~0ull ? INT_MAX : (int)hi);
+    const int bestDist2 = (int)__reduce_min_sync(0xffffffffu, (unsigned)contrib);
+    const int bestDist = (int)ghi, bi = glo & 0xFFFF;
+    if (bestDist <= 50 && (float)bestDist < __fmul_rn((float)bestDist2, a.ratio)) {
+      if (lane == 0) {
+        if (m21[bi] >= 0) m12[m21[bi]] = -1;
+        m12[i1] = bi; m21[bi] = i1; mdist[bi] = bestDist;
+        if (a.checkOri) { const int bin = rot_bin(k1[i1].angle, k2[bi].angle); binof[i1] = bin; s_hist[bin] += 1; }
+      }
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  int k_a = -1, k_b = -1, k_c = -1;
+  if (a.checkOri) three_maxima(s_hist, k_a, k_b, k_c);
+  for (int i = lane; i < n1; i += 32) {
+    int m = m12[i];
+    if (a.checkOri && m >= 0) {
+      const int b = binof[i];
+      if (b != k_a && b != k_b && b != k_c) { m = -1; m12[i] = -1; }
+    }
+    if (m >= 0) { prev[2 * i] = k2[m].x; prev[2 * i + 1] = k2[m].y; ++nm; }
+  }
+  nm = __reduce_add_sync(0xffffffffu, nm);
+  if (lane == 0) a.nm[p] = nm;
+}
+
+// ------------------------------------------------------------------------------------------
+// K7: one CTA per pair; B descriptors transposed in shared memory ([word][j], conflict-free).
+constexpr int kKnnThreads = 256;
+
+__global__ void __launch_bounds__(kKnnThreads) k_knn_ratio(KnnArgs a, int capPad) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint32_t* Bt = reinterpret_cast<uint32_t*>(smem);            // [8][capPad]
+  uint8_t* used = reinterpret_cast<uint8_t*>(Bt + 8 * capPad);  // [capPad]
+  __shared__ unsigned s_key[kKnnThreads / 32];
+  __shared__ int s_sec[kKnnThreads / 32];
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_nm;
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nA = a.nA[p], nB = a.nB[p];
+  const uint32_t* dA = reinterpret_cast<const uint32_t*>(a.dA + (size_t)p * a.cap * 32);
+  const uint32_t* dB = reinterpret_cast<const uint32_t*>(a.dB + (size_t)p * a.cap * 32);
+  const float* angA = a.angA + (size_t)p * a.cap;
+  const float* angB = a.angB + (size_t)p * a.cap;
+  int* m12 = a.m12 + (size_t)p * a.cap;
+  int* binof = a.scratch + (size_t)p * a.cap;
+
+  for (int idx = tid; idx < nB * 8; idx += kKnnThreads) { const int j = idx >> 3, w = idx & 7; Bt[w * capPad + j] = __ldg(dB + idx); }
+  for (int j = tid; j < capPad; j += kKnnThreads) used[j] = 0;
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (tid == 0) s_nm = 0;
+  __syncthreads();
+
+  for (int i = 0; i < nA; ++i) {
+    uint32_t q[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) q[w] = __ldg(dA + (size_t)i * 8 + w);
+    unsigned b1 = 256u << 16;   // bestDist1 = 256, no index
+    int b2 = 256;
+    for (int j = tid; j < nB; j += kKnnThreads) {
+      if (used[j]) continue;
+      int d = 0;
+#pragma unroll
+      for (int w = 0; w < 8; w += 2)
+        d += __popcll(((unsigned long long)(q[w + 1] ^ Bt[(w + 1) * capPad + j]) << 32) | (q[w] ^ Bt[w * capPad + j]));
+      const unsigned key = ((unsigned)d << 16) | (unsigned)j;
+      if (d < (int)(b1 >> 16)) { b2 = (int)(b1 >> 16); b1 = key; }      // strict '<' keeps the first j, :586
+      else if (d < b2) b2 = d;
+    }
+    const unsigned wmin = __reduce_min_sync(0xffffffffu, b1);
+    const int wsec = (int)__reduce_min_sync(0xffffffffu, (unsigned)(b1 == wmin ? b2 : (int)(b1 >> 16)));
+    if (lane == 0) { s_key[warp] = wmin; s_sec[warp] = wsec; }
+    __syncthreads();
+    if (tid == 0) {
+      unsigned g = s_key[0];
+      int own = 0;
+      for (int w = 1; w < kKnnThreads / 32; ++w) if (s_key[w] < g) { g = s_key[w]; own = w; }
+      int sec = s_sec[own];
+      for (int w = 0; w < kKnnThreads / 32; ++w) if (w != own) sec = min(sec, (int)(s_key[w] >> 16));
+      const int best = (int)(g >> 16), bi = g & 0xFFFF;
+      int m = -1, bin = -1;
+      const bool pass = a.strict ? best < a.th : best <= a.th;
+      if (pass && (float)best < __fmul_rn(a.ratio, (float)sec)) {
+        m = bi; used[bi] = 1; s_nm += 1;
+        if (a.checkOri) { bin = rot_bin(angA[i], angB[bi]); s_hist[bin] += 1; }
+      }
+      m12[i] = m; binof[i] = bin;
+    }
+    __syncthreads();
+  }
+  if (a.checkOri) {
+    int k_a, k_b, k_c;
+    three_maxima(s_hist, k_a, k_b, k_c);
+    int drop = 0;
+    for (int i = tid; i < nA; i += kKnnThreads) {
+      const int b = binof[i];
+      if (b >= 0 && b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
+    }
+    if (drop) atomicSub(&s_nm, drop);
+    __syncthreads();
+  }
+  if (tid == 0) a.nm[p] = s_nm;
+}
+
+int launch_search_init(const InitMatchArgs& a, cudaStream_t st) {
+  k_search_init<<<a.n_pairs, 32, 0, st>>>(a);
+  return 1;
+}
+
+int launch_knn_ratio(const KnnArgs& a, cudaStream_t st) {
+  const int capPad = (a.cap + 31) & ~31;
+  const size_t smem = (size_t)capPad * 33;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_knn_ratio, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_knn_ratio<<<a.n_pairs, kKnnThreads, smem, st>>>(a, capPad);
+  return 1;
+}
+
+}  // namespace orbx

@@ -1,0 +1,193 @@
+// K5 — stereo matching for rectified pairs, batched over frames.
+//
+// Replaces Frame::ComputeStereoMatches (src/Frame.cc:466-640).
+//   k_stereo_match : one warp per left keypoint.
+//     (i)  descriptor search.  The reference buckets right keypoints into a per-row table
+//          (:476-493) and scans the left keypoint's row in ascending iR with a strict "<"
+//          (:522-548).  Equivalent without the table: among all iR with
+//          floor(yR-r) <= (int)vL <= ceil(yR+r), |octave difference| <= 1 and uL-maxD <= uR <= uL,
+//          take the minimum of (distance, iR) lexicographically.  Lanes stride over iR, 4x
+//          __popcll per candidate, one REDUX min over the packed key.
+//     (ii) 11x11 SAD over 11 shifts on the pyramid level of the left keypoint (:552-592), integer
+//          arithmetic (the reference's float L1 norm of integer-valued patches is exact),
+//          first minimum wins; parabola refinement in the reference's float operation order
+//          with un-fused intrinsics (:597-622).
+//   k_stereo_median: one CTA per frame; the median SAD (element size/2 of the sorted list, :627)
+//     by rank counting, then the 1.5*1.4*median cut (:628-639).
+#include <climits>
+
+#include "orbx_internal.h"
+
+namespace orbx {
+
+constexpr int kStWarps = 8;
+constexpr int kStPerCta = 64;   // left keypoints per CTA
+
+__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4* __restrict__ b) {
+  const uint4 b0 = __ldg(b), b1 = __ldg(b + 1);
+  const unsigned long long x0 = ((unsigned long long)(a0.y ^ b0.y) << 32) | (a0.x ^ b0.x);
+  const unsigned long long x1 = ((unsigned long long)(a0.w ^ b0.w) << 32) | (a0.z ^ b0.z);
+  const unsigned long long x2 = ((unsigned long long)(a1.y ^ b1.y) << 32) | (a1.x ^ b1.x);
+  const unsigned long long x3 = ((unsigned long long)(a1.w ^ b1.w) << 32) | (a1.z ^ b1.z);
+  return __popcll(x0) + __popcll(x1) + __popcll(x2) + __popcll(x3);
+}
+
+__global__ void __launch_bounds__(kStWarps * 32) k_stereo_match(StereoArgs a, int chunks) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int capR = a.R.kp_cap;
+  float* s_x = reinterpret_cast<float*>(smem);
+  short* s_min = reinterpret_cast<short*>(s_x + capR);
+  short* s_max = s_min + capR;
+  int8_t* s_oct = reinterpret_cast<int8_t*>(s_max + capR);
+  uint8_t* s_patch = reinterpret_cast<uint8_t*>(s_oct) + ((capR + 15) & ~15);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int img = blockIdx.x / chunks, chunk = blockIdx.x - img * chunks;
+  const int slotL = a.slotL0 + img, slotR = a.slotR0 + img;
+  const int nL = a.L.nkp[slotL], nR = a.R.nkp[slotR];
+  if (chunk * kStPerCta >= nL) return;
+  const orbx_keypoint* kL = a.L.kps + (size_t)slotL * a.L.kp_cap;
+  const orbx_keypoint* kR = a.R.kps + (size_t)slotR * a.R.kp_cap;
+  const uint8_t* dL = a.L.desc + (size_t)slotL * a.L.kp_cap * 32;
+  const uint8_t* dR = a.R.desc + (size_t)slotR * a.R.kp_cap * 32;
+
+  for (int i = tid; i < nR; i += kStWarps * 32) {
+    const orbx_keypoint kp = kR[i];
+    const float r = __fmul_rn(2.0f, a.L.geom[kp.octave].scale);                     // :487
+    s_max[i] = (short)(int)ceilf(__fadd_rn(kp.y, r));
+    s_min[i] = (short)(int)floorf(__fsub_rn(kp.y, r));
+    s_oct[i] = (int8_t)kp.octave;
+    s_x[i] = kp.x;
+  }
+  __syncthreads();
+
+  uint8_t* lp = s_patch + warp * 384;   // 11x11 left patch
+  uint8_t* rp = lp + 128;               // 11x21 right strip
+  for (int t = 0; t < kStPerCta / kStWarps; ++t) {
+    const int iL = chunk * kStPerCta + t * kStWarps + warp;
+    if (iL >= nL) break;
+    const size_t oi = (size_t)img * a.cap + iL;
+    if (lane == 0) { a.uRight[oi] = -1.f; a.depth[oi] = -1.f; a.sad[oi] = -1; }
+    const orbx_keypoint kl = kL[iL];
+    const int lvl = kl.octave;
+    const float uL = kl.x, vL = kl.y;
+    const int row = (int)vL;
+    const float minU = __fsub_rn(uL, a.maxD), maxU = uL;
+    if (maxU < 0) continue;
+    const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32));
+    const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32) + 1);
+    unsigned best = 100u << 16;                                                      // TH_HIGH
+    for (int iR = lane; iR < nR; iR += 32) {
+      if (row < s_min[iR] || row > s_max[iR]) continue;
+      const int oc = s_oct[iR];
+      if (oc < lvl - 1 || oc > lvl + 1) continue;
+      const float uR = s_x[iR];
+      if (uR >= minU && uR <= maxU) {
+        const unsigned d = (unsigned)hamming256(a0, a1, reinterpret_cast<const uint4*>(dR + (size_t)iR * 32));
+        best = min(best, (d << 16) | (unsigned)iR);
+      }
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if ((best >> 16) >= 75u) continue;                                               // (TH_HIGH+TH_LOW)/2
+    const int bestR = best & 0xFFFF;
+    const float uR0 = s_x[bestR];
+    const LevelGeom& gl = a.L.geom[lvl];
+    const LevelGeom& gr = a.R.geom[lvl];
+    const float inv = gl.inv_scale;
+    const float su = roundf(__fmul_rn(kl.x, inv)), sv = roundf(__fmul_rn(kl.y, inv)), sr = roundf(__fmul_rn(uR0, inv));
+    if (sr < 0.f || __fadd_rn(sr, 11.f) >= (float)gr.w) continue;                    // :573-575
+    const int cy = (int)sv, cxl = (int)su, cxr = (int)sr;
+    const uint8_t* pl = a.L.pyr + gl.plane_off + (size_t)slotL * gl.plane_stride + (size_t)(kEdge + cy - 5) * gl.pitch + kEdge + cxl - 5;
+    const uint8_t* pr = a.R.pyr + gr.plane_off + (size_t)slotR * gr.plane_stride + (size_t)(kEdge + cy - 5) * gr.pitch + kEdge + cxr - 10;
+    __syncwarp();
+    for (int idx = lane; idx < 121; idx += 32) { const int dy = idx / 11, dx = idx - dy * 11; lp[idx] = __ldg(pl + (size_t)dy * gl.pitch + dx); }
+    for (int idx = lane; idx < 231; idx += 32) { const int dy = idx / 21, dx = idx - dy * 21; rp[idx] = __ldg(pr + (size_t)dy * gr.pitch + dx); }
+    __syncwarp();
+    const int cl = lp[60];
+    int la[4], off[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int idx = lane + 32 * q;
+      const int dy = idx / 11, dx = idx - dy * 11;
+      la[q] = idx < 121 ? (int)lp[idx] - cl : 0;
+      off[q] = idx < 121 ? dy * 21 + dx + 5 : -1;
+    }
+    int bestSad = INT_MAX, bestInc = 0;
+    float dist[11];
+#pragma unroll
+    for (int inc = -5; inc <= 5; ++inc) {
+      const int cr = rp[5 * 21 + 10 + inc];
+      int s = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (off[q] >= 0) s += abs(la[q] - ((int)rp[off[q] + inc] - cr));
+      s = __reduce_add_sync(0xffffffffu, s);
+      if (s < bestSad) { bestSad = s; bestInc = inc; }
+      dist[inc + 5] = (float)s;
+    }
+    if (bestInc == -5 || bestInc == 5) continue;                                     // :594
+    float d1 = dist[0], d2 = dist[1], d3 = dist[2];
+#pragma unroll
+    for (int q = 1; q <= 9; ++q)
+      if (bestInc + 5 == q) { d1 = dist[q - 1]; d2 = dist[q]; d3 = dist[q + 1]; }
+    const float delta = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+    if (delta < -1.f || delta > 1.f) continue;
+    float bestu = __fmul_rn(gl.scale, __fadd_rn(__fadd_rn(sr, (float)bestInc), delta));
+    float disp = __fsub_rn(uL, bestu);
+    if (disp >= 0.f && disp < a.maxD) {
+      if (disp <= 0.f) { disp = 0.01f; bestu = (float)((double)uL - 0.01); }
+      if (lane == 0) { a.depth[oi] = __fdiv_rn(a.bf, disp); a.uRight[oi] = bestu; a.sad[oi] = bestSad; }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) k_stereo_median(StereoArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  int* vals = reinterpret_cast<int*>(smem);
+  __shared__ int s_cnt, s_med, s_kept;
+  const int img = blockIdx.x, tid = threadIdx.x;
+  const int nL = a.L.nkp[a.slotL0 + img];
+  const size_t base = (size_t)img * a.cap;
+  if (tid == 0) { s_cnt = 0; s_med = 0; s_kept = 0; }
+  __syncthreads();
+  for (int i = tid; i < nL; i += 256) {
+    const int s = a.sad[base + i];
+    if (s >= 0) vals[atomicAdd(&s_cnt, 1)] = s;
+  }
+  __syncthreads();
+  const int cnt = s_cnt;
+  if (cnt == 0) { if (tid == 0) a.nMatches[img] = 0; return; }   // the reference reads an empty vector here
+  const int k = cnt / 2;
+  for (int i = tid; i < cnt; i += 256) {
+    const int v = vals[i];
+    int lt = 0, le = 0;
+    for (int j = 0; j < cnt; ++j) { const int w = vals[j]; lt += w < v; le += w <= v; }
+    if (lt <= k && k < le) s_med = v;
+  }
+  __syncthreads();
+  const float th = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_med);
+  int kept = 0;
+  for (int i = tid; i < nL; i += 256) {
+    const int s = a.sad[base + i];
+    if (s < 0) continue;
+    if ((float)s < th) ++kept;
+    else { a.uRight[base + i] = -1.f; a.depth[base + i] = -1.f; }
+  }
+  atomicAdd(&s_kept, kept);
+  __syncthreads();
+  if (tid == 0) a.nMatches[img] = s_kept;
+}
+
+int launch_stereo(const StereoArgs& a, cudaStream_t st) {
+  const int capR = a.R.kp_cap, capL = a.L.kp_cap;
+  const int chunks = (capL + kStPerCta - 1) / kStPerCta;
+  const size_t smem1 = (size_t)capR * 8 + ((capR + 15) & ~15) + kStWarps * 384;
+  if (smem1 > 48 * 1024) cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
+  k_stereo_match<<<a.n * chunks, kStWarps * 32, smem1, st>>>(a, chunks);
+  const size_t smem2 = (size_t)capL * 4;
+  if (smem2 > 48 * 1024) cudaFuncSetAttribute(k_stereo_median, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+  k_stereo_median<<<a.n, 256, smem2, st>>>(a);
+  return 2;
+}
+
+}  // namespace orbx

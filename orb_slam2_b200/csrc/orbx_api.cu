@@ -1,0 +1,583 @@
+// Host side of the orbx C ABI (include/orbx.h): handle, geometry tables, launch orchestration.
+//
+// The arithmetic in make_tables()/configure() follows the reference's constructor and level
+// set-up to the letter, because quotas, level sizes and resize weights feed bit-exact kernels:
+//   scale/sigma tables, quotas, umax   src/ORBextractor.cc:410-470
+//   level sizes                         src/ORBextractor.cc:1111-1112
+//   FAST cell grid                      src/ORBextractor.cc:773-787
+//   quad-tree roots                     src/ORBextractor.cc:543-563
+//   cv::resize tap weights              OpenCV resize.cpp (INTER_LINEAR, 8-bit): see DESIGN.md
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "orbx_internal.h"
+
+using namespace orbx;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<unsigned long long> g_launches{0};
+
+orbx_status fail(orbx_status s, const std::string& msg) { g_err = msg; return s; }
+
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(ORBX_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));     \
+  } while (0)
+
+const int8_t kPattern[1024] = {
+#include "brief_pattern.inc"
+};
+
+inline int cv_round(double v) { return (int)std::lrint(v); }
+inline int cv_round(float v) { return (int)std::lrintf(v); }
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Totals {
+  size_t pyr_bytes = 0;
+  int cells = 0, pool = 0, lvlkp = 0, taps = 0, win_w = 0, win_h = 0, node_cap = 0;
+};
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+struct orbx_extractor {
+  orbx_params P{};
+  int device = 0, max_w = 0, max_h = 0, max_batch = 0, nlevels = 0;
+  float scale[kMaxLevels], inv[kMaxLevels], sigma2[kMaxLevels], invsigma2[kMaxLevels];
+  int quota[kMaxLevels];
+  int umax[kHalfPatch + 1];
+  int kp_cap = 0;
+  // geometry of the image size currently configured
+  int cur_w = 0, cur_h = 0;
+  LevelGeom hg[kMaxLevels];
+  Totals cur, capy;
+  std::vector<ResizeTap> htaps;
+  DeviceLayout L{};
+  // device arenas
+  LevelGeom* d_geom = nullptr; ResizeTap* d_taps = nullptr; int* d_umax = nullptr; char4* d_pattern = nullptr;
+  uint8_t* d_in = nullptr;
+  float* d_uright = nullptr; float* d_depth = nullptr; int* d_sad = nullptr; int* d_nmatch = nullptr;
+  int slots_valid = 0;
+};
+
+namespace {
+
+void make_tables(orbx_extractor* e) {
+  const int nl = e->nlevels;
+  const double sf = (double)e->P.scale_factor;   // the reference keeps scaleFactor as double (ORBextractor.h:101)
+  e->scale[0] = 1.0f; e->sigma2[0] = 1.0f;
+  for (int i = 1; i < nl; ++i) {
+    e->scale[i] = (float)(e->scale[i - 1] * sf);
+    e->sigma2[i] = e->scale[i] * e->scale[i];
+  }
+  for (int i = 0; i < nl; ++i) { e->inv[i] = 1.0f / e->scale[i]; e->invsigma2[i] = 1.0f / e->sigma2[i]; }
+  const float factor = (float)(1.0f / sf);
+  float want = e->P.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+  int sum = 0;
+  for (int l = 0; l < nl - 1; ++l) {
+    e->quota[l] = cv_round(want);
+    sum += e->quota[l];
+    want *= factor;
+  }
+  e->quota[nl - 1] = std::max(e->P.nfeatures - sum, 0);
+  const int vmax = (int)std::floor(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+  const int vmin = (int)std::ceil(kHalfPatch * std::sqrt(2.f) / 2);
+  const double r2 = kHalfPatch * kHalfPatch;
+  for (int v = 0; v <= vmax; ++v) e->umax[v] = cv_round(std::sqrt(r2 - v * v));
+  for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+    while (e->umax[v0] == e->umax[v0 + 1]) ++v0;
+    e->umax[v] = v0;
+    ++v0;
+  }
+}
+
+void resize_taps(int dn, int sn, ResizeTap* out) {
+  const double inv = (double)dn / sn, sc = 1.0 / inv;
+  for (int d = 0; d < dn; ++d) {
+    float f = (float)((d + 0.5) * sc - 0.5);
+    int s = (int)std::floor(f);
+    f -= s;
+    if (s < 0) { s = 0; f = 0.f; }
+    if (s >= sn - 1) { s = sn - 1; f = 0.f; }
+    out[d].ofs = s;
+    out[d].a0 = (short)cv_round((1.f - f) * 2048.f);
+    out[d].a1 = (short)cv_round(f * 2048.f);
+  }
+}
+
+// Level geometry for a w x h image.  nslots fixes the per-level plane arrays.
+orbx_status geometry(const orbx_extractor* e, int w, int h, int nslots, LevelGeom* g, Totals* t,
+                     std::vector<ResizeTap>* taps) {
+  *t = Totals();
+  if (taps) taps->clear();
+  size_t pyr_off = 0;
+  for (int l = 0; l < e->nlevels; ++l) {
+    LevelGeom& q = g[l];
+    std::memset(&q, 0, sizeof(q));
+    q.w = cv_round((float)w * e->inv[l]);
+    q.h = cv_round((float)h * e->inv[l]);
+    if (q.w < 2 * kFastBorder + 30 || q.h < 2 * kFastBorder + 30)
+      return fail(ORBX_ERR_GEOMETRY, "pyramid level " + std::to_string(l) + " is smaller than 62 px");
+    q.pitch = (int)align_up(q.w + 2 * kEdge, 16);
+    q.rows = q.h + 2 * kEdge;
+    q.plane_stride = align_up((size_t)q.pitch * q.rows, 256);
+    q.plane_off = pyr_off;
+    pyr_off += q.plane_stride * nslots;
+    if (l > 0) {
+      q.xtab_off = t->taps; q.ytab_off = t->taps + q.w;
+      t->taps += q.w + q.h;
+      if (taps) {
+        taps->resize(t->taps);
+        resize_taps(q.w, g[l - 1].w, taps->data() + q.xtab_off);
+        resize_taps(q.h, g[l - 1].h, taps->data() + q.ytab_off);
+      }
+    }
+    // FAST cells
+    q.maxBX = q.w - kEdge + 3; q.maxBY = q.h - kEdge + 3;
+    const float width = (float)(q.maxBX - kFastBorder), height = (float)(q.maxBY - kFastBorder);
+    q.nCols = (int)(width / 30.f); q.nRows = (int)(height / 30.f);
+    q.wCell = (int)std::ceil(width / q.nCols); q.hCell = (int)std::ceil(height / q.nRows);
+    q.cell_base = t->cells;
+    t->cells += q.nCols * q.nRows;
+    t->win_w = std::max(t->win_w, q.wCell + 6); t->win_h = std::max(t->win_h, q.hCell + 6);
+    // candidate pool bound: kept corners are strict 3x3 maxima, at most ceil(iw/2)*ceil(ih/2) per cell
+    long long cap = 0;
+    for (int i = 0; i < q.nRows; ++i)
+      for (int j = 0; j < q.nCols; ++j) {
+        const int x0 = kFastBorder + j * q.wCell, y0 = kFastBorder + i * q.hCell;
+        if (y0 >= q.maxBY - 3 || x0 >= q.maxBX - 6) continue;
+        const int ww = std::min(x0 + q.wCell + 6, q.maxBX) - x0, hh = std::min(y0 + q.hCell + 6, q.maxBY) - y0;
+        if (ww < 7 || hh < 7) continue;
+        cap += (long long)((ww - 6 + 1) / 2) * ((hh - 6 + 1) / 2);
+      }
+    if (cap >= (1 << 24)) return fail(ORBX_ERR_GEOMETRY, "level too large for 24-bit candidate indices");
+    q.cand_cap = (int)align_up((size_t)cap + 1, 4);
+    q.cand_off = t->pool;
+    t->pool += q.cand_cap;
+    // quad-tree
+    q.quota = e->quota[l];
+    q.treeW = q.maxBX - kFastBorder; q.treeH = q.maxBY - kFastBorder;
+    q.nIni = (int)std::round((float)q.treeW / q.treeH);
+    if (q.nIni < 1 || q.nIni > kMaxRoots)
+      return fail(ORBX_ERR_GEOMETRY, "aspect ratio outside [0.5, 16.5): round(W/H) must be 1..16");
+    q.hX = (float)q.treeW / q.nIni;
+    for (int i = 0; i < q.nIni; ++i) { q.root_x0[i] = (int)(q.hX * (float)i); q.root_x1[i] = (int)(q.hX * (float)(i + 1)); }
+    q.node_cap = std::max(q.quota + 3, 4 * q.nIni) + 1;
+    t->node_cap = std::max(t->node_cap, q.node_cap);
+    q.lvl_kp_off = t->lvlkp;
+    t->lvlkp += std::max(q.quota + 3, 4 * kMaxRoots);
+    q.scale = e->scale[l]; q.inv_scale = e->inv[l];
+    q.patch_size = (int)(31 * e->scale[l]);
+  }
+  t->pyr_bytes = pyr_off;
+  t->node_cap = (int)align_up(t->node_cap, 32);
+  return ORBX_OK;
+}
+
+orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
+  if (w == e->cur_w && h == e->cur_h) return ORBX_OK;
+  if (w > e->max_w || h > e->max_h) return fail(ORBX_ERR_CAPACITY, "image larger than max_w x max_h given at create");
+  LevelGeom g[kMaxLevels];
+  Totals t;
+  std::vector<ResizeTap> taps;
+  orbx_status s = geometry(e, w, h, e->max_batch, g, &t, &taps);
+  if (s != ORBX_OK) return s;
+  if (t.pyr_bytes > e->capy.pyr_bytes || t.cells > e->capy.cells || t.pool > e->capy.pool || t.taps > e->capy.taps ||
+      t.lvlkp > e->capy.lvlkp || t.node_cap > e->capy.node_cap || t.win_w > e->capy.win_w || t.win_h > e->capy.win_h)
+    return fail(ORBX_ERR_CAPACITY, "image geometry needs more device memory than reserved at create");
+  // the previous geometry may still be in use by kernels queued on another stream
+  CU(cudaDeviceSynchronize());
+  std::memcpy(e->hg, g, sizeof(g));
+  e->cur = t;
+  e->htaps = taps;
+  CU(cudaMemcpyAsync(e->d_geom, e->hg, sizeof(LevelGeom) * e->nlevels, cudaMemcpyHostToDevice, st));
+  if (!taps.empty()) CU(cudaMemcpyAsync(e->d_taps, e->htaps.data(), sizeof(ResizeTap) * taps.size(), cudaMemcpyHostToDevice, st));
+  CU(cudaStreamSynchronize(st));
+  e->cur_w = w; e->cur_h = h;
+  e->L.cells_per_slot = t.cells; e->L.pool_per_slot = t.pool; e->L.lvlkp_per_slot = t.lvlkp;   // all <= reserved capacity
+  e->slots_valid = 0;
+  return ORBX_OK;
+}
+
+template <typename T>
+orbx_status dev_alloc(T** p, size_t count) {
+  CU(cudaMalloc((void**)p, std::max<size_t>(count, 1) * sizeof(T)));
+  return ORBX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+orbx_status orbx_extractor_create(const orbx_params* params, int max_w, int max_h, int max_batch, int device,
+                                  orbx_extractor** out) {
+  if (!params || !out) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  *out = nullptr;
+  if (params->nlevels < 1 || params->nlevels > kMaxLevels) return fail(ORBX_ERR_BAD_ARG, "nlevels must be 1..8");
+  if (params->nfeatures < 1 || params->nfeatures > 30000) return fail(ORBX_ERR_BAD_ARG, "nfeatures must be 1..30000");
+  if (!(params->scale_factor > 1.0f) || params->scale_factor > 4.0f) return fail(ORBX_ERR_BAD_ARG, "scale_factor must be in (1, 4]");
+  if (params->ini_th_fast < 1 || params->ini_th_fast > 254 || params->min_th_fast < 1 || params->min_th_fast > 254)
+    return fail(ORBX_ERR_BAD_ARG, "FAST thresholds must be in [1, 254]");
+  if (max_w < 1 || max_h < 1 || max_w > kMaxDim + 1 || max_h > kMaxDim + 1) return fail(ORBX_ERR_BAD_ARG, "max_w/max_h must be 1..4096");
+  if (max_batch < 1) return fail(ORBX_ERR_BAD_ARG, "max_batch must be >= 1");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(ORBX_ERR_CUDA, "no CUDA device: orbx has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(ORBX_ERR_BAD_ARG, "device index out of range");
+  DeviceGuard guard(device);
+
+  orbx_extractor* e = new orbx_extractor();
+  e->P = *params; e->device = device; e->max_w = max_w; e->max_h = max_h; e->max_batch = max_batch;
+  e->nlevels = params->nlevels;
+  make_tables(e);
+  LevelGeom g[kMaxLevels];
+  orbx_status s = geometry(e, max_w, max_h, max_batch, g, &e->capy, nullptr);
+  if (s != ORBX_OK) { delete e; return s; }
+  if (e->capy.node_cap > 3072) { delete e; return fail(ORBX_ERR_CAPACITY, "per-level feature quota too large for the quad-tree kernel (node_cap > 3072)"); }
+  e->capy.win_w = e->capy.win_h = 66;   // a FAST cell is at most 60 px wide/high (+6 rim) for any smaller image
+  e->kp_cap = e->capy.lvlkp;
+  if (e->kp_cap > 65535) { delete e; return fail(ORBX_ERR_CAPACITY, "more than 65535 keypoints per image"); }
+
+  DeviceLayout& L = e->L;
+  L.nlevels = e->nlevels; L.nslots = max_batch;
+  L.cells_per_slot = e->capy.cells; L.pool_per_slot = e->capy.pool; L.lvlkp_per_slot = e->capy.lvlkp; L.kp_cap = e->kp_cap;
+  L.ini_th = params->ini_th_fast; L.min_th = params->min_th_fast;
+  const size_t nb = (size_t)max_batch;
+#define ALLOC(ptr, count) do { s = dev_alloc(&(ptr), (count)); if (s != ORBX_OK) { orbx_extractor_destroy(e); return s; } } while (0)
+  ALLOC(e->d_geom, kMaxLevels);
+  ALLOC(e->d_taps, (size_t)e->capy.taps);
+  ALLOC(e->d_umax, kHalfPatch + 1);
+  ALLOC(e->d_pattern, 256);
+  ALLOC(e->d_in, nb * max_w * max_h);
+  ALLOC(L.pyr, e->capy.pyr_bytes);
+  ALLOC(L.celltab, nb * e->capy.cells);
+  ALLOC(L.poolcnt, nb * kMaxLevels);
+  ALLOC(L.pool, nb * e->capy.pool);
+  ALLOC(L.okeys, nb * e->capy.pool);
+  ALLOC(L.knode, nb * e->capy.pool);
+  ALLOC(L.lvlkp, nb * e->capy.lvlkp);
+  ALLOC(L.lvlcnt, nb * kMaxLevels);
+  ALLOC(L.nkeys, nb * kMaxLevels);
+  ALLOC(L.kps, nb * e->kp_cap);
+  ALLOC(L.desc, nb * e->kp_cap * 32);
+  ALLOC(L.nkp, nb);
+  ALLOC(L.err, nb);
+  ALLOC(e->d_uright, nb * e->kp_cap);
+  ALLOC(e->d_depth, nb * e->kp_cap);
+  ALLOC(e->d_sad, nb * e->kp_cap);
+  ALLOC(e->d_nmatch, nb);
+#undef ALLOC
+  L.geom = e->d_geom; L.taps = e->d_taps;
+  cudaError_t ce = cudaMemcpy(e->d_umax, e->umax, sizeof(e->umax), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaMemcpy(e->d_pattern, kPattern, 1024, cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaMemset(L.nkp, 0, nb * sizeof(int));
+  if (ce == cudaSuccess) ce = cudaMemset(L.pyr, 0, e->capy.pyr_bytes);
+  if (ce != cudaSuccess) { orbx_extractor_destroy(e); return fail(ORBX_ERR_CUDA, cudaGetErrorString(ce)); }
+  *out = e;
+  return ORBX_OK;
+}
+
+void orbx_extractor_destroy(orbx_extractor* e) {
+  if (!e) return;
+  DeviceGuard guard(e->device);
+  cudaDeviceSynchronize();
+  DeviceLayout& L = e->L;
+  void* ptrs[] = {e->d_geom, e->d_taps, e->d_umax, e->d_pattern, e->d_in, L.pyr, L.celltab, L.poolcnt, L.pool, L.okeys,
+                  L.knode, L.lvlkp, L.lvlcnt, L.nkeys, L.kps, L.desc, L.nkp, L.err, e->d_uright, e->d_depth, e->d_sad,
+                  e->d_nmatch};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  delete e;
+}
+
+orbx_status orbx_get_tables(const orbx_extractor* e, int* nlevels, float* scale, float* inv_scale, float* sigma2,
+                            float* inv_sigma2, int* quota) {
+  if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
+  if (nlevels) *nlevels = e->nlevels;
+  for (int i = 0; i < e->nlevels; ++i) {
+    if (scale) scale[i] = e->scale[i];
+    if (inv_scale) inv_scale[i] = e->inv[i];
+    if (sigma2) sigma2[i] = e->sigma2[i];
+    if (inv_sigma2) inv_sigma2[i] = e->invsigma2[i];
+    if (quota) quota[i] = e->quota[i];
+  }
+  return ORBX_OK;
+}
+
+int orbx_max_keypoints(const orbx_extractor* e) { return e ? e->kp_cap : 0; }
+
+orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, int w, int h, int stride,
+                               size_t image_stride, int src_on_device, int first_slot, void* stream) {
+  if (!e || !imgs) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n < 1 || w < 1 || h < 1 || stride < w) return fail(ORBX_ERR_BAD_ARG, "bad image size or stride");
+  if (first_slot < 0 || first_slot + n > e->max_batch) return fail(ORBX_ERR_CAPACITY, "slots exceed max_batch");
+  cudaStream_t st = (cudaStream_t)stream;
+  DeviceGuard guard(e->device);
+  orbx_status s = configure(e, w, h, st);
+  if (s != ORBX_OK) return s;
+  const uint8_t* src = imgs;
+  int src_pitch = stride;
+  size_t src_istride = image_stride;
+  if (!src_on_device) {
+    uint8_t* dst = e->d_in + (size_t)first_slot * w * h;
+    if (stride == w && image_stride == (size_t)w * h) {
+      CU(cudaMemcpyAsync(dst, imgs, (size_t)n * w * h, cudaMemcpyHostToDevice, st));
+    } else {
+      for (int i = 0; i < n; ++i)
+        CU(cudaMemcpy2DAsync(dst + (size_t)i * w * h, w, imgs + (size_t)i * image_stride, stride, w, h, cudaMemcpyHostToDevice, st));
+    }
+    src = dst; src_pitch = w; src_istride = (size_t)w * h;
+  }
+  CU(cudaMemsetAsync(e->L.poolcnt + (size_t)first_slot * kMaxLevels, 0, (size_t)n * kMaxLevels * sizeof(int), st));
+  int launches = 0;
+  launches += launch_pyramid(e->L, e->hg, src, src_pitch, src_istride, first_slot, n, st);
+  launches += launch_fast(e->L, e->hg, first_slot, n, e->cur.win_w, e->cur.win_h, st);
+  launches += launch_octree(e->L, first_slot, n, e->cur.node_cap, st);
+  launches += launch_describe(e->L, first_slot, n, e->d_umax, e->d_pattern, st);
+  g_launches += launches;
+  CU(cudaGetLastError());
+  e->slots_valid = std::max(e->slots_valid, first_slot + n);
+  return ORBX_OK;
+}
+
+orbx_status orbx_fetch_results(orbx_extractor* e, int first_slot, int n, orbx_keypoint* kps, uint8_t* desc, int* counts,
+                               int cap, int dst_on_device, void* stream) {
+  if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
+  if (n < 1 || first_slot < 0 || first_slot + n > e->max_batch) return fail(ORBX_ERR_CAPACITY, "slots exceed max_batch");
+  if ((kps || desc) && cap < e->kp_cap) return fail(ORBX_ERR_CAPACITY, "cap smaller than orbx_max_keypoints()");
+  cudaStream_t st = (cudaStream_t)stream;
+  DeviceGuard guard(e->device);
+  const cudaMemcpyKind kind = dst_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  const size_t kc = (size_t)e->kp_cap;
+  if (counts) CU(cudaMemcpyAsync(counts, e->L.nkp + first_slot, (size_t)n * sizeof(int), kind, st));
+  if (kps) CU(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_keypoint), e->L.kps + first_slot * kc, kc * sizeof(orbx_keypoint),
+                                kc * sizeof(orbx_keypoint), n, kind, st));
+  if (desc) CU(cudaMemcpy2DAsync(desc, (size_t)cap * 32, e->L.desc + first_slot * kc * 32, kc * 32, kc * 32, n, kind, st));
+  return ORBX_OK;
+}
+
+orbx_status orbx_extract(orbx_extractor* e, const uint8_t* img, int w, int h, int stride, orbx_keypoint* kps, uint8_t* desc,
+                         int cap, int* n, void* stream) {
+  if (!e || !n) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  *n = 0;
+  if (!img || w <= 0 || h <= 0) return ORBX_OK;   // empty image: silent return, src/ORBextractor.cc:1046
+  if (!kps || !desc) return fail(ORBX_ERR_BAD_ARG, "null output buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  DeviceGuard guard(e->device);
+  orbx_status s = orbx_extract_batch(e, img, 1, w, h, stride, (size_t)stride * h, 0, 0, stream);
+  if (s != ORBX_OK) return s;
+  int count = 0;
+  CU(cudaMemcpyAsync(&count, e->L.nkp, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (count > cap) return fail(ORBX_ERR_CAPACITY, "keypoint buffer too small: need " + std::to_string(count));
+  if (count) {
+    CU(cudaMemcpyAsync(kps, e->L.kps, (size_t)count * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(desc, e->L.desc, (size_t)count * 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  *n = count;
+  return ORBX_OK;
+}
+
+orbx_status orbx_pyramid_level(const orbx_extractor* e, int slot, int level, const uint8_t** dev_ptr, int* w, int* h, int* stride) {
+  if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
+  if (e->cur_w == 0) return fail(ORBX_ERR_STATE, "no image extracted yet");
+  if (slot < 0 || slot >= e->max_batch || level < 0 || level >= e->nlevels) return fail(ORBX_ERR_BAD_ARG, "slot/level out of range");
+  const LevelGeom& g = e->hg[level];
+  if (dev_ptr) *dev_ptr = e->L.pyr + g.plane_off + (size_t)slot * g.plane_stride + (size_t)kEdge * g.pitch + kEdge;
+  if (w) *w = g.w;
+  if (h) *h = g.h;
+  if (stride) *stride = g.pitch;
+  return ORBX_OK;
+}
+
+orbx_status orbx_download_level(orbx_extractor* e, int slot, int level, uint8_t* dst) {
+  if (!e || !dst) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (e->cur_w == 0) return fail(ORBX_ERR_STATE, "no image extracted yet");
+  if (slot < 0 || slot >= e->max_batch || level < 0 || level >= e->nlevels) return fail(ORBX_ERR_BAD_ARG, "slot/level out of range");
+  DeviceGuard guard(e->device);
+  const LevelGeom& g = e->hg[level];
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy2D(dst, g.w + 2 * kEdge, e->L.pyr + g.plane_off + (size_t)slot * g.plane_stride, g.pitch, g.w + 2 * kEdge, g.rows,
+                  cudaMemcpyDeviceToHost));
+  return ORBX_OK;
+}
+
+orbx_status orbx_debug_candidates(orbx_extractor* e, int slot, int level, uint32_t* out, int cap, int* n) {
+  if (!e || !out || !n) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (e->cur_w == 0) return fail(ORBX_ERR_STATE, "no image extracted yet");
+  if (slot < 0 || slot >= e->max_batch || level < 0 || level >= e->nlevels) return fail(ORBX_ERR_BAD_ARG, "slot/level out of range");
+  DeviceGuard guard(e->device);
+  CU(cudaDeviceSynchronize());
+  int cnt = 0;
+  CU(cudaMemcpy(&cnt, e->L.nkeys + slot * kMaxLevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+  *n = cnt;
+  const int m = std::min(cnt, cap);
+  if (m > 0) CU(cudaMemcpy(out, e->L.okeys + (size_t)slot * e->L.pool_per_slot + e->hg[level].cand_off, (size_t)m * 4, cudaMemcpyDeviceToHost));
+  return ORBX_OK;
+}
+
+orbx_status orbx_debug_level_keys(orbx_extractor* e, int slot, int level, uint32_t* out, int cap, int* n) {
+  if (!e || !out || !n) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (e->cur_w == 0) return fail(ORBX_ERR_STATE, "no image extracted yet");
+  if (slot < 0 || slot >= e->max_batch || level < 0 || level >= e->nlevels) return fail(ORBX_ERR_BAD_ARG, "slot/level out of range");
+  DeviceGuard guard(e->device);
+  CU(cudaDeviceSynchronize());
+  int cnt = 0;
+  CU(cudaMemcpy(&cnt, e->L.lvlcnt + slot * kMaxLevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+  *n = cnt;
+  const int m = std::min(cnt, cap);
+  if (m > 0) CU(cudaMemcpy(out, e->L.lvlkp + (size_t)slot * e->L.lvlkp_per_slot + e->hg[level].lvl_kp_off, (size_t)m * 4, cudaMemcpyDeviceToHost));
+  return ORBX_OK;
+}
+
+orbx_status orbx_stereo_match_batch(orbx_extractor* eL, int slotL0, orbx_extractor* eR, int slotR0, int n, float bf, float fx,
+                                    float* u_right, float* depth, int* n_matches, int cap, int dst_on_device, void* stream) {
+  if (!eL || !eR) return fail(ORBX_ERR_BAD_ARG, "null extractor");
+  if (n < 1 || slotL0 < 0 || slotR0 < 0 || slotL0 + n > eL->max_batch || slotR0 + n > eR->max_batch)
+    return fail(ORBX_ERR_CAPACITY, "slots exceed max_batch");
+  if (eL->cur_w == 0 || eR->cur_w == 0 || slotL0 + n > eL->slots_valid || slotR0 + n > eR->slots_valid)
+    return fail(ORBX_ERR_STATE, "stereo matching needs a preceding extract on those slots");
+  if (eL->cur_w != eR->cur_w || eL->cur_h != eR->cur_h || eL->nlevels != eR->nlevels || eL->device != eR->device)
+    return fail(ORBX_ERR_BAD_ARG, "left and right extractor differ in image size, levels or device");
+  if (!(bf > 0.f) || !(fx > 0.f)) return fail(ORBX_ERR_BAD_ARG, "bf and fx must be positive");
+  if ((u_right || depth) && cap < eL->kp_cap) return fail(ORBX_ERR_CAPACITY, "cap smaller than orbx_max_keypoints()");
+  cudaStream_t st = (cudaStream_t)stream;
+  DeviceGuard guard(eL->device);
+  StereoArgs a;
+  a.L = eL->L; a.R = eR->L; a.slotL0 = slotL0; a.slotR0 = slotR0; a.n = n;
+  a.bf = bf;
+  const float mb = bf / fx;     // Frame::mb (hazard H4)
+  a.maxD = bf / mb;             // src/Frame.cc:498
+  const bool direct = dst_on_device && u_right && depth && n_matches;
+  a.uRight = direct ? u_right : eL->d_uright;
+  a.depth = direct ? depth : eL->d_depth;
+  a.nMatches = direct ? n_matches : eL->d_nmatch;
+  a.sad = eL->d_sad;
+  a.cap = direct ? cap : eL->kp_cap;
+  g_launches += launch_stereo(a, st);
+  CU(cudaGetLastError());
+  if (!direct) {
+    const cudaMemcpyKind kind = dst_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    const size_t kc = (size_t)eL->kp_cap;
+    if (u_right) CU(cudaMemcpy2DAsync(u_right, (size_t)cap * 4, eL->d_uright, kc * 4, kc * 4, n, kind, st));
+    if (depth) CU(cudaMemcpy2DAsync(depth, (size_t)cap * 4, eL->d_depth, kc * 4, kc * 4, n, kind, st));
+    if (n_matches) CU(cudaMemcpyAsync(n_matches, eL->d_nmatch, (size_t)n * sizeof(int), kind, st));
+  }
+  return ORBX_OK;
+}
+
+int orbx_hamming256(const uint8_t* a, const uint8_t* b) {
+  int d = 0;
+  for (int i = 0; i < 4; ++i) {
+    unsigned long long u, v;
+    std::memcpy(&u, a + 8 * i, 8);
+    std::memcpy(&v, b + 8 * i, 8);
+    d += __builtin_popcountll(u ^ v);
+  }
+  return d;
+}
+
+}  // extern "C"
+
+// Stages host arrays through stream-ordered device allocations when on_device == 0.
+namespace {
+struct Staged {
+  cudaStream_t st;
+  std::vector<void*> bufs;
+  explicit Staged(cudaStream_t s) : st(s) {}
+  ~Staged() { for (void* p : bufs) cudaFreeAsync(p, st); }
+  cudaError_t alloc(void** p, size_t bytes) {
+    cudaError_t e = cudaMallocAsync(p, std::max<size_t>(bytes, 16), st);
+    if (e == cudaSuccess) bufs.push_back(*p);
+    return e;
+  }
+  template <typename T>
+  cudaError_t in(const T* host, size_t count, int on_device, const T** out) {
+    if (on_device) { *out = host; return cudaSuccess; }
+    void* d = nullptr;
+    cudaError_t e = alloc(&d, count * sizeof(T));
+    if (e != cudaSuccess) return e;
+    *out = (const T*)d;
+    return cudaMemcpyAsync(d, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
+  }
+};
+}  // namespace
+
+extern "C" {
+
+orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const int* n1, const orbx_keypoint* kps2,
+                                   const uint8_t* desc2, const int* n2, int n_pairs, int cap, int cols, int rows, float* prev_xy,
+                                   float nnratio, int window, int check_orientation, int* matches12, int* n_matches,
+                                   int on_device, void* stream) {
+  if (!kps1 || !desc1 || !n1 || !kps2 || !desc2 || !n2 || !prev_xy || !matches12 || !n_matches)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_pairs < 1 || cap < 1 || cap > 65535 || cols < 1 || rows < 1 || window < 0) return fail(ORBX_ERR_BAD_ARG, "bad sizes");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_pairs, pc = np * cap;
+  InitMatchArgs a;
+  CU(sg.in(kps1, pc, on_device, &a.k1)); CU(sg.in(desc1, pc * 32, on_device, &a.d1)); CU(sg.in(n1, np, on_device, &a.n1));
+  CU(sg.in(kps2, pc, on_device, &a.k2)); CU(sg.in(desc2, pc * 32, on_device, &a.d2)); CU(sg.in(n2, np, on_device, &a.n2));
+  const float* prev_in = nullptr;
+  CU(sg.in((const float*)prev_xy, pc * 2, on_device, &prev_in));
+  a.prev = const_cast<float*>(prev_in);
+  if (on_device) { a.m12 = matches12; a.nm = n_matches; }
+  else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
+  CU(sg.alloc((void**)&a.scratch, pc * 4 * sizeof(int)));
+  a.n_pairs = n_pairs; a.cap = cap;
+  a.invW = 64.0f / (float)cols; a.invH = 48.0f / (float)rows;   // src/Frame.cc:212-213 (mnMinX = 0, mnMaxX = cols)
+  a.ratio = nnratio; a.window = (float)window; a.checkOri = check_orientation;
+  g_launches += launch_search_init(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(prev_xy, a.prev, pc * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
+orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const int* nA, const uint8_t* descB, const float* angB,
+                                 const int* nB, int n_pairs, int cap, int th, float nnratio, int check_orientation, int strict_lt,
+                                 int* matches12, int* n_matches, int on_device, void* stream) {
+  if (!descA || !angA || !nA || !descB || !angB || !nB || !matches12 || !n_matches) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_pairs < 1 || cap < 1 || cap > 6000) return fail(ORBX_ERR_BAD_ARG, "cap must be 1..6000 (B descriptors are held in shared memory)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_pairs, pc = np * cap;
+  KnnArgs a;
+  CU(sg.in(descA, pc * 32, on_device, &a.dA)); CU(sg.in(angA, pc, on_device, &a.angA)); CU(sg.in(nA, np, on_device, &a.nA));
+  CU(sg.in(descB, pc * 32, on_device, &a.dB)); CU(sg.in(angB, pc, on_device, &a.angB)); CU(sg.in(nB, np, on_device, &a.nB));
+  if (on_device) { a.m12 = matches12; a.nm = n_matches; }
+  else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
+  CU(sg.alloc((void**)&a.scratch, pc * sizeof(int)));
+  a.n_pairs = n_pairs; a.cap = cap; a.th = th; a.ratio = nnratio; a.checkOri = check_orientation; a.strict = strict_lt;
+  g_launches += launch_knn_ratio(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
+const char* orbx_last_error_string(void) { return g_err.c_str(); }
+unsigned long long orbx_kernel_launch_count(void) { return g_launches.load(); }
+const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
+
+}  // extern "C"

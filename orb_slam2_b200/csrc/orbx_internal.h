@@ -1,0 +1,107 @@
+// Internal definitions shared by the orbx kernels and the C-ABI host code.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/orbx.h"
+
+namespace orbx {
+
+constexpr int kEdge = 19;          // EDGE_THRESHOLD, src/ORBextractor.cc:74
+constexpr int kFastBorder = 16;    // EDGE_THRESHOLD-3, src/ORBextractor.cc:773
+constexpr int kHalfPatch = 15;     // HALF_PATCH_SIZE
+constexpr int kMaxLevels = 8;
+constexpr int kMaxRoots = 16;
+constexpr int kMaxDim = 4095;      // x,y are packed in 12 bits
+
+// packed candidate / level keypoint: x | y<<12 | response<<24 (response = FAST score, 1..254)
+__host__ __device__ inline uint32_t pack_xyr(int x, int y, int r) { return (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)r << 24); }
+__host__ __device__ inline int unpack_x(uint32_t p) { return p & 0xFFF; }
+__host__ __device__ inline int unpack_y(uint32_t p) { return (p >> 12) & 0xFFF; }
+__host__ __device__ inline int unpack_r(uint32_t p) { return p >> 24; }
+
+struct ResizeTap {  // one destination coordinate of cv::resize INTER_LINEAR
+  int ofs;          // source index of the first tap
+  short a0, a1;     // 11-bit fixed-point weights of taps ofs, ofs+1
+};
+
+struct LevelGeom {
+  int w, h;              // level (ROI) size
+  int pitch, rows;       // bordered plane: pitch bytes per row (multiple of 16), rows = h + 38
+  size_t plane_off;      // byte offset of slot 0's plane of this level inside the pyramid arena
+  size_t plane_stride;   // bytes between consecutive slots' planes of this level
+  int xtab_off, ytab_off;  // offsets (in ResizeTap) of this level's resize tables
+  // FAST cell grid (src/ORBextractor.cc:773-806)
+  int maxBX, maxBY, nCols, nRows, wCell, hCell;
+  int cell_base;         // index of this level's first cell in the per-slot cell table
+  int cand_off, cand_cap;  // this level's segment of the per-slot candidate pool
+  // quad-tree (src/ORBextractor.cc:539-563)
+  int quota, nIni, treeW, treeH, node_cap, lvl_kp_off;
+  float hX;
+  int root_x0[kMaxRoots], root_x1[kMaxRoots];
+  float scale, inv_scale;
+  int patch_size;
+};
+
+struct DeviceLayout {    // per-handle pointers handed to kernels by value
+  int nlevels, nslots;
+  int cells_per_slot, pool_per_slot, lvlkp_per_slot, kp_cap;
+  int ini_th, min_th;
+  const LevelGeom* geom;     // [nlevels]
+  const ResizeTap* taps;
+  uint8_t* pyr;
+  uint2* celltab;            // [nslots][cells_per_slot] {pool offset, count}
+  int* poolcnt;              // [nslots][kMaxLevels]
+  uint32_t* pool;            // [nslots][pool_per_slot]
+  uint32_t* okeys;           // [nslots][pool_per_slot] candidates in reference order
+  uint16_t* knode;           // [nslots][pool_per_slot]
+  uint32_t* lvlkp;           // [nslots][lvlkp_per_slot] post-quad-tree keypoints, level coords
+  int* lvlcnt;               // [nslots][kMaxLevels]
+  int* nkeys;                // [nslots][kMaxLevels] ordered candidate count
+  orbx_keypoint* kps;        // [nslots][kp_cap]
+  uint8_t* desc;             // [nslots][kp_cap][32]
+  int* nkp;                  // [nslots]
+  int* err;                  // [nslots]
+};
+
+__host__ __device__ inline int reflect101(int i, int n) {
+  if (i < 0) i = -i;
+  if (i >= n) i = 2 * n - 2 - i;
+  return i;
+}
+
+// kernel launchers (each returns the number of kernel launches it made)
+int launch_pyramid(const DeviceLayout& L, const LevelGeom* hgeom, const uint8_t* src, int src_pitch,
+                   size_t src_img_stride, int first_slot, int n, cudaStream_t st);
+int launch_fast(const DeviceLayout& L, const LevelGeom* hgeom, int first_slot, int n, int win_w, int win_h, cudaStream_t st);
+int launch_octree(const DeviceLayout& L, int first_slot, int n, int node_cap, cudaStream_t st);
+int launch_describe(const DeviceLayout& L, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st);
+
+struct StereoArgs {
+  DeviceLayout L, R;
+  int slotL0, slotR0, n;
+  float bf, maxD;
+  float* uRight; float* depth; int* nMatches; int* sad;  // device, [n][cap]
+  int cap;
+};
+int launch_stereo(const StereoArgs& a, cudaStream_t st);
+
+struct InitMatchArgs {
+  const orbx_keypoint* k1; const uint8_t* d1; const int* n1;
+  const orbx_keypoint* k2; const uint8_t* d2; const int* n2;
+  int n_pairs, cap; float invW, invH; float* prev; float ratio; float window; int checkOri;
+  int* m12; int* nm;
+  int* scratch;  // per pair: cap ints (matched distance) + cap ints (matches21) + cap ints (grid order)
+};
+int launch_search_init(const InitMatchArgs& a, cudaStream_t st);
+
+struct KnnArgs {
+  const uint8_t* dA; const float* angA; const int* nA;
+  const uint8_t* dB; const float* angB; const int* nB;
+  int n_pairs, cap, th; float ratio; int checkOri, strict;
+  int* m12; int* nm;
+  int* scratch;  // per pair: cap ints (rotation bin per A feature)
+};
+int launch_knn_ratio(const KnnArgs& a, cudaStream_t st);
+
+}  // namespace orbx

@@ -1,0 +1,80 @@
+"""CPU-side checks of the drop-in boundary: liborbx.so builds/loads and exports exactly the entry
+points include/orbx.h declares; argument validation that needs no GPU; the oracle is not reachable
+from the product package."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    txt = open(os.path.join(ROOT, "include", "orbx.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(orbx_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_exports_every_declared_symbol():
+    from orb_slam2_b200 import api, build
+    build.build()
+    lib = ctypes.CDLL(api.library_path())
+    names = _declared()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/orbx.h but not exported"
+    assert sorted(api.EXPORTS) == [n for n in names if n in api.EXPORTS]
+    out = subprocess.run(["nm", "-D", "--defined-only", api.library_path()], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (orbx_[a-z0-9_]+)", out))
+    assert exported == set(names), exported ^ set(names)
+
+
+def test_header_cites_reference_for_each_entry_point():
+    txt = open(os.path.join(ROOT, "include", "orbx.h")).read()
+    for sym in ["orbx_extractor_create", "orbx_extract", "orbx_stereo_match_batch", "orbx_search_init_batch",
+                "orbx_knn_ratio_batch", "orbx_hamming256", "orbx_pyramid_level", "orbx_get_tables"]:
+        head = txt[:txt.index(sym + "(")]
+        comment = head[head.rindex("/*"):]
+        assert re.search(r"src/\w+\.cc:\d+|include/\w+\.h:\d+", comment), sym
+
+
+def test_host_helpers_without_gpu():
+    from orb_slam2_b200 import ORBmatcher
+    import numpy as np
+    z = np.zeros(32, np.uint8); o = np.full(32, 255, np.uint8)
+    assert ORBmatcher.DescriptorDistance(z, o) == 256
+    assert ORBmatcher.DescriptorDistance(z, z) == 0
+    assert (ORBmatcher.TH_LOW, ORBmatcher.TH_HIGH, ORBmatcher.HISTO_LENGTH) == (50, 100, 30)
+
+
+def test_bad_arguments_rejected_before_touching_the_gpu():
+    from orb_slam2_b200 import api
+    L = api.lib()
+    h = ctypes.c_void_p()
+    p = api._Params(1000, 1.2, 9, 20, 7)
+    assert L.orbx_extractor_create(ctypes.byref(p), 640, 480, 1, 0, ctypes.byref(h)) == api.ERR_BAD_ARG
+    p = api._Params(1000, 1.2, 8, 300, 7)
+    assert L.orbx_extractor_create(ctypes.byref(p), 640, 480, 1, 0, ctypes.byref(h)) == api.ERR_BAD_ARG
+    assert b"threshold" in L.orbx_last_error_string()
+    assert L.orbx_extractor_create(None, 640, 480, 1, 0, ctypes.byref(h)) == api.ERR_BAD_ARG
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from orb_slam2_b200 import ORBextractor, OrbxError
+    with pytest.raises(OrbxError) as ei:
+        ORBextractor(1000, 1.2, 8, 20, 7, max_w=640, max_h=480)
+    assert ei.value.status == 4    # ORBX_ERR_CUDA: fails loudly, nothing is computed on the CPU
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "orb_slam2_b200")
+    for dp, _, fns in os.walk(pkg):
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".h", ".hpp", ".cpp")):
+                txt = open(os.path.join(dp, fn)).read()
+                assert "pyoracle" not in txt and "orb_oracle" not in txt and "liborb_oracle" not in txt, fn

@@ -1,0 +1,266 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (orb_slam2_b200.api -> liborbx.so),
+against the CPU oracle on the same seeded synthetic inputs.  Integer, byte and index results must
+be bit-exact; angles are bit-exact (fmad-off build + restated libm); stereo sub-pixel uRight is
+checked both bit-for-bit and against the 1e-3 px tolerance BASELINE.json states.
+Sizes are the three BASELINE shapes (KITTI 1241x376/2000, EuRoC 752x480/1200, TUM 640x480/1000)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from orb_slam2_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [("kitti", 1241, 376, 2000), ("euroc", 752, 480, 1200), ("tum", 640, 480, 1000)]
+UR_TOL = 1e-3   # px, BASELINE.json north_star
+
+
+@pytest.fixture(scope="module")
+def gx():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import orb_slam2_b200 as pkg
+    return pkg
+
+
+def _ext(gx, w, h, nf, batch=1):
+    return gx.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=batch)
+
+
+@pytest.mark.parametrize("name,w,h,nf", CONFIGS)
+def test_pyramid_bit_exact(gx, oracle, name, w, h, nf):
+    img = synth.mono_frame(0, w, h)
+    E = oracle.Extractor(nf); E.extract(img)
+    G = _ext(gx, w, h, nf); G(img)
+    for l in range(8):
+        assert np.array_equal(G.level(0, l), E.level(l)), f"{name} level {l}"
+
+
+@pytest.mark.parametrize("name,w,h,nf", CONFIGS)
+def test_fast_candidates_bit_exact_and_ordered(gx, oracle, name, w, h, nf):
+    img = synth.mono_frame(1, w, h)
+    E = oracle.Extractor(nf); E.extract(img)
+    G = _ext(gx, w, h, nf); G(img)
+    fallback = 0
+    for l in range(8):
+        c = E.candidates(l)
+        ref = np.stack([c["x"], c["y"], c["response"]], 1).astype(np.int32)
+        got = G.debug_candidates(0, l)
+        assert got.shape == ref.shape and np.array_equal(got, ref), f"{name} level {l}: {len(got)} vs {len(ref)}"
+        fallback += int((ref[:, 2] < 20).sum())
+    assert fallback > 0
+
+
+@pytest.mark.parametrize("name,w,h,nf", CONFIGS)
+def test_quadtree_keys_bit_exact(gx, oracle, name, w, h, nf):
+    img = synth.mono_frame(2, w, h)
+    E = oracle.Extractor(nf); E.extract(img)
+    G = _ext(gx, w, h, nf); G(img)
+    for l in range(8):
+        k = E.level_keys(l)
+        ref = np.stack([k["x"], k["y"], k["response"]], 1).astype(np.int32)
+        got = G.debug_level_keys(0, l)
+        assert got.shape == ref.shape and np.array_equal(got, ref), f"{name} level {l}: {len(got)} vs {len(ref)}"
+
+
+@pytest.mark.parametrize("name,w,h,nf", CONFIGS + [("tum_ini2x", 640, 480, 2000)])
+def test_extract_keypoints_and_descriptors_bit_exact(gx, oracle, name, w, h, nf):
+    G = _ext(gx, w, h, nf)
+    E = oracle.Extractor(nf)
+    for f in range(3):
+        img = synth.mono_frame(10 + f, w, h)
+        rk, rd = E.extract(img)
+        gk, gd = G(img)
+        assert len(gk) == len(rk)
+        for field in ("octave", "x", "y", "size", "response", "class_id"):
+            assert np.array_equal(gk[field], rk[field]), (name, f, field)
+        assert np.array_equal(gk["angle"].view(np.uint32), rk["angle"].view(np.uint32)), (name, f, "angle bits")
+        assert gk.tobytes() == rk.tobytes()
+        assert np.array_equal(gd, rd), (name, f, "descriptors", int((gd != rd).any(1).sum()))
+
+
+def test_reference_golden_digests_through_gpu(gx):
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "ref_extract.json")))
+    cache = {}
+    for case in gold["cases"]:
+        key = (case["w"], case["h"], case["nfeatures"])
+        if key not in cache:
+            cache[key] = _ext(gx, *key)
+        img = synth.mono_frame(case["frame"], case["w"], case["h"])
+        k, d = cache[key](img)
+        assert len(k) == case["count"]
+        assert hashlib.sha256(k.tobytes()).hexdigest() == case["kps_sha256"], case["name"]
+        assert hashlib.sha256(d.tobytes()).hexdigest() == case["desc_sha256"], case["name"]
+
+
+def test_batch_equals_single_and_is_deterministic(gx, oracle):
+    w, h, nf, n = 752, 480, 1200, 6
+    imgs = np.stack([synth.mono_frame(20 + i, w, h) for i in range(n)])
+    G = _ext(gx, w, h, nf, batch=n)
+    G.extract_batch(imgs)
+    first = G.fetch(0, n)
+    G.extract_batch(imgs)
+    again = G.fetch(0, n)
+    E = oracle.Extractor(nf)
+    for i in range(n):
+        rk, rd = E.extract(imgs[i])
+        assert first[i][0].tobytes() == rk.tobytes() and np.array_equal(first[i][1], rd), i
+        assert again[i][0].tobytes() == rk.tobytes() and np.array_equal(again[i][1], rd), i
+    # a device-resident batch gives the same bytes as the host-staged one
+    import torch
+    dev = torch.from_numpy(imgs).cuda()
+    G.extract_batch(dev)
+    third = G.fetch(0, n)
+    for i in range(n):
+        assert third[i][0].tobytes() == first[i][0].tobytes() and np.array_equal(third[i][1], first[i][1])
+
+
+def test_strided_input_and_getters(gx, oracle):
+    w, h, nf = 640, 480, 1000
+    big = np.zeros((h, w + 37), np.uint8)
+    big[:, :w] = synth.mono_frame(30, w, h)
+    view = big[:, :w]                                   # row stride != width
+    G = _ext(gx, w, h, nf)
+    k, d = G(view)
+    rk, rd = oracle.Extractor(nf).extract(np.ascontiguousarray(view))
+    assert k.tobytes() == rk.tobytes() and np.array_equal(d, rd)
+    t = oracle.Extractor(nf).tables()
+    assert np.array_equal(G.GetScaleFactors(), t["scale"]) and np.array_equal(G.GetInverseScaleFactors(), t["inv"])
+    assert np.array_equal(G.GetScaleSigmaSquares(), t["sigma2"]) and np.array_equal(G.GetInverseScaleSigmaSquares(), t["invsigma2"])
+    assert np.array_equal(G.features_per_level(), t["quota"]) and G.GetLevels() == 8
+    pyr = G.mvImagePyramid
+    assert pyr[0].shape == (h, w) and np.array_equal(pyr[0], view)
+
+
+def test_edge_cases(gx):
+    G = _ext(gx, 640, 480, 1000)
+    k, d = G(np.zeros((0, 0), np.uint8))                 # empty image: silent return
+    assert len(k) == 0 and d.shape == (0, 32)
+    k, d = G(np.full((480, 640), 77, np.uint8))          # no corner anywhere
+    assert len(k) == 0
+    with pytest.raises(gx.OrbxError) as ei:              # level 7 would be < 62 px wide
+        gx.ORBextractor(500, 1.2, 8, 20, 7, max_w=200, max_h=160)
+    assert ei.value.status == 2
+    with pytest.raises(gx.OrbxError) as ei:              # larger than reserved
+        G(np.zeros((600, 800), np.uint8))
+    assert ei.value.status == 3
+    # a smaller image on the same handle re-derives the level geometry
+    img = synth.mono_frame(31, 400, 300)
+    k, d = G(img)
+    from oracle import pyoracle
+    rk, rd = pyoracle.Extractor(1000).extract(img)
+    assert k.tobytes() == rk.tobytes() and np.array_equal(d, rd)
+
+
+@pytest.mark.parametrize("name,cfg", [("kitti", synth.KITTI), ("euroc", synth.EUROC)])
+def test_stereo_matches(gx, oracle, name, cfg):
+    w, h, nf, bf, fx = cfg["w"], cfg["h"], cfg["nfeatures"], cfg["bf"], cfg["fx"]
+    n = 3
+    pairs = [synth.stereo_pair(40 + i, w, h) for i in range(n)]
+    G = _ext(gx, w, h, nf, batch=2 * n)
+    G.extract_batch(np.stack([p[0] for p in pairs] + [p[1] for p in pairs]))
+    ur, dp, nm = gx.ComputeStereoMatches(G, G, bf, fx, n=n, slotL0=0, slotR0=n)
+    res = G.fetch(0, 2 * n)
+    for i in range(n):
+        EL, ER = oracle.Extractor(nf), oracle.Extractor(nf)
+        kl, dl = EL.extract(pairs[i][0]); kr, dr = ER.extract(pairs[i][1])
+        assert res[i][0].tobytes() == kl.tobytes() and res[n + i][0].tobytes() == kr.tobytes()
+        rur, rdp, rsad, rm = oracle.stereo(EL, ER, kl, dl, kr, dr, bf, fx)
+        cnt = len(kl)
+        assert int(nm[i]) == rm, (name, i)
+        assert np.array_equal(ur[i, :cnt] >= 0, rur >= 0)                       # same match set
+        assert np.max(np.abs(ur[i, :cnt] - rur)) <= UR_TOL                      # stated tolerance
+        assert np.array_equal(ur[i, :cnt].view(np.uint32), rur.view(np.uint32))  # and in fact bit-exact
+        assert np.array_equal(dp[i, :cnt].view(np.uint32), rdp.view(np.uint32))
+        assert rm > 100
+
+
+def test_stereo_two_handles_like_the_reference(gx, oracle):
+    cfg = synth.KITTI
+    w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
+    L, R, _ = synth.stereo_pair(50, w, h)
+    GL, GR = _ext(gx, w, h, nf), _ext(gx, w, h, nf)       # mpORBextractorLeft / Right
+    kl, dl = GL(L); kr, dr = GR(R)
+    ur, dp, nm = gx.ComputeStereoMatches(GL, GR, cfg["bf"], cfg["fx"])
+    EL, ER = oracle.Extractor(nf), oracle.Extractor(nf)
+    okl, odl = EL.extract(L); okr, odr = ER.extract(R)
+    rur, rdp, _, rm = oracle.stereo(EL, ER, okl, odl, okr, odr, cfg["bf"], cfg["fx"])
+    assert int(nm[0]) == rm and np.array_equal(ur[0, :len(kl)].view(np.uint32), rur.view(np.uint32))
+    flat = np.full((h, w), 90, np.uint8)                  # nothing to match: all -1, zero matches
+    GL(flat); GR(flat)
+    ur, dp, nm = gx.ComputeStereoMatches(GL, GR, cfg["bf"], cfg["fx"])
+    assert int(nm[0]) == 0
+
+
+@pytest.mark.parametrize("nf", [1000, 2000])
+def test_search_for_initialization(gx, oracle, nf):
+    w, h = 640, 480
+    G = _ext(gx, w, h, nf)
+    F1s, F2s, prevs, refs = [], [], [], []
+    for p in range(4):
+        a, b, _ = synth.mono_pair(60 + p, w, h)
+        k1, d1 = G(a); k2, d2 = G(b)
+        prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+        refs.append(oracle.search_init(k1, d1, k2, d2, w, h, prev, 0.9, 100, True))
+        F1s.append(gx.Frame(k1, d1, w, h)); F2s.append(gx.Frame(k2, d2, w, h)); prevs.append(prev.copy())
+    nm, m12 = gx.ORBmatcher(0.9, True).SearchForInitializationBatch(F1s, F2s, prevs, 100)
+    for p in range(4):
+        rm12, rn, rprev = refs[p]
+        assert nm[p] == rn and np.array_equal(m12[p], rm12), p
+        assert np.array_equal(prevs[p], rprev), p
+        assert rn > 20
+    # no orientation check, tight window: different branch mix
+    k1, d1 = F1s[0].mvKeysUn, F1s[0].mDescriptors
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    rm12, rn, _ = oracle.search_init(k1, d1, F2s[0].mvKeysUn, F2s[0].mDescriptors, w, h, prev, 0.9, 40, False)
+    n1, g12 = gx.ORBmatcher(0.9, False).SearchForInitialization(F1s[0], F2s[0], prev.copy(), 40)
+    assert n1 == rn and np.array_equal(g12, rm12)
+
+
+def test_knn_ratio_bruteforce(gx, oracle):
+    w, h, nf = 1241, 376, 2000
+    G = _ext(gx, w, h, nf)
+    As, Bs, refs = [], [], []
+    for p in range(3):
+        a, b, _ = synth.mono_pair(70 + p, w, h)
+        k1, d1 = G(a); k2, d2 = G(b)
+        As.append((d1, k1["angle"])); Bs.append((d2, k2["angle"]))
+        refs.append(oracle.knn_ratio(d1, k1["angle"], d2, k2["angle"], 50, 0.75, True, True))
+    nm, m12 = gx.ORBmatcher(0.75, True).SearchByBoWBatch(As, Bs, strict=True)
+    for p in range(3):
+        assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), p
+        assert refs[p][1] > 100
+    r = oracle.knn_ratio(As[0][0], As[0][1], Bs[0][0], Bs[0][1], 50, 0.7, False, False)
+    n1, g = gx.ORBmatcher(0.7, False).SearchByBoW(As[0][0], As[0][1], Bs[0][0], Bs[0][1], strict=False)
+    assert n1 == r[1] and np.array_equal(g, r[0])
+    # ragged: empty B side, single-feature A side
+    n1, g = gx.ORBmatcher(0.75, True).SearchByBoW(As[0][0][:1], As[0][1][:1], Bs[0][0][:0], Bs[0][1][:0])
+    assert n1 == 0 and g.tolist() == [-1]
+
+
+def test_full_size_batch_properties(gx):
+    """BASELINE-sized batch (KITTI stereo): properties that need no oracle — identical frames give
+    identical bytes in every slot, output is level-major, per-level counts within [quota, quota+3],
+    descriptors of a frame matched against themselves give distance 0 on the diagonal."""
+    cfg = synth.KITTI
+    w, h, nf, n = cfg["w"], cfg["h"], cfg["nfeatures"], 32
+    L, R, _ = synth.stereo_pair(80, w, h)
+    G = _ext(gx, w, h, nf, batch=2 * n)
+    G.extract_batch(np.stack([L] * n + [R] * n))
+    ur, dp, nm = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=n, slotL0=0, slotR0=n)
+    res = G.fetch(0, 2 * n)
+    quota = G.features_per_level()
+    for i in range(1, n):
+        assert res[i][0].tobytes() == res[0][0].tobytes() and np.array_equal(res[i][1], res[0][1])
+        assert res[n + i][0].tobytes() == res[n][0].tobytes()
+        assert np.array_equal(ur[i].view(np.uint32), ur[0].view(np.uint32)) and nm[i] == nm[0]
+    k = res[0][0]
+    assert np.all(np.diff(k["octave"]) >= 0)
+    per = [int((k["octave"] == l).sum()) for l in range(8)]
+    assert all(quota[l] <= per[l] <= quota[l] + 3 for l in range(8)), per
+    d = res[0][1]
+    assert all(gx.ORBmatcher.DescriptorDistance(d[i], d[i]) == 0 for i in range(0, len(d), 97))
+    assert nm[0] > 100
