@@ -178,6 +178,8 @@ class ORBextractor:
             return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
         if image.dtype != np.uint8 or image.ndim != 2:
             raise OrbxError(ERR_BAD_ARG, "image must be a 2-D uint8 array (CV_8UC1)")   # assert at src/ORBextractor.cc:1050
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)          # rows must be dense; the row stride may exceed the width
         h, w = image.shape
         if self._h is None:
             self._create(w, h)

@@ -83,7 +83,7 @@ def synth_image(seed, w, h, nrect=1200, ndisc=400):
 def _add_noise(img, seed, amp=2):
     s = _Stream(seed)
     n = (s.bytes(img.shape).astype(np.int32) % (2 * amp + 1)) - amp
-    return np.clip(img.astype(np.int32) + n, 0, 255).astype(np.uint8)
+    return np.ascontiguousarray(np.clip(img.astype(np.int32) + n, 0, 255).astype(np.uint8))
 
 
 def stereo_pair(frame_idx, w, h, band=47, dmin=2, dmax=64):
@@ -104,7 +104,7 @@ def mono_pair(frame_idx, w, h, maxshift=40):
     a = synth_image(seed, w, h)
     dx, dy = (int(v) for v in _Stream(seed + 2).ints(2, -maxshift, maxshift))
     ys = np.clip(np.arange(h) - dy, 0, h - 1); xs = np.clip(np.arange(w) - dx, 0, w - 1)
-    b = a[ys][:, xs]
+    b = np.ascontiguousarray(a[ys][:, xs])
     return a, _add_noise(b, seed + 1), (dx, dy)
 
 
