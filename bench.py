@@ -1,0 +1,344 @@
+#!/usr/bin/env python3
+"""bench.py — stereo frames/s of ORB extraction + stereo matching (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+A step is one pass of the hot path over one batch of B synthetic KITTI-shaped stereo pairs
+(1241x376, nFeatures 2000, 8 levels, 1.2; BASELINE.json configs[1]) on every rank:
+pyramid -> FAST cells -> quad-tree -> orientation+blur+rBRIEF (both eyes) -> ComputeStereoMatches.
+Independent frames are sharded over ranks (weak scaling, no data-path collective); NCCL only
+gathers {frames, keypoints, matches, checksum} after the timed region.
+
+  value : whole-job stereo frames/s, inputs already resident in HBM
+  e2e   : the same through the C ABI with pinned HOST buffers: H2D of every image and D2H of all
+          results (keypoints, descriptors, uRight, depth, counts) inside the timed region
+  roofline    : the dominant kernel, algorithmic bytes / CUDA-event time vs measured HBM peak
+  cpu_baseline: the CPU oracle (port of the reference's path) on this box's host cores
+  --impl reference: the CPU path alone, all host threads, same metric (rank 0 only)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from orb_slam2_b200 import synth  # noqa: E402
+
+CFG = synth.KITTI
+PARAMS = (CFG["nfeatures"], 1.2, 8, 20, 7)
+NSETS = 3            # input sets rotated between steps so inputs are never L2-resident from the last step
+L2_MB = 126
+
+
+def level_sizes(w, h):
+    s = np.float32(1.0); out = []
+    for l in range(8):
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+        s = np.float32(np.float64(s) * np.float64(np.float32(1.2)))
+    return out
+
+
+def algorithmic_bytes(w, h, nf, cands_per_eye, kps_per_eye):
+    """Compulsory bytes per STEREO frame, per stage and for the whole path."""
+    lv = level_sizes(w, h)
+    raw = sum(a * b for a, b in lv)
+    bordered = sum((a + 38) * (b + 38) for a, b in lv)
+    st = {
+        "pyramid": 2 * (w * h + bordered),
+        "fast": 2 * (raw + 4 * cands_per_eye),
+        "quadtree": 2 * (4 * cands_per_eye + 4 * kps_per_eye),
+        "describe": 2 * kps_per_eye * (43 * 43 + 60),
+        "stereo_match": 2 * kps_per_eye * 60 + kps_per_eye * (11 * 32 + 8),
+        "stereo_median": kps_per_eye * 12,
+    }
+    path = 2 * w * h + 2 * bordered + 2 * nf * 60 + nf * 8      # 4 666 350 B for KITTI
+    return st, path
+
+
+def make_inputs(rank, batch):
+    """NSETS x (2*batch, h, w): first `batch` left eyes then `batch` right eyes.  Distinct seeded pairs;
+    odd sets reuse the pairs flipped vertically (keeps the horizontal disparity structure)."""
+    w, h = CFG["w"], CFG["h"]
+    need = batch * ((NSETS + 1) // 2)
+    pairs = [synth.stereo_pair(100000 * rank + i, w, h)[:2] for i in range(need)]
+    sets = []
+    for s in range(NSETS):
+        chunk = pairs[(s // 2) * batch:(s // 2 + 1) * batch]
+        flip = s % 2 == 1
+        L = [np.flipud(p[0]) if flip else p[0] for p in chunk]
+        R = [np.flipud(p[1]) if flip else p[1] for p in chunk]
+        sets.append(np.ascontiguousarray(np.stack(L + R)))
+    return sets
+
+
+class ClockSampler:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu):
+        self.gpu, self.proc, self.lines = gpu, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_sample(nframes, distinct=32):
+    """nframes KITTI-shaped stereo pairs for the CPU legs (at most `distinct` different ones, tiled)."""
+    w, h = CFG["w"], CFG["h"]
+    pairs = [synth.stereo_pair(900000 + i, w, h)[:2] for i in range(min(nframes, distinct))]
+    idx = [i % len(pairs) for i in range(nframes)]
+    return np.stack([pairs[i][0] for i in idx]), np.stack([pairs[i][1] for i in idx])
+
+
+def cpu_baseline(nframes, threads):
+    """The oracle port of the reference's path on the host cores (one stereo frame per std::thread)."""
+    from oracle import pyoracle as O
+    L, R = cpu_sample(nframes)
+    O.bench_stereo(L[:threads], R[:threads], PARAMS, CFG["bf"], CFG["fx"], threads)          # warm caches / threads
+    secs, keys, matches = O.bench_stereo(L, R, PARAMS, CFG["bf"], CFG["fx"], threads)
+    return nframes / secs, secs, keys, matches
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path on the host cores.  The
+    reference's own Frame.cc/ORBmatcher.cc cannot be compiled here (they pull in DBoW2/Eigen/OpenCV),
+    so the timed code is the oracle port (checked byte-identical against the reference's compiled
+    ORBextractor.cc, oracle/_ref) — kind "port"."""
+    if rank != 0:
+        return
+    from oracle import pyoracle as O
+    O.build()
+    threads = O.hardware_threads()
+    per_step = 2 * threads
+    L, R = cpu_sample(per_step)
+    for _ in range(args.warmup):
+        O.bench_stereo(L, R, PARAMS, CFG["bf"], CFG["fx"], threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        O.bench_stereo(L, R, PARAMS, CFG["bf"], CFG["fx"], threads)
+    secs = time.perf_counter() - t0
+    val = per_step * args.steps / secs
+    sample = f"{per_step} KITTI-shaped stereo pairs per step, one pair per std::thread, {threads} threads"
+    line = {"impl": "reference", "metric": "stereo_frames_per_sec_orb_extract_plus_stereo_match", "value": val,
+            "unit": "stereo frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1000 * secs / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "KITTI-shaped 1241x376 stereo, nFeatures=2000, 8 levels, scale 1.2, ORB extraction + ComputeStereoMatches",
+                       "frames_per_step": per_step},
+            "cpu_baseline": {"value": val, "unit": "stereo frames/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "stereo frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="stereo pairs per step per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import orb_slam2_b200 as gx
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the CUDA path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B, w, h, nf = args.batch, CFG["w"], CFG["h"], CFG["nfeatures"]
+    bf, fx = CFG["bf"], CFG["fx"]
+
+    sets = make_inputs(rank, B)
+    host = [torch.from_numpy(s).pin_memory() for s in sets]
+    dev = [t.cuda(non_blocking=True) for t in host]
+    G = [gx.ORBextractor(*PARAMS, max_w=w, max_h=h, max_batch=2 * B, device=local) for _ in range(2)]
+    cap = G[0].kp_cap
+    d_ur = torch.empty((B, cap), dtype=torch.float32, device="cuda"); d_dp = torch.empty_like(d_ur)
+    d_nm = torch.empty(B, dtype=torch.int32, device="cuda")
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    # pinned result buffers for the end-to-end leg, one set per pipeline stage
+    h_out = [dict(kps=torch.empty((2 * B, cap, 28), dtype=torch.uint8).pin_memory(),
+                  desc=torch.empty((2 * B, cap, 32), dtype=torch.uint8).pin_memory(),
+                  cnt=torch.empty(2 * B, dtype=torch.int32).pin_memory(),
+                  ur=torch.empty((B, cap), dtype=torch.float32).pin_memory(),
+                  dp=torch.empty((B, cap), dtype=torch.float32).pin_memory(),
+                  nm=torch.empty(B, dtype=torch.int32).pin_memory()) for _ in range(2)]
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def step_resident(i, g, st):
+        g.extract_batch(dev[i % NSETS], 0, st.cuda_stream)
+        gx.ComputeStereoMatches(g, g, bf, fx, n=B, slotL0=0, slotR0=B, out=(d_ur, d_dp, d_nm), stream=st.cuda_stream)
+
+    def step_e2e(i, g, st, o):
+        s = st.cuda_stream
+        g.extract_batch(host[i % NSETS], 0, s)                                    # H2D of 2B images inside
+        g.fetch_into(0, 2 * B, o["kps"], o["desc"], o["cnt"], s)                  # D2H keypoints, descriptors, counts
+        gx.ComputeStereoMatches(g, g, bf, fx, n=B, slotL0=0, slotR0=B, out=(o["ur"], o["dp"], o["nm"]), stream=s)
+
+    # ---- device-resident throughput ("value") ----
+    st0 = streams[0]
+    for i in range(args.warmup):
+        step_resident(i, G[0], st0)
+    torch.cuda.synchronize()
+    G[0].set_profiling(True)
+    sampler = ClockSampler(local); sampler.start()
+    launches0 = gx.kernel_launch_count()
+    barrier(); torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record(st0)
+    for i in range(args.steps):
+        step_resident(i, G[0], st0)
+    e1.record(st0)
+    torch.cuda.synchronize(); barrier()
+    ms = e0.elapsed_time(e1)
+    launches = gx.kernel_launch_count() - launches0
+    prof = G[0].get_profile()
+    G[0].set_profiling(False)
+    res = G[0].fetch(0, 2 * B)
+    nkp = np.array([len(r[0]) for r in res]); matches = d_nm.cpu().numpy()
+    cands = 0
+    for l in range(8):
+        cands += len(G[0].debug_candidates(0, l))
+    checksum = int(np.bitwise_xor.reduce(np.frombuffer(res[0][1].tobytes(), np.uint64))) if len(res[0][1]) else 0
+
+    # ---- end to end through the C ABI with host buffers, two handles/streams ping-pong ----
+    for i in range(args.warmup):
+        step_e2e(i, G[i & 1], streams[i & 1], h_out[i & 1])
+    torch.cuda.synchronize(); barrier()
+    ee0 = torch.cuda.Event(enable_timing=True); ee1 = torch.cuda.Event(enable_timing=True)
+    ee0.record(streams[0])
+    for i in range(args.steps):
+        step_e2e(i, G[i & 1], streams[i & 1], h_out[i & 1])
+    streams[0].wait_stream(streams[1])
+    ee1.record(streams[0])
+    torch.cuda.synchronize(); barrier()
+    ms_e2e = ee0.elapsed_time(ee1)
+    clocks = sampler.stop()
+    assert int(h_out[(args.steps - 1) & 1]["cnt"].sum()) > 0 and int(h_out[(args.steps - 1) & 1]["nm"].sum()) > 0
+
+    # ---- max over ranks, totals over ranks ----
+    tvec = torch.tensor([ms, ms_e2e], dtype=torch.float64, device="cuda")
+    rec = torch.tensor([B * args.steps, int(nkp.sum()), int(matches.sum()), checksum & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tvec, op=dist.ReduceOp.MAX)
+        allrec = [torch.zeros_like(rec) for _ in range(world)]
+        dist.all_gather(allrec, rec)                      # the only collective of the job: counts + checksums
+        rec_all = torch.stack(allrec).cpu().numpy()
+    else:
+        rec_all = rec.cpu().numpy()[None]
+    ms, ms_e2e = float(tvec[0]), float(tvec[1])
+    frames_total = int(rec_all[:, 0].sum())
+
+    if rank == 0:
+        value = frames_total / (ms / 1000.0)
+        e2e_val = frames_total / (ms_e2e / 1000.0)
+        h2d = 2 * B * w * h
+        d2h = 2 * B * cap * 60 + 2 * B * 4 + 2 * B * cap * 4 + B * 4
+        kps_eye = float(nkp.mean()); cands_eye = float(cands)
+        stage_bytes, path_bytes = algorithmic_bytes(w, h, nf, cands_eye, kps_eye)
+        stage_ms = {s: (v[0] / v[1] if v[1] else 0.0) for s, v in prof.items()}
+        top = max(stage_ms, key=stage_ms.get)
+        peak, peak_src = measured_hbm_peak()
+        ach = stage_bytes[top] * B / (stage_ms[top] / 1000.0) / 1e9 if stage_ms[top] > 0 else 0.0
+        line = {
+            "metric": "stereo_frames_per_sec_orb_extract_plus_stereo_match", "value": value, "unit": "stereo frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "KITTI-shaped 1241x376 stereo, nFeatures=2000, 8 levels, scale 1.2, ORB extraction + ComputeStereoMatches (BASELINE.json configs[1])",
+                       "stereo_pairs_per_step_per_gpu": B, "sharding": f"independent frames, {world} rank(s), no data-path collective",
+                       "l2": f"inputs rotate over {NSETS} sets of {2 * B * w * h / 1e6:.0f} MB (> {L2_MB} MB L2 in total); per-step intermediates {2 * B * 1.8:.0f} MB",
+                       "bf": bf, "fx": fx},
+            "e2e": {"value": e2e_val, "unit": "stereo frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps, "pipeline": "2 handles x 2 streams, pinned host buffers"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": stage_bytes[top] * B,
+                         "note": "front end is instruction-issue / latency bound, not HBM bound (DESIGN.md); see profiles/ for ncu issue utilisation"},
+            "stage_ms_per_step": stage_ms,
+            "path": {"algorithmic_bytes_per_stereo_frame": path_bytes, "achieved_gbs": path_bytes * B / (ms / args.steps / 1000.0) / 1e9,
+                     "frac_of_hbm_peak": path_bytes * B / (ms / args.steps / 1000.0) / 1e9 / peak},
+            "results": {"keypoints_per_eye": kps_eye, "fast_candidates_per_eye": cands_eye, "stereo_matches_per_frame": float(matches.mean()),
+                        "per_rank": rec_all.tolist()},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import pyoracle as O
+            O.build()
+            threads = O.hardware_threads()
+            nfr = 8 * threads                               # ~10-20 s of CPU work
+            v, secs, _, _ = cpu_baseline(nfr, threads)
+            line["cpu_baseline"] = {"value": v, "unit": "stereo frames/s", "cores": threads, "kind": "port",
+                                    "sample": f"{nfr} KITTI-shaped stereo pairs, one pair per std::thread on {threads} threads, {secs:.1f} s"}
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

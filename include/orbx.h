@@ -156,6 +156,17 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
 
 /* ---- misc -------------------------------------------------------------------------------- */
 
+/* Per-stage device timing for roofline reports (no counterpart in the reference, which only
+ * wall-clocks whole frames, Examples/Stereo/stereo_kitti.cc:80-97).  When enabled, extract_batch
+ * and stereo_match_batch bracket each stage with CUDA events on the launching stream.
+ * orbx_get_profile synchronises the device, adds up what was recorded since the last call and
+ * resets: ms[s] = total milliseconds of stage s, calls[s] = number of recorded passes.
+ * Stages: 0 pyramid (all level launches), 1 FAST cells, 2 quad-tree, 3 orientation+blur+rBRIEF,
+ * 4 stereo search+SAD, 5 stereo median cut. */
+#define ORBX_N_STAGES 6
+orbx_status orbx_set_profiling(orbx_extractor* ext, int enable);
+orbx_status orbx_get_profile(orbx_extractor* ext, float* ms, int* calls);
+
 /* Message of the last failing call on the calling thread ("" if none). */
 const char* orbx_last_error_string(void);
 /* Number of kernels launched by this library in the calling process so far (for bench.py). */

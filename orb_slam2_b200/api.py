@@ -42,7 +42,10 @@ EXPORTS = ["orbx_extractor_create", "orbx_extractor_destroy", "orbx_get_tables",
            "orbx_extract", "orbx_extract_batch", "orbx_fetch_results", "orbx_pyramid_level",
            "orbx_download_level", "orbx_debug_candidates", "orbx_debug_level_keys",
            "orbx_stereo_match_batch", "orbx_hamming256", "orbx_search_init_batch", "orbx_knn_ratio_batch",
-           "orbx_last_error_string", "orbx_kernel_launch_count", "orbx_version"]
+           "orbx_last_error_string", "orbx_kernel_launch_count", "orbx_version", "orbx_set_profiling",
+           "orbx_get_profile"]
+
+STAGES = ["pyramid", "fast", "quadtree", "describe", "stereo_match", "stereo_median"]
 
 
 def library_path():
@@ -82,6 +85,8 @@ def lib():
         L.orbx_pyramid_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
+        L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]
+        L.orbx_get_profile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -217,6 +222,15 @@ class ORBextractor:
         self.fetch_into(first_slot, n, kps, desc, cnt)
         _sync(self.device)
         return [(kps[i, :cnt[i]].copy(), desc[i, :cnt[i]].copy()) for i in range(n)]
+
+    def set_profiling(self, enable=True):
+        _check(lib().orbx_set_profiling(self._h, int(enable)))
+
+    def get_profile(self):
+        """{stage: (total ms, recorded passes)} since the last call (synchronises the device)."""
+        ms = np.zeros(len(STAGES), np.float32); calls = np.zeros(len(STAGES), np.int32)
+        _check(lib().orbx_get_profile(self._h, ms.ctypes.data, calls.ctypes.data))
+        return {s: (float(ms[i]), int(calls[i])) for i, s in enumerate(STAGES)}
 
     def level(self, slot, level):
         """Bordered pyramid plane (h+38, w+38) of one slot, as the reference's mvImagePyramid backing store."""

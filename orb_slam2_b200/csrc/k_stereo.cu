@@ -178,12 +178,13 @@ __global__ void __launch_bounds__(256) k_stereo_median(StereoArgs a) {
   if (tid == 0) a.nMatches[img] = s_kept;
 }
 
-int launch_stereo(const StereoArgs& a, cudaStream_t st) {
+int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid) {
   const int capR = a.R.kp_cap, capL = a.L.kp_cap;
   const int chunks = (capL + kStPerCta - 1) / kStPerCta;
   const size_t smem1 = (size_t)capR * 8 + ((capR + 15) & ~15) + kStWarps * 384;
   if (smem1 > 48 * 1024) cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
   k_stereo_match<<<a.n * chunks, kStWarps * 32, smem1, st>>>(a, chunks);
+  if (ev_mid) cudaEventRecord(ev_mid, st);
   const size_t smem2 = (size_t)capL * 4;
   if (smem2 > 48 * 1024) cudaFuncSetAttribute(k_stereo_median, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
   k_stereo_median<<<a.n, 256, smem2, st>>>(a);

@@ -71,6 +71,11 @@ struct orbx_extractor {
   uint8_t* d_in = nullptr;
   float* d_uright = nullptr; float* d_depth = nullptr; int* d_sad = nullptr; int* d_nmatch = nullptr;
   int slots_valid = 0;
+  // optional per-stage timing: a ring of event sets, 5 boundaries per extract pass, 3 per stereo pass
+  bool profiling = false;
+  static constexpr int kRing = 64;
+  cudaEvent_t ev_ext[kRing][5] = {}; int n_ext = 0;
+  cudaEvent_t ev_st[kRing][3] = {}; int n_st = 0;
 };
 
 namespace {
@@ -299,6 +304,11 @@ void orbx_extractor_destroy(orbx_extractor* e) {
                   L.knode, L.lvlkp, L.lvlcnt, L.nkeys, L.kps, L.desc, L.nkp, L.err, e->d_uright, e->d_depth, e->d_sad,
                   e->d_nmatch};
   for (void* p : ptrs) if (p) cudaFree(p);
+  if (e->ev_ext[0][0])
+    for (int i = 0; i < orbx_extractor::kRing; ++i) {
+      for (int j = 0; j < 5; ++j) cudaEventDestroy(e->ev_ext[i][j]);
+      for (int j = 0; j < 3; ++j) cudaEventDestroy(e->ev_st[i][j]);
+    }
   delete e;
 }
 
@@ -342,10 +352,16 @@ orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, in
   }
   CU(cudaMemsetAsync(e->L.poolcnt + (size_t)first_slot * kMaxLevels, 0, (size_t)n * kMaxLevels * sizeof(int), st));
   int launches = 0;
+  cudaEvent_t* ev = (e->profiling && e->n_ext < orbx_extractor::kRing) ? e->ev_ext[e->n_ext++] : nullptr;
+  if (ev) cudaEventRecord(ev[0], st);
   launches += launch_pyramid(e->L, e->hg, src, src_pitch, src_istride, first_slot, n, st);
+  if (ev) cudaEventRecord(ev[1], st);
   launches += launch_fast(e->L, e->hg, first_slot, n, e->cur.win_w, e->cur.win_h, st);
+  if (ev) cudaEventRecord(ev[2], st);
   launches += launch_octree(e->L, first_slot, n, e->cur.node_cap, st);
+  if (ev) cudaEventRecord(ev[3], st);
   launches += launch_describe(e->L, first_slot, n, e->d_umax, e->d_pattern, st);
+  if (ev) cudaEventRecord(ev[4], st);
   g_launches += launches;
   CU(cudaGetLastError());
   e->slots_valid = std::max(e->slots_valid, first_slot + n);
@@ -467,7 +483,10 @@ orbx_status orbx_stereo_match_batch(orbx_extractor* eL, int slotL0, orbx_extract
   a.nMatches = direct ? n_matches : eL->d_nmatch;
   a.sad = eL->d_sad;
   a.cap = direct ? cap : eL->kp_cap;
-  g_launches += launch_stereo(a, st);
+  cudaEvent_t* ev = (eL->profiling && eL->n_st < orbx_extractor::kRing) ? eL->ev_st[eL->n_st++] : nullptr;
+  if (ev) cudaEventRecord(ev[0], st);
+  g_launches += launch_stereo(a, st, ev ? ev[1] : nullptr);
+  if (ev) cudaEventRecord(ev[2], st);
   CU(cudaGetLastError());
   if (!direct) {
     const cudaMemcpyKind kind = dst_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
@@ -573,6 +592,41 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
     CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
   }
+  return ORBX_OK;
+}
+
+orbx_status orbx_set_profiling(orbx_extractor* e, int enable) {
+  if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
+  DeviceGuard guard(e->device);
+  if (enable && !e->ev_ext[0][0]) {
+    for (int i = 0; i < orbx_extractor::kRing; ++i) {
+      for (int j = 0; j < 5; ++j) CU(cudaEventCreate(&e->ev_ext[i][j]));
+      for (int j = 0; j < 3; ++j) CU(cudaEventCreate(&e->ev_st[i][j]));
+    }
+  }
+  e->profiling = enable != 0;
+  e->n_ext = e->n_st = 0;
+  return ORBX_OK;
+}
+
+orbx_status orbx_get_profile(orbx_extractor* e, float* ms, int* calls) {
+  if (!e || !ms || !calls) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  DeviceGuard guard(e->device);
+  CU(cudaDeviceSynchronize());
+  for (int s = 0; s < ORBX_N_STAGES; ++s) { ms[s] = 0.f; calls[s] = 0; }
+  for (int i = 0; i < e->n_ext; ++i)
+    for (int s = 0; s < 4; ++s) {
+      float t = 0.f;
+      CU(cudaEventElapsedTime(&t, e->ev_ext[i][s], e->ev_ext[i][s + 1]));
+      ms[s] += t; calls[s] += 1;
+    }
+  for (int i = 0; i < e->n_st; ++i)
+    for (int s = 0; s < 2; ++s) {
+      float t = 0.f;
+      CU(cudaEventElapsedTime(&t, e->ev_st[i][s], e->ev_st[i][s + 1]));
+      ms[4 + s] += t; calls[4 + s] += 1;
+    }
+  e->n_ext = e->n_st = 0;
   return ORBX_OK;
 }
 

@@ -84,7 +84,7 @@ struct StereoArgs {
   float* uRight; float* depth; int* nMatches; int* sad;  // device, [n][cap]
   int cap;
 };
-int launch_stereo(const StereoArgs& a, cudaStream_t st);
+int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid);
 
 struct InitMatchArgs {
   const orbx_keypoint* k1; const uint8_t* d1; const int* n1;
