@@ -280,16 +280,10 @@ def main():
     assert int(h_out[(args.steps - 1) & 1]["cnt"].sum()) > 0 and int(h_out[(args.steps - 1) & 1]["nm"].sum()) > 0
 
     # ---- max over ranks, totals over ranks ----
-    tvec = torch.tensor([ms, ms_e2e], dtype=torch.float64, device="cuda")
-    rec = torch.tensor([B * args.steps, int(nkp.sum()), int(matches.sum()), checksum & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tvec, op=dist.ReduceOp.MAX)
-        allrec = [torch.zeros_like(rec) for _ in range(world)]
-        dist.all_gather(allrec, rec)                      # the only collective of the job: counts + checksums
-        rec_all = torch.stack(allrec).cpu().numpy()
-    else:
-        rec_all = rec.cpu().numpy()[None]
-    ms, ms_e2e = float(tvec[0]), float(tvec[1])
+    from orb_slam2_b200 import sharding
+    ms, ms_e2e = sharding.max_over_ranks([ms, ms_e2e], device="cuda")
+    rec = sharding.make_record(B * args.steps, int(nkp.sum()), int(matches.sum()), checksum)
+    rec_all = sharding.gather_records(rec, device="cuda")     # the only collective of the job: counts + checksums
     frames_total = int(rec_all[:, 0].sum())
 
     if rank == 0:

@@ -167,6 +167,9 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
 orbx_status orbx_set_profiling(orbx_extractor* ext, int enable);
 orbx_status orbx_get_profile(orbx_extractor* ext, float* ms, int* calls);
 
+/* cudaStreamSynchronize for callers that do not link the CUDA runtime themselves. */
+orbx_status orbx_stream_synchronize(void* stream);
+
 /* Message of the last failing call on the calling thread ("" if none). */
 const char* orbx_last_error_string(void);
 /* Number of kernels launched by this library in the calling process so far (for bench.py). */

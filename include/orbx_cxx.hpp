@@ -1,0 +1,153 @@
+// orbx_cxx.hpp — source-compatible C++ stand-ins for the two reference classes on the hot path,
+// implemented on the C ABI in orbx.h.  Header only; compile it against the OpenCV headers the
+// rest of ORB-SLAM2 already uses (it needs cv::Mat, cv::KeyPoint, cv::InputArray/OutputArray).
+//
+//   ORB_SLAM2::ORBextractor   replaces include/ORBextractor.h + src/ORBextractor.cc
+//   ORB_SLAM2::ORBmatcher     the hot-path subset of include/ORBmatcher.h (DescriptorDistance,
+//                             SearchForInitialization on flat arrays); the other searches keep
+//                             using the reference implementation and call DescriptorDistance
+//   ORB_SLAM2::ComputeStereoMatchesGPU   body for Frame::ComputeStereoMatches (src/Frame.cc:466)
+//
+// Same constructor arguments, same operator() signature, same getters, same public
+// mvImagePyramid member (filled on demand by DownloadPyramid(), because the stereo matcher reads
+// the pyramid on the device).  Errors that the reference turns into assert()/cv::Exception
+// surface as std::runtime_error carrying orbx_last_error_string().
+#ifndef ORBX_CXX_HPP_
+#define ORBX_CXX_HPP_
+
+#include <opencv2/core/core.hpp>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "orbx.h"
+
+namespace ORB_SLAM2 {
+
+inline void orbx_check(orbx_status s) {
+  if (s != ORBX_OK) throw std::runtime_error(std::string("orbx: ") + orbx_last_error_string());
+}
+
+class ORBextractor {
+ public:
+  enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+  ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0)
+      : device_(device), handle_(nullptr) {
+    params_.nfeatures = nfeatures; params_.scale_factor = scaleFactor; params_.nlevels = nlevels;
+    params_.ini_th_fast = iniThFAST; params_.min_th_fast = minThFAST;
+    mvImagePyramid.resize(nlevels);
+  }
+  ~ORBextractor() { orbx_extractor_destroy(handle_); }
+  ORBextractor(const ORBextractor&) = delete;
+  ORBextractor& operator=(const ORBextractor&) = delete;
+
+  // Mask is ignored, as in the reference (include/ORBextractor.h:58).
+  void operator()(cv::InputArray _image, cv::InputArray /*mask*/, std::vector<cv::KeyPoint>& keypoints,
+                  cv::OutputArray _descriptors) {
+    if (_image.empty()) return;                                   // src/ORBextractor.cc:1046
+    cv::Mat image = _image.getMat();
+    if (image.type() != CV_8UC1) throw std::runtime_error("orbx: image must be CV_8UC1");   // assert at :1050
+    Ensure(image.cols, image.rows);
+    static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint layout");
+    const int cap = orbx_max_keypoints(handle_);
+    keypoints.resize(cap);
+    std::vector<unsigned char> desc((size_t)cap * 32);
+    int n = 0;
+    orbx_check(orbx_extract(handle_, image.data, image.cols, image.rows, (int)image.step,
+                            reinterpret_cast<orbx_keypoint*>(keypoints.data()), desc.data(), cap, &n, nullptr));
+    keypoints.resize(n);
+    if (n == 0) { _descriptors.release(); return; }
+    _descriptors.create(n, 32, CV_8U);
+    cv::Mat out = _descriptors.getMat();
+    for (int i = 0; i < n; ++i) std::copy(desc.begin() + (size_t)i * 32, desc.begin() + (size_t)(i + 1) * 32, out.ptr(i));
+  }
+
+  int GetLevels() { return params_.nlevels; }
+  float GetScaleFactor() { return params_.scale_factor; }
+  std::vector<float> GetScaleFactors() { return Table(0); }
+  std::vector<float> GetInverseScaleFactors() { return Table(1); }
+  std::vector<float> GetScaleSigmaSquares() { return Table(2); }
+  std::vector<float> GetInverseScaleSigmaSquares() { return Table(3); }
+
+  // The reference's public pyramid (include/ORBextractor.h:85).  Host copies are made only when
+  // somebody asks: level l is the inner ROI of a (w+38) x (h+38) bordered plane, as upstream.
+  std::vector<cv::Mat> mvImagePyramid;
+  void DownloadPyramid() {
+    for (int l = 0; l < params_.nlevels; ++l) {
+      int w = 0, h = 0;
+      orbx_check(orbx_pyramid_level(handle_, 0, l, nullptr, &w, &h, nullptr));
+      cv::Mat whole(h + 38, w + 38, CV_8UC1);
+      orbx_check(orbx_download_level(handle_, 0, l, whole.data));
+      mvImagePyramid[l] = whole(cv::Rect(19, 19, w, h));
+    }
+  }
+
+  orbx_extractor* handle() { return handle_; }
+  // Sizes the device arenas; called lazily by operator() with the first image's size.
+  void Ensure(int w, int h, int max_batch = 1) {
+    if (handle_) return;
+    orbx_check(orbx_extractor_create(&params_, w, h, max_batch, device_, &handle_));
+  }
+
+ private:
+  std::vector<float> Table(int which) {
+    float t[4][8]; int n = 0;
+    if (!handle_) throw std::runtime_error("orbx: extractor tables need Ensure(w,h) or a first extraction");
+    orbx_check(orbx_get_tables(handle_, &n, t[0], t[1], t[2], t[3], nullptr));
+    return std::vector<float>(t[which], t[which] + n);
+  }
+  orbx_params params_;
+  int device_;
+  orbx_extractor* handle_;
+};
+
+// Body of Frame::ComputeStereoMatches (src/Frame.cc:466-640): call right after both ExtractORB
+// threads joined (src/Frame.cc:78-81).  N = mvKeys.size().
+inline void ComputeStereoMatchesGPU(ORBextractor& left, ORBextractor& right, int N, float mbf, float fx,
+                                    std::vector<float>& mvuRight, std::vector<float>& mvDepth) {
+  const int cap = orbx_max_keypoints(left.handle());
+  std::vector<float> ur(cap, -1.f), dp(cap, -1.f);
+  int nmatches = 0;
+  orbx_check(orbx_stereo_match_batch(left.handle(), 0, right.handle(), 0, 1, mbf, fx, ur.data(), dp.data(), &nmatches, cap, 0, nullptr));
+  orbx_check(orbx_stream_synchronize(nullptr));
+  mvuRight.assign(ur.begin(), ur.begin() + N);
+  mvDepth.assign(dp.begin(), dp.begin() + N);
+}
+
+class ORBmatcher {
+ public:
+  static const int TH_LOW = 50, TH_HIGH = 100, HISTO_LENGTH = 30;   // src/ORBmatcher.cc:37-39
+  ORBmatcher(float nnratio = 0.6f, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+
+  static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return orbx_hamming256(a.ptr(), b.ptr()); }
+
+  // SearchForInitialization on the arrays Frame holds (mvKeysUn, mDescriptors of F1 and F2, image
+  // bounds); vbPrevMatched and vnMatches12 as in include/ORBmatcher.h:69.
+  int SearchForInitialization(const std::vector<cv::KeyPoint>& keys1, const cv::Mat& desc1,
+                              const std::vector<cv::KeyPoint>& keys2, const cv::Mat& desc2, int cols, int rows,
+                              std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10) {
+    const int n1 = (int)keys1.size(), n2 = (int)keys2.size(), cap = std::max(std::max(n1, n2), 1);
+    std::vector<orbx_keypoint> k1(cap), k2(cap);
+    std::vector<unsigned char> d1((size_t)cap * 32), d2((size_t)cap * 32);
+    std::vector<float> prev((size_t)cap * 2);
+    for (int i = 0; i < n1; ++i) { k1[i] = reinterpret_cast<const orbx_keypoint&>(keys1[i]); std::copy(desc1.ptr(i), desc1.ptr(i) + 32, &d1[(size_t)i * 32]);
+                                   prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
+    for (int i = 0; i < n2; ++i) { k2[i] = reinterpret_cast<const orbx_keypoint&>(keys2[i]); std::copy(desc2.ptr(i), desc2.ptr(i) + 32, &d2[(size_t)i * 32]); }
+    vnMatches12.assign(cap, -1);
+    int nm = 0;
+    orbx_check(orbx_search_init_batch(k1.data(), d1.data(), &n1, k2.data(), d2.data(), &n2, 1, cap, cols, rows, prev.data(), mfNNratio,
+                                      windowSize, mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nm, 0, nullptr));
+    vnMatches12.resize(n1);
+    for (int i = 0; i < n1; ++i) { vbPrevMatched[i].x = prev[2 * i]; vbPrevMatched[i].y = prev[2 * i + 1]; }
+    return nm;
+  }
+
+ protected:
+  float mfNNratio;
+  bool mbCheckOrientation;
+};
+
+}  // namespace ORB_SLAM2
+#endif  // ORBX_CXX_HPP_

@@ -630,6 +630,11 @@ orbx_status orbx_get_profile(orbx_extractor* e, float* ms, int* calls) {
   return ORBX_OK;
 }
 
+orbx_status orbx_stream_synchronize(void* stream) {
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return ORBX_OK;
+}
+
 const char* orbx_last_error_string(void) { return g_err.c_str(); }
 unsigned long long orbx_kernel_launch_count(void) { return g_launches.load(); }
 const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }

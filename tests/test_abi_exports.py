@@ -78,3 +78,15 @@ def test_product_does_not_import_oracle():
             if fn.endswith((".py", ".cu", ".h", ".hpp", ".cpp")):
                 txt = open(os.path.join(dp, fn)).read()
                 assert "pyoracle" not in txt and "orb_oracle" not in txt and "liborb_oracle" not in txt, fn
+
+
+def test_cxx_wrapper_header_compiles(tmp_path):
+    """include/orbx_cxx.hpp (the ORB_SLAM2::ORBextractor / ORBmatcher stand-ins) must compile as
+    C++11 against OpenCV-shaped headers; the oracle's cv shim stands in for OpenCV here."""
+    src = tmp_path / "t.cpp"
+    src.write_text('#include "orbx_cxx.hpp"\n'
+                   'int main(){ ORB_SLAM2::ORBextractor e(1000,1.2f,8,20,7); ORB_SLAM2::ORBmatcher m(0.9f,true);\n'
+                   ' std::vector<cv::KeyPoint> k; cv::Mat img, d; e(img, cv::Mat(), k, d); return e.GetLevels()==8 ? 0 : 1; }\n')
+    r = subprocess.run(["g++", "-std=gnu++14", "-fsyntax-only", "-I", os.path.join(ROOT, "include"),
+                        "-I", os.path.join(ROOT, "oracle", "cvshim"), str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
