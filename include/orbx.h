@@ -154,6 +154,27 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
                                  int cap, int th, float nnratio, int check_orientation, int strict_lt,
                                  int* matches12, int* n_matches, int on_device, void* stream);
 
+/* The brute-force search of orbx_knn_ratio_batch for ONE pair, for callers that must not
+ * allocate.  It has no counterpart in the reference.  Some callers cannot afford or are not
+ * allowed a CUDA allocation on this path: a tracking thread with a per-frame deadline
+ * (cudaMalloc/cudaFree serialise on a device-wide lock and may stall behind another thread), a
+ * process whose device memory is fully owned by a pool, a plug-in host that audits allocations.
+ * orbx_knn_ratio_batch takes its scratch from cudaMallocAsync; this entry point calls no
+ * cudaMalloc, cudaFree or any other allocating routine.  Its scratch is a fixed 20 KiB array that
+ * is part of the library image: every GPU that loads liborbx.so holds it until the process exits.
+ *   - all pointers are DEVICE pointers (inputs descA/angA/descB/angB, outputs matches12[nA] and
+ *     n_matches[1]); the call is asynchronous on `stream`
+ *   - at most ORBX_NOALLOC_MAX_FEATURES features per side, otherwise ORBX_ERR_CAPACITY
+ *   - the first call on each device looks up the array's device address and raises the kernel's
+ *     shared-memory limit; make that first call outside any stream capture
+ *   - all calls on one GPU share the array (it keeps the last call's contents; the kernel
+ *     re-clears what it needs zeroed): calls that overlap on the GPU race, so order them */
+#define ORBX_NOALLOC_MAX_FEATURES 4096
+orbx_status orbx_knn_ratio_noalloc(const uint8_t* descA, const float* angA, int nA, const uint8_t* descB,
+                                   const float* angB, int nB, int th, float nnratio,
+                                   int check_orientation, int strict_lt, int* matches12,
+                                   int* n_matches, void* stream);
+
 /* ---- misc -------------------------------------------------------------------------------- */
 
 /* Per-stage device timing for roofline reports (no counterpart in the reference, which only

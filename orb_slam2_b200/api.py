@@ -43,7 +43,7 @@ EXPORTS = ["orbx_extractor_create", "orbx_extractor_destroy", "orbx_get_tables",
            "orbx_download_level", "orbx_debug_candidates", "orbx_debug_level_keys",
            "orbx_stereo_match_batch", "orbx_hamming256", "orbx_search_init_batch", "orbx_knn_ratio_batch",
            "orbx_last_error_string", "orbx_kernel_launch_count", "orbx_version", "orbx_set_profiling",
-           "orbx_get_profile", "orbx_stream_synchronize"]
+           "orbx_get_profile", "orbx_stream_synchronize", "orbx_knn_ratio_noalloc"]
 
 STAGES = ["pyramid", "fast", "quadtree", "describe", "stereo_match", "stereo_median"]
 
@@ -86,6 +86,8 @@ def lib():
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_stream_synchronize.argtypes = [C.c_void_p]
+        L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                             C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]
         L.orbx_get_profile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _LIB = L

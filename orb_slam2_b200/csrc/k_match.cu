@@ -238,4 +238,128 @@ int launch_knn_ratio(const KnnArgs& a, cudaStream_t st) {
   return 1;
 }
 
+// ------------------------------------------------------------------------------------------
+// K7 without any allocation (orbx_knn_ratio_noalloc, include/orbx.h).
+//
+// Who needs this: code that runs where the CUDA allocator must not be touched — a tracking
+// thread with a hard per-frame deadline (cudaMalloc/cudaFree take a device-wide lock and can
+// stall for milliseconds behind another thread's allocation), a process that has handed all of
+// its device memory to a pool and forbids further driver allocations, or a plug-in loaded into a
+// host that audits allocations.  The batched entry point above obtains its scratch with
+// cudaMallocAsync; this one keeps the scratch in a fixed array that is part of the library image.
+//
+// The array below is that scratch: one rotation-histogram bin per A feature (int) followed by one
+// "already matched" flag per B feature (byte).  It exists once per GPU that loads liborbx.so and
+// stays until the process exits; every call on that GPU uses the same bytes.  Consequences:
+//   * sizes are capped at kNoAllocMax features per side; larger inputs are rejected
+//   * the array still holds the previous call's contents, so the kernel clears the flags it
+//     relies on being zero before it reads them (the bins are written before they are read)
+//   * two calls that overlap on the GPU (different streams, or different host threads without
+//     ordering) race on the array; serialise them
+// In host code `g_knn_static` is only a handle for the runtime, not a device address: the kernel
+// must be given the address that cudaGetSymbolAddress reports for the current device.
+constexpr int kNoAllocMax = 4096;   // features per side; scratch = 4096*4 + 4096 bytes = 20 KiB per GPU
+static __device__ __align__(256) unsigned char g_knn_static[kNoAllocMax * sizeof(int) + kNoAllocMax];
+
+__global__ void __launch_bounds__(kKnnThreads) k_knn_ratio_static(const uint32_t* __restrict__ dA, const float* __restrict__ angA, int nA,
+                                                                  const uint32_t* __restrict__ dB, const float* __restrict__ angB, int nB,
+                                                                  int th, float ratio, int checkOri, int strict, int* m12, int* nm,
+                                                                  unsigned char* scratch, int capPad) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint32_t* Bt = reinterpret_cast<uint32_t*>(smem);                 // [8][capPad] transposed B descriptors
+  int* binof = reinterpret_cast<int*>(scratch);                     // [kNoAllocMax]
+  unsigned char* used = scratch + kNoAllocMax * sizeof(int);        // [kNoAllocMax], must start at 0
+  __shared__ unsigned s_key[kKnnThreads / 32];
+  __shared__ int s_sec[kKnnThreads / 32];
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_nm;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int idx = tid; idx < nB * 8; idx += kKnnThreads) { const int j = idx >> 3, w = idx & 7; Bt[w * capPad + j] = __ldg(dB + idx); }
+  for (int j = tid; j < nB; j += kKnnThreads) used[j] = 0;          // stale flags from the previous call
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (tid == 0) s_nm = 0;
+  __syncthreads();
+  for (int i = 0; i < nA; ++i) {
+    uint32_t q[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) q[w] = __ldg(dA + (size_t)i * 8 + w);
+    unsigned b1 = 256u << 16;
+    int b2 = 256;
+    for (int j = tid; j < nB; j += kKnnThreads) {
+      if (used[j]) continue;
+      int d = 0;
+#pragma unroll
+      for (int w = 0; w < 8; w += 2)
+        d += __popcll(((unsigned long long)(q[w + 1] ^ Bt[(w + 1) * capPad + j]) << 32) | (q[w] ^ Bt[w * capPad + j]));
+      const unsigned key = ((unsigned)d << 16) | (unsigned)j;
+      if (d < (int)(b1 >> 16)) { b2 = (int)(b1 >> 16); b1 = key; }
+      else if (d < b2) b2 = d;
+    }
+    const unsigned wmin = __reduce_min_sync(0xffffffffu, b1);
+    const int wsec = (int)__reduce_min_sync(0xffffffffu, (unsigned)(b1 == wmin ? b2 : (int)(b1 >> 16)));
+    if (lane == 0) { s_key[warp] = wmin; s_sec[warp] = wsec; }
+    __syncthreads();
+    if (tid == 0) {
+      unsigned g = s_key[0];
+      int own = 0;
+      for (int w = 1; w < kKnnThreads / 32; ++w) if (s_key[w] < g) { g = s_key[w]; own = w; }
+      int sec = s_sec[own];
+      for (int w = 0; w < kKnnThreads / 32; ++w) if (w != own) sec = min(sec, (int)(s_key[w] >> 16));
+      const int best = (int)(g >> 16), bi = g & 0xFFFF;
+      int m = -1, bin = -1;
+      const bool pass = strict ? best < th : best <= th;
+      if (pass && (float)best < __fmul_rn(ratio, (float)sec)) {
+        m = bi; used[bi] = 1; s_nm += 1;
+        if (checkOri) { bin = rot_bin(angA[i], angB[bi]); s_hist[bin] += 1; }
+      }
+      m12[i] = m; binof[i] = bin;
+    }
+    __syncthreads();
+  }
+  if (checkOri) {
+    int k_a, k_b, k_c;
+    three_maxima(s_hist, k_a, k_b, k_c);
+    int drop = 0;
+    for (int i = tid; i < nA; i += kKnnThreads) {
+      const int b = binof[i];
+      if (b >= 0 && b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
+    }
+    if (drop) atomicSub(&s_nm, drop);
+    __syncthreads();
+  }
+  if (tid == 0) *nm = s_nm;
+}
+
 }  // namespace orbx
+
+// Device address of the static scratch, looked up once per device (with that device current).
+static unsigned char* g_knn_static_addr[64] = {};
+
+extern "C" orbx_status orbx_knn_ratio_noalloc(const uint8_t* descA, const float* angA, int nA, const uint8_t* descB,
+                                              const float* angB, int nB, int th, float nnratio, int check_orientation,
+                                              int strict_lt, int* matches12, int* n_matches, void* stream) {
+  using namespace orbx;
+  if (!descA || !angA || !descB || !angB || !matches12 || !n_matches) return set_error(ORBX_ERR_BAD_ARG, "null argument");
+  if (nA < 0 || nB < 0) return set_error(ORBX_ERR_BAD_ARG, "negative feature count");
+  if (nA > kNoAllocMax || nB > kNoAllocMax)
+    return set_error(ORBX_ERR_CAPACITY, "orbx_knn_ratio_noalloc handles at most 4096 features per side (fixed static scratch)");
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return set_error(ORBX_ERR_CUDA, "cudaGetDevice failed");
+  const int capPad = (kNoAllocMax + 31) & ~31;
+  const size_t smem = (size_t)capPad * 32;
+  if (!g_knn_static_addr[dev]) {   // one-time set-up for this device: allocates nothing, but must precede stream capture
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_knn_static);
+    if (e != cudaSuccess || !p) return set_error(ORBX_ERR_CUDA, cudaGetErrorString(e));
+    e = cudaFuncSetAttribute(k_knn_ratio_static, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return set_error(ORBX_ERR_CUDA, cudaGetErrorString(e));
+    g_knn_static_addr[dev] = static_cast<unsigned char*>(p);
+  }
+  k_knn_ratio_static<<<1, kKnnThreads, smem, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint32_t*>(descA), angA, nA, reinterpret_cast<const uint32_t*>(descB), angB, nB, th, nnratio,
+      check_orientation, strict_lt, matches12, n_matches, g_knn_static_addr[dev], capPad);
+  count_launches(1);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error(ORBX_ERR_CUDA, cudaGetErrorString(e));
+  return ORBX_OK;
+}

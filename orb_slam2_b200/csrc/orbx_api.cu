@@ -53,6 +53,11 @@ struct DeviceGuard {
 
 }  // namespace
 
+namespace orbx {
+orbx_status set_error(orbx_status s, const char* msg) { return fail(s, msg); }
+void count_launches(int n) { g_launches += n; }
+}  // namespace orbx
+
 struct orbx_extractor {
   orbx_params P{};
   int device = 0, max_w = 0, max_h = 0, max_batch = 0, nlevels = 0;

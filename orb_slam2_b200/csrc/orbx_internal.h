@@ -104,4 +104,8 @@ struct KnnArgs {
 };
 int launch_knn_ratio(const KnnArgs& a, cudaStream_t st);
 
+// shared by the extern "C" entry points that live outside orbx_api.cu
+orbx_status set_error(orbx_status s, const char* msg);
+void count_launches(int n);
+
 }  // namespace orbx
