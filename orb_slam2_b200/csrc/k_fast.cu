@@ -29,7 +29,7 @@ __device__ __forceinline__ uint32_t vmin3(uint32_t a, uint32_t b, uint32_t c) { 
 __device__ __forceinline__ uint32_t vmax3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
 
 // Arc score of the pixel at c (shared-memory window, row pitch wp).  Returns S in [-255, 255].
-__device__ __forceinline__ int arc_score(const uint8_t* c, int wp) {
+__device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
   const int v = c[0];
   const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
   uint32_t P[16];
@@ -58,12 +58,13 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, int wp) {
   return max((int)(s & 0xFFFF), (int)(s >> 16)) - 256;
 }
 
-// smem per warp: window [win_rows][win_pitch] (reused as the code map) + S map [(ih+2)][s_pitch]
-__global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, int first_slot, int n, int win_pitch,
-                                                                int win_rows, int s_pitch, int s_rows) {
+// smem per warp: window [win_rows][WP] (pixels keep their global 4-byte phase so rows are staged
+// with aligned 32-bit loads) + S map [win_rows-6][WP].
+template <int WP>
+__global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, int first_slot, int n, int win_rows) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int win_bytes = win_pitch * win_rows, s_bytes = s_pitch * s_rows;
+  const int win_bytes = WP * win_rows, s_bytes = WP * (win_rows - 6);
   uint8_t* win = smem + (size_t)warp * (win_bytes + s_bytes);
   uint8_t* smap = win + win_bytes;
 
@@ -86,49 +87,66 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
   }
   const int iw = ww - 6, ih = hh - 6;
 
-  // stage the window; clear the S map (its 1-px rim stays 0 = "not a corner")
-  const uint8_t* roi = L.pyr + g.plane_off + (size_t)slot * g.plane_stride + (size_t)kEdge * g.pitch + kEdge;
-  for (int r = 0; r < hh; ++r) {
-    const uint8_t* srow = roi + (size_t)(y0 + r) * g.pitch + x0;
-    for (int x = lane; x < ww; x += 32) win[r * win_pitch + x] = __ldg(srow + x);
+  // stage the window with aligned word loads (plane base is 256-B aligned, pitch a multiple of 16)
+  const int phase = (kEdge + x0) & 3;
+  {
+    const uint8_t* src = L.pyr + g.plane_off + (size_t)slot * g.plane_stride + (size_t)(kEdge + y0) * g.pitch + (kEdge + x0 - phase);
+    const int wpr = (ww + phase + 3) >> 2;          // words per row
+    const int total = wpr * hh;
+    for (int i = lane; i < total; i += 32) {
+      const int r = i / wpr, w = i - r * wpr;
+      reinterpret_cast<uint32_t*>(win + r * WP)[w] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * g.pitch) + w);
+    }
   }
-  for (int i = lane; i < (s_bytes >> 2); i += 32) reinterpret_cast<uint32_t*>(smap)[i] = 0u;
   __syncwarp();
 
-  // pass 1: S for every tested pixel
-  for (int cb = 0; cb < iw; cb += 32) {
-    const int xx = cb + lane;
+  // pass 1: S for every tested pixel; per lane (= column) a bit mask of rows with S > minTh
+  unsigned long long hot[2] = {0ull, 0ull};
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch) {
+    const int xx = ch * 32 + lane;
     if (xx < iw) {
+      const uint8_t* cptr = win + 3 * WP + phase + xx + 3;
+      uint8_t* sptr = smap + xx;
+      unsigned long long m = 0ull;
       for (int yy = 0; yy < ih; ++yy) {
-        const int s = arc_score(win + (yy + 3) * win_pitch + xx + 3, win_pitch);
-        smap[(yy + 1) * s_pitch + xx + 1] = (uint8_t)max(s, 0);
+        const int sc = arc_score(cptr, WP);
+        sptr[0] = (uint8_t)max(sc, 0);
+        m |= (unsigned long long)(sc > L.min_th) << yy;
+        cptr += WP; sptr += WP;
       }
+      hot[ch] = m;
     }
   }
   __syncwarp();
 
-  // pass 2: strict 3x3 maxima -> code 2 (corner at iniTh), 1 (corner at minTh only), 0
-  uint8_t* code = win;  // the window is dead from here on
-  int cnt_ini = 0, cnt_min = 0;
-  for (int yy = 0; yy < ih; ++yy)
-    for (int cb = 0; cb < iw; cb += 32) {
-      const int xx = cb + lane;
-      int cd = 0;
-      if (xx < iw) {
-        const uint8_t* p = smap + (yy + 1) * s_pitch + xx + 1;
-        const int s = p[0];
-        if (s > L.min_th) {
-          const bool mx = p[-1] < s && p[1] < s && p[-s_pitch - 1] < s && p[-s_pitch] < s && p[-s_pitch + 1] < s &&
-                          p[s_pitch - 1] < s && p[s_pitch] < s && p[s_pitch + 1] < s;
-          if (mx) cd = s > L.ini_th ? 2 : 1;
-        }
-        code[yy * iw + xx] = (uint8_t)cd;
+  // pass 2 (sparse): strict 3x3 maxima among the hot pixels
+  unsigned long long k_ini[2] = {0ull, 0ull}, k_min[2] = {0ull, 0ull};
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch) {
+    const int xx = ch * 32 + lane;
+    unsigned long long m = hot[ch];
+    while (m) {
+      const int yy = __ffsll((long long)m) - 1;
+      m &= m - 1;
+      const uint8_t* p = smap + yy * WP + xx;
+      const int sc = p[0];
+      const bool up = yy > 0, dn = yy < ih - 1, lf = xx > 0, rt = xx < iw - 1;
+      bool mx = true;
+      if (lf) mx = mx && p[-1] < sc;
+      if (rt) mx = mx && p[1] < sc;
+      if (up) { mx = mx && p[-WP] < sc; if (lf) mx = mx && p[-WP - 1] < sc; if (rt) mx = mx && p[-WP + 1] < sc; }
+      if (dn) { mx = mx && p[WP] < sc; if (lf) mx = mx && p[WP - 1] < sc; if (rt) mx = mx && p[WP + 1] < sc; }
+      if (mx) {
+        k_min[ch] |= 1ull << yy;
+        if (sc > L.ini_th) k_ini[ch] |= 1ull << yy;
       }
-      cnt_ini += __popc(__ballot_sync(0xffffffffu, cd == 2));
-      cnt_min += __popc(__ballot_sync(0xffffffffu, cd >= 1));
     }
-  const int need = cnt_ini > 0 ? 2 : 1;              // src/ORBextractor.cc:812: retry iff empty
-  const int total = cnt_ini > 0 ? cnt_ini : cnt_min;
+  }
+  const int cnt_ini = __reduce_add_sync(0xffffffffu, __popcll(k_ini[0]) + __popcll(k_ini[1]));
+  const int cnt_min = __reduce_add_sync(0xffffffffu, __popcll(k_min[0]) + __popcll(k_min[1]));
+  const bool use_ini = cnt_ini > 0;                    // src/ORBextractor.cc:812: retry at minTh iff empty
+  const int total = use_ini ? cnt_ini : cnt_min;
   int base = 0;
   if (lane == 0) {
     if (total > 0) base = atomicAdd(L.poolcnt + slot * kMaxLevels + level, total);
@@ -136,33 +154,45 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
   }
   if (total == 0) return;
   base = __shfl_sync(0xffffffffu, base, 0);
-  __syncwarp();
+  const unsigned long long keep0 = use_ini ? k_ini[0] : k_min[0], keep1 = use_ini ? k_ini[1] : k_min[1];
+  const unsigned long long any = keep0 | keep1;
+  unsigned long long rows = ((unsigned long long)__reduce_or_sync(0xffffffffu, (unsigned)(any >> 32)) << 32) |
+                            __reduce_or_sync(0xffffffffu, (unsigned)any);
 
-  // pass 3: emit in pixel row-major order
+  // pass 3: emit in pixel row-major order (rows that hold a corner only)
   uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
   int run = 0;
-  for (int yy = 0; yy < ih; ++yy)
-    for (int cb = 0; cb < iw; cb += 32) {
-      const int xx = cb + lane;
-      const bool keep = xx < iw && code[yy * iw + xx] >= need;
+  while (rows) {
+    const int yy = __ffsll((long long)rows) - 1;
+    rows &= rows - 1;
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+      const bool keep = ((ch ? keep1 : keep0) >> yy) & 1ull;
       const uint32_t bal = __ballot_sync(0xffffffffu, keep);
       if (keep) {
+        const int xx = ch * 32 + lane;
         const int pos = base + run + __popc(bal & ((1u << lane) - 1u));
-        const int resp = (int)smap[(yy + 1) * s_pitch + xx + 1] - 1;
+        const int resp = (int)smap[yy * WP + xx] - 1;
         if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
       }
       run += __popc(bal);
     }
+  }
 }
 
 int launch_fast(const DeviceLayout& L, const LevelGeom* hg, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
   (void)hg;
-  const int win_pitch = (win_w + 3) & ~3, win_rows = win_h;
-  const int s_pitch = ((win_w - 6 + 2) + 3) & ~3, s_rows = win_h - 6 + 2;
-  const size_t smem = (size_t)kFastWarps * (win_pitch * win_rows + s_pitch * s_rows);
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const long long cells = (long long)n * L.cells_per_slot;
-  k_fast_cells<<<(unsigned)((cells + kFastWarps - 1) / kFastWarps), kFastWarps * 32, smem, st>>>(L, first_slot, n, win_pitch, win_rows, s_pitch, s_rows);
+  const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
+  if (win_w + 6 <= 48) {   // a staged row (phase + width, rounded up to words) must fit the pitch
+    const size_t smem = (size_t)kFastWarps * 48 * (2 * win_h - 6);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_fast_cells<48><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
+  } else {
+    const size_t smem = (size_t)kFastWarps * 72 * (2 * win_h - 6);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<72>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_fast_cells<72><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
+  }
   return 1;
 }
 

@@ -6,8 +6,8 @@
 // point: 11-bit tap weights (generated on the host in float exactly as OpenCV does, see
 // orbx_api.cu), int32 horizontal pass, ((b*(H>>4))>>16 ... +2)>>2 vertical pass.
 //
-// Design: one thread produces 16 consecutive bytes of one bordered row and stores them as one
-// 128-bit word.  A border pixel equals the interior pixel at the reflected coordinate, so it is
+// Design: one thread produces 4 (level 0: 16) consecutive bytes of one bordered row and stores
+// them as one word.  A border pixel equals the interior pixel at the reflected coordinate, so it is
 // computed with the same formula instead of being copied afterwards — no intra-level dependency,
 // one launch per level for the whole batch.  HBM-bound in principle (reads L2-hot source rows).
 #include "orbx_internal.h"
@@ -42,44 +42,41 @@ __global__ void __launch_bounds__(256) k_border_level0(DeviceLayout L, const uin
   *reinterpret_cast<uint4*>(dst) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
 }
 
+// One thread = 4 consecutive output bytes (one 32-bit store): a warp writes 128 contiguous bytes and
+// reads 32 contiguous tap entries (two 128-bit loads per thread), so every request is coalesced.
+// The tap tables are indexed by BORDERED coordinates (reflection and the zero pad columns are
+// baked in on the host), so the kernel has no branches.
 __global__ void __launch_bounds__(256) k_resize_level(DeviceLayout L, int level, int first_slot, int n) {
   const LevelGeom g = L.geom[level];
   const LevelGeom gs = L.geom[level - 1];
-  const int vec_per_row = g.pitch >> 4;
-  const long long per_img = (long long)vec_per_row * g.rows;
+  const int wpr = g.pitch >> 2;                       // words per bordered row
+  const long long per_img = (long long)wpr * g.rows;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= per_img * n) return;
   const int img = (int)(tid / per_img);
   const int rem = (int)(tid - (long long)img * per_img);
-  const int by = rem / vec_per_row, bx0 = (rem - by * vec_per_row) << 4;
-  const ResizeTap ty = L.taps[g.ytab_off + reflect101(by - kEdge, g.h)];
+  const int by = rem / wpr, bx0 = (rem - by * wpr) << 2;
+  const ResizeTap ty = L.taps[g.ytab_off + by];
   const uint8_t* sroi = L.pyr + gs.plane_off + (size_t)(first_slot + img) * gs.plane_stride + (size_t)kEdge * gs.pitch + kEdge;
   const uint8_t* p0 = sroi + (size_t)ty.ofs * gs.pitch;
   const uint8_t* p1 = sroi + (size_t)min(ty.ofs + 1, gs.h - 1) * gs.pitch;
-  const ResizeTap* xt = L.taps + g.xtab_off;
+  const uint4* xt = reinterpret_cast<const uint4*>(L.taps + g.xtab_off + bx0);
+  const uint4 q0 = __ldg(xt), q1 = __ldg(xt + 1);
+  const int ofs[4] = {(int)q0.x, (int)q0.z, (int)q1.x, (int)q1.z};
+  const uint32_t wts[4] = {q0.y, q0.w, q1.y, q1.w};
   const int b0 = ty.a0, b1 = ty.a1;
-  uint32_t wds[4];
+  uint32_t v = 0;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    uint32_t v = 0;
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int bx = bx0 + q * 4 + b;
-      uint32_t px = 0;
-      if (bx < g.w + 2 * kEdge) {
-        const ResizeTap tx = xt[reflect101(bx - kEdge, g.w)];
-        const int s0 = tx.ofs, s1 = min(tx.ofs + 1, gs.w - 1);
-        const int h0 = (int)p0[s0] * tx.a0 + (int)p0[s1] * tx.a1;
-        const int h1 = (int)p1[s0] * tx.a0 + (int)p1[s1] * tx.a1;
-        int r = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-        px = (uint32_t)min(max(r, 0), 255);
-      }
-      v |= px << (8 * b);
-    }
-    wds[q] = v;
+  for (int b = 0; b < 4; ++b) {
+    const int a0 = (short)(wts[b] & 0xffff), a1 = (short)(wts[b] >> 16);
+    const int s0 = ofs[b], s1 = min(s0 + 1, gs.w - 1);
+    const int h0 = (int)p0[s0] * a0 + (int)p0[s1] * a1;
+    const int h1 = (int)p1[s0] * a0 + (int)p1[s1] * a1;
+    const int r = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+    v |= (uint32_t)min(max(r, 0), 255) << (8 * b);
   }
   uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)by * g.pitch + bx0;
-  *reinterpret_cast<uint4*>(dst) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+  *reinterpret_cast<uint32_t*>(dst) = v;
 }
 
 int launch_pyramid(const DeviceLayout& L, const LevelGeom* hg, const uint8_t* src, int src_pitch,
@@ -91,7 +88,7 @@ int launch_pyramid(const DeviceLayout& L, const LevelGeom* hg, const uint8_t* sr
     ++launches;
   }
   for (int l = 1; l < L.nlevels; ++l) {
-    long long total = (long long)(hg[l].pitch >> 4) * hg[l].rows * n;
+    long long total = (long long)(hg[l].pitch >> 2) * hg[l].rows * n;
     k_resize_level<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, l, first_slot, n);
     ++launches;
   }

@@ -147,12 +147,20 @@ orbx_status geometry(const orbx_extractor* e, int w, int h, int nslots, LevelGeo
     q.plane_off = pyr_off;
     pyr_off += q.plane_stride * nslots;
     if (l > 0) {
-      q.xtab_off = t->taps; q.ytab_off = t->taps + q.w;
-      t->taps += q.w + q.h;
+      // tap tables in BORDERED coordinates: entry bx holds the taps of ROI column reflect101(bx-19),
+      // pad columns get zero weights (-> pixel 0); 4-entry (32-byte) aligned for 128-bit loads
+      q.xtab_off = t->taps; q.ytab_off = t->taps + q.pitch;
+      t->taps += q.pitch + (int)align_up(q.rows, 4);
       if (taps) {
         taps->resize(t->taps);
-        resize_taps(q.w, g[l - 1].w, taps->data() + q.xtab_off);
-        resize_taps(q.h, g[l - 1].h, taps->data() + q.ytab_off);
+        std::vector<ResizeTap> tx(q.w), ty(q.h);
+        resize_taps(q.w, g[l - 1].w, tx.data());
+        resize_taps(q.h, g[l - 1].h, ty.data());
+        ResizeTap zero; zero.ofs = 0; zero.a0 = 0; zero.a1 = 0;
+        for (int bx = 0; bx < q.pitch; ++bx)
+          (*taps)[q.xtab_off + bx] = bx < q.w + 2 * kEdge ? tx[reflect101(bx - kEdge, q.w)] : zero;
+        for (int by = 0; by < (int)align_up(q.rows, 4); ++by)
+          (*taps)[q.ytab_off + by] = by < q.rows ? ty[reflect101(by - kEdge, q.h)] : zero;
       }
     }
     // FAST cells
