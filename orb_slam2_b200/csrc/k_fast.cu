@@ -28,23 +28,22 @@ constexpr int kFastWarps = 4;
 __device__ __forceinline__ uint32_t vmin3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_s16x2(a, b, c); }
 __device__ __forceinline__ uint32_t vmax3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
 
+// Ring pixel k of the pixel at c, packed for both polarities: lo = d_k + 256, hi = -d_k + 256.
+#define ORBX_RING(k, ptr, off) P[k] = (ptr)[off] * 0xFFFFu + base
+
 // Arc score of the pixel at c (shared-memory window, row pitch wp).  Returns S in [-255, 255].
-__device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
-  const int v = c[0];
-  const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
-  uint32_t P[16];
+// P[0], P[4], P[8], P[12] (the compass points) must already be filled in.
+__device__ __forceinline__ int arc_score_rest(const uint8_t* c, const int wp, const uint32_t base, uint32_t (&P)[16]) {
   const uint8_t* r3 = c + 3 * wp;
   const uint8_t* r2 = c + 2 * wp;
   const uint8_t* r1 = c + wp;
   const uint8_t* q1 = c - wp;
   const uint8_t* q2 = c - 2 * wp;
   const uint8_t* q3 = c - 3 * wp;
-  P[0] = r3[0] * 0xFFFFu + base;   P[1] = r3[1] * 0xFFFFu + base;   P[2] = r2[2] * 0xFFFFu + base;
-  P[3] = r1[3] * 0xFFFFu + base;   P[4] = c[3] * 0xFFFFu + base;    P[5] = q1[3] * 0xFFFFu + base;
-  P[6] = q2[2] * 0xFFFFu + base;   P[7] = q3[1] * 0xFFFFu + base;   P[8] = q3[0] * 0xFFFFu + base;
-  P[9] = q3[-1] * 0xFFFFu + base;  P[10] = q2[-2] * 0xFFFFu + base; P[11] = q1[-3] * 0xFFFFu + base;
-  P[12] = c[-3] * 0xFFFFu + base;  P[13] = r1[-3] * 0xFFFFu + base; P[14] = r2[-2] * 0xFFFFu + base;
-  P[15] = r3[-1] * 0xFFFFu + base;
+  ORBX_RING(1, r3, 1);   ORBX_RING(2, r2, 2);    ORBX_RING(3, r1, 3);
+  ORBX_RING(5, q1, 3);   ORBX_RING(6, q2, 2);    ORBX_RING(7, q3, 1);
+  ORBX_RING(9, q3, -1);  ORBX_RING(10, q2, -2);  ORBX_RING(11, q1, -3);
+  ORBX_RING(13, r1, -3); ORBX_RING(14, r2, -2);  ORBX_RING(15, r3, -1);
   uint32_t m3[16];
 #pragma unroll
   for (int k = 0; k < 16; ++k) m3[k] = vmin3(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
@@ -57,10 +56,25 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
   uint32_t s = vmax3(g, h, h);
   return max((int)(s & 0xFFFF), (int)(s >> 16)) - 256;
 }
+// Compass pre-test: any 9-arc of the 16-ring holds two neighbouring compass points, so
+// S <= max over the 4 neighbouring compass pairs of min(d) (per polarity).  Fills P[0,4,8,12].
+__device__ __forceinline__ int compass_bound(const uint8_t* c, const int wp, const uint32_t base, uint32_t (&P)[16]) {
+  ORBX_RING(0, c + 3 * wp, 0); ORBX_RING(4, c, 3); ORBX_RING(8, c - 3 * wp, 0); ORBX_RING(12, c, -3);
+  const uint32_t a = vmin3(P[0], P[4], P[4]), b = vmin3(P[4], P[8], P[8]), d = vmin3(P[8], P[12], P[12]), e = vmin3(P[12], P[0], P[0]);
+  const uint32_t m = vmax3(vmax3(a, b, d), e, e);
+  return max((int)(m & 0xFFFF), (int)(m >> 16)) - 256;
+}
+__device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
+  const int v = c[0];
+  const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
+  uint32_t P[16];
+  compass_bound(c, wp, base, P);
+  return arc_score_rest(c, wp, base, P);
+}
 
 // smem per warp: window [win_rows][WP] (pixels keep their global 4-byte phase so rows are staged
 // with aligned 32-bit loads) + S map [win_rows-6][WP].
-template <int WP>
+template <int WP, bool WIDE>
 __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, int first_slot, int n, int win_rows) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -100,6 +114,42 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
   }
   __syncwarp();
 
+  unsigned long long k_ini[2] = {0ull, 0ull}, k_min[2] = {0ull, 0ull};
+  if (!WIDE) {
+    // Narrow cells (iw <= 32): lane = column, rows streamed top to bottom.  The 3x3 maximum test of
+    // row yy-1 runs as soon as row yy is scored, with the neighbour columns read by warp shuffles,
+    // so no S map is written; only kept corners store their score (for the response).
+    // Pixels that fail the compass pre-test at minTh cannot be corners: they score 0, and a whole
+    // warp-row of them skips the 16-point evaluation.
+    const bool act = lane < iw;
+    const uint8_t* cptr = win + 3 * WP + phase + lane + 3;
+    int a = 0, b = 0;
+    for (int yy = 0; yy <= ih; ++yy) {
+      int cur = 0;
+      if (yy < ih) {
+        const int v = cptr[0];
+        const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
+        uint32_t P[16];
+        const bool need = act && compass_bound(cptr, WP, base, P) > L.min_th;
+        if (__any_sync(0xffffffffu, need)) {
+          const int sc = arc_score_rest(cptr, WP, base, P);
+          cur = need ? max(sc, 0) : 0;
+        }
+        cptr += WP;
+      }
+      const int t3 = max(max(a, b), cur);
+      int lft = __shfl_up_sync(0xffffffffu, t3, 1), rgt = __shfl_down_sync(0xffffffffu, t3, 1);
+      if (lane == 0) lft = 0;
+      if (lane == 31) rgt = 0;
+      const int nb = max(max(lft, rgt), max(a, cur));
+      if (b > nb && b > L.min_th) {
+        k_min[0] |= 1ull << (yy - 1);
+        if (b > L.ini_th) k_ini[0] |= 1ull << (yy - 1);
+        smap[(yy - 1) * WP + lane] = (uint8_t)b;
+      }
+      a = b; b = cur;
+    }
+  } else {
   // pass 1: S for every tested pixel; per lane (= column) a bit mask of rows with S > minTh
   unsigned long long hot[2] = {0ull, 0ull};
 #pragma unroll
@@ -121,7 +171,6 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
   __syncwarp();
 
   // pass 2 (sparse): strict 3x3 maxima among the hot pixels
-  unsigned long long k_ini[2] = {0ull, 0ull}, k_min[2] = {0ull, 0ull};
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     const int xx = ch * 32 + lane;
@@ -143,6 +192,8 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
       }
     }
   }
+  }
+  __syncwarp();
   const int cnt_ini = __reduce_add_sync(0xffffffffu, __popcll(k_ini[0]) + __popcll(k_ini[1]));
   const int cnt_min = __reduce_add_sync(0xffffffffu, __popcll(k_min[0]) + __popcll(k_min[1]));
   const bool use_ini = cnt_ini > 0;                    // src/ORBextractor.cc:812: retry at minTh iff empty
@@ -180,19 +231,22 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
   }
 }
 
+template <int WP, bool WIDE>
+static void launch_fast_t(const DeviceLayout& L, int first_slot, int n, int win_h, unsigned grid, cudaStream_t st) {
+  const size_t smem = (size_t)kFastWarps * WP * (2 * win_h - 6);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_fast_cells<WP, WIDE><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
+}
+
 int launch_fast(const DeviceLayout& L, const LevelGeom* hg, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
   (void)hg;
   const long long cells = (long long)n * L.cells_per_slot;
   const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
-  if (win_w + 6 <= 48) {   // a staged row (phase + width, rounded up to words) must fit the pitch
-    const size_t smem = (size_t)kFastWarps * 48 * (2 * win_h - 6);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_fast_cells<48><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
-  } else {
-    const size_t smem = (size_t)kFastWarps * 72 * (2 * win_h - 6);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<72>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_fast_cells<72><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
-  }
+  // a staged row (phase + width, rounded up to words) must fit the pitch; cells of at most 32
+  // tested columns take the shuffle-based path
+  if (win_w - 6 <= 32) launch_fast_t<48, false>(L, first_slot, n, win_h, grid, st);
+  else if (win_w + 6 <= 48) launch_fast_t<48, true>(L, first_slot, n, win_h, grid, st);
+  else launch_fast_t<72, true>(L, first_slot, n, win_h, grid, st);
   return 1;
 }
 

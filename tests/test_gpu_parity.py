@@ -135,6 +135,22 @@ def test_strided_input_and_getters(gx, oracle):
     assert pyr[0].shape == (h, w) and np.array_equal(pyr[0], view)
 
 
+@pytest.mark.parametrize("w,h,nf", [(366, 270, 600), (400, 300, 800), (1024, 768, 1500), (331, 250, 500)])
+def test_odd_shapes_exercise_every_fast_variant(gx, oracle, w, h, nf):
+    """Cell widths of 33-36 and 37+ px take the wide FAST kernels (366x270 and 400x300 have such
+    cells on their top levels); 1024x768 is a 4:3 shape with one quad-tree root."""
+    img = synth.mono_frame(33, w, h)
+    G = _ext(gx, w, h, nf)
+    E = oracle.Extractor(nf)
+    rk, rd = E.extract(img)
+    gk, gd = G(img)
+    for l in range(8):
+        c = E.candidates(l)
+        ref = np.stack([c["x"], c["y"], c["response"]], 1).astype(np.int32)
+        assert np.array_equal(G.debug_candidates(0, l), ref), f"level {l}"
+    assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+
+
 def test_edge_cases(gx):
     G = _ext(gx, 640, 480, 1000)
     k, d = G(np.zeros((0, 0), np.uint8))                 # empty image: silent return
