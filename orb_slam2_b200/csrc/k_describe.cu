@@ -19,11 +19,14 @@
 namespace orbx {
 
 constexpr int kDescWarps = 4;
-constexpr int kTileR = 43, kTileP = 48;   // raw tile rows / pitch, centre (21,21)
-constexpr int kHpP = 40;                  // horizontal-pass pitch (uint16), 43 rows x 37 cols
-constexpr int kBlP = 40, kBlR = 37;       // blurred tile pitch / rows, centre (18,18)
-constexpr int kWarpSmem = kTileR * kTileP + kTileR * kHpP * 2 + kBlR * kBlP;   // 2064 + 3440 + 1480
-static_assert(kWarpSmem % 8 == 0, "per-warp smem must keep 8-byte alignment");
+constexpr int kTileR = 43, kTileP = 48;   // raw tile rows / pitch; tile column 0 sits at smem column `phase`
+constexpr int kHtC = 40, kHtP = 46;       // horizontal pass, TRANSPOSED: [column][row] uint16, 46-entry pitch (bank-conflict free)
+constexpr int kBlP = 40, kBlR = 38;       // blurred tile pitch / rows (row 37 is scratch), centre (18, phase+18)
+constexpr int kWarpSmem = kTileR * kTileP + kHtC * kHtP * 2 + kBlR * kBlP;   // 2064 + 3680 + 1520
+static_assert(kWarpSmem % 16 == 0, "per-warp smem must keep 16-byte alignment");
+
+// 7x7 sigma-2 taps of cv2's 8-bit path, {18,34,48,56,48,34,18}/256, packed for dp4a / dp2a
+__device__ __forceinline__ unsigned pk4(unsigned a, unsigned b, unsigned c, unsigned d) { return a | (b << 8) | (c << 16) | (d << 24); }
 
 struct SinCosTab { double sign[4], hpi_inv, hpi, c0, c1, c2, c3, c4, s1, s2, s3; };
 __constant__ SinCosTab c_sincos[2] = {
@@ -84,8 +87,8 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, in
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* raw = smem + (size_t)warp * kWarpSmem;
-  uint16_t* hp = reinterpret_cast<uint16_t*>(raw + kTileR * kTileP);
-  uint8_t* bl = raw + kTileR * kTileP + kTileR * kHpP * 2;
+  uint16_t* ht = reinterpret_cast<uint16_t*>(raw + kTileR * kTileP);
+  uint8_t* bl = raw + kTileR * kTileP + kHtC * kHtP * 2;
 
   const int img = blockIdx.x / ctas_per_img;
   if (img >= n_img) return;
@@ -110,13 +113,18 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, in
   const uint32_t key = L.lvlkp[(size_t)slot * L.lvlkp_per_slot + g.lvl_kp_off + (j - lvl_first)];
   const int px = unpack_x(key), py = unpack_y(key), resp = unpack_r(key);
 
-  // stage the 43x43 raw tile whose centre is the keypoint (bordered-plane coords: +19)
+  // stage the 43x43 raw tile whose centre is the keypoint (bordered-plane coords: +19) with aligned
+  // 32-bit loads: 12 words per row starting at the 4-byte boundary below the tile's first column
   const uint8_t* plane = L.pyr + g.plane_off + (size_t)slot * g.plane_stride;
-  const uint8_t* src = plane + (size_t)(py + kEdge - 21) * g.pitch + (px + kEdge - 21);
-  for (int r = 0; r < kTileR; ++r) {
-    const uint8_t* s = src + (size_t)r * g.pitch;
-    raw[r * kTileP + lane] = __ldg(s + lane);
-    if (lane < kTileR - 32) raw[r * kTileP + 32 + lane] = __ldg(s + 32 + lane);
+  const int tx0 = px + kEdge - 21, phase = tx0 & 3;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(plane + (size_t)(py + kEdge - 21) * g.pitch + (tx0 - phase));
+    const int wpitch = g.pitch >> 2;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(raw);
+    for (int i = lane; i < kTileR * 12; i += 32) {
+      const int r = i / 12, w = i - r * 12;
+      dst[i] = __ldg(src + (size_t)r * wpitch + w);
+    }
   }
   __syncwarp();
 
@@ -125,7 +133,7 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, in
   if (lane < 2 * kHalfPatch + 1) {
     const int v = lane - kHalfPatch;
     const int d = umax[v < 0 ? -v : v];
-    const uint8_t* row = raw + (21 + v) * kTileP + 21;
+    const uint8_t* row = raw + (21 + v) * kTileP + phase + 21;
     int si = 0;
     for (int u = -d; u <= d; ++u) {
       const int I = row[u];
@@ -141,26 +149,57 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, in
   }
   const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-  // separable fixed-point blur of the 37x37 region the descriptor can reach
-  for (int idx = lane; idx < kTileR * 37; idx += 32) {
-    const int r = idx / 37, c = idx - r * 37;
-    const uint8_t* p = raw + r * kTileP + c;
-    hp[r * kHpP + c] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
+  // separable fixed-point blur of the region the descriptor can reach.
+  // Horizontal pass: one task = 4 adjacent smem columns of one row from 3 aligned words, 10 dp4a
+  // (the 7 taps slide over the packed bytes by shifting the coefficient vectors, not the data);
+  // results go to a transposed uint16 array so the vertical pass can pair rows in one word.
+  {
+    const unsigned A0 = pk4(18, 34, 48, 56), A1 = pk4(48, 34, 18, 0);
+    const unsigned B0 = pk4(0, 18, 34, 48), B1 = pk4(56, 48, 34, 18);
+    const unsigned C0 = pk4(0, 0, 18, 34), C1 = pk4(48, 56, 48, 34), C2 = pk4(18, 0, 0, 0);
+    const unsigned D0 = pk4(0, 0, 0, 18), D1 = pk4(34, 48, 56, 48), D2 = pk4(34, 18, 0, 0);
+    const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw);
+    for (int t = lane; t < kTileR * 10; t += 32) {
+      const int r = t / 10, gq = t - r * 10;
+      const uint32_t w0 = rw[r * 12 + gq], w1 = rw[r * 12 + gq + 1], w2 = rw[r * 12 + gq + 2];
+      uint16_t* o = ht + (4 * gq) * kHtP + r;
+      o[0] = (uint16_t)__dp4a(w1, A1, __dp4a(w0, A0, 0u));
+      o[kHtP] = (uint16_t)__dp4a(w1, B1, __dp4a(w0, B0, 0u));
+      o[2 * kHtP] = (uint16_t)__dp4a(w2, C2, __dp4a(w1, C1, __dp4a(w0, C0, 0u)));
+      o[3 * kHtP] = (uint16_t)__dp4a(w2, D2, __dp4a(w1, D1, __dp4a(w0, D0, 0u)));
+    }
   }
   __syncwarp();
-  for (int idx = lane; idx < kBlR * 37; idx += 32) {
-    const int r = idx / 37, c = idx - r * 37;
-    const uint16_t* p = hp + r * kHpP + c;
-    const uint32_t acc = 18u * (p[0] + p[6 * kHpP]) + 34u * (p[kHpP] + p[5 * kHpP]) + 48u * (p[2 * kHpP] + p[4 * kHpP]) +
-                         56u * p[3 * kHpP] + 32768u;
-    bl[r * kBlP + c] = (uint8_t)(acc >> 16);
+  // Vertical pass: one task = one column and half of the rows, walking down two output rows per
+  // step with a 4-word sliding window and 8 dp2a (u16 x u8).  Rounding constant rides in the
+  // accumulator.  37 columns x 2 halves = 74 tasks; consecutive lanes take consecutive columns.
+  {
+    const unsigned E0 = pk4(18, 34, 0, 0), E1 = pk4(48, 56, 0, 0), E2 = pk4(48, 34, 0, 0), E3 = pk4(18, 0, 0, 0);
+    const unsigned F0 = pk4(0, 18, 0, 0), F1 = pk4(34, 48, 0, 0), F2 = pk4(56, 48, 0, 0), F3 = pk4(34, 18, 0, 0);
+    for (int t = lane; t < 74; t += 32) {
+      const int half = t >= 37, col = phase + (half ? t - 37 : t);
+      const int r0 = half ? 18 : 0;
+      const uint32_t* hc = reinterpret_cast<const uint32_t*>(ht + col * kHtP + r0);
+      uint32_t W0 = hc[0], W1 = hc[1], W2 = hc[2];
+      uint8_t* o = bl + r0 * kBlP + col;
+#pragma unroll 2
+      for (int sidx = 0; sidx < 10; ++sidx) {
+        const uint32_t W3 = hc[sidx + 3];
+        const unsigned e = __dp2a_lo(W3, E3, __dp2a_lo(W2, E2, __dp2a_lo(W1, E1, __dp2a_lo(W0, E0, 32768u))));
+        const unsigned f = __dp2a_lo(W3, F3, __dp2a_lo(W2, F2, __dp2a_lo(W1, F1, __dp2a_lo(W0, F0, 32768u))));
+        o[0] = (uint8_t)(e >> 16);
+        o[kBlP] = (uint8_t)(f >> 16);
+        o += 2 * kBlP;
+        W0 = W1; W1 = W2; W2 = W3;
+      }
+    }
   }
   __syncwarp();
 
   // steered BRIEF: lane i produces descriptor byte i (tests 8i .. 8i+7)
   const float rad = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
   const float ca = libm_sincos(rad, 1), sb = libm_sincos(rad, 0);
-  const uint8_t* ctr = bl + 18 * kBlP + 18;
+  const uint8_t* ctr = bl + 18 * kBlP + phase + 18;
   uint32_t byte = 0;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
