@@ -72,15 +72,20 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
   return arc_score_rest(c, wp, base, P);
 }
 
-// smem per warp: window [win_rows][WP] (pixels keep their global 4-byte phase so rows are staged
-// with aligned 32-bit loads) + S map [win_rows-6][WP].
-template <int WP, bool WIDE>
+// Shared memory per warp (all pitches WP bytes):
+//   win   [win_rows][WP]      staged window; pixels keep their global 4-byte phase (aligned word loads)
+//   smap  [win_rows-4][WP]    sparse S map with a 1-px zero rim: holds S only where S > minTh
+//   queue [(win_rows-6)*(WP-12)] uint16 (yy<<6 | xx): compass survivors, then (in place) the hot list
+//   rows  [2][64][2] uint32   kept-corner bit masks per tested row, for minTh and for iniTh
+template <int WP>
 __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, int first_slot, int n, int win_rows) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int win_bytes = WP * win_rows, s_bytes = WP * (win_rows - 6);
-  uint8_t* win = smem + (size_t)warp * (win_bytes + s_bytes);
+  const int win_bytes = WP * win_rows, s_bytes = WP * (win_rows - 4), q_bytes = 2 * (win_rows - 6) * (WP - 12);
+  uint8_t* win = smem + (size_t)warp * (win_bytes + s_bytes + q_bytes + 1024);
   uint8_t* smap = win + win_bytes;
+  uint16_t* queue = reinterpret_cast<uint16_t*>(smap + s_bytes);
+  uint32_t* rows = reinterpret_cast<uint32_t*>(smap + s_bytes + q_bytes);
 
   const long long gcell = (long long)blockIdx.x * kFastWarps + warp;
   if (gcell >= (long long)n * L.cells_per_slot) return;
@@ -100,6 +105,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
     return;
   }
   const int iw = ww - 6, ih = hh - 6;
+  const int min_th = L.min_th, ini_th = L.ini_th;
 
   // stage the window with aligned word loads (plane base is 256-B aligned, pitch a multiple of 16)
   const int phase = (kEdge + x0) & 3;
@@ -112,90 +118,89 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
       reinterpret_cast<uint32_t*>(win + r * WP)[w] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * g.pitch) + w);
     }
   }
+  for (int i = lane; i < ((ih + 2) * WP) >> 2; i += 32) reinterpret_cast<uint32_t*>(smap)[i] = 0u;
+  for (int i = lane; i < 256; i += 32) rows[i] = 0u;
   __syncwarp();
 
-  unsigned long long k_ini[2] = {0ull, 0ull}, k_min[2] = {0ull, 0ull};
-  if (!WIDE) {
-    // Narrow cells (iw <= 32): lane = column, rows streamed top to bottom.  The 3x3 maximum test of
-    // row yy-1 runs as soon as row yy is scored, with the neighbour columns read by warp shuffles,
-    // so no S map is written; only kept corners store their score (for the response).
-    // Pixels that fail the compass pre-test at minTh cannot be corners: they score 0, and a whole
-    // warp-row of them skips the 16-point evaluation.
-    const bool act = lane < iw;
-    const uint8_t* cptr = win + 3 * WP + phase + lane + 3;
-    int a = 0, b = 0;
-    for (int yy = 0; yy <= ih; ++yy) {
-      int cur = 0;
-      if (yy < ih) {
-        const int v = cptr[0];
-        const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
-        uint32_t P[16];
-        const bool need = act && compass_bound(cptr, WP, base, P) > L.min_th;
-        if (__any_sync(0xffffffffu, need)) {
-          const int sc = arc_score_rest(cptr, WP, base, P);
-          cur = need ? max(sc, 0) : 0;
-        }
-        cptr += WP;
-      }
-      const int t3 = max(max(a, b), cur);
-      int lft = __shfl_up_sync(0xffffffffu, t3, 1), rgt = __shfl_down_sync(0xffffffffu, t3, 1);
-      if (lane == 0) lft = 0;
-      if (lane == 31) rgt = 0;
-      const int nb = max(max(lft, rgt), max(a, cur));
-      if (b > nb && b > L.min_th) {
-        k_min[0] |= 1ull << (yy - 1);
-        if (b > L.ini_th) k_ini[0] |= 1ull << (yy - 1);
-        smap[(yy - 1) * WP + lane] = (uint8_t)b;
-      }
-      a = b; b = cur;
-    }
-  } else {
-  // pass 1: S for every tested pixel; per lane (= column) a bit mask of rows with S > minTh
-  unsigned long long hot[2] = {0ull, 0ull};
+  // stage 1: compass pre-test for every tested pixel (lane = column, up to two 32-column chunks).
+  // A pixel whose bound is <= minTh cannot be a corner at either threshold.
+  unsigned long long cand[2] = {0ull, 0ull};
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     const int xx = ch * 32 + lane;
     if (xx < iw) {
       const uint8_t* cptr = win + 3 * WP + phase + xx + 3;
-      uint8_t* sptr = smap + xx;
       unsigned long long m = 0ull;
       for (int yy = 0; yy < ih; ++yy) {
-        const int sc = arc_score(cptr, WP);
-        sptr[0] = (uint8_t)max(sc, 0);
-        m |= (unsigned long long)(sc > L.min_th) << yy;
-        cptr += WP; sptr += WP;
+        const int v = cptr[0];
+        const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
+        uint32_t P[16];
+        m |= (unsigned long long)(compass_bound(cptr, WP, base, P) > min_th) << yy;
+        cptr += WP;
       }
-      hot[ch] = m;
+      cand[ch] = m;
+    }
+  }
+  // survivors -> one warp-wide queue, so that the expensive stage below is load balanced
+  int ncand;
+  {
+    const int mine = __popcll(cand[0]) + __popcll(cand[1]);
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    ncand = __shfl_sync(0xffffffffu, incl, 31);
+    int pos = incl - mine;
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+      unsigned long long m = cand[ch];
+      while (m) {
+        const int yy = __ffsll((long long)m) - 1;
+        m &= m - 1;
+        queue[pos++] = (uint16_t)((yy << 6) | (ch * 32 + lane));
+      }
     }
   }
   __syncwarp();
 
-  // pass 2 (sparse): strict 3x3 maxima among the hot pixels
-#pragma unroll
-  for (int ch = 0; ch < 2; ++ch) {
-    const int xx = ch * 32 + lane;
-    unsigned long long m = hot[ch];
-    while (m) {
-      const int yy = __ffsll((long long)m) - 1;
-      m &= m - 1;
-      const uint8_t* p = smap + yy * WP + xx;
-      const int sc = p[0];
-      const bool up = yy > 0, dn = yy < ih - 1, lf = xx > 0, rt = xx < iw - 1;
-      bool mx = true;
-      if (lf) mx = mx && p[-1] < sc;
-      if (rt) mx = mx && p[1] < sc;
-      if (up) { mx = mx && p[-WP] < sc; if (lf) mx = mx && p[-WP - 1] < sc; if (rt) mx = mx && p[-WP + 1] < sc; }
-      if (dn) { mx = mx && p[WP] < sc; if (lf) mx = mx && p[WP - 1] < sc; if (rt) mx = mx && p[WP + 1] < sc; }
-      if (mx) {
-        k_min[ch] |= 1ull << yy;
-        if (sc > L.ini_th) k_ini[ch] |= 1ull << yy;
-      }
+  // stage 2: full 16-point arc score, one survivor per lane per iteration; the ones with S > minTh
+  // ("hot") go to the S map and, compacted in place, to the front of the queue
+  int nhot = 0;
+  for (int i = 0; i < ncand; i += 32) {
+    const bool valid = i + lane < ncand;
+    const int e = valid ? queue[i + lane] : 0;
+    const int yy = e >> 6, xx = e & 63;
+    const int sc = arc_score(win + (yy + 3) * WP + phase + xx + 3, WP);
+    const bool is_hot = valid && sc > min_th;
+    const uint32_t bal = __ballot_sync(0xffffffffu, is_hot);
+    if (is_hot) {
+      queue[nhot + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)e;
+      smap[(yy + 1) * WP + xx + 1] = (uint8_t)sc;
     }
-  }
+    nhot += __popc(bal);
   }
   __syncwarp();
-  const int cnt_ini = __reduce_add_sync(0xffffffffu, __popcll(k_ini[0]) + __popcll(k_ini[1]));
-  const int cnt_min = __reduce_add_sync(0xffffffffu, __popcll(k_min[0]) + __popcll(k_min[1]));
+
+  // stage 3: strict 3x3 maxima among the hot pixels (neighbours that are not hot read as 0)
+  int cnt_ini = 0, cnt_min = 0;
+  for (int i = 0; i < nhot; i += 32) {
+    const bool valid = i + lane < nhot;
+    const int e = valid ? queue[i + lane] : 0;
+    const int yy = e >> 6, xx = e & 63;
+    const uint8_t* p = smap + (yy + 1) * WP + xx + 1;
+    const int sc = p[0];
+    const int m1 = __vimax3_s32(p[-WP - 1], p[-WP], p[-WP + 1]), m2 = __vimax3_s32(p[-1], p[1], p[WP - 1]);
+    const int m3 = __vimax3_s32(p[WP], p[WP + 1], m1);
+    const bool kept = valid && sc > max(m2, m3);
+    const bool kept_ini = kept && sc > ini_th;
+    if (kept) atomicOr(&rows[yy * 2 + (xx >> 5)], 1u << (xx & 31));
+    if (kept_ini) atomicOr(&rows[128 + yy * 2 + (xx >> 5)], 1u << (xx & 31));
+    cnt_min += __popc(__ballot_sync(0xffffffffu, kept));
+    cnt_ini += __popc(__ballot_sync(0xffffffffu, kept_ini));
+  }
+  __syncwarp();
   const bool use_ini = cnt_ini > 0;                    // src/ORBextractor.cc:812: retry at minTh iff empty
   const int total = use_ini ? cnt_ini : cnt_min;
   int base = 0;
@@ -205,48 +210,48 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
   }
   if (total == 0) return;
   base = __shfl_sync(0xffffffffu, base, 0);
-  const unsigned long long keep0 = use_ini ? k_ini[0] : k_min[0], keep1 = use_ini ? k_ini[1] : k_min[1];
-  const unsigned long long any = keep0 | keep1;
-  unsigned long long rows = ((unsigned long long)__reduce_or_sync(0xffffffffu, (unsigned)(any >> 32)) << 32) |
-                            __reduce_or_sync(0xffffffffu, (unsigned)any);
 
-  // pass 3: emit in pixel row-major order (rows that hold a corner only)
+  // emit in pixel row-major order: lane r owns tested rows r and r+32
+  const uint32_t* km = rows + (use_ini ? 128 : 0);
   uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
-  int run = 0;
-  while (rows) {
-    const int yy = __ffsll((long long)rows) - 1;
-    rows &= rows - 1;
 #pragma unroll
-    for (int ch = 0; ch < 2; ++ch) {
-      const bool keep = ((ch ? keep1 : keep0) >> yy) & 1ull;
-      const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-      if (keep) {
-        const int xx = ch * 32 + lane;
-        const int pos = base + run + __popc(bal & ((1u << lane) - 1u));
-        const int resp = (int)smap[yy * WP + xx] - 1;
-        if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
-      }
-      run += __popc(bal);
+  for (int half = 0; half < 2; ++half) {
+    const int yy = half * 32 + lane;
+    const uint32_t w0 = yy < ih ? km[yy * 2] : 0u, w1 = yy < ih ? km[yy * 2 + 1] : 0u;
+    const int mine = __popc(w0) + __popc(w1);
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    int pos = base + incl - mine;
+    base += __shfl_sync(0xffffffffu, incl, 31);
+    unsigned long long m = ((unsigned long long)w1 << 32) | w0;
+    while (m) {
+      const int xx = __ffsll((long long)m) - 1;
+      m &= m - 1;
+      const int resp = (int)smap[(yy + 1) * WP + xx + 1] - 1;
+      if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
+      ++pos;
     }
   }
 }
 
-template <int WP, bool WIDE>
+template <int WP>
 static void launch_fast_t(const DeviceLayout& L, int first_slot, int n, int win_h, unsigned grid, cudaStream_t st) {
-  const size_t smem = (size_t)kFastWarps * WP * (2 * win_h - 6);
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_fast_cells<WP, WIDE><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
+  const size_t smem = (size_t)kFastWarps * (WP * win_h + WP * (win_h - 4) + 2 * (win_h - 6) * (WP - 12) + 1024);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_fast_cells<WP><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
 }
 
 int launch_fast(const DeviceLayout& L, const LevelGeom* hg, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
   (void)hg;
   const long long cells = (long long)n * L.cells_per_slot;
   const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
-  // a staged row (phase + width, rounded up to words) must fit the pitch; cells of at most 32
-  // tested columns take the shuffle-based path
-  if (win_w - 6 <= 32) launch_fast_t<48, false>(L, first_slot, n, win_h, grid, st);
-  else if (win_w + 6 <= 48) launch_fast_t<48, true>(L, first_slot, n, win_h, grid, st);
-  else launch_fast_t<72, true>(L, first_slot, n, win_h, grid, st);
+  // a staged row (phase + width, rounded up to words) must fit the smem pitch
+  if (win_w + 6 <= 48) launch_fast_t<48>(L, first_slot, n, win_h, grid, st);
+  else launch_fast_t<72>(L, first_slot, n, win_h, grid, st);
   return 1;
 }
 
