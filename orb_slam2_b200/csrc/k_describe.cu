@@ -15,15 +15,19 @@
 // All float math is written with explicit round-to-nearest intrinsics (never contracted to FMA),
 // sinf/cosf are the restated glibc routines (double polynomial), see DESIGN.md hazards H2/H3.
 #include "orbx_internal.h"
+#include "tma_utils.cuh"
 
 namespace orbx {
 
 constexpr int kDescWarps = 4;
-constexpr int kTileR = 43, kTileP = 48;   // raw tile rows / pitch; tile column 0 sits at smem column `phase`
+constexpr int kKpPerWarp = 4;             // keypoints per warp: the next tile is in flight while this one is processed
+constexpr int kTileR = kDescTileH, kTileP = kDescTileW;   // raw tile rows / pitch (TMA box); the keypoint sits at (21, phase16+21)
 constexpr int kHtC = 40, kHtP = 46;       // horizontal pass, TRANSPOSED: [column][row] uint16, 46-entry pitch (bank-conflict free)
-constexpr int kBlP = 40, kBlR = 38;       // blurred tile pitch / rows (row 37 is scratch), centre (18, phase+18)
-constexpr int kWarpSmem = kTileR * kTileP + kHtC * kHtP * 2 + kBlR * kBlP;   // 2064 + 3680 + 1520
-static_assert(kWarpSmem % 16 == 0, "per-warp smem must keep 16-byte alignment");
+constexpr int kBlP = 40, kBlR = 38;       // blurred tile pitch / rows (row 37 is scratch), centre (18,18)
+// per-warp shared memory, 128-byte aligned pieces: 2 raw tiles (double buffer) | Ht | blurred | 2 mbarriers
+constexpr int kOffTile1 = 2816, kOffHt = 5632, kOffBl = 9344, kOffBar = 10880, kWarpSmem = 11008;
+static_assert(kTileR * kTileP <= kOffTile1 && kOffHt + kHtC * kHtP * 2 <= kOffBl && kOffBl + kBlR * kBlP <= kOffBar, "smem carve-up");
+static_assert(kWarpSmem % 128 == 0 && kOffTile1 % 128 == 0, "TMA destinations must be 128-byte aligned");
 
 // 7x7 sigma-2 taps of cv2's 8-bit path, {18,34,48,56,48,34,18}/256, packed for dp4a / dp2a
 __device__ __forceinline__ unsigned pk4(unsigned a, unsigned b, unsigned c, unsigned d) { return a | (b << 8) | (c << 16) | (d << 24); }
@@ -82,20 +86,34 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
-__global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, int first_slot, int n_img, int ctas_per_img,
-                                                              const int* __restrict__ umax, const char4* __restrict__ pattern) {
-  extern __shared__ __align__(16) uint8_t smem[];
+struct KpRef { int level, px, py, resp; };
+
+// keypoint j of the level-major concatenation of the per-level lists (src/ORBextractor.cc:1073-1103)
+__device__ __forceinline__ KpRef locate_kp(const DeviceLayout& L, int slot, int j, int incl, int myc, int lane) {
+  const uint32_t lvl_mask = __ballot_sync(0xffffffffu, lane < L.nlevels && j < incl);
+  KpRef k;
+  k.level = __ffs(lvl_mask) - 1;
+  const int lvl_first = __shfl_sync(0xffffffffu, incl - myc, k.level);
+  const uint32_t key = L.lvlkp[(size_t)slot * L.lvlkp_per_slot + L.geom[k.level].lvl_kp_off + (j - lvl_first)];
+  k.px = unpack_x(key); k.py = unpack_y(key); k.resp = unpack_r(key);
+  return k;
+}
+
+__global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
+                                                              int n_img, int ctas_per_img, const int* __restrict__ umax,
+                                                              const char4* __restrict__ pattern) {
+  extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint8_t* raw = smem + (size_t)warp * kWarpSmem;
-  uint16_t* ht = reinterpret_cast<uint16_t*>(raw + kTileR * kTileP);
-  uint8_t* bl = raw + kTileR * kTileP + kHtC * kHtP * 2;
+  uint8_t* wbase = smem + (size_t)warp * kWarpSmem;
+  uint16_t* ht = reinterpret_cast<uint16_t*>(wbase + kOffHt);
+  uint8_t* bl = wbase + kOffBl;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(wbase + kOffBar);
 
   const int img = blockIdx.x / ctas_per_img;
   if (img >= n_img) return;
   const int slot = first_slot + img;
-  const int j = (blockIdx.x - img * ctas_per_img) * kDescWarps + warp;   // output keypoint index
+  const int j0 = ((blockIdx.x - img * ctas_per_img) * kDescWarps + warp) * kKpPerWarp;   // first output keypoint of this warp
 
-  // level-major concatenation of the per-level lists (src/ORBextractor.cc:1073-1103)
   const int myc = lane < L.nlevels ? L.lvlcnt[slot * kMaxLevels + lane] : 0;
   int incl = myc;
 #pragma unroll
@@ -103,37 +121,44 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, in
     const int t = __shfl_up_sync(0xffffffffu, incl, o);
     if (lane >= o) incl += t;
   }
-  const int total = __shfl_sync(0xffffffffu, incl, 31);
-  if (j == 0 && lane == 0) L.nkp[slot] = min(total, L.kp_cap);
-  if (j >= total || j >= L.kp_cap) return;
-  const uint32_t lvl_mask = __ballot_sync(0xffffffffu, lane < L.nlevels && j < incl);
-  const int level = __ffs(lvl_mask) - 1;
-  const int lvl_first = __shfl_sync(0xffffffffu, incl - myc, level);
-  const LevelGeom& g = L.geom[level];
-  const uint32_t key = L.lvlkp[(size_t)slot * L.lvlkp_per_slot + g.lvl_kp_off + (j - lvl_first)];
-  const int px = unpack_x(key), py = unpack_y(key), resp = unpack_r(key);
+  const int total = min(__shfl_sync(0xffffffffu, incl, 31), L.kp_cap);
+  if (j0 == 0 && lane == 0) L.nkp[slot] = total;
+  if (j0 >= total) return;
+  const int nk = min(kKpPerWarp, total - j0);
 
-  // stage the 43x43 raw tile whose centre is the keypoint (bordered-plane coords: +19) with aligned
-  // 32-bit loads: 12 words per row starting at the 4-byte boundary below the tile's first column
-  const uint8_t* plane = L.pyr + g.plane_off + (size_t)slot * g.plane_stride;
-  const int tx0 = px + kEdge - 21, phase = tx0 & 3;
-  {
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(plane + (size_t)(py + kEdge - 21) * g.pitch + (tx0 - phase));
-    const int wpitch = g.pitch >> 2;
-    uint32_t* dst = reinterpret_cast<uint32_t*>(raw);
-    for (int i = lane; i < kTileR * 12; i += 32) {
-      const int r = i / 12, w = i - r * 12;
-      dst[i] = __ldg(src + (size_t)r * wpitch + w);
+  if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); fence_barrier_init(); }
+  __syncwarp();
+  // TMA: the 64x43 box that holds the 43x43 tile centred on the keypoint, straight from the bordered plane (+19 offset)
+  KpRef nxt = locate_kp(L, slot, j0, incl, myc, lane);
+  if (lane == 0) {
+    mbar_expect_tx(&bars[0], kTileR * kTileP);
+    tma_load_3d(wbase, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, &bars[0]);
+  }
+
+  for (int t = 0; t < nk; ++t) {
+  const KpRef cur = nxt;
+  const int j = j0 + t;
+  if (t + 1 < nk) {                                   // warp-uniform
+    nxt = locate_kp(L, slot, j + 1, incl, myc, lane);
+    if (lane == 0) {
+      uint8_t* dst = wbase + (((t + 1) & 1) ? kOffTile1 : 0);
+      mbar_expect_tx(&bars[(t + 1) & 1], kTileR * kTileP);
+      tma_load_3d(dst, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, &bars[(t + 1) & 1]);
     }
   }
-  __syncwarp();
+  const uint8_t* raw = wbase + ((t & 1) ? kOffTile1 : 0);
+  const int level = cur.level, px = cur.px, py = cur.py, resp = cur.resp;
+  const LevelGeom& g = L.geom[level];
+  // the TMA box starts at the 16-byte boundary below the tile: tile column 0 is smem column phase16
+  const int phase16 = (px + kEdge - 21) & 15, g0 = phase16 >> 2, phase = phase16 & 3;
+  mbar_wait(&bars[t & 1], (t >> 1) & 1);
 
   // intensity-centroid moments over the radius-15 disc, int32 (src/ORBextractor.cc:77-104)
   int m10 = 0, m01 = 0;
   if (lane < 2 * kHalfPatch + 1) {
     const int v = lane - kHalfPatch;
     const int d = umax[v < 0 ? -v : v];
-    const uint8_t* row = raw + (21 + v) * kTileP + phase + 21;
+    const uint8_t* row = raw + (21 + v) * kTileP + phase16 + 21;
     int si = 0;
     for (int u = -d; u <= d; ++u) {
       const int I = row[u];
@@ -161,7 +186,8 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, in
     const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw);
     for (int t = lane; t < kTileR * 10; t += 32) {
       const int r = t / 10, gq = t - r * 10;
-      const uint32_t w0 = rw[r * 12 + gq], w1 = rw[r * 12 + gq + 1], w2 = rw[r * 12 + gq + 2];
+      const uint32_t* rp = rw + r * (kTileP / 4) + g0 + gq;
+      const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
       uint16_t* o = ht + (4 * gq) * kHtP + r;
       o[0] = (uint16_t)__dp4a(w1, A1, __dp4a(w0, A0, 0u));
       o[kHtP] = (uint16_t)__dp4a(w1, B1, __dp4a(w0, B0, 0u));
@@ -225,12 +251,15 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, in
     kp.class_id = -1;
     L.kps[oi] = kp;
   }
+  __syncwarp();                                       // every lane is done with this tile, Ht and the blurred patch
+  }
 }
 
-int launch_describe(const DeviceLayout& L, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st) {
-  const int ctas_per_img = (L.kp_cap + kDescWarps - 1) / kDescWarps;
+int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st) {
+  const int per_cta = kDescWarps * kKpPerWarp;
+  const int ctas_per_img = (L.kp_cap + per_cta - 1) / per_cta;
   const size_t smem = (size_t)kDescWarps * kWarpSmem;
-  k_describe<<<n * ctas_per_img, kDescWarps * 32, smem, st>>>(L, first_slot, n, ctas_per_img, d_umax, d_pattern);
+  k_describe<<<n * ctas_per_img, kDescWarps * 32, smem, st>>>(L, maps, first_slot, n, ctas_per_img, d_umax, d_pattern);
   return 1;
 }
 

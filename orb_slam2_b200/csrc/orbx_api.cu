@@ -71,6 +71,7 @@ struct orbx_extractor {
   Totals cur, capy;
   std::vector<ResizeTap> htaps;
   DeviceLayout L{};
+  TmaMaps desc_maps{};       // per-level tensor maps with the K4 tile box
   // device arenas
   LevelGeom* d_geom = nullptr; ResizeTap* d_taps = nullptr; int* d_umax = nullptr; char4* d_pattern = nullptr;
   uint8_t* d_in = nullptr;
@@ -205,6 +206,33 @@ orbx_status geometry(const orbx_extractor* e, int w, int h, int nslots, LevelGeo
   return ORBX_OK;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+orbx_status encode_level_maps(const orbx_extractor* e, const LevelGeom* g, int box_w, int box_h, TmaMaps* out) {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    if (q != cudaDriverEntryPointSuccess || !p) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
+    fn = (EncodeTiledFn)p;
+  }
+  for (int l = 0; l < e->nlevels; ++l) {
+    const cuuint64_t dims[3] = {(cuuint64_t)g[l].pitch, (cuuint64_t)g[l].rows, (cuuint64_t)e->max_batch};
+    const cuuint64_t strides[2] = {(cuuint64_t)g[l].pitch, (cuuint64_t)g[l].plane_stride};
+    const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = fn(&out->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, e->L.pyr + g[l].plane_off, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for level " + std::to_string(l) + " (CUresult " + std::to_string((int)r) + ")");
+  }
+  return ORBX_OK;
+}
+
 orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
   if (w == e->cur_w && h == e->cur_h) return ORBX_OK;
   if (w > e->max_w || h > e->max_h) return fail(ORBX_ERR_CAPACITY, "image larger than max_w x max_h given at create");
@@ -216,8 +244,12 @@ orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
   if (t.pyr_bytes > e->capy.pyr_bytes || t.cells > e->capy.cells || t.pool > e->capy.pool || t.taps > e->capy.taps ||
       t.lvlkp > e->capy.lvlkp || t.node_cap > e->capy.node_cap || t.win_w > e->capy.win_w || t.win_h > e->capy.win_h)
     return fail(ORBX_ERR_CAPACITY, "image geometry needs more device memory than reserved at create");
+  TmaMaps maps;
+  s = encode_level_maps(e, g, kDescTileW, kDescTileH, &maps);
+  if (s != ORBX_OK) return s;
   // the previous geometry may still be in use by kernels queued on another stream
   CU(cudaDeviceSynchronize());
+  e->desc_maps = maps;
   std::memcpy(e->hg, g, sizeof(g));
   e->cur = t;
   e->htaps = taps;
@@ -373,7 +405,7 @@ orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, in
   if (ev) cudaEventRecord(ev[2], st);
   launches += launch_octree(e->L, first_slot, n, e->cur.node_cap, st);
   if (ev) cudaEventRecord(ev[3], st);
-  launches += launch_describe(e->L, first_slot, n, e->d_umax, e->d_pattern, st);
+  launches += launch_describe(e->L, e->desc_maps, first_slot, n, e->d_umax, e->d_pattern, st);
   if (ev) cudaEventRecord(ev[4], st);
   g_launches += launches;
   CU(cudaGetLastError());
