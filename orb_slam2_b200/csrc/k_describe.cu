@@ -30,7 +30,16 @@ static_assert(kTileR * kTileP <= kOffTile1 && kOffHt + kHtC * kHtP * 2 <= kOffBl
 static_assert(kWarpSmem % 128 == 0 && kOffTile1 % 128 == 0, "TMA destinations must be 128-byte aligned");
 
 // 7x7 sigma-2 taps of cv2's 8-bit path, {18,34,48,56,48,34,18}/256, packed for dp4a / dp2a
-__device__ __forceinline__ unsigned pk4(unsigned a, unsigned b, unsigned c, unsigned d) { return a | (b << 8) | (c << 16) | (d << 24); }
+__device__ __forceinline__ unsigned pk4(unsigned a, unsigned b, unsigned c, unsigned d) {
+  // the asm keeps the packed taps in an ordinary register: as compile-time constants they are
+  // re-materialised through the uniform datapath (one UMOV per dot product) inside the hot loops
+  unsigned r;
+  asm volatile("mov.b32 %0, %1;" : "=r"(r) : "r"(a | (b << 8) | (c << 16) | (d << 24)));
+  return r;
+}
+
+// umax of the reference for HALF_PATCH_SIZE = 15 (src/ORBextractor.cc:454-469)
+__device__ constexpr int kUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
 struct SinCosTab { double sign[4], hpi_inv, hpi, c0, c1, c2, c3, c4, s1, s2, s3; };
 __constant__ SinCosTab c_sincos[2] = {
@@ -153,19 +162,22 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   const int phase16 = (px + kEdge - 21) & 15, g0 = phase16 >> 2, phase = phase16 & 3;
   mbar_wait(&bars[t & 1], (t >> 1) & 1);
 
-  // intensity-centroid moments over the radius-15 disc, int32 (src/ORBextractor.cc:77-104)
-  int m10 = 0, m01 = 0;
-  if (lane < 2 * kHalfPatch + 1) {
-    const int v = lane - kHalfPatch;
-    const int d = umax[v < 0 ? -v : v];
-    const uint8_t* row = raw + (21 + v) * kTileP + phase16 + 21;
-    int si = 0;
-    for (int u = -d; u <= d; ++u) {
-      const int I = row[u];
-      si += I;
-      m10 += u * I;
+  // intensity-centroid moments over the radius-15 disc, int32 (src/ORBextractor.cc:77-104).
+  // lane = column u (31 of them), rows unrolled: every load is independent, the disc half-width
+  // of each row is a compile-time constant (kUmax, checked against the host table at create).
+  int m10, m01;
+  {
+    const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+    const uint8_t* colp = raw + 21 * kTileP + phase16 + 21 + (lane < 31 ? u : 0);
+    int s_all = 0, s_v = 0;
+#pragma unroll
+    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+      const int I = (lane < 31 && au <= kUmax[v < 0 ? -v : v]) ? (int)colp[v * kTileP] : 0;
+      s_all += I;
+      s_v += v * I;
     }
-    m01 = v * si;
+    m10 = u * s_all;
+    m01 = s_v;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {

@@ -293,6 +293,10 @@ orbx_status orbx_extractor_create(const orbx_params* params, int max_w, int max_
   e->P = *params; e->device = device; e->max_w = max_w; e->max_h = max_h; e->max_batch = max_batch;
   e->nlevels = params->nlevels;
   make_tables(e);
+  {
+    static const int expect[kHalfPatch + 1] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+    if (std::memcmp(e->umax, expect, sizeof(expect)) != 0) { delete e; return fail(ORBX_ERR_STATE, "umax table differs from the constant compiled into k_describe"); }
+  }
   LevelGeom g[kMaxLevels];
   orbx_status s = geometry(e, max_w, max_h, max_batch, g, &e->capy, nullptr);
   if (s != ORBX_OK) { delete e; return s; }
