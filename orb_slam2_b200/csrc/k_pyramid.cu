@@ -57,9 +57,10 @@ __global__ void __launch_bounds__(256) k_resize_level(DeviceLayout L, int level,
   const int rem = (int)(tid - (long long)img * per_img);
   const int by = rem / wpr, bx0 = (rem - by * wpr) << 2;
   const ResizeTap ty = L.taps[g.ytab_off + by];
-  const uint8_t* sroi = L.pyr + gs.plane_off + (size_t)(first_slot + img) * gs.plane_stride + (size_t)kEdge * gs.pitch + kEdge;
-  const uint8_t* p0 = sroi + (size_t)ty.ofs * gs.pitch;
-  const uint8_t* p1 = sroi + (size_t)min(ty.ofs + 1, gs.h - 1) * gs.pitch;
+  // The second tap of an edge pixel has weight 0 (OpenCV clamps the index instead): reading one
+  // column / row past the ROI lands in the plane's own border, so no index clamp is needed.
+  const uint8_t* p0 = L.pyr + gs.plane_off + (size_t)(first_slot + img) * gs.plane_stride + (size_t)(kEdge + ty.ofs) * gs.pitch + kEdge;
+  const uint8_t* p1 = p0 + gs.pitch;
   const uint4* xt = reinterpret_cast<const uint4*>(L.taps + g.xtab_off + bx0);
   const uint4 q0 = __ldg(xt), q1 = __ldg(xt + 1);
   const int ofs[4] = {(int)q0.x, (int)q0.z, (int)q1.x, (int)q1.z};
@@ -68,12 +69,14 @@ __global__ void __launch_bounds__(256) k_resize_level(DeviceLayout L, int level,
   uint32_t v = 0;
 #pragma unroll
   for (int b = 0; b < 4; ++b) {
-    const int a0 = (short)(wts[b] & 0xffff), a1 = (short)(wts[b] >> 16);
-    const int s0 = ofs[b], s1 = min(s0 + 1, gs.w - 1);
-    const int h0 = (int)p0[s0] * a0 + (int)p0[s1] * a1;
-    const int h1 = (int)p1[s0] * a0 + (int)p1[s1] * a1;
+    const int a0 = (int)(wts[b] & 0xffff), a1 = (int)(wts[b] >> 16);   // weights are in [0, 2048]
+    const uint8_t* s0 = p0 + ofs[b];
+    const uint8_t* s1 = p1 + ofs[b];
+    const int h0 = (int)s0[0] * a0 + (int)s0[1] * a1;
+    const int h1 = (int)s1[0] * a0 + (int)s1[1] * a1;
+    // <= 255 by construction (weights sum to <= 2049), so no saturation is needed
     const int r = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-    v |= (uint32_t)min(max(r, 0), 255) << (8 * b);
+    v |= (uint32_t)r << (8 * b);
   }
   uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)by * g.pitch + bx0;
   *reinterpret_cast<uint32_t*>(dst) = v;
