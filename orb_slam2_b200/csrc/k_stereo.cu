@@ -32,13 +32,18 @@ __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const 
   return __popcll(x0) + __popcll(x1) + __popcll(x2) + __popcll(x3);
 }
 
+constexpr int kRowBinShift = 3;          // right keypoints are binned by (int)y >> 3
+constexpr int kMaxBins = 520;            // images up to 4160 rows
+
 __global__ void __launch_bounds__(kStWarps * 32) k_stereo_match(StereoArgs a, int chunks) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int capR = a.R.kp_cap;
   float* s_x = reinterpret_cast<float*>(smem);
-  short* s_min = reinterpret_cast<short*>(s_x + capR);
+  int* s_bin = reinterpret_cast<int*>(s_x + capR);                 // [kMaxBins+1] start offsets, then as many cursors
+  short* s_min = reinterpret_cast<short*>(s_bin + 2 * (kMaxBins + 1));
   short* s_max = s_min + capR;
-  int8_t* s_oct = reinterpret_cast<int8_t*>(s_max + capR);
+  unsigned short* s_idx = reinterpret_cast<unsigned short*>(s_max + capR);
+  int8_t* s_oct = reinterpret_cast<int8_t*>(s_idx + capR);
   uint8_t* s_patch = reinterpret_cast<uint8_t*>(s_oct) + ((capR + 15) & ~15);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -51,15 +56,47 @@ __global__ void __launch_bounds__(kStWarps * 32) k_stereo_match(StereoArgs a, in
   const uint8_t* dL = a.L.desc + (size_t)slotL * a.L.kp_cap * 32;
   const uint8_t* dR = a.R.desc + (size_t)slotR * a.R.kp_cap * 32;
 
+  // Right keypoints, counting-sorted into 8-row bins (the reference's vRowIndices table,
+  // src/Frame.cc:476-493, coarsened): a left keypoint on row v only has to look at the bins that
+  // can hold a right keypoint with floor(y-r) <= v <= ceil(y+r).  The order inside a bin is
+  // irrelevant because the winner is the lexicographic minimum of (distance, iR).
+  const int nbins = min(kMaxBins, (a.L.geom[0].h >> kRowBinShift) + 1);
+  int* s_cur = s_bin + kMaxBins + 1;
+  for (int i = tid; i <= nbins; i += kStWarps * 32) { s_bin[i] = 0; s_cur[i] = 0; }
+  __syncthreads();
   for (int i = tid; i < nR; i += kStWarps * 32) {
-    const orbx_keypoint kp = kR[i];
-    const float r = __fmul_rn(2.0f, a.L.geom[kp.octave].scale);                     // :487
-    s_max[i] = (short)(int)ceilf(__fadd_rn(kp.y, r));
-    s_min[i] = (short)(int)floorf(__fsub_rn(kp.y, r));
-    s_oct[i] = (int8_t)kp.octave;
-    s_x[i] = kp.x;
+    const int b = min(max((int)kR[i].y >> kRowBinShift, 0), nbins - 1);
+    atomicAdd(&s_bin[b + 1], 1);
   }
   __syncthreads();
+  if (warp == 0) {           // inclusive scan of the counts -> bin start offsets
+    int carry = 0;
+    for (int base = 0; base <= nbins; base += 32) {
+      const int i = base + lane;
+      int v = i <= nbins ? s_bin[i] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+      }
+      if (i <= nbins) s_bin[i] = v + carry;
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < nR; i += kStWarps * 32) {
+    const orbx_keypoint kp = kR[i];
+    const int b = min(max((int)kp.y >> kRowBinShift, 0), nbins - 1);
+    const int pos = s_bin[b] + atomicAdd(&s_cur[b], 1);
+    const float r = __fmul_rn(2.0f, a.L.geom[kp.octave].scale);                     // :487
+    s_max[pos] = (short)(int)ceilf(__fadd_rn(kp.y, r));
+    s_min[pos] = (short)(int)floorf(__fsub_rn(kp.y, r));
+    s_oct[pos] = (int8_t)kp.octave;
+    s_x[pos] = kp.x;
+    s_idx[pos] = (unsigned short)i;
+  }
+  __syncthreads();
+  const int reach = (int)ceilf(__fmul_rn(2.0f, a.L.geom[a.L.nlevels - 1].scale)) + 2;   // max |(int)yR - row| of a candidate
 
   uint8_t* lp = s_patch + warp * 384;   // 11x11 left patch
   uint8_t* rp = lp + 128;               // 11x21 right strip
@@ -77,20 +114,23 @@ __global__ void __launch_bounds__(kStWarps * 32) k_stereo_match(StereoArgs a, in
     const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32));
     const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32) + 1);
     unsigned best = 100u << 16;                                                      // TH_HIGH
-    for (int iR = lane; iR < nR; iR += 32) {
-      if (row < s_min[iR] || row > s_max[iR]) continue;
-      const int oc = s_oct[iR];
+    const int b_lo = min(max((row - reach) >> kRowBinShift, 0), nbins - 1), b_hi = min(max((row + reach) >> kRowBinShift, 0), nbins - 1);
+    const int e_end = s_bin[b_hi + 1];
+    for (int e = s_bin[b_lo] + lane; e < e_end; e += 32) {
+      if (row < s_min[e] || row > s_max[e]) continue;
+      const int oc = s_oct[e];
       if (oc < lvl - 1 || oc > lvl + 1) continue;
-      const float uR = s_x[iR];
+      const float uR = s_x[e];
       if (uR >= minU && uR <= maxU) {
+        const unsigned iR = s_idx[e];
         const unsigned d = (unsigned)hamming256(a0, a1, reinterpret_cast<const uint4*>(dR + (size_t)iR * 32));
-        best = min(best, (d << 16) | (unsigned)iR);
+        best = min(best, (d << 16) | iR);
       }
     }
     best = __reduce_min_sync(0xffffffffu, best);
     if ((best >> 16) >= 75u) continue;                                               // (TH_HIGH+TH_LOW)/2
     const int bestR = best & 0xFFFF;
-    const float uR0 = s_x[bestR];
+    const float uR0 = kR[bestR].x;
     const LevelGeom& gl = a.L.geom[lvl];
     const LevelGeom& gr = a.R.geom[lvl];
     const float inv = gl.inv_scale;
@@ -181,7 +221,7 @@ __global__ void __launch_bounds__(256) k_stereo_median(StereoArgs a) {
 int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid) {
   const int capR = a.R.kp_cap, capL = a.L.kp_cap;
   const int chunks = (capL + kStPerCta - 1) / kStPerCta;
-  const size_t smem1 = (size_t)capR * 8 + ((capR + 15) & ~15) + kStWarps * 384;
+  const size_t smem1 = (size_t)capR * 10 + ((capR + 15) & ~15) + kStWarps * 384 + 2 * (kMaxBins + 1) * sizeof(int);
   if (smem1 > 48 * 1024) cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
   k_stereo_match<<<a.n * chunks, kStWarps * 32, smem1, st>>>(a, chunks);
   if (ev_mid) cudaEventRecord(ev_mid, st);
