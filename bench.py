@@ -130,6 +130,17 @@ def measured_hbm_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(stage, batch):
+    """DRAM bytes per launch of a stage from the committed ncu capture (profiles/traffic.json), or None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if t.get("stereo_pairs_per_step") == batch:
+            return t["dram_bytes_per_step"].get(stage)
+    except Exception:
+        pass
+    return None
+
+
 def cpu_sample(nframes, distinct=32):
     """nframes KITTI-shaped stereo pairs for the CPU legs (at most `distinct` different ones, tiled)."""
     w, h = CFG["w"], CFG["h"]
@@ -310,7 +321,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": measured_traffic(top, B), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": stage_bytes[top] * B,
                          "note": "front end is instruction-issue / latency bound, not HBM bound (DESIGN.md); see profiles/ for ncu issue utilisation"},
             "stage_ms_per_step": stage_ms,
@@ -323,7 +334,7 @@ def main():
             from oracle import pyoracle as O
             O.build()
             threads = O.hardware_threads()
-            nfr = 8 * threads                               # ~10-20 s of CPU work
+            nfr = 16 * threads                              # ~10-30 s of CPU work
             v, secs, _, _ = cpu_baseline(nfr, threads)
             line["cpu_baseline"] = {"value": v, "unit": "stereo frames/s", "cores": threads, "kind": "port",
                                     "sample": f"{nfr} KITTI-shaped stereo pairs, one pair per std::thread on {threads} threads, {secs:.1f} s"}
