@@ -13,7 +13,7 @@
 //          first minimum wins; parabola refinement in the reference's float operation order
 //          with un-fused intrinsics (:597-622).
 //   k_stereo_median: one CTA per frame; the median SAD (element size/2 of the sorted list, :627)
-//     by rank counting, then the 1.5*1.4*median cut (:628-639).
+//     by bisection over the value range, then the 1.5*1.4*median cut (:628-639).
 #include <climits>
 
 #include "orbx_internal.h"
@@ -21,7 +21,7 @@
 namespace orbx {
 
 constexpr int kStWarps = 8;
-constexpr int kStPerCta = 64;   // left keypoints per CTA
+constexpr int kStPerCta = 64;   // left keypoints per CTA (the bin sort of the right keypoints is redone per CTA)
 
 __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4* __restrict__ b) {
   const uint4 b0 = __ldg(b), b1 = __ldg(b + 1);
@@ -181,41 +181,61 @@ __global__ void __launch_bounds__(kStWarps * 32) k_stereo_match(StereoArgs a, in
   }
 }
 
-__global__ void __launch_bounds__(256) k_stereo_median(StereoArgs a) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  int* vals = reinterpret_cast<int*>(smem);
-  __shared__ int s_cnt, s_med, s_kept;
-  const int img = blockIdx.x, tid = threadIdx.x;
+constexpr int kMedThreads = 1024;
+// The reference sorts (SAD, iL) and reads element size/2 (src/Frame.cc:626-627).  Only that element's
+// SAD value matters: it is the smallest v with #(SAD <= v) > size/2, found by bisection over the
+// value range (SAD <= 121*510 < 2^16) with one block-wide count per step.
+__global__ void __launch_bounds__(kMedThreads) k_stereo_median(StereoArgs a) {
+  __shared__ int s_part[kMedThreads / 32];
+  __shared__ int s_tot;
+  const int img = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nL = a.L.nkp[a.slotL0 + img];
   const size_t base = (size_t)img * a.cap;
-  if (tid == 0) { s_cnt = 0; s_med = 0; s_kept = 0; }
-  __syncthreads();
-  for (int i = tid; i < nL; i += 256) {
-    const int s = a.sad[base + i];
-    if (s >= 0) vals[atomicAdd(&s_cnt, 1)] = s;
-  }
-  __syncthreads();
-  const int cnt = s_cnt;
+  // up to 4 values per thread in registers (kp_cap <= 4096 for any accepted configuration is not
+  // guaranteed, so the tail is re-read from memory in the rare larger case)
+  int v[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) { const int i = tid + q * kMedThreads; v[q] = i < nL ? a.sad[base + i] : -1; }
+  auto block_count = [&](int limit) {      // #(0 <= SAD <= limit) over the whole frame
+    int c = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) c += (v[q] >= 0 && v[q] <= limit);
+    for (int i = tid + 4 * kMedThreads; i < nL; i += kMedThreads) { const int s = a.sad[base + i]; c += (s >= 0 && s <= limit); }
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) s_part[warp] = c;
+    __syncthreads();
+    if (warp == 0) {
+      const int t = __reduce_add_sync(0xffffffffu, s_part[lane]);
+      if (lane == 0) s_tot = t;
+    }
+    __syncthreads();
+    const int r = s_tot;
+    __syncthreads();
+    return r;
+  };
+  const int cnt = block_count(0x7fffffff);
   if (cnt == 0) { if (tid == 0) a.nMatches[img] = 0; return; }   // the reference reads an empty vector here
   const int k = cnt / 2;
-  for (int i = tid; i < cnt; i += 256) {
-    const int v = vals[i];
-    int lt = 0, le = 0;
-    for (int j = 0; j < cnt; ++j) { const int w = vals[j]; lt += w < v; le += w <= v; }
-    if (lt <= k && k < le) s_med = v;
+  int lo = 0, hi = 65535;                  // invariant: count(<= hi) > k
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (block_count(mid) > k) hi = mid; else lo = mid + 1;
   }
-  __syncthreads();
-  const float th = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_med);
+  const float th = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)lo);
   int kept = 0;
-  for (int i = tid; i < nL; i += 256) {
+  for (int i = tid; i < nL; i += kMedThreads) {
     const int s = a.sad[base + i];
     if (s < 0) continue;
     if ((float)s < th) ++kept;
     else { a.uRight[base + i] = -1.f; a.depth[base + i] = -1.f; }
   }
-  atomicAdd(&s_kept, kept);
+  kept = __reduce_add_sync(0xffffffffu, kept);
+  if (lane == 0) s_part[warp] = kept;
   __syncthreads();
-  if (tid == 0) a.nMatches[img] = s_kept;
+  if (warp == 0) {
+    const int t = __reduce_add_sync(0xffffffffu, s_part[lane]);
+    if (lane == 0) a.nMatches[img] = t;
+  }
 }
 
 int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid) {
@@ -225,9 +245,8 @@ int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid) {
   if (smem1 > 48 * 1024) cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
   k_stereo_match<<<a.n * chunks, kStWarps * 32, smem1, st>>>(a, chunks);
   if (ev_mid) cudaEventRecord(ev_mid, st);
-  const size_t smem2 = (size_t)capL * 4;
-  if (smem2 > 48 * 1024) cudaFuncSetAttribute(k_stereo_median, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-  k_stereo_median<<<a.n, 256, smem2, st>>>(a);
+  (void)capL;
+  k_stereo_median<<<a.n, kMedThreads, 0, st>>>(a);
   return 2;
 }
 
