@@ -10,7 +10,10 @@
 // them as one word.  A border pixel equals the interior pixel at the reflected coordinate, so it is
 // computed with the same formula instead of being copied afterwards — no intra-level dependency,
 // one launch per level for the whole batch.  HBM-bound in principle (reads L2-hot source rows).
+#include <algorithm>
+
 #include "orbx_internal.h"
+#include "tma_utils.cuh"
 
 namespace orbx {
 
@@ -82,8 +85,101 @@ __global__ void __launch_bounds__(256) k_resize_level(DeviceLayout L, int level,
   *reinterpret_cast<uint32_t*>(dst) = v;
 }
 
+// Tiled variant (used when the scale factor keeps a tile's source footprint inside the static
+// shared-memory budget, i.e. for the usual 1.2): one CTA = 32 x 128 bordered output pixels.
+//   1. the source footprint (rows/cols spanned by the tile's taps, reflection included because the
+//      tap tables are in bordered coordinates) is fetched by ONE TMA box load (192 x 48 bytes from
+//      the 16-byte boundary below the footprint; the hardware zero-fills outside the plane)
+//   2. horizontal pass once per SOURCE row (1.2x fewer than two per output row), (h >> 4) as uint16
+//   3. vertical pass, 4 pixels per thread, (b*H) >> 16 as one multiply-high with the +2 rounding
+//      riding in the accumulator; one aligned 32-bit store per thread, a warp writes 128 B
+constexpr int kRtTH = 32, kRtTW = 128, kRtSH = kResizeBoxH, kRtSWP = kResizeBoxW;
+
+__global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __grid_constant__ TmaMaps maps, int level, int first_slot,
+                                                      int n, int tiles_x, int tiles_y) {
+  __shared__ __align__(128) uint8_t s_src[kRtSH * kRtSWP];
+  __shared__ __align__(16) uint16_t s_h[kRtSH * kRtTW];
+  __shared__ ResizeTap s_ty[kRtTH];
+  __shared__ int s_lim[4];   // sx_lo, sx_hi, sy_lo, sy_hi (inclusive, source ROI coordinates)
+  __shared__ __align__(8) uint64_t s_bar;
+  const LevelGeom& g = L.geom[level];
+  const int t = threadIdx.x;
+  const int per_img = tiles_x * tiles_y;
+  const int img = blockIdx.x / per_img, tile = blockIdx.x - img * per_img;
+  if (img >= n) return;
+  const int tyi = tile / tiles_x, txi = tile - tyi * tiles_x;
+  const int bx0 = txi * kRtTW, by0 = tyi * kRtTH;
+  const int tw = min(kRtTW, g.pitch - bx0), th = min(kRtTH, g.rows - by0);
+  if (t == 0) {
+    s_lim[0] = 1 << 30; s_lim[1] = -1; s_lim[2] = 1 << 30; s_lim[3] = -1;
+    mbar_init(&s_bar, 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const int c = t & (kRtTW - 1);
+  ResizeTap tx; tx.ofs = 0; tx.a0 = 0; tx.a1 = 0;
+  if (c < tw) {
+    tx = L.taps[g.xtab_off + bx0 + c];
+    if (t < kRtTW) { atomicMin(&s_lim[0], tx.ofs); atomicMax(&s_lim[1], tx.ofs + 1); }
+  }
+  if (t < th) {
+    const ResizeTap ty = L.taps[g.ytab_off + by0 + t];
+    s_ty[t] = ty;
+    atomicMin(&s_lim[2], ty.ofs); atomicMax(&s_lim[3], ty.ofs + 1);
+  }
+  __syncthreads();
+  const int sx_lo = s_lim[0], sy_lo = s_lim[2];
+  const int SH = s_lim[3] - sy_lo + 1;
+  const int phase = (kEdge + sx_lo) & 15;            // smem column of source column sx_lo
+  if (t == 0) {
+    mbar_expect_tx(&s_bar, kRtSH * kRtSWP);
+    tma_load_3d(s_src, &maps.m[level - 1], (kEdge + sx_lo) & ~15, kEdge + sy_lo, first_slot + img, &s_bar);
+  }
+  mbar_wait(&s_bar, 0);
+  if (c < tw) {
+    const int a0 = tx.a0, a1 = tx.a1;
+    const uint8_t* p = s_src + (t >> 7) * kRtSWP + (tx.ofs - sx_lo + phase);
+    uint16_t* o = s_h + (t >> 7) * kRtTW + c;
+    for (int r = t >> 7; r < SH; r += 2) {
+      o[0] = (uint16_t)(((int)p[0] * a0 + (int)p[1] * a1) >> 4);
+      p += 2 * kRtSWP; o += 2 * kRtTW;
+    }
+  }
+  __syncthreads();
+  const int c4 = (t & 31) * 4;
+  if (c4 < tw) {
+    uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)by0 * g.pitch + bx0 + c4;
+    for (int r = t >> 5; r < th; r += 8) {
+      const ResizeTap ty = s_ty[r];
+      const uint16_t* h0 = s_h + (ty.ofs - sy_lo) * kRtTW + c4;
+      const uint2 u0 = *reinterpret_cast<const uint2*>(h0), u1 = *reinterpret_cast<const uint2*>(h0 + kRtTW);
+      const unsigned b0 = (unsigned)ty.a0 << 16, b1 = (unsigned)ty.a1 << 16;   // mulhi(b << 16, H) == (b * H) >> 16
+      const unsigned r0 = (__umulhi(b0, u0.x & 0xffff) + __umulhi(b1, u1.x & 0xffff) + 2u) >> 2;
+      const unsigned r1 = (__umulhi(b0, u0.x >> 16) + __umulhi(b1, u1.x >> 16) + 2u) >> 2;
+      const unsigned r2 = (__umulhi(b0, u0.y & 0xffff) + __umulhi(b1, u1.y & 0xffff) + 2u) >> 2;
+      const unsigned r3 = (__umulhi(b0, u0.y >> 16) + __umulhi(b1, u1.y >> 16) + 2u) >> 2;
+      *reinterpret_cast<uint32_t*>(dst + (size_t)r * g.pitch) = r0 | (r1 << 8) | (r2 << 16) | (r3 << 24);
+    }
+  }
+}
+
+// Does every 32x128 tile of this level fit the static source-footprint budget?  (host, from the tap tables)
+bool resize_tiled_fits(const LevelGeom& g, const ResizeTap* taps) {
+  for (int bx0 = 0; bx0 < g.pitch; bx0 += kRtTW) {
+    int lo = 1 << 30, hi = -1;
+    for (int c = bx0; c < std::min(bx0 + kRtTW, g.pitch); ++c) { lo = std::min(lo, taps[g.xtab_off + c].ofs); hi = std::max(hi, taps[g.xtab_off + c].ofs + 1); }
+    if (hi - lo + 1 + 15 > kRtSWP) return false;   // + up to 15 columns below the footprint for the 16-byte aligned TMA start
+  }
+  for (int by0 = 0; by0 < g.rows; by0 += kRtTH) {
+    int lo = 1 << 30, hi = -1;
+    for (int r = by0; r < std::min(by0 + kRtTH, g.rows); ++r) { lo = std::min(lo, taps[g.ytab_off + r].ofs); hi = std::max(hi, taps[g.ytab_off + r].ofs + 1); }
+    if (hi - lo + 1 > kRtSH) return false;
+  }
+  return true;
+}
+
 int launch_pyramid(const DeviceLayout& L, const LevelGeom* hg, const uint8_t* src, int src_pitch,
-                   size_t src_img_stride, int first_slot, int n, cudaStream_t st) {
+                   size_t src_img_stride, int first_slot, int n, unsigned tiled_mask, const TmaMaps* resize_maps, cudaStream_t st) {
   int launches = 0;
   {
     long long total = (long long)(hg[0].pitch >> 4) * hg[0].rows * n;
@@ -91,8 +187,13 @@ int launch_pyramid(const DeviceLayout& L, const LevelGeom* hg, const uint8_t* sr
     ++launches;
   }
   for (int l = 1; l < L.nlevels; ++l) {
-    long long total = (long long)(hg[l].pitch >> 2) * hg[l].rows * n;
-    k_resize_level<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, l, first_slot, n);
+    if (tiled_mask & (1u << l)) {
+      const int tiles_x = (hg[l].pitch + kRtTW - 1) / kRtTW, tiles_y = (hg[l].rows + kRtTH - 1) / kRtTH;
+      k_resize_tiled<<<(unsigned)(tiles_x * tiles_y * n), 256, 0, st>>>(L, *resize_maps, l, first_slot, n, tiles_x, tiles_y);
+    } else {
+      long long total = (long long)(hg[l].pitch >> 2) * hg[l].rows * n;
+      k_resize_level<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, l, first_slot, n);
+    }
     ++launches;
   }
   return launches;

@@ -72,6 +72,8 @@ struct orbx_extractor {
   std::vector<ResizeTap> htaps;
   DeviceLayout L{};
   TmaMaps desc_maps{};       // per-level tensor maps with the K4 tile box
+  TmaMaps resize_maps{};     // per-level tensor maps with the K1 source-footprint box
+  unsigned tiled_mask = 0;   // levels whose resize runs through the shared-memory tiled kernel
   // device arenas
   LevelGeom* d_geom = nullptr; ResizeTap* d_taps = nullptr; int* d_umax = nullptr; char4* d_pattern = nullptr;
   uint8_t* d_in = nullptr;
@@ -157,11 +159,14 @@ orbx_status geometry(const orbx_extractor* e, int w, int h, int nslots, LevelGeo
         std::vector<ResizeTap> tx(q.w), ty(q.h);
         resize_taps(q.w, g[l - 1].w, tx.data());
         resize_taps(q.h, g[l - 1].h, ty.data());
-        ResizeTap zero; zero.ofs = 0; zero.a0 = 0; zero.a1 = 0;
+        // pad entries: zero weights (-> pixel 0) at the last valid source offset, so that they do not
+        // widen the source footprint of a tile
+        ResizeTap padx = tx[reflect101(q.w + kEdge - 1, q.w)], pady = ty[reflect101(q.h + kEdge - 1, q.h)];
+        padx.a0 = padx.a1 = 0; pady.a0 = pady.a1 = 0;
         for (int bx = 0; bx < q.pitch; ++bx)
-          (*taps)[q.xtab_off + bx] = bx < q.w + 2 * kEdge ? tx[reflect101(bx - kEdge, q.w)] : zero;
+          (*taps)[q.xtab_off + bx] = bx < q.w + 2 * kEdge ? tx[reflect101(bx - kEdge, q.w)] : padx;
         for (int by = 0; by < (int)align_up(q.rows, 4); ++by)
-          (*taps)[q.ytab_off + by] = by < q.rows ? ty[reflect101(by - kEdge, q.h)] : zero;
+          (*taps)[q.ytab_off + by] = by < q.rows ? ty[reflect101(by - kEdge, q.h)] : pady;
       }
     }
     // FAST cells
@@ -244,12 +249,18 @@ orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
   if (t.pyr_bytes > e->capy.pyr_bytes || t.cells > e->capy.cells || t.pool > e->capy.pool || t.taps > e->capy.taps ||
       t.lvlkp > e->capy.lvlkp || t.node_cap > e->capy.node_cap || t.win_w > e->capy.win_w || t.win_h > e->capy.win_h)
     return fail(ORBX_ERR_CAPACITY, "image geometry needs more device memory than reserved at create");
-  TmaMaps maps;
+  TmaMaps maps, rmaps;
   s = encode_level_maps(e, g, kDescTileW, kDescTileH, &maps);
+  if (s != ORBX_OK) return s;
+  s = encode_level_maps(e, g, kResizeBoxW, kResizeBoxH, &rmaps);
   if (s != ORBX_OK) return s;
   // the previous geometry may still be in use by kernels queued on another stream
   CU(cudaDeviceSynchronize());
   e->desc_maps = maps;
+  e->resize_maps = rmaps;
+  e->tiled_mask = 0;
+  for (int l = 1; l < e->nlevels; ++l)
+    if (resize_tiled_fits(g[l], taps.data())) e->tiled_mask |= 1u << l;
   std::memcpy(e->hg, g, sizeof(g));
   e->cur = t;
   e->htaps = taps;
@@ -403,7 +414,7 @@ orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, in
   int launches = 0;
   cudaEvent_t* ev = (e->profiling && e->n_ext < orbx_extractor::kRing) ? e->ev_ext[e->n_ext++] : nullptr;
   if (ev) cudaEventRecord(ev[0], st);
-  launches += launch_pyramid(e->L, e->hg, src, src_pitch, src_istride, first_slot, n, st);
+  launches += launch_pyramid(e->L, e->hg, src, src_pitch, src_istride, first_slot, n, e->tiled_mask, &e->resize_maps, st);
   if (ev) cudaEventRecord(ev[1], st);
   launches += launch_fast(e->L, e->hg, first_slot, n, e->cur.win_w, e->cur.win_h, st);
   if (ev) cudaEventRecord(ev[2], st);

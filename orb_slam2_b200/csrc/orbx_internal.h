@@ -73,11 +73,13 @@ __host__ __device__ inline int reflect101(int i, int n) {
 
 // one TMA tensor map per pyramid level (passed to kernels as a __grid_constant__ parameter)
 struct TmaMaps { CUtensorMap m[kMaxLevels]; };
+constexpr int kResizeBoxW = 192, kResizeBoxH = 48;  // K1 tiled resize: source footprint box
 constexpr int kDescTileW = 64, kDescTileH = 43;   // K4 tile box: TMA needs a 16-byte aligned start, so 43+15 columns -> 64
 
 // kernel launchers (each returns the number of kernel launches it made)
 int launch_pyramid(const DeviceLayout& L, const LevelGeom* hgeom, const uint8_t* src, int src_pitch,
-                   size_t src_img_stride, int first_slot, int n, cudaStream_t st);
+                   size_t src_img_stride, int first_slot, int n, unsigned tiled_mask, const TmaMaps* resize_maps, cudaStream_t st);
+bool resize_tiled_fits(const LevelGeom& g, const ResizeTap* taps);
 int launch_fast(const DeviceLayout& L, const LevelGeom* hgeom, int first_slot, int n, int win_w, int win_h, cudaStream_t st);
 int launch_octree(const DeviceLayout& L, int first_slot, int n, int node_cap, cudaStream_t st);
 int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st);
