@@ -15,6 +15,8 @@
 //   cv_round           <- cvRound                         called at src/ORBextractor.cc:81,115,119,442,460,1112
 //   libm_sinf/cosf     <- glibc sinf/cosf                 called at src/ORBextractor.cc:113
 #pragma once
+#include <emmintrin.h>
+
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -102,12 +104,20 @@ static inline int reflect101(int i, int n) {
 }
 
 // dst is (w+2b) x (h+2b) with row pitch dpitch; src is w x h with pitch spitch (isolated).
+// src may be the interior of dst itself (the reference borders every level in place,
+// src/ORBextractor.cc:1122): interior rows are then left alone and only read.
 inline void border_reflect101(const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int dpitch,
                               int b) {
-  for (int y = -b; y < h + b; ++y) {
-    const uint8_t* s = src + (size_t)reflect101(y, h) * spitch;
+  const bool in_place = src == dst + (size_t)b * dpitch + b;
+  for (int y = 0; y < h; ++y) {                       // interior rows first: copy + left/right margins
+    const uint8_t* s = src + (size_t)y * spitch;
     uint8_t* d = dst + (size_t)(y + b) * dpitch;
-    for (int x = -b; x < w + b; ++x) d[x + b] = s[reflect101(x, w)];
+    if (!in_place) std::memcpy(d + b, s, w);
+    for (int x = 1; x <= b; ++x) { d[b - x] = s[reflect101(-x, w)]; d[b + w - 1 + x] = s[reflect101(w - 1 + x, w)]; }
+  }
+  for (int y = 1; y <= b; ++y) {                      // top/bottom margins are copies of finished rows
+    std::memcpy(dst + (size_t)(b - y) * dpitch, dst + (size_t)(b + reflect101(-y, h)) * dpitch, w + 2 * b);
+    std::memcpy(dst + (size_t)(b + h - 1 + y) * dpitch, dst + (size_t)(b + reflect101(h - 1 + y, h)) * dpitch, w + 2 * b);
   }
 }
 
@@ -132,17 +142,28 @@ inline void resize_linear_u8(const uint8_t* src, int sw, int sh, int spitch, uin
   };
   coeffs(dw, sw, xo, xa);
   coeffs(dh, sh, yo, ya);
-  std::vector<int> r0(dw), r1(dw);
-  for (int y = 0; y < dh; ++y) {
-    int sy0 = yo[y], sy1 = std::min(sy0 + 1, sh - 1);
-    const uint8_t* p0 = src + (size_t)sy0 * spitch;
-    const uint8_t* p1 = src + (size_t)sy1 * spitch;
+  // the horizontal pass of a source row is computed once and reused by the (up to two)
+  // destination rows that tap it, as OpenCV's resize does with its row ring buffer
+  std::vector<int> hb[2] = {std::vector<int>(dw), std::vector<int>(dw)};
+  int have[2] = {-1, -1};
+  auto hrow = [&](int sy) -> const int* {
+    for (int k = 0; k < 2; ++k) if (have[k] == sy) return hb[k].data();
+    const int k = (have[0] < have[1]) ? 0 : 1;       // evict the older (smaller) row
+    const uint8_t* p = src + (size_t)sy * spitch;
+    int* o = hb[k].data();
     for (int x = 0; x < dw; ++x) {
-      int sx0 = xo[x], sx1 = std::min(sx0 + 1, sw - 1);
-      r0[x] = p0[sx0] * xa[2 * x] + p0[sx1] * xa[2 * x + 1];
-      r1[x] = p1[sx0] * xa[2 * x] + p1[sx1] * xa[2 * x + 1];
+      const int sx0 = xo[x], sx1 = std::min(sx0 + 1, sw - 1);
+      o[x] = p[sx0] * xa[2 * x] + p[sx1] * xa[2 * x + 1];
     }
-    int b0 = ya[2 * y], b1 = ya[2 * y + 1];
+    have[k] = sy;
+    return o;
+  };
+  for (int y = 0; y < dh; ++y) {
+    const int sy0 = yo[y], sy1 = std::min(sy0 + 1, sh - 1);
+    const int* r0 = hrow(sy0);
+    const int* r1 = hrow(sy1);
+    r0 = hrow(sy0);                                   // (r0 may have been evicted by the second call when both are new)
+    const int b0 = ya[2 * y], b1 = ya[2 * y + 1];
     uint8_t* d = dst + (size_t)y * dpitch;
     for (int x = 0; x < dw; ++x) {
       int v = (((b0 * (r0[x] >> 4)) >> 16) + ((b1 * (r1[x] >> 4)) >> 16) + 2) >> 2;
@@ -156,18 +177,14 @@ inline void resize_linear_u8(const uint8_t* src, int sw, int sh, int spitch, uin
 inline void gauss7_sigma2(const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int dpitch) {
   static const int k[7] = {18, 34, 48, 56, 48, 34, 18};
   std::vector<uint16_t> hp((size_t)w * h);
+  std::vector<uint8_t> pad(w + 6);
   for (int y = 0; y < h; ++y) {
     const uint8_t* s = src + (size_t)y * spitch;
+    for (int x = -3; x < w + 3; ++x) pad[x + 3] = (x >= 0 && x < w) ? s[x] : s[reflect101(x, w)];
     uint16_t* o = &hp[(size_t)y * w];
-    for (int x = 0; x < w; ++x) {
-      int acc = 0;
-      if (x >= 3 && x < w - 3) {
-        for (int i = 0; i < 7; ++i) acc += k[i] * s[x + i - 3];
-      } else {
-        for (int i = 0; i < 7; ++i) acc += k[i] * s[reflect101(x + i - 3, w)];
-      }
-      o[x] = (uint16_t)acc;
-    }
+    const uint8_t* p = pad.data();
+    for (int x = 0; x < w; ++x)
+      o[x] = (uint16_t)(18 * (p[x] + p[x + 6]) + 34 * (p[x + 1] + p[x + 5]) + 48 * (p[x + 2] + p[x + 4]) + 56 * p[x + 3]);
   }
   for (int y = 0; y < h; ++y) {
     uint8_t* d = dst + (size_t)y * dpitch;
@@ -206,17 +223,52 @@ static inline int fast_arc_score(const uint8_t* p, int pitch) {
 // cv::FAST(img, kps, t, nonmaxSuppression=true), TYPE_9_16.  Pixels closer than 3 to the window
 // edge are never tested; NMS is strict against the 8 neighbours inside the same window, where a
 // neighbour that is not a corner at t counts as 0.  Output is row-major.
+// Sixteen pixels at a time with SSE2, the way OpenCV's own SIMD path works (compass pre-test on
+// ring pixels 0/4/8/12, then a running count of consecutive brighter / darker ring pixels over
+// 25 positions); the score of the survivors comes from fast_arc_score.  This keeps the CPU
+// baseline honest: a scalar FAST would flatter the GPU.
 inline void fast9_16(const uint8_t* img, int w, int h, int pitch, int t, std::vector<FastPt>& out) {
   out.clear();
   if (w < 7 || h < 7) return;
-  std::vector<int> sc((size_t)w * h, 0);
-  // ring offsets of the 8 opposite pairs (k, k+8): any 9-arc holds one pixel of every pair, so a
-  // corner needs every pair to have a pixel on the same side of the [v-t, v+t] band.
-  const int pa[8] = {3 * pitch, 3 * pitch + 1, 2 * pitch + 2, pitch + 3, 3, -pitch + 3, -2 * pitch + 2, -3 * pitch + 1};
+  static thread_local std::vector<int> sc;
+  sc.assign((size_t)w * h, 0);
+  const int ox[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
+  const int oy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+  int ofs[25];
+  for (int k = 0; k < 25; ++k) ofs[k] = oy[k & 15] * pitch + ox[k & 15];
+  const __m128i delta = _mm_set1_epi8((char)0x80), tt = _mm_set1_epi8((char)t), k8 = _mm_set1_epi8(8);
   bool any = false;
   for (int y = 3; y < h - 3; ++y) {
     const uint8_t* row = img + (size_t)y * pitch;
-    for (int x = 3; x < w - 3; ++x) {
+    int x = 3;
+    for (; x + 16 <= w - 3; x += 16) {
+      const uint8_t* p = row + x;
+      const __m128i m = _mm_loadu_si128((const __m128i*)p);
+      const __m128i v0 = _mm_xor_si128(_mm_adds_epu8(m, tt), delta), v1 = _mm_xor_si128(_mm_subs_epu8(m, tt), delta);
+      const __m128i x0 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(p + ofs[0])), delta);
+      const __m128i x1 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(p + ofs[4])), delta);
+      const __m128i x2 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(p + ofs[8])), delta);
+      const __m128i x3 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(p + ofs[12])), delta);
+      const __m128i b0 = _mm_cmpgt_epi8(x0, v0), b1 = _mm_cmpgt_epi8(x1, v0), b2 = _mm_cmpgt_epi8(x2, v0), b3 = _mm_cmpgt_epi8(x3, v0);
+      const __m128i d0 = _mm_cmpgt_epi8(v1, x0), d1 = _mm_cmpgt_epi8(v1, x1), d2 = _mm_cmpgt_epi8(v1, x2), d3 = _mm_cmpgt_epi8(v1, x3);
+      __m128i pre = _mm_or_si128(_mm_or_si128(_mm_and_si128(b0, b1), _mm_and_si128(b1, b2)), _mm_or_si128(_mm_and_si128(b2, b3), _mm_and_si128(b3, b0)));
+      pre = _mm_or_si128(pre, _mm_or_si128(_mm_or_si128(_mm_and_si128(d0, d1), _mm_and_si128(d1, d2)), _mm_or_si128(_mm_and_si128(d2, d3), _mm_and_si128(d3, d0))));
+      if (!_mm_movemask_epi8(pre)) continue;
+      __m128i c0 = _mm_setzero_si128(), c1 = c0, mx0 = c0, mx1 = c0;
+      for (int k = 0; k < 25; ++k) {
+        const __m128i xx = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(p + ofs[k])), delta);
+        const __m128i g0 = _mm_cmpgt_epi8(xx, v0), g1 = _mm_cmpgt_epi8(v1, xx);
+        c0 = _mm_and_si128(_mm_sub_epi8(c0, g0), g0);
+        c1 = _mm_and_si128(_mm_sub_epi8(c1, g1), g1);
+        mx0 = _mm_max_epu8(mx0, c0);
+        mx1 = _mm_max_epu8(mx1, c1);
+      }
+      int mask = _mm_movemask_epi8(_mm_cmpgt_epi8(_mm_max_epu8(mx0, mx1), k8));
+      for (int b = 0; mask; ++b, mask >>= 1)
+        if (mask & 1) { sc[(size_t)y * w + x + b] = fast_arc_score(p + b, pitch) - 1; any = true; }
+    }
+    const int pa[8] = {ofs[0], ofs[1], ofs[2], ofs[3], ofs[4], ofs[5], ofs[6], ofs[7]};
+    for (; x < w - 3; ++x) {        // scalar tail: opposite-pair pre-test, then the score
       const uint8_t* p = row + x;
       const int v = p[0], lo = v - t, hi = v + t;
       int m = 3;
@@ -225,14 +277,14 @@ inline void fast9_16(const uint8_t* img, int w, int h, int pitch, int t, std::ve
         m &= ((a < lo) | (b < lo)) | (((a > hi) | (b > hi)) << 1);
       }
       if (!m) continue;
-      int s = fast_arc_score(p, pitch);
+      const int s = fast_arc_score(p, pitch);
       if (s > t) { sc[(size_t)y * w + x] = s - 1; any = true; }
     }
   }
   if (!any) return;
   for (int y = 3; y < h - 3; ++y)
     for (int x = 3; x < w - 3; ++x) {
-      int s = sc[(size_t)y * w + x];
+      const int s = sc[(size_t)y * w + x];
       if (s == 0) continue;  // not a corner (for t >= 1 a corner has score S-1 >= t >= 1)
       const int* c = &sc[(size_t)y * w + x];
       if (s > c[-1] && s > c[1] && s > c[-w - 1] && s > c[-w] && s > c[-w + 1] && s > c[w - 1] &&

@@ -265,9 +265,7 @@ class Extractor {
       } else {
         const Plane& q = pyr[l - 1];
         resize_linear_u8(q.roi(), q.w, q.h, q.pitch, p.roi(), p.w, p.h, p.pitch);
-        std::vector<uint8_t> tmp((size_t)p.w * p.h);
-        for (int y = 0; y < p.h; ++y) std::memcpy(&tmp[(size_t)y * p.w], p.roi() + (size_t)y * p.pitch, p.w);
-        border_reflect101(tmp.data(), p.w, p.h, p.w, p.buf.data(), p.pitch, kEdge);
+        border_reflect101(p.roi(), p.w, p.h, p.pitch, p.buf.data(), p.pitch, kEdge);   // in place, as the reference
       }
     }
     return 0;
