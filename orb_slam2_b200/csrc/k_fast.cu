@@ -20,6 +20,7 @@
 // popc); the cell table records {pool offset, count} so K3 can restore the reference's
 // cell-row-major candidate order.
 #include "orbx_internal.h"
+#include "tma_utils.cuh"
 
 namespace orbx {
 
@@ -72,186 +73,200 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
   return arc_score_rest(c, wp, base, P);
 }
 
-// Shared memory per warp (all pitches WP bytes):
-//   win   [win_rows][WP]      staged window; pixels keep their global 4-byte phase (aligned word loads)
-//   smap  [win_rows-4][WP]    sparse S map with a 1-px zero rim: holds S only where S > minTh
-//   queue [(win_rows-6)*(WP-12)] uint16 (yy<<6 | xx): compass survivors, then (in place) the hot list
+// Shared memory per warp:
+//   win   [win_rows][WP]      window box fetched by TMA from the 16-byte boundary below the cell's first
+//                             column (WP = 64 or 96); pixel (x, y) of the window sits at [y][phase16 + x]
+//   smap  [win_rows-4][SP]    sparse S map with a 1-px zero rim: holds S only where S > minTh
+//   queue [(win_rows-6)*(SP-4)] uint16 (yy<<6 | xx): compass survivors, then (in place) the hot list
 //   rows  [2][64][2] uint32   kept-corner bit masks per tested row, for minTh and for iniTh
+//   bar   one mbarrier
+// A warp walks kCellsPerWarp consecutive cells; the window of the next cell is requested as soon
+// as the scoring stage has finished with the current one, so its latency hides behind the
+// maxima / emission stages.
+constexpr int kCellsPerWarp = 4;
+
 template <int WP>
-__global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, int first_slot, int n, int win_rows) {
-  extern __shared__ __align__(16) uint8_t smem[];
+__global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
+                                                                int n, int win_rows) {
+  constexpr int SP = WP - 16;                 // S-map pitch: 48 (cells up to 36 tested columns) or 80
+  extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int win_bytes = WP * win_rows, s_bytes = WP * (win_rows - 4), q_bytes = 2 * (win_rows - 6) * (WP - 12);
-  uint8_t* win = smem + (size_t)warp * (win_bytes + s_bytes + q_bytes + 1024);
+  const int win_bytes = WP * win_rows, s_bytes = SP * (win_rows - 4), q_bytes = 2 * (win_rows - 6) * (SP - 4);
+  const int per_warp = (win_bytes + s_bytes + q_bytes + 1024 + 16 + 127) & ~127;
+  uint8_t* win = smem + (size_t)warp * per_warp;
   uint8_t* smap = win + win_bytes;
   uint16_t* queue = reinterpret_cast<uint16_t*>(smap + s_bytes);
   uint32_t* rows = reinterpret_cast<uint32_t*>(smap + s_bytes + q_bytes);
-
-  const long long gcell = (long long)blockIdx.x * kFastWarps + warp;
-  if (gcell >= (long long)n * L.cells_per_slot) return;
-  const int img = (int)(gcell / L.cells_per_slot);
-  const int c = (int)(gcell - (long long)img * L.cells_per_slot);
-  const int slot = first_slot + img;
-  int level = 0;
-  for (int l = 1; l < L.nlevels; ++l)
-    if (c >= L.geom[l].cell_base) level = l;
-  const LevelGeom& g = L.geom[level];
-  const int ci = c - g.cell_base, ci_row = ci / g.nCols, ci_col = ci - ci_row * g.nCols;
-  const int x0 = kFastBorder + ci_col * g.wCell, y0 = kFastBorder + ci_row * g.hCell;
-  const int ww = min(x0 + g.wCell + 6, g.maxBX) - x0, hh = min(y0 + g.hCell + 6, g.maxBY) - y0;
-  uint2* cell_out = L.celltab + (size_t)slot * L.cells_per_slot + c;
-  if (y0 >= g.maxBY - 3 || x0 >= g.maxBX - 6 || ww < 7 || hh < 7) {  // src/ORBextractor.cc:794,802
-    if (lane == 0) *cell_out = make_uint2(0u, 0u);
-    return;
-  }
-  const int iw = ww - 6, ih = hh - 6;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smap + s_bytes + q_bytes + 1024);
   const int min_th = L.min_th, ini_th = L.ini_th;
 
-  // stage the window with aligned word loads (plane base is 256-B aligned, pitch a multiple of 16)
-  const int phase = (kEdge + x0) & 3;
-  {
-    const uint8_t* src = L.pyr + g.plane_off + (size_t)slot * g.plane_stride + (size_t)(kEdge + y0) * g.pitch + (kEdge + x0 - phase);
-    const int wpr = (ww + phase + 3) >> 2;          // words per row
-    const int total = wpr * hh;
-    for (int i = lane; i < total; i += 32) {
-      const int r = i / wpr, w = i - r * wpr;
-      reinterpret_cast<uint32_t*>(win + r * WP)[w] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * g.pitch) + w);
-    }
-  }
-  for (int i = lane; i < ((ih + 2) * WP) >> 2; i += 32) reinterpret_cast<uint32_t*>(smap)[i] = 0u;
-  for (int i = lane; i < 256; i += 32) rows[i] = 0u;
-  __syncwarp();
+  const long long total_cells = (long long)n * L.cells_per_slot;
+  const long long cell0 = ((long long)blockIdx.x * kFastWarps + warp) * kCellsPerWarp;
+  if (cell0 >= total_cells) return;
+  const int ncell = (int)min((long long)kCellsPerWarp, total_cells - cell0);
 
-  // stage 1: compass pre-test for every tested pixel (lane = column, up to two 32-column chunks).
-  // A pixel whose bound is <= minTh cannot be a corner at either threshold.
-  unsigned long long cand[2] = {0ull, 0ull};
-#pragma unroll
-  for (int ch = 0; ch < 2; ++ch) {
-    const int xx = ch * 32 + lane;
-    if (xx < iw) {
-      const uint8_t* cptr = win + 3 * WP + phase + xx + 3;
-      unsigned long long m = 0ull;
-      for (int yy = 0; yy < ih; ++yy) {
-        const int v = cptr[0];
-        const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
-        uint32_t P[16];
-        m |= (unsigned long long)(compass_bound(cptr, WP, base, P) > min_th) << yy;
-        cptr += WP;
-      }
-      cand[ch] = m;
+  struct Cell { int slot, c, level, x0, y0, ww, hh; bool skip; };
+  auto locate = [&](long long gcell) {
+    Cell k;
+    const int img = (int)(gcell / L.cells_per_slot);
+    k.c = (int)(gcell - (long long)img * L.cells_per_slot);
+    k.slot = first_slot + img;
+    k.level = 0;
+    for (int l = 1; l < L.nlevels; ++l)
+      if (k.c >= L.geom[l].cell_base) k.level = l;
+    const LevelGeom& g = L.geom[k.level];
+    const int ci = k.c - g.cell_base, ci_row = ci / g.nCols, ci_col = ci - ci_row * g.nCols;
+    k.x0 = kFastBorder + ci_col * g.wCell; k.y0 = kFastBorder + ci_row * g.hCell;
+    k.ww = min(k.x0 + g.wCell + 6, g.maxBX) - k.x0; k.hh = min(k.y0 + g.hCell + 6, g.maxBY) - k.y0;
+    k.skip = k.y0 >= g.maxBY - 3 || k.x0 >= g.maxBX - 6 || k.ww < 7 || k.hh < 7;   // src/ORBextractor.cc:794,802
+    return k;
+  };
+  auto request = [&](const Cell& k) {         // lane 0: one TMA box load for the cell's window
+    mbar_expect_tx(bar, (uint32_t)win_bytes);
+    tma_load_3d(win, &maps.m[k.level], (kEdge + k.x0) & ~15, kEdge + k.y0, k.slot, bar);
+  };
+
+  if (lane == 0) { mbar_init(bar, 1); fence_barrier_init(); }
+  __syncwarp();
+  Cell nxt = locate(cell0);
+  int waited = 0;                             // TMA requests consumed so far (skipped cells make none) -> mbarrier parity
+  if (!nxt.skip && lane == 0) request(nxt);
+
+  for (int kc = 0; kc < ncell; ++kc) {
+    const Cell cur = nxt;
+    if (kc + 1 < ncell) nxt = locate(cell0 + kc + 1);
+    const LevelGeom& g = L.geom[cur.level];
+    uint2* cell_out = L.celltab + (size_t)cur.slot * L.cells_per_slot + cur.c;
+    if (cur.skip) {
+      if (lane == 0) *cell_out = make_uint2(0u, 0u);
+      if (kc + 1 < ncell && !nxt.skip && lane == 0) request(nxt);
+      continue;
     }
-  }
-  // survivors -> one warp-wide queue, so that the expensive stage below is load balanced
-  int ncand;
-  {
-    const int mine = __popcll(cand[0]) + __popcll(cand[1]);
-    int incl = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
-    }
-    ncand = __shfl_sync(0xffffffffu, incl, 31);
-    int pos = incl - mine;
+    const int x0 = cur.x0, y0 = cur.y0, iw = cur.ww - 6, ih = cur.hh - 6, slot = cur.slot, level = cur.level;
+    const int phase = (kEdge + x0) & 15;
+
+    for (int i = lane; i < ((ih + 2) * SP) >> 2; i += 32) reinterpret_cast<uint32_t*>(smap)[i] = 0u;
+    for (int i = lane; i < 256; i += 32) rows[i] = 0u;
+    mbar_wait(bar, waited & 1);
+    ++waited;
+
+    // stage 1: compass pre-test for every tested pixel (lane = column, up to two 32-column chunks);
+    // a pixel whose bound is <= minTh cannot be a corner at either threshold.  Survivors are
+    // appended to one warp-wide queue (ballot + popc) so that stage 2 is load balanced.
+    int ncand = 0;
 #pragma unroll
     for (int ch = 0; ch < 2; ++ch) {
-      unsigned long long m = cand[ch];
-      while (m) {
-        const int yy = __ffsll((long long)m) - 1;
-        m &= m - 1;
-        queue[pos++] = (uint16_t)((yy << 6) | (ch * 32 + lane));
+      const int xx = ch * 32 + lane;
+      if (ch * 32 < iw) {                     // warp-uniform
+        const uint8_t* cptr = win + 3 * WP + phase + min(xx, iw - 1) + 3;
+        for (int yy = 0; yy < ih; ++yy) {
+          const int v = cptr[0];
+          const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
+          uint32_t P[16];
+          const bool pass = xx < iw && compass_bound(cptr, WP, base, P) > min_th;
+          const uint32_t bal = __ballot_sync(0xffffffffu, pass);
+          if (pass) queue[ncand + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)((yy << 6) | xx);
+          ncand += __popc(bal);
+          cptr += WP;
+        }
       }
     }
-  }
-  __syncwarp();
+    __syncwarp();
 
-  // stage 2: full 16-point arc score, one survivor per lane per iteration; the ones with S > minTh
-  // ("hot") go to the S map and, compacted in place, to the front of the queue
-  int nhot = 0;
-  for (int i = 0; i < ncand; i += 32) {
-    const bool valid = i + lane < ncand;
-    const int e = valid ? queue[i + lane] : 0;
-    const int yy = e >> 6, xx = e & 63;
-    const int sc = arc_score(win + (yy + 3) * WP + phase + xx + 3, WP);
-    const bool is_hot = valid && sc > min_th;
-    const uint32_t bal = __ballot_sync(0xffffffffu, is_hot);
-    if (is_hot) {
-      queue[nhot + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)e;
-      smap[(yy + 1) * WP + xx + 1] = (uint8_t)sc;
+    // stage 2: full 16-point arc score, one survivor per lane per iteration; the ones with S > minTh
+    // ("hot") go to the S map and, compacted in place, to the front of the queue
+    int nhot = 0;
+    for (int i = 0; i < ncand; i += 32) {
+      const bool valid = i + lane < ncand;
+      const int e = valid ? queue[i + lane] : 0;
+      const int yy = e >> 6, xx = e & 63;
+      const int sc = arc_score(win + (yy + 3) * WP + phase + xx + 3, WP);
+      const bool is_hot = valid && sc > min_th;
+      const uint32_t bal = __ballot_sync(0xffffffffu, is_hot);
+      if (is_hot) {
+        queue[nhot + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)e;
+        smap[(yy + 1) * SP + xx + 1] = (uint8_t)sc;
+      }
+      nhot += __popc(bal);
     }
-    nhot += __popc(bal);
-  }
-  __syncwarp();
+    __syncwarp();
+    // the window is dead: fetch the next cell's while the maxima / emission stages run
+    if (kc + 1 < ncell && !nxt.skip && lane == 0) { fence_proxy_async(); request(nxt); }
 
-  // stage 3: strict 3x3 maxima among the hot pixels (neighbours that are not hot read as 0)
-  int cnt_ini = 0, cnt_min = 0;
-  for (int i = 0; i < nhot; i += 32) {
-    const bool valid = i + lane < nhot;
-    const int e = valid ? queue[i + lane] : 0;
-    const int yy = e >> 6, xx = e & 63;
-    const uint8_t* p = smap + (yy + 1) * WP + xx + 1;
-    const int sc = p[0];
-    const int m1 = __vimax3_s32(p[-WP - 1], p[-WP], p[-WP + 1]), m2 = __vimax3_s32(p[-1], p[1], p[WP - 1]);
-    const int m3 = __vimax3_s32(p[WP], p[WP + 1], m1);
-    const bool kept = valid && sc > max(m2, m3);
-    const bool kept_ini = kept && sc > ini_th;
-    if (kept) atomicOr(&rows[yy * 2 + (xx >> 5)], 1u << (xx & 31));
-    if (kept_ini) atomicOr(&rows[128 + yy * 2 + (xx >> 5)], 1u << (xx & 31));
-    cnt_min += __popc(__ballot_sync(0xffffffffu, kept));
-    cnt_ini += __popc(__ballot_sync(0xffffffffu, kept_ini));
-  }
-  __syncwarp();
-  const bool use_ini = cnt_ini > 0;                    // src/ORBextractor.cc:812: retry at minTh iff empty
-  const int total = use_ini ? cnt_ini : cnt_min;
-  int base = 0;
-  if (lane == 0) {
-    if (total > 0) base = atomicAdd(L.poolcnt + slot * kMaxLevels + level, total);
-    *cell_out = make_uint2((uint32_t)base, (uint32_t)total);
-  }
-  if (total == 0) return;
-  base = __shfl_sync(0xffffffffu, base, 0);
-
-  // emit in pixel row-major order: lane r owns tested rows r and r+32
-  const uint32_t* km = rows + (use_ini ? 128 : 0);
-  uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
+    // stage 3: strict 3x3 maxima among the hot pixels (neighbours that are not hot read as 0)
+    int cnt_ini = 0, cnt_min = 0;
+    for (int i = 0; i < nhot; i += 32) {
+      const bool valid = i + lane < nhot;
+      const int e = valid ? queue[i + lane] : 0;
+      const int yy = e >> 6, xx = e & 63;
+      const uint8_t* p = smap + (yy + 1) * SP + xx + 1;
+      const int sc = p[0];
+      const int m1 = __vimax3_s32(p[-SP - 1], p[-SP], p[-SP + 1]), m2 = __vimax3_s32(p[-1], p[1], p[SP - 1]);
+      const int m3 = __vimax3_s32(p[SP], p[SP + 1], m1);
+      const bool kept = valid && sc > max(m2, m3);
+      const bool kept_ini = kept && sc > ini_th;
+      if (kept) atomicOr(&rows[yy * 2 + (xx >> 5)], 1u << (xx & 31));
+      if (kept_ini) atomicOr(&rows[128 + yy * 2 + (xx >> 5)], 1u << (xx & 31));
+      cnt_min += __popc(__ballot_sync(0xffffffffu, kept));
+      cnt_ini += __popc(__ballot_sync(0xffffffffu, kept_ini));
+    }
+    __syncwarp();
+    const bool use_ini = cnt_ini > 0;                    // src/ORBextractor.cc:812: retry at minTh iff empty
+    const int total = use_ini ? cnt_ini : cnt_min;
+    int base = 0;
+    if (lane == 0) {
+      if (total > 0) base = atomicAdd(L.poolcnt + slot * kMaxLevels + level, total);
+      *cell_out = make_uint2((uint32_t)base, (uint32_t)total);
+    }
+    if (total > 0) {                                     // warp-uniform
+      base = __shfl_sync(0xffffffffu, base, 0);
+      // emit in pixel row-major order: lane r owns tested rows r and r+32
+      const uint32_t* km = rows + (use_ini ? 128 : 0);
+      uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
 #pragma unroll
-  for (int half = 0; half < 2; ++half) {
-    const int yy = half * 32 + lane;
-    const uint32_t w0 = yy < ih ? km[yy * 2] : 0u, w1 = yy < ih ? km[yy * 2 + 1] : 0u;
-    const int mine = __popc(w0) + __popc(w1);
-    int incl = mine;
+      for (int half = 0; half < 2; ++half) {
+        const int yy = half * 32 + lane;
+        const uint32_t w0 = yy < ih ? km[yy * 2] : 0u, w1 = yy < ih ? km[yy * 2 + 1] : 0u;
+        const int mine = __popc(w0) + __popc(w1);
+        int incl = mine;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
+        for (int o = 1; o < 32; o <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        int pos = base + incl - mine;
+        base += __shfl_sync(0xffffffffu, incl, 31);
+        unsigned long long m = ((unsigned long long)w1 << 32) | w0;
+        while (m) {
+          const int xx = __ffsll((long long)m) - 1;
+          m &= m - 1;
+          const int resp = (int)smap[(yy + 1) * SP + xx + 1] - 1;
+          if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
+          ++pos;
+        }
+      }
     }
-    int pos = base + incl - mine;
-    base += __shfl_sync(0xffffffffu, incl, 31);
-    unsigned long long m = ((unsigned long long)w1 << 32) | w0;
-    while (m) {
-      const int xx = __ffsll((long long)m) - 1;
-      m &= m - 1;
-      const int resp = (int)smap[(yy + 1) * WP + xx + 1] - 1;
-      if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
-      ++pos;
-    }
+    __syncwarp();                                        // smap / rows / queue are reused by the next cell
   }
 }
 
 template <int WP>
-static void launch_fast_t(const DeviceLayout& L, int first_slot, int n, int win_h, unsigned grid, cudaStream_t st) {
-  const size_t smem = (size_t)kFastWarps * (WP * win_h + WP * (win_h - 4) + 2 * (win_h - 6) * (WP - 12) + 1024);
+static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_h, cudaStream_t st) {
+  constexpr int SP = WP - 16;
+  const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + 2 * (win_h - 6) * (SP - 4) + 1024 + 16 + 127) & ~(size_t)127;
+  const size_t smem = kFastWarps * per_warp;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_fast_cells<WP><<<grid, kFastWarps * 32, smem, st>>>(L, first_slot, n, win_h);
+  const long long cells = (long long)n * L.cells_per_slot;
+  const long long per_cta = (long long)kFastWarps * kCellsPerWarp;
+  k_fast_cells<WP><<<(unsigned)((cells + per_cta - 1) / per_cta), kFastWarps * 32, smem, st>>>(L, maps, first_slot, n, win_h);
 }
 
-int launch_fast(const DeviceLayout& L, const LevelGeom* hg, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
-  (void)hg;
-  const long long cells = (long long)n * L.cells_per_slot;
-  const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
-  // a staged row (phase + width, rounded up to words) must fit the smem pitch
-  if (win_w + 6 <= 48) launch_fast_t<48>(L, first_slot, n, win_h, grid, st);
-  else launch_fast_t<72>(L, first_slot, n, win_h, grid, st);
+int fast_window_pitch(int win_w) { return win_w + 15 <= 64 ? 64 : 96; }
+
+int launch_fast(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
+  // the TMA box starts at the 16-byte boundary below the window: phase (<= 15) + width must fit the pitch
+  if (fast_window_pitch(win_w) == 64) launch_fast_t<64>(L, maps, first_slot, n, win_h, st);
+  else launch_fast_t<96>(L, maps, first_slot, n, win_h, st);
   return 1;
 }
 

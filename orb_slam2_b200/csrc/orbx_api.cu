@@ -73,6 +73,7 @@ struct orbx_extractor {
   DeviceLayout L{};
   TmaMaps desc_maps{};       // per-level tensor maps with the K4 tile box
   TmaMaps resize_maps{};     // per-level tensor maps with the K1 source-footprint box
+  TmaMaps fast_maps{};       // per-level tensor maps with the K2 cell-window box
   unsigned tiled_mask = 0;   // levels whose resize runs through the shared-memory tiled kernel
   // device arenas
   LevelGeom* d_geom = nullptr; ResizeTap* d_taps = nullptr; int* d_umax = nullptr; char4* d_pattern = nullptr;
@@ -249,7 +250,9 @@ orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
   if (t.pyr_bytes > e->capy.pyr_bytes || t.cells > e->capy.cells || t.pool > e->capy.pool || t.taps > e->capy.taps ||
       t.lvlkp > e->capy.lvlkp || t.node_cap > e->capy.node_cap || t.win_w > e->capy.win_w || t.win_h > e->capy.win_h)
     return fail(ORBX_ERR_CAPACITY, "image geometry needs more device memory than reserved at create");
-  TmaMaps maps, rmaps;
+  TmaMaps maps, rmaps, fmaps;
+  s = encode_level_maps(e, g, fast_window_pitch(t.win_w), t.win_h, &fmaps);
+  if (s != ORBX_OK) return s;
   s = encode_level_maps(e, g, kDescTileW, kDescTileH, &maps);
   if (s != ORBX_OK) return s;
   s = encode_level_maps(e, g, kResizeBoxW, kResizeBoxH, &rmaps);
@@ -258,6 +261,7 @@ orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
   CU(cudaDeviceSynchronize());
   e->desc_maps = maps;
   e->resize_maps = rmaps;
+  e->fast_maps = fmaps;
   e->tiled_mask = 0;
   for (int l = 1; l < e->nlevels; ++l)
     if (resize_tiled_fits(g[l], taps.data())) e->tiled_mask |= 1u << l;
@@ -416,7 +420,7 @@ orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, in
   if (ev) cudaEventRecord(ev[0], st);
   launches += launch_pyramid(e->L, e->hg, src, src_pitch, src_istride, first_slot, n, e->tiled_mask, &e->resize_maps, st);
   if (ev) cudaEventRecord(ev[1], st);
-  launches += launch_fast(e->L, e->hg, first_slot, n, e->cur.win_w, e->cur.win_h, st);
+  launches += launch_fast(e->L, e->fast_maps, first_slot, n, e->cur.win_w, e->cur.win_h, st);
   if (ev) cudaEventRecord(ev[2], st);
   launches += launch_octree(e->L, first_slot, n, e->cur.node_cap, st);
   if (ev) cudaEventRecord(ev[3], st);
