@@ -190,6 +190,83 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def secondary_workloads(gx, torch, local):
+    """BASELINE.json configs 3-5 as side measurements (single GPU, device-resident, CUDA events):
+    EuRoC-shaped stereo frames/s, SearchForInitialization pairs/s (TUM shape, 1000 features),
+    brute-force kNN+ratio pairs/s (2000 x 2000 descriptors).  Not the headline; reported for coverage."""
+    import ctypes as C
+    out = {}
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    st = torch.cuda.current_stream().cuda_stream
+    # --- config 3: EuRoC 752x480 stereo, nFeatures 1200 ---
+    cfg = synth.EUROC
+    w, h, B = cfg["w"], cfg["h"], 128
+    pairs = [synth.stereo_pair(500000 + i, w, h)[:2] for i in range(16)]
+    batch = np.stack([pairs[i % 16][0] for i in range(B)] + [pairs[i % 16][1] for i in range(B)])
+    dev = torch.from_numpy(batch).cuda()
+    G = gx.ORBextractor(cfg["nfeatures"], 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=2 * B, device=local)
+    cap = G.kp_cap
+    ur = torch.empty((B, cap), dtype=torch.float32, device="cuda"); dp = torch.empty_like(ur)
+    nm = torch.empty(B, dtype=torch.int32, device="cuda")
+    def step():
+        G.extract_batch(dev, 0, st)
+        gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=B, slotL0=0, slotR0=B, out=(ur, dp, nm), stream=st)
+    for _ in range(3):
+        step()
+    a, b = ev(), ev(); a.record(); [step() for _ in range(5)]; b.record(); torch.cuda.synchronize()
+    out["euroc_stereo_frames_per_s"] = 5 * B / (a.elapsed_time(b) / 1e3)
+    G.close()
+    # --- config 4: SearchForInitialization, 640x480 pairs, 1000 features, ratio 0.9, window 100 ---
+    w, h, P = 640, 480, 256
+    G = gx.ORBextractor(1000, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=2 * P, device=local)
+    cap = G.kp_cap
+    mp = [synth.mono_pair(700000 + i, w, h)[:2] for i in range(8)]
+    batch = np.stack([mp[i % 8][0] for i in range(P)] + [mp[i % 8][1] for i in range(P)])
+    G.extract_batch(torch.from_numpy(batch).cuda(), 0, st)
+    kps = torch.empty((2 * P, cap, 28), dtype=torch.uint8, device="cuda"); desc = torch.empty((2 * P, cap, 32), dtype=torch.uint8, device="cuda")
+    cnt = torch.empty(2 * P, dtype=torch.int32, device="cuda")
+    G.fetch_into(0, 2 * P, kps, desc, cnt, st)
+    torch.cuda.synchronize()
+    prev0 = kps.view(torch.float32).reshape(2 * P, cap, 7)[:P, :, :2].contiguous()
+    m12 = torch.empty((P, cap), dtype=torch.int32, device="cuda"); nmm = torch.empty(P, dtype=torch.int32, device="cuda")
+    L = gx.lib()
+    def init_step():
+        prev = prev0.clone()
+        rc = L.orbx_search_init_batch(kps.data_ptr(), desc.data_ptr(), cnt.data_ptr(), kps[P:].data_ptr(), desc[P:].data_ptr(), cnt[P:].data_ptr(),
+                                      P, cap, w, h, prev.data_ptr(), 0.9, 100, 1, m12.data_ptr(), nmm.data_ptr(), 1, st)
+        assert rc == 0, L.orbx_last_error_string()
+    for _ in range(2):
+        init_step()
+    a, b = ev(), ev(); a.record(); [init_step() for _ in range(5)]; b.record(); torch.cuda.synchronize()
+    out["search_for_initialization_pairs_per_s"] = 5 * P / (a.elapsed_time(b) / 1e3)
+    out["search_for_initialization_matches_per_pair"] = float(nmm.float().mean())
+    G.close()
+    # --- config 5: brute-force 256-bit kNN + ratio, 2000 x 2000 (KITTI-shaped frames), ratio 0.75 ---
+    w, h, P = 1241, 376, 128
+    G = gx.ORBextractor(2000, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=2 * P, device=local)
+    cap = G.kp_cap
+    mp = [synth.mono_pair(800000 + i, w, h)[:2] for i in range(8)]
+    batch = np.stack([mp[i % 8][0] for i in range(P)] + [mp[i % 8][1] for i in range(P)])
+    G.extract_batch(torch.from_numpy(batch).cuda(), 0, st)
+    kps = torch.empty((2 * P, cap, 28), dtype=torch.uint8, device="cuda"); desc = torch.empty((2 * P, cap, 32), dtype=torch.uint8, device="cuda")
+    cnt = torch.empty(2 * P, dtype=torch.int32, device="cuda")
+    G.fetch_into(0, 2 * P, kps, desc, cnt, st)
+    torch.cuda.synchronize()
+    ang = kps.view(torch.float32).reshape(2 * P, cap, 7)[:, :, 3].contiguous()
+    m12 = torch.empty((P, cap), dtype=torch.int32, device="cuda"); nmm = torch.empty(P, dtype=torch.int32, device="cuda")
+    def knn_step():
+        rc = L.orbx_knn_ratio_batch(desc.data_ptr(), ang.data_ptr(), cnt.data_ptr(), desc[P:].data_ptr(), ang[P:].data_ptr(), cnt[P:].data_ptr(),
+                                    P, cap, 50, 0.75, 1, 1, m12.data_ptr(), nmm.data_ptr(), 1, st)
+        assert rc == 0, L.orbx_last_error_string()
+    for _ in range(2):
+        knn_step()
+    a, b = ev(), ev(); a.record(); [knn_step() for _ in range(3)]; b.record(); torch.cuda.synchronize()
+    out["knn_ratio_2000x2000_pairs_per_s"] = 3 * P / (a.elapsed_time(b) / 1e3)
+    out["knn_ratio_matches_per_pair"] = float(nmm.float().mean())
+    G.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -198,6 +275,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="stereo pairs per step per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the configs 3-5 side measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -340,6 +418,13 @@ def main():
                                     "sample": f"{nfr} KITTI-shaped stereo pairs, one pair per std::thread on {threads} threads, {secs:.1f} s"}
         else:
             line["cpu_baseline"] = None
+        if world == 1 and not args.no_secondary and not args.no_cpu_baseline:
+            try:
+                for g in G:
+                    g.close()
+                line["secondary"] = secondary_workloads(gx, torch, local)
+            except Exception as exc:                       # side measurements must never cost the headline
+                line["secondary"] = {"error": repr(exc)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
