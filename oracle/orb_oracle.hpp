@@ -258,6 +258,7 @@ class Extractor {
       p.w = cv_round((float)w * invScale[l]);
       p.h = cv_round((float)h * invScale[l]);
       if (p.w < 2 * (kEdge - 3) + 30 || p.h < 2 * (kEdge - 3) + 30) return -1;
+      if (l > 0 && pyr[l - 1].w == 2 * p.w && pyr[l - 1].h == 2 * p.h) return -3;   // OpenCV would use INTER_AREA here
       p.pitch = p.w + 2 * kEdge;
       p.buf.assign((size_t)p.pitch * (p.h + 2 * kEdge), 0);
       if (l == 0) {

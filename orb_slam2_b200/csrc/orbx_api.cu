@@ -150,6 +150,8 @@ orbx_status geometry(const orbx_extractor* e, int w, int h, int nslots, LevelGeo
     q.plane_stride = align_up((size_t)q.pitch * q.rows, 256);
     q.plane_off = pyr_off;
     pyr_off += q.plane_stride * nslots;
+    if (l > 0 && g[l - 1].w == 2 * q.w && g[l - 1].h == 2 * q.h)
+      return fail(ORBX_ERR_GEOMETRY, "level " + std::to_string(l) + " is an exact 2x decimation: cv::resize(INTER_LINEAR) silently switches to INTER_AREA there, which this library does not reproduce");
     if (l > 0) {
       // tap tables in BORDERED coordinates: entry bx holds the taps of ROI column reflect101(bx-19),
       // pad columns get zero weights (-> pixel 0); 4-entry (32-byte) aligned for 128-bit loads

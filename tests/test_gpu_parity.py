@@ -151,6 +151,29 @@ def test_odd_shapes_exercise_every_fast_variant(gx, oracle, w, h, nf):
     assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
 
 
+@pytest.mark.parametrize("nf,sf,nl,ini,mn", [(500, 1.2, 4, 20, 7), (3000, 1.2, 8, 30, 10), (800, 1.5, 5, 20, 7), (1000, 1.1, 8, 15, 5), (1, 1.2, 8, 20, 7)])
+def test_other_extractor_parameters(gx, oracle, nf, sf, nl, ini, mn):
+    """Other constructor arguments than the three dataset configs: fewer levels, a scale factor
+    whose resize footprint does not fit the tiled kernel (1.5 -> generic resize kernel), other FAST
+    thresholds, a degenerate one-feature budget."""
+    w, h = 752, 480
+    img = synth.mono_frame(35, w, h)
+    G = gx.ORBextractor(nf, sf, nl, ini, mn, max_w=w, max_h=h)
+    E = oracle.Extractor(nf, sf, nl, ini, mn)
+    rk, rd = E.extract(img)
+    gk, gd = G(img)
+    for l in range(nl):
+        assert np.array_equal(G.level(0, l), E.level(l)), f"pyramid level {l}"
+    assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    assert np.array_equal(G.features_per_level(), E.tables()["quota"][:nl])
+
+
+def test_exact_2x_scale_is_rejected(gx):
+    with pytest.raises(gx.OrbxError) as ei:              # cv::resize would switch to INTER_AREA
+        gx.ORBextractor(1000, 2.0, 3, 20, 7, max_w=640, max_h=480)
+    assert ei.value.status == 2 and "INTER_AREA" in str(ei.value)
+
+
 def test_edge_cases(gx):
     G = _ext(gx, 640, 480, 1000)
     k, d = G(np.zeros((0, 0), np.uint8))                 # empty image: silent return
