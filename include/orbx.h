@@ -154,6 +154,26 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
                                  int cap, int th, float nnratio, int check_orientation, int strict_lt,
                                  int* matches12, int* n_matches, int on_device, void* stream);
 
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:45-129; the
+ * local-map search of every tracked frame, called from src/Tracking.cc:1192) for n_frames independent
+ * frames.  Frame f: n[f] keypoints at kps + f*cap (undistorted keypoints, descriptors, mvuRight),
+ * image bounds cols x rows for the 64x48 feature grid, scale_factors = mvScaleFactors.  Its m[f] map
+ * points at index f*mcap carry what Frame::isInFrustum left in each MapPoint (src/Frame.cc:316-322):
+ * mp_in_view (mbTrackInView && !isBad()), mp_proj_x/y/xr (mTrackProjX/Y/XR), mp_level
+ * (mnTrackScaleLevel), mp_view_cos (mTrackViewCos), mp_desc (GetDescriptor()), mp_obs (Observations()).
+ * frame_obs[f*cap + i] (in/out) is F.mvpMapPoints[i] on entry: -1 = none, else that point's
+ * Observations(); assigned[f*cap + i] receives the index of the map point matched to keypoint i by this
+ * call (-1 = none), n_matches[f] the return value.  nnratio/th as in the reference (0.8 and 1 or 3 at
+ * src/Tracking.cc:1185-1192).  All pointers host or all device per on_device. */
+orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right,
+                                         const int* n, int n_frames, int cap, int cols, int rows,
+                                         const float* scale_factors, int nlevels, const uint8_t* mp_in_view,
+                                         const float* mp_proj_x, const float* mp_proj_y, const float* mp_proj_xr,
+                                         const int* mp_level, const float* mp_view_cos, const uint8_t* mp_desc,
+                                         const int* mp_obs, const int* m, int mcap, float th, float nnratio,
+                                         int* frame_obs, int* assigned, int* n_matches, int on_device,
+                                         void* stream);
+
 /* The brute-force search of orbx_knn_ratio_batch for ONE pair, for callers that must not
  * allocate.  It has no counterpart in the reference.  Some callers cannot afford or are not
  * allowed a CUDA allocation on this path: a tracking thread with a per-frame deadline

@@ -68,6 +68,14 @@ int orbo_knn_ratio(const uint8_t* dA, const float* angA, int nA, const uint8_t* 
   return knn_ratio_bucket(dA, angA, nA, dB, angB, nB, th, ratio, checkOri != 0, strict != 0, m12);
 }
 
+int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,
+                            const uint8_t* inView, const float* projX, const float* projY, const float* projXR, const int* level,
+                            const float* viewCos, const uint8_t* mpDesc, const int* mpObs, int m, float th, float nnratio,
+                            int* frameObs, int* assigned) {
+  return search_by_projection_points(k, d, uRight, n, cols, rows, scale, inView, projX, projY, projXR, level, viewCos, mpDesc,
+                                     mpObs, m, th, nnratio, frameObs, assigned);
+}
+
 int orbo_hamming256(const uint8_t* a, const uint8_t* b) { return hamming256(a, b); }
 
 // --- primitives, exported so tests can pin them against cv2 -------------------------------

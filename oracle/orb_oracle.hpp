@@ -548,6 +548,51 @@ inline int search_for_init(const KeyPt* k1, const uint8_t* d1, int n1, const Key
   return nm;
 }
 
+// ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)  src/ORBmatcher.cc:45-129,
+// the local-map search Tracking::SearchLocalPoints runs on every frame (src/Tracking.cc:1192).
+// The MapPoint fields it reads are what Frame::isInFrustum left behind (src/Frame.cc:316-322):
+// inView (mbTrackInView && !isBad), projX/projY/projXR, level (mnTrackScaleLevel), viewCos, the
+// point's descriptor and Observations().  frameObs[i] is the state of F.mvpMapPoints[i] on entry:
+// -1 = none, else that point's Observations(); assigned[i] receives the index of the map point
+// matched to keypoint i by this call (-1 = none).  Returns nmatches.
+inline int search_by_projection_points(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols,
+                                       int rows, const float* scale, const uint8_t* inView, const float* projX,
+                                       const float* projY, const float* projXR, const int* level,
+                                       const float* viewCos, const uint8_t* mpDesc, const int* mpObs, int m,
+                                       float th, float nnratio, int* frameObs, int* assigned) {
+  for (int i = 0; i < n; ++i) assigned[i] = -1;
+  FrameGrid grid(k, n, cols, rows);
+  const bool bFactor = th != 1.0;
+  int nm = 0;
+  std::vector<int> cand;
+  for (int iMP = 0; iMP < m; ++iMP) {
+    if (!inView[iMP]) continue;
+    const int lvl = level[iMP];
+    float r = (viewCos[iMP] > 0.998) ? 2.5f : 4.0f;     // RadiusByViewingCos, :131-137
+    if (bFactor) r *= th;
+    grid.in_area(k, projX[iMP], projY[iMP], r * scale[lvl], lvl - 1, lvl, cand);
+    if (cand.empty()) continue;
+    int best = 256, bestLvl = -1, best2 = 256, bestLvl2 = -1, bestIdx = -1;
+    for (int idx : cand) {
+      if (frameObs[idx] > 0) continue;                    // F.mvpMapPoints[idx] && Observations() > 0
+      if (uRight[idx] > 0) {
+        const float er = std::fabs(projXR[iMP] - uRight[idx]);
+        if (er > r * scale[lvl]) continue;
+      }
+      const int dist = hamming256(mpDesc + 32 * (size_t)iMP, d + 32 * (size_t)idx);
+      if (dist < best) { best2 = best; best = dist; bestLvl2 = bestLvl; bestLvl = k[idx].octave; bestIdx = idx; }
+      else if (dist < best2) { bestLvl2 = k[idx].octave; best2 = dist; }
+    }
+    if (best <= 100) {
+      if (bestLvl == bestLvl2 && (float)best > nnratio * (float)best2) continue;
+      assigned[bestIdx] = iMP;
+      frameObs[bestIdx] = mpObs[iMP];
+      ++nm;
+    }
+  }
+  return nm;
+}
+
 // ORBmatcher::SearchByBoW(KF,KF) with every feature valid and a single vocabulary bucket holding
 // all features of each side in index order (BASELINE config 5).  strict: best < th (KF,KF form,
 // src/ORBmatcher.cc:598) vs best <= th (KF,Frame form, :228).

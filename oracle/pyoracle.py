@@ -113,6 +113,20 @@ def knn_ratio(dA, angA, dB, angB, th=50, ratio=0.75, check_ori=True, strict=True
     return m12, n
 
 
+def search_projection(k, d, uright, cols, rows, scale, mp, th=1.0, nnratio=0.8, frame_obs=None):
+    """mp: dict of arrays inview(u8), projx, projy, projxr (f32), level (i32), viewcos (f32), desc (m,32), obs (i32)."""
+    k = np.ascontiguousarray(k); d = np.ascontiguousarray(d); n = len(k); m = len(mp["level"])
+    uright = np.ascontiguousarray(uright, np.float32); scale = np.ascontiguousarray(scale, np.float32)
+    fo = np.full(n, -1, np.int32) if frame_obs is None else np.ascontiguousarray(frame_obs, np.int32).copy()
+    assigned = np.zeros(n, np.int32)
+    a = {key: np.ascontiguousarray(mp[key], dt) for key, dt in [("inview", np.uint8), ("projx", np.float32), ("projy", np.float32),
+         ("projxr", np.float32), ("level", np.int32), ("viewcos", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
+    nm = lib().orbo_search_projection(_p(k), _p(d), _p(uright), n, cols, rows, _p(scale), _p(a["inview"]), _p(a["projx"]), _p(a["projy"]),
+                                      _p(a["projxr"]), _p(a["level"]), _p(a["viewcos"]), _p(a["desc"]), _p(a["obs"]), m,
+                                      C.c_float(th), C.c_float(nnratio), _p(fo), _p(assigned))
+    return assigned, nm, fo
+
+
 def resize(src, dw, dh):
     src = np.ascontiguousarray(src, np.uint8)
     dst = np.zeros((dh, dw), np.uint8)

@@ -43,7 +43,8 @@ EXPORTS = ["orbx_extractor_create", "orbx_extractor_destroy", "orbx_get_tables",
            "orbx_download_level", "orbx_debug_candidates", "orbx_debug_level_keys",
            "orbx_stereo_match_batch", "orbx_hamming256", "orbx_search_init_batch", "orbx_knn_ratio_batch",
            "orbx_last_error_string", "orbx_kernel_launch_count", "orbx_version", "orbx_set_profiling",
-           "orbx_get_profile", "orbx_stream_synchronize", "orbx_knn_ratio_noalloc"]
+           "orbx_get_profile", "orbx_stream_synchronize", "orbx_knn_ratio_noalloc",
+           "orbx_search_projection_batch"]
 
 STAGES = ["pyramid", "fast", "quadtree", "describe", "stereo_match", "stereo_median"]
 
@@ -86,6 +87,8 @@ def lib():
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_stream_synchronize.argtypes = [C.c_void_p]
+        L.orbx_search_projection_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 9 +
+                                                   [C.c_int, C.c_float, C.c_float] + [C.c_void_p] * 3 + [C.c_int, C.c_void_p])
         L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                              C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]
@@ -327,6 +330,25 @@ class ORBmatcher:
         for p, pr in enumerate(prevs):
             pr[:] = pv[p, :n1[p]]
         return [int(v) for v in nm], [m12[p, :n1[p]].copy() for p in range(npairs)]
+
+    def SearchByProjection(self, F, uRight, scale_factors, mp, th=1.0, frame_obs=None):
+        """SearchByProjection(Frame&, const vector<MapPoint*>&, th): mp is a dict of per-map-point arrays
+        inview, projx, projy, projxr, level, viewcos, desc (m x 32), obs.  Returns (nmatches, assigned, frame_obs)."""
+        k = np.ascontiguousarray(F.mvKeysUn); d = np.ascontiguousarray(F.mDescriptors, np.uint8)
+        n, m = len(k), len(mp["level"])
+        cap, mcap = max(n, 1), max(m, 1)
+        ur = np.ascontiguousarray(uRight, np.float32); sc = np.ascontiguousarray(scale_factors, np.float32)
+        fo = np.full(cap, -1, np.int32) if frame_obs is None else np.ascontiguousarray(frame_obs, np.int32).copy()
+        a = {key: np.ascontiguousarray(mp[key], dt) for key, dt in [("inview", np.uint8), ("projx", np.float32), ("projy", np.float32),
+             ("projxr", np.float32), ("level", np.int32), ("viewcos", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
+        cn = np.array([n], np.int32); cm = np.array([m], np.int32)
+        assigned = np.zeros(cap, np.int32); nm = np.zeros(1, np.int32)
+        _check(lib().orbx_search_projection_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, cn.ctypes.data, 1, cap, F.cols, F.rows,
+                                                  sc.ctypes.data, len(sc), a["inview"].ctypes.data, a["projx"].ctypes.data,
+                                                  a["projy"].ctypes.data, a["projxr"].ctypes.data, a["level"].ctypes.data,
+                                                  a["viewcos"].ctypes.data, a["desc"].ctypes.data, a["obs"].ctypes.data, cm.ctypes.data,
+                                                  mcap, th, self.mfNNratio, fo.ctypes.data, assigned.ctypes.data, nm.ctypes.data, 0, None))
+        return int(nm[0]), assigned[:n].copy(), fo[:n].copy()
 
     def SearchByBoW(self, descA, angA, descB, angB, strict=True):
         """SearchByBoW(KF,KF) with one bucket holding all features (brute-force kNN + ratio)."""

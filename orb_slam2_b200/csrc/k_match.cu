@@ -225,6 +225,139 @@ __global__ void __launch_bounds__(kKnnThreads) k_knn_ratio(KnnArgs a, int capPad
   if (tid == 0) a.nm[p] = s_nm;
 }
 
+// ------------------------------------------------------------------------------------------
+// K8  k_search_projection <- ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)
+//                            src/ORBmatcher.cc:45-129 (+ RadiusByViewingCos :131-137), the local-map
+//                            search of every tracked frame (src/Tracking.cc:1192).
+// One warp per frame, map points in index order (an accepted match occupies its keypoint for the
+// points that follow, H6).  The frame's keypoints are counting-sorted by their 64x48 grid cell
+// (Frame::AssignFeaturesToGrid / PosInGrid, src/Frame.cc:230-245,382-392) in shared memory, so a map
+// point only touches the cell columns of its search window, each a contiguous run; best and second
+// best are the two smallest keys  distance<<32 | cell<<16 | index  (= the reference's first-wins
+// streaming in GetFeaturesInArea order).
+constexpr int kGridCells = 64 * 48;
+
+__global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float2* sxy = reinterpret_cast<float2*>(smem);                       // [cap] sorted by cell
+  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);          // [cap] octave<<28 | cell<<16 | index
+  int* soff = reinterpret_cast<int*>(smeta + a.cap);                   // [kGridCells + 1] cell c = [soff[c], soff[c+1])
+  const int p = blockIdx.x, lane = threadIdx.x;
+  const int n = a.n[p], m = a.m[p];
+  const orbx_keypoint* k = a.k + (size_t)p * a.cap;
+  const uint32_t* d = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
+  const float* uRight = a.uRight + (size_t)p * a.cap;
+  int* frameObs = a.frameObs + (size_t)p * a.cap;
+  int* assigned = a.assigned + (size_t)p * a.cap;
+  const size_t mo = (size_t)p * a.mcap;
+
+  for (int i = lane; i <= kGridCells; i += 32) soff[i] = 0;
+  for (int i = lane; i < n; i += 32) assigned[i] = -1;
+  __syncwarp();
+  for (int i = lane; i < n; i += 32) {
+    const int gx = (int)roundf(__fmul_rn(k[i].x, a.invW)), gy = (int)roundf(__fmul_rn(k[i].y, a.invH));
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) atomicAdd(&soff[gx * 48 + gy + 1], 1);
+  }
+  __syncwarp();
+  int carry = 0;                                                       // inclusive scan: soff[c+1] = end of cell c
+  for (int base = 0; base <= kGridCells; base += 32) {
+    const int i = base + lane;
+    int v = i <= kGridCells ? soff[i] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += t;
+    }
+    if (i <= kGridCells) soff[i] = v + carry;
+    carry += __shfl_sync(0xffffffffu, v, 31);
+  }
+  __syncwarp();
+  // scatter: soff[c+1] currently = end of cell c; fill each cell from its end downwards, which leaves
+  // soff[c+1] = start of cell c, i.e. after the loop cell c = [soff[c+1], old end) -> shift by one
+  for (int i = lane; i < n; i += 32) {
+    const orbx_keypoint kp = k[i];
+    const int gx = (int)roundf(__fmul_rn(kp.x, a.invW)), gy = (int)roundf(__fmul_rn(kp.y, a.invH));
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) {
+      const int c = gx * 48 + gy;
+      const int pos = atomicSub(&soff[c + 1], 1) - 1;
+      sxy[pos] = make_float2(kp.x, kp.y);
+      smeta[pos] = ((uint32_t)kp.octave << 28) | ((uint32_t)c << 16) | (uint32_t)i;
+    }
+  }
+  __syncwarp();
+  // now soff[c+1] = start of cell c and soff[c+2] = start of cell c+1 = end of cell c; soff[0] = 0 is unused
+  const int* cstart = soff + 1;                                         // cell c = [cstart[c], cstart[c+1]) for c < kGridCells-1
+  const int n_in_grid = carry;                                          // end of the last cell
+
+  int nm = 0;
+  for (int iMP = 0; iMP < m; ++iMP) {
+    if (!a.inView[mo + iMP]) continue;
+    const int lvl = min(max(a.level[mo + iMP], 0), a.nlevels - 1);
+    float r = ((double)a.viewCos[mo + iMP] > 0.998) ? 2.5f : 4.0f;
+    if (a.th != 1.0f) r = __fmul_rn(r, a.th);
+    const float R = __fmul_rn(r, a.scale[lvl]);
+    const float x = a.projX[mo + iMP], y = a.projY[mo + iMP];
+    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(x, R), a.invW)));
+    if (cx0 >= 64) continue;
+    const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(x, R), a.invW)));
+    if (cx1 < 0) continue;
+    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(y, R), a.invH)));
+    if (cy0 >= 48) continue;
+    const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(y, R), a.invH)));
+    if (cy1 < 0) continue;
+    const float xr = a.projXR[mo + iMP];
+    uint32_t q[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) q[w] = __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (mo + iMP) * 32) + w);
+    unsigned long long k1 = ~0ull, k2 = ~0ull;
+    for (int ix = cx0; ix <= cx1; ++ix) {
+      const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
+      const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : n_in_grid;
+      for (int e = e_lo + lane; e < e_hi; e += 32) {
+        const uint32_t meta = smeta[e];
+        const int oct = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
+        if (oct < lvl - 1 || oct > lvl) continue;                                     // GetFeaturesInArea level window
+        const float2 pt = sxy[e];
+        if (!(fabsf(__fsub_rn(pt.x, x)) < R && fabsf(__fsub_rn(pt.y, y)) < R)) continue;
+        if (frameObs[idx] > 0) continue;                                              // already holds an observed map point
+        const float ur = uRight[idx];
+        if (ur > 0.f && fabsf(__fsub_rn(xr, ur)) > R) continue;
+        const int dist = ham8(q, d + (size_t)idx * 8);
+        const unsigned long long key = ((unsigned long long)dist << 32) | (meta & 0x0FFFFFFFu);
+        if (key < k1) { k2 = k1; k1 = key; }
+        else if (key < k2) k2 = key;
+      }
+    }
+    // warp merge of the two smallest keys
+    const unsigned hi1 = (unsigned)(k1 >> 32), lo1 = (unsigned)k1;
+    const unsigned ghi = __reduce_min_sync(0xffffffffu, hi1);
+    if (ghi == 0xffffffffu) continue;                                                 // no candidate at all
+    const unsigned glo = __reduce_min_sync(0xffffffffu, hi1 == ghi ? lo1 : 0xffffffffu);
+    const bool owner = hi1 == ghi && lo1 == glo;
+    const unsigned long long mine2 = owner ? k2 : k1;                                 // best key of "the rest" held by this lane
+    const unsigned hi2 = (unsigned)(mine2 >> 32), lo2 = (unsigned)mine2;
+    const unsigned shi = __reduce_min_sync(0xffffffffu, hi2);
+    const unsigned slo = __reduce_min_sync(0xffffffffu, hi2 == shi ? lo2 : 0xffffffffu);
+    const int bestDist = (int)ghi, bestIdx = (int)(glo & 0xFFFF);
+    if (bestDist > 100) continue;                                                     // TH_HIGH
+    const int bestLvl = k[bestIdx].octave;
+    const int bestDist2 = shi == 0xffffffffu ? 256 : (int)shi;
+    const int bestLvl2 = shi == 0xffffffffu ? -1 : k[slo & 0xFFFF].octave;
+    if (bestLvl == bestLvl2 && (float)bestDist > __fmul_rn(a.ratio, (float)bestDist2)) continue;
+    if (lane == 0) { assigned[bestIdx] = iMP; frameObs[bestIdx] = a.mpObs[mo + iMP]; }
+    ++nm;
+    __syncwarp();
+  }
+  if (lane == 0) a.nm[p] = nm;
+}
+
+int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
+  const size_t smem = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_search_projection<<<a.n_pairs, 32, smem, st>>>(a);
+  return 1;
+}
+
 int launch_search_init(const InitMatchArgs& a, cudaStream_t st) {
   k_search_init<<<a.n_pairs, 32, 0, st>>>(a);
   return 1;

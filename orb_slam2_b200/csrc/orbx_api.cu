@@ -661,6 +661,49 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
   return ORBX_OK;
 }
 
+orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right, const int* n,
+                                         int n_frames, int cap, int cols, int rows, const float* scale_factors, int nlevels,
+                                         const uint8_t* mp_in_view, const float* mp_proj_x, const float* mp_proj_y,
+                                         const float* mp_proj_xr, const int* mp_level, const float* mp_view_cos,
+                                         const uint8_t* mp_desc, const int* mp_obs, const int* m, int mcap, float th,
+                                         float nnratio, int* frame_obs, int* assigned, int* n_matches, int on_device,
+                                         void* stream) {
+  if (!kps || !desc || !u_right || !n || !scale_factors || !mp_in_view || !mp_proj_x || !mp_proj_y || !mp_proj_xr || !mp_level ||
+      !mp_view_cos || !mp_desc || !mp_obs || !m || !frame_obs || !assigned || !n_matches)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_frames < 1 || cap < 1 || cap > 8192 || mcap < 1 || cols < 1 || rows < 1 || nlevels < 1 || nlevels > kMaxLevels)
+    return fail(ORBX_ERR_BAD_ARG, "bad sizes (cap <= 8192, nlevels <= 8)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t nf = (size_t)n_frames, fc = nf * cap, fm = nf * mcap;
+  ProjArgs a;
+  CU(sg.in(kps, fc, on_device, &a.k)); CU(sg.in(desc, fc * 32, on_device, &a.d)); CU(sg.in(u_right, fc, on_device, &a.uRight));
+  CU(sg.in(n, nf, on_device, &a.n));
+  CU(sg.in(mp_in_view, fm, on_device, &a.inView)); CU(sg.in(mp_proj_x, fm, on_device, &a.projX)); CU(sg.in(mp_proj_y, fm, on_device, &a.projY));
+  CU(sg.in(mp_proj_xr, fm, on_device, &a.projXR)); CU(sg.in(mp_level, fm, on_device, &a.level)); CU(sg.in(mp_view_cos, fm, on_device, &a.viewCos));
+  CU(sg.in(mp_desc, fm * 32, on_device, &a.mpDesc)); CU(sg.in(mp_obs, fm, on_device, &a.mpObs)); CU(sg.in(m, nf, on_device, &a.m));
+  const int* fo_in = nullptr;
+  CU(sg.in((const int*)frame_obs, fc, on_device, &fo_in));
+  a.frameObs = const_cast<int*>(fo_in);
+  if (on_device) { a.assigned = assigned; a.nm = n_matches; }
+  else { CU(sg.alloc((void**)&a.assigned, fc * 4)); CU(sg.alloc((void**)&a.nm, nf * 4)); }
+  a.n_pairs = n_frames; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels;
+  a.invW = 64.0f / (float)cols; a.invH = 48.0f / (float)rows; a.th = th; a.ratio = nnratio;
+  for (int i = 0; i < kMaxLevels; ++i) a.scale[i] = 1.f;
+  if (on_device) CU(cudaMemcpyAsync(a.scale, scale_factors, sizeof(float) * nlevels, cudaMemcpyDeviceToHost, st));
+  else std::memcpy(a.scale, scale_factors, sizeof(float) * nlevels);
+  if (on_device) CU(cudaStreamSynchronize(st));
+  g_launches += launch_search_projection(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(assigned, a.assigned, fc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_matches, a.nm, nf * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(frame_obs, a.frameObs, fc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
 orbx_status orbx_set_profiling(orbx_extractor* e, int enable) {
   if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
   DeviceGuard guard(e->device);

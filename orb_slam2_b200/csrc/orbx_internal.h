@@ -112,6 +112,17 @@ struct KnnArgs {
 };
 int launch_knn_ratio(const KnnArgs& a, cudaStream_t st);
 
+struct ProjArgs {
+  const orbx_keypoint* k; const uint8_t* d; const float* uRight; const int* n;          // frame side, [P][cap]
+  const uint8_t* inView; const float* projX; const float* projY; const float* projXR;  // map-point side, [P][mcap]
+  const int* level; const float* viewCos; const uint8_t* mpDesc; const int* mpObs; const int* m;
+  int n_pairs, cap, mcap, nlevels;
+  float invW, invH, th, ratio;
+  float scale[kMaxLevels];
+  int* frameObs; int* assigned; int* nm;
+};
+int launch_search_projection(const ProjArgs& a, cudaStream_t st);
+
 // shared by the extern "C" entry points that live outside orbx_api.cu
 orbx_status set_error(orbx_status s, const char* msg);
 void count_launches(int n);

@@ -280,6 +280,45 @@ def test_knn_ratio_bruteforce(gx, oracle):
     assert n1 == 0 and g.tolist() == [-1]
 
 
+@pytest.mark.parametrize("th", [1.0, 3.0])
+def test_search_by_projection_local_map(gx, oracle, th):
+    """SearchByProjection(Frame, MapPoints): map points come from a second, shifted view of the scene
+    (their descriptors, octaves and noisy predicted positions), some already-occupied keypoints, some
+    points out of view, stereo uRight checks on."""
+    cfg = synth.KITTI
+    w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
+    G = _ext(gx, w, h, nf, batch=2)
+    L, R, _ = synth.stereo_pair(90, w, h)
+    a, b, (dx, dy) = synth.mono_pair(91, w, h)
+    G.extract_batch(np.stack([L, R]))
+    ur, dp, nm = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=1, slotL0=0, slotR0=1)
+    (kf, df), _ = G.fetch(0, 2)
+    k2, d2 = G(L[::-1, ::-1].copy())                       # a different view as the "map": rotate by 180 degrees
+    rng = np.random.default_rng(int(th * 10))
+    m = len(k2)
+    mp = dict(inview=(rng.random(m) < 0.9).astype(np.uint8),
+              projx=(w - 1 - k2["x"] + rng.normal(0, 2.0, m)).astype(np.float32),
+              projy=(h - 1 - k2["y"] + rng.normal(0, 2.0, m)).astype(np.float32),
+              level=np.clip(k2["octave"] + rng.integers(0, 2, m), 0, 7).astype(np.int32),
+              viewcos=rng.choice([0.9, 0.9985, 0.999], m).astype(np.float32),
+              desc=d2.copy(), obs=rng.integers(0, 4, m).astype(np.int32))
+    mp["projxr"] = (mp["projx"] - rng.uniform(0, 40, m)).astype(np.float32)
+    # descriptors of a 180-degree view do not match; plant the frame's own descriptors with a few bit flips
+    near = np.array([np.argmin((kf["x"] - px) ** 2 + (kf["y"] - py) ** 2) for px, py in zip(mp["projx"], mp["projy"])])
+    mp["desc"] = df[near].copy()
+    flips = rng.integers(0, 256, (m, 12))
+    for i in range(m):
+        for bit in flips[i][:rng.integers(0, 12)]:
+            mp["desc"][i, bit >> 3] ^= np.uint8(1 << (bit & 7))
+    n = len(kf)
+    frame_obs = np.where(rng.random(n) < 0.1, rng.integers(0, 3, n), -1).astype(np.int32)
+    scale = G.GetScaleFactors()
+    ras, rn, rfo = oracle.search_projection(kf, df, ur[0, :n], w, h, scale, mp, th, 0.8, frame_obs)
+    gn, gas, gfo = gx.ORBmatcher(0.8, True).SearchByProjection(gx.Frame(kf, df, w, h), ur[0, :n], scale, mp, th, frame_obs)
+    assert gn == rn and np.array_equal(gas, ras) and np.array_equal(gfo, rfo)
+    assert rn > 300
+
+
 def test_full_size_batch_properties(gx):
     """BASELINE-sized batch (KITTI stereo): properties that need no oracle — identical frames give
     identical bytes in every slot, output is level-major, per-level counts within [quota, quota+3],
