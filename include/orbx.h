@@ -174,6 +174,26 @@ orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t
                                          int* frame_obs, int* assigned, int* n_matches, int on_device,
                                          void* stream);
 
+/* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono) (src/ORBmatcher.cc:1328-1470;
+ * the motion-model search, called from src/Tracking.cc:886,892) for n_frames independent frame pairs.
+ * Current frame f as in orbx_search_projection_batch (kps/desc/u_right/n, cols x rows, scale_factors).
+ * Last frame f: n_last[f] entries at index f*lcap: last_valid (mvpMapPoints[i] && !mvbOutlier[i]),
+ * last_xw (the map point's world position, 3 floats), last_octave / last_angle (mvKeys[i].octave,
+ * mvKeysUn[i].angle), mp_desc (GetDescriptor()), mp_obs (Observations()).  pose[f*12..] is
+ * CurrentFrame.mTcw: Rcw row-major (9 floats) then tcw (3).  mode[f]: 0, 1 = bForward, 2 = bBackward
+ * (the caller evaluates src/ORBmatcher.cc:1347-1348).  fx, fy, cx, cy, bf are the Frame's intrinsics.
+ * frame_obs / assigned / n_matches as in orbx_search_projection_batch (assigned = index into the last
+ * frame).  All pointers host or all device per on_device. */
+orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right,
+                                               const int* n, int n_frames, int cap, int cols, int rows,
+                                               const float* scale_factors, int nlevels, const float* pose,
+                                               const int* mode, float fx, float fy, float cx, float cy, float bf,
+                                               const uint8_t* last_valid, const float* last_xw,
+                                               const int* last_octave, const float* last_angle,
+                                               const uint8_t* mp_desc, const int* mp_obs, const int* n_last,
+                                               int lcap, float th, int check_orientation, int* frame_obs,
+                                               int* assigned, int* n_matches, int on_device, void* stream);
+
 /* The brute-force search of orbx_knn_ratio_batch for ONE pair, for callers that must not
  * allocate.  It has no counterpart in the reference.  Some callers cannot afford or are not
  * allowed a CUDA allocation on this path: a tracking thread with a per-frame deadline

@@ -76,6 +76,21 @@ int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight
                                      mpObs, m, th, nnratio, frameObs, assigned);
 }
 
+int orbo_search_projection_frame(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,
+                                  const float* Rcw, const float* tcw, float fx, float fy, float cx, float cy, float bf,
+                                  const uint8_t* lastValid, const float* lastXw, const int* lastOctave, const float* lastAngle,
+                                  const uint8_t* mpDesc, const int* mpObs, int nLast, float th, int mode, int checkOri, int* frameObs,
+                                  int* assigned) {
+  return search_by_projection_frame(k, d, uRight, n, cols, rows, scale, Rcw, tcw, fx, fy, cx, cy, bf, lastValid, lastXw, lastOctave,
+                                    lastAngle, mpDesc, mpObs, nLast, th, mode, checkOri != 0, frameObs, assigned);
+}
+
+void orbo_transform_points(const float* Rcw, const float* tcw, const float* xw, float* out, int n) {
+  for (int i = 0; i < n; ++i)
+    for (int r = 0; r < 3; ++r)
+      out[3 * i + r] = ((Rcw[3 * r] * xw[3 * i] + Rcw[3 * r + 1] * xw[3 * i + 1]) + Rcw[3 * r + 2] * xw[3 * i + 2]) + tcw[r];
+}
+
 int orbo_hamming256(const uint8_t* a, const uint8_t* b) { return hamming256(a, b); }
 
 // --- primitives, exported so tests can pin them against cv2 -------------------------------

@@ -593,6 +593,70 @@ inline int search_by_projection_points(const KeyPt* k, const uint8_t* d, const f
   return nm;
 }
 
+// ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono)  src/ORBmatcher.cc:1328-1470,
+// the motion-model search of every tracked frame (src/Tracking.cc:886,892).  Flat form: per keypoint
+// of the last frame, lastValid = (mvpMapPoints[i] && !mvbOutlier[i]), the map point's world position,
+// descriptor and Observations(), the keypoint's octave and angle.  Rcw/tcw are CurrentFrame.mTcw
+// (row-major 3x3 and 3x1).  mode: 0 = neither, 1 = bForward, 2 = bBackward (the caller evaluates
+// :1347-1348 from tlc and mb).  Camera-frame coordinates use OpenCV's small-matrix gemm arithmetic,
+// which tests/test_oracle_cv2.py pins against cv2.gemm: float products and sums, left to right.
+inline int search_by_projection_frame(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols,
+                                      int rows, const float* scale, const float* Rcw, const float* tcw, float fx,
+                                      float fy, float cx, float cy, float bf, const uint8_t* lastValid,
+                                      const float* lastXw, const int* lastOctave, const float* lastAngle,
+                                      const uint8_t* mpDesc, const int* mpObs, int nLast, float th, int mode,
+                                      bool checkOri, int* frameObs, int* assigned) {
+  for (int i = 0; i < n; ++i) assigned[i] = -1;
+  FrameGrid grid(k, n, cols, rows);
+  std::vector<int> hist[kHisto];
+  std::vector<int> cand;
+  int nm = 0;
+  for (int i = 0; i < nLast; ++i) {
+    if (!lastValid[i]) continue;
+    const float* X = lastXw + 3 * (size_t)i;
+    float c3[3];
+    for (int r = 0; r < 3; ++r) c3[r] = ((Rcw[3 * r] * X[0] + Rcw[3 * r + 1] * X[1]) + Rcw[3 * r + 2] * X[2]) + tcw[r];
+    const float xc = c3[0], yc = c3[1];
+    const float invzc = (float)(1.0 / c3[2]);
+    if (invzc < 0) continue;
+    const float u = fx * xc * invzc + cx, v = fy * yc * invzc + cy;
+    if (u < 0.f || u > (float)cols) continue;
+    if (v < 0.f || v > (float)rows) continue;
+    const int oct = lastOctave[i];
+    const float radius = th * scale[oct];
+    if (mode == 1) grid.in_area(k, u, v, radius, oct, -1, cand);
+    else if (mode == 2) grid.in_area(k, u, v, radius, 0, oct, cand);
+    else grid.in_area(k, u, v, radius, oct - 1, oct + 1, cand);
+    if (cand.empty()) continue;
+    int best = 256, bestIdx = -1;
+    for (int i2 : cand) {
+      if (frameObs[i2] > 0) continue;
+      if (uRight[i2] > 0) {
+        const float ur = u - bf * invzc;
+        const float er = std::fabs(ur - uRight[i2]);
+        if (er > radius) continue;
+      }
+      const int dist = hamming256(mpDesc + 32 * (size_t)i, d + 32 * (size_t)i2);
+      if (dist < best) { best = dist; bestIdx = i2; }
+    }
+    if (best <= 100) {
+      assigned[bestIdx] = i;
+      frameObs[bestIdx] = mpObs[i];
+      ++nm;
+      if (checkOri) hist[rot_bin(lastAngle[i], k[bestIdx].angle)].push_back(bestIdx);
+    }
+  }
+  if (checkOri) {
+    int a = -1, b = -1, c = -1;
+    three_maxima(hist, kHisto, a, b, c);
+    for (int i = 0; i < kHisto; ++i) {
+      if (i == a || i == b || i == c) continue;
+      for (int idx : hist[i]) { assigned[idx] = -1; --nm; }
+    }
+  }
+  return nm;
+}
+
 // ORBmatcher::SearchByBoW(KF,KF) with every feature valid and a single vocabulary bucket holding
 // all features of each side in index order (BASELINE config 5).  strict: best < th (KF,KF form,
 // src/ORBmatcher.cc:598) vs best <= th (KF,Frame form, :228).

@@ -127,6 +127,30 @@ def search_projection(k, d, uright, cols, rows, scale, mp, th=1.0, nnratio=0.8, 
     return assigned, nm, fo
 
 
+def search_projection_frame(k, d, uright, cols, rows, scale, Rcw, tcw, cam, last, th=15.0, mode=0, check_ori=True, frame_obs=None):
+    """cam = (fx, fy, cx, cy, bf); last: dict valid(u8), xw (n,3 f32), octave (i32), angle (f32), desc (n,32), obs (i32)."""
+    k = np.ascontiguousarray(k); d = np.ascontiguousarray(d); n = len(k); nl = len(last["octave"])
+    uright = np.ascontiguousarray(uright, np.float32); scale = np.ascontiguousarray(scale, np.float32)
+    Rcw = np.ascontiguousarray(Rcw, np.float32); tcw = np.ascontiguousarray(tcw, np.float32)
+    fo = np.full(n, -1, np.int32) if frame_obs is None else np.ascontiguousarray(frame_obs, np.int32).copy()
+    assigned = np.zeros(n, np.int32)
+    a = {key: np.ascontiguousarray(last[key], dt) for key, dt in [("valid", np.uint8), ("xw", np.float32), ("octave", np.int32),
+         ("angle", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
+    fx, fy, cx, cy, bf = (C.c_float(v) for v in cam)
+    nm = lib().orbo_search_projection_frame(_p(k), _p(d), _p(uright), n, cols, rows, _p(scale), _p(Rcw), _p(tcw), fx, fy, cx, cy, bf,
+                                            _p(a["valid"]), _p(a["xw"]), _p(a["octave"]), _p(a["angle"]), _p(a["desc"]), _p(a["obs"]), nl,
+                                            C.c_float(th), mode, int(check_ori), _p(fo), _p(assigned))
+    return assigned, nm, fo
+
+
+def project_points(Rcw, tcw, xw):
+    """The oracle's camera-frame transform (for pinning against cv2.gemm)."""
+    Rcw = np.ascontiguousarray(Rcw, np.float32); tcw = np.ascontiguousarray(tcw, np.float32); xw = np.ascontiguousarray(xw, np.float32)
+    out = np.zeros_like(xw)
+    lib().orbo_transform_points(_p(Rcw), _p(tcw), _p(xw), _p(out), len(xw))
+    return out
+
+
 def resize(src, dw, dh):
     src = np.ascontiguousarray(src, np.uint8)
     dst = np.zeros((dh, dw), np.uint8)

@@ -44,7 +44,7 @@ EXPORTS = ["orbx_extractor_create", "orbx_extractor_destroy", "orbx_get_tables",
            "orbx_stereo_match_batch", "orbx_hamming256", "orbx_search_init_batch", "orbx_knn_ratio_batch",
            "orbx_last_error_string", "orbx_kernel_launch_count", "orbx_version", "orbx_set_profiling",
            "orbx_get_profile", "orbx_stream_synchronize", "orbx_knn_ratio_noalloc",
-           "orbx_search_projection_batch"]
+           "orbx_search_projection_batch", "orbx_search_projection_frame_batch"]
 
 STAGES = ["pyramid", "fast", "quadtree", "describe", "stereo_match", "stereo_median"]
 
@@ -87,6 +87,9 @@ def lib():
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_stream_synchronize.argtypes = [C.c_void_p]
+        L.orbx_search_projection_frame_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 4 + [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] +
+                                                         [C.c_float] * 5 + [C.c_void_p] * 7 + [C.c_int, C.c_float, C.c_int] +
+                                                         [C.c_void_p] * 3 + [C.c_int, C.c_void_p])
         L.orbx_search_projection_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 9 +
                                                    [C.c_int, C.c_float, C.c_float] + [C.c_void_p] * 3 + [C.c_int, C.c_void_p])
         L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
@@ -348,6 +351,28 @@ class ORBmatcher:
                                                   a["projy"].ctypes.data, a["projxr"].ctypes.data, a["level"].ctypes.data,
                                                   a["viewcos"].ctypes.data, a["desc"].ctypes.data, a["obs"].ctypes.data, cm.ctypes.data,
                                                   mcap, th, self.mfNNratio, fo.ctypes.data, assigned.ctypes.data, nm.ctypes.data, 0, None))
+        return int(nm[0]), assigned[:n].copy(), fo[:n].copy()
+
+    def SearchByProjectionFrame(self, F, uRight, scale_factors, Rcw, tcw, cam, last, th=15.0, mode=0, frame_obs=None):
+        """SearchByProjection(Frame& Current, const Frame& Last, th, bMono).  cam = (fx, fy, cx, cy, bf); last is a dict
+        of per-last-keypoint arrays valid, xw (n,3), octave, angle, desc (n,32), obs.  Returns (nmatches, assigned, frame_obs)."""
+        k = np.ascontiguousarray(F.mvKeysUn); d = np.ascontiguousarray(F.mDescriptors, np.uint8)
+        n, nl = len(k), len(last["octave"])
+        cap, lcap = max(n, 1), max(nl, 1)
+        ur = np.ascontiguousarray(uRight, np.float32); sc = np.ascontiguousarray(scale_factors, np.float32)
+        pose = np.concatenate([np.asarray(Rcw, np.float32).ravel(), np.asarray(tcw, np.float32).ravel()]).astype(np.float32)
+        fo = np.full(cap, -1, np.int32) if frame_obs is None else np.ascontiguousarray(frame_obs, np.int32).copy()
+        a = {key: np.ascontiguousarray(last[key], dt) for key, dt in [("valid", np.uint8), ("xw", np.float32), ("octave", np.int32),
+             ("angle", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
+        cn = np.array([n], np.int32); cl = np.array([nl], np.int32); md = np.array([mode], np.int32)
+        assigned = np.zeros(cap, np.int32); nm = np.zeros(1, np.int32)
+        fx, fy, cx, cy, bf = cam
+        _check(lib().orbx_search_projection_frame_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, cn.ctypes.data, 1, cap, F.cols, F.rows,
+                                                        sc.ctypes.data, len(sc), pose.ctypes.data, md.ctypes.data, fx, fy, cx, cy, bf,
+                                                        a["valid"].ctypes.data, a["xw"].ctypes.data, a["octave"].ctypes.data,
+                                                        a["angle"].ctypes.data, a["desc"].ctypes.data, a["obs"].ctypes.data, cl.ctypes.data,
+                                                        lcap, th, int(self.mbCheckOrientation), fo.ctypes.data, assigned.ctypes.data,
+                                                        nm.ctypes.data, 0, None))
         return int(nm[0]), assigned[:n].copy(), fo[:n].copy()
 
     def SearchByBoW(self, descA, angA, descB, angB, strict=True):

@@ -237,25 +237,16 @@ __global__ void __launch_bounds__(kKnnThreads) k_knn_ratio(KnnArgs a, int capPad
 // streaming in GetFeaturesInArea order).
 constexpr int kGridCells = 64 * 48;
 
-__global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  float2* sxy = reinterpret_cast<float2*>(smem);                       // [cap] sorted by cell
-  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);          // [cap] octave<<28 | cell<<16 | index
-  int* soff = reinterpret_cast<int*>(smeta + a.cap);                   // [kGridCells + 1] cell c = [soff[c], soff[c+1])
-  const int p = blockIdx.x, lane = threadIdx.x;
-  const int n = a.n[p], m = a.m[p];
-  const orbx_keypoint* k = a.k + (size_t)p * a.cap;
-  const uint32_t* d = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
-  const float* uRight = a.uRight + (size_t)p * a.cap;
-  int* frameObs = a.frameObs + (size_t)p * a.cap;
-  int* assigned = a.assigned + (size_t)p * a.cap;
-  const size_t mo = (size_t)p * a.mcap;
-
+// Counting sort of a frame's keypoints by 64x48 grid cell (Frame::AssignFeaturesToGrid / PosInGrid,
+// src/Frame.cc:230-245,382-392), one warp.  On return cell c occupies [soff[c+1], soff[c+2]) of
+// sxy / smeta (the last cell ends at the returned count); keypoints outside the grid are dropped,
+// as the reference does.  smeta = octave<<28 | cell<<16 | keypoint index.
+__device__ __forceinline__ int grid_sort(const orbx_keypoint* k, int n, float invW, float invH, float2* sxy, uint32_t* smeta,
+                                         int* soff, int lane) {
   for (int i = lane; i <= kGridCells; i += 32) soff[i] = 0;
-  for (int i = lane; i < n; i += 32) assigned[i] = -1;
   __syncwarp();
   for (int i = lane; i < n; i += 32) {
-    const int gx = (int)roundf(__fmul_rn(k[i].x, a.invW)), gy = (int)roundf(__fmul_rn(k[i].y, a.invH));
+    const int gx = (int)roundf(__fmul_rn(k[i].x, invW)), gy = (int)roundf(__fmul_rn(k[i].y, invH));
     if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) atomicAdd(&soff[gx * 48 + gy + 1], 1);
   }
   __syncwarp();
@@ -272,11 +263,10 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
     carry += __shfl_sync(0xffffffffu, v, 31);
   }
   __syncwarp();
-  // scatter: soff[c+1] currently = end of cell c; fill each cell from its end downwards, which leaves
-  // soff[c+1] = start of cell c, i.e. after the loop cell c = [soff[c+1], old end) -> shift by one
+  // fill each cell from its end downwards: afterwards soff[c+1] = start of cell c
   for (int i = lane; i < n; i += 32) {
     const orbx_keypoint kp = k[i];
-    const int gx = (int)roundf(__fmul_rn(kp.x, a.invW)), gy = (int)roundf(__fmul_rn(kp.y, a.invH));
+    const int gx = (int)roundf(__fmul_rn(kp.x, invW)), gy = (int)roundf(__fmul_rn(kp.y, invH));
     if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) {
       const int c = gx * 48 + gy;
       const int pos = atomicSub(&soff[c + 1], 1) - 1;
@@ -285,9 +275,26 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
     }
   }
   __syncwarp();
-  // now soff[c+1] = start of cell c and soff[c+2] = start of cell c+1 = end of cell c; soff[0] = 0 is unused
-  const int* cstart = soff + 1;                                         // cell c = [cstart[c], cstart[c+1]) for c < kGridCells-1
-  const int n_in_grid = carry;                                          // end of the last cell
+  return carry;
+}
+
+__global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float2* sxy = reinterpret_cast<float2*>(smem);                       // [cap] sorted by cell
+  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);          // [cap] octave<<28 | cell<<16 | index
+  int* soff = reinterpret_cast<int*>(smeta + a.cap);                   // [kGridCells + 1] cell c = [soff[c], soff[c+1])
+  const int p = blockIdx.x, lane = threadIdx.x;
+  const int n = a.n[p], m = a.m[p];
+  const orbx_keypoint* k = a.k + (size_t)p * a.cap;
+  const uint32_t* d = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
+  const float* uRight = a.uRight + (size_t)p * a.cap;
+  int* frameObs = a.frameObs + (size_t)p * a.cap;
+  int* assigned = a.assigned + (size_t)p * a.cap;
+  const size_t mo = (size_t)p * a.mcap;
+
+  for (int i = lane; i < n; i += 32) assigned[i] = -1;
+  const int n_in_grid = grid_sort(k, n, a.invW, a.invH, sxy, smeta, soff, lane);
+  const int* cstart = soff + 1;                                         // cell c = [cstart[c], cstart[c+1]); the last cell ends at n_in_grid
 
   int nm = 0;
   for (int iMP = 0; iMP < m; ++iMP) {
@@ -355,6 +362,115 @@ int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
   const size_t smem = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   k_search_projection<<<a.n_pairs, 32, smem, st>>>(a);
+  return 1;
+}
+
+// ------------------------------------------------------------------------------------------
+// K9  k_search_projection_frame <- ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono)
+//                                  src/ORBmatcher.cc:1328-1470, the motion-model search (src/Tracking.cc:886,892).
+// Same structure as K8.  Camera-frame coordinates follow OpenCV's small-matrix gemm (float products
+// and sums, left to right, + t; pinned against cv2.gemm in tests/test_oracle_cv2.py).  The rotation
+// histogram is applied after the ordered pass from a per-match event list.
+__global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float2* sxy = reinterpret_cast<float2*>(smem);
+  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);
+  int* soff = reinterpret_cast<int*>(smeta + a.cap);
+  __shared__ int s_hist[kHisto];
+  const int p = blockIdx.x, lane = threadIdx.x;
+  const int n = a.n[p], nLast = a.nLast[p], mode = a.mode[p];
+  const orbx_keypoint* k = a.k + (size_t)p * a.cap;
+  const uint32_t* d = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
+  const float* uRight = a.uRight + (size_t)p * a.cap;
+  int* frameObs = a.frameObs + (size_t)p * a.cap;
+  int* assigned = a.assigned + (size_t)p * a.cap;
+  int* events = a.events + (size_t)p * a.lcap;
+  const size_t lo = (size_t)p * a.lcap;
+  const float* T = a.pose + (size_t)p * 12;
+
+  for (int i = lane; i < n; i += 32) assigned[i] = -1;
+  if (lane < kHisto) s_hist[lane] = 0;
+  const int n_in_grid = grid_sort(k, n, a.invW, a.invH, sxy, smeta, soff, lane);
+  const int* cstart = soff + 1;
+
+  int nm = 0;
+  for (int i = 0; i < nLast; ++i) {
+    if (!a.lastValid[lo + i]) continue;
+    const float X0 = a.lastXw[(lo + i) * 3], X1 = a.lastXw[(lo + i) * 3 + 1], X2 = a.lastXw[(lo + i) * 3 + 2];
+    float c3[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+      c3[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[3 * r], X0), __fmul_rn(T[3 * r + 1], X1)), __fmul_rn(T[3 * r + 2], X2)), T[9 + r]);
+    const float invzc = (float)(1.0 / (double)c3[2]);
+    if (invzc < 0.f) continue;
+    const float u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, c3[0]), invzc), a.cx), v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, c3[1]), invzc), a.cy);
+    if (u < 0.f || u > a.cols || v < 0.f || v > a.rows) continue;
+    if (!(u == u) || !(v == v)) continue;                                              // NaN never passes the reference's window either
+    const int oct = min(max(a.lastOctave[lo + i], 0), a.nlevels - 1);
+    const float R = __fmul_rn(a.th, a.scale[oct]);
+    const int l_lo = mode == 1 ? oct : (mode == 2 ? 0 : oct - 1), l_hi = mode == 1 ? 99 : (mode == 2 ? oct : oct + 1);
+    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(u, R), a.invW)));
+    if (cx0 >= 64) continue;
+    const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(u, R), a.invW)));
+    if (cx1 < 0) continue;
+    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(v, R), a.invH)));
+    if (cy0 >= 48) continue;
+    const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(v, R), a.invH)));
+    if (cy1 < 0) continue;
+    const float ur_pred = __fsub_rn(u, __fmul_rn(a.bf, invzc));
+    uint32_t q[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) q[w] = __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (lo + i) * 32) + w);
+    unsigned long long best = ~0ull;
+    for (int ix = cx0; ix <= cx1; ++ix) {
+      const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
+      const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : n_in_grid;
+      for (int e = e_lo + lane; e < e_hi; e += 32) {
+        const uint32_t meta = smeta[e];
+        const int oct2 = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
+        if (oct2 < l_lo || oct2 > l_hi) continue;
+        const float2 pt = sxy[e];
+        if (!(fabsf(__fsub_rn(pt.x, u)) < R && fabsf(__fsub_rn(pt.y, v)) < R)) continue;
+        if (frameObs[idx] > 0) continue;
+        const float ur = uRight[idx];
+        if (ur > 0.f && fabsf(__fsub_rn(ur_pred, ur)) > R) continue;
+        const unsigned long long key = ((unsigned long long)ham8(q, d + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
+        best = min(best, key);
+      }
+    }
+    const unsigned hi1 = (unsigned)(best >> 32), lo1 = (unsigned)best;
+    const unsigned ghi = __reduce_min_sync(0xffffffffu, hi1);
+    if (ghi > 100u) continue;                                                         // none, or worse than TH_HIGH
+    const unsigned glo = __reduce_min_sync(0xffffffffu, hi1 == ghi ? lo1 : 0xffffffffu);
+    const int bestIdx = (int)(glo & 0xFFFF);
+    if (lane == 0) {
+      assigned[bestIdx] = i;
+      frameObs[bestIdx] = a.mpObs[lo + i];
+      int bin = 0;
+      if (a.checkOri) { bin = rot_bin(a.lastAngle[lo + i], k[bestIdx].angle); s_hist[bin] += 1; }
+      events[nm] = (bin << 16) | bestIdx;
+    }
+    ++nm;
+    __syncwarp();
+  }
+  __syncwarp();
+  if (a.checkOri) {
+    int k_a, k_b, k_c;
+    three_maxima(s_hist, k_a, k_b, k_c);
+    int drop = 0;
+    for (int e = lane; e < nm; e += 32) {
+      const int bin = events[e] >> 16, idx = events[e] & 0xFFFF;
+      if (bin != k_a && bin != k_b && bin != k_c) { assigned[idx] = -1; ++drop; }
+    }
+    nm -= __reduce_add_sync(0xffffffffu, drop);
+  }
+  if (lane == 0) a.nm[p] = nm;
+}
+
+int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st) {
+  const size_t smem = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_projection_frame, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_search_projection_frame<<<a.n_pairs, 32, smem, st>>>(a);
   return 1;
 }
 

@@ -704,6 +704,50 @@ orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t
   return ORBX_OK;
 }
 
+orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right, const int* n,
+                                               int n_frames, int cap, int cols, int rows, const float* scale_factors, int nlevels,
+                                               const float* pose, const int* mode, float fx, float fy, float cx, float cy, float bf,
+                                               const uint8_t* last_valid, const float* last_xw, const int* last_octave,
+                                               const float* last_angle, const uint8_t* mp_desc, const int* mp_obs, const int* n_last,
+                                               int lcap, float th, int check_orientation, int* frame_obs, int* assigned,
+                                               int* n_matches, int on_device, void* stream) {
+  if (!kps || !desc || !u_right || !n || !scale_factors || !pose || !mode || !last_valid || !last_xw || !last_octave || !last_angle ||
+      !mp_desc || !mp_obs || !n_last || !frame_obs || !assigned || !n_matches)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_frames < 1 || cap < 1 || cap > 8192 || lcap < 1 || cols < 1 || rows < 1 || nlevels < 1 || nlevels > kMaxLevels)
+    return fail(ORBX_ERR_BAD_ARG, "bad sizes (cap <= 8192, nlevels <= 8)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t nf = (size_t)n_frames, fc = nf * cap, fl = nf * lcap;
+  ProjFrameArgs a;
+  CU(sg.in(kps, fc, on_device, &a.k)); CU(sg.in(desc, fc * 32, on_device, &a.d)); CU(sg.in(u_right, fc, on_device, &a.uRight));
+  CU(sg.in(n, nf, on_device, &a.n)); CU(sg.in(pose, nf * 12, on_device, &a.pose)); CU(sg.in(mode, nf, on_device, &a.mode));
+  CU(sg.in(last_valid, fl, on_device, &a.lastValid)); CU(sg.in(last_xw, fl * 3, on_device, &a.lastXw));
+  CU(sg.in(last_octave, fl, on_device, &a.lastOctave)); CU(sg.in(last_angle, fl, on_device, &a.lastAngle));
+  CU(sg.in(mp_desc, fl * 32, on_device, &a.mpDesc)); CU(sg.in(mp_obs, fl, on_device, &a.mpObs)); CU(sg.in(n_last, nf, on_device, &a.nLast));
+  const int* fo_in = nullptr;
+  CU(sg.in((const int*)frame_obs, fc, on_device, &fo_in));
+  a.frameObs = const_cast<int*>(fo_in);
+  if (on_device) { a.assigned = assigned; a.nm = n_matches; }
+  else { CU(sg.alloc((void**)&a.assigned, fc * 4)); CU(sg.alloc((void**)&a.nm, nf * 4)); }
+  CU(sg.alloc((void**)&a.events, fl * 4));
+  a.n_pairs = n_frames; a.cap = cap; a.lcap = lcap; a.nlevels = nlevels; a.checkOri = check_orientation;
+  a.invW = 64.0f / (float)cols; a.invH = 48.0f / (float)rows; a.cols = (float)cols; a.rows = (float)rows;
+  a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = bf; a.th = th;
+  for (int i = 0; i < kMaxLevels; ++i) a.scale[i] = 1.f;
+  if (on_device) { CU(cudaMemcpyAsync(a.scale, scale_factors, sizeof(float) * nlevels, cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+  else std::memcpy(a.scale, scale_factors, sizeof(float) * nlevels);
+  g_launches += launch_search_projection_frame(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(assigned, a.assigned, fc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_matches, a.nm, nf * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(frame_obs, a.frameObs, fc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
 orbx_status orbx_set_profiling(orbx_extractor* e, int enable) {
   if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
   DeviceGuard guard(e->device);

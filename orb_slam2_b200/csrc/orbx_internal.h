@@ -123,6 +123,20 @@ struct ProjArgs {
 };
 int launch_search_projection(const ProjArgs& a, cudaStream_t st);
 
+struct ProjFrameArgs {
+  const orbx_keypoint* k; const uint8_t* d; const float* uRight; const int* n;          // current frame, [P][cap]
+  const uint8_t* lastValid; const float* lastXw; const int* lastOctave; const float* lastAngle;   // last frame, [P][lcap]
+  const uint8_t* mpDesc; const int* mpObs; const int* nLast;
+  const float* pose;          // [P][12]: Rcw row-major (9) then tcw (3)
+  const int* mode;            // [P]: 0 neither, 1 forward, 2 backward
+  int n_pairs, cap, lcap, nlevels, checkOri;
+  float invW, invH, cols, rows, fx, fy, cx, cy, bf, th;
+  float scale[kMaxLevels];
+  int* frameObs; int* assigned; int* nm;
+  int* events;                // scratch [P][lcap]: bin<<16 | keypoint index per accepted match
+};
+int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st);
+
 // shared by the extern "C" entry points that live outside orbx_api.cu
 orbx_status set_error(orbx_status s, const char* msg);
 void count_launches(int n);

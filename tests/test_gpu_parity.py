@@ -319,6 +319,43 @@ def test_search_by_projection_local_map(gx, oracle, th):
     assert rn > 300
 
 
+@pytest.mark.parametrize("mode,th,ori", [(0, 15.0, True), (1, 7.0, True), (2, 15.0, False)])
+def test_search_by_projection_motion_model(gx, oracle, mode, th, ori):
+    """SearchByProjection(Current, Last): last-frame stereo points are back-projected to 3-D, moved by a
+    small pose change and searched for in a noisy copy of the same view."""
+    cfg = synth.KITTI
+    w, h, nf, bf, fx = cfg["w"], cfg["h"], cfg["nfeatures"], cfg["bf"], cfg["fx"]
+    fy, cx, cy = fx, 607.19, 185.22                              # Examples/Stereo/KITTI00-02.yaml
+    L, R, _ = synth.stereo_pair(95, w, h)
+    G = _ext(gx, w, h, nf, batch=2)
+    G.extract_batch(np.stack([L, R]))
+    ur, dp, nm = gx.ComputeStereoMatches(G, G, bf, fx, n=1, slotL0=0, slotR0=1)
+    (kl, dl), _ = G.fetch(0, 2)
+    nl = len(kl)
+    z = dp[0, :nl]
+    rng = np.random.default_rng(mode)
+    last = dict(valid=((z > 0) & (rng.random(nl) < 0.9)).astype(np.uint8),
+                xw=np.stack([(kl["x"] - cx) * z / fx, (kl["y"] - cy) * z / fy, z], 1).astype(np.float32),
+                octave=kl["octave"].astype(np.int32), angle=kl["angle"].astype(np.float32), desc=dl.copy(),
+                obs=rng.integers(0, 4, nl).astype(np.int32))
+    cur_img = synth._add_noise(L, 4242, amp=3)
+    cur_r = synth._add_noise(R, 4243, amp=3)
+    G.extract_batch(np.stack([cur_img, cur_r]))
+    ur2, dp2, _ = gx.ComputeStereoMatches(G, G, bf, fx, n=1, slotL0=0, slotR0=1)
+    (kc, dc), _ = G.fetch(0, 2)
+    n = len(kc)
+    ang = 0.002
+    Rcw = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]], np.float32)
+    tcw = np.array([0.05, 0.01, 0.3 if mode == 2 else -0.3], np.float32)
+    frame_obs = np.where(rng.random(n) < 0.08, rng.integers(0, 3, n), -1).astype(np.int32)
+    scale = G.GetScaleFactors()
+    cam = (fx, fy, cx, cy, bf)
+    ras, rn, rfo = oracle.search_projection_frame(kc, dc, ur2[0, :n], w, h, scale, Rcw, tcw, cam, last, th, mode, ori, frame_obs)
+    gn, gas, gfo = gx.ORBmatcher(0.9, ori).SearchByProjectionFrame(gx.Frame(kc, dc, w, h), ur2[0, :n], scale, Rcw, tcw, cam, last, th, mode, frame_obs)
+    assert gn == rn and np.array_equal(gas, ras) and np.array_equal(gfo, rfo)
+    assert rn > 100
+
+
 def test_full_size_batch_properties(gx):
     """BASELINE-sized batch (KITTI stereo): properties that need no oracle — identical frames give
     identical bytes in every slot, output is level-major, per-level counts within [quota, quota+3],

@@ -157,3 +157,17 @@ def test_pyramid_and_candidates_match_cv2_pipeline(oracle, w, h, nf):
         assert len(c) > E.tables()["quota"][l]          # the careful quad-tree phase is exercised
         fallback += int((c["response"] < 20).sum())
     assert fallback > 0                                   # the minThFAST retry is exercised
+
+
+def test_camera_transform_matches_cv2_gemm(oracle):
+    """SearchByProjection computes x3Dc = Rcw*x3Dw + tcw with cv::Mat operators (src/ORBmatcher.cc:1362),
+    i.e. cv::gemm on a 3x3 and a 3x1 CV_32F matrix.  Pin the oracle's arithmetic (float products and
+    sums, left to right, then + t) against the real gemm."""
+    rng = np.random.default_rng(4)
+    for _ in range(40):
+        R = rng.normal(0, 1, (3, 3)).astype(np.float32)
+        t = rng.normal(0, 5, (3, 1)).astype(np.float32)
+        X = rng.normal(0, 30, (500, 3)).astype(np.float32)
+        ours = oracle.project_points(R, t.ravel(), X)
+        ref = np.stack([cv2.gemm(R, X[i].reshape(3, 1), 1.0, t, 1.0).ravel() for i in range(len(X))])
+        assert np.array_equal(ours.view(np.uint32), ref.view(np.uint32))
