@@ -356,6 +356,44 @@ def test_search_by_projection_motion_model(gx, oracle, mode, th, ori):
     assert rn > 100
 
 
+def test_euroc_shard_of_512_frames(gx, oracle):
+    """BASELINE config 3: one GPU's contiguous 512-frame shard of the 4096-frame EuRoC-shaped sequence,
+    processed in 4 batches of 128 stereo pairs.  Distinct frames are checked against the oracle; the
+    frames that repeat (the synthetic sequence cycles through 32 pairs) must reproduce them byte for byte."""
+    from orb_slam2_b200 import sharding
+    cfg = synth.EUROC
+    w, h, nf, B = cfg["w"], cfg["h"], cfg["nfeatures"], 128
+    lo, hi = sharding.shard_range(4096, 8, 3)
+    assert hi - lo == 512
+    pairs = [synth.stereo_pair(lo + i, w, h)[:2] for i in range(32)]
+    G = _ext(gx, w, h, nf, batch=2 * B)
+    ref = {}
+    for i in (0, 7, 31):
+        EL, ER = oracle.Extractor(nf), oracle.Extractor(nf)
+        kl, dl = EL.extract(pairs[i][0]); kr, dr = ER.extract(pairs[i][1])
+        ref[i] = (kl, dl, kr, dr, oracle.stereo(EL, ER, kl, dl, kr, dr, cfg["bf"], cfg["fx"]))
+    first = None
+    for b in range(4):
+        idx = [(b * B + j) % 32 for j in range(B)]
+        G.extract_batch(np.stack([pairs[i][0] for i in idx] + [pairs[i][1] for i in idx]))
+        ur, dp, nm = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=B, slotL0=0, slotR0=B)
+        res = G.fetch(0, 2 * B)
+        for j, i in enumerate(idx):
+            if i in ref and j < 32:
+                kl, dl, kr, dr, (rur, rdp, _, rm) = ref[i]
+                assert res[j][0].tobytes() == kl.tobytes() and np.array_equal(res[j][1], dl)
+                assert res[B + j][0].tobytes() == kr.tobytes() and np.array_equal(res[B + j][1], dr)
+                assert int(nm[j]) == rm and np.array_equal(ur[j, :len(kl)].view(np.uint32), rur.view(np.uint32))
+            if j >= 32:                                    # repeats of frame j % 32 inside the same batch
+                assert res[j][0].tobytes() == res[j % 32][0].tobytes() and np.array_equal(res[j][1], res[j % 32][1])
+                assert np.array_equal(ur[j].view(np.uint32), ur[j % 32].view(np.uint32)) and nm[j] == nm[j % 32]
+        sig = (res[0][0].tobytes(), ur[:32].tobytes())
+        if first is None:
+            first = sig
+        else:
+            assert sig == first                            # every batch of the shard starts on the same frame
+
+
 def test_full_size_batch_properties(gx):
     """BASELINE-sized batch (KITTI stereo): properties that need no oracle — identical frames give
     identical bytes in every slot, output is level-major, per-level counts within [quota, quota+3],
