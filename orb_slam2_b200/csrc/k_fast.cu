@@ -77,8 +77,8 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
 //   win   [win_rows][WP]      window box fetched by TMA from the 16-byte boundary below the cell's first
 //                             column (WP = 64 or 96); pixel (x, y) of the window sits at [y][phase16 + x]
 //   smap  [win_rows-4][SP]    sparse S map with a 1-px zero rim: holds S only where S > minTh
-//   queue [(win_rows-6)*(SP-4)] uint16 (yy<<6 | xx): compass survivors, then (in place) the hot list
-//   rows  [2][64][2] uint32   kept-corner bit masks per tested row, for minTh and for iniTh
+//   queue [(win_rows-6)*iw_max] uint16 (yy<<6 | xx): compass survivors, then (in place) the hot list
+//   rows  [64][2] uint32      kept-corner bit mask per tested row (strict 3x3 maxima above minTh)
 //   bar   one mbarrier
 // A warp walks kCellsPerWarp consecutive cells; the window of the next cell is requested as soon
 // as the scoring stage has finished with the current one, so its latency hides behind the
@@ -87,17 +87,17 @@ constexpr int kCellsPerWarp = 4;
 
 template <int WP>
 __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
-                                                                int n, int win_rows) {
+                                                                int n, int win_rows, int iw_max) {
   constexpr int SP = WP - 16;                 // S-map pitch: 48 (cells up to 36 tested columns) or 80
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int win_bytes = WP * win_rows, s_bytes = SP * (win_rows - 4), q_bytes = 2 * (win_rows - 6) * (SP - 4);
-  const int per_warp = (win_bytes + s_bytes + q_bytes + 1024 + 16 + 127) & ~127;
+  const int win_bytes = WP * win_rows, s_bytes = SP * (win_rows - 4), q_bytes = (2 * (win_rows - 6) * iw_max + 7) & ~7;
+  const int per_warp = (win_bytes + s_bytes + q_bytes + 512 + 16 + 127) & ~127;
   uint8_t* win = smem + (size_t)warp * per_warp;
   uint8_t* smap = win + win_bytes;
   uint16_t* queue = reinterpret_cast<uint16_t*>(smap + s_bytes);
   uint32_t* rows = reinterpret_cast<uint32_t*>(smap + s_bytes + q_bytes);
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smap + s_bytes + q_bytes + 1024);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smap + s_bytes + q_bytes + 512);
   const int min_th = L.min_th, ini_th = L.ini_th;
 
   const long long total_cells = (long long)n * L.cells_per_slot;
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
     const int phase = (kEdge + x0) & 15;
 
     for (int i = lane; i < ((ih + 2) * SP) >> 2; i += 32) reinterpret_cast<uint32_t*>(smap)[i] = 0u;
-    for (int i = lane; i < 256; i += 32) rows[i] = 0u;
+    for (int i = lane; i < 128; i += 32) rows[i] = 0u;
     mbar_wait(bar, waited & 1);
     ++waited;
 
@@ -206,7 +206,6 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
       const bool kept = valid && sc > max(m2, m3);
       const bool kept_ini = kept && sc > ini_th;
       if (kept) atomicOr(&rows[yy * 2 + (xx >> 5)], 1u << (xx & 31));
-      if (kept_ini) atomicOr(&rows[128 + yy * 2 + (xx >> 5)], 1u << (xx & 31));
       cnt_min += __popc(__ballot_sync(0xffffffffu, kept));
       cnt_ini += __popc(__ballot_sync(0xffffffffu, kept_ini));
     }
@@ -220,14 +219,21 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
     }
     if (total > 0) {                                     // warp-uniform
       base = __shfl_sync(0xffffffffu, base, 0);
-      // emit in pixel row-major order: lane r owns tested rows r and r+32
-      const uint32_t* km = rows + (use_ini ? 128 : 0);
+      // emit in pixel row-major order: lane r owns tested rows r and r+32.  When iniTh found corners
+      // only those are emitted: the kept mask is filtered by S > iniTh on the fly.
       uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
+      const int s_need = use_ini ? ini_th : 0;
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         const int yy = half * 32 + lane;
-        const uint32_t w0 = yy < ih ? km[yy * 2] : 0u, w1 = yy < ih ? km[yy * 2 + 1] : 0u;
-        const int mine = __popc(w0) + __popc(w1);
+        unsigned long long m = yy < ih ? (((unsigned long long)rows[yy * 2 + 1] << 32) | rows[yy * 2]) : 0ull;
+        const uint8_t* srow = smap + (yy + 1) * SP + 1;
+        if (use_ini) {                                   // warp-uniform
+          unsigned long long f = 0ull, t = m;
+          while (t) { const int xx = __ffsll((long long)t) - 1; t &= t - 1; if ((int)srow[xx] > s_need) f |= 1ull << xx; }
+          m = f;
+        }
+        const int mine = __popcll(m);
         int incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -236,11 +242,10 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
         }
         int pos = base + incl - mine;
         base += __shfl_sync(0xffffffffu, incl, 31);
-        unsigned long long m = ((unsigned long long)w1 << 32) | w0;
         while (m) {
           const int xx = __ffsll((long long)m) - 1;
           m &= m - 1;
-          const int resp = (int)smap[(yy + 1) * SP + xx + 1] - 1;
+          const int resp = (int)srow[xx] - 1;
           if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
           ++pos;
         }
@@ -251,22 +256,23 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
 }
 
 template <int WP>
-static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_h, cudaStream_t st) {
+static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
   constexpr int SP = WP - 16;
-  const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + 2 * (win_h - 6) * (SP - 4) + 1024 + 16 + 127) & ~(size_t)127;
+  const int iw_max = win_w - 6;
+  const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + ((2 * (win_h - 6) * iw_max + 7) & ~7) + 512 + 16 + 127) & ~(size_t)127;
   const size_t smem = kFastWarps * per_warp;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const long long cells = (long long)n * L.cells_per_slot;
   const long long per_cta = (long long)kFastWarps * kCellsPerWarp;
-  k_fast_cells<WP><<<(unsigned)((cells + per_cta - 1) / per_cta), kFastWarps * 32, smem, st>>>(L, maps, first_slot, n, win_h);
+  k_fast_cells<WP><<<(unsigned)((cells + per_cta - 1) / per_cta), kFastWarps * 32, smem, st>>>(L, maps, first_slot, n, win_h, iw_max);
 }
 
 int fast_window_pitch(int win_w) { return win_w + 15 <= 64 ? 64 : 96; }
 
 int launch_fast(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
   // the TMA box starts at the 16-byte boundary below the window: phase (<= 15) + width must fit the pitch
-  if (fast_window_pitch(win_w) == 64) launch_fast_t<64>(L, maps, first_slot, n, win_h, st);
-  else launch_fast_t<96>(L, maps, first_slot, n, win_h, st);
+  if (fast_window_pitch(win_w) == 64) launch_fast_t<64>(L, maps, first_slot, n, win_w, win_h, st);
+  else launch_fast_t<96>(L, maps, first_slot, n, win_w, win_h, st);
   return 1;
 }
 
