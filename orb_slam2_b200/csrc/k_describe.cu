@@ -24,10 +24,12 @@ constexpr int kKpPerWarp = 4;             // keypoints per warp: the next tile i
 constexpr int kTileR = kDescTileH, kTileP = kDescTileW;   // raw tile rows / pitch (TMA box); the keypoint sits at (21, phase16+21)
 constexpr int kHtC = 40, kHtP = 46;       // horizontal pass, TRANSPOSED: [column][row] uint16, 46-entry pitch (bank-conflict free)
 constexpr int kBlP = 40, kBlR = 38;       // blurred tile pitch / rows (row 37 is scratch), centre (18,18)
-// per-warp shared memory, 128-byte aligned pieces: 2 raw tiles (double buffer) | Ht | blurred | 2 mbarriers
-constexpr int kOffTile1 = 2816, kOffHt = 5632, kOffBl = 9344, kOffBar = 10880, kWarpSmem = 11008;
-static_assert(kTileR * kTileP <= kOffTile1 && kOffHt + kHtC * kHtP * 2 <= kOffBl && kOffBl + kBlR * kBlP <= kOffBar, "smem carve-up");
-static_assert(kWarpSmem % 128 == 0 && kOffTile1 % 128 == 0, "TMA destinations must be 128-byte aligned");
+// per-warp shared memory, 128-byte aligned pieces: raw tile | Ht | blurred | mbarrier.  The raw tile is
+// dead once the moments and the horizontal pass have read it, so the NEXT keypoint's tile is requested
+// right then and lands while the vertical pass and the descriptor of this one run.
+constexpr int kOffHt = 2816, kOffBl = 6528, kOffBar = 8064, kWarpSmem = 8192;
+static_assert(kTileR * kTileP <= kOffHt && kOffHt + kHtC * kHtP * 2 <= kOffBl && kOffBl + kBlR * kBlP <= kOffBar, "smem carve-up");
+static_assert(kWarpSmem % 128 == 0, "TMA destinations must be 128-byte aligned");
 
 // 7x7 sigma-2 taps of cv2's 8-bit path, {18,34,48,56,48,34,18}/256, packed for dp4a / dp2a
 __device__ __forceinline__ unsigned pk4(unsigned a, unsigned b, unsigned c, unsigned d) {
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   uint8_t* wbase = smem + (size_t)warp * kWarpSmem;
   uint16_t* ht = reinterpret_cast<uint16_t*>(wbase + kOffHt);
   uint8_t* bl = wbase + kOffBl;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(wbase + kOffBar);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(wbase + kOffBar);
 
   const int img = blockIdx.x / ctas_per_img;
   if (img >= n_img) return;
@@ -135,32 +137,24 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   if (j0 >= total) return;
   const int nk = min(kKpPerWarp, total - j0);
 
-  if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); fence_barrier_init(); }
+  if (lane == 0) { mbar_init(bar, 1); fence_barrier_init(); }
   __syncwarp();
   // TMA: the 64x43 box that holds the 43x43 tile centred on the keypoint, straight from the bordered plane (+19 offset)
   KpRef nxt = locate_kp(L, slot, j0, incl, myc, lane);
   if (lane == 0) {
-    mbar_expect_tx(&bars[0], kTileR * kTileP);
-    tma_load_3d(wbase, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, &bars[0]);
+    mbar_expect_tx(bar, kTileR * kTileP);
+    tma_load_3d(wbase, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, bar);
   }
+  const uint8_t* raw = wbase;
 
   for (int t = 0; t < nk; ++t) {
   const KpRef cur = nxt;
   const int j = j0 + t;
-  if (t + 1 < nk) {                                   // warp-uniform
-    nxt = locate_kp(L, slot, j + 1, incl, myc, lane);
-    if (lane == 0) {
-      uint8_t* dst = wbase + (((t + 1) & 1) ? kOffTile1 : 0);
-      mbar_expect_tx(&bars[(t + 1) & 1], kTileR * kTileP);
-      tma_load_3d(dst, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, &bars[(t + 1) & 1]);
-    }
-  }
-  const uint8_t* raw = wbase + ((t & 1) ? kOffTile1 : 0);
   const int level = cur.level, px = cur.px, py = cur.py, resp = cur.resp;
   const LevelGeom& g = L.geom[level];
   // the TMA box starts at the 16-byte boundary below the tile: tile column 0 is smem column phase16
   const int phase16 = (px + kEdge - 21) & 15, g0 = phase16 >> 2, phase = phase16 & 3;
-  mbar_wait(&bars[t & 1], (t >> 1) & 1);
+  mbar_wait(bar, t & 1);
 
   // intensity-centroid moments over the radius-15 disc, int32 (src/ORBextractor.cc:77-104).
   // lane = column u (31 of them), rows unrolled: every load is independent, the disc half-width
@@ -208,6 +202,14 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
     }
   }
   __syncwarp();
+  if (t + 1 < nk) {                                   // warp-uniform: the raw tile is dead, fetch the next keypoint's
+    nxt = locate_kp(L, slot, j + 1, incl, myc, lane);
+    if (lane == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(bar, kTileR * kTileP);
+      tma_load_3d(wbase, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, bar);
+    }
+  }
   // Vertical pass: one task = one column and half of the rows, walking down two output rows per
   // step with a 4-word sliding window and 8 dp2a (u16 x u8).  Rounding constant rides in the
   // accumulator.  37 columns x 2 halves = 74 tasks; consecutive lanes take consecutive columns.
