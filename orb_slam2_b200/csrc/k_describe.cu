@@ -23,13 +23,14 @@ constexpr int kDescWarps = 4;
 constexpr int kKpPerWarp = 4;             // keypoints per warp: the next tile is in flight while this one is processed
 constexpr int kTileR = kDescTileH, kTileP = kDescTileW;   // raw tile rows / pitch (TMA box); the keypoint sits at (21, phase16+21)
 constexpr int kHtC = 40, kHtP = 46;       // horizontal pass, TRANSPOSED: [column][row] uint16, 46-entry pitch (bank-conflict free)
-constexpr int kBlP = 40, kBlR = 38;       // blurred tile pitch / rows (row 37 is scratch), centre (18,18)
-// per-warp shared memory, 128-byte aligned pieces: raw tile | Ht | blurred | mbarrier.  The raw tile is
-// dead once the moments and the horizontal pass have read it, so the NEXT keypoint's tile is requested
-// right then and lands while the vertical pass and the descriptor of this one run.
-constexpr int kOffHt = 2816, kOffBl = 6528, kOffBar = 8064, kWarpSmem = 8192;
-static_assert(kTileR * kTileP <= kOffHt && kOffHt + kHtC * kHtP * 2 <= kOffBl && kOffBl + kBlR * kBlP <= kOffBar, "smem carve-up");
-static_assert(kWarpSmem % 128 == 0, "TMA destinations must be 128-byte aligned");
+constexpr int kBlC = 40, kBlP = 44;       // blurred patch, TRANSPOSED: [column][row] bytes, rows 0..37 (row 37 is scratch), centre (18,18)
+// per-warp shared memory: raw tile | Ht | blurred | mbarrier.  The raw tile is dead once the moments and
+// the horizontal pass have read it, so the NEXT keypoint's tile is requested right then and lands while
+// the vertical pass and the descriptor of this one run.  The CTA's tail holds the test pattern as floats.
+constexpr int kOffHt = 2816, kOffBl = 6528, kOffBar = 8288, kWarpSmem = 8320;
+constexpr int kPatBytes = 32 * 8 * 16;    // [test-in-byte 8][lane 32] float4 {x0, y0, x1, y1}
+static_assert(kTileR * kTileP <= kOffHt && kOffHt + kHtC * kHtP * 2 <= kOffBl && kOffBl + kBlC * kBlP <= kOffBar, "smem carve-up");
+static_assert(kWarpSmem % 128 == 0 && kOffBar % 8 == 0, "TMA destinations must be 128-byte aligned");
 
 // 7x7 sigma-2 taps of cv2's 8-bit path, {18,34,48,56,48,34,18}/256, packed for dp4a / dp2a
 __device__ __forceinline__ unsigned pk4(unsigned a, unsigned b, unsigned c, unsigned d) {
@@ -41,7 +42,10 @@ __device__ __forceinline__ unsigned pk4(unsigned a, unsigned b, unsigned c, unsi
 }
 
 // umax of the reference for HALF_PATCH_SIZE = 15 (src/ORBextractor.cc:454-469)
-__device__ constexpr int kUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+// The disc is symmetric (|u| <= umax[|v|]  <=>  |v| <= umax[|u|]), so a lane that owns column u just needs
+// its own row limit umax[|u|]; the table rides in one 64-bit literal, one nibble per entry.
+// umax[0..15] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3}; the host checks its table against this at create
+constexpr unsigned long long kUmaxNibbles = 0x3689ABCDDEEEFFFFull;
 
 struct SinCosTab { double sign[4], hpi_inv, hpi, c0, c1, c2, c3, c4, s1, s2, s3; };
 __constant__ SinCosTab c_sincos[2] = {
@@ -97,6 +101,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
+template <int N> struct IntC { static constexpr int value = N; };
 struct KpRef { int level, px, py, resp; };
 
 // keypoint j of the level-major concatenation of the per-level lists (src/ORBextractor.cc:1073-1103)
@@ -119,6 +124,12 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   uint16_t* ht = reinterpret_cast<uint16_t*>(wbase + kOffHt);
   uint8_t* bl = wbase + kOffBl;
   uint64_t* bar = reinterpret_cast<uint64_t*>(wbase + kOffBar);
+  float4* pat = reinterpret_cast<float4*>(smem + kDescWarps * kWarpSmem);
+  for (int i = threadIdx.x; i < 256; i += kDescWarps * 32) {          // i = lane * 8 + test
+    const char4 q = __ldg(pattern + i);
+    pat[(i & 7) * 32 + (i >> 3)] = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
+  }
+  __syncthreads();
 
   const int img = blockIdx.x / ctas_per_img;
   if (img >= n_img) return;
@@ -162,13 +173,13 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   int m10, m01;
   {
     const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+    const int vlim = lane < 31 ? (int)((kUmaxNibbles >> (4 * (au & 15))) & 15ull) : -1;
     const uint8_t* colp = raw + 21 * kTileP + phase16 + 21 + (lane < 31 ? u : 0);
-    int s_all = 0, s_v = 0;
+    int s_all = lane < 31 ? (int)colp[0] : 0, s_v = 0;
 #pragma unroll
-    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-      const int I = (lane < 31 && au <= kUmax[v < 0 ? -v : v]) ? (int)colp[v * kTileP] : 0;
-      s_all += I;
-      s_v += v * I;
+    for (int v = 1; v <= kHalfPatch; ++v) {
+      const int a = colp[v * kTileP], b = colp[-v * kTileP];   // always inside the tile: load first, then decide
+      if (v <= vlim) { s_all += a + b; s_v += v * (a - b); }
     }
     m10 = u * s_all;
     m01 = s_v;
@@ -189,16 +200,19 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
     const unsigned B0 = pk4(0, 18, 34, 48), B1 = pk4(56, 48, 34, 18);
     const unsigned C0 = pk4(0, 0, 18, 34), C1 = pk4(48, 56, 48, 34), C2 = pk4(18, 0, 0, 0);
     const unsigned D0 = pk4(0, 0, 0, 18), D1 = pk4(34, 48, 56, 48), D2 = pk4(34, 18, 0, 0);
-    const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw);
-    for (int t = lane; t < kTileR * 10; t += 32) {
-      const int r = t / 10, gq = t - r * 10;
-      const uint32_t* rp = rw + r * (kTileP / 4) + g0 + gq;
-      const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
-      uint16_t* o = ht + (4 * gq) * kHtP + r;
-      o[0] = (uint16_t)__dp4a(w1, A1, __dp4a(w0, A0, 0u));
-      o[kHtP] = (uint16_t)__dp4a(w1, B1, __dp4a(w0, B0, 0u));
-      o[2 * kHtP] = (uint16_t)__dp4a(w2, C2, __dp4a(w1, C1, __dp4a(w0, C0, 0u)));
-      o[3 * kHtP] = (uint16_t)__dp4a(w2, D2, __dp4a(w1, D1, __dp4a(w0, D0, 0u)));
+    // lanes 0..29: 3 rows x 10 four-column groups per sweep, 15 sweeps (43 rows); all offsets are immediates
+    const int lr = lane / 10, gq = lane - lr * 10;
+    const uint32_t* rp = reinterpret_cast<const uint32_t*>(raw) + lr * (kTileP / 4) + g0 + gq;
+    uint16_t* o = ht + (4 * gq) * kHtP + lr;
+#pragma unroll
+    for (int it = 0; it < 15; ++it) {
+      if (lane < 30 && 3 * it + lr < kTileR) {
+        const uint32_t w0 = rp[it * 3 * (kTileP / 4)], w1 = rp[it * 3 * (kTileP / 4) + 1], w2 = rp[it * 3 * (kTileP / 4) + 2];
+        o[3 * it] = (uint16_t)__dp4a(w1, A1, __dp4a(w0, A0, 0u));
+        o[3 * it + kHtP] = (uint16_t)__dp4a(w1, B1, __dp4a(w0, B0, 0u));
+        o[3 * it + 2 * kHtP] = (uint16_t)__dp4a(w2, C2, __dp4a(w1, C1, __dp4a(w0, C0, 0u)));
+        o[3 * it + 3 * kHtP] = (uint16_t)__dp4a(w2, D2, __dp4a(w1, D1, __dp4a(w0, D0, 0u)));
+      }
     }
   }
   __syncwarp();
@@ -210,28 +224,35 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
       tma_load_3d(wbase, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, bar);
     }
   }
-  // Vertical pass: one task = one column and half of the rows, walking down two output rows per
-  // step with a 4-word sliding window and 8 dp2a (u16 x u8).  Rounding constant rides in the
-  // accumulator.  37 columns x 2 halves = 74 tasks; consecutive lanes take consecutive columns.
+  // Vertical pass: one task = one column and a run of row pairs, walking down two output rows per
+  // step with a 4-word sliding window and 8 dp2a (u16 x u8); the rounding constant rides in the
+  // accumulator and the two result bytes leave as one 16-bit store into the transposed patch.
+  // 37 columns x rows 0..37: two sweeps of 10-step tasks (columns x {rows 0-19, rows 18-37}), and the
+  // last 10 half-columns cut in three 4-step pieces so that the third sweep keeps 30 lanes busy.
   {
     const unsigned E0 = pk4(18, 34, 0, 0), E1 = pk4(48, 56, 0, 0), E2 = pk4(48, 34, 0, 0), E3 = pk4(18, 0, 0, 0);
     const unsigned F0 = pk4(0, 18, 0, 0), F1 = pk4(34, 48, 0, 0), F2 = pk4(56, 48, 0, 0), F3 = pk4(34, 18, 0, 0);
-    for (int t = lane; t < 74; t += 32) {
-      const int half = t >= 37, col = phase + (half ? t - 37 : t);
-      const int r0 = half ? 18 : 0;
-      const uint32_t* hc = reinterpret_cast<const uint32_t*>(ht + col * kHtP + r0);
+    auto vrun = [&](const int col, const int rbase, auto nsteps) {
+      const uint32_t* hc = reinterpret_cast<const uint32_t*>(ht + col * kHtP + rbase);
+      uint16_t* o = reinterpret_cast<uint16_t*>(bl + col * kBlP + rbase);
       uint32_t W0 = hc[0], W1 = hc[1], W2 = hc[2];
-      uint8_t* o = bl + r0 * kBlP + col;
-#pragma unroll 2
-      for (int sidx = 0; sidx < 10; ++sidx) {
+#pragma unroll
+      for (int sidx = 0; sidx < decltype(nsteps)::value; ++sidx) {
         const uint32_t W3 = hc[sidx + 3];
         const unsigned e = __dp2a_lo(W3, E3, __dp2a_lo(W2, E2, __dp2a_lo(W1, E1, __dp2a_lo(W0, E0, 32768u))));
         const unsigned f = __dp2a_lo(W3, F3, __dp2a_lo(W2, F2, __dp2a_lo(W1, F1, __dp2a_lo(W0, F0, 32768u))));
-        o[0] = (uint8_t)(e >> 16);
-        o[kBlP] = (uint8_t)(f >> 16);
-        o += 2 * kBlP;
+        o[sidx] = (uint16_t)__byte_perm(e, f, 0x0062);   // byte 2 of e (row), byte 2 of f (row + 1)
         W0 = W1; W1 = W2; W2 = W3;
       }
+    };
+    vrun(phase + lane, 0, IntC<10>{});
+    {
+      const int t = 32 + lane, half = t >= 37;
+      vrun(phase + (half ? t - 37 : t), half ? 18 : 0, IntC<10>{});
+    }
+    if (lane < 30) {
+      const int q = lane / 3, part = lane - 3 * q;
+      vrun(phase + 27 + q, 18 + 6 * part, IntC<4>{});
     }
   }
   __syncwarp();
@@ -239,17 +260,20 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   // steered BRIEF: lane i produces descriptor byte i (tests 8i .. 8i+7)
   const float rad = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
   const float ca = libm_sincos(rad, 1), sb = libm_sincos(rad, 0);
-  const uint8_t* ctr = bl + 18 * kBlP + phase + 18;
+  // cvRound (round half to even) by the 1.5*2^23 trick: adding the constant rounds the sum to an integer
+  // exactly like lrintf, and the integer then sits in the low mantissa bits
+  const float kMagic = 12582912.0f;
+  const uint32_t kBias = 0x4B400000u * (uint32_t)(kBlP + 1);
+  const uint8_t* ctr = bl + (phase + 18) * kBlP + 18;
   uint32_t byte = 0;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    const char4 q = __ldg(pattern + lane * 8 + t);
-    const float x0 = (float)q.x, y0 = (float)q.y, x1 = (float)q.z, y1 = (float)q.w;
-    const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
-    const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
-    const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
-    const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-    const int v0 = ctr[r0 * kBlP + c0], v1 = ctr[r1 * kBlP + c1];
+    const float4 q = pat[t * 32 + lane];
+    const uint32_t r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(q.x, sb), __fmul_rn(q.y, ca)), kMagic));
+    const uint32_t c0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(q.x, ca), __fmul_rn(q.y, sb)), kMagic));
+    const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(q.z, sb), __fmul_rn(q.w, ca)), kMagic));
+    const uint32_t c1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(q.z, ca), __fmul_rn(q.w, sb)), kMagic));
+    const int v0 = ctr[(int)(c0 * kBlP + r0 - kBias)], v1 = ctr[(int)(c1 * kBlP + r1 - kBias)];
     byte |= (uint32_t)(v0 < v1) << t;
   }
   const size_t oi = (size_t)slot * L.kp_cap + j;
@@ -272,7 +296,7 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
 int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st) {
   const int per_cta = kDescWarps * kKpPerWarp;
   const int ctas_per_img = (L.kp_cap + per_cta - 1) / per_cta;
-  const size_t smem = (size_t)kDescWarps * kWarpSmem;
+  const size_t smem = (size_t)kDescWarps * kWarpSmem + kPatBytes;
   k_describe<<<n * ctas_per_img, kDescWarps * 32, smem, st>>>(L, maps, first_slot, n, ctas_per_img, d_umax, d_pattern);
   return 1;
 }
