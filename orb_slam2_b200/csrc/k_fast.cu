@@ -58,19 +58,21 @@ __device__ __forceinline__ int arc_score_rest(const uint8_t* c, const int wp, co
   return max((int)(s & 0xFFFF), (int)(s >> 16)) - 256;
 }
 // Compass pre-test: any 9-arc of the 16-ring holds two neighbouring compass points, so
-// S <= max over the 4 neighbouring compass pairs of min(d) (per polarity).  Fills P[0,4,8,12].
-__device__ __forceinline__ int compass_bound(const uint8_t* c, const int wp, const uint32_t base, uint32_t (&P)[16]) {
+// S <= max over the 4 neighbouring compass pairs of min(d) (per polarity).  Fills P[0,4,8,12] and
+// returns the bound of both polarities packed as (bound + 256) in each half.
+__device__ __forceinline__ uint32_t pack_base(const int v) {     // lo = v + 256, hi = 256 - v, one IMAD
+  return (uint32_t)v * 0xFFFF0001u + 0x01000100u;
+}
+__device__ __forceinline__ uint32_t compass_packed(const uint8_t* c, const int wp, uint32_t (&P)[16]) {
+  const uint32_t base = pack_base(c[0]);
   ORBX_RING(0, c + 3 * wp, 0); ORBX_RING(4, c, 3); ORBX_RING(8, c - 3 * wp, 0); ORBX_RING(12, c, -3);
   const uint32_t a = vmin3(P[0], P[4], P[4]), b = vmin3(P[4], P[8], P[8]), d = vmin3(P[8], P[12], P[12]), e = vmin3(P[12], P[0], P[0]);
-  const uint32_t m = vmax3(vmax3(a, b, d), e, e);
-  return max((int)(m & 0xFFFF), (int)(m >> 16)) - 256;
+  return vmax3(vmax3(a, b, d), e, e);
 }
 __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
-  const int v = c[0];
-  const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
   uint32_t P[16];
-  compass_bound(c, wp, base, P);
-  return arc_score_rest(c, wp, base, P);
+  compass_packed(c, wp, P);
+  return arc_score_rest(c, wp, pack_base(c[0]), P);
 }
 
 // Shared memory per warp:
@@ -151,24 +153,48 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
     ++waited;
 
     // stage 1: compass pre-test for every tested pixel (lane = column, up to two 32-column chunks);
-    // a pixel whose bound is <= minTh cannot be a corner at either threshold.  Survivors are
-    // appended to one warp-wide queue (ballot + popc) so that stage 2 is load balanced.
+    // a pixel whose bound is <= minTh cannot be a corner at either threshold.  The ballot of row yy is
+    // parked in lane yy; after the sweep every lane appends its row's survivors to one warp-wide queue
+    // (prefix sum of the per-row counts), row-major, so that stage 2 is load balanced and reads
+    // neighbouring columns.  The threshold test is done on the packed pair: adding
+    // 0x8000 - (minTh + 257) to each half sets its bit 15 iff bound > minTh.
     int ncand = 0;
+    const uint32_t kpass = (uint32_t)(0x8000 - 257 - min_th) * 0x00010001u;
 #pragma unroll
     for (int ch = 0; ch < 2; ++ch) {
-      const int xx = ch * 32 + lane;
       if (ch * 32 < iw) {                     // warp-uniform
+        const int xx = ch * 32 + lane;
         const uint8_t* cptr = win + 3 * WP + phase + min(xx, iw - 1) + 3;
-        for (int yy = 0; yy < ih; ++yy) {
-          const int v = cptr[0];
-          const uint32_t base = (uint32_t)(v + 256) | ((uint32_t)(256 - v) << 16);
+        const uint32_t colmask = iw - ch * 32 >= 32 ? 0xffffffffu : (1u << (iw - ch * 32)) - 1u;
+        uint32_t rm0 = 0u, rm1 = 0u;
+        const int h0 = min(ih, 32);
+        for (int yy = 0; yy < h0; ++yy) {
           uint32_t P[16];
-          const bool pass = xx < iw && compass_bound(cptr, WP, base, P) > min_th;
-          const uint32_t bal = __ballot_sync(0xffffffffu, pass);
-          if (pass) queue[ncand + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)((yy << 6) | xx);
-          ncand += __popc(bal);
+          const uint32_t bal = __ballot_sync(0xffffffffu, ((compass_packed(cptr, WP, P) + kpass) & 0x80008000u) != 0u);
+          if (lane == yy) rm0 = bal;
           cptr += WP;
         }
+        for (int yy = 32; yy < ih; ++yy) {
+          uint32_t P[16];
+          const uint32_t bal = __ballot_sync(0xffffffffu, ((compass_packed(cptr, WP, P) + kpass) & 0x80008000u) != 0u);
+          if (lane == yy - 32) rm1 = bal;
+          cptr += WP;
+        }
+        rm0 &= colmask; rm1 &= colmask;
+        const int mine = __popc(rm0) | (__popc(rm1) << 16);      // rows 0-31 first, then rows 32+
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        const int tot = __shfl_sync(0xffffffffu, incl, 31), excl = incl - mine;
+        uint16_t* q0 = queue + ncand + (excl & 0xffff);
+        uint16_t* q1 = queue + ncand + (tot & 0xffff) + (excl >> 16);
+        ncand += (tot & 0xffff) + (tot >> 16);
+        const int tag = (lane << 6) | (ch * 32);
+        while (rm0) { const int b = __ffs((int)rm0) - 1; rm0 &= rm0 - 1u; *q0++ = (uint16_t)(tag + b); }
+        while (rm1) { const int b = __ffs((int)rm1) - 1; rm1 &= rm1 - 1u; *q1++ = (uint16_t)(tag + (32 << 6) + b); }
       }
     }
     __syncwarp();
