@@ -27,19 +27,32 @@ __global__ void __launch_bounds__(256) k_border_level0(DeviceLayout L, const uin
   const int img = (int)(tid / per_img);
   const int rem = (int)(tid - (long long)img * per_img);
   const int by = rem / vec_per_row, bx0 = (rem - by * vec_per_row) << 4;
-  const uint8_t* s = src + (size_t)img * src_img_stride + (size_t)reflect101(by - kEdge, g.h) * src_pitch;
+  const int sy = reflect101(by - kEdge, g.h), x0 = bx0 - kEdge;
+  const uint8_t* s = src + (size_t)img * src_img_stride + (size_t)sy * src_pitch;
   uint32_t wds[4];
+  if (x0 >= 0 && x0 + 16 <= g.w && (sy + 1 < g.h || x0 + 20 <= g.w)) {
+    // interior (all but the first two and the last vectors of a row): the 16 source bytes start at an
+    // arbitrary address, so read the 5 aligned words that cover them and funnel-shift to the byte
+    // phase.  The guard keeps the fifth word inside the image (the next row, or this row's own tail).
+    const uintptr_t a = reinterpret_cast<uintptr_t>(s + x0);
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    const int sh = (int)(a & 3) * 8;
+    const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3), w4 = __ldg(wp + 4);
+    wds[0] = __funnelshift_r(w0, w1, sh); wds[1] = __funnelshift_r(w1, w2, sh);
+    wds[2] = __funnelshift_r(w2, w3, sh); wds[3] = __funnelshift_r(w3, w4, sh);
+  } else {
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    uint32_t v = 0;
+    for (int q = 0; q < 4; ++q) {
+      uint32_t v = 0;
 #pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int bx = bx0 + q * 4 + b;
-      uint32_t px = 0;
-      if (bx < g.w + 2 * kEdge) px = __ldg(s + reflect101(bx - kEdge, g.w));
-      v |= px << (8 * b);
+      for (int b = 0; b < 4; ++b) {
+        const int bx = bx0 + q * 4 + b;
+        uint32_t px = 0;
+        if (bx < g.w + 2 * kEdge) px = __ldg(s + reflect101(bx - kEdge, g.w));
+        v |= px << (8 * b);
+      }
+      wds[q] = v;
     }
-    wds[q] = v;
   }
   uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)by * g.pitch + bx0;
   *reinterpret_cast<uint4*>(dst) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
@@ -98,8 +111,8 @@ constexpr int kRtTH = 32, kRtTW = 128, kRtSH = kResizeBoxH, kRtSWP = kResizeBoxW
 __global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __grid_constant__ TmaMaps maps, int level, int first_slot,
                                                       int n, int tiles_x, int tiles_y) {
   __shared__ __align__(128) uint8_t s_src[kRtSH * kRtSWP];
-  __shared__ __align__(16) uint16_t s_h[kRtSH * kRtTW];
-  __shared__ ResizeTap s_ty[kRtTH];
+  __shared__ __align__(16) uint32_t s_h[kRtSH * kRtTW];
+  __shared__ int4 s_ty[kRtTH];          // {row offset into s_h, a0 << 16, a1 << 16, -}
   __shared__ int s_lim[4];   // sx_lo, sx_hi, sy_lo, sy_hi (inclusive, source ROI coordinates)
   __shared__ __align__(8) uint64_t s_bar;
   const LevelGeom& g = L.geom[level];
@@ -122,10 +135,10 @@ __global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __gr
     tx = L.taps[g.xtab_off + bx0 + c];
     if (t < kRtTW) { atomicMin(&s_lim[0], tx.ofs); atomicMax(&s_lim[1], tx.ofs + 1); }
   }
+  ResizeTap tyr; tyr.ofs = 0; tyr.a0 = 0; tyr.a1 = 0;
   if (t < th) {
-    const ResizeTap ty = L.taps[g.ytab_off + by0 + t];
-    s_ty[t] = ty;
-    atomicMin(&s_lim[2], ty.ofs); atomicMax(&s_lim[3], ty.ofs + 1);
+    tyr = L.taps[g.ytab_off + by0 + t];
+    atomicMin(&s_lim[2], tyr.ofs); atomicMax(&s_lim[3], tyr.ofs + 1);
   }
   __syncthreads();
   const int sx_lo = s_lim[0], sy_lo = s_lim[2];
@@ -135,30 +148,37 @@ __global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __gr
     mbar_expect_tx(&s_bar, kRtSH * kRtSWP);
     tma_load_3d(s_src, &maps.m[level - 1], (kEdge + sx_lo) & ~15, kEdge + sy_lo, first_slot + img, &s_bar);
   }
+  // mulhi(b << 16, H) == (b * H) >> 16: the vertical weights are kept pre-shifted
+  if (t < th) s_ty[t] = make_int4((tyr.ofs - sy_lo) * kRtTW, tyr.a0 << 16, tyr.a1 << 16, 0);
   mbar_wait(&s_bar, 0);
   if (c < tw) {
     const int a0 = tx.a0, a1 = tx.a1;
     const uint8_t* p = s_src + (t >> 7) * kRtSWP + (tx.ofs - sx_lo + phase);
-    uint16_t* o = s_h + (t >> 7) * kRtTW + c;
-    for (int r = t >> 7; r < SH; r += 2) {
-      o[0] = (uint16_t)(((int)p[0] * a0 + (int)p[1] * a1) >> 4);
-      p += 2 * kRtSWP; o += 2 * kRtTW;
+    uint32_t* o = s_h + (t >> 7) * kRtTW + c;
+#pragma unroll
+    for (int k = 0; k < kRtSH / 2; ++k) {            // source rows (t >> 7) + 2k; SH is CTA-uniform
+      if ((k & 3) == 0 && 2 * k >= SH) break;
+      o[2 * k * kRtTW] = (uint32_t)(((int)p[2 * k * kRtSWP] * a0 + (int)p[2 * k * kRtSWP + 1] * a1) >> 4);
     }
   }
   __syncthreads();
   const int c4 = (t & 31) * 4;
   if (c4 < tw) {
-    uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)by0 * g.pitch + bx0 + c4;
-    for (int r = t >> 5; r < th; r += 8) {
-      const ResizeTap ty = s_ty[r];
-      const uint16_t* h0 = s_h + (ty.ofs - sy_lo) * kRtTW + c4;
-      const uint2 u0 = *reinterpret_cast<const uint2*>(h0), u1 = *reinterpret_cast<const uint2*>(h0 + kRtTW);
-      const unsigned b0 = (unsigned)ty.a0 << 16, b1 = (unsigned)ty.a1 << 16;   // mulhi(b << 16, H) == (b * H) >> 16
-      const unsigned r0 = (__umulhi(b0, u0.x & 0xffff) + __umulhi(b1, u1.x & 0xffff) + 2u) >> 2;
-      const unsigned r1 = (__umulhi(b0, u0.x >> 16) + __umulhi(b1, u1.x >> 16) + 2u) >> 2;
-      const unsigned r2 = (__umulhi(b0, u0.y & 0xffff) + __umulhi(b1, u1.y & 0xffff) + 2u) >> 2;
-      const unsigned r3 = (__umulhi(b0, u0.y >> 16) + __umulhi(b1, u1.y >> 16) + 2u) >> 2;
-      *reinterpret_cast<uint32_t*>(dst + (size_t)r * g.pitch) = r0 | (r1 << 8) | (r2 << 16) | (r3 << 24);
+    uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)(by0 + (t >> 5)) * g.pitch + bx0 + c4;
+    const size_t step = (size_t)8 * g.pitch;
+#pragma unroll
+    for (int k = 0; k < kRtTH / 8; ++k) {
+      const int r = (t >> 5) + 8 * k;
+      if (r < th) {
+        const int4 ty = s_ty[r];
+        const uint4 u0 = *reinterpret_cast<const uint4*>(s_h + ty.x + c4), u1 = *reinterpret_cast<const uint4*>(s_h + ty.x + kRtTW + c4);
+        const unsigned b0 = (unsigned)ty.y, b1 = (unsigned)ty.z;
+        const unsigned r0 = (__umulhi(b1, u1.x) + (__umulhi(b0, u0.x) + 2u)) >> 2;
+        const unsigned r1 = (__umulhi(b1, u1.y) + (__umulhi(b0, u0.y) + 2u)) >> 2;
+        const unsigned r2 = (__umulhi(b1, u1.z) + (__umulhi(b0, u0.z) + 2u)) >> 2;
+        const unsigned r3 = (__umulhi(b1, u1.w) + (__umulhi(b0, u0.w) + 2u)) >> 2;
+        *reinterpret_cast<uint32_t*>(dst + k * step) = (r1 * 256u + r0) + ((r3 * 256u + r2) << 16);
+      }
     }
   }
 }
