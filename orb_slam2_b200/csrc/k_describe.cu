@@ -22,14 +22,14 @@ namespace orbx {
 constexpr int kDescWarps = 4;
 constexpr int kKpPerWarp = 4;             // keypoints per warp: the next tile is in flight while this one is processed
 constexpr int kTileR = kDescTileH, kTileP = kDescTileW;   // raw tile rows / pitch (TMA box); the keypoint sits at (21, phase16+21)
-constexpr int kHtC = 40, kHtP = 46;       // horizontal pass, TRANSPOSED: [column][row] uint16, 46-entry pitch (bank-conflict free)
+constexpr int kHtC = 40, kHtP = 46;       // horizontal pass, TRANSPOSED: [column][row] uint16, 46-entry pitch (bank-conflict free reads)
+constexpr int kHtSkew = 4;                // columns 32+ sit two words further: the 10 four-column groups of a store sweep then hit 10 distinct banks
 constexpr int kBlC = 40, kBlP = 44;       // blurred patch, TRANSPOSED: [column][row] bytes, rows 0..37 (row 37 is scratch), centre (18,18)
 // per-warp shared memory: raw tile | Ht | blurred | mbarrier.  The raw tile is dead once the moments and
 // the horizontal pass have read it, so the NEXT keypoint's tile is requested right then and lands while
-// the vertical pass and the descriptor of this one run.  The CTA's tail holds the test pattern as floats.
+// the vertical pass and the descriptor of this one run.  
 constexpr int kOffHt = 2816, kOffBl = 6528, kOffBar = 8288, kWarpSmem = 8320;
-constexpr int kPatBytes = 32 * 8 * 16;    // [test-in-byte 8][lane 32] float4 {x0, y0, x1, y1}
-static_assert(kTileR * kTileP <= kOffHt && kOffHt + kHtC * kHtP * 2 <= kOffBl && kOffBl + kBlC * kBlP <= kOffBar, "smem carve-up");
+static_assert(kTileR * kTileP <= kOffHt && kOffHt + (kHtC * kHtP + kHtSkew) * 2 <= kOffBl && kOffBl + kBlC * kBlP <= kOffBar, "smem carve-up");
 static_assert(kWarpSmem % 128 == 0 && kOffBar % 8 == 0, "TMA destinations must be 128-byte aligned");
 
 // 7x7 sigma-2 taps of cv2's 8-bit path, {18,34,48,56,48,34,18}/256, packed for dp4a / dp2a
@@ -115,7 +115,7 @@ __device__ __forceinline__ KpRef locate_kp(const DeviceLayout& L, int slot, int 
   return k;
 }
 
-__global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
+__global__ void __launch_bounds__(kDescWarps * 32, 6) k_describe(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
                                                               int n_img, int ctas_per_img, const int* __restrict__ umax,
                                                               const char4* __restrict__ pattern) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -124,12 +124,6 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   uint16_t* ht = reinterpret_cast<uint16_t*>(wbase + kOffHt);
   uint8_t* bl = wbase + kOffBl;
   uint64_t* bar = reinterpret_cast<uint64_t*>(wbase + kOffBar);
-  float4* pat = reinterpret_cast<float4*>(smem + kDescWarps * kWarpSmem);
-  for (int i = threadIdx.x; i < 256; i += kDescWarps * 32) {          // i = lane * 8 + test
-    const char4 q = __ldg(pattern + i);
-    pat[(i & 7) * 32 + (i >> 3)] = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
-  }
-  __syncthreads();
 
   const int img = blockIdx.x / ctas_per_img;
   if (img >= n_img) return;
@@ -157,6 +151,14 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
     tma_load_3d(wbase, &maps.m[nxt.level], (nxt.px + kEdge - 21) & ~15, nxt.py + kEdge - 21, slot, bar);
   }
   const uint8_t* raw = wbase;
+
+  // this lane's 8 tests {x0, y0, x1, y1} as floats, resident in registers for all keypoints of the warp
+  float4 pat[8];
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    const char4 q = __ldg(pattern + lane * 8 + t);
+    pat[t] = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
+  }
 
   for (int t = 0; t < nk; ++t) {
   const KpRef cur = nxt;
@@ -203,7 +205,7 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
     // lanes 0..29: 3 rows x 10 four-column groups per sweep, 15 sweeps (43 rows); all offsets are immediates
     const int lr = lane / 10, gq = lane - lr * 10;
     const uint32_t* rp = reinterpret_cast<const uint32_t*>(raw) + lr * (kTileP / 4) + g0 + gq;
-    uint16_t* o = ht + (4 * gq) * kHtP + lr;
+    uint16_t* o = ht + (4 * gq) * kHtP + lr + (gq >= 8 ? kHtSkew : 0);
 #pragma unroll
     for (int it = 0; it < 15; ++it) {
       if (lane < 30 && 3 * it + lr < kTileR) {
@@ -233,7 +235,7 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
     const unsigned E0 = pk4(18, 34, 0, 0), E1 = pk4(48, 56, 0, 0), E2 = pk4(48, 34, 0, 0), E3 = pk4(18, 0, 0, 0);
     const unsigned F0 = pk4(0, 18, 0, 0), F1 = pk4(34, 48, 0, 0), F2 = pk4(56, 48, 0, 0), F3 = pk4(34, 18, 0, 0);
     auto vrun = [&](const int col, const int rbase, auto nsteps) {
-      const uint32_t* hc = reinterpret_cast<const uint32_t*>(ht + col * kHtP + rbase);
+      const uint32_t* hc = reinterpret_cast<const uint32_t*>(ht + col * kHtP + rbase + (col >= 32 ? kHtSkew : 0));
       uint16_t* o = reinterpret_cast<uint16_t*>(bl + col * kBlP + rbase);
       uint32_t W0 = hc[0], W1 = hc[1], W2 = hc[2];
 #pragma unroll
@@ -268,7 +270,7 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
   uint32_t byte = 0;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    const float4 q = pat[t * 32 + lane];
+    const float4 q = pat[t];
     const uint32_t r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(q.x, sb), __fmul_rn(q.y, ca)), kMagic));
     const uint32_t c0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(q.x, ca), __fmul_rn(q.y, sb)), kMagic));
     const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(q.z, sb), __fmul_rn(q.w, ca)), kMagic));
@@ -296,7 +298,7 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_describe(DeviceLayout L, co
 int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st) {
   const int per_cta = kDescWarps * kKpPerWarp;
   const int ctas_per_img = (L.kp_cap + per_cta - 1) / per_cta;
-  const size_t smem = (size_t)kDescWarps * kWarpSmem + kPatBytes;
+  const size_t smem = (size_t)kDescWarps * kWarpSmem;
   k_describe<<<n * ctas_per_img, kDescWarps * 32, smem, st>>>(L, maps, first_slot, n, ctas_per_img, d_umax, d_pattern);
   return 1;
 }
