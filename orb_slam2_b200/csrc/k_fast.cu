@@ -80,7 +80,7 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
 //                             column (WP = 64 or 96); pixel (x, y) of the window sits at [y][phase16 + x]
 //   smap  [win_rows-4][SP]    sparse S map with a 1-px zero rim: holds S only where S > minTh
 //   queue [(win_rows-6)*iw_max] uint16 (yy<<6 | xx): compass survivors, then (in place) the hot list
-//   rows  [64][2] uint32      kept-corner bit mask per tested row (strict 3x3 maxima above minTh)
+//   rows  2 x [win_rows-6][2] uint32  kept-corner bit masks per tested row: strict 3x3 maxima above minTh / above iniTh
 //   bar   one mbarrier
 // A warp walks kCellsPerWarp consecutive cells; the window of the next cell is requested as soon
 // as the scoring stage has finished with the current one, so its latency hides behind the
@@ -88,18 +88,19 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
 constexpr int kCellsPerWarp = 4;
 
 template <int WP>
-__global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
+__global__ void __launch_bounds__(kFastWarps * 32, 8) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
                                                                 int n, int win_rows, int iw_max) {
   constexpr int SP = WP - 16;                 // S-map pitch: 48 (cells up to 36 tested columns) or 80
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int win_bytes = WP * win_rows, s_bytes = SP * (win_rows - 4), q_bytes = (2 * (win_rows - 6) * iw_max + 7) & ~7;
-  const int per_warp = (win_bytes + s_bytes + q_bytes + 512 + 16 + 127) & ~127;
+  const int m_words = 4 * (win_rows - 6);      // two mask sets (kept above minTh / above iniTh), two words per tested row
+  const int per_warp = (win_bytes + s_bytes + q_bytes + 4 * m_words + 16 + 127) & ~127;
   uint8_t* win = smem + (size_t)warp * per_warp;
   uint8_t* smap = win + win_bytes;
   uint16_t* queue = reinterpret_cast<uint16_t*>(smap + s_bytes);
   uint32_t* rows = reinterpret_cast<uint32_t*>(smap + s_bytes + q_bytes);
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smap + s_bytes + q_bytes + 512);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smap + s_bytes + q_bytes + 4 * m_words);
   const int min_th = L.min_th, ini_th = L.ini_th;
 
   const long long total_cells = (long long)n * L.cells_per_slot;
@@ -107,7 +108,13 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
   if (cell0 >= total_cells) return;
   const int ncell = (int)min((long long)kCellsPerWarp, total_cells - cell0);
 
-  struct Cell { int slot, c, level, x0, y0, ww, hh; bool skip; };
+  struct Cell { int slot, c, level, col, row, x0, y0, ww, hh; bool skip; };
+  auto finish = [&](Cell& k) {                // window of cell (col, row) of its level
+    const LevelGeom& g = L.geom[k.level];
+    k.x0 = kFastBorder + k.col * g.wCell; k.y0 = kFastBorder + k.row * g.hCell;
+    k.ww = min(k.x0 + g.wCell + 6, g.maxBX) - k.x0; k.hh = min(k.y0 + g.hCell + 6, g.maxBY) - k.y0;
+    k.skip = k.y0 >= g.maxBY - 3 || k.x0 >= g.maxBX - 6 || k.ww < 7 || k.hh < 7;   // src/ORBextractor.cc:794,802
+  };
   auto locate = [&](long long gcell) {
     Cell k;
     const int img = (int)(gcell / L.cells_per_slot);
@@ -117,10 +124,23 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
     for (int l = 1; l < L.nlevels; ++l)
       if (k.c >= L.geom[l].cell_base) k.level = l;
     const LevelGeom& g = L.geom[k.level];
-    const int ci = k.c - g.cell_base, ci_row = ci / g.nCols, ci_col = ci - ci_row * g.nCols;
-    k.x0 = kFastBorder + ci_col * g.wCell; k.y0 = kFastBorder + ci_row * g.hCell;
-    k.ww = min(k.x0 + g.wCell + 6, g.maxBX) - k.x0; k.hh = min(k.y0 + g.hCell + 6, g.maxBY) - k.y0;
-    k.skip = k.y0 >= g.maxBY - 3 || k.x0 >= g.maxBX - 6 || k.ww < 7 || k.hh < 7;   // src/ORBextractor.cc:794,802
+    const int ci = k.c - g.cell_base;
+    k.row = ci / g.nCols; k.col = ci - k.row * g.nCols;
+    finish(k);
+    return k;
+  };
+  auto advance = [&](const Cell& p) {         // the cell after p in (image, level, row, column) order
+    Cell k = p;
+    ++k.c; ++k.col;
+    if (k.c == L.cells_per_slot) { k.c = 0; ++k.slot; k.level = 0; k.col = 0; k.row = 0; }
+    else if (k.col == L.geom[k.level].nCols) {
+      k.col = 0; ++k.row;
+      if (k.level + 1 < L.nlevels && k.c >= L.geom[k.level + 1].cell_base) {
+        k.row = 0;
+        do ++k.level; while (k.level + 1 < L.nlevels && k.c >= L.geom[k.level + 1].cell_base);
+      }
+    }
+    finish(k);
     return k;
   };
   auto request = [&](const Cell& k) {         // lane 0: one TMA box load for the cell's window
@@ -136,7 +156,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
 
   for (int kc = 0; kc < ncell; ++kc) {
     const Cell cur = nxt;
-    if (kc + 1 < ncell) nxt = locate(cell0 + kc + 1);
+    if (kc + 1 < ncell) nxt = advance(cur);
     const LevelGeom& g = L.geom[cur.level];
     uint2* cell_out = L.celltab + (size_t)cur.slot * L.cells_per_slot + cur.c;
     if (cur.skip) {
@@ -147,8 +167,8 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
     const int x0 = cur.x0, y0 = cur.y0, iw = cur.ww - 6, ih = cur.hh - 6, slot = cur.slot, level = cur.level;
     const int phase = (kEdge + x0) & 15;
 
-    for (int i = lane; i < ((ih + 2) * SP) >> 2; i += 32) reinterpret_cast<uint32_t*>(smap)[i] = 0u;
-    for (int i = lane; i < 128; i += 32) rows[i] = 0u;
+    for (int i = lane; i < ((ih + 2) * SP) >> 4; i += 32) reinterpret_cast<uint4*>(smap)[i] = make_uint4(0u, 0u, 0u, 0u);   // SP % 16 == 0
+    for (int i = lane; i < m_words; i += 32) rows[i] = 0u;
     mbar_wait(bar, waited & 1);
     ++waited;
 
@@ -232,6 +252,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
       const bool kept = valid && sc > max(m2, m3);
       const bool kept_ini = kept && sc > ini_th;
       if (kept) atomicOr(&rows[yy * 2 + (xx >> 5)], 1u << (xx & 31));
+      if (kept_ini) atomicOr(&rows[(m_words >> 1) + yy * 2 + (xx >> 5)], 1u << (xx & 31));
       cnt_min += __popc(__ballot_sync(0xffffffffu, kept));
       cnt_ini += __popc(__ballot_sync(0xffffffffu, kept_ini));
     }
@@ -245,20 +266,15 @@ __global__ void __launch_bounds__(kFastWarps * 32) k_fast_cells(DeviceLayout L, 
     }
     if (total > 0) {                                     // warp-uniform
       base = __shfl_sync(0xffffffffu, base, 0);
-      // emit in pixel row-major order: lane r owns tested rows r and r+32.  When iniTh found corners
-      // only those are emitted: the kept mask is filtered by S > iniTh on the fly.
+      // emit in pixel row-major order: lane r owns tested rows r and r+32; when iniTh found corners only
+      // those are emitted (second mask set)
       uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
-      const int s_need = use_ini ? ini_th : 0;
+      const uint32_t* km = rows + (use_ini ? (m_words >> 1) : 0);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         const int yy = half * 32 + lane;
-        unsigned long long m = yy < ih ? (((unsigned long long)rows[yy * 2 + 1] << 32) | rows[yy * 2]) : 0ull;
+        unsigned long long m = yy < ih ? (((unsigned long long)km[yy * 2 + 1] << 32) | km[yy * 2]) : 0ull;
         const uint8_t* srow = smap + (yy + 1) * SP + 1;
-        if (use_ini) {                                   // warp-uniform
-          unsigned long long f = 0ull, t = m;
-          while (t) { const int xx = __ffsll((long long)t) - 1; t &= t - 1; if ((int)srow[xx] > s_need) f |= 1ull << xx; }
-          m = f;
-        }
         const int mine = __popcll(m);
         int incl = mine;
 #pragma unroll
@@ -285,7 +301,7 @@ template <int WP>
 static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
   constexpr int SP = WP - 16;
   const int iw_max = win_w - 6;
-  const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + ((2 * (win_h - 6) * iw_max + 7) & ~7) + 512 + 16 + 127) & ~(size_t)127;
+  const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + ((2 * (win_h - 6) * iw_max + 7) & ~7) + 16 * (win_h - 6) + 16 + 127) & ~(size_t)127;
   const size_t smem = kFastWarps * per_warp;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const long long cells = (long long)n * L.cells_per_slot;
