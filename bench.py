@@ -263,6 +263,7 @@ def secondary_workloads(gx, torch, local):
     a, b = ev(), ev(); a.record(); [knn_step() for _ in range(3)]; b.record(); torch.cuda.synchronize()
     out["knn_ratio_2000x2000_pairs_per_s"] = 3 * P / (a.elapsed_time(b) / 1e3)
     out["knn_ratio_matches_per_pair"] = float(nmm.float().mean())
+    out["_knn_distances_per_pair"] = float((cnt[:P].double() * cnt[P:].double()).mean())
     G.close()
     return out
 
@@ -418,11 +419,17 @@ def main():
                                     "sample": f"{nfr} KITTI-shaped stereo pairs, one pair per std::thread on {threads} threads, {secs:.1f} s"}
         else:
             line["cpu_baseline"] = None
-        if world == 1 and not args.no_secondary and not args.no_cpu_baseline:
+        if world == 1 and not args.no_secondary:
             try:
                 for g in G:
                     g.close()
-                line["secondary"] = secondary_workloads(gx, torch, local)
+                sec = secondary_workloads(gx, torch, local)
+                # K7 is POPC-issue bound: 4 POPC per 256-bit distance (carry-save tree) against the measured
+                # 0.5 warp-POPC / clk / SM (tools/pipe_probe.cu, profiles/r1d_pipe_rates.jsonl)
+                mhz = (line.get("clocks") or {}).get("sm_mhz") or 1920.0
+                popc_peak = 148 * 16 * mhz * 1e6
+                sec["knn_popc_issue_frac"] = sec["knn_ratio_2000x2000_pairs_per_s"] * sec.pop("_knn_distances_per_pair") * 4 / popc_peak
+                line["secondary"] = sec
             except Exception as exc:                       # side measurements must never cost the headline
                 line["secondary"] = {"error": repr(exc)}
         print(json.dumps(line), flush=True)

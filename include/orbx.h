@@ -148,7 +148,8 @@ orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* des
  * vocabulary bucket holding all features of each side in index order: brute-force best/second
  * best 256-bit Hamming, threshold (strict_lt: best < th as in the KF/KF form :598, else best <= th
  * as in the KF/Frame form :228), ratio test, greedy exclusion of matched B features, rotation
- * histogram.  Batched over n_pairs like orbx_search_init_batch; ang = keypoint angles. */
+ * histogram.  Batched over n_pairs like orbx_search_init_batch; ang = keypoint angles.  th is 0..255
+ * (the reference passes TH_LOW = 50); cap <= 6000. */
 orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const int* nA,
                                  const uint8_t* descB, const float* angB, const int* nB, int n_pairs,
                                  int cap, int th, float nnratio, int check_orientation, int strict_lt,

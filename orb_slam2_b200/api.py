@@ -375,12 +375,13 @@ class ORBmatcher:
                                                         nm.ctypes.data, 0, None))
         return int(nm[0]), assigned[:n].copy(), fo[:n].copy()
 
-    def SearchByBoW(self, descA, angA, descB, angB, strict=True):
-        """SearchByBoW(KF,KF) with one bucket holding all features (brute-force kNN + ratio)."""
-        r = self.SearchByBoWBatch([(descA, angA)], [(descB, angB)], strict)
+    def SearchByBoW(self, descA, angA, descB, angB, strict=True, th=None):
+        """SearchByBoW(KF,KF) with one bucket holding all features (brute-force kNN + ratio).
+        th defaults to TH_LOW (src/ORBmatcher.cc:37,596)."""
+        r = self.SearchByBoWBatch([(descA, angA)], [(descB, angB)], strict, th)
         return r[0][0], r[1][0]
 
-    def SearchByBoWBatch(self, As, Bs, strict=True):
+    def SearchByBoWBatch(self, As, Bs, strict=True, th=None):
         npairs = len(As)
         cap = max(max(len(a[0]) for a in As), max(len(b[0]) for b in Bs), 1)
         dA = np.zeros((npairs, cap, 32), np.uint8); dB = np.zeros((npairs, cap, 32), np.uint8)
@@ -391,6 +392,6 @@ class ORBmatcher:
             dA[p, :nA[p]] = da; aA[p, :nA[p]] = aa; dB[p, :nB[p]] = db; aB[p, :nB[p]] = ab
         m12 = np.zeros((npairs, cap), np.int32); nm = np.zeros(npairs, np.int32)
         _check(lib().orbx_knn_ratio_batch(dA.ctypes.data, aA.ctypes.data, nA.ctypes.data, dB.ctypes.data, aB.ctypes.data,
-                                          nB.ctypes.data, npairs, cap, self.TH_LOW, self.mfNNratio,
+                                          nB.ctypes.data, npairs, cap, self.TH_LOW if th is None else int(th), self.mfNNratio,
                                           int(self.mbCheckOrientation), int(strict), m12.ctypes.data, nm.ctypes.data, 0, None))
         return [int(v) for v in nm], [m12[p, :nA[p]].copy() for p in range(npairs)]

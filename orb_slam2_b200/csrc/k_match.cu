@@ -15,6 +15,7 @@
 // floor/ceil always covers the round()-assigned cell of such a keypoint).  The grid only fixes
 // the enumeration order (cell x, cell y, index), which matters for ties on the best distance;
 // it is carried as a 64-bit key  distance<<32 | cell<<16 | index  reduced with min.
+#include <algorithm>
 #include <climits>
 
 #include "orbx_internal.h"
@@ -150,79 +151,197 @@ __global__ void __launch_bounds__(32) k_search_init(InitMatchArgs a) {
 // ------------------------------------------------------------------------------------------
 // K7: one CTA per pair; B descriptors transposed in shared memory ([word][j], conflict-free).
 constexpr int kKnnThreads = 256;
+constexpr int kTopK = 8;
 
-__global__ void __launch_bounds__(kKnnThreads) k_knn_ratio(KnnArgs a, int capPad) {
+// K7 runs in two launches.
+//   k_knn_topk    every A descriptor scans ALL B descriptors of its pair (no dependency yet) and keeps its
+//                 kTopK nearest as sorted keys  distance<<16 | j.  One thread = one query, B rows are
+//                 broadcast from shared memory.  The 256-bit popcount goes through a carry-save adder
+//                 tree (8 LOP3) so that only 4 POPC are issued per distance: POPC is the slowest pipe on
+//                 this path (0.5 warp instructions / clk / SM, profiles/r1d_pipe_rates.jsonl).
+//                 Keys at or above `sentinel` are never kept: a second-best that far away passes the ratio
+//                 test against any best <= th, a best that far away fails the threshold (launch_knn_ratio).
+//   k_knn_resolve one warp per pair walks the queries in index order (hazard H6: vbMatched2): best and
+//                 second-best are the first two list entries whose B feature is still free.  The list is
+//                 exact unless fewer than two of its entries are free while it is full; then the warp
+//                 rescans all B descriptors for that query.
+__device__ __forceinline__ uint32_t lop3_xor3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r;
+}
+__device__ __forceinline__ uint32_t lop3_maj(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r;
+}
+// popcount of the 256-bit xor of q and (b0, b1)
+__device__ __forceinline__ int ham256_csa(const uint32_t (&q)[8], const uint4 b0, const uint4 b1) {
+  const uint32_t x0 = q[0] ^ b0.x, x1 = q[1] ^ b0.y, x2 = q[2] ^ b0.z, x3 = q[3] ^ b0.w;
+  const uint32_t x4 = q[4] ^ b1.x, x5 = q[5] ^ b1.y, x6 = q[6] ^ b1.z, x7 = q[7] ^ b1.w;
+  const uint32_t s0 = lop3_xor3(x0, x1, x2), c0 = lop3_maj(x0, x1, x2);
+  const uint32_t s1 = lop3_xor3(x3, x4, x5), c1 = lop3_maj(x3, x4, x5);
+  const uint32_t s2 = lop3_xor3(s0, s1, x6), c2 = lop3_maj(s0, s1, x6);
+  const uint32_t t0 = lop3_xor3(c0, c1, c2), f0 = lop3_maj(c0, c1, c2);
+  return (__popc(s2) + __popc(x7)) + 2 * __popc(t0) + 4 * __popc(f0);
+}
+
+__global__ void __launch_bounds__(kKnnThreads) k_knn_topk(KnnArgs a, int qblocks, uint32_t sentinel) {
   extern __shared__ __align__(16) uint8_t smem[];
-  uint32_t* Bt = reinterpret_cast<uint32_t*>(smem);            // [8][capPad]
-  uint8_t* used = reinterpret_cast<uint8_t*>(Bt + 8 * capPad);  // [capPad]
-  __shared__ unsigned s_key[kKnnThreads / 32];
-  __shared__ int s_sec[kKnnThreads / 32];
+  uint4* Bs = reinterpret_cast<uint4*>(smem);                  // [nB][2]
+  const int p = blockIdx.x / qblocks, qb = blockIdx.x - p * qblocks, tid = threadIdx.x;
+  const int nA = a.nA[p], nB = a.nB[p];
+  if (qb * kKnnThreads >= nA) return;
+  const uint4* dB = reinterpret_cast<const uint4*>(a.dB + (size_t)p * a.cap * 32);
+  for (int idx = tid; idx < nB * 2; idx += kKnnThreads) Bs[idx] = __ldg(dB + idx);
+  __syncthreads();
+  const int i = qb * kKnnThreads + tid;
+  if (i >= nA) return;
+  uint32_t q[8];
+  {
+    const uint4* dA = reinterpret_cast<const uint4*>(a.dA + ((size_t)p * a.cap + i) * 32);
+    const uint4 q0 = __ldg(dA), q1 = __ldg(dA + 1);
+    q[0] = q0.x; q[1] = q0.y; q[2] = q0.z; q[3] = q0.w; q[4] = q1.x; q[5] = q1.y; q[6] = q1.z; q[7] = q1.w;
+  }
+  uint32_t top[kTopK];
+#pragma unroll
+  for (int k = 0; k < kTopK; ++k) top[k] = sentinel;
+#pragma unroll 2
+  for (int j = 0; j < nB; ++j) {
+    const uint32_t key = ((uint32_t)ham256_csa(q, Bs[2 * j], Bs[2 * j + 1]) << 16) + (uint32_t)j;
+    if (key < top[kTopK - 1]) {                                // rare: only neighbours closer than the sentinel
+      top[kTopK - 1] = key;
+#pragma unroll
+      for (int k = kTopK - 1; k > 0; --k) {
+        const uint32_t lo = min(top[k - 1], top[k]), hi = max(top[k - 1], top[k]);
+        top[k - 1] = lo; top[k] = hi;
+      }
+    }
+  }
+  uint4* out = reinterpret_cast<uint4*>(a.topk + ((size_t)p * a.cap + i) * kTopK);
+  out[0] = make_uint4(top[0], top[1], top[2], top[3]);
+  out[1] = make_uint4(top[4], top[5], top[6], top[7]);
+}
+
+__global__ void __launch_bounds__(32) k_knn_resolve(KnnArgs a, uint32_t sentinel) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int uwords = (a.cap + 31) / 32;
+  uint32_t* used = reinterpret_cast<uint32_t*>(smem);          // bit j: B feature j already matched (vbMatched2)
+  int* claim = reinterpret_cast<int*>(used + uwords);          // [cap] lowest lane of the current group that wants B feature j
   __shared__ int s_hist[kHisto];
-  __shared__ int s_nm;
-  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int p = blockIdx.x, lane = threadIdx.x;
   const int nA = a.nA[p], nB = a.nB[p];
   const uint32_t* dA = reinterpret_cast<const uint32_t*>(a.dA + (size_t)p * a.cap * 32);
   const uint32_t* dB = reinterpret_cast<const uint32_t*>(a.dB + (size_t)p * a.cap * 32);
   const float* angA = a.angA + (size_t)p * a.cap;
   const float* angB = a.angB + (size_t)p * a.cap;
+  const uint4* tk = reinterpret_cast<const uint4*>(a.topk + (size_t)p * a.cap * kTopK);
   int* m12 = a.m12 + (size_t)p * a.cap;
-  int* binof = a.scratch + (size_t)p * a.cap;
-
-  for (int idx = tid; idx < nB * 8; idx += kKnnThreads) { const int j = idx >> 3, w = idx & 7; Bt[w * capPad + j] = __ldg(dB + idx); }
-  for (int j = tid; j < capPad; j += kKnnThreads) used[j] = 0;
-  if (tid < kHisto) s_hist[tid] = 0;
-  if (tid == 0) s_nm = 0;
-  __syncthreads();
-
-  for (int i = 0; i < nA; ++i) {
-    uint32_t q[8];
+  for (int w = lane; w < uwords; w += 32) used[w] = 0u;
+  for (int j = lane; j < a.cap; j += 32) claim[j] = 32;
+  if (lane < kHisto) s_hist[lane] = 0;
+  __syncwarp();
+  const int far = min((int)(sentinel >> 16), 256);             // stands for "at least the sentinel distance, or none"
+  int nm = 0;
+  // Queries are taken 32 at a time, one per lane, and decided together; a lane's decision stands if no
+  // earlier lane of the group took a B feature that is on its list.  The group commits up to the first lane
+  // for which that fails (or whose list is exhausted), repairs that lane, and goes on from there, so the
+  // outcome is the one of the index-ordered loop of the reference.
+  uint4 n0 = make_uint4(sentinel, sentinel, sentinel, sentinel), n1 = n0;
+  if (lane < nA) { n0 = __ldg(tk + 2 * lane); n1 = __ldg(tk + 2 * lane + 1); }
+  for (int i0 = 0; i0 < nA; i0 += 32) {
+    const int i = i0 + lane;
+    const bool active = i < nA;
+    const uint32_t key[kTopK] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+    if (i + 32 < nA) { n0 = __ldg(tk + 2 * (i + 32)); n1 = __ldg(tk + 2 * (i + 32) + 1); }
+    const bool full = key[kTopK - 1] < sentinel;               // sorted: the last entry is valid iff all are
+    int start = 0;
+    while (true) {
+      const bool eval = active && lane >= start;
+      int cnt = 0, best = 256, bi = 0, sec = 256;
+      uint32_t freem = 0u;
+      if (eval) {
 #pragma unroll
-    for (int w = 0; w < 8; ++w) q[w] = __ldg(dA + (size_t)i * 8 + w);
-    unsigned b1 = 256u << 16;   // bestDist1 = 256, no index
-    int b2 = 256;
-    for (int j = tid; j < nB; j += kKnnThreads) {
-      if (used[j]) continue;
-      int d = 0;
-#pragma unroll
-      for (int w = 0; w < 8; w += 2)
-        d += __popcll(((unsigned long long)(q[w + 1] ^ Bt[(w + 1) * capPad + j]) << 32) | (q[w] ^ Bt[w * capPad + j]));
-      const unsigned key = ((unsigned)d << 16) | (unsigned)j;
-      if (d < (int)(b1 >> 16)) { b2 = (int)(b1 >> 16); b1 = key; }      // strict '<' keeps the first j, :586
-      else if (d < b2) b2 = d;
-    }
-    const unsigned wmin = __reduce_min_sync(0xffffffffu, b1);
-    const int wsec = (int)__reduce_min_sync(0xffffffffu, (unsigned)(b1 == wmin ? b2 : (int)(b1 >> 16)));
-    if (lane == 0) { s_key[warp] = wmin; s_sec[warp] = wsec; }
-    __syncthreads();
-    if (tid == 0) {
-      unsigned g = s_key[0];
-      int own = 0;
-      for (int w = 1; w < kKnnThreads / 32; ++w) if (s_key[w] < g) { g = s_key[w]; own = w; }
-      int sec = s_sec[own];
-      for (int w = 0; w < kKnnThreads / 32; ++w) if (w != own) sec = min(sec, (int)(s_key[w] >> 16));
-      const int best = (int)(g >> 16), bi = g & 0xFFFF;
-      int m = -1, bin = -1;
-      const bool pass = a.strict ? best < a.th : best <= a.th;
-      if (pass && (float)best < __fmul_rn(a.ratio, (float)sec)) {
-        m = bi; used[bi] = 1; s_nm += 1;
-        if (a.checkOri) { bin = rot_bin(angA[i], angB[bi]); s_hist[bin] += 1; }
+        for (int k = 0; k < kTopK; ++k) {
+          const uint32_t j = key[k] & 0xffffu;
+          if (key[k] < sentinel && ((used[j >> 5] >> (j & 31)) & 1u) == 0u) {
+            freem |= 1u << k;
+            if (cnt == 0) { best = (int)(key[k] >> 16); bi = (int)j; }
+            else if (cnt == 1) sec = (int)(key[k] >> 16);
+            ++cnt;
+          }
+        }
       }
-      m12[i] = m; binof[i] = bin;
+      const bool rescan = eval && cnt < 2 && full;              // the list cannot tell best and second best any more
+      if (cnt == 1 && !full) sec = far;                         // every B below the sentinel distance was on the list
+      const bool pass = eval && !rescan && cnt > 0 && (a.strict ? best < a.th : best <= a.th) &&
+                        (float)best < __fmul_rn(a.ratio, (float)sec);
+      if (pass) atomicMin(&claim[bi], lane);
+      __syncwarp();
+      bool conflict = false;
+      if (eval) {
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k)
+          if (((freem >> k) & 1u) && claim[key[k] & 0xffffu] < lane) conflict = true;
+      }
+      const uint32_t stop = __ballot_sync(0xffffffffu, conflict || rescan);
+      const int first = stop ? __ffs((int)stop) - 1 : 32;
+      __syncwarp();
+      if (pass) claim[bi] = 32;
+      if (eval && lane < first) {
+        m12[i] = pass ? bi : -1;
+        if (pass) { atomicOr(&used[bi >> 5], 1u << (bi & 31)); ++nm; }
+      }
+      __syncwarp();
+      if (first == 32) break;
+      start = first;
+      if (__shfl_sync(0xffffffffu, (int)rescan, first)) {       // exact rescan of query i0 + first (src/ORBmatcher.cc:574-594)
+        const int iq = i0 + first;
+        uint32_t qd[8];
+#pragma unroll
+        for (int w = 0; w < 8; ++w) qd[w] = __ldg(dA + (size_t)iq * 8 + w);
+        unsigned b1 = 256u << 16;
+        int b2 = 256;
+        for (int jj = lane; jj < nB; jj += 32) {
+          if ((used[jj >> 5] >> (jj & 31)) & 1u) continue;
+          uint32_t bd[8];
+#pragma unroll
+          for (int w = 0; w < 8; ++w) bd[w] = __ldg(dB + (size_t)jj * 8 + w);
+          const int d = ham8(qd, bd);
+          const unsigned kk = ((unsigned)d << 16) | (unsigned)jj;
+          if (d < (int)(b1 >> 16)) { b2 = (int)(b1 >> 16); b1 = kk; }
+          else if (d < b2) b2 = d;
+        }
+        const unsigned wmin = __reduce_min_sync(0xffffffffu, b1);
+        const int rsec = (int)__reduce_min_sync(0xffffffffu, (unsigned)(b1 == wmin ? b2 : (int)(b1 >> 16)));
+        const int rbest = (int)(wmin >> 16), rbi = (int)(wmin & 0xffffu);
+        const bool rpass = (a.strict ? rbest < a.th : rbest <= a.th) && (float)rbest < __fmul_rn(a.ratio, (float)rsec);
+        if (lane == first) {
+          m12[iq] = rpass ? rbi : -1;
+          if (rpass) { used[rbi >> 5] |= 1u << (rbi & 31); ++nm; }
+        }
+        __syncwarp();
+        start = first + 1;
+      }
     }
-    __syncthreads();
   }
-  if (a.checkOri) {
+  nm = __reduce_add_sync(0xffffffffu, nm);
+  __syncwarp();
+  if (a.checkOri) {                                            // rotation consistency, src/ORBmatcher.cc:607-652
+    for (int i = lane; i < nA; i += 32) {
+      const int m = m12[i];
+      if (m >= 0) atomicAdd(&s_hist[rot_bin(angA[i], angB[m])], 1);
+    }
+    __syncwarp();
     int k_a, k_b, k_c;
     three_maxima(s_hist, k_a, k_b, k_c);
     int drop = 0;
-    for (int i = tid; i < nA; i += kKnnThreads) {
-      const int b = binof[i];
-      if (b >= 0 && b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
+    for (int i = lane; i < nA; i += 32) {
+      const int m = m12[i];
+      if (m >= 0) {
+        const int b = rot_bin(angA[i], angB[m]);
+        if (b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
+      }
     }
-    if (drop) atomicSub(&s_nm, drop);
-    __syncthreads();
+    nm -= __reduce_add_sync(0xffffffffu, drop);
   }
-  if (tid == 0) a.nm[p] = s_nm;
+  if (lane == 0) a.nm[p] = nm;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -480,11 +599,19 @@ int launch_search_init(const InitMatchArgs& a, cudaStream_t st) {
 }
 
 int launch_knn_ratio(const KnnArgs& a, cudaStream_t st) {
-  const int capPad = (a.cap + 31) & ~31;
-  const size_t smem = (size_t)capPad * 33;
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_knn_ratio, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_knn_ratio<<<a.n_pairs, kKnnThreads, smem, st>>>(a, capPad);
-  return 1;
+  // Smallest second-best distance that passes the ratio test against ANY acceptable best (<= th); it is also
+  // kept above th, so a best at that distance can never be accepted.  Neighbours that far need no tracking.
+  int dstar = 257;
+  for (int s2 = 0; s2 <= 256; ++s2)
+    if ((float)a.th < a.ratio * (float)s2) { dstar = s2; break; }
+  dstar = std::min(std::max(dstar, a.th + 1), 257);
+  const uint32_t sentinel = (uint32_t)dstar << 16;
+  const int qblocks = (a.cap + kKnnThreads - 1) / kKnnThreads;
+  const size_t smem = (size_t)a.cap * 32;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_knn_topk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_knn_topk<<<a.n_pairs * qblocks, kKnnThreads, smem, st>>>(a, qblocks, sentinel);
+  k_knn_resolve<<<a.n_pairs, 32, (size_t)((a.cap + 31) / 32) * 4 + (size_t)a.cap * 4, st>>>(a, sentinel);
+  return 2;
 }
 
 // ------------------------------------------------------------------------------------------

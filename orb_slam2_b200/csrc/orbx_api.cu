@@ -641,6 +641,9 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
                                  int* matches12, int* n_matches, int on_device, void* stream) {
   if (!descA || !angA || !nA || !descB || !angB || !nB || !matches12 || !n_matches) return fail(ORBX_ERR_BAD_ARG, "null argument");
   if (n_pairs < 1 || cap < 1 || cap > 6000) return fail(ORBX_ERR_BAD_ARG, "cap must be 1..6000 (B descriptors are held in shared memory)");
+  // a 256-bit distance is at most 256 and "no candidate" is 256 too: th >= 256 would accept a match with no feature
+  // (the reference's bestIdx2 = -1 write, src/ORBmatcher.cc:596-600, unreachable there because TH_LOW is 50)
+  if (th < 0 || th > 255) return fail(ORBX_ERR_BAD_ARG, "th must be 0..255");
   cudaStream_t st = (cudaStream_t)stream;
   Staged sg(st);
   const size_t np = (size_t)n_pairs, pc = np * cap;
@@ -649,7 +652,7 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
   CU(sg.in(descB, pc * 32, on_device, &a.dB)); CU(sg.in(angB, pc, on_device, &a.angB)); CU(sg.in(nB, np, on_device, &a.nB));
   if (on_device) { a.m12 = matches12; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
-  CU(sg.alloc((void**)&a.scratch, pc * sizeof(int)));
+  CU(sg.alloc((void**)&a.topk, pc * 8 * sizeof(uint32_t)));
   a.n_pairs = n_pairs; a.cap = cap; a.th = th; a.ratio = nnratio; a.checkOri = check_orientation; a.strict = strict_lt;
   g_launches += launch_knn_ratio(a, st);
   CU(cudaGetLastError());

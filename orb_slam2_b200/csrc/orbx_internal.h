@@ -108,7 +108,7 @@ struct KnnArgs {
   const uint8_t* dB; const float* angB; const int* nB;
   int n_pairs, cap, th; float ratio; int checkOri, strict;
   int* m12; int* nm;
-  int* scratch;  // per pair: cap ints (rotation bin per A feature)
+  uint32_t* topk;  // per pair: cap x 8 sorted keys distance<<16 | j (nearest B features of every A feature)
 };
 int launch_knn_ratio(const KnnArgs& a, cudaStream_t st);
 

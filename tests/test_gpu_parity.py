@@ -280,6 +280,46 @@ def test_knn_ratio_bruteforce(gx, oracle):
     assert n1 == 0 and g.tolist() == [-1]
 
 
+@pytest.mark.parametrize("th,ratio,strict", [(50, 0.75, True), (50, 0.95, False), (100, 0.9, False), (255, 0.999, False), (30, 0.2, True), (255, 1.5, False)])
+def test_knn_ratio_crowded_neighbourhoods(gx, oracle, th, ratio, strict):
+    """K7's ordered resolve under pressure: groups of identical queries facing ladders of near-copies in B
+    (each accepted match consumes the nearest free copy, so a query's eight nearest B features are all
+    taken and the warp has to rescan), exact duplicates (second == best, ratio test fails), and
+    thresholds / ratios that move or disable the far-neighbour cut-off."""
+    rng = np.random.default_rng(1234 + th)
+    def flip(d, bits):
+        o = d.copy()
+        for b in bits: o[b >> 3] ^= np.uint8(1 << (b & 7))
+        return o
+    A, B = [], []
+    for g in range(6):
+        x = rng.integers(0, 256, 32, dtype=np.uint8)
+        nq = 14 + g
+        for _ in range(nq): A.append(x.copy())
+        perm = rng.permutation(256)
+        for k in range(nq + 4): B.append(flip(x, perm[:k * (1 + (g & 1))]))   # k (or 2k) bits away from x
+    for _ in range(40):                                                       # unrelated descriptors and exact duplicates
+        y = rng.integers(0, 256, 32, dtype=np.uint8)
+        A.append(y.copy()); B.append(y.copy()); B.append(y.copy())
+    for _ in range(300):
+        A.append(rng.integers(0, 256, 32, dtype=np.uint8)); B.append(rng.integers(0, 256, 32, dtype=np.uint8))
+    A = np.stack(A); B = np.stack(B)
+    ia, ib = rng.permutation(len(A)), rng.permutation(len(B))
+    A, B = np.ascontiguousarray(A[ia]), np.ascontiguousarray(B[ib])
+    angA = rng.uniform(0, 360, len(A)).astype(np.float32); angB = rng.uniform(0, 360, len(B)).astype(np.float32)
+    for ori in (True, False):
+        r = oracle.knn_ratio(A, angA, B, angB, th, ratio, ori, strict)
+        n1, g = gx.ORBmatcher(ratio, ori).SearchByBoW(A, angA, B, angB, th=th, strict=strict)
+        assert n1 == r[1] and np.array_equal(g, r[0]), (ori, n1, r[1])
+    if ratio >= 0.9:
+        assert r[1] > 30                                                       # ladders deeper than the eight-entry lists
+    # fewer B features than the list length, and a single B feature
+    for nb in (1, 3, 7, 8, 9):
+        r = oracle.knn_ratio(A[:50], angA[:50], B[:nb], angB[:nb], th, ratio, False, strict)
+        n1, g = gx.ORBmatcher(ratio, False).SearchByBoW(A[:50], angA[:50], B[:nb], angB[:nb], th=th, strict=strict)
+        assert n1 == r[1] and np.array_equal(g, r[0]), nb
+
+
 @pytest.mark.parametrize("th", [1.0, 3.0])
 def test_search_by_projection_local_map(gx, oracle, th):
     """SearchByProjection(Frame, MapPoints): map points come from a second, shifted view of the scene
