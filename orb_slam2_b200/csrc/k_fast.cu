@@ -66,8 +66,16 @@ __device__ __forceinline__ uint32_t pack_base(const int v) {     // lo = v + 256
 __device__ __forceinline__ uint32_t compass_packed(const uint8_t* c, const int wp, uint32_t (&P)[16]) {
   const uint32_t base = pack_base(c[0]);
   ORBX_RING(0, c + 3 * wp, 0); ORBX_RING(4, c, 3); ORBX_RING(8, c - 3 * wp, 0); ORBX_RING(12, c, -3);
-  const uint32_t a = vmin3(P[0], P[4], P[4]), b = vmin3(P[4], P[8], P[8]), d = vmin3(P[8], P[12], P[12]), e = vmin3(P[12], P[0], P[0]);
-  return vmax3(vmax3(a, b, d), e, e);
+  // the four neighbouring pairs are all (one of N/S) x (one of E/W):  max over them of min(a, b) = min(max(N,S), max(E,W))
+  return vmin3(vmax3(P[0], P[8], P[8]), vmax3(P[4], P[12], P[12]), 0x7fff7fffu);
+}
+// Stage-1 form of the same bound with the threshold folded in: `bias` = 0x8000 - 257 - minTh added to both
+// halves of the base commutes with min / max (unsigned halves, no carry: every half stays within
+// 0x8000 +- 512), and bit 15 of a half is then set iff that polarity's bound exceeds minTh.
+__device__ __forceinline__ uint32_t compass_pass_bits(const uint8_t* c, const int wp, const uint32_t base_bias) {
+  const uint32_t base = (uint32_t)c[0] * 0xFFFF0001u + base_bias;
+  const uint32_t n = c[3 * wp] * 0xFFFFu + base, e = c[3] * 0xFFFFu + base, s = c[-3 * wp] * 0xFFFFu + base, w = c[-3] * 0xFFFFu + base;
+  return __vimin3_u16x2(__vimax3_u16x2(n, s, s), __vimax3_u16x2(e, w, w), 0xffffffffu) & 0x80008000u;
 }
 __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
   uint32_t P[16];
@@ -176,10 +184,9 @@ __global__ void __launch_bounds__(kFastWarps * 32, 8) k_fast_cells(DeviceLayout 
     // a pixel whose bound is <= minTh cannot be a corner at either threshold.  The ballot of row yy is
     // parked in lane yy; after the sweep every lane appends its row's survivors to one warp-wide queue
     // (prefix sum of the per-row counts), row-major, so that stage 2 is load balanced and reads
-    // neighbouring columns.  The threshold test is done on the packed pair: adding
-    // 0x8000 - (minTh + 257) to each half sets its bit 15 iff bound > minTh.
+    // neighbouring columns.  The threshold rides in the packed base (compass_pass_bits).
     int ncand = 0;
-    const uint32_t kpass = (uint32_t)(0x8000 - 257 - min_th) * 0x00010001u;
+    const uint32_t kpass = 0x01000100u + (uint32_t)(0x8000 - 257 - min_th) * 0x00010001u;
 #pragma unroll
     for (int ch = 0; ch < 2; ++ch) {
       if (ch * 32 < iw) {                     // warp-uniform
@@ -189,14 +196,12 @@ __global__ void __launch_bounds__(kFastWarps * 32, 8) k_fast_cells(DeviceLayout 
         uint32_t rm0 = 0u, rm1 = 0u;
         const int h0 = min(ih, 32);
         for (int yy = 0; yy < h0; ++yy) {
-          uint32_t P[16];
-          const uint32_t bal = __ballot_sync(0xffffffffu, ((compass_packed(cptr, WP, P) + kpass) & 0x80008000u) != 0u);
+          const uint32_t bal = __ballot_sync(0xffffffffu, compass_pass_bits(cptr, WP, kpass) != 0u);
           if (lane == yy) rm0 = bal;
           cptr += WP;
         }
         for (int yy = 32; yy < ih; ++yy) {
-          uint32_t P[16];
-          const uint32_t bal = __ballot_sync(0xffffffffu, ((compass_packed(cptr, WP, P) + kpass) & 0x80008000u) != 0u);
+          const uint32_t bal = __ballot_sync(0xffffffffu, compass_pass_bits(cptr, WP, kpass) != 0u);
           if (lane == yy - 32) rm1 = bal;
           cptr += WP;
         }
