@@ -277,6 +277,7 @@ __global__ void __launch_bounds__(kFastWarps * 32, 8) k_fast_cells(DeviceLayout 
       const uint32_t* km = rows + (use_ini ? (m_words >> 1) : 0);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
+        if (half * 32 >= ih) break;                        // warp-uniform: most cells have at most 32 tested rows
         const int yy = half * 32 + lane;
         unsigned long long m = yy < ih ? (((unsigned long long)km[yy * 2 + 1] << 32) | km[yy * 2]) : 0ull;
         const uint8_t* srow = smap + (yy + 1) * SP + 1;
