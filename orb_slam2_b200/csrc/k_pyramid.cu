@@ -17,23 +17,26 @@
 
 namespace orbx {
 
+// Level 0: one thread = 16 consecutive bytes of one bordered row.  blockIdx.z = image; blockIdx.y = 0 walks
+// the interior vectors of all rows (16 source bytes at an arbitrary address: 5 aligned words + funnel shift),
+// blockIdx.y = 1 the few vectors per row that touch the reflected border or the pad, byte by byte - kept in
+// separate warps so that the common case never executes the slow branch.
 __global__ void __launch_bounds__(256) k_border_level0(DeviceLayout L, const uint8_t* __restrict__ src, int src_pitch,
-                                                        size_t src_img_stride, int first_slot, int n) {
+                                                        size_t src_img_stride, int first_slot, int v_lo, int n_int) {
   const LevelGeom g = L.geom[0];
-  const int vec_per_row = g.pitch >> 4;
-  const long long per_img = (long long)vec_per_row * g.rows;
-  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid >= per_img * n) return;
-  const int img = (int)(tid / per_img);
-  const int rem = (int)(tid - (long long)img * per_img);
-  const int by = rem / vec_per_row, bx0 = (rem - by * vec_per_row) << 4;
+  const int vec_per_row = g.pitch >> 4, n_edge = vec_per_row - n_int;
+  const int img = blockIdx.z, edge = blockIdx.y;
+  const int per_row = edge ? n_edge : n_int;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= per_row * g.rows) return;
+  const int by = idx / per_row, k = idx - by * per_row;
+  const int v = edge ? (k < v_lo ? k : k + n_int) : v_lo + k;
+  const int bx0 = v << 4;
   const int sy = reflect101(by - kEdge, g.h), x0 = bx0 - kEdge;
   const uint8_t* s = src + (size_t)img * src_img_stride + (size_t)sy * src_pitch;
   uint32_t wds[4];
-  if (x0 >= 0 && x0 + 16 <= g.w && (sy + 1 < g.h || x0 + 20 <= g.w)) {
-    // interior (all but the first two and the last vectors of a row): the 16 source bytes start at an
-    // arbitrary address, so read the 5 aligned words that cover them and funnel-shift to the byte
-    // phase.  The guard keeps the fifth word inside the image (the next row, or this row's own tail).
+  if (!edge && (sy + 1 < g.h || x0 + 20 <= g.w)) {
+    // the guard keeps the fifth word inside the image (the next row, or this row's own tail)
     const uintptr_t a = reinterpret_cast<uintptr_t>(s + x0);
     const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
     const int sh = (int)(a & 3) * 8;
@@ -43,15 +46,15 @@ __global__ void __launch_bounds__(256) k_border_level0(DeviceLayout L, const uin
   } else {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      uint32_t v = 0;
+      uint32_t wv = 0;
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
         const int bx = bx0 + q * 4 + b;
         uint32_t px = 0;
         if (bx < g.w + 2 * kEdge) px = __ldg(s + reflect101(bx - kEdge, g.w));
-        v |= px << (8 * b);
+        wv |= px << (8 * b);
       }
-      wds[q] = v;
+      wds[q] = wv;
     }
   }
   uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)by * g.pitch + bx0;
@@ -108,8 +111,7 @@ __global__ void __launch_bounds__(256) k_resize_level(DeviceLayout L, int level,
 //      riding in the accumulator; one aligned 32-bit store per thread, a warp writes 128 B
 constexpr int kRtTH = 32, kRtTW = 128, kRtSH = kResizeBoxH, kRtSWP = kResizeBoxW;
 
-__global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __grid_constant__ TmaMaps maps, int level, int first_slot,
-                                                      int n, int tiles_x, int tiles_y) {
+__global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __grid_constant__ TmaMaps maps, int level, int first_slot) {
   __shared__ __align__(128) uint8_t s_src[kRtSH * kRtSWP];
   __shared__ __align__(16) uint32_t s_h[kRtSH * kRtTW];
   __shared__ int4 s_ty[kRtTH];          // {row offset into s_h, a0 << 16, a1 << 16, -}
@@ -117,10 +119,7 @@ __global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __gr
   __shared__ __align__(8) uint64_t s_bar;
   const LevelGeom& g = L.geom[level];
   const int t = threadIdx.x;
-  const int per_img = tiles_x * tiles_y;
-  const int img = blockIdx.x / per_img, tile = blockIdx.x - img * per_img;
-  if (img >= n) return;
-  const int tyi = tile / tiles_x, txi = tile - tyi * tiles_x;
+  const int txi = blockIdx.x, tyi = blockIdx.y, img = blockIdx.z;   // grid = (tiles_x, tiles_y, images)
   const int bx0 = txi * kRtTW, by0 = tyi * kRtTH;
   const int tw = min(kRtTW, g.pitch - bx0), th = min(kRtTH, g.rows - by0);
   if (t == 0) {
@@ -165,7 +164,7 @@ __global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __gr
   const int c4 = (t & 31) * 4;
   if (c4 < tw) {
     uint8_t* dst = L.pyr + g.plane_off + (size_t)(first_slot + img) * g.plane_stride + (size_t)(by0 + (t >> 5)) * g.pitch + bx0 + c4;
-    const size_t step = (size_t)8 * g.pitch;
+    const int step = 8 * g.pitch;                      // a level plane is far below 2 GB: 32-bit row offsets
 #pragma unroll
     for (int k = 0; k < kRtTH / 8; ++k) {
       const int r = (t >> 5) + 8 * k;
@@ -202,14 +201,19 @@ int launch_pyramid(const DeviceLayout& L, const LevelGeom* hg, const uint8_t* sr
                    size_t src_img_stride, int first_slot, int n, unsigned tiled_mask, const TmaMaps* resize_maps, cudaStream_t st) {
   int launches = 0;
   {
-    long long total = (long long)(hg[0].pitch >> 4) * hg[0].rows * n;
-    k_border_level0<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, src, src_pitch, src_img_stride, first_slot, n);
+    // interior vectors: all 16 source bytes inside the row, x0 = 16 v - 19 >= 0 and x0 + 16 <= w
+    const int vec_per_row = hg[0].pitch >> 4;
+    const int v_lo = (kEdge + 15) / 16, v_hi = std::min((hg[0].w + kEdge - 16) / 16, vec_per_row - 1);
+    const int n_int = std::max(v_hi - v_lo + 1, 0);
+    const int per_row = std::max(n_int, vec_per_row - n_int);
+    const unsigned blocks = (unsigned)(((long long)per_row * hg[0].rows + 255) / 256);
+    k_border_level0<<<dim3(blocks, 2, (unsigned)n), 256, 0, st>>>(L, src, src_pitch, src_img_stride, first_slot, n_int > 0 ? v_lo : 0, n_int);
     ++launches;
   }
   for (int l = 1; l < L.nlevels; ++l) {
     if (tiled_mask & (1u << l)) {
       const int tiles_x = (hg[l].pitch + kRtTW - 1) / kRtTW, tiles_y = (hg[l].rows + kRtTH - 1) / kRtTH;
-      k_resize_tiled<<<(unsigned)(tiles_x * tiles_y * n), 256, 0, st>>>(L, *resize_maps, l, first_slot, n, tiles_x, tiles_y);
+      k_resize_tiled<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)n), 256, 0, st>>>(L, *resize_maps, l, first_slot);
     } else {
       long long total = (long long)(hg[l].pitch >> 2) * hg[l].rows * n;
       k_resize_level<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, l, first_slot, n);
