@@ -195,6 +195,39 @@ orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const u
                                                int lcap, float th, int check_orientation, int* frame_obs,
                                                int* assigned, int* n_matches, int on_device, void* stream);
 
+/* ---- Frame construction after extraction --------------------------------- */
+
+/* mK and mDistCoef of a Frame: fx, fy, cx, cy and OpenCV's k1, k2, p1, p2, k3 (src/Tracking.cc:57-87). */
+typedef struct orbx_camera {
+  float fx, fy, cx, cy, k1, k2, p1, p2, k3;
+} orbx_camera;
+
+#define ORBX_GRID_COLS 64 /* FRAME_GRID_COLS, include/Frame.h:38 */
+#define ORBX_GRID_ROWS 48 /* FRAME_GRID_ROWS, include/Frame.h:37 */
+
+/* Frame::UndistortKeyPoints (src/Frame.cc:404-434: cv::undistortPoints(mat, mat, mK, mDistCoef, Mat(), mK),
+ * a plain copy when k1 == 0), Frame::ComputeImageBounds (src/Frame.cc:436-464, image size cols x rows) and
+ * Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:230-245, 382-392) for n_frames frames of one camera.
+ * Frame f: n[f] keypoints at kps + f*cap.  kps_un receives mvKeysUn in the same layout; bounds[6] receives
+ * mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv; the grid comes back as
+ * mGrid flattened: cell c = ix*48 + iy holds cell_items[f*cap + cell_start[f*3073 + c] ..
+ * f*cap + cell_start[f*3073 + c + 1]) in the reference's push_back (index) order.  All pointers host or all
+ * device per on_device. */
+orbx_status orbx_undistort_grid_batch(const orbx_keypoint* kps, const int* n, int n_frames, int cap,
+                                      const orbx_camera* camera, int cols, int rows, orbx_keypoint* kps_un,
+                                      float* bounds, int* cell_start, int* cell_items, int on_device,
+                                      void* stream);
+
+/* Frame::GetFeaturesInArea(x, y, r, minLevel, maxLevel) (src/Frame.cc:327-380) for n_queries queries against
+ * the frames prepared by orbx_undistort_grid_batch: query q asks frame q_frame[q].  out_idx[q*qcap ..] receives
+ * the keypoint indices in the reference's order (cell column, cell row, index), out_cnt[q] their number; when
+ * it exceeds qcap only the first qcap are written.  All pointers host or all device per on_device. */
+orbx_status orbx_features_in_area_batch(const orbx_keypoint* kps_un, const int* n, int n_frames, int cap,
+                                        const float* bounds, const int* cell_start, const int* cell_items,
+                                        const int* q_frame, const float* q_x, const float* q_y, const float* q_r,
+                                        const int* q_min_level, const int* q_max_level, int n_queries, int qcap,
+                                        int* out_idx, int* out_cnt, int on_device, void* stream);
+
 /* The brute-force search of orbx_knn_ratio_batch for ONE pair, for callers that must not
  * allocate.  It has no counterpart in the reference.  Some callers cannot afford or are not
  * allowed a CUDA allocation on this path: a tracking thread with a per-frame deadline

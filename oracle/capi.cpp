@@ -93,6 +93,37 @@ void orbo_transform_points(const float* Rcw, const float* tcw, const float* xw, 
 
 int orbo_hamming256(const uint8_t* a, const uint8_t* b) { return hamming256(a, b); }
 
+// cam = {fx, fy, cx, cy, k1, k2, p1, p2, k3}
+void orbo_undistort_points(const float* cam, const float* xy, int n, float* out) {
+  Camera c; std::memcpy(&c, cam, sizeof(c));
+  for (int i = 0; i < n; ++i) undistort_point(c, xy[2 * i], xy[2 * i + 1], out + 2 * i, out + 2 * i + 1);
+}
+// Frame::UndistortKeyPoints + ComputeImageBounds + AssignFeaturesToGrid: kun, bounds {minX,maxX,minY,maxY,invW,invH},
+// cell_start[64*48+1] / items[n] (cell = ix*48 + iy, insertion order inside a cell)
+void orbo_undistort_grid(const float* cam, const KeyPt* k, int n, int cols, int rows, KeyPt* kun, float* bounds,
+                         int* cell_start, int* items) {
+  Camera c; std::memcpy(&c, cam, sizeof(c));
+  undistort_keypoints(c, k, n, kun);
+  image_bounds(c, cols, rows, bounds);
+  FrameGrid g(kun, n, bounds);
+  bounds[4] = g.invW; bounds[5] = g.invH;
+  int pos = 0;
+  for (int ix = 0; ix < kGridCols; ++ix)
+    for (int iy = 0; iy < kGridRows; ++iy) {
+      cell_start[ix * kGridRows + iy] = pos;
+      for (int idx : g.cell[ix][iy]) items[pos++] = idx;
+    }
+  cell_start[kGridCols * kGridRows] = pos;
+}
+int orbo_features_in_area(const KeyPt* kun, int n, const float* bounds, float x, float y, float r, int minLevel,
+                          int maxLevel, int* out, int cap) {
+  FrameGrid g(kun, n, bounds);
+  std::vector<int> v;
+  g.in_area(kun, x, y, r, minLevel, maxLevel, v);
+  for (int i = 0; i < (int)v.size() && i < cap; ++i) out[i] = v[i];
+  return (int)v.size();
+}
+
 // --- primitives, exported so tests can pin them against cv2 -------------------------------
 void orbo_resize(const uint8_t* s, int sw, int sh, int sp, uint8_t* d, int dw, int dh, int dp) {
   resize_linear_u8(s, sw, sh, sp, d, dw, dh, dp);

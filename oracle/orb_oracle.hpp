@@ -462,14 +462,68 @@ constexpr int kGridCols = 64, kGridRows = 48, kHisto = 30;
 
 // The 64x48 bucket grid of a frame (Frame::AssignFeaturesToGrid, src/Frame.cc:230-245) for an
 // undistorted camera (k1 == 0): bounds are [0,cols) x [0,rows).
+// cv::undistortPoints(src, dst, K, distCoef, noArray(), K) as Frame::UndistortKeyPoints and
+// Frame::ComputeImageBounds call it (src/Frame.cc:404-434, 436-464): OpenCV 4.13 normalises with K,
+// runs exactly 5 fixed-point iterations of the radial/tangential model in double (the 6-argument
+// overload passes TermCriteria(MAX_ITER, 5, 0.01), so there is no early exit on the error), and
+// re-projects with P = K.  d = {k1, k2, p1, p2, k3}.  Pinned against cv2.undistortPoints in
+// tests/test_oracle_cv2.py.
+struct Camera { float fx, fy, cx, cy, d[5]; };
+inline void undistort_point(const Camera& c, float u, float v, float* ox, float* oy) {
+  const double fx = c.fx, fy = c.fy, cx = c.cx, cy = c.cy, ifx = 1. / fx, ify = 1. / fy;
+  double k[12] = {c.d[0], c.d[1], c.d[2], c.d[3], c.d[4], 0, 0, 0, 0, 0, 0, 0};
+  double x = ((double)u - cx) * ifx, y = ((double)v - cy) * ify;
+  const double x0 = x, y0 = y;
+  for (int j = 0; j < 5; ++j) {
+    const double r2 = x * x + y * y;
+    const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+    if (icdist < 0) { x = ((double)u - cx) * ifx; y = ((double)v - cy) * ify; break; }
+    const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+    const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+    x = (x0 - deltaX) * icdist;
+    y = (y0 - deltaY) * icdist;
+  }
+  const double xx = fx * x + 0. * y + cx, yy = 0. * x + fy * y + cy, ww = 1. / (0. * x + 0. * y + 1.);
+  *ox = (float)(xx * ww); *oy = (float)(yy * ww);
+}
+// Frame::UndistortKeyPoints (src/Frame.cc:404-434): a copy when k1 == 0
+inline void undistort_keypoints(const Camera& c, const KeyPt* k, int n, KeyPt* out) {
+  for (int i = 0; i < n; ++i) {
+    out[i] = k[i];
+    if (c.d[0] != 0.f) undistort_point(c, k[i].x, k[i].y, &out[i].x, &out[i].y);
+  }
+}
+// Frame::ComputeImageBounds (src/Frame.cc:436-464) -> {mnMinX, mnMaxX, mnMinY, mnMaxY}
+inline void image_bounds(const Camera& c, int cols, int rows, float b[4]) {
+  if (c.d[0] != 0.f) {
+    float px[4], py[4];
+    const float cu[4] = {0.f, (float)cols, 0.f, (float)cols}, cv[4] = {0.f, 0.f, (float)rows, (float)rows};
+    for (int i = 0; i < 4; ++i) undistort_point(c, cu[i], cv[i], &px[i], &py[i]);
+    b[0] = std::min(px[0], px[2]); b[1] = std::max(px[1], px[3]);
+    b[2] = std::min(py[0], py[1]); b[3] = std::max(py[2], py[3]);
+  } else {
+    b[0] = 0.f; b[1] = (float)cols; b[2] = 0.f; b[3] = (float)rows;
+  }
+}
+
+// Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea (src/Frame.cc:230-245, 327-392)
 struct FrameGrid {
-  float invW, invH;
+  float minX = 0.f, minY = 0.f, invW, invH;
   std::vector<int> cell[kGridCols][kGridRows];
   FrameGrid(const KeyPt* k, int n, int cols, int rows) {
     invW = (float)kGridCols / (float)cols;
     invH = (float)kGridRows / (float)rows;
+    assign(k, n);
+  }
+  FrameGrid(const KeyPt* k, int n, const float b[4]) {          // undistorted bounds, src/Frame.cc:101-102
+    minX = b[0]; minY = b[2];
+    invW = (float)kGridCols / (b[1] - b[0]);
+    invH = (float)kGridRows / (b[3] - b[2]);
+    assign(k, n);
+  }
+  void assign(const KeyPt* k, int n) {
     for (int i = 0; i < n; ++i) {
-      int gx = (int)std::round((k[i].x - 0.f) * invW), gy = (int)std::round((k[i].y - 0.f) * invH);
+      int gx = (int)std::round((k[i].x - minX) * invW), gy = (int)std::round((k[i].y - minY) * invH);
       if (gx < 0 || gx >= kGridCols || gy < 0 || gy >= kGridRows) continue;
       cell[gx][gy].push_back(i);
     }
@@ -477,13 +531,13 @@ struct FrameGrid {
   void in_area(const KeyPt* k, float x, float y, float r, int minLevel, int maxLevel,
                std::vector<int>& out) const {
     out.clear();
-    const int cx0 = std::max(0, (int)std::floor((x - 0.f - r) * invW));
+    const int cx0 = std::max(0, (int)std::floor((x - minX - r) * invW));
     if (cx0 >= kGridCols) return;
-    const int cx1 = std::min(kGridCols - 1, (int)std::ceil((x - 0.f + r) * invW));
+    const int cx1 = std::min(kGridCols - 1, (int)std::ceil((x - minX + r) * invW));
     if (cx1 < 0) return;
-    const int cy0 = std::max(0, (int)std::floor((y - 0.f - r) * invH));
+    const int cy0 = std::max(0, (int)std::floor((y - minY - r) * invH));
     if (cy0 >= kGridRows) return;
-    const int cy1 = std::min(kGridRows - 1, (int)std::ceil((y - 0.f + r) * invH));
+    const int cy1 = std::min(kGridRows - 1, (int)std::ceil((y - minY + r) * invH));
     if (cy1 < 0) return;
     const bool chk = (minLevel > 0) || (maxLevel >= 0);
     for (int ix = cx0; ix <= cx1; ++ix)

@@ -113,6 +113,37 @@ def knn_ratio(dA, angA, dB, angB, th=50, ratio=0.75, check_ori=True, strict=True
     return m12, n
 
 
+def _cam(cam):
+    """cam: (fx, fy, cx, cy, k1, k2, p1, p2, k3) -> float32[9]"""
+    c = np.zeros(9, np.float32); c[:len(cam)] = np.asarray(cam, np.float32)
+    return c
+
+
+def undistort_points(cam, xy):
+    """cv::undistortPoints(xy, K, distCoef, noArray(), K) restated (src/Frame.cc:423)."""
+    xy = np.ascontiguousarray(xy, np.float32); out = np.empty_like(xy); c = _cam(cam)
+    lib().orbo_undistort_points(_p(c), _p(xy), len(xy), _p(out))
+    return out
+
+
+def undistort_grid(cam, k, cols, rows):
+    """Frame::UndistortKeyPoints + ComputeImageBounds + AssignFeaturesToGrid.
+    Returns (mvKeysUn, bounds[6] = minX,maxX,minY,maxY,invW,invH, cell_start[3073], items)."""
+    k = np.ascontiguousarray(k); n = len(k); c = _cam(cam)
+    kun = np.zeros(n, KP_DTYPE); bounds = np.zeros(6, np.float32)
+    cs = np.zeros(64 * 48 + 1, np.int32); items = np.zeros(max(n, 1), np.int32)
+    lib().orbo_undistort_grid(_p(c), _p(k), n, cols, rows, _p(kun), _p(bounds), _p(cs), _p(items))
+    return kun, bounds, cs, items[:cs[-1]]
+
+
+def features_in_area(kun, bounds, x, y, r, min_level=-1, max_level=-1):
+    """Frame::GetFeaturesInArea (src/Frame.cc:327-380) -> indices in the reference's order."""
+    kun = np.ascontiguousarray(kun); out = np.zeros(max(len(kun), 1), np.int32)
+    L = lib(); L.orbo_features_in_area.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+    n = L.orbo_features_in_area(_p(kun), len(kun), _p(np.ascontiguousarray(bounds, np.float32)), x, y, r, min_level, max_level, _p(out), len(out))
+    return out[:n].copy()
+
+
 def search_projection(k, d, uright, cols, rows, scale, mp, th=1.0, nnratio=0.8, frame_obs=None):
     """mp: dict of arrays inview(u8), projx, projy, projxr (f32), level (i32), viewcos (f32), desc (m,32), obs (i32)."""
     k = np.ascontiguousarray(k); d = np.ascontiguousarray(d); n = len(k); m = len(mp["level"])

@@ -94,6 +94,8 @@ def lib():
                                                    [C.c_int, C.c_float, C.c_float] + [C.c_void_p] * 3 + [C.c_int, C.c_void_p])
         L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                              C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orbx_undistort_grid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
+        L.orbx_features_in_area_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]
         L.orbx_get_profile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _LIB = L
@@ -294,6 +296,60 @@ class Frame:
 
     def __init__(self, keypoints, descriptors, cols, rows):
         self.mvKeysUn, self.mDescriptors, self.cols, self.rows = keypoints, descriptors, cols, rows
+
+
+class _Camera(C.Structure):
+    _fields_ = [(f, C.c_float) for f in ("fx", "fy", "cx", "cy", "k1", "k2", "p1", "p2", "k3")]
+
+
+GRID_COLS, GRID_ROWS = 64, 48
+
+
+class FrameGrids:
+    """Frame::UndistortKeyPoints + ComputeImageBounds + AssignFeaturesToGrid (src/Frame.cc:404-464, 230-245) for a
+    batch of frames of one camera, and GetFeaturesInArea (src/Frame.cc:327-380) on the result.
+    camera = (fx, fy, cx, cy, k1, k2, p1, p2[, k3])."""
+
+    def __init__(self, keypoint_lists, camera, cols, rows):
+        cam = list(camera) + [0.0] * (9 - len(camera))
+        self.camera = _Camera(*[float(v) for v in cam])
+        nf = len(keypoint_lists)
+        self.cap = cap = max(max((len(k) for k in keypoint_lists), default=1), 1)
+        self.n = np.array([len(k) for k in keypoint_lists], np.int32)
+        kps = np.zeros((nf, cap), KP_DTYPE)
+        for f, k in enumerate(keypoint_lists):
+            kps[f, :len(k)] = k
+        self.kps_un = np.zeros((nf, cap), KP_DTYPE)
+        self.bounds = np.zeros(6, np.float32)
+        self.cell_start = np.zeros((nf, GRID_COLS * GRID_ROWS + 1), np.int32)
+        self.cell_items = np.zeros((nf, cap), np.int32)
+        _check(lib().orbx_undistort_grid_batch(kps.ctypes.data, self.n.ctypes.data, nf, cap, C.byref(self.camera), cols, rows,
+                                               self.kps_un.ctypes.data, self.bounds.ctypes.data, self.cell_start.ctypes.data,
+                                               self.cell_items.ctypes.data, 0, None))
+
+    @property
+    def mvKeysUn(self):
+        return [self.kps_un[f, :self.n[f]] for f in range(len(self.n))]
+
+    def cell(self, f, ix, iy):
+        """mGrid[ix][iy] of frame f."""
+        c = ix * GRID_ROWS + iy
+        return self.cell_items[f, self.cell_start[f, c]:self.cell_start[f, c + 1]]
+
+    def GetFeaturesInArea(self, queries, qcap=None):
+        """queries: iterable of (frame, x, y, r, minLevel, maxLevel) -> list of index arrays in the reference's order."""
+        q = list(queries)
+        nq = len(q)
+        qcap = int(qcap or self.cap)
+        qf = np.array([v[0] for v in q], np.int32); qx = np.array([v[1] for v in q], np.float32)
+        qy = np.array([v[2] for v in q], np.float32); qr = np.array([v[3] for v in q], np.float32)
+        lo = np.array([v[4] for v in q], np.int32); hi = np.array([v[5] for v in q], np.int32)
+        out = np.zeros((nq, qcap), np.int32); cnt = np.zeros(nq, np.int32)
+        _check(lib().orbx_features_in_area_batch(self.kps_un.ctypes.data, self.n.ctypes.data, len(self.n), self.cap,
+                                                 self.bounds.ctypes.data, self.cell_start.ctypes.data, self.cell_items.ctypes.data,
+                                                 qf.ctypes.data, qx.ctypes.data, qy.ctypes.data, qr.ctypes.data, lo.ctypes.data,
+                                                 hi.ctypes.data, nq, qcap, out.ctypes.data, cnt.ctypes.data, 0, None))
+        return [out[i, :min(cnt[i], qcap)].copy() for i in range(nq)], cnt
 
 
 class ORBmatcher:

@@ -664,6 +664,67 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
   return ORBX_OK;
 }
 
+orbx_status orbx_undistort_grid_batch(const orbx_keypoint* kps, const int* n, int n_frames, int cap, const orbx_camera* camera,
+                                      int cols, int rows, orbx_keypoint* kps_un, float* bounds, int* cell_start, int* cell_items,
+                                      int on_device, void* stream) {
+  if (!kps || !n || !camera || !kps_un || !bounds || !cell_start || !cell_items) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_frames < 1 || cap < 1 || cols < 1 || rows < 1) return fail(ORBX_ERR_BAD_ARG, "bad sizes");
+  if (!(camera->fx != 0.f) || !(camera->fy != 0.f)) return fail(ORBX_ERR_BAD_ARG, "fx and fy must be non-zero");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t nf = (size_t)n_frames, fc = nf * cap, cells = nf * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1);
+  FrameGridArgs a;
+  CU(sg.in(kps, fc, on_device, &a.k)); CU(sg.in(n, nf, on_device, &a.n));
+  if (on_device) { a.kun = kps_un; a.bounds = bounds; a.cell_start = cell_start; a.items = cell_items; }
+  else {
+    CU(sg.alloc((void**)&a.kun, fc * sizeof(orbx_keypoint))); CU(sg.alloc((void**)&a.bounds, 6 * sizeof(float)));
+    CU(sg.alloc((void**)&a.cell_start, cells * sizeof(int))); CU(sg.alloc((void**)&a.items, fc * sizeof(int)));
+  }
+  a.n_frames = n_frames; a.cap = cap; a.cols = cols; a.rows = rows; a.cam = *camera;
+  g_launches += launch_undistort_grid(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(kps_un, a.kun, fc * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(bounds, a.bounds, 6 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(cell_start, a.cell_start, cells * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(cell_items, a.items, fc * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
+orbx_status orbx_features_in_area_batch(const orbx_keypoint* kps_un, const int* n, int n_frames, int cap, const float* bounds,
+                                        const int* cell_start, const int* cell_items, const int* q_frame, const float* q_x,
+                                        const float* q_y, const float* q_r, const int* q_min_level, const int* q_max_level,
+                                        int n_queries, int qcap, int* out_idx, int* out_cnt, int on_device, void* stream) {
+  if (!kps_un || !n || !bounds || !cell_start || !cell_items || !q_frame || !q_x || !q_y || !q_r || !q_min_level || !q_max_level ||
+      !out_idx || !out_cnt)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_frames < 1 || cap < 1 || n_queries < 1 || qcap < 1) return fail(ORBX_ERR_BAD_ARG, "bad sizes");
+  if (!on_device)
+    for (int q = 0; q < n_queries; ++q)
+      if (q_frame[q] < 0 || q_frame[q] >= n_frames) return fail(ORBX_ERR_BAD_ARG, "q_frame out of range");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t nf = (size_t)n_frames, fc = nf * cap, cells = nf * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1), nq = (size_t)n_queries;
+  AreaArgs a;
+  CU(sg.in(kps_un, fc, on_device, &a.kun)); CU(sg.in(bounds, 6, on_device, &a.bounds));
+  CU(sg.in(cell_start, cells, on_device, &a.cell_start)); CU(sg.in(cell_items, fc, on_device, &a.items));
+  CU(sg.in(q_frame, nq, on_device, &a.q_frame)); CU(sg.in(q_x, nq, on_device, &a.q_x)); CU(sg.in(q_y, nq, on_device, &a.q_y));
+  CU(sg.in(q_r, nq, on_device, &a.q_r)); CU(sg.in(q_min_level, nq, on_device, &a.q_min_level)); CU(sg.in(q_max_level, nq, on_device, &a.q_max_level));
+  if (on_device) { a.out_idx = out_idx; a.out_cnt = out_cnt; }
+  else { CU(sg.alloc((void**)&a.out_idx, nq * qcap * sizeof(int))); CU(sg.alloc((void**)&a.out_cnt, nq * sizeof(int))); }
+  a.cap = cap; a.n_queries = n_queries; a.qcap = qcap;
+  g_launches += launch_features_in_area(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(out_idx, a.out_idx, nq * qcap * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out_cnt, a.out_cnt, nq * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
 orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right, const int* n,
                                          int n_frames, int cap, int cols, int rows, const float* scale_factors, int nlevels,
                                          const uint8_t* mp_in_view, const float* mp_proj_x, const float* mp_proj_y,

@@ -137,6 +137,22 @@ struct ProjFrameArgs {
 };
 int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st);
 
+struct FrameGridArgs {
+  const orbx_keypoint* k; const int* n; int n_frames, cap, cols, rows;
+  orbx_camera cam;
+  orbx_keypoint* kun; float* bounds; int* cell_start; int* items;
+};
+int launch_undistort_grid(const FrameGridArgs& a, cudaStream_t st);
+
+struct AreaArgs {
+  const orbx_keypoint* kun; int cap;
+  const float* bounds; const int* cell_start; const int* items;
+  const int* q_frame; const float* q_x; const float* q_y; const float* q_r; const int* q_min_level; const int* q_max_level;
+  int n_queries, qcap;
+  int* out_idx; int* out_cnt;
+};
+int launch_features_in_area(const AreaArgs& a, cudaStream_t st);
+
 // shared by the extern "C" entry points that live outside orbx_api.cu
 orbx_status set_error(orbx_status s, const char* msg);
 void count_launches(int n);

@@ -457,3 +457,48 @@ def test_full_size_batch_properties(gx):
     d = res[0][1]
     assert all(gx.ORBmatcher.DescriptorDistance(d[i], d[i]) == 0 for i in range(0, len(d), 97))
     assert nm[0] > 100
+
+
+TUM1_CAM = (517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+
+
+@pytest.mark.parametrize("cam,w,h", [(TUM1_CAM, 640, 480), ((718.856, 718.856, 607.1928, 185.2157, 0, 0, 0, 0, 0), 1241, 376),
+                                     ((458.654, 457.296, 367.215, 248.375, -0.28340811, 0.07395907, 0.00019359, 1.76187114e-05), 752, 480)])
+def test_undistort_grid_and_features_in_area(gx, oracle, cam, w, h):
+    """K10 / K11: mvKeysUn bit-exact (double-precision undistortPoints restated on the device),
+    image bounds, the 64x48 grid in push_back order, GetFeaturesInArea in the reference's enumeration order.
+    Distorted (TUM1, EuRoC raw) and rectified (KITTI: plain copy) cameras; frames of different sizes in one batch."""
+    G = _ext(gx, w, h, 1000)
+    frames = [synth.mono_frame(300 + i, w, h) for i in range(3)]
+    kls = [G(f)[0] for f in frames]
+    kls[1] = kls[1][:417]                                     # ragged batch
+    kls.append(kls[0][:0])                                    # an empty frame
+    FG = gx.FrameGrids(kls, cam, w, h)
+    rng = np.random.default_rng(7)
+    for f, k in enumerate(kls):
+        kun, b, cs, items = oracle.undistort_grid(cam, k, w, h)
+        got = FG.mvKeysUn[f]
+        assert np.array_equal(got.view(np.uint8), kun.view(np.uint8)), f
+        assert np.array_equal(FG.bounds.view(np.uint32), b.view(np.uint32))
+        assert np.array_equal(FG.cell_start[f], cs), f
+        assert np.array_equal(FG.cell_items[f, :cs[-1]], items), f
+    if cam[4] != 0:
+        assert not np.array_equal(FG.mvKeysUn[0]["x"], kls[0]["x"])
+        assert FG.bounds[0] != 0.0
+    else:
+        assert np.array_equal(FG.mvKeysUn[0]["x"], kls[0]["x"]) and FG.bounds[0] == 0.0 and FG.bounds[1] == w
+    queries = []
+    for _ in range(300):
+        f = int(rng.integers(0, len(kls)))
+        lo, hi = (-1, -1) if rng.random() < 0.4 else (int(rng.integers(0, 3)), int(rng.integers(-1, 8)))
+        queries.append((f, float(rng.uniform(-30, w + 30)), float(rng.uniform(-30, h + 30)), float(rng.uniform(1, 150)), lo, hi))
+    queries.append((0, -500.0, 100.0, 10.0, -1, -1))           # window left of the grid
+    queries.append((0, w / 2, h / 2, 5000.0, -1, -1))          # window covering everything
+    got, cnt = FG.GetFeaturesInArea(queries)
+    for (f, x, y, r, lo, hi), g, c in zip(queries, got, cnt):
+        want = oracle.features_in_area(FG.mvKeysUn[f], FG.bounds, x, y, r, lo, hi)
+        assert c == len(want) and np.array_equal(g, want), (f, x, y, r, lo, hi)
+    assert cnt[-1] == len(kls[0])
+    # truncation: count is still the full count, the first qcap indices are written
+    got2, cnt2 = FG.GetFeaturesInArea(queries[-1:], qcap=10)
+    assert cnt2[0] == len(kls[0]) and np.array_equal(got2[0], got[-1][:10])

@@ -171,3 +171,61 @@ def test_camera_transform_matches_cv2_gemm(oracle):
         ours = oracle.project_points(R, t.ravel(), X)
         ref = np.stack([cv2.gemm(R, X[i].reshape(3, 1), 1.0, t, 1.0).ravel() for i in range(len(X))])
         assert np.array_equal(ours.view(np.uint32), ref.view(np.uint32))
+
+
+TUM1 = (517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+TUM2 = (520.908620, 521.007327, 325.141442, 249.701764, 0.231222, -0.784899, -0.003257, -0.000105, 0.917205)
+
+
+@pytest.mark.parametrize("cam", [TUM1, TUM2, (458.654, 457.296, 367.215, 248.375, -0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0)])
+def test_undistort_points_matches_cv2(oracle, cam):
+    O = oracle
+    """Frame::UndistortKeyPoints / ComputeImageBounds call cv::undistortPoints(mat, mat, mK, mDistCoef, Mat(), mK)
+    (src/Frame.cc:423, :449): the restatement must give the same float32 bits, corners and far-out points included."""
+    rng = np.random.default_rng(11)
+    pts = np.stack([rng.uniform(-40, 800, 40000), rng.uniform(-40, 560, 40000)], 1).astype(np.float32)
+    pts[:4] = [[0, 0], [640, 0], [0, 480], [640, 480]]
+    K = np.array([[cam[0], 0, cam[2]], [0, cam[1], cam[3]], [0, 0, 1]], np.float32)
+    D = np.array(cam[4:], np.float32)
+    ref = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, D, None, K).reshape(-1, 2)
+    got = O.undistort_points(cam, pts)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+
+
+def test_image_bounds_and_grid_restatement(oracle):
+    O = oracle
+    """bounds from the four undistorted corners (src/Frame.cc:436-464); the grid puts every keypoint in cell
+    round((x - minX) * invW), round((y - minY) * invH), inside a cell in index order (src/Frame.cc:230-245)."""
+    rng = np.random.default_rng(5)
+    n = 1500
+    k = np.zeros(n, O.KP_DTYPE)
+    k["x"] = rng.uniform(19, 621, n).astype(np.float32); k["y"] = rng.uniform(19, 461, n).astype(np.float32)
+    k["octave"] = rng.integers(0, 8, n)
+    kun, b, cs, items = O.undistort_grid(TUM1, k, 640, 480)
+    K = np.array([[TUM1[0], 0, TUM1[2]], [0, TUM1[1], TUM1[3]], [0, 0, 1]], np.float32)
+    corners = cv2.undistortPoints(np.array([[[0, 0]], [[640, 0]], [[0, 480]], [[640, 480]]], np.float32), K, np.array(TUM1[4:], np.float32), None, K).reshape(4, 2)
+    assert b[0] == min(corners[0, 0], corners[2, 0]) and b[1] == max(corners[1, 0], corners[3, 0])
+    assert b[2] == min(corners[0, 1], corners[1, 1]) and b[3] == max(corners[2, 1], corners[3, 1])
+    assert b[4] == np.float32(64) / (b[1] - b[0]) and b[5] == np.float32(48) / (b[3] - b[2])
+    gx = np.floor((kun["x"] - b[0]) * b[4] + np.float32(0.5)).astype(int); gy = np.floor((kun["y"] - b[2]) * b[5] + np.float32(0.5)).astype(int)
+    ok = (gx >= 0) & (gx < 64) & (gy >= 0) & (gy < 48)
+    assert cs[-1] == ok.sum() == len(items)
+    for c in rng.integers(0, 64 * 48, 200):
+        want = np.nonzero(ok & (gx * 48 + gy == c))[0]
+        assert np.array_equal(items[cs[c]:cs[c + 1]], want)
+    # GetFeaturesInArea: brute force over the same predicate, order = cell column, cell row, index
+    for _ in range(50):
+        x, y, r = rng.uniform(0, 640), rng.uniform(0, 480), rng.uniform(5, 120)
+        lo, hi = (-1, -1) if rng.random() < 0.5 else (int(rng.integers(0, 4)), int(rng.integers(3, 8)))
+        got = O.features_in_area(kun, b, x, y, r, lo, hi)
+        x32, y32, r32 = np.float32(x), np.float32(y), np.float32(r)
+        m = ok & (np.abs(kun["x"] - x32) < r32) & (np.abs(kun["y"] - y32) < r32)
+        if lo > 0 or hi >= 0:
+            m &= kun["octave"] >= lo
+            if hi >= 0: m &= kun["octave"] <= hi
+        cx0 = max(0, int(np.floor((x32 - b[0] - r32) * b[4]))); cx1 = min(63, int(np.ceil((x32 - b[0] + r32) * b[4])))
+        cy0 = max(0, int(np.floor((y32 - b[2] - r32) * b[5]))); cy1 = min(47, int(np.ceil((y32 - b[2] + r32) * b[5])))
+        m &= (gx >= cx0) & (gx <= cx1) & (gy >= cy0) & (gy <= cy1)
+        idx = np.nonzero(m)[0]
+        want = idx[np.lexsort((idx, gy[idx], gx[idx]))]
+        assert np.array_equal(got, want)
