@@ -264,6 +264,38 @@ def secondary_workloads(gx, torch, local):
     out["knn_ratio_2000x2000_pairs_per_s"] = 3 * P / (a.elapsed_time(b) / 1e3)
     out["knn_ratio_matches_per_pair"] = float(nmm.float().mean())
     out["_knn_distances_per_pair"] = float((cnt[:P].double() * cnt[P:].double()).mean())
+    # --- UndistortKeyPoints + image bounds + grid for the frames above (TUM1 distortion), and
+    #     GetFeaturesInArea queries against them (window 100 px around every keypoint of the first frames) ---
+    cam = (C.c_float * 9)(517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+    F = 2 * P
+    kun = torch.empty_like(kps); bounds = torch.empty(6, dtype=torch.float32, device="cuda")
+    cstart = torch.empty((F, 64 * 48 + 1), dtype=torch.int32, device="cuda"); citems = torch.empty((F, cap), dtype=torch.int32, device="cuda")
+    def grid_step():
+        rc = L.orbx_undistort_grid_batch(kps.data_ptr(), cnt.data_ptr(), F, cap, cam, w, h, kun.data_ptr(), bounds.data_ptr(),
+                                         cstart.data_ptr(), citems.data_ptr(), 1, st)
+        assert rc == 0, L.orbx_last_error_string()
+    for _ in range(2):
+        grid_step()
+    a, b = ev(), ev(); a.record(); [grid_step() for _ in range(5)]; b.record(); torch.cuda.synchronize()
+    out["undistort_grid_frames_per_s"] = 5 * F / (a.elapsed_time(b) / 1e3)
+    nq = 64 * 2000
+    kf = kun.view(torch.float32).reshape(F, cap, 7)
+    qf = torch.arange(64, dtype=torch.int32, device="cuda").repeat_interleave(2000)
+    qi = torch.arange(2000, device="cuda").repeat(64)
+    qx = kf[qf.long(), qi, 0].contiguous(); qy = kf[qf.long(), qi, 1].contiguous()
+    qr = torch.full((nq,), 100.0, dtype=torch.float32, device="cuda")
+    qlo = torch.zeros(nq, dtype=torch.int32, device="cuda"); qhi = torch.zeros(nq, dtype=torch.int32, device="cuda")
+    oidx = torch.empty((nq, 256), dtype=torch.int32, device="cuda"); ocnt = torch.empty(nq, dtype=torch.int32, device="cuda")
+    def area_step():
+        rc = L.orbx_features_in_area_batch(kun.data_ptr(), cnt.data_ptr(), F, cap, bounds.data_ptr(), cstart.data_ptr(), citems.data_ptr(),
+                                           qf.data_ptr(), qx.data_ptr(), qy.data_ptr(), qr.data_ptr(), qlo.data_ptr(), qhi.data_ptr(),
+                                           nq, 256, oidx.data_ptr(), ocnt.data_ptr(), 1, st)
+        assert rc == 0, L.orbx_last_error_string()
+    for _ in range(2):
+        area_step()
+    a, b = ev(), ev(); a.record(); [area_step() for _ in range(5)]; b.record(); torch.cuda.synchronize()
+    out["features_in_area_queries_per_s"] = 5 * nq / (a.elapsed_time(b) / 1e3)
+    out["features_in_area_hits_per_query"] = float(ocnt.float().mean())
     G.close()
     return out
 

@@ -7,6 +7,8 @@
 //                             SearchForInitialization on flat arrays); the other searches keep
 //                             using the reference implementation and call DescriptorDistance
 //   ORB_SLAM2::ComputeStereoMatchesGPU   body for Frame::ComputeStereoMatches (src/Frame.cc:466)
+//   ORB_SLAM2::FrameGridGPU              bodies for UndistortKeyPoints / ComputeImageBounds / AssignFeaturesToGrid /
+//                                        GetFeaturesInArea (src/Frame.cc:230-245, 327-464)
 //
 // Same constructor arguments, same operator() signature, same getters, same public
 // mvImagePyramid member (filled on demand by DownloadPyramid(), because the stereo matcher reads
@@ -17,6 +19,7 @@
 
 #include <opencv2/core/core.hpp>
 
+#include <algorithm>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -115,6 +118,40 @@ inline void ComputeStereoMatchesGPU(ORBextractor& left, ORBextractor& right, int
   mvuRight.assign(ur.begin(), ur.begin() + N);
   mvDepth.assign(dp.begin(), dp.begin() + N);
 }
+
+// Bodies for Frame::UndistortKeyPoints + ComputeImageBounds + AssignFeaturesToGrid (src/Frame.cc:404-464, 230-245)
+// and Frame::GetFeaturesInArea (src/Frame.cc:327-380).  mK is the 3x3 CV_32F camera matrix, mDistCoef the 4x1 or
+// 5x1 CV_32F coefficient vector of the Frame constructors.
+struct FrameGridGPU {
+  std::vector<cv::KeyPoint> mvKeysUn;
+  float mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+  std::vector<int> cell_start, cell_items;   // mGrid[ix][iy] = cell_items[cell_start[ix*48+iy] .. cell_start[ix*48+iy+1])
+
+  void Build(const std::vector<cv::KeyPoint>& mvKeys, const cv::Mat& mK, const cv::Mat& mDistCoef, int cols, int rows) {
+    orbx_camera cam = {mK.at<float>(0, 0), mK.at<float>(1, 1), mK.at<float>(0, 2), mK.at<float>(1, 2), 0, 0, 0, 0, 0};
+    float* d = &cam.k1;
+    for (int i = 0; i < (int)mDistCoef.total() && i < 5; ++i) d[i] = mDistCoef.at<float>(i);
+    const int n = (int)mvKeys.size(), cap = std::max(n, 1);
+    mvKeysUn.resize(cap);
+    cell_start.assign(ORBX_GRID_COLS * ORBX_GRID_ROWS + 1, 0); cell_items.assign(cap, 0);
+    float b[6];
+    std::vector<cv::KeyPoint> in(mvKeys); in.resize(cap);
+    orbx_check(orbx_undistort_grid_batch(reinterpret_cast<const orbx_keypoint*>(in.data()), &n, 1, cap, &cam, cols, rows,
+                                         reinterpret_cast<orbx_keypoint*>(mvKeysUn.data()), b, cell_start.data(), cell_items.data(), 0, nullptr));
+    mvKeysUn.resize(n);
+    mnMinX = b[0]; mnMaxX = b[1]; mnMinY = b[2]; mnMaxY = b[3]; mfGridElementWidthInv = b[4]; mfGridElementHeightInv = b[5];
+  }
+  std::vector<size_t> GetFeaturesInArea(float x, float y, float r, int minLevel = -1, int maxLevel = -1) const {
+    const int n = (int)mvKeysUn.size(), cap = std::max(n, 1), q_frame = 0;
+    const float b[6] = {mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv};
+    std::vector<cv::KeyPoint> in(mvKeysUn); in.resize(cap);
+    std::vector<int> idx(cap);
+    int cnt = 0;
+    orbx_check(orbx_features_in_area_batch(reinterpret_cast<const orbx_keypoint*>(in.data()), &n, 1, cap, b, cell_start.data(), cell_items.data(),
+                                           &q_frame, &x, &y, &r, &minLevel, &maxLevel, 1, cap, idx.data(), &cnt, 0, nullptr));
+    return std::vector<size_t>(idx.begin(), idx.begin() + cnt);
+  }
+};
 
 class ORBmatcher {
  public:

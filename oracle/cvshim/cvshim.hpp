@@ -110,6 +110,9 @@ class Mat {
   }
   template <typename T> T& at(int y, int x) { return *(T*)(data + (size_t)y * step + x * sizeof(T)); }
   template <typename T> const T& at(int y, int x) const { return *(const T*)(data + (size_t)y * step + x * sizeof(T)); }
+  template <typename T> T& at(int i) { return ((T*)data)[i]; }                     // continuous row / column vectors
+  template <typename T> const T& at(int i) const { return ((const T*)data)[i]; }
+  size_t total() const { return (size_t)rows * cols; }
   uchar* ptr(int y = 0) { return data + (size_t)y * step; }
   const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
   template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
