@@ -264,6 +264,19 @@ def secondary_workloads(gx, torch, local):
     out["knn_ratio_2000x2000_pairs_per_s"] = 3 * P / (a.elapsed_time(b) / 1e3)
     out["knn_ratio_matches_per_pair"] = float(nmm.float().mean())
     out["_knn_distances_per_pair"] = float((cnt[:P].double() * cnt[P:].double()).mean())
+    # --- SearchByBoW(KF,KF) over vocabulary buckets; stand-in vocabulary: 100 nodes from descriptor bits ---
+    node = ((desc[:, :, 0].int() >> 4) * 7 + (desc[:, :, 1].int() >> 5)).contiguous()          # 0..111, equal for most true matches
+    valid = torch.ones((2 * P, cap), dtype=torch.uint8, device="cuda")
+    def bow_step():
+        rc = L.orbx_search_by_bow_batch(desc.data_ptr(), ang.data_ptr(), valid.data_ptr(), node.data_ptr(), cnt.data_ptr(),
+                                        desc[P:].data_ptr(), ang[P:].data_ptr(), valid[P:].data_ptr(), node[P:].data_ptr(), cnt[P:].data_ptr(),
+                                        P, cap, 50, 0.75, 1, 1, m12.data_ptr(), nmm.data_ptr(), 1, st)
+        assert rc == 0, L.orbx_last_error_string()
+    for _ in range(2):
+        bow_step()
+    a, b = ev(), ev(); a.record(); [bow_step() for _ in range(3)]; b.record(); torch.cuda.synchronize()
+    out["search_by_bow_buckets_pairs_per_s"] = 3 * P / (a.elapsed_time(b) / 1e3)
+    out["search_by_bow_matches_per_pair"] = float(nmm.float().mean())
     # --- UndistortKeyPoints + image bounds + grid for the frames above (TUM1 distortion), and
     #     GetFeaturesInArea queries against them (window 100 px around every keypoint of the first frames) ---
     cam = (C.c_float * 9)(517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314)

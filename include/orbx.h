@@ -195,6 +195,21 @@ orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const u
                                                int lcap, float th, int check_orientation, int* frame_obs,
                                                int* assigned, int* n_matches, int on_device, void* stream);
 
+/* ORBmatcher::SearchByBoW with the vocabulary buckets of DBoW2, both forms:
+ *   SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)  src/ORBmatcher.cc:522-655: strict_lt = 1, validB = pMP2 && !isBad()
+ *   SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) src/ORBmatcher.cc:159-288: strict_lt = 0, validB = all ones
+ * for n_pairs independent pairs.  A side = the first keyframe: descA/angA (mvKeysUn[i].angle), validA[i] =
+ * (pMP1 && !pMP1->isBad()), nodeA[i] = the FeatureVector node of feature i (the key under which
+ * mFeatVec lists i; >= 0); B side likewise.  Features are visited in the reference's order (ascending node id,
+ * then ascending index inside a node, Thirdparty/DBoW2/DBoW2/FeatureVector.cpp:28-45), candidates are the
+ * still unmatched valid B features of the same node.  matches12[p*cap + i] = B index or -1 (for the frame
+ * form vpMapPointMatches[matches12[i]] = vpMapPointsKF[i]); th is 0..255 (TH_LOW = 50), cap <= 4096. */
+orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, const uint8_t* validA, const int* nodeA,
+                                     const int* nA, const uint8_t* descB, const float* angB, const uint8_t* validB,
+                                     const int* nodeB, const int* nB, int n_pairs, int cap, int th, float nnratio,
+                                     int check_orientation, int strict_lt, int* matches12, int* n_matches,
+                                     int on_device, void* stream);
+
 /* ---- Frame construction after extraction --------------------------------- */
 
 /* mK and mDistCoef of a Frame: fx, fy, cx, cy and OpenCV's k1, k2, p1, p2, k3 (src/Tracking.cc:57-87). */

@@ -68,6 +68,12 @@ int orbo_knn_ratio(const uint8_t* dA, const float* angA, int nA, const uint8_t* 
   return knn_ratio_bucket(dA, angA, nA, dB, angB, nB, th, ratio, checkOri != 0, strict != 0, m12);
 }
 
+int orbo_search_by_bow(const uint8_t* dA, const float* angA, const uint8_t* validA, const int* nodeA, int nA, const uint8_t* dB,
+                       const float* angB, const uint8_t* validB, const int* nodeB, int nB, int th, float ratio, int checkOri,
+                       int strict, int* m12) {
+  return search_by_bow(dA, angA, validA, nodeA, nA, dB, angB, validB, nodeB, nB, th, ratio, checkOri != 0, strict != 0, m12);
+}
+
 int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,
                             const uint8_t* inView, const float* projX, const float* projY, const float* projXR, const int* level,
                             const float* viewCos, const uint8_t* mpDesc, const int* mpObs, int m, float th, float nnratio,

@@ -747,4 +747,65 @@ inline int knn_ratio_bucket(const uint8_t* dA, const float* angA, int nA, const 
   return nm;
 }
 
+// ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ...) (src/ORBmatcher.cc:522-655, strict = true: bestDist1 < TH_LOW)
+// and SearchByBoW(KeyFrame*, Frame&, ...) (src/ORBmatcher.cc:159-288, strict = false: bestDist1 <= TH_LOW) on flat
+// arrays.  The DBoW2::FeatureVector of each side is given as the vocabulary node id of every feature
+// (nodeA/nodeB; std::map iteration = ascending node id, the index list of a node is in ascending feature index,
+// Thirdparty/DBoW2/DBoW2/FeatureVector.cpp:28-45).  validA = pMP1 && !pMP1->isBad(); validB = pMP2 && !isBad() for
+// the keyframe form, all ones for the frame form.  m12[i] = matched B index or -1.
+inline int search_by_bow(const uint8_t* dA, const float* angA, const uint8_t* validA, const int* nodeA, int nA,
+                         const uint8_t* dB, const float* angB, const uint8_t* validB, const int* nodeB, int nB, int th,
+                         float ratio, bool checkOri, bool strict, int* m12) {
+  std::vector<std::pair<int, std::vector<int>>> fa, fb;                 // FeatureVector: (node, indices) ascending
+  auto build = [](const int* node, int n, std::vector<std::pair<int, std::vector<int>>>& f) {
+    std::vector<std::pair<int, int>> o(n);
+    for (int i = 0; i < n; ++i) o[i] = {node[i], i};
+    std::sort(o.begin(), o.end());
+    for (auto& e : o) {
+      if (f.empty() || f.back().first != e.first) f.push_back({e.first, {}});
+      f.back().second.push_back(e.second);
+    }
+  };
+  build(nodeA, nA, fa); build(nodeB, nB, fb);
+  for (int i = 0; i < nA; ++i) m12[i] = -1;
+  std::vector<char> used(nB, 0);
+  std::vector<int> hist[kHisto];
+  int nm = 0;
+  size_t ia = 0, ib = 0;
+  while (ia < fa.size() && ib < fb.size()) {
+    if (fa[ia].first == fb[ib].first) {
+      for (int i : fa[ia].second) {
+        if (!validA[i]) continue;
+        int b1 = 256, b2 = 256, bi = -1;
+        for (int j : fb[ib].second) {
+          if (used[j] || !validB[j]) continue;
+          const int d = hamming256(dA + 32 * (size_t)i, dB + 32 * (size_t)j);
+          if (d < b1) { b2 = b1; b1 = d; bi = j; }
+          else if (d < b2) b2 = d;
+        }
+        const bool pass = strict ? (b1 < th) : (b1 <= th);
+        if (pass && (float)b1 < ratio * (float)b2) {
+          m12[i] = bi; used[bi] = 1;
+          if (checkOri) hist[rot_bin(angA[i], angB[bi])].push_back(i);
+          ++nm;
+        }
+      }
+      ++ia; ++ib;
+    } else if (fa[ia].first < fb[ib].first) {
+      while (ia < fa.size() && fa[ia].first < fb[ib].first) ++ia;     // lower_bound
+    } else {
+      while (ib < fb.size() && fb[ib].first < fa[ia].first) ++ib;
+    }
+  }
+  if (checkOri) {
+    int a = -1, b = -1, c = -1;
+    three_maxima(hist, kHisto, a, b, c);
+    for (int i = 0; i < kHisto; ++i) {
+      if (i == a || i == b || i == c) continue;
+      for (int idx : hist[i]) { m12[idx] = -1; --nm; }
+    }
+  }
+  return nm;
+}
+
 }  // namespace orbo

@@ -113,6 +113,18 @@ def knn_ratio(dA, angA, dB, angB, th=50, ratio=0.75, check_ori=True, strict=True
     return m12, n
 
 
+def search_by_bow(dA, angA, validA, nodeA, dB, angB, validB, nodeB, th=50, ratio=0.75, check_ori=True, strict=True):
+    """ORBmatcher::SearchByBoW (KF,KF: strict=True; KF,Frame: strict=False) with per-feature vocabulary node ids."""
+    dA = np.ascontiguousarray(dA); dB = np.ascontiguousarray(dB)
+    angA = np.ascontiguousarray(angA, np.float32); angB = np.ascontiguousarray(angB, np.float32)
+    validA = np.ascontiguousarray(validA, np.uint8); validB = np.ascontiguousarray(validB, np.uint8)
+    nodeA = np.ascontiguousarray(nodeA, np.int32); nodeB = np.ascontiguousarray(nodeB, np.int32)
+    m12 = np.zeros(max(len(dA), 1), np.int32)
+    n = lib().orbo_search_by_bow(_p(dA), _p(angA), _p(validA), _p(nodeA), len(dA), _p(dB), _p(angB), _p(validB), _p(nodeB), len(dB),
+                                 th, C.c_float(ratio), int(check_ori), int(strict), _p(m12))
+    return m12[:len(dA)], n
+
+
 def _cam(cam):
     """cam: (fx, fy, cx, cy, k1, k2, p1, p2, k3) -> float32[9]"""
     c = np.zeros(9, np.float32); c[:len(cam)] = np.asarray(cam, np.float32)

@@ -94,6 +94,7 @@ def lib():
                                                    [C.c_int, C.c_float, C.c_float] + [C.c_void_p] * 3 + [C.c_int, C.c_void_p])
         L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                              C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orbx_search_by_bow_batch.argtypes = [C.c_void_p] * 10 + [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_undistort_grid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
         L.orbx_features_in_area_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]
@@ -436,6 +437,26 @@ class ORBmatcher:
         th defaults to TH_LOW (src/ORBmatcher.cc:37,596)."""
         r = self.SearchByBoWBatch([(descA, angA)], [(descB, angB)], strict, th)
         return r[0][0], r[1][0]
+
+    def SearchByBoWNodes(self, sidesA, sidesB, strict=True, th=None):
+        """SearchByBoW with vocabulary buckets, batched.  Each side = (desc, angles, valid, node) per pair; strict=True is
+        the (KeyFrame, KeyFrame) form (src/ORBmatcher.cc:522), strict=False the (KeyFrame, Frame) form (:159).
+        Returns (nmatches per pair, matches12 per pair)."""
+        npairs = len(sidesA)
+        cap = max(max(len(a[0]) for a in sidesA), max(len(b[0]) for b in sidesB), 1)
+        def pack(sides):
+            d = np.zeros((npairs, cap, 32), np.uint8); ang = np.zeros((npairs, cap), np.float32)
+            val = np.zeros((npairs, cap), np.uint8); node = np.zeros((npairs, cap), np.int32); n = np.zeros(npairs, np.int32)
+            for p, (dd, aa, vv, nn) in enumerate(sides):
+                n[p] = len(dd); d[p, :n[p]] = dd; ang[p, :n[p]] = aa; val[p, :n[p]] = vv; node[p, :n[p]] = nn
+            return d, ang, val, node, n
+        dA, aA, vA, nodA, nA = pack(sidesA); dB, aB, vB, nodB, nB = pack(sidesB)
+        m12 = np.zeros((npairs, cap), np.int32); nm = np.zeros(npairs, np.int32)
+        _check(lib().orbx_search_by_bow_batch(dA.ctypes.data, aA.ctypes.data, vA.ctypes.data, nodA.ctypes.data, nA.ctypes.data,
+                                              dB.ctypes.data, aB.ctypes.data, vB.ctypes.data, nodB.ctypes.data, nB.ctypes.data,
+                                              npairs, cap, self.TH_LOW if th is None else int(th), self.mfNNratio,
+                                              int(self.mbCheckOrientation), int(strict), m12.ctypes.data, nm.ctypes.data, 0, None))
+        return [int(v) for v in nm], [m12[p, :nA[p]].copy() for p in range(npairs)]
 
     def SearchByBoWBatch(self, As, Bs, strict=True, th=None):
         npairs = len(As)

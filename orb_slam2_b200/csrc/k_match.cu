@@ -593,6 +593,153 @@ int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st) {
   return 1;
 }
 
+// ------------------------------------------------------------------------------------------
+// K12: ORBmatcher::SearchByBoW with real vocabulary buckets, both forms:
+//   (KeyFrame*, KeyFrame*)  src/ORBmatcher.cc:522-655   strict: bestDist1 <  TH_LOW, validB = pMP2 && !isBad()
+//   (KeyFrame*, Frame&)     src/ORBmatcher.cc:159-288           bestDist1 <= TH_LOW, validB = all
+// The FeatureVector of a side is given as one vocabulary node id per feature.  One CTA per pair:
+//   1. both sides are sorted by (node, feature index) with a block bitonic sort - that is the
+//      std::map / push_back order the reference iterates in - and the B descriptors are staged in
+//      shared memory (bit j of `used` starts as !validB[j], so invalid and matched features are
+//      skipped by the same test);
+//   2. warp 0 walks the A side in that order (hazard H6: vbMatched2 / vpMapPointMatches), its lanes
+//      scan the B run of the same node; the A descriptors are fetched four queries ahead.
+constexpr int kBowThreads = 128;
+
+__global__ void __launch_bounds__(kBowThreads) k_search_by_bow(BowArgs a, int capPad) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  unsigned long long* keyA = reinterpret_cast<unsigned long long*>(smem);          // [capPad] node<<32 | index, sorted
+  unsigned long long* keyB = keyA + capPad;                                         // [capPad]
+  uint32_t* Bs = reinterpret_cast<uint32_t*>(keyB + capPad);                        // [cap][8] B descriptors
+  uint32_t* used = Bs + (size_t)a.cap * 8;                                          // [(cap+31)/32]
+  __shared__ int s_hist[kHisto];
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+  const int nA = a.nA[p], nB = a.nB[p];
+  const size_t po = (size_t)p * a.cap;
+  const uint32_t* dA = reinterpret_cast<const uint32_t*>(a.dA + po * 32);
+  const uint32_t* dB = reinterpret_cast<const uint32_t*>(a.dB + po * 32);
+  const float* angA = a.angA + po;
+  const float* angB = a.angB + po;
+  int* m12 = a.m12 + po;
+
+  for (int i = tid; i < capPad; i += kBowThreads) {
+    keyA[i] = i < nA ? (((unsigned long long)(uint32_t)a.nodeA[po + i] << 32) | (unsigned)i) : ~0ull;
+    keyB[i] = i < nB ? (((unsigned long long)(uint32_t)a.nodeB[po + i] << 32) | (unsigned)i) : ~0ull;
+  }
+  for (int i = tid; i < nB * 8; i += kBowThreads) Bs[i] = __ldg(dB + i);
+  for (int w = tid; w < (a.cap + 31) / 32; w += kBowThreads) {
+    uint32_t bits = 0u;
+    for (int b = 0; b < 32; ++b) { const int j = w * 32 + b; if (j < nB && !a.validB[po + j]) bits |= 1u << b; }
+    used[w] = bits;
+  }
+  for (int i = tid; i < nA; i += kBowThreads) m12[i] = -1;
+  if (tid < kHisto) s_hist[tid] = 0;
+  __syncthreads();
+  for (int k = 2; k <= capPad; k <<= 1)                                             // bitonic sort, both arrays together
+    for (int jj = k >> 1; jj > 0; jj >>= 1) {
+      for (int i = tid; i < capPad; i += kBowThreads) {
+        const int l = i ^ jj;
+        if (l > i) {
+          const bool up = (i & k) == 0;
+          unsigned long long x = keyA[i], y = keyA[l];
+          if ((x > y) == up) { keyA[i] = y; keyA[l] = x; }
+          x = keyB[i]; y = keyB[l];
+          if ((x > y) == up) { keyB[i] = y; keyB[l] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  if (tid >= 32) return;
+
+  int nm = 0, b0 = 0, b1 = 0;
+  uint32_t cur_node = 0xffffffffu;
+  bool have_node = false;
+  // A descriptors four queries ahead: lane l holds word (l & 7) of query t + (l >> 3)
+  auto fetch = [&](int t) -> uint32_t {
+    const int tt = t + (lane >> 3);
+    return tt < nA ? __ldg(dA + (size_t)(uint32_t)(keyA[tt] & 0xffffffffu) * 8 + (lane & 7)) : 0u;
+  };
+  uint32_t qw = fetch(0);
+  for (int t0 = 0; t0 < nA; t0 += 4) {
+    const uint32_t qcur = qw;
+    qw = fetch(t0 + 4);
+    for (int s = 0; s < 4 && t0 + s < nA; ++s) {
+      const unsigned long long ka = keyA[t0 + s];
+      const uint32_t node = (uint32_t)(ka >> 32);
+      const int i = (int)(ka & 0xffffffffu);
+      if (!have_node || node != cur_node) {                    // B run of this node: [b0, b1) (the lower_bound steps)
+        have_node = true; cur_node = node;
+        b0 = b1;
+        while (true) {
+          const int e = b0 + lane;
+          const int c = __popc(__ballot_sync(0xffffffffu, e < nB && (uint32_t)(keyB[e] >> 32) < node));
+          b0 += c;
+          if (c < 32) break;
+        }
+        b1 = b0;
+        while (true) {
+          const int e = b1 + lane;
+          const int c = __popc(__ballot_sync(0xffffffffu, e < nB && (uint32_t)(keyB[e] >> 32) == node));
+          b1 += c;
+          if (c < 32) break;
+        }
+      }
+      if (!a.validA[po + i] || b0 == b1) continue;              // warp-uniform
+      uint32_t q[8];
+#pragma unroll
+      for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, qcur, s * 8 + w);
+      unsigned k1 = 256u << 16;
+      int k2 = 256;
+      for (int e = b0 + lane; e < b1; e += 32) {
+        const int j = (int)(keyB[e] & 0xffffffffu);
+        if ((used[j >> 5] >> (j & 31)) & 1u) continue;
+        const int d = ham8(q, Bs + (size_t)j * 8);
+        const unsigned kk = ((unsigned)d << 16) | (unsigned)j;
+        if (d < (int)(k1 >> 16)) { k2 = (int)(k1 >> 16); k1 = kk; }
+        else if (d < k2) k2 = d;
+      }
+      const unsigned wmin = __reduce_min_sync(0xffffffffu, k1);
+      const int sec = (int)__reduce_min_sync(0xffffffffu, (unsigned)(k1 == wmin ? k2 : (int)(k1 >> 16)));
+      const int best = (int)(wmin >> 16), bi = (int)(wmin & 0xffffu);
+      const bool pass = (a.strict ? best < a.th : best <= a.th) && (float)best < __fmul_rn(a.ratio, (float)sec);
+      if (pass) {
+        if (lane == 0) { m12[i] = bi; used[bi >> 5] |= 1u << (bi & 31); }
+        ++nm;
+        __syncwarp();
+      }
+    }
+  }
+  __syncwarp();
+  if (a.checkOri) {
+    for (int i = lane; i < nA; i += 32) {
+      const int m = m12[i];
+      if (m >= 0) atomicAdd(&s_hist[rot_bin(angA[i], angB[m])], 1);
+    }
+    __syncwarp();
+    int k_a, k_b, k_c;
+    three_maxima(s_hist, k_a, k_b, k_c);
+    int drop = 0;
+    for (int i = lane; i < nA; i += 32) {
+      const int m = m12[i];
+      if (m >= 0) {
+        const int b = rot_bin(angA[i], angB[m]);
+        if (b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
+      }
+    }
+    nm -= __reduce_add_sync(0xffffffffu, drop);
+  }
+  if (lane == 0) a.nm[p] = nm;
+}
+
+int launch_search_by_bow(const BowArgs& a, cudaStream_t st) {
+  int capPad = 32;
+  while (capPad < a.cap) capPad <<= 1;
+  const size_t smem = (size_t)capPad * 16 + (size_t)a.cap * 32 + (size_t)((a.cap + 31) / 32) * 4;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_by_bow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_search_by_bow<<<a.n_pairs, kBowThreads, smem, st>>>(a, capPad);
+  return 1;
+}
+
 int launch_search_init(const InitMatchArgs& a, cudaStream_t st) {
   k_search_init<<<a.n_pairs, 32, 0, st>>>(a);
   return 1;

@@ -664,6 +664,35 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
   return ORBX_OK;
 }
 
+orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, const uint8_t* validA, const int* nodeA, const int* nA,
+                                     const uint8_t* descB, const float* angB, const uint8_t* validB, const int* nodeB, const int* nB,
+                                     int n_pairs, int cap, int th, float nnratio, int check_orientation, int strict_lt, int* matches12,
+                                     int* n_matches, int on_device, void* stream) {
+  if (!descA || !angA || !validA || !nodeA || !nA || !descB || !angB || !validB || !nodeB || !nB || !matches12 || !n_matches)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_pairs < 1 || cap < 1 || cap > 4096) return fail(ORBX_ERR_BAD_ARG, "cap must be 1..4096 (both sort arrays and the B descriptors are held in shared memory)");
+  if (th < 0 || th > 255) return fail(ORBX_ERR_BAD_ARG, "th must be 0..255");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_pairs, pc = np * cap;
+  BowArgs a;
+  CU(sg.in(descA, pc * 32, on_device, &a.dA)); CU(sg.in(angA, pc, on_device, &a.angA)); CU(sg.in(validA, pc, on_device, &a.validA));
+  CU(sg.in(nodeA, pc, on_device, &a.nodeA)); CU(sg.in(nA, np, on_device, &a.nA));
+  CU(sg.in(descB, pc * 32, on_device, &a.dB)); CU(sg.in(angB, pc, on_device, &a.angB)); CU(sg.in(validB, pc, on_device, &a.validB));
+  CU(sg.in(nodeB, pc, on_device, &a.nodeB)); CU(sg.in(nB, np, on_device, &a.nB));
+  if (on_device) { a.m12 = matches12; a.nm = n_matches; }
+  else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
+  a.n_pairs = n_pairs; a.cap = cap; a.th = th; a.ratio = nnratio; a.checkOri = check_orientation; a.strict = strict_lt;
+  g_launches += launch_search_by_bow(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
 orbx_status orbx_undistort_grid_batch(const orbx_keypoint* kps, const int* n, int n_frames, int cap, const orbx_camera* camera,
                                       int cols, int rows, orbx_keypoint* kps_un, float* bounds, int* cell_start, int* cell_items,
                                       int on_device, void* stream) {

@@ -137,6 +137,14 @@ struct ProjFrameArgs {
 };
 int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st);
 
+struct BowArgs {
+  const uint8_t* dA; const float* angA; const uint8_t* validA; const int* nodeA; const int* nA;
+  const uint8_t* dB; const float* angB; const uint8_t* validB; const int* nodeB; const int* nB;
+  int n_pairs, cap, th; float ratio; int checkOri, strict;
+  int* m12; int* nm;
+};
+int launch_search_by_bow(const BowArgs& a, cudaStream_t st);
+
 struct FrameGridArgs {
   const orbx_keypoint* k; const int* n; int n_frames, cap, cols, rows;
   orbx_camera cam;

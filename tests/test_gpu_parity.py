@@ -502,3 +502,42 @@ def test_undistort_grid_and_features_in_area(gx, oracle, cam, w, h):
     # truncation: count is still the full count, the first qcap indices are written
     got2, cnt2 = FG.GetFeaturesInArea(queries[-1:], qcap=10)
     assert cnt2[0] == len(kls[0]) and np.array_equal(got2[0], got[-1][:10])
+
+
+def _vocab_nodes(desc, words):
+    """A stand-in vocabulary: node = nearest of `words` in Hamming distance (ties -> lowest id), ids spread out."""
+    x = np.unpackbits(desc, axis=1).astype(np.int16); wv = np.unpackbits(words, axis=1).astype(np.int16)
+    d = (x[:, None, :] != wv[None, :, :]).sum(-1)
+    return (d.argmin(1) * 37 + 5).astype(np.int32)
+
+
+@pytest.mark.parametrize("strict,ratio,ori", [(True, 0.75, True), (False, 0.7, True), (False, 0.9, False)])
+def test_search_by_bow_with_vocabulary_buckets(gx, oracle, strict, ratio, ori):
+    """K12: SearchByBoW(KF,KF) / (KF,Frame) over per-node buckets, in the reference's node / index
+    order, with invalid map points on both sides, nodes present on one side only, ragged pairs and an empty side."""
+    w, h, nf = 1241, 376, 2000
+    G = _ext(gx, w, h, nf)
+    rng = np.random.default_rng(99)
+    words = rng.integers(0, 256, (96, 32), dtype=np.uint8)
+    sidesA, sidesB, refs = [], [], []
+    for p in range(3):
+        a, b, _ = synth.mono_pair(170 + p, w, h)
+        k1, d1 = G(a); k2, d2 = G(b)
+        if p == 1: k2, d2 = k2[:700], d2[:700]
+        if p == 2: words[:, :] = rng.integers(0, 256, (96, 32), dtype=np.uint8); words = words[:7]   # few, crowded nodes
+        n1, n2 = _vocab_nodes(d1, words), _vocab_nodes(d2, words)
+        n2[n2 == n2.max()] = 10 ** 6                        # a node the A side does not have
+        v1 = (rng.random(len(d1)) < 0.8).astype(np.uint8)
+        v2 = np.ones(len(d2), np.uint8) if not strict else (rng.random(len(d2)) < 0.85).astype(np.uint8)
+        sidesA.append((d1, k1["angle"], v1, n1)); sidesB.append((d2, k2["angle"], v2, n2))
+        refs.append(oracle.search_by_bow(d1, k1["angle"], v1, n1, d2, k2["angle"], v2, n2, 50, ratio, ori, strict))
+    sidesA.append((sidesA[0][0][:5], sidesA[0][1][:5], sidesA[0][2][:5], sidesA[0][3][:5]))
+    sidesB.append((sidesB[0][0][:0], sidesB[0][1][:0], sidesB[0][2][:0], sidesB[0][3][:0]))
+    refs.append((np.full(5, -1, np.int32), 0))
+    nm, m12 = gx.ORBmatcher(ratio, ori).SearchByBoWNodes(sidesA, sidesB, strict=strict)
+    for p in range(4):
+        assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), (p, nm[p], refs[p][1])
+    assert refs[0][1] > 50 and refs[2][1] > 50
+    # matches never cross nodes and never use an invalid feature
+    m = m12[0]; ok = m >= 0
+    assert np.array_equal(sidesA[0][3][ok], sidesB[0][3][m[ok]]) and sidesA[0][2][ok].all() and sidesB[0][2][m[ok]].all()
