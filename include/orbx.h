@@ -210,6 +210,15 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
                                      int check_orientation, int strict_lt, int* matches12, int* n_matches,
                                      int on_device, void* stream);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305) for n_points map points.  Map point m:
+ * counts[m] observed descriptors (those of the keyframes that are not bad, in mObservations order) at
+ * desc + m*kcap*32.  best_idx[m] receives the index of the descriptor with the least median Hamming distance
+ * to all of them (the reference's sorted-row element [0.5*(N-1)], first index on ties; -1 when counts[m] == 0,
+ * where the reference leaves mDescriptor alone); best_desc, if not NULL, receives that descriptor (32 bytes per
+ * map point, untouched when counts[m] == 0).  kcap <= 1024. */
+orbx_status orbx_distinctive_descriptors_batch(const uint8_t* desc, const int* counts, int n_points, int kcap,
+                                               int* best_idx, uint8_t* best_desc, int on_device, void* stream);
+
 /* ---- Frame construction after extraction --------------------------------- */
 
 /* mK and mDistCoef of a Frame: fx, fy, cx, cy and OpenCV's k1, k2, p1, p2, k3 (src/Tracking.cc:57-87). */

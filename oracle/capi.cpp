@@ -74,6 +74,8 @@ int orbo_search_by_bow(const uint8_t* dA, const float* angA, const uint8_t* vali
   return search_by_bow(dA, angA, validA, nodeA, nA, dB, angB, validB, nodeB, nB, th, ratio, checkOri != 0, strict != 0, m12);
 }
 
+int orbo_distinctive_descriptor(const uint8_t* d, int n) { return distinctive_descriptor(d, n); }
+
 int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,
                             const uint8_t* inView, const float* projX, const float* projY, const float* projXR, const int* level,
                             const float* viewCos, const uint8_t* mpDesc, const int* mpObs, int m, float th, float nnratio,

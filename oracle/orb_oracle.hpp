@@ -808,4 +808,19 @@ inline int search_by_bow(const uint8_t* dA, const float* angA, const uint8_t* va
   return nm;
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305): among the N observed descriptors, the one
+// whose median distance to all of them (itself included, sorted row element [0.5*(N-1)]) is least; first on ties.
+inline int distinctive_descriptor(const uint8_t* d, int N) {
+  if (N <= 0) return -1;
+  int bestMedian = INT_MAX, bestIdx = 0;
+  std::vector<int> row(N);
+  for (int i = 0; i < N; ++i) {
+    for (int j = 0; j < N; ++j) row[j] = i == j ? 0 : hamming256(d + 32 * (size_t)i, d + 32 * (size_t)j);
+    std::sort(row.begin(), row.end());
+    const int median = row[(int)(0.5 * (N - 1))];
+    if (median < bestMedian) { bestMedian = median; bestIdx = i; }
+  }
+  return bestIdx;
+}
+
 }  // namespace orbo

@@ -125,6 +125,12 @@ def search_by_bow(dA, angA, validA, nodeA, dB, angB, validB, nodeB, th=50, ratio
     return m12[:len(dA)], n
 
 
+def distinctive_descriptor(desc):
+    """MapPoint::ComputeDistinctiveDescriptors: index of the descriptor with the least median distance."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    return int(lib().orbo_distinctive_descriptor(_p(desc), len(desc)))
+
+
 def _cam(cam):
     """cam: (fx, fy, cx, cy, k1, k2, p1, p2, k3) -> float32[9]"""
     c = np.zeros(9, np.float32); c[:len(cam)] = np.asarray(cam, np.float32)

@@ -95,6 +95,7 @@ def lib():
         L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                              C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_search_by_bow_batch.argtypes = [C.c_void_p] * 10 + [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_distinctive_descriptors_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_undistort_grid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
         L.orbx_features_in_area_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]
@@ -297,6 +298,19 @@ class Frame:
 
     def __init__(self, keypoints, descriptors, cols, rows):
         self.mvKeysUn, self.mDescriptors, self.cols, self.rows = keypoints, descriptors, cols, rows
+
+
+def ComputeDistinctiveDescriptors(descriptor_lists):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305) for a batch of map points: descriptor_lists[m] is
+    the (N_m, 32) uint8 array of map point m's observed descriptors.  Returns (best index per map point, (M, 32) descriptors)."""
+    m = len(descriptor_lists)
+    kcap = max(max((len(d) for d in descriptor_lists), default=1), 1)
+    desc = np.zeros((m, kcap, 32), np.uint8); counts = np.zeros(m, np.int32)
+    for i, d in enumerate(descriptor_lists):
+        counts[i] = len(d); desc[i, :len(d)] = d
+    best = np.zeros(m, np.int32); out = np.zeros((m, 32), np.uint8)
+    _check(lib().orbx_distinctive_descriptors_batch(desc.ctypes.data, counts.ctypes.data, m, kcap, best.ctypes.data, out.ctypes.data, 0, None))
+    return best, out
 
 
 class _Camera(C.Structure):

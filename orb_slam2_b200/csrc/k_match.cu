@@ -740,6 +740,60 @@ int launch_search_by_bow(const BowArgs& a, cudaStream_t st) {
   return 1;
 }
 
+// ------------------------------------------------------------------------------------------
+// K13: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305), batched over map points
+// (SURVEY.md 8f rank 3).  One warp per map point: its N observed descriptors sit in shared memory; for
+// every row i the lanes take the columns j, the 257-bin histogram of the row gives the element
+// [(N-1)/2] of the sorted row without sorting; the least median wins, first index on ties.
+constexpr int kDistWarps = 4;
+
+__global__ void __launch_bounds__(kDistWarps * 32) k_distinctive(DistinctArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mp = blockIdx.x * kDistWarps + warp;
+  if (mp >= a.n_points) return;
+  uint32_t* D = reinterpret_cast<uint32_t*>(smem) + (size_t)warp * (a.kcap * 8 + 288);   // [kcap][8]
+  int* hist = reinterpret_cast<int*>(D + (size_t)a.kcap * 8);                             // [288] (257 used)
+  const int N = min(a.counts[mp], a.kcap);
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(a.desc + (size_t)mp * a.kcap * 32);
+  for (int i = lane; i < N * 8; i += 32) D[i] = __ldg(src + i);
+  __syncwarp();
+  int bestMedian = INT_MAX, bestIdx = N > 0 ? 0 : -1;
+  const int rank = (N - 1) / 2;                                  // (int)(0.5 * (N - 1))
+  for (int i = 0; i < N; ++i) {
+    for (int b = lane; b < 288; b += 32) hist[b] = 0;
+    __syncwarp();
+    uint32_t q[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) q[w] = D[i * 8 + w];
+    for (int j = lane; j < N; j += 32) atomicAdd(&hist[ham8(q, D + (size_t)j * 8)], 1);   // d(i,i) = 0 as in the reference
+    __syncwarp();
+    int run = 0, median = 256;
+    for (int c = 0; c < 9; ++c) {
+      int v = hist[c * 32 + lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+      }
+      const uint32_t hit = __ballot_sync(0xffffffffu, run + v >= rank + 1);
+      if (hit) { median = c * 32 + __ffs((int)hit) - 1; break; }
+      run += __shfl_sync(0xffffffffu, v, 31);
+    }
+    if (median < bestMedian) { bestMedian = median; bestIdx = i; }
+    __syncwarp();
+  }
+  if (lane == 0) a.best_idx[mp] = bestIdx;
+  if (a.best_desc && bestIdx >= 0 && lane < 8) reinterpret_cast<uint32_t*>(a.best_desc + (size_t)mp * 32)[lane] = D[bestIdx * 8 + lane];
+}
+
+int launch_distinctive(const DistinctArgs& a, cudaStream_t st) {
+  const size_t smem = (size_t)kDistWarps * ((size_t)a.kcap * 8 + 288) * 4;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_distinctive, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_distinctive<<<(a.n_points + kDistWarps - 1) / kDistWarps, kDistWarps * 32, smem, st>>>(a);
+  return 1;
+}
+
 int launch_search_init(const InitMatchArgs& a, cudaStream_t st) {
   k_search_init<<<a.n_pairs, 32, 0, st>>>(a);
   return 1;

@@ -693,6 +693,32 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
   return ORBX_OK;
 }
 
+orbx_status orbx_distinctive_descriptors_batch(const uint8_t* desc, const int* counts, int n_points, int kcap, int* best_idx,
+                                               uint8_t* best_desc, int on_device, void* stream) {
+  if (!desc || !counts || !best_idx) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_points < 1 || kcap < 1 || kcap > 1024) return fail(ORBX_ERR_BAD_ARG, "kcap must be 1..1024 (a map point's descriptors are held in shared memory)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_points;
+  DistinctArgs a;
+  CU(sg.in(desc, np * kcap * 32, on_device, &a.desc)); CU(sg.in(counts, np, on_device, &a.counts));
+  a.best_desc = nullptr;
+  if (on_device) { a.best_idx = best_idx; a.best_desc = best_desc; }
+  else {
+    CU(sg.alloc((void**)&a.best_idx, np * 4));
+    if (best_desc) { CU(sg.alloc((void**)&a.best_desc, np * 32)); CU(cudaMemcpyAsync(a.best_desc, best_desc, np * 32, cudaMemcpyHostToDevice, st)); }
+  }
+  a.n_points = n_points; a.kcap = kcap;
+  g_launches += launch_distinctive(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(best_idx, a.best_idx, np * 4, cudaMemcpyDeviceToHost, st));
+    if (best_desc) CU(cudaMemcpyAsync(best_desc, a.best_desc, np * 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
 orbx_status orbx_undistort_grid_batch(const orbx_keypoint* kps, const int* n, int n_frames, int cap, const orbx_camera* camera,
                                       int cols, int rows, orbx_keypoint* kps_un, float* bounds, int* cell_start, int* cell_items,
                                       int on_device, void* stream) {

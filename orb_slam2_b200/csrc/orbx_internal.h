@@ -145,6 +145,12 @@ struct BowArgs {
 };
 int launch_search_by_bow(const BowArgs& a, cudaStream_t st);
 
+struct DistinctArgs {
+  const uint8_t* desc; const int* counts; int n_points, kcap;
+  int* best_idx; uint8_t* best_desc;
+};
+int launch_distinctive(const DistinctArgs& a, cudaStream_t st);
+
 struct FrameGridArgs {
   const orbx_keypoint* k; const int* n; int n_frames, cap, cols, rows;
   orbx_camera cam;

@@ -541,3 +541,24 @@ def test_search_by_bow_with_vocabulary_buckets(gx, oracle, strict, ratio, ori):
     # matches never cross nodes and never use an invalid feature
     m = m12[0]; ok = m >= 0
     assert np.array_equal(sidesA[0][3][ok], sidesB[0][3][m[ok]]) and sidesA[0][2][ok].all() and sidesB[0][2][m[ok]].all()
+
+
+def test_distinctive_descriptors(gx, oracle):
+    """K13 (SURVEY 8f rank 3): MapPoint::ComputeDistinctiveDescriptors, median by histogram vs the reference's sort.
+    Clusters of noisy copies of a descriptor with 1..200 observations, exact duplicates (ties -> first), empty lists."""
+    rng = np.random.default_rng(21)
+    lists = []
+    for n in [1, 2, 3, 4, 5, 8, 31, 32, 33, 64, 100, 200] + list(rng.integers(2, 60, 40)):
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        noise = np.packbits(rng.random((n, 256)) < rng.uniform(0.02, 0.25), axis=1)
+        lists.append(base[None, :] ^ noise)
+    lists.append(np.repeat(rng.integers(0, 256, (1, 32), dtype=np.uint8), 7, 0))     # all equal: index 0
+    lists.append(np.zeros((0, 32), np.uint8))                                          # no observation
+    lists.append(rng.integers(0, 256, (50, 32), dtype=np.uint8))                       # unrelated descriptors
+    best, out = gx.ComputeDistinctiveDescriptors(lists)
+    for m, d in enumerate(lists):
+        want = oracle.distinctive_descriptor(d)
+        assert best[m] == want, (m, len(d), best[m], want)
+        if want >= 0:
+            assert np.array_equal(out[m], d[want])
+    assert best[-2] == -1 and best[-3] == 0
