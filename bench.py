@@ -313,6 +313,25 @@ def secondary_workloads(gx, torch, local):
     return out
 
 
+def bind_near_gpu(torch, local):
+    """Pins this rank's threads to the CPU cores NVML reports as local to its GPU, so that the pinned host
+    buffers of the end-to-end leg are allocated (first touched) on the GPU's own NUMA node.  Best effort."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(local).uuid)
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        before = len(os.sched_getaffinity(0))
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        after = len(os.sched_getaffinity(0))
+        return f"nvml gpu-local cpus: {after} of {before}"
+    except Exception as exc:
+        return f"unchanged ({type(exc).__name__})"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -336,6 +355,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the CUDA path has no CPU fallback")
     torch.cuda.set_device(local)
+    all_cpus = os.sched_getaffinity(0)
+    affinity = bind_near_gpu(torch, local)      # before any pinned allocation: first touch decides the NUMA node
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -441,7 +462,7 @@ def main():
                        "l2": f"inputs rotate over {NSETS} sets of {2 * B * w * h / 1e6:.0f} MB (> {L2_MB} MB L2 in total); per-step intermediates {2 * B * 1.8:.0f} MB",
                        "bf": bf, "fx": fx},
             "e2e": {"value": e2e_val, "unit": "stereo frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "pipeline": "2 handles x 2 streams, pinned host buffers"},
+                    "ms_per_step": ms_e2e / args.steps, "pipeline": "2 handles x 2 streams, pinned host buffers", "cpu_affinity": affinity},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -457,6 +478,7 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             from oracle import pyoracle as O
             O.build()
+            os.sched_setaffinity(0, all_cpus)               # the CPU leg gets every core again
             threads = O.hardware_threads()
             nfr = 16 * threads                              # ~10-30 s of CPU work
             v, secs, _, _ = cpu_baseline(nfr, threads)
