@@ -210,6 +210,24 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
                                      int check_orientation, int strict_lt, int* matches12, int* n_matches,
                                      int on_device, void* stream);
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:657-823, with
+ * CheckDistEpipolarLine :140-157; called from src/LocalMapping.cc:296) for n_pairs independent keyframe pairs.
+ * Side 1 of pair p at index p*cap: kps1 = mvKeysUn, desc1, has_mp1[i] = (GetMapPoint(i) != NULL), u_right1 = mvuRight,
+ * node1 = FeatureVector node per feature (as in orbx_search_by_bow_batch); side 2 likewise.  F12 + p*9 = the
+ * fundamental matrix row-major; pose2 + p*12 = KF2's Rcw row-major then tcw; Cw + p*3 = KF1's camera centre;
+ * cam2 + p*4 = fx, fy, cx, cy of KF2 (the epipole of :664-670 is computed from these);
+ * scale_factors2 / level_sigma2_2 = KF2's mvScaleFactors / mvLevelSigma2 (nlevels entries).
+ * matches12[p*cap + i] receives vMatches12[i] (the KF2 index or -1; vMatchedPairs is the list of (i, matches12[i])
+ * with matches12[i] >= 0 in index order), n_matches[p] the return value.  cap <= 4096. */
+orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const uint8_t* has_mp1,
+                                            const float* u_right1, const int* node1, const int* n1,
+                                            const orbx_keypoint* kps2, const uint8_t* desc2, const uint8_t* has_mp2,
+                                            const float* u_right2, const int* node2, const int* n2, int n_pairs, int cap,
+                                            const float* F12, const float* pose2, const float* Cw, const float* cam2,
+                                            const float* scale_factors2, const float* level_sigma2_2, int nlevels,
+                                            int only_stereo, int check_orientation, int* matches12, int* n_matches,
+                                            int on_device, void* stream);
+
 /* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305) for n_points map points.  Map point m:
  * counts[m] observed descriptors (those of the keyframes that are not bad, in mObservations order) at
  * desc + m*kcap*32.  best_idx[m] receives the index of the descriptor with the least median Hamming distance

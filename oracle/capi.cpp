@@ -74,6 +74,14 @@ int orbo_search_by_bow(const uint8_t* dA, const float* angA, const uint8_t* vali
   return search_by_bow(dA, angA, validA, nodeA, nA, dB, angB, validB, nodeB, nB, th, ratio, checkOri != 0, strict != 0, m12);
 }
 
+int orbo_search_for_triangulation(const KeyPt* k1, const uint8_t* d1, const uint8_t* hasMp1, const float* uR1, const int* node1, int n1,
+                                  const KeyPt* k2, const uint8_t* d2, const uint8_t* hasMp2, const float* uR2, const int* node2, int n2,
+                                  const float* F12, const float* pose2, const float* Cw, const float* cam2, const float* scale2,
+                                  const float* sigma2_2, int onlyStereo, int checkOri, int* m12) {
+  return search_for_triangulation(k1, d1, hasMp1, uR1, node1, n1, k2, d2, hasMp2, uR2, node2, n2, F12, pose2, Cw, cam2, scale2, sigma2_2,
+                                  onlyStereo != 0, checkOri != 0, m12);
+}
+
 int orbo_distinctive_descriptor(const uint8_t* d, int n) { return distinctive_descriptor(d, n); }
 
 int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,

@@ -808,6 +808,86 @@ inline int search_by_bow(const uint8_t* dA, const float* angA, const uint8_t* va
   return nm;
 }
 
+// ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-823) + CheckDistEpipolarLine (:140-157) on flat arrays.
+// hasMp = GetMapPoint(idx) != NULL, uRight = mvuRight, node = FeatureVector node per feature (as in search_by_bow).
+// pose2 = R2w row-major (9) then t2w (3), Cw = camera centre of KF1; cam2 = fx, fy, cx, cy of KF2.  The epipole uses
+// OpenCV's small-matrix gemm arithmetic for R2w*Cw+t2w (float products and sums left to right).  Note that the
+// reference never sets vbMatched2 (:686, :723): several features of KF1 may take the same feature of KF2, and the
+// queries are independent.  m12[i] = matched KF2 index or -1; the caller lists the pairs in index order (:812-818).
+inline int search_for_triangulation(const KeyPt* k1, const uint8_t* d1, const uint8_t* hasMp1, const float* uR1, const int* node1,
+                                    int n1, const KeyPt* k2, const uint8_t* d2, const uint8_t* hasMp2, const float* uR2,
+                                    const int* node2, int n2, const float* F12, const float* pose2, const float* Cw,
+                                    const float* cam2, const float* scale2, const float* sigma2_2, bool onlyStereo,
+                                    bool checkOri, int* m12) {
+  float C2[3];
+  for (int r = 0; r < 3; ++r) C2[r] = ((pose2[3 * r] * Cw[0] + pose2[3 * r + 1] * Cw[1]) + pose2[3 * r + 2] * Cw[2]) + pose2[9 + r];
+  const float invz = 1.0f / C2[2];
+  const float ex = cam2[0] * C2[0] * invz + cam2[2], ey = cam2[1] * C2[1] * invz + cam2[3];
+  std::vector<std::pair<int, std::vector<int>>> fa, fb;
+  auto build = [](const int* node, int n, std::vector<std::pair<int, std::vector<int>>>& f) {
+    std::vector<std::pair<int, int>> o(n);
+    for (int i = 0; i < n; ++i) o[i] = {node[i], i};
+    std::sort(o.begin(), o.end());
+    for (auto& e : o) {
+      if (f.empty() || f.back().first != e.first) f.push_back({e.first, {}});
+      f.back().second.push_back(e.second);
+    }
+  };
+  build(node1, n1, fa); build(node2, n2, fb);
+  for (int i = 0; i < n1; ++i) m12[i] = -1;
+  std::vector<int> hist[kHisto];
+  int nm = 0;
+  size_t ia = 0, ib = 0;
+  while (ia < fa.size() && ib < fb.size()) {
+    if (fa[ia].first == fb[ib].first) {
+      for (int idx1 : fa[ia].second) {
+        if (hasMp1[idx1]) continue;
+        const bool st1 = uR1[idx1] >= 0;
+        if (onlyStereo && !st1) continue;
+        const KeyPt& kp1 = k1[idx1];
+        int bestDist = 50, bestIdx2 = -1;
+        for (int idx2 : fb[ib].second) {
+          if (hasMp2[idx2]) continue;
+          const bool st2 = uR2[idx2] >= 0;
+          if (onlyStereo && !st2) continue;
+          const int dist = hamming256(d1 + 32 * (size_t)idx1, d2 + 32 * (size_t)idx2);
+          if (dist > 50 || dist > bestDist) continue;
+          const KeyPt& kp2 = k2[idx2];
+          if (!st1 && !st2) {
+            const float distex = ex - kp2.x, distey = ey - kp2.y;
+            if (distex * distex + distey * distey < 100 * scale2[kp2.octave]) continue;
+          }
+          const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+          const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+          const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+          const float num = a * kp2.x + b * kp2.y + c, den = a * a + b * b;
+          if (den == 0) continue;
+          const float dsqr = num * num / den;
+          if ((double)dsqr < 3.84 * (double)sigma2_2[kp2.octave]) { bestIdx2 = idx2; bestDist = dist; }
+        }
+        if (bestIdx2 >= 0) {
+          m12[idx1] = bestIdx2; ++nm;
+          if (checkOri) hist[rot_bin(kp1.angle, k2[bestIdx2].angle)].push_back(idx1);
+        }
+      }
+      ++ia; ++ib;
+    } else if (fa[ia].first < fb[ib].first) {
+      while (ia < fa.size() && fa[ia].first < fb[ib].first) ++ia;
+    } else {
+      while (ib < fb.size() && fb[ib].first < fa[ia].first) ++ib;
+    }
+  }
+  if (checkOri) {
+    int a = -1, b = -1, c = -1;
+    three_maxima(hist, kHisto, a, b, c);
+    for (int i = 0; i < kHisto; ++i) {
+      if (i == a || i == b || i == c) continue;
+      for (int idx : hist[i]) { m12[idx] = -1; --nm; }
+    }
+  }
+  return nm;
+}
+
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305): among the N observed descriptors, the one
 // whose median distance to all of them (itself included, sorted row element [0.5*(N-1)]) is least; first on ties.
 inline int distinctive_descriptor(const uint8_t* d, int N) {

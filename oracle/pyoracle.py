@@ -125,6 +125,21 @@ def search_by_bow(dA, angA, validA, nodeA, dB, angB, validB, nodeB, th=50, ratio
     return m12[:len(dA)], n
 
 
+def search_for_triangulation(k1, d1, has1, ur1, node1, k2, d2, has2, ur2, node2, F12, pose2, Cw, cam2, scale2, sigma2_2,
+                             only_stereo=False, check_ori=True):
+    """ORBmatcher::SearchForTriangulation on flat arrays -> (vMatches12, nmatches)."""
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: np.ascontiguousarray(a, np.uint8)
+    i32 = lambda a: np.ascontiguousarray(a, np.int32)
+    k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+    args = [k1, u8(d1), u8(has1), f32(ur1), i32(node1)], [k2, u8(d2), u8(has2), f32(ur2), i32(node2)]
+    tail = [f32(F12).reshape(9), f32(pose2).reshape(12), f32(Cw).reshape(3), f32(cam2), f32(scale2), f32(sigma2_2)]
+    m12 = np.zeros(max(len(k1), 1), np.int32)
+    n = lib().orbo_search_for_triangulation(*[_p(a) for a in args[0]], len(k1), *[_p(a) for a in args[1]], len(k2),
+                                            *[_p(a) for a in tail], int(only_stereo), int(check_ori), _p(m12))
+    return m12[:len(k1)], n
+
+
 def distinctive_descriptor(desc):
     """MapPoint::ComputeDistinctiveDescriptors: index of the descriptor with the least median distance."""
     desc = np.ascontiguousarray(desc, np.uint8)

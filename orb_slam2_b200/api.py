@@ -95,6 +95,7 @@ def lib():
         L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                              C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_search_by_bow_batch.argtypes = [C.c_void_p] * 10 + [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_search_triangulation_batch.argtypes = [C.c_void_p] * 12 + [C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_distinctive_descriptors_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_undistort_grid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
         L.orbx_features_in_area_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -451,6 +452,30 @@ class ORBmatcher:
         th defaults to TH_LOW (src/ORBmatcher.cc:37,596)."""
         r = self.SearchByBoWBatch([(descA, angA)], [(descB, angB)], strict, th)
         return r[0][0], r[1][0]
+
+    def SearchForTriangulation(self, kf1, kf2, F12, pose2, Cw, cam2, scale_factors2, level_sigma2_2, bOnlyStereo=False):
+        """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-823) for a batch of keyframe pairs.
+        kf1[p] / kf2[p] = dict(kps=mvKeysUn, desc, has_mp, u_right, node); F12[p] 3x3, pose2[p] = (R2w 3x3, t2w 3), Cw[p] 3,
+        cam2[p] = (fx, fy, cx, cy).  Returns (nmatches per pair, vMatches12 per pair)."""
+        npairs = len(kf1)
+        cap = max(max(len(k["kps"]) for k in kf1), max(len(k["kps"]) for k in kf2), 1)
+        def pack(kfs):
+            k = np.zeros((npairs, cap), KP_DTYPE); d = np.zeros((npairs, cap, 32), np.uint8); hm = np.zeros((npairs, cap), np.uint8)
+            ur = np.full((npairs, cap), -1, np.float32); nd = np.zeros((npairs, cap), np.int32); n = np.zeros(npairs, np.int32)
+            for p, kf in enumerate(kfs):
+                n[p] = len(kf["kps"]); k[p, :n[p]] = kf["kps"]; d[p, :n[p]] = kf["desc"]; hm[p, :n[p]] = kf["has_mp"]
+                ur[p, :n[p]] = kf["u_right"]; nd[p, :n[p]] = kf["node"]
+            return k, d, hm, ur, nd, n
+        A = pack(kf1); B = pack(kf2)
+        F = np.ascontiguousarray(np.asarray(F12, np.float32).reshape(npairs, 9))
+        T = np.ascontiguousarray(np.stack([np.concatenate([np.asarray(R, np.float32).reshape(9), np.asarray(t, np.float32).reshape(3)]) for R, t in pose2]))
+        Cc = np.ascontiguousarray(np.asarray(Cw, np.float32).reshape(npairs, 3)); K = np.ascontiguousarray(np.asarray(cam2, np.float32).reshape(npairs, 4))
+        sc = np.ascontiguousarray(scale_factors2, np.float32); sg = np.ascontiguousarray(level_sigma2_2, np.float32)
+        m12 = np.zeros((npairs, cap), np.int32); nm = np.zeros(npairs, np.int32)
+        _check(lib().orbx_search_triangulation_batch(*[x.ctypes.data for x in A], *[x.ctypes.data for x in B], npairs, cap,
+                                                     F.ctypes.data, T.ctypes.data, Cc.ctypes.data, K.ctypes.data, sc.ctypes.data, sg.ctypes.data,
+                                                     len(sc), int(bOnlyStereo), int(self.mbCheckOrientation), m12.ctypes.data, nm.ctypes.data, 0, None))
+        return [int(v) for v in nm], [m12[p, :A[5][p]].copy() for p in range(npairs)]
 
     def SearchByBoWNodes(self, sidesA, sidesB, strict=True, th=None):
         """SearchByBoW with vocabulary buckets, batched.  Each side = (desc, angles, valid, node) per pair; strict=True is

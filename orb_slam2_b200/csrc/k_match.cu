@@ -741,6 +741,125 @@ int launch_search_by_bow(const BowArgs& a, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------------------------------
+// K14: ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-823) with CheckDistEpipolarLine (:140-157),
+// batched over keyframe pairs.  The reference never sets vbMatched2, so the features of
+// KF1 are independent: one thread per KF1 feature.  One CTA per pair sorts the KF2 side by (node, index) and
+// stages its descriptors in shared memory; a thread finds the run of its node by binary search and walks it in
+// index order with the reference's acceptance rule (dist <= TH_LOW, dist <= best so far, epipole and epipolar
+// checks), i.e. the LAST candidate of least distance that passes the checks.
+__global__ void __launch_bounds__(kBowThreads) k_search_triangulation(TriArgs a, int capPad) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  unsigned long long* keyB = reinterpret_cast<unsigned long long*>(smem);          // [capPad] node<<32 | index, sorted
+  uint32_t* Bs = reinterpret_cast<uint32_t*>(keyB + capPad);                        // [cap][8]
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_nm;
+  __shared__ float s_epi[2];
+  const int p = blockIdx.x, tid = threadIdx.x;
+  const int n1 = a.n1[p], n2 = a.n2[p];
+  const size_t po = (size_t)p * a.cap;
+  const orbx_keypoint* k1 = a.k1 + po; const orbx_keypoint* k2 = a.k2 + po;
+  const uint32_t* d1 = reinterpret_cast<const uint32_t*>(a.d1 + po * 32);
+  const uint32_t* d2 = reinterpret_cast<const uint32_t*>(a.d2 + po * 32);
+  int* m12 = a.m12 + po;
+  for (int i = tid; i < capPad; i += kBowThreads)
+    keyB[i] = i < n2 ? (((unsigned long long)(uint32_t)a.node2[po + i] << 32) | (unsigned)i) : ~0ull;
+  for (int i = tid; i < n2 * 8; i += kBowThreads) Bs[i] = __ldg(d2 + i);
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (tid == 0) {
+    s_nm = 0;
+    const float* T = a.pose2 + (size_t)p * 12; const float* C = a.Cw + (size_t)p * 3; const float* K = a.cam2 + (size_t)p * 4;
+    float C2[3];
+    for (int r = 0; r < 3; ++r)                                                     // R2w*Cw + t2w, cv::gemm arithmetic (src/ORBmatcher.cc:667)
+      C2[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[3 * r], C[0]), __fmul_rn(T[3 * r + 1], C[1])), __fmul_rn(T[3 * r + 2], C[2])), T[9 + r]);
+    const float invz = __fdiv_rn(1.0f, C2[2]);
+    s_epi[0] = __fadd_rn(__fmul_rn(__fmul_rn(K[0], C2[0]), invz), K[2]);
+    s_epi[1] = __fadd_rn(__fmul_rn(__fmul_rn(K[1], C2[1]), invz), K[3]);
+  }
+  __syncthreads();
+  for (int k = 2; k <= capPad; k <<= 1)
+    for (int jj = k >> 1; jj > 0; jj >>= 1) {
+      for (int i = tid; i < capPad; i += kBowThreads) {
+        const int l = i ^ jj;
+        if (l > i) {
+          const bool up = (i & k) == 0;
+          const unsigned long long x = keyB[i], y = keyB[l];
+          if ((x > y) == up) { keyB[i] = y; keyB[l] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  const float* F = a.F12 + (size_t)p * 9;
+  const float ex = s_epi[0], ey = s_epi[1];
+  int nm = 0;
+  for (int i = tid; i < n1; i += kBowThreads) {
+    int best2 = -1;
+    const bool st1 = a.uR1[po + i] >= 0.f;
+    if (!a.hasMp1[po + i] && !(a.onlyStereo && !st1)) {
+      const uint32_t node = (uint32_t)a.node1[po + i];
+      int lo = 0, hi = n2;                                                          // first entry with node2 >= node
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if ((uint32_t)(keyB[mid] >> 32) < node) lo = mid + 1; else hi = mid; }
+      uint32_t q[8];
+#pragma unroll
+      for (int w = 0; w < 8; ++w) q[w] = __ldg(d1 + (size_t)i * 8 + w);
+      const orbx_keypoint kp1 = k1[i];
+      const float la = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, F[0]), __fmul_rn(kp1.y, F[3])), F[6]);
+      const float lb = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, F[1]), __fmul_rn(kp1.y, F[4])), F[7]);
+      const float lc = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, F[2]), __fmul_rn(kp1.y, F[5])), F[8]);
+      const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+      int bestDist = 50;                                                            // TH_LOW
+      for (int e = lo; e < n2 && (uint32_t)(keyB[e] >> 32) == node; ++e) {
+        const int j = (int)(keyB[e] & 0xffffffffu);
+        const int dist = ham8(q, Bs + (size_t)j * 8);
+        if (dist > 50 || dist > bestDist) continue;
+        if (a.hasMp2[po + j]) continue;
+        const bool st2 = a.uR2[po + j] >= 0.f;
+        if (a.onlyStereo && !st2) continue;
+        const orbx_keypoint kp2 = k2[j];
+        if (!st1 && !st2) {
+          const float dx = __fsub_rn(ex, kp2.x), dy = __fsub_rn(ey, kp2.y);
+          if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, a.scale2[kp2.octave])) continue;
+        }
+        if (den == 0.f) continue;
+        const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, kp2.x), __fmul_rn(lb, kp2.y)), lc);
+        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+        if ((double)dsqr < __dmul_rn(3.84, (double)a.sigma2_2[kp2.octave])) { best2 = j; bestDist = dist; }
+      }
+    }
+    m12[i] = best2;
+    if (best2 >= 0) {
+      ++nm;
+      if (a.checkOri) atomicAdd(&s_hist[rot_bin(k1[i].angle, k2[best2].angle)], 1);
+    }
+  }
+  if (nm) atomicAdd(&s_nm, nm);
+  __syncthreads();
+  if (a.checkOri) {
+    int k_a, k_b, k_c;
+    three_maxima(s_hist, k_a, k_b, k_c);
+    int drop = 0;
+    for (int i = tid; i < n1; i += kBowThreads) {
+      const int m = m12[i];                                                         // written by this same thread above
+      if (m >= 0) {
+        const int b = rot_bin(k1[i].angle, k2[m].angle);
+        if (b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
+      }
+    }
+    if (drop) atomicSub(&s_nm, drop);
+    __syncthreads();
+  }
+  if (tid == 0) a.nm[p] = s_nm;
+}
+
+int launch_search_triangulation(const TriArgs& a, cudaStream_t st) {
+  int capPad = 32;
+  while (capPad < a.cap) capPad <<= 1;
+  const size_t smem = (size_t)capPad * 8 + (size_t)a.cap * 32;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_triangulation, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_search_triangulation<<<a.n_pairs, kBowThreads, smem, st>>>(a, capPad);
+  return 1;
+}
+
+// ------------------------------------------------------------------------------------------
 // K13: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305), batched over map points
 // (SURVEY.md 8f rank 3).  One warp per map point: its N observed descriptors sit in shared memory; for
 // every row i the lanes take the columns j, the 257-bin histogram of the row gives the element

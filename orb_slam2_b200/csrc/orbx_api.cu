@@ -693,6 +693,47 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
   return ORBX_OK;
 }
 
+orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const uint8_t* has_mp1, const float* u_right1,
+                                            const int* node1, const int* n1, const orbx_keypoint* kps2, const uint8_t* desc2,
+                                            const uint8_t* has_mp2, const float* u_right2, const int* node2, const int* n2, int n_pairs,
+                                            int cap, const float* F12, const float* pose2, const float* Cw, const float* cam2,
+                                            const float* scale_factors2, const float* level_sigma2_2, int nlevels, int only_stereo,
+                                            int check_orientation, int* matches12, int* n_matches, int on_device, void* stream) {
+  if (!kps1 || !desc1 || !has_mp1 || !u_right1 || !node1 || !n1 || !kps2 || !desc2 || !has_mp2 || !u_right2 || !node2 || !n2 || !F12 ||
+      !pose2 || !Cw || !cam2 || !scale_factors2 || !level_sigma2_2 || !matches12 || !n_matches)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_pairs < 1 || cap < 1 || cap > 4096 || nlevels < 1 || nlevels > kMaxLevels) return fail(ORBX_ERR_BAD_ARG, "bad sizes (cap <= 4096, nlevels <= 8)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_pairs, pc = np * cap;
+  TriArgs a;
+  CU(sg.in(kps1, pc, on_device, &a.k1)); CU(sg.in(desc1, pc * 32, on_device, &a.d1)); CU(sg.in(has_mp1, pc, on_device, &a.hasMp1));
+  CU(sg.in(u_right1, pc, on_device, &a.uR1)); CU(sg.in(node1, pc, on_device, &a.node1)); CU(sg.in(n1, np, on_device, &a.n1));
+  CU(sg.in(kps2, pc, on_device, &a.k2)); CU(sg.in(desc2, pc * 32, on_device, &a.d2)); CU(sg.in(has_mp2, pc, on_device, &a.hasMp2));
+  CU(sg.in(u_right2, pc, on_device, &a.uR2)); CU(sg.in(node2, pc, on_device, &a.node2)); CU(sg.in(n2, np, on_device, &a.n2));
+  CU(sg.in(F12, np * 9, on_device, &a.F12)); CU(sg.in(pose2, np * 12, on_device, &a.pose2)); CU(sg.in(Cw, np * 3, on_device, &a.Cw));
+  CU(sg.in(cam2, np * 4, on_device, &a.cam2));
+  if (on_device) {
+    CU(cudaMemcpyAsync(a.scale2, scale_factors2, nlevels * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(a.sigma2_2, level_sigma2_2, nlevels * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  } else {
+    std::memcpy(a.scale2, scale_factors2, nlevels * sizeof(float)); std::memcpy(a.sigma2_2, level_sigma2_2, nlevels * sizeof(float));
+  }
+  for (int l = nlevels; l < kMaxLevels; ++l) { a.scale2[l] = a.scale2[nlevels - 1]; a.sigma2_2[l] = a.sigma2_2[nlevels - 1]; }
+  if (on_device) { a.m12 = matches12; a.nm = n_matches; }
+  else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
+  a.n_pairs = n_pairs; a.cap = cap; a.onlyStereo = only_stereo; a.checkOri = check_orientation;
+  g_launches += launch_search_triangulation(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
 orbx_status orbx_distinctive_descriptors_batch(const uint8_t* desc, const int* counts, int n_points, int kcap, int* best_idx,
                                                uint8_t* best_desc, int on_device, void* stream) {
   if (!desc || !counts || !best_idx) return fail(ORBX_ERR_BAD_ARG, "null argument");

@@ -145,6 +145,16 @@ struct BowArgs {
 };
 int launch_search_by_bow(const BowArgs& a, cudaStream_t st);
 
+struct TriArgs {
+  const orbx_keypoint* k1; const uint8_t* d1; const uint8_t* hasMp1; const float* uR1; const int* node1; const int* n1;
+  const orbx_keypoint* k2; const uint8_t* d2; const uint8_t* hasMp2; const float* uR2; const int* node2; const int* n2;
+  const float* F12; const float* pose2; const float* Cw; const float* cam2;   // [P][9], [P][12], [P][3], [P][4]
+  float scale2[kMaxLevels], sigma2_2[kMaxLevels];
+  int n_pairs, cap, onlyStereo, checkOri;
+  int* m12; int* nm;
+};
+int launch_search_triangulation(const TriArgs& a, cudaStream_t st);
+
 struct DistinctArgs {
   const uint8_t* desc; const int* counts; int n_points, kcap;
   int* best_idx; uint8_t* best_desc;

@@ -562,3 +562,34 @@ def test_distinctive_descriptors(gx, oracle):
         if want >= 0:
             assert np.array_equal(out[m], d[want])
     assert best[-2] == -1 and best[-3] == 0
+
+
+@pytest.mark.parametrize("only_stereo,ori", [(False, True), (True, True), (False, False)])
+def test_search_for_triangulation(gx, oracle, only_stereo, ori):
+    """K14: SearchForTriangulation + CheckDistEpipolarLine.  The second keyframe is a translated
+    view, so F12 = [t]x of the image translation makes true matches lie on their epipolar lines; the epipole is put
+    inside the image so that the mono-mono exclusion zone fires; stereo / mono features and existing map points mixed."""
+    w, h, nf = 1241, 376, 2000
+    G = _ext(gx, w, h, nf)
+    scale, sigma2 = np.asarray(G.GetScaleFactors(), np.float32), np.asarray(G.GetScaleSigmaSquares(), np.float32)
+    rng = np.random.default_rng(314)
+    words = rng.integers(0, 256, (64, 32), dtype=np.uint8)
+    kf1, kf2, F12, poses, Cws, cams, refs = [], [], [], [], [], [], []
+    for p in range(3):
+        a, b, (dx, dy) = synth.mono_pair(230 + p, w, h)
+        k1, d1 = G(a); k2, d2 = G(b)
+        if p == 2: k1, d1 = k1[:900], d1[:900]
+        mk = lambda k, d: dict(kps=k, desc=d, has_mp=(rng.random(len(k)) < 0.3).astype(np.uint8),
+                               u_right=np.where(rng.random(len(k)) < 0.5, k["x"] - 3.0, -1.0).astype(np.float32), node=_vocab_nodes(d, words))
+        A, B = mk(k1, d1), mk(k2, d2)
+        t = np.array([dx, dy, 0.0]) / max(np.hypot(dx, dy), 1.0)
+        F = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]], np.float32) + rng.normal(0, 1e-4, (3, 3)).astype(np.float32)
+        R = np.eye(3, dtype=np.float32); tw = np.array([0.02 * p, -0.01, 1.0], np.float32); Cw = np.array([0.1, 0.05, 0.03 * p], np.float32)
+        cam = np.array([718.856, 718.856, 607.1928, 185.2157], np.float32)
+        kf1.append(A); kf2.append(B); F12.append(F); poses.append((R, tw)); Cws.append(Cw); cams.append(cam)
+        refs.append(oracle.search_for_triangulation(k1, d1, A["has_mp"], A["u_right"], A["node"], k2, d2, B["has_mp"], B["u_right"], B["node"],
+                                                    F, np.concatenate([R.reshape(9), tw]), Cw, cam, scale, sigma2, only_stereo, ori))
+    nm, m12 = gx.ORBmatcher(0.6, ori).SearchForTriangulation(kf1, kf2, F12, poses, Cws, cams, scale, sigma2, bOnlyStereo=only_stereo)
+    for p in range(3):
+        assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), (p, nm[p], refs[p][1])
+    assert refs[0][1] > (5 if only_stereo else 30)
