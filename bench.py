@@ -141,6 +141,15 @@ def measured_traffic(stage, batch):
     return None
 
 
+def measured_issue(stage):
+    """Issue-slot / ALU-pipe / L1 utilisation of a stage from the committed ncu capture (profiles/traffic.json), or None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return dict(t["issue"][stage], source=t["issue"]["source"])
+    except Exception:
+        return None
+
+
 def cpu_sample(nframes, distinct=32):
     """nframes KITTI-shaped stereo pairs for the CPU legs (at most `distinct` different ones, tiled)."""
     w, h = CFG["w"], CFG["h"]
@@ -466,7 +475,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": measured_traffic(top, B), "peak_source": peak_src,
+                         "traffic": measured_traffic(top, B), "peak_source": peak_src, "issue": measured_issue(top),
                          "algorithmic_bytes_per_launch": stage_bytes[top] * B,
                          "note": "front end is instruction-issue / latency bound, not HBM bound (DESIGN.md); see profiles/ for ncu issue utilisation"},
             "stage_ms_per_step": stage_ms,
