@@ -286,6 +286,23 @@ def secondary_workloads(gx, torch, local):
     a, b = ev(), ev(); a.record(); [bow_step() for _ in range(3)]; b.record(); torch.cuda.synchronize()
     out["search_by_bow_buckets_pairs_per_s"] = 3 * P / (a.elapsed_time(b) / 1e3)
     out["search_by_bow_matches_per_pair"] = float(nmm.float().mean())
+    # --- DBoW2 transform (Frame::ComputeBoW) of the same frames against a synthetic vocabulary of
+    #     ORBvoc.txt's shape (k = 10, L = 6: 1.1 M nodes, 60 Hamming distances per feature), levelsup = 4 ---
+    V = synth.vocabulary_fast(4242, 10, 6)
+    voc = gx.ORBVocabulary(V, weighting=0, norm=1, device=local)
+    F2 = 2 * P
+    wo = torch.empty((F2, cap), dtype=torch.int32, device="cuda"); no = torch.empty_like(wo); bw = torch.empty_like(wo)
+    bv = torch.empty((F2, cap), dtype=torch.float64, device="cuda"); bc = torch.empty(F2, dtype=torch.int32, device="cuda")
+    def voc_step():
+        rc = L.orbx_bow_transform_batch(voc.h, desc.data_ptr(), cnt.data_ptr(), F2, cap, 4, wo.data_ptr(), no.data_ptr(), bw.data_ptr(),
+                                        bv.data_ptr(), bc.data_ptr(), 1, st)
+        assert rc == 0, L.orbx_last_error_string()
+    for _ in range(2):
+        voc_step()
+    a, b = ev(), ev(); a.record(); [voc_step() for _ in range(3)]; b.record(); torch.cuda.synchronize()
+    out["bow_transform_frames_per_s"] = 3 * F2 / (a.elapsed_time(b) / 1e3)
+    out["bow_transform_words_per_frame"] = float(bc.float().mean())
+    voc.close()
     # --- UndistortKeyPoints + image bounds + grid for the frames above (TUM1 distortion), and
     #     GetFeaturesInArea queries against them (window 100 px around every keypoint of the first frames) ---
     cam = (C.c_float * 9)(517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314)

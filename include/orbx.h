@@ -210,6 +210,34 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
                                      int check_orientation, int strict_lt, int* matches12, int* n_matches,
                                      int on_device, void* stream);
 
+/* ---- DBoW2 vocabulary transform ------------------------------------------ */
+
+typedef struct orbx_vocabulary orbx_vocabulary;
+
+/* A DBoW2 TemplatedVocabulary<FORB::TDescriptor, FORB> (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) copied to the
+ * device as flat arrays.  n_nodes nodes, node 0 = root; node_desc = m_nodes[i].descriptor (32 bytes each);
+ * the children of node i are children[child_first[i] .. child_first[i] + child_count[i]) in m_nodes[i].children
+ * order (child_count 0 = leaf); node_word[i] / node_weight[i] = m_nodes[i].word_id / .weight (used for leaves).
+ * L = m_L; weighting = m_weighting (0 TF_IDF, 1 TF, 2 IDF, 3 BINARY); norm = what
+ * m_scoring_object->mustNormalize reports (0 no normalisation, 1 L1, 2 L2).  ORBvoc.txt: k 10, L 6, TF_IDF, L1. */
+orbx_status orbx_vocabulary_create(const uint8_t* node_desc, const int* child_first, const int* child_count,
+                                   const int* children, int n_children, const int* node_word,
+                                   const double* node_weight, int n_nodes, int L, int weighting, int norm, int device,
+                                   orbx_vocabulary** out);
+void orbx_vocabulary_destroy(orbx_vocabulary* voc);
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1127-1196) as Frame::ComputeBoW
+ * and KeyFrame::ComputeBoW call it (src/Frame.cc:395-402, src/KeyFrame.cc:74-84; levelsup = 4) for n_frames frames:
+ * frame f has n[f] descriptors at desc + f*cap*32.  word_of / node_of [f*cap + i] receive the word id of feature i
+ * and its node at level L - levelsup (-1, -1 when the word is stopped, i.e. weight 0): mFeatVec is node_of read as
+ * "node -> features in index order", the form orbx_search_by_bow_batch / orbx_search_triangulation_batch take.
+ * mBowVec of frame f comes back as bow_count[f] (word, value) pairs at bow_word / bow_val + f*cap in ascending word
+ * id, with the reference's double arithmetic (weights added per feature in feature order, normalised by the sum
+ * taken in word order).  cap <= 8192.  All pointers host or all device per on_device. */
+orbx_status orbx_bow_transform_batch(const orbx_vocabulary* voc, const uint8_t* desc, const int* n, int n_frames,
+                                     int cap, int levelsup, int* word_of, int* node_of, int* bow_word,
+                                     double* bow_val, int* bow_count, int on_device, void* stream);
+
 /* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:657-823, with
  * CheckDistEpipolarLine :140-157; called from src/LocalMapping.cc:296) for n_pairs independent keyframe pairs.
  * Side 1 of pair p at index p*cap: kps1 = mvKeysUn, desc1, has_mp1[i] = (GetMapPoint(i) != NULL), u_right1 = mvuRight,

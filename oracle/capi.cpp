@@ -82,6 +82,13 @@ int orbo_search_for_triangulation(const KeyPt* k1, const uint8_t* d1, const uint
                                   onlyStereo != 0, checkOri != 0, m12);
 }
 
+int orbo_voc_transform(const uint8_t* vdesc, const int* child_first, const int* child_count, const int* children, const int* word_id,
+                       const double* weight, int L, const uint8_t* desc, int n, int levelsup, int weighting, int norm, int* word_of,
+                       int* node_of, int* bow_word, double* bow_val) {
+  VocabView V{vdesc, child_first, child_count, children, word_id, weight, L};
+  return voc_transform(V, desc, n, levelsup, weighting, norm, word_of, node_of, bow_word, bow_val);
+}
+
 int orbo_distinctive_descriptor(const uint8_t* d, int n) { return distinctive_descriptor(d, n); }
 
 int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,

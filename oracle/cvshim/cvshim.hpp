@@ -12,7 +12,10 @@
 #include <cmath>
 #include <cstddef>
 #include <cstring>
+#include <iostream>
 #include <memory>
+#include <sstream>
+#include <string>
 #include <stdexcept>
 #include <vector>
 
@@ -116,6 +119,7 @@ class Mat {
   uchar* ptr(int y = 0) { return data + (size_t)y * step; }
   const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
   template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
+  template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step); }
   static MatZeros zeros(int r, int c, int) { return MatZeros{r, c}; }
   Mat(const MatZeros& z) { alloc(z.rows, z.cols); }
   // like cv::Mat = MatExpr: a destination of the right size is filled in place (the reference
@@ -185,5 +189,29 @@ static inline float fastAtan2(float y, float x) { return orbo::fast_atan2_deg(y,
 struct KeyPointsFilter {  // only named by the reference's disabled ComputeKeyPointsOld path
   static void retainBest(std::vector<KeyPoint>&, int) { throw std::logic_error("dead path"); }
 };
+
+// cv::FileStorage / cv::FileNode are only named by DBoW2's YAML save()/load() (Thirdparty/DBoW2/DBoW2/
+// TemplatedVocabulary.h:1456-1640), virtual members that must compile but are never called by oracle/_ref: the
+// text-file loader the reference uses (:1337-1420) does not touch them.  Every use throws.
+struct FileNode {
+  FileNode operator[](const char*) const { throw std::logic_error("cv::FileStorage is not part of the shim"); }
+  FileNode operator[](const std::string&) const { throw std::logic_error("cv::FileStorage is not part of the shim"); }
+  FileNode operator[](int) const { throw std::logic_error("cv::FileStorage is not part of the shim"); }
+  size_t size() const { return 0; }
+  operator int() const { throw std::logic_error("cv::FileStorage is not part of the shim"); }
+  operator double() const { throw std::logic_error("cv::FileStorage is not part of the shim"); }
+  operator std::string() const { throw std::logic_error("cv::FileStorage is not part of the shim"); }
+};
+template <typename T> static inline void operator>>(const FileNode&, T&) { throw std::logic_error("cv::FileStorage is not part of the shim"); }
+struct FileStorage {
+  enum { READ = 0, WRITE = 1 };
+  FileStorage() {}
+  FileStorage(const char*, int) {}
+  FileStorage(const std::string&, int) {}
+  bool isOpened() const { return false; }
+  FileNode operator[](const char*) const { return FileNode(); }
+  FileNode operator[](const std::string&) const { return FileNode(); }
+};
+template <typename T> static inline FileStorage& operator<<(FileStorage& f, const T&) { throw std::logic_error("cv::FileStorage is not part of the shim"); return f; }
 
 }  // namespace cv

@@ -25,6 +25,7 @@
 #pragma once
 #include <algorithm>
 #include <climits>
+#include <cmath>
 #include <cstdint>
 #include <list>
 #include <utility>
@@ -886,6 +887,66 @@ inline int search_for_triangulation(const KeyPt* k1, const uint8_t* d1, const ui
     }
   }
   return nm;
+}
+
+// DBoW2 TemplatedVocabulary::transform (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1196 for a feature set,
+// :1216-1258 for one feature, FORB::distance FORB.cpp:81-101, BowVector::addWeight / addIfNotExist / normalize
+// BowVector.cpp:32-92, FeatureVector::addFeature FeatureVector.cpp:28-45), as Frame::ComputeBoW calls it
+// (src/Frame.cc:395-402, levelsup = 4).  The vocabulary tree is given flat: for node n its children are
+// children[child_first[n] .. child_first[n] + child_count[n]) in m_nodes[n].children order, a leaf has
+// child_count 0 and carries word_id / weight.  weighting: 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY; norm: 0 none, 1 L1, 2 L2
+// (what ScoringObject::mustNormalize returns; ORBvoc.txt is TF_IDF + L1).
+struct VocabView {
+  const uint8_t* desc; const int* child_first; const int* child_count; const int* children;
+  const int* word_id; const double* weight; int L;
+};
+inline void voc_transform_one(const VocabView& V, const uint8_t* f, int levelsup, int* word, double* w, int* nid) {
+  const int nid_level = V.L - levelsup;
+  if (nid_level <= 0) *nid = 0;
+  int final_id = 0, level = 0;
+  do {
+    ++level;
+    const int* ch = V.children + V.child_first[final_id];
+    const int nc = V.child_count[final_id];
+    final_id = ch[0];
+    int best = hamming256(f, V.desc + 32 * (size_t)final_id);
+    for (int c = 1; c < nc; ++c) {
+      const int d = hamming256(f, V.desc + 32 * (size_t)ch[c]);
+      if (d < best) { best = d; final_id = ch[c]; }
+    }
+    if (level == nid_level) *nid = final_id;
+  } while (V.child_count[final_id] > 0);
+  *word = V.word_id[final_id]; *w = V.weight[final_id];
+}
+// Returns the BowVector size; bow_word / bow_val in ascending word id; word_of / node_of per feature (-1 if stopped).
+inline int voc_transform(const VocabView& V, const uint8_t* desc, int n, int levelsup, int weighting, int norm,
+                         int* word_of, int* node_of, int* bow_word, double* bow_val) {
+  std::vector<std::pair<int, double>> v;                               // BowVector (std::map) kept sorted
+  auto find = [&](int id) { return std::lower_bound(v.begin(), v.end(), std::make_pair(id, -1e300)); };
+  for (int i = 0; i < n; ++i) {
+    int id, nid = 0; double w;
+    voc_transform_one(V, desc + 32 * (size_t)i, levelsup, &id, &w, &nid);
+    word_of[i] = -1; node_of[i] = -1;
+    if (w > 0) {
+      auto it = find(id);
+      const bool exists = it != v.end() && it->first == id;
+      if (weighting <= 1) { if (exists) it->second += w; else v.insert(it, {id, w}); }
+      else if (!exists) v.insert(it, {id, w});
+      word_of[i] = id; node_of[i] = nid;
+    }
+  }
+  if (weighting <= 1 && !v.empty() && norm == 0) {
+    const double nd = (double)v.size();
+    for (auto& e : v) e.second /= nd;
+  }
+  if (norm != 0) {
+    double nrm = 0.0;
+    if (norm == 1) for (auto& e : v) nrm += std::fabs(e.second);
+    else { for (auto& e : v) nrm += e.second * e.second; nrm = std::sqrt(nrm); }
+    if (nrm > 0.0) for (auto& e : v) e.second /= nrm;
+  }
+  for (size_t k = 0; k < v.size(); ++k) { bow_word[k] = v[k].first; bow_val[k] = v[k].second; }
+  return (int)v.size();
 }
 
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305): among the N observed descriptors, the one

@@ -140,6 +140,58 @@ def search_for_triangulation(k1, d1, has1, ur1, node1, k2, d2, has2, ur2, node2,
     return m12[:len(k1)], n
 
 
+def voc_transform(voc, desc, levelsup=4, weighting=0, norm=1):
+    """DBoW2 TemplatedVocabulary::transform on a flat vocabulary (dict: desc, child_first, child_count, children, word_id,
+    weight, L) -> (word per feature, node per feature, BowVector words, BowVector values)."""
+    desc = np.ascontiguousarray(desc, np.uint8); n = len(desc)
+    wo = np.zeros(max(n, 1), np.int32); no = np.zeros(max(n, 1), np.int32)
+    bw = np.zeros(max(n, 1), np.int32); bv = np.zeros(max(n, 1), np.float64)
+    m = lib().orbo_voc_transform(_p(voc["desc"]), _p(voc["child_first"]), _p(voc["child_count"]), _p(voc["children"]), _p(voc["word_id"]),
+                                 _p(voc["weight"]), int(voc["L"]), _p(desc), n, levelsup, weighting, norm, _p(wo), _p(no), _p(bw), _p(bv))
+    return wo[:n], no[:n], bw[:m].copy(), bv[:m].copy()
+
+
+def ref_dbow_available():
+    return os.path.exists(os.path.join(_HERE, "_ref", "orbref_dbow"))
+
+
+def write_vocabulary_text(voc, path, scoring, weighting):
+    """The reference's text vocabulary format (TemplatedVocabulary::loadFromTextFile, TemplatedVocabulary.h:1337-1420):
+    'k L scoring weighting', then one line per node in id order: parent, isLeaf, 32 descriptor bytes, weight.
+    No trailing newline (the loader would read it as one more node)."""
+    n = len(voc["desc"]); parent = np.zeros(n, np.int64)
+    for p in range(n):
+        for c in range(voc["child_count"][p]):
+            parent[voc["children"][voc["child_first"][p] + c]] = p
+    lines = [f'{voc["k"]} {voc["L"]} {scoring} {weighting}']
+    for i in range(1, n):
+        lines.append(f'{parent[i]} {1 if voc["child_count"][i] == 0 else 0} ' + " ".join(str(int(b)) for b in voc["desc"][i]) +
+                     f' {voc["weight"][i]:.17g}')
+    with open(path, "w") as f:
+        f.write("\n".join(lines))
+
+
+def ref_dbow_transform(voc, desc, levelsup, scoring, weighting):
+    """Runs the REFERENCE's DBoW2 (oracle/_ref/orbref_dbow) -> (node per feature, BowVector words, BowVector values)."""
+    import tempfile
+    desc = np.ascontiguousarray(desc, np.uint8)
+    with tempfile.TemporaryDirectory() as td:
+        vp, dp = os.path.join(td, "voc.txt"), os.path.join(td, "desc.bin")
+        write_vocabulary_text(voc, vp, scoring, weighting); desc.tofile(dp)
+        out = subprocess.run([os.path.join(_HERE, "_ref", "orbref_dbow"), vp, dp, str(levelsup)], capture_output=True, text=True, check=True)
+    bw, bv = [], []
+    node = np.full(len(desc), -1, np.int32)
+    for line in out.stdout.splitlines():
+        t = line.split()
+        if t[0] == "B":
+            bw.append(int(t[1])); bv.append(float.fromhex(t[2]))
+        elif t[0] == "V":
+            idx = [int(x) for x in t[2:]]
+            assert idx == sorted(idx)
+            node[idx] = int(t[1])
+    return node, np.array(bw, np.int32), np.array(bv, np.float64)
+
+
 def distinctive_descriptor(desc):
     """MapPoint::ComputeDistinctiveDescriptors: index of the descriptor with the least median distance."""
     desc = np.ascontiguousarray(desc, np.uint8)

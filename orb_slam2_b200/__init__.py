@@ -3,5 +3,5 @@
 Only the hot path is here: ORBextractor::operator(), Frame::ComputeStereoMatches and the
 ORBmatcher Hamming searches, behind the C ABI in include/orbx.h (csrc/ builds liborbx.so).
 """
-from .api import (KP_DTYPE, ComputeDistinctiveDescriptors, ComputeStereoMatches, Frame, FrameGrids, ORBextractor, ORBmatcher, OrbxError,  # noqa: F401
+from .api import (KP_DTYPE, ComputeDistinctiveDescriptors, ComputeStereoMatches, Frame, FrameGrids, ORBVocabulary, ORBextractor, ORBmatcher, OrbxError,  # noqa: F401
                   kernel_launch_count, lib, library_path)

@@ -96,6 +96,10 @@ def lib():
                                              C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_search_by_bow_batch.argtypes = [C.c_void_p] * 10 + [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_search_triangulation_batch.argtypes = [C.c_void_p] * 12 + [C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_vocabulary_create.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p, C.c_void_p] + [C.c_int] * 5 + [C.c_void_p]
+        L.orbx_vocabulary_destroy.argtypes = [C.c_void_p]
+        L.orbx_vocabulary_destroy.restype = None
+        L.orbx_bow_transform_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p]
         L.orbx_distinctive_descriptors_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_undistort_grid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
         L.orbx_features_in_area_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -299,6 +303,43 @@ class Frame:
 
     def __init__(self, keypoints, descriptors, cols, rows):
         self.mvKeysUn, self.mDescriptors, self.cols, self.rows = keypoints, descriptors, cols, rows
+
+
+class ORBVocabulary:
+    """A DBoW2 ORB vocabulary on the device (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) and its transform(), the
+    call behind Frame::ComputeBoW (src/Frame.cc:395-402).  voc = dict(desc, child_first, child_count, children, word_id,
+    weight, L) as flat arrays; weighting 0 = TF_IDF, norm 1 = L1 are ORBvoc.txt's settings."""
+
+    def __init__(self, voc, weighting=0, norm=1, device=0):
+        self.h = C.c_void_p()
+        a = lambda k, t: np.ascontiguousarray(voc[k], t)
+        d, cf, cc, ch, wi, wt = a("desc", np.uint8), a("child_first", np.int32), a("child_count", np.int32), a("children", np.int32), \
+            a("word_id", np.int32), a("weight", np.float64)
+        _check(lib().orbx_vocabulary_create(d.ctypes.data, cf.ctypes.data, cc.ctypes.data, ch.ctypes.data, len(ch), wi.ctypes.data,
+                                            wt.ctypes.data, len(cf), int(voc["L"]), weighting, norm, device, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().orbx_vocabulary_destroy(self.h); self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def transform(self, descriptor_lists, levelsup=4):
+        """Returns per frame (word per feature, node per feature, BowVector words, BowVector values)."""
+        nf = len(descriptor_lists)
+        cap = max(max((len(d) for d in descriptor_lists), default=1), 1)
+        desc = np.zeros((nf, cap, 32), np.uint8); n = np.zeros(nf, np.int32)
+        for f, d in enumerate(descriptor_lists):
+            n[f] = len(d); desc[f, :len(d)] = d
+        wo = np.zeros((nf, cap), np.int32); no = np.zeros((nf, cap), np.int32); bw = np.zeros((nf, cap), np.int32)
+        bv = np.zeros((nf, cap), np.float64); bc = np.zeros(nf, np.int32)
+        _check(lib().orbx_bow_transform_batch(self.h, desc.ctypes.data, n.ctypes.data, nf, cap, levelsup, wo.ctypes.data, no.ctypes.data,
+                                              bw.ctypes.data, bv.ctypes.data, bc.ctypes.data, 0, None))
+        return [(wo[f, :n[f]].copy(), no[f, :n[f]].copy(), bw[f, :bc[f]].copy(), bv[f, :bc[f]].copy()) for f in range(nf)]
 
 
 def ComputeDistinctiveDescriptors(descriptor_lists):

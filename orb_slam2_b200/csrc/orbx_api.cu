@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <type_traits>
 #include <string>
 #include <vector>
 
@@ -688,6 +689,104 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
   if (!on_device) {
     CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
+struct orbx_vocabulary {
+  int device = 0, n_nodes = 0, n_words = 0, L = 0, weighting = 0, norm = 0;
+  uint8_t* desc = nullptr; int* child_first = nullptr; int* child_count = nullptr; int* children = nullptr; int* word = nullptr;
+  double* weight = nullptr; double* wweight = nullptr;
+};
+
+void orbx_vocabulary_destroy(orbx_vocabulary* v) {
+  if (!v) return;
+  DeviceGuard g(v->device);
+  void* ptrs[] = {v->desc, v->child_first, v->child_count, v->children, v->word, v->weight, v->wweight};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  delete v;
+}
+
+orbx_status orbx_vocabulary_create(const uint8_t* node_desc, const int* child_first, const int* child_count, const int* children,
+                                   int n_children, const int* node_word, const double* node_weight, int n_nodes, int L, int weighting,
+                                   int norm, int device, orbx_vocabulary** out) {
+  if (!node_desc || !child_first || !child_count || !children || !node_word || !node_weight || !out) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_nodes < 2 || n_children < 1 || L < 1 || L > 10 || weighting < 0 || weighting > 3 || norm < 0 || norm > 2)
+    return fail(ORBX_ERR_BAD_ARG, "bad vocabulary sizes (L 1..10, weighting 0..3, norm 0..2)");
+  // the tree must be walkable: children ranges inside the list, child ids inside the node table, the root not a leaf,
+  // every leaf carrying a word id; the depth bound keeps a malformed (cyclic) table from hanging the kernel
+  int n_words = 0;
+  for (int i = 0; i < n_nodes; ++i) {
+    if (child_count[i] < 0 || child_first[i] < 0 || (long long)child_first[i] + child_count[i] > n_children) return fail(ORBX_ERR_BAD_ARG, "children range outside the list");
+    if (child_count[i] == 0) { if (node_word[i] < 0) return fail(ORBX_ERR_BAD_ARG, "leaf without a word id"); n_words = std::max(n_words, node_word[i] + 1); }
+  }
+  if (child_count[0] == 0) return fail(ORBX_ERR_BAD_ARG, "the root has no children");
+  for (int c = 0; c < n_children; ++c)
+    if (children[c] <= 0 || children[c] >= n_nodes) return fail(ORBX_ERR_BAD_ARG, "child id outside the node table");
+  {
+    std::vector<int> depth(n_nodes, -1);
+    std::vector<int> stack{0};
+    depth[0] = 0;
+    while (!stack.empty()) {
+      const int u = stack.back(); stack.pop_back();
+      for (int c = 0; c < child_count[u]; ++c) {
+        const int w = children[child_first[u] + c];
+        if (depth[w] >= 0) return fail(ORBX_ERR_BAD_ARG, "a node has two parents");
+        depth[w] = depth[u] + 1;
+        if (depth[w] > 16) return fail(ORBX_ERR_BAD_ARG, "tree deeper than 16 levels");
+        stack.push_back(w);
+      }
+    }
+  }
+  std::vector<double> wweight(n_words, 0.0);
+  for (int i = 0; i < n_nodes; ++i) if (child_count[i] == 0) wweight[node_word[i]] = node_weight[i];
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(ORBX_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(ORBX_ERR_BAD_ARG, "bad device index");
+  DeviceGuard g(device);
+  orbx_vocabulary* v = new orbx_vocabulary;
+  v->device = device; v->n_nodes = n_nodes; v->n_words = n_words; v->L = L; v->weighting = weighting; v->norm = norm;
+  auto up = [&](auto** dst, const auto* src, size_t count) -> bool {
+    using T = std::remove_pointer_t<std::remove_pointer_t<decltype(dst)>>;
+    if (cudaMalloc((void**)dst, std::max<size_t>(count, 1) * sizeof(T)) != cudaSuccess) return false;
+    return cudaMemcpy(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice) == cudaSuccess;
+  };
+  const bool ok = up(&v->desc, node_desc, (size_t)n_nodes * 32) && up(&v->child_first, child_first, (size_t)n_nodes) &&
+                  up(&v->child_count, child_count, (size_t)n_nodes) && up(&v->children, children, (size_t)n_children) &&
+                  up(&v->word, node_word, (size_t)n_nodes) && up(&v->weight, node_weight, (size_t)n_nodes) &&
+                  up(&v->wweight, wweight.data(), (size_t)n_words);
+  if (!ok) { orbx_vocabulary_destroy(v); return fail(ORBX_ERR_CUDA, "vocabulary upload failed"); }
+  *out = v;
+  return ORBX_OK;
+}
+
+orbx_status orbx_bow_transform_batch(const orbx_vocabulary* voc, const uint8_t* desc, const int* n, int n_frames, int cap, int levelsup,
+                                     int* word_of, int* node_of, int* bow_word, double* bow_val, int* bow_count, int on_device,
+                                     void* stream) {
+  if (!voc || !desc || !n || !word_of || !node_of || !bow_word || !bow_val || !bow_count) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_frames < 1 || cap < 1 || cap > 8192 || levelsup < 0) return fail(ORBX_ERR_BAD_ARG, "bad sizes (cap <= 8192)");
+  DeviceGuard g(voc->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t nf = (size_t)n_frames, fc = nf * cap;
+  BowTrArgs a;
+  a.v_desc = voc->desc; a.v_child_first = voc->child_first; a.v_child_count = voc->child_count; a.v_children = voc->children;
+  a.v_word = voc->word; a.v_weight = voc->weight; a.v_wweight = voc->wweight;
+  a.L = voc->L; a.levelsup = levelsup; a.weighting = voc->weighting; a.norm = voc->norm;
+  CU(sg.in(desc, fc * 32, on_device, &a.desc)); CU(sg.in(n, nf, on_device, &a.n));
+  if (on_device) { a.word_of = word_of; a.node_of = node_of; a.bow_word = bow_word; a.bow_val = bow_val; a.bow_count = bow_count; }
+  else {
+    CU(sg.alloc((void**)&a.word_of, fc * 4)); CU(sg.alloc((void**)&a.node_of, fc * 4)); CU(sg.alloc((void**)&a.bow_word, fc * 4));
+    CU(sg.alloc((void**)&a.bow_val, fc * 8)); CU(sg.alloc((void**)&a.bow_count, nf * 4));
+  }
+  a.n_frames = n_frames; a.cap = cap;
+  g_launches += launch_bow_transform(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(word_of, a.word_of, fc * 4, cudaMemcpyDeviceToHost, st)); CU(cudaMemcpyAsync(node_of, a.node_of, fc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(bow_word, a.bow_word, fc * 4, cudaMemcpyDeviceToHost, st)); CU(cudaMemcpyAsync(bow_val, a.bow_val, fc * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(bow_count, a.bow_count, nf * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
   }
   return ORBX_OK;

@@ -145,6 +145,16 @@ struct BowArgs {
 };
 int launch_search_by_bow(const BowArgs& a, cudaStream_t st);
 
+struct BowTrArgs {
+  // vocabulary (device): node descriptors, children lists, leaf word ids / weights, weight per word id
+  const uint8_t* v_desc; const int* v_child_first; const int* v_child_count; const int* v_children; const int* v_word;
+  const double* v_weight; const double* v_wweight;
+  int L, levelsup, weighting, norm;
+  const uint8_t* desc; const int* n; int n_frames, cap;
+  int* word_of; int* node_of; int* bow_word; double* bow_val; int* bow_count;
+};
+int launch_bow_transform(const BowTrArgs& a, cudaStream_t st);
+
 struct TriArgs {
   const orbx_keypoint* k1; const uint8_t* d1; const uint8_t* hasMp1; const float* uR1; const int* node1; const int* n1;
   const orbx_keypoint* k2; const uint8_t* d2; const uint8_t* hasMp2; const float* uR2; const int* node2; const int* n2;

@@ -110,3 +110,64 @@ def mono_pair(frame_idx, w, h, maxshift=40):
 
 def mono_frame(frame_idx, w, h):
     return synth_image(BASE_SEED + 16 * frame_idx + 12, w, h)
+
+
+def vocabulary(seed, k=10, L=4, stop_fraction=0.02, train=None):
+    """A synthetic DBoW2-shaped vocabulary tree (there is no ORBvoc.txt in the reference tree): k children per node,
+    L levels, node ids in breadth-first creation order with the root = 0 (as TemplatedVocabulary::create numbers them),
+    leaves are the words (ids in leaf order).  Node descriptors: a child = its parent with a random 1/8 of the bits
+    re-drawn, so that descents are decided by real distances; weights = idf-like positive doubles, a few words
+    stopped (weight 0).  `train` (optional (N,32) uint8) seeds the first level with real descriptors."""
+    rng = np.random.default_rng(seed)
+    desc = [np.zeros(32, np.uint8)]; child_first = [0]; child_count = [0]; children = []; level = [0]
+    frontier = [0]
+    for lv in range(1, L + 1):
+        nxt = []
+        for pnode in frontier:
+            child_first[pnode] = len(children); child_count[pnode] = k
+            for c in range(k):
+                nid = len(desc)
+                if lv == 1:
+                    d = train[rng.integers(0, len(train))].copy() if train is not None and len(train) else rng.integers(0, 256, 32, dtype=np.uint8)
+                else:
+                    flip = np.packbits(rng.random(256) < 0.125)
+                    d = desc[pnode] ^ (flip & rng.integers(0, 256, 32, dtype=np.uint8))
+                desc.append(d); child_first.append(0); child_count.append(0); level.append(lv)
+                children.append(nid); nxt.append(nid)
+        frontier = nxt
+    n = len(desc)
+    word_id = np.full(n, -1, np.int32); weight = np.zeros(n, np.float64)
+    leaves = [i for i in range(n) if child_count[i] == 0]
+    word_id[leaves] = np.arange(len(leaves), dtype=np.int32)
+    w = np.log(rng.uniform(1.5, 4000.0, len(leaves)))
+    w[rng.random(len(leaves)) < stop_fraction] = 0.0
+    weight[leaves] = w
+    return dict(desc=np.ascontiguousarray(np.stack(desc)), child_first=np.array(child_first, np.int32),
+                child_count=np.array(child_count, np.int32), children=np.array(children, np.int32),
+                word_id=word_id, weight=weight, L=L, k=k)
+
+
+def vocabulary_fast(seed, k=10, L=6):
+    """Same tree shape as vocabulary(), generated level by level with array operations (ORBvoc.txt's k = 10, L = 6
+    is 1.1 M nodes); for throughput measurements, not tied to the golden vectors."""
+    rng = np.random.default_rng(seed)
+    levels = [np.zeros((1, 32), np.uint8)]
+    for lv in range(1, L + 1):
+        par = np.repeat(levels[-1], k, axis=0)
+        if lv == 1:
+            cur = rng.integers(0, 256, par.shape, dtype=np.uint8)
+        else:
+            flip = np.packbits(rng.random((len(par), 256)) < 0.125, axis=1)
+            cur = par ^ (flip & rng.integers(0, 256, par.shape, dtype=np.uint8))
+        levels.append(cur)
+    desc = np.ascontiguousarray(np.concatenate(levels))
+    n = len(desc)
+    first = np.cumsum([0] + [len(x) for x in levels])            # id of the first node of each level
+    child_first = np.zeros(n, np.int32); child_count = np.zeros(n, np.int32)
+    inner = first[L]                                              # nodes below this id have children
+    child_count[:inner] = k
+    child_first[:inner] = np.arange(inner, dtype=np.int64) * k    # children list = ids 1.. in order
+    children = np.arange(1, n, dtype=np.int32)
+    word_id = np.full(n, -1, np.int32); word_id[inner:] = np.arange(n - inner, dtype=np.int32)
+    weight = np.zeros(n, np.float64); weight[inner:] = np.log(rng.uniform(1.5, 4000.0, n - inner))
+    return dict(desc=desc, child_first=child_first, child_count=child_count, children=children, word_id=word_id, weight=weight, L=L, k=k)

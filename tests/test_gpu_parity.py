@@ -593,3 +593,26 @@ def test_search_for_triangulation(gx, oracle, only_stereo, ori):
     for p in range(3):
         assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), (p, nm[p], refs[p][1])
     assert refs[0][1] > (5 if only_stereo else 30)
+
+
+@pytest.mark.parametrize("k,L,levelsup,weighting,norm", [(10, 4, 2, 0, 1), (10, 3, 4, 0, 1), (6, 5, 3, 1, 2), (10, 4, 2, 2, 1), (8, 3, 1, 3, 0), (10, 4, 2, 1, 0)])
+def test_bow_transform(gx, oracle, k, L, levelsup, weighting, norm):
+    """K15: DBoW2 transform on a synthetic vocabulary tree (the reference ships no ORBvoc.txt):
+    word and node per feature bit-exact, BowVector words in order and values equal to the last bit of the double
+    (weights summed per feature in feature order, normalised by the sum in word order), stopped words dropped;
+    all weighting / normalisation modes, levelsup beyond the tree (node = root), ragged and empty frames."""
+    w, h = 1241, 376
+    G = _ext(gx, w, h, 2000)
+    lists = [G(synth.mono_frame(400 + i, w, h))[1] for i in range(2)]
+    V = synth.vocabulary(17 + L, k, L, stop_fraction=0.05, train=lists[0])
+    lists.append(lists[1][:333]); lists.append(lists[0][:0]); lists.append(np.repeat(lists[0][:1], 40, 0))   # one word, 40 times
+    voc = gx.ORBVocabulary(V, weighting=weighting, norm=norm)
+    got = voc.transform(lists, levelsup)
+    for f, d in enumerate(lists):
+        wo, no, bw, bv = oracle.voc_transform(V, d, levelsup, weighting, norm)
+        g = got[f]
+        assert np.array_equal(g[0], wo) and np.array_equal(g[1], no), f
+        assert np.array_equal(g[2], bw), f
+        assert np.array_equal(g[3].view(np.uint64), bv.view(np.uint64)), (f, np.abs(g[3] - bv).max() if len(bv) else 0)
+    assert len(got[0][2]) > 100 and (got[0][0] < 0).any()
+    voc.close()

@@ -114,3 +114,38 @@ def test_stereo_and_matchers_behave(oracle):
     assert nn == (mm >= 0).sum() and nn > 100
     used = mm[mm >= 0]
     assert len(set(used.tolist())) == len(used)                   # greedy exclusion: B side unique
+
+
+# ---- DBoW2 transform (K15): the oracle against the reference's own Thirdparty/DBoW2 ----------------------------
+import importlib.util as _ilu
+
+_spec = _ilu.spec_from_file_location("gen_golden_bow", os.path.join(os.path.dirname(__file__), "..", "tools", "gen_golden_bow.py"))
+_gb = _ilu.module_from_spec(_spec); _spec.loader.exec_module(_gb)
+GOLD_BOW = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "ref_bow.json")))
+
+
+@pytest.mark.parametrize("case", GOLD_BOW["cases"], ids=lambda c: f"k{c['k']}L{c['L']}w{c['weighting']}s{c['scoring']}")
+def test_oracle_bow_transform_matches_reference_golden(oracle, case):
+    """tests/golden/ref_bow.json was written by the reference's DBoW2 compiled in place (tools/gen_golden_bow.py)."""
+    V = synth.vocabulary(case["seed"], case["k"], case["L"], stop_fraction=0.05)
+    assert hashlib.sha256(V["desc"].tobytes() + V["weight"].tobytes()).hexdigest() == case["voc_sha256"], "synthetic vocabulary drifted"
+    D = _gb.descriptors(case["seed"] + 100, V)
+    assert hashlib.sha256(D.tobytes()).hexdigest() == case["desc_sha256"]
+    wo, no, bw, bv = oracle.voc_transform(V, D, case["levelsup"], case["weighting"], case["norm"])
+    assert len(bw) == case["bow_size"] and int((no < 0).sum()) == case["stopped"]
+    assert bw[:4].tolist() == case["first_words"] and [float(v).hex() for v in bv[:4]] == case["first_values_hex"]
+    assert hashlib.sha256(bw.tobytes()).hexdigest() == case["bow_words_sha256"]
+    assert hashlib.sha256(bv.tobytes()).hexdigest() == case["bow_values_sha256"]
+    assert hashlib.sha256(no.tobytes()).hexdigest() == case["nodes_sha256"]
+
+
+def test_oracle_bow_transform_matches_reference_binary(oracle):
+    if not oracle.ref_dbow_available():
+        pytest.skip("oracle/_ref/orbref_dbow not built (needs /root/reference: make -C oracle ref)")
+    for seed, k, L, levelsup, scoring, weighting, norm in [(31, 10, 3, 2, 0, 0, 1), (32, 7, 4, 4, 1, 1, 2), (33, 9, 3, 1, 5, 2, 0)]:
+        V = synth.vocabulary(seed, k, L, stop_fraction=0.1)
+        D = _gb.descriptors(seed, V, 900)
+        node, bw, bv = oracle.ref_dbow_transform(V, D, levelsup, scoring, weighting)
+        wo, no, obw, obv = oracle.voc_transform(V, D, levelsup, weighting, norm)
+        assert np.array_equal(no, node) and np.array_equal(obw, bw)
+        assert np.array_equal(obv.view(np.uint64), bv.view(np.uint64))
