@@ -293,4 +293,28 @@ inline void fast9_16(const uint8_t* img, int w, int h, int pitch, int t, std::ve
     }
 }
 
+// cv::undistortPoints(src, dst, K, distCoef, noArray(), K) as Frame::UndistortKeyPoints and
+// Frame::ComputeImageBounds call it (src/Frame.cc:404-434, 436-464): OpenCV 4.13 normalises with K,
+// runs exactly 5 fixed-point iterations of the radial/tangential model in double (the 6-argument
+// overload passes TermCriteria(MAX_ITER, 5, 0.01), so there is no early exit on the error), and
+// re-projects with P = K.  d = {k1, k2, p1, p2, k3}.  Pinned against cv2.undistortPoints in
+// tests/test_oracle_cv2.py.
+struct Camera { float fx, fy, cx, cy, d[5]; };
+inline void undistort_point(const Camera& c, float u, float v, float* ox, float* oy) {
+  const double fx = c.fx, fy = c.fy, cx = c.cx, cy = c.cy, ifx = 1. / fx, ify = 1. / fy;
+  double k[12] = {c.d[0], c.d[1], c.d[2], c.d[3], c.d[4], 0, 0, 0, 0, 0, 0, 0};
+  double x = ((double)u - cx) * ifx, y = ((double)v - cy) * ify;
+  const double x0 = x, y0 = y;
+  for (int j = 0; j < 5; ++j) {
+    const double r2 = x * x + y * y;
+    const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+    if (icdist < 0) { x = ((double)u - cx) * ifx; y = ((double)v - cy) * ify; break; }
+    const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+    const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+    x = (x0 - deltaX) * icdist;
+    y = (y0 - deltaY) * icdist;
+  }
+  const double xx = fx * x + 0. * y + cx, yy = 0. * x + fy * y + cy, ww = 1. / (0. * x + 0. * y + 1.);
+  *ox = (float)(xx * ww); *oy = (float)(yy * ww);
+}
 }  // namespace orbo

@@ -151,6 +151,85 @@ def voc_transform(voc, desc, levelsup=4, weighting=0, norm=1):
     return wo[:n], no[:n], bw[:m].copy(), bv[:m].copy()
 
 
+REF_SLAM_BIN = os.path.join(_HERE, "_ref", "orbref_slam")
+
+
+def ref_slam_available():
+    return os.path.exists(REF_SLAM_BIN)
+
+
+def _calib_bytes(cam, bf, th_depth=35.0):
+    """cam: (fx, fy, cx, cy[, k1, k2, p1, p2, k3])"""
+    c = np.zeros(11, np.float32); c[:len(cam)] = np.asarray(cam, np.float32); c[9] = bf; c[10] = th_depth
+    return c.tobytes()
+
+
+def _run_ref_slam(cmd, payload):
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        with open(fin, "wb") as f:
+            f.write(payload)
+        subprocess.run([REF_SLAM_BIN, cmd, fin, fout], check=True, capture_output=True)
+        return open(fout, "rb").read()
+
+
+class _Rd:
+    def __init__(self, raw):
+        self.raw, self.off = raw, 0
+
+    def arr(self, dtype, count, shape=None):
+        dt = np.dtype(dtype)
+        a = np.frombuffer(self.raw, dt, count, self.off).copy(); self.off += dt.itemsize * count
+        return a.reshape(shape) if shape is not None else a
+
+    def i32(self):
+        return int(self.arr(np.int32, 1)[0])
+
+    def frame(self):
+        n = self.i32()
+        return dict(keys=self.arr(KP_DTYPE, n), keys_un=self.arr(KP_DTYPE, n), desc=self.arr(np.uint8, 32 * n, (n, 32)),
+                    u_right=self.arr(np.float32, n), depth=self.arr(np.float32, n))
+
+
+def ref_slam_stereo(imL, imR, nfeatures, cam, bf):
+    """The REFERENCE's stereo Frame constructor (src/Frame.cc:61-117): extraction of both eyes + ComputeStereoMatches."""
+    imL = np.ascontiguousarray(imL, np.uint8); imR = np.ascontiguousarray(imR, np.uint8); h, w = imL.shape
+    rd = _Rd(_run_ref_slam("stereo", np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, bf) + imL.tobytes() + imR.tobytes()))
+    F = rd.frame(); nr = rd.i32()
+    F["keys_right"] = rd.arr(KP_DTYPE, nr); F["desc_right"] = rd.arr(np.uint8, 32 * nr, (nr, 32))
+    return F
+
+
+def ref_slam_init(im1, im2, nfeatures, cam, ratio=0.9, window=100, check_ori=True):
+    """The REFERENCE's monocular Frame constructor twice + ORBmatcher::SearchForInitialization.
+    Returns (F1, F2, nmatches, vnMatches12, vbPrevMatched after the call)."""
+    im1 = np.ascontiguousarray(im1, np.uint8); im2 = np.ascontiguousarray(im2, np.uint8); h, w = im1.shape
+    pay = (np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, 0.0) + np.float32(ratio).tobytes() +
+           np.array([window, int(check_ori)], np.int32).tobytes() + im1.tobytes() + im2.tobytes())
+    rd = _Rd(_run_ref_slam("init", pay))
+    F1, F2 = rd.frame(), rd.frame()
+    n = rd.i32(); n1 = len(F1["keys"])
+    return F1, F2, n, rd.arr(np.int32, n1), rd.arr(np.float32, 2 * n1, (n1, 2))
+
+
+def ref_slam_grid(im, nfeatures, cam, queries):
+    """The REFERENCE's monocular Frame constructor on a (possibly distorted) camera: mvKeysUn, image bounds, mGrid, and
+    Frame::GetFeaturesInArea for queries [(x, y, r, minLevel, maxLevel), ...]."""
+    im = np.ascontiguousarray(im, np.uint8); h, w = im.shape
+    q = b"".join(np.array(t[:3], np.float32).tobytes() + np.array(t[3:5], np.int32).tobytes() for t in queries)
+    rd = _Rd(_run_ref_slam("grid", np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, 0.0) + np.int32(len(queries)).tobytes() + q + im.tobytes()))
+    F = rd.frame()
+    bounds = rd.arr(np.float32, 6)
+    cells = []
+    for _ in range(64 * 48):
+        c = rd.i32(); cells.append(rd.arr(np.int32, c))
+    hits = []
+    for _ in queries:
+        c = rd.i32(); hits.append(rd.arr(np.int32, c))
+    return F, bounds, cells, hits
+
+
 def ref_dbow_available():
     return os.path.exists(os.path.join(_HERE, "_ref", "orbref_dbow"))
 

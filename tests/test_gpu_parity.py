@@ -616,3 +616,42 @@ def test_bow_transform(gx, oracle, k, L, levelsup, weighting, norm):
         assert np.array_equal(g[3].view(np.uint64), bv.view(np.uint64)), (f, np.abs(g[3] - bv).max() if len(bv) else 0)
     assert len(got[0][2]) > 100 and (got[0][0] < 0).any()
     voc.close()
+
+
+def test_cuda_path_reproduces_reference_goldens(gx):
+    """The CUDA path against tests/golden/ref_slam.json directly — digests written by the reference's own Frame.cc /
+    ORBmatcher.cc compiled in place (tools/gen_golden_slam.py), no oracle in between: stereo uRight / depth bits of the
+    stereo Frame constructor, SearchForInitialization matches, mvKeysUn / bounds / grid / GetFeaturesInArea."""
+    import hashlib, importlib.util, json, os
+    here = os.path.dirname(__file__)
+    gold = json.load(open(os.path.join(here, "golden", "ref_slam.json")))
+    spec = importlib.util.spec_from_file_location("gen_golden_slam", os.path.join(here, "..", "tools", "gen_golden_slam.py"))
+    gs = importlib.util.module_from_spec(spec); spec.loader.exec_module(gs)
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    for case in gold["stereo"]:
+        cfg = dict(kitti=synth.KITTI, euroc=synth.EUROC)[case["name"]]
+        L, R, _ = synth.stereo_pair(case["seed"], cfg["w"], cfg["h"])
+        G = _ext(gx, cfg["w"], cfg["h"], cfg["nfeatures"], batch=2)
+        G.extract_batch(np.stack([L, R]))
+        ur, dp, nm = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=1, slotL0=0, slotR0=1)
+        (kl, _), (kr, _) = G.fetch(0, 2)
+        n = len(kl)
+        assert n == case["n"] and len(kr) == case["n_right"] and sha(kl) == case["keys_sha256"]
+        assert int(nm[0]) == case["matches"] and sha(ur[0, :n]) == case["u_right_sha256"] and sha(dp[0, :n]) == case["depth_sha256"]
+    for case in gold["init"]:
+        a, b, _ = synth.mono_pair(case["seed"], 640, 480)
+        G = _ext(gx, 640, 480, 1000)
+        k1, d1 = G(a); k2, d2 = G(b)
+        prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+        n, m12 = gx.ORBmatcher(case["ratio"], case["check_ori"]).SearchForInitialization(gx.Frame(k1, d1, 640, 480), gx.Frame(k2, d2, 640, 480), prev, case["window"])
+        assert n == case["nmatches"] and sha(m12.astype(np.int32)) == case["matches12_sha256"] and sha(prev) == case["prev_sha256"]
+    for case in gold["grid"]:
+        w, h = case["w"], case["h"]
+        k, _ = _ext(gx, w, h, case["nfeatures"])(synth.mono_frame(case["frame"], w, h))
+        FG = gx.FrameGrids([k], case["cam"], w, h)
+        assert sha(FG.mvKeysUn[0]) == case["keys_un_sha256"] and [float(v).hex() for v in FG.bounds] == case["bounds_hex"]
+        cells = [FG.cell(0, c // 48, c % 48) for c in range(64 * 48)]
+        assert sha(np.concatenate([np.array([len(c)], np.int32) for c in cells] + cells)) == case["cells_sha256"]
+        hits, cnt = FG.GetFeaturesInArea([(0,) + q for q in gs.grid_queries(case["frame"], w, h)])
+        assert int(cnt.sum()) == case["total_hits"]
+        assert sha(np.concatenate([np.array([len(x)], np.int32) for x in hits] + hits)) == case["hits_sha256"]

@@ -149,3 +149,66 @@ def test_oracle_bow_transform_matches_reference_binary(oracle):
         wo, no, obw, obv = oracle.voc_transform(V, D, levelsup, weighting, norm)
         assert np.array_equal(no, node) and np.array_equal(obw, bw)
         assert np.array_equal(obv.view(np.uint64), bv.view(np.uint64))
+
+
+# ---- Frame.cc / ORBmatcher.cc: the oracle against the reference's own sources compiled in place (oracle/_ref/orbref_slam) ----
+_spec2 = _ilu.spec_from_file_location("gen_golden_slam", os.path.join(os.path.dirname(__file__), "..", "tools", "gen_golden_slam.py"))
+_gs = _ilu.module_from_spec(_spec2); _spec2.loader.exec_module(_gs)
+GOLD_SLAM = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "ref_slam.json")))
+_sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.mark.parametrize("case", GOLD_SLAM["stereo"], ids=lambda c: f"{c['name']}-{c['seed']}")
+def test_oracle_stereo_matches_reference_golden(oracle, case):
+    """uRight / depth of the reference's stereo Frame constructor (Frame::ComputeStereoMatches, src/Frame.cc:466-640)."""
+    cfg = dict(kitti=synth.KITTI, euroc=synth.EUROC)[case["name"]]
+    L, R, _ = synth.stereo_pair(case["seed"], cfg["w"], cfg["h"])
+    EL, ER = oracle.Extractor(cfg["nfeatures"]), oracle.Extractor(cfg["nfeatures"])
+    kl, dl = EL.extract(L); kr, dr = ER.extract(R)
+    assert len(kl) == case["n"] and len(kr) == case["n_right"] and _sha(kl) == case["keys_sha256"]
+    ur, dp, _, _ = oracle.stereo(EL, ER, kl, dl, kr, dr, cfg["bf"], cfg["fx"])
+    assert int((ur >= 0).sum()) == case["matches"]
+    assert _sha(ur) == case["u_right_sha256"] and _sha(dp) == case["depth_sha256"]
+
+
+@pytest.mark.parametrize("case", GOLD_SLAM["init"], ids=lambda c: f"{c['seed']}-w{c['window']}")
+def test_oracle_search_for_initialization_matches_reference_golden(oracle, case):
+    a, b, _ = synth.mono_pair(case["seed"], 640, 480)
+    E = oracle.Extractor(1000)
+    k1, d1 = E.extract(a); k2, d2 = E.extract(b)
+    assert len(k1) == case["n1"] and len(k2) == case["n2"]
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    m12, n, prev = oracle.search_init(k1, d1, k2, d2, 640, 480, prev, case["ratio"], case["window"], case["check_ori"])
+    assert n == case["nmatches"] and _sha(m12) == case["matches12_sha256"] and _sha(prev) == case["prev_sha256"]
+
+
+@pytest.mark.parametrize("case", GOLD_SLAM["grid"], ids=lambda c: c["name"])
+def test_oracle_frame_grid_matches_reference_golden(oracle, case):
+    """mvKeysUn, image bounds, mGrid and GetFeaturesInArea of the reference's monocular Frame constructor."""
+    w, h = case["w"], case["h"]
+    k, _ = oracle.Extractor(case["nfeatures"]).extract(synth.mono_frame(case["frame"], w, h))
+    kun, b, cs, items = oracle.undistort_grid(case["cam"], k, w, h)
+    assert len(k) == case["n"] and _sha(kun) == case["keys_un_sha256"]
+    assert [float(v).hex() for v in b] == case["bounds_hex"]
+    cells = [items[cs[c]:cs[c + 1]] for c in range(64 * 48)]
+    assert _sha(np.concatenate([np.array([len(c)], np.int32) for c in cells] + cells)) == case["cells_sha256"]
+    hits = [oracle.features_in_area(kun, b, *q) for q in _gs.grid_queries(case["frame"], w, h)]
+    assert sum(len(x) for x in hits) == case["total_hits"]
+    assert _sha(np.concatenate([np.array([len(x)], np.int32) for x in hits] + hits)) == case["hits_sha256"]
+
+
+def test_oracle_matches_reference_slam_binary(oracle):
+    if not oracle.ref_slam_available():
+        pytest.skip("oracle/_ref/orbref_slam not built (needs /root/reference: make -C oracle ref)")
+    cfg = synth.KITTI
+    L, R, _ = synth.stereo_pair(41, cfg["w"], cfg["h"])
+    F = oracle.ref_slam_stereo(L, R, cfg["nfeatures"], _gs.KITTI_CAM, cfg["bf"])
+    EL, ER = oracle.Extractor(cfg["nfeatures"]), oracle.Extractor(cfg["nfeatures"])
+    kl, dl = EL.extract(L); kr, dr = ER.extract(R)
+    ur, dp, _, _ = oracle.stereo(EL, ER, kl, dl, kr, dr, cfg["bf"], cfg["fx"])
+    assert kl.tobytes() == F["keys"].tobytes() and ur.tobytes() == F["u_right"].tobytes() and dp.tobytes() == F["depth"].tobytes()
+    a, b, _ = synth.mono_pair(42, 640, 480)
+    F1, F2, n, m12, prev = oracle.ref_slam_init(a, b, 1000, _gs.TUM1[:4], 0.9, 100, True)
+    p0 = np.stack([F1["keys_un"]["x"], F1["keys_un"]["y"]], 1).astype(np.float32)
+    om, on, oprev = oracle.search_init(F1["keys_un"], F1["desc"], F2["keys_un"], F2["desc"], 640, 480, p0, 0.9, 100, True)
+    assert on == n and np.array_equal(om, m12) and oprev.tobytes() == prev.tobytes()
