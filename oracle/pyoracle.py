@@ -230,6 +230,68 @@ def ref_slam_grid(im, nfeatures, cam, queries):
     return F, bounds, cells, hits
 
 
+def kf_rule(i, salt, pct):
+    """Which stereo features get a MapPoint in ref_slam_kf (mirrors kf_rule in oracle/ref_slam_cmds.inc)."""
+    return int((((i + 1) * 2654435761 + salt * 40503) & 0xFFFFFFFF) >> 16) % 100 < pct
+
+
+def ref_slam_kf(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, pct1=60, pct2=50, ratio_kk=0.75, ratio_kf=0.7,
+                th_proj=3.0, th_last=15.0, check_ori=True, only_stereo=False, mono=False):
+    """Two real KeyFrames with real MapPoints and DBoW2 feature vectors, and the REFERENCE's SearchByBoW (both forms),
+    SearchForTriangulation and SearchByProjection (both forms) on them.  voc = flat vocabulary dict (written out in the
+    reference's text format, L1_NORM + TF_IDF).  Returns a dict of everything the restatements need and the results."""
+    import tempfile
+    ims = [np.ascontiguousarray(x, np.uint8) for x in (L1, R1, L2, R2)]
+    h, w = ims[0].shape
+    with tempfile.TemporaryDirectory() as td:
+        vp = os.path.join(td, "voc.txt")
+        write_vocabulary_text(voc, vp, 0, 0)
+        pb = vp.encode()
+        pay = (np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, bf) + np.array([pct1, pct2], np.int32).tobytes() +
+               np.array([ratio_kk, ratio_kf, th_proj, th_last], np.float32).tobytes() +
+               np.array([int(check_ori), int(only_stereo), int(mono)], np.int32).tobytes() +
+               np.asarray(T1, np.float32).reshape(16).tobytes() + np.asarray(T2, np.float32).reshape(16).tobytes() +
+               np.asarray(F12, np.float32).reshape(9).tobytes() + np.int32(len(pb)).tobytes() + pb + b"".join(x.tobytes() for x in ims))
+        rd = _Rd(_run_ref_slam("kf", pay))
+    o = dict(F1=rd.frame(), F2=rd.frame())
+    n1, n2 = len(o["F1"]["keys"]), len(o["F2"]["keys"])
+    o["node1"], o["node2"], o["nodec"] = rd.arr(np.int32, n1), rd.arr(np.int32, n2), rd.arr(np.int32, n2)
+    o["has1"], o["has2"] = rd.arr(np.uint8, n1), rd.arr(np.uint8, n2)
+    m = rd.i32()
+    mp = np.zeros(m, np.dtype([("idx", "<i4"), ("xw", "<f4", 3), ("normal", "<f4", 3), ("desc", "u1", 32), ("obs", "<i4"), ("dmin", "<f4"), ("dmax", "<f4")]))
+    for k in range(m):
+        mp[k] = (rd.i32(), rd.arr(np.float32, 3), rd.arr(np.float32, 3), rd.arr(np.uint8, 32), rd.i32(), rd.arr(np.float32, 1)[0], rd.arr(np.float32, 1)[0])
+    o["mps1"] = mp; o["Ow1"] = rd.arr(np.float32, 3)
+    o["bow_kk"] = (rd.i32(), rd.arr(np.int32, n1))
+    o["bow_kf"] = (rd.i32(), rd.arr(np.int32, n2))
+    nt, npairs = rd.i32(), rd.i32()
+    o["tri"] = (nt, rd.arr(np.int32, 2 * npairs, (npairs, 2)))
+    trk = np.zeros(m, np.dtype([("inview", "<i4"), ("projx", "<f4"), ("projy", "<f4"), ("projxr", "<f4"), ("level", "<i4"), ("viewcos", "<f4")]))
+    for k in range(m):
+        trk[k] = (rd.i32(), *rd.arr(np.float32, 3), rd.i32(), rd.arr(np.float32, 1)[0])
+    o["track"] = trk
+    o["proj"] = (rd.i32(), rd.arr(np.int32, n2))
+    o["proj_last"] = (rd.i32(), rd.arr(np.int32, n2))
+    return o
+
+
+def ref_slam_distinct(descriptor_lists, image, nfeatures=2000, cam=(700.0, 700.0, 600.0, 180.0)):
+    """The REFERENCE's MapPoint::ComputeDistinctiveDescriptors on real MapPoints / KeyFrames: descriptor_lists[m] = (N_m, 32)
+    observed descriptors of map point m (N_m >= 1).  Returns the (M, 32) chosen descriptors."""
+    image = np.ascontiguousarray(image, np.uint8); h, w = image.shape
+    M = len(descriptor_lists); nmax = max(len(d) for d in descriptor_lists)
+    desc = np.zeros((M, nmax, 32), np.uint8); counts = np.zeros(M, np.int32)
+    for m, d in enumerate(descriptor_lists):
+        counts[m] = len(d); desc[m, :len(d)] = d
+    pay = (np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, 40.0) + np.array([M, nmax], np.int32).tobytes() +
+           counts.tobytes() + desc.tobytes() + image.tobytes())
+    rd = _Rd(_run_ref_slam("distinct", pay))
+    out = np.zeros((M, 32), np.uint8)
+    for m in range(M):
+        rd.i32(); out[m] = rd.arr(np.uint8, 32)
+    return out
+
+
 def ref_dbow_available():
     return os.path.exists(os.path.join(_HERE, "_ref", "orbref_dbow"))
 

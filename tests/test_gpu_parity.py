@@ -655,3 +655,67 @@ def test_cuda_path_reproduces_reference_goldens(gx):
         hits, cnt = FG.GetFeaturesInArea([(0,) + q for q in gs.grid_queries(case["frame"], w, h)])
         assert int(cnt.sum()) == case["total_hits"]
         assert sha(np.concatenate([np.array([len(x)], np.int32) for x in hits] + hits)) == case["hits_sha256"]
+
+
+def test_cuda_keyframe_searches_reproduce_reference(gx):
+    """K7 / K8 / K9 / K12 / K13 / K14 / K15 against what the REFERENCE's ORBmatcher.cc / MapPoint.cc produced on real KeyFrames
+    and MapPoints (tests/golden/ref_kf_*.npz, ref_slam.json written by oracle/_ref/orbref_slam): frames, stereo depth and
+    feature-vector nodes come from the CUDA path itself, only the MapPoint / isInFrustum fields come from the fixture."""
+    import hashlib, importlib.util, os
+    spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
+    kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
+    from oracle.pyoracle import kf_rule                        # index rule only, no oracle arithmetic
+    gs, P = kc.gs, kc.gs.KF_PARAMS
+    cfg = synth.KITTI
+    w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
+    for case in kc.GOLD["kf"]:
+        ims, V, T1, T2, F12 = gs.kf_case_inputs(case["seed"], case["L"])
+        fx = np.load(os.path.join(kc.HERE, "golden", case["fixture"]))
+        ori, only_stereo = case["check_ori"], case["only_stereo"]
+        G = _ext(gx, w, h, nf, batch=4)
+        G.extract_batch(np.stack([ims[0], ims[2], ims[1], ims[3]]))
+        ur, dp, _ = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=2, slotL0=0, slotR0=2)
+        (k1, d1), (k2, d2) = G.fetch(0, 2)
+        ur1, dp1, ur2, dp2 = ur[0, :len(k1)], dp[0, :len(k1)], ur[1, :len(k2)], dp[1, :len(k2)]
+        scale, sigma2 = np.asarray(G.GetScaleFactors(), np.float32), np.asarray(G.GetScaleSigmaSquares(), np.float32)
+        voc = gx.ORBVocabulary(V)
+        (_, node1, _, _), (_, node2, _, _) = voc.transform([d1, d2], 4)
+        voc.close()
+        assert np.array_equal(node1, fx["node1"]) and np.array_equal(node2, fx["node2"])        # K15 vs the reference's mFeatVec
+        has1 = np.array([dp1[i] > 0 and kf_rule(i, 0, P["pct1"]) for i in range(len(k1))], np.uint8)
+        has2 = np.array([dp2[i] > 0 and kf_rule(i, 1, P["pct2"]) for i in range(len(k2))], np.uint8)
+        assert np.array_equal(has1, fx["has1"]) and np.array_equal(has2, fx["has2"])
+        # K12: SearchByBoW(KF, KF) and (KF, Frame)
+        M = gx.ORBmatcher(P["ratio_kk"], ori)
+        nm, m12 = M.SearchByBoWNodes([(d1, k1["angle"], has1, node1)], [(d2, k2["angle"], has2, node2)], strict=True)
+        assert nm[0] == case["n_bow_kk"] and np.array_equal(m12[0], fx["bow_kk"])
+        if case["L"] <= 4:                                       # K7: one bucket = brute force over the valid features
+            va, vb = has1.astype(bool), has2.astype(bool)
+            nk, mk = M.SearchByBoW(d1[va], k1["angle"][va], d2[vb], k2["angle"][vb], strict=True)
+            full = np.full(len(va), -1, np.int32); full[np.nonzero(va)[0][mk >= 0]] = np.nonzero(vb)[0][mk[mk >= 0]]
+            assert nk == case["n_bow_kk"] and np.array_equal(full, fx["bow_kk"])
+        nm, m12 = gx.ORBmatcher(P["ratio_kf"], ori).SearchByBoWNodes([(d1, k1["angle"], has1, node1)], [(d2, k2["angle"], np.ones(len(d2), np.uint8), node2)], strict=False)
+        inv = np.full(len(d2), -1, np.int32); ok = m12[0] >= 0; inv[m12[0][ok]] = np.nonzero(ok)[0]
+        assert nm[0] == case["n_bow_kf"] and np.array_equal(inv, fx["bow_kf"])
+        # K14: SearchForTriangulation
+        nm, m12 = gx.ORBmatcher(0.6, ori).SearchForTriangulation([dict(kps=k1, desc=d1, has_mp=has1, u_right=ur1, node=node1)],
+                                                                 [dict(kps=k2, desc=d2, has_mp=has2, u_right=ur2, node=node2)], [F12], [(T2[:3, :3], T2[:3, 3])],
+                                                                 [fx["Ow1"]], [np.array(gs.KITTI_CAM, np.float32)], scale, sigma2, bOnlyStereo=only_stereo)
+        assert nm[0] == case["n_tri"] and np.array_equal(np.stack([np.nonzero(m12[0] >= 0)[0], m12[0][m12[0] >= 0]], 1).astype(np.int32), fx["tri"])
+        # K8: SearchByProjection(Frame, MapPoints) with the reference's isInFrustum fields
+        mp, tr = fx["mps1"], fx["track"]
+        mpd = dict(inview=tr["inview"].astype(np.uint8), projx=tr["projx"], projy=tr["projy"], projxr=tr["projxr"], level=tr["level"], viewcos=tr["viewcos"],
+                   desc=mp["desc"], obs=mp["obs"])
+        Fc = gx.Frame(k2, d2, w, h)
+        n, a, _ = gx.ORBmatcher(0.8, True).SearchByProjection(Fc, ur2, scale, mpd, P["th_proj"])
+        assert n == case["n_proj"] and np.array_equal(a, fx["proj"])
+        # K9: SearchByProjection(CurrentFrame, LastFrame)
+        n1 = len(k1)
+        last = dict(valid=has1, xw=np.zeros((n1, 3), np.float32), octave=k1["octave"], angle=k1["angle"], desc=np.zeros((n1, 32), np.uint8), obs=np.zeros(n1, np.int32))
+        last["xw"][mp["idx"]] = mp["xw"]; last["desc"][mp["idx"]] = mp["desc"]; last["obs"][mp["idx"]] = mp["obs"]
+        n, a, _ = gx.ORBmatcher(0.9, ori).SearchByProjectionFrame(Fc, ur2, scale, T2[:3, :3], T2[:3, 3], gs.KITTI_CAM + (cfg["bf"],), last, P["th_last"], 0)
+        assert n == case["n_proj_last"] and np.array_equal(a, fx["proj_last"])
+    # K13 against MapPoint::ComputeDistinctiveDescriptors of the reference
+    lists = gs.distinct_lists(kc.GOLD["distinct"]["seed"])
+    best, out = gx.ComputeDistinctiveDescriptors(lists)
+    assert hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest() == kc.GOLD["distinct"]["chosen_sha256"]

@@ -212,3 +212,66 @@ def test_oracle_matches_reference_slam_binary(oracle):
     p0 = np.stack([F1["keys_un"]["x"], F1["keys_un"]["y"]], 1).astype(np.float32)
     om, on, oprev = oracle.search_init(F1["keys_un"], F1["desc"], F2["keys_un"], F2["desc"], 640, 480, p0, 0.9, 100, True)
     assert on == n and np.array_equal(om, m12) and oprev.tobytes() == prev.tobytes()
+
+
+# ---- KeyFrame / MapPoint based searches: the oracle against results the reference's own ORBmatcher.cc produced on real
+#      KeyFrames and MapPoints (tests/golden/ref_kf_*.npz written by oracle/_ref/orbref_slam) --------------------------------
+_spec3 = _ilu.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
+_kc = _ilu.module_from_spec(_spec3); _spec3.loader.exec_module(_kc)
+
+
+@pytest.mark.parametrize("case", GOLD_SLAM["kf"], ids=lambda c: f"kf{c['seed']}-L{c['L']}")
+def test_oracle_keyframe_searches_match_reference(oracle, case):
+    c = _kc.build(oracle, case)
+    F1, F2, fx = c["F1"], c["F2"], c["fx"]
+    w, h = c["cfg"]["w"], c["cfg"]["h"]
+    ori, only_stereo = case["check_ori"], case["only_stereo"]
+    assert _sha(F1["keys"]) == case["keys1_sha256"] and _sha(F2["u_right"]) == case["u_right2_sha256"]
+    # what the restatements derive themselves agrees with what the reference's KeyFrames held
+    assert np.array_equal(c["node1"], fx["node1"]) and np.array_equal(c["node2"], fx["node2"]) and np.array_equal(c["node2"], fx["nodec"])
+    assert np.array_equal(c["has1"], fx["has1"]) and np.array_equal(c["has2"], fx["has2"])
+    P = _kc.gs.KF_PARAMS
+    # SearchByBoW(KF, KF)  src/ORBmatcher.cc:522
+    m, n = oracle.search_by_bow(F1["desc"], F1["keys"]["angle"], c["has1"], c["node1"], F2["desc"], F2["keys"]["angle"], c["has2"], c["node2"],
+                                50, P["ratio_kk"], ori, True)
+    assert n == case["n_bow_kk"] and np.array_equal(m, fx["bow_kk"])
+    if case["L"] <= 4:                                   # one bucket: the brute-force form (K7) gives the same as the bucketed one
+        va, vb = c["has1"].astype(bool), c["has2"].astype(bool)
+        mk, nk = oracle.knn_ratio(F1["desc"][va], F1["keys"]["angle"][va], F2["desc"][vb], F2["keys"]["angle"][vb], 50, P["ratio_kk"], ori, True)
+        full = np.full(len(va), -1, np.int32); full[np.nonzero(va)[0][mk >= 0]] = np.nonzero(vb)[0][mk[mk >= 0]]
+        assert nk == n and np.array_equal(full, m)
+    # SearchByBoW(KF, Frame)  :159  (the reference indexes its result by frame feature)
+    m, n = oracle.search_by_bow(F1["desc"], F1["keys"]["angle"], c["has1"], c["node1"], F2["desc"], F2["keys"]["angle"], np.ones(len(F2["desc"]), np.uint8),
+                                c["node2"], 50, P["ratio_kf"], ori, False)
+    inv = np.full(len(F2["desc"]), -1, np.int32); ok = m >= 0; inv[m[ok]] = np.nonzero(ok)[0]
+    assert n == case["n_bow_kf"] and np.array_equal(inv, fx["bow_kf"])
+    # SearchForTriangulation  :657
+    T2 = c["T2"]
+    m, n = oracle.search_for_triangulation(F1["keys"], F1["desc"], c["has1"], F1["u_right"], c["node1"], F2["keys"], F2["desc"], c["has2"], F2["u_right"],
+                                           c["node2"], c["F12"], np.concatenate([T2[:3, :3].reshape(9), T2[:3, 3]]), fx["Ow1"], np.array(c["cam"], np.float32),
+                                           c["scale"], c["sigma2"], only_stereo, ori)
+    assert n == case["n_tri"] and np.array_equal(np.stack([np.nonzero(m >= 0)[0], m[m >= 0]], 1).astype(np.int32), fx["tri"])
+    # SearchByProjection(Frame, MapPoints)  :45, fed with the tracking fields the reference's Frame::isInFrustum produced
+    mp, tr = fx["mps1"], fx["track"]
+    mpd = dict(inview=tr["inview"].astype(np.uint8), projx=tr["projx"], projy=tr["projy"], projxr=tr["projxr"], level=tr["level"], viewcos=tr["viewcos"],
+               desc=mp["desc"], obs=mp["obs"])
+    a, n, _ = oracle.search_projection(F2["keys"], F2["desc"], F2["u_right"], w, h, c["scale"], mpd, P["th_proj"], 0.8)
+    assert n == case["n_proj"] and np.array_equal(a, fx["proj"])
+    # SearchByProjection(CurrentFrame, LastFrame)  :1328
+    n1 = len(F1["keys"])
+    last = dict(valid=c["has1"], xw=np.zeros((n1, 3), np.float32), octave=F1["keys"]["octave"], angle=F1["keys"]["angle"], desc=np.zeros((n1, 32), np.uint8),
+                obs=np.zeros(n1, np.int32))
+    last["xw"][mp["idx"]] = mp["xw"]; last["desc"][mp["idx"]] = mp["desc"]; last["obs"][mp["idx"]] = mp["obs"]
+    a, n, _ = oracle.search_projection_frame(F2["keys"], F2["desc"], F2["u_right"], w, h, c["scale"], T2[:3, :3], T2[:3, 3], c["cam"] + (c["cfg"]["bf"],), last,
+                                             P["th_last"], 0, ori)
+    assert n == case["n_proj_last"] and np.array_equal(a, fx["proj_last"])
+    assert min(case["n_bow_kk"], case["n_bow_kf"], case["n_tri"], case["n_proj"], case["n_proj_last"]) > 20
+
+
+def test_oracle_distinctive_descriptors_match_reference(oracle):
+    """MapPoint::ComputeDistinctiveDescriptors of the reference, run on real MapPoints observed by up to 100 real KeyFrames."""
+    lists = _kc.gs.distinct_lists(GOLD_SLAM["distinct"]["seed"])
+    chosen = np.stack([d[oracle.distinctive_descriptor(d)] for d in lists])
+    assert _sha(chosen) == GOLD_SLAM["distinct"]["chosen_sha256"]
+    if oracle.ref_slam_available():
+        assert np.array_equal(oracle.ref_slam_distinct(lists, synth.mono_frame(1, 1241, 376)), chosen)

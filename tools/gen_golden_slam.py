@@ -28,6 +28,42 @@ def grid_queries(seed, w, h, n=200):
     return out
 
 
+# (seed, vocabulary levels L, only_stereo, mono, check_ori): L = 3 with levelsup 4 puts every feature in the root node,
+# i.e. SearchByBoW degenerates to the one-bucket brute-force search (K7)
+KF_CASES = [(5, 5, False, False, True), (7, 3, False, True, False), (6, 5, True, False, True)]
+KF_PARAMS = dict(pct1=60, pct2=50, ratio_kk=0.75, ratio_kf=0.7, th_proj=3.0, th_last=15.0)
+
+
+def shifted(img, dx, dy, seed):
+    rng = np.random.default_rng(seed)
+    out = np.roll(np.roll(img, dy, 0), dx, 1).astype(np.int16) + rng.integers(-2, 3, img.shape)
+    return np.clip(out, 0, 255).astype(np.uint8)
+
+
+def kf_case_inputs(seed, L):
+    """Two stereo frames (the second = the first shifted by (3, 1) px plus noise), a synthetic vocabulary, poses and F12."""
+    cfg = synth.KITTI
+    L1, R1, _ = synth.stereo_pair(seed, cfg["w"], cfg["h"])
+    L2, R2 = shifted(L1, 3, 1, seed + 1000), shifted(R1, 3, 1, seed + 2000)
+    V = synth.vocabulary(77 + seed, 10, L, stop_fraction=0.0)
+    T1 = np.eye(4, dtype=np.float32); T2 = np.eye(4, dtype=np.float32); T2[:3, 3] = (0.05, -0.02, 0.0)
+    K = np.array([[KITTI_CAM[0], 0, KITTI_CAM[2]], [0, KITTI_CAM[1], KITTI_CAM[3]], [0, 0, 1]], np.float64)
+    t12 = -(T2[:3, 3].astype(np.float64))
+    tx = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]])
+    F12 = (np.linalg.inv(K).T @ tx @ np.linalg.inv(K)).astype(np.float32)
+    return (L1, R1, L2, R2), V, T1, T2, F12
+
+
+def distinct_lists(seed=21):
+    rng = np.random.default_rng(seed)
+    lists = []
+    for n in [1, 2, 3, 4, 5, 8, 31, 32, 33, 64, 100] + list(rng.integers(2, 60, 30)):
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        lists.append(base[None, :] ^ np.packbits(rng.random((n, 256)) < rng.uniform(0.02, 0.25), axis=1))
+    lists.append(np.repeat(rng.integers(0, 256, (1, 32), dtype=np.uint8), 7, 0))
+    return lists
+
+
 if __name__ == "__main__":
     out = {"generator": "tools/gen_golden_slam.py", "source": "oracle/_ref/orbref_slam (reference src/Frame.cc, src/ORBmatcher.cc, ... compiled in place)",
            "stereo": [], "init": [], "grid": []}
@@ -48,5 +84,22 @@ if __name__ == "__main__":
         out["grid"].append(dict(name=name, w=w, h=h, nfeatures=nf, cam=list(cam), frame=frame, n=len(F["keys"]), keys_un_sha256=sha(F["keys_un"]),
                                 bounds_hex=[float(v).hex() for v in b], cells_sha256=sha(np.concatenate([np.array([len(c)], np.int32) for c in cells] + cells)),
                                 hits_sha256=sha(np.concatenate([np.array([len(x)], np.int32) for x in hits] + hits)), total_hits=int(sum(len(x) for x in hits))))
+    # KeyFrame / MapPoint based searches: the reference-made MapPoint fields, isInFrustum tracking fields and results go to
+    # small .npz fixtures (they are inputs the restatements cannot derive without the reference's KeyFrame machinery)
+    out["kf"] = []
+    cfg = synth.KITTI
+    for seed, L, only_stereo, mono, ori in KF_CASES:
+        ims, V, T1, T2, F12 = kf_case_inputs(seed, L)
+        o = O.ref_slam_kf(*ims, cfg["nfeatures"], KITTI_CAM, cfg["bf"], V, T1, T2, F12, check_ori=ori, only_stereo=only_stereo, mono=mono, **KF_PARAMS)
+        name = f"ref_kf_{seed}.npz"
+        np.savez_compressed(os.path.join(ROOT, "tests/golden", name), mps1=o["mps1"], track=o["track"], Ow1=o["Ow1"],
+                            node1=o["node1"], node2=o["node2"], nodec=o["nodec"], has1=o["has1"], has2=o["has2"],
+                            bow_kk=o["bow_kk"][1], bow_kf=o["bow_kf"][1], tri=o["tri"][1], proj=o["proj"][1], proj_last=o["proj_last"][1])
+        out["kf"].append(dict(seed=seed, L=L, only_stereo=only_stereo, mono=mono, check_ori=ori, fixture=name, n1=len(o["F1"]["keys"]),
+                              n2=len(o["F2"]["keys"]), map_points=len(o["mps1"]), keys1_sha256=sha(o["F1"]["keys"]), u_right2_sha256=sha(o["F2"]["u_right"]),
+                              n_bow_kk=o["bow_kk"][0], n_bow_kf=o["bow_kf"][0], n_tri=o["tri"][0], n_proj=o["proj"][0], n_proj_last=o["proj_last"][0]))
+    lists = distinct_lists()
+    chosen = O.ref_slam_distinct(lists, synth.mono_frame(1, 1241, 376))
+    out["distinct"] = dict(seed=21, n=len(lists), chosen_sha256=sha(chosen))
     json.dump(out, open(os.path.join(ROOT, "tests/golden/ref_slam.json"), "w"), indent=1)
     print("wrote", {k: len(v) for k, v in out.items() if isinstance(v, list)})
