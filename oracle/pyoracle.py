@@ -292,6 +292,22 @@ def ref_slam_distinct(descriptor_lists, image, nfeatures=2000, cam=(700.0, 700.0
     return out
 
 
+def ref_slam_bench(imgsL, imgsR, nfeatures, cam, bf, threads, reps=1):
+    """Times the REFERENCE's stereo Frame constructor (extraction of both eyes in two threads + ComputeStereoMatches) on
+    `threads` std::threads, one stereo frame per thread at a time.  Returns (seconds, keypoints, stereo matches)."""
+    import tempfile
+    imgsL = np.ascontiguousarray(imgsL, np.uint8); imgsR = np.ascontiguousarray(imgsR, np.uint8)
+    n, h, w = imgsL.shape
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        with open(fin, "wb") as f:
+            f.write(np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, bf) + np.array([n, threads, reps], np.int32).tobytes())
+            f.write(imgsL.tobytes()); f.write(imgsR.tobytes())
+        res = subprocess.run([REF_SLAM_BIN, "bench", fin, fout], check=True, capture_output=True, text=True)
+    secs, keys, matches = res.stdout.strip().splitlines()[-1].split()
+    return float(secs), int(keys), int(matches)
+
+
 def ref_dbow_available():
     return os.path.exists(os.path.join(_HERE, "_ref", "orbref_dbow"))
 
