@@ -527,7 +527,7 @@ def main():
             O.build()
             os.sched_setaffinity(0, all_cpus)               # the CPU leg gets every core again
             threads = O.hardware_threads()
-            nfr = (4 if reference_built() else 16) * threads    # ~10-30 s of CPU work
+            nfr = 16 * threads                              # ~10-30 s of CPU work
             v, secs, kind = cpu_baseline(nfr, threads)
             how = ("the reference's stereo Frame constructor compiled in place (oracle/_ref/orbref_slam: src/Frame.cc, src/ORBextractor.cc, "
                    f"src/ORBmatcher.cc; OpenCV calls served by oracle/cv_prims.hpp), {max(1, threads // 2)} frames in flight x 2 extractor threads"
@@ -535,7 +535,7 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "stereo frames/s", "cores": threads, "kind": kind,
                                     "sample": f"{nfr} KITTI-shaped stereo pairs, {how}, {threads} host threads, {secs:.1f} s"}
             if kind == "reference":                          # the faster restatement beside it, for scale
-                pv = nfr * 4 / O.bench_stereo(*cpu_sample(nfr * 4), PARAMS, CFG["bf"], CFG["fx"], threads)[0]
+                pv = nfr / O.bench_stereo(*cpu_sample(nfr), PARAMS, CFG["bf"], CFG["fx"], threads)[0]
                 line["cpu_baseline"]["oracle_port_value"] = pv
         else:
             line["cpu_baseline"] = None
