@@ -256,6 +256,46 @@ orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uin
                                             int only_stereo, int check_orientation, int* matches12, int* n_matches,
                                             int on_device, void* stream);
 
+/* The search of ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975; src/LocalMapping.cc:483-534) for n_kfs
+ * independent (keyframe, candidate list) problems.  Keyframe p at index p*cap: kps_un = mvKeysUn, desc, u_right = mvuRight,
+ * n[p] features; its feature grid as orbx_undistort_grid_batch returns it (grid_bounds[6], cell_start, cell_items);
+ * kf_bounds + p*4 = the KeyFrame's own mnMinX, mnMaxX, mnMinY, mnMaxY (ints in the reference, include/KeyFrame.h:185-188);
+ * pose + p*12 = Rcw row-major then tcw; Ow + p*3 = GetCameraCenter(); fx..bf, scale_factors, inv_level_sigma2,
+ * log_scale_factor = mfLogScaleFactor are the keyframe's.  Candidate k of problem p at index p*mcap + k: mp_valid =
+ * (pMP && !pMP->isBad() && !pMP->IsInKeyFrame(pKF)), mp_xw = GetWorldPos(), mp_normal = GetNormal(), mp_min_dist /
+ * mp_max_dist = mfMinDistance / mfMaxDistance (what Get{Min,Max}DistanceInvariance() return divided by 0.8 / 1.2),
+ * mp_desc = GetDescriptor(); m[p] candidates.  best_idx[p*mcap + k] receives bestIdx when bestDist <= TH_LOW, else -1.
+ * The map update of :944-966 (Replace / AddObservation + AddMapPoint, nFused++) stays with the caller, in candidate
+ * order: the search of one candidate does not depend on the updates of the others. */
+orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* desc, const float* u_right, const int* n,
+                                   int n_kfs, int cap, const float* grid_bounds, const int* cell_start,
+                                   const int* cell_items, const float* kf_bounds, const float* pose, const float* Ow,
+                                   float fx, float fy, float cx, float cy, float bf, const float* scale_factors,
+                                   const float* inv_level_sigma2, int nlevels, float log_scale_factor,
+                                   const uint8_t* mp_valid, const float* mp_xw, const float* mp_normal,
+                                   const float* mp_min_dist, const float* mp_max_dist, const uint8_t* mp_desc,
+                                   const int* m, int mcap, float th, int* best_idx, int on_device, void* stream);
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1102-1326; src/LoopClosing.cc:328)
+ * for n_pairs independent keyframe pairs.  Keyframe 1 of pair p at index p*cap (kps1 = mvKeysUn, desc1, n1, its grid
+ * cell_start1 / cell_items1, kf_bounds1, pose1 = Rcw then tcw), keyframe 2 likewise; grid_bounds, fx..cy (pKF1's, as the
+ * reference uses them for both directions), scale_factors, log_scale_factor shared.  xf + p*24 = sR12 (9), t12 (3),
+ * sR21 (9), t21 (3) exactly as :1119-1122 compute them.  The map points of keyframe 1 that take part (pMP && !isBad() &&
+ * !vbAlreadyMatched1[i1]) are listed at index p*mcap: mp1_index = i1, mp1_xw, mp1_min_dist / mp1_max_dist (mfMinDistance /
+ * mfMaxDistance), mp1_desc, m1[p] of them; keyframe 2 likewise with vbAlreadyMatched2.  matches12[p*cap + i1] receives the
+ * feature index in keyframe 2 whose map point becomes vpMatches12[i1] (-1 = left as it was), n_found[p] the return value. */
+orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const int* n1, const int* cell_start1,
+                                      const int* cell_items1, const float* kf_bounds1, const float* pose1,
+                                      const orbx_keypoint* kps2, const uint8_t* desc2, const int* n2, const int* cell_start2,
+                                      const int* cell_items2, const float* kf_bounds2, const float* pose2, int n_pairs,
+                                      int cap, const float* grid_bounds, float fx, float fy, float cx, float cy,
+                                      const float* scale_factors, int nlevels, float log_scale_factor, const float* xf,
+                                      const int* mp1_index, const float* mp1_xw, const float* mp1_min_dist,
+                                      const float* mp1_max_dist, const uint8_t* mp1_desc, const int* m1,
+                                      const int* mp2_index, const float* mp2_xw, const float* mp2_min_dist,
+                                      const float* mp2_max_dist, const uint8_t* mp2_desc, const int* m2, int mcap,
+                                      float th, int* matches12, int* n_found, int on_device, void* stream);
+
 /* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305) for n_points map points.  Map point m:
  * counts[m] observed descriptors (those of the keyframes that are not bad, in mObservations order) at
  * desc + m*kcap*32.  best_idx[m] receives the index of the descriptor with the least median Hamming distance

@@ -89,6 +89,22 @@ int orbo_voc_transform(const uint8_t* vdesc, const int* child_first, const int* 
   return voc_transform(V, desc, n, levelsup, weighting, norm, word_of, node_of, bow_word, bow_val);
 }
 
+// kf = {fx, fy, cx, cy, bf, logScale, minX, maxX, minY, maxY}; xf = R1(9) t1(3) R2(9) t2(3) Ow(3); mode bits: 1 two_step,
+// 2 dist_from_centre, 4 angle_check, 8 stereo_check, 16 invz_double
+void orbo_project_search(const KeyPt* k, const uint8_t* d, const float* uRight, int n, const float* kf, const float* scale,
+                         const float* invSigma2, int nlevels, const float* xf, const uint8_t* valid, const float* xw,
+                         const float* normal, const float* dmin, const float* dmax, const uint8_t* mpDesc, int m, float th, int mode,
+                         int thDist, int* best) {
+  KFSearchView K{k, d, uRight, n, {kf[6], kf[7], kf[8], kf[9]}, scale, invSigma2, nlevels, kf[5], kf[0], kf[1], kf[2], kf[3], kf[4]};
+  FrameGrid grid(k, n, K.bounds);
+  ProjMode M{(mode & 1) != 0, (mode & 2) != 0, (mode & 4) != 0, (mode & 8) != 0, (mode & 16) != 0, thDist};
+  for (int i = 0; i < m; ++i)
+    best[i] = valid[i] ? project_search_one(K, grid, xf, xf + 9, xf + 12, xf + 21, xf + 24, xw + 3 * i, normal + 3 * i, dmin[i], dmax[i],
+                                            mpDesc + 32 * (size_t)i, th, M)
+                       : -1;
+}
+float orbo_logf(float x) { return libm_logf(x); }
+
 int orbo_distinctive_descriptor(const uint8_t* d, int n) { return distinctive_descriptor(d, n); }
 
 int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,

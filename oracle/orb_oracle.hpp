@@ -925,6 +925,74 @@ inline int voc_transform(const VocabView& V, const uint8_t* desc, int n, int lev
   return (int)v.size();
 }
 
+// The projection searches of the back end on flat arrays: ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975)
+// and the two passes of ORBmatcher::SearchBySim3 (:1102-1326).  A map point is carried into the keyframe's camera by one or
+// two rigid / similarity steps (gemm arithmetic: float products, sums left to right), projected, range- and (Fuse) angle-
+// checked, its pyramid level predicted with MapPoint::PredictScale (src/MapPoint.cc:385-400: ceil(logf(dmax/dist)/logScale)),
+// and the best descriptor among the keyframe's features in the window (KeyFrame::GetFeaturesInArea order, levels
+// [pred-1, pred]) is taken.  Returns the keypoint index or -1.
+struct KFSearchView {
+  const KeyPt* k; const uint8_t* d; const float* uRight; int n;
+  float bounds[4];                                   // mnMinX, mnMaxX, mnMinY, mnMaxY
+  const float* scale; const float* invSigma2; int nlevels; float logScale;
+  float fx, fy, cx, cy, bf;
+};
+struct ProjMode {
+  bool two_step;          // Sim3: p = (R2,t2) o (R1,t1);  Fuse: p = (R1,t1)
+  bool dist_from_centre;  // Fuse: dist3D = |p3Dw - Ow|, else |p in the target camera|
+  bool angle_check;       // Fuse: PO.dot(Pn) < 0.5*dist3D rejects
+  bool stereo_check;      // Fuse: chi2 gate on the reprojection error (7.8 stereo / 5.99 mono)
+  bool invz_double;       // 1.0/z (double, then float) vs 1/z (float)
+  int th_dist;            // TH_LOW (Fuse) / TH_HIGH (SearchBySim3)
+};
+inline int project_search_one(const KFSearchView& K, const FrameGrid& grid, const float* R1, const float* t1, const float* R2,
+                              const float* t2, const float* Ow, const float* xw, const float* normal, float dmin, float dmax,   // dmin / dmax = mfMinDistance / mfMaxDistance
+                              const uint8_t* desc, float th, const ProjMode& M) {
+  float p[3], q[3];
+  for (int r = 0; r < 3; ++r) p[r] = ((R1[3 * r] * xw[0] + R1[3 * r + 1] * xw[1]) + R1[3 * r + 2] * xw[2]) + t1[r];
+  if (M.two_step) { for (int r = 0; r < 3; ++r) q[r] = ((R2[3 * r] * p[0] + R2[3 * r + 1] * p[1]) + R2[3 * r + 2] * p[2]) + t2[r]; }
+  else { q[0] = p[0]; q[1] = p[1]; q[2] = p[2]; }
+  if (q[2] < 0.0f) return -1;
+  const float invz = M.invz_double ? (float)(1.0 / (double)q[2]) : 1 / q[2];
+  const float x = q[0] * invz, y = q[1] * invz;
+  const float u = K.fx * x + K.cx, v = K.fy * y + K.cy;
+  if (!(u >= K.bounds[0] && u < K.bounds[1] && v >= K.bounds[2] && v < K.bounds[3])) return -1;   // KeyFrame::IsInImage
+  const float ur = u - K.bf * invz;
+  float PO[3] = {q[0], q[1], q[2]};
+  if (M.dist_from_centre) for (int r = 0; r < 3; ++r) PO[r] = xw[r] - Ow[r];
+  const float dist3D = (float)std::sqrt((double)PO[0] * PO[0] + (double)PO[1] * PO[1] + (double)PO[2] * PO[2]);   // cv::norm: double sums
+  if (dist3D < 0.8f * dmin || dist3D > 1.2f * dmax) return -1;      // Get{Min,Max}DistanceInvariance, src/MapPoint.cc:373-383
+  if (M.angle_check) {
+    const double dot = (double)PO[0] * normal[0] + (double)PO[1] * normal[1] + (double)PO[2] * normal[2];           // Mat::dot: double sums
+    if (dot < 0.5 * dist3D) return -1;
+  }
+  const float ratio = dmax / dist3D;
+  int level = (int)std::ceil(libm_logf(ratio) / K.logScale);
+  if (level < 0) level = 0; else if (level >= K.nlevels) level = K.nlevels - 1;
+  const float radius = th * K.scale[level];
+  std::vector<int> cand;
+  grid.in_area(K.k, u, v, radius, -1, -1, cand);
+  int bestDist = INT_MAX, bestIdx = -1;
+  for (int idx : cand) {
+    const KeyPt& kp = K.k[idx];
+    if (kp.octave < level - 1 || kp.octave > level) continue;
+    if (M.stereo_check) {
+      const float ex = u - kp.x, ey = v - kp.y;
+      if (K.uRight[idx] >= 0) {
+        const float er = ur - K.uRight[idx];
+        const float e2 = ex * ex + ey * ey + er * er;
+        if (e2 * K.invSigma2[kp.octave] > 7.8) continue;
+      } else {
+        const float e2 = ex * ex + ey * ey;
+        if (e2 * K.invSigma2[kp.octave] > 5.99) continue;
+      }
+    }
+    const int dist = hamming256(desc, K.d + 32 * (size_t)idx);
+    if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+  }
+  return bestDist <= M.th_dist ? bestIdx : -1;
+}
+
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305): among the N observed descriptors, the one
 // whose median distance to all of them (itself included, sorted row element [0.5*(N-1)]) is least; first on ties.
 inline int distinctive_descriptor(const uint8_t* d, int N) {

@@ -272,6 +272,15 @@ def ref_slam_kf(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, pct1=60, p
     o["track"] = trk
     o["proj"] = (rd.i32(), rd.arr(np.int32, n2))
     o["proj_last"] = (rd.i32(), rd.arr(np.int32, n2))
+    m2 = rd.i32()
+    mp2 = np.zeros(m2, mp.dtype)
+    for k in range(m2):
+        mp2[k] = (rd.i32(), rd.arr(np.float32, 3), rd.arr(np.float32, 3), rd.arr(np.uint8, 32), rd.i32(), rd.arr(np.float32, 1)[0], rd.arr(np.float32, 1)[0])
+    o["mps2"] = mp2
+    o["log_scale"] = float(rd.arr(np.float32, 1)[0]); o["kf_bounds"] = rd.arr(np.float32, 4); o["inv_sigma2"] = rd.arr(np.float32, 8)
+    o["sim3_xf"] = dict(sR12=rd.arr(np.float32, 9, (3, 3)), t12=rd.arr(np.float32, 3), sR21=rd.arr(np.float32, 9, (3, 3)), t21=rd.arr(np.float32, 3))
+    o["sim3"] = (rd.i32(), rd.arr(np.int32, n1))
+    o["fuse"] = (rd.i32(), rd.arr(np.int32, m))
     return o
 
 
@@ -347,6 +356,25 @@ def ref_dbow_transform(voc, desc, levelsup, scoring, weighting):
             assert idx == sorted(idx)
             node[idx] = int(t[1])
     return node, np.array(bw, np.int32), np.array(bv, np.float64)
+
+
+FUSE_MODE = 2 | 4 | 8            # Fuse(pKF, vpMapPoints, th): distance from the camera centre, viewing angle, chi2 gate, 1/z in float
+SIM3_MODE = 1 | 16               # SearchBySim3 passes: two transforms, distance in the target camera, 1.0/z in double
+
+
+def project_search(k, d, uright, kf, scale, inv_sigma2, xf, mp, th, mode, th_dist):
+    """Fuse / SearchBySim3 search part.  kf = (fx, fy, cx, cy, bf, logScale, minX, maxX, minY, maxY); xf = dict(R1, t1[, R2, t2][, Ow]);
+    mp = dict(valid, xw (m,3), normal (m,3), dmin, dmax, desc (m,32)).  Returns the best keypoint per map point (-1 = none)."""
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    k = np.ascontiguousarray(k); d = np.ascontiguousarray(d, np.uint8); m = len(mp["dmin"])
+    x = np.concatenate([f32(xf["R1"]).reshape(9), f32(xf["t1"]).reshape(3), f32(xf.get("R2", np.eye(3))).reshape(9),
+                        f32(xf.get("t2", np.zeros(3))).reshape(3), f32(xf.get("Ow", np.zeros(3))).reshape(3)])
+    best = np.zeros(max(m, 1), np.int32)
+    L = lib(); L.orbo_project_search.restype = None
+    L.orbo_project_search(_p(k), _p(d), _p(f32(uright)), len(k), _p(f32(kf)), _p(f32(scale)), _p(f32(inv_sigma2)), len(scale), _p(x),
+                          _p(np.ascontiguousarray(mp["valid"], np.uint8)), _p(f32(mp["xw"])), _p(f32(mp["normal"])), _p(f32(mp["dmin"])),
+                          _p(f32(mp["dmax"])), _p(np.ascontiguousarray(mp["desc"], np.uint8)), m, C.c_float(th), int(mode), int(th_dist), _p(best))
+    return best[:m]
 
 
 def distinctive_descriptor(desc):

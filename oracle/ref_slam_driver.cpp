@@ -26,6 +26,17 @@
 #include <string>
 #include <vector>
 
+#include <list>
+#include <map>
+#include <mutex>
+#include <set>
+#include <sstream>
+#include <thread>
+#include <opencv2/core/core.hpp>
+// the driver reads a few protected members of the reference's classes (MapPoint::mfMinDistance / mfMaxDistance);
+// the class layouts are unchanged, only the access checks are lifted for this translation unit
+#define protected public
+#define private public
 #include "Frame.h"
 #include "KeyFrame.h"
 #include "KeyFrameDatabase.h"
@@ -34,6 +45,8 @@
 #include "ORBVocabulary.h"
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#undef protected
+#undef private
 
 static char* g_base = nullptr;
 static std::atomic<size_t> g_off(0);

@@ -100,6 +100,10 @@ def lib():
         L.orbx_vocabulary_destroy.argtypes = [C.c_void_p]
         L.orbx_vocabulary_destroy.restype = None
         L.orbx_bow_transform_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p]
+        L.orbx_fuse_search_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_float] * 5 + [C.c_void_p, C.c_void_p, C.c_int, C.c_float] +
+                                             [C.c_void_p] * 7 + [C.c_int, C.c_float, C.c_void_p, C.c_int, C.c_void_p])
+        L.orbx_search_by_sim3_batch.argtypes = ([C.c_void_p] * 14 + [C.c_int, C.c_int, C.c_void_p] + [C.c_float] * 4 + [C.c_void_p, C.c_int, C.c_float, C.c_void_p] +
+                                                [C.c_void_p] * 12 + [C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p])
         L.orbx_distinctive_descriptors_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_undistort_grid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
         L.orbx_features_in_area_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -517,6 +521,57 @@ class ORBmatcher:
                                                      F.ctypes.data, T.ctypes.data, Cc.ctypes.data, K.ctypes.data, sc.ctypes.data, sg.ctypes.data,
                                                      len(sc), int(bOnlyStereo), int(self.mbCheckOrientation), m12.ctypes.data, nm.ctypes.data, 0, None))
         return [int(v) for v in nm], [m12[p, :A[5][p]].copy() for p in range(npairs)]
+
+    @staticmethod
+    def FuseSearch(grids, f, u_right, desc, kf_bounds, Rcw, tcw, Ow, cam, scale_factors, inv_level_sigma2, log_scale_factor, mp, th=3.0):
+        """The search of ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975) for keyframe f of `grids` (a FrameGrids):
+        cam = (fx, fy, cx, cy, bf); mp = dict(valid, xw, normal, dmin, dmax, desc) with dmin / dmax = mfMinDistance / mfMaxDistance.
+        Returns bestIdx per candidate (-1 = no keypoint within TH_LOW)."""
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        cap = grids.cap; n = int(grids.n[f]); m = len(mp["dmin"]); mcap = max(m, 1)
+        k = np.ascontiguousarray(grids.kps_un[f]); d = np.zeros((cap, 32), np.uint8); d[:n] = desc
+        ur = np.full(cap, -1, np.float32); ur[:n] = u_right
+        pose = np.concatenate([f32(Rcw).reshape(9), f32(tcw).reshape(3)])
+        pad = lambda a, shape, dt: (lambda o: (o.__setitem__(slice(0, m), np.asarray(a, dt).reshape((m,) + shape)), o)[1])(np.zeros((mcap,) + shape, dt))
+        best = np.zeros(mcap, np.int32)
+        nn = np.array([n], np.int32); mm = np.array([m], np.int32)
+        cs = np.ascontiguousarray(grids.cell_start[f]); ci = np.ascontiguousarray(grids.cell_items[f])
+        kb = f32(kf_bounds); sc = f32(scale_factors); isg = f32(inv_level_sigma2); ow = f32(Ow)
+        arrs = [pad(mp["valid"], (), np.uint8), pad(mp["xw"], (3,), np.float32), pad(mp["normal"], (3,), np.float32), pad(mp["dmin"], (), np.float32),
+                pad(mp["dmax"], (), np.float32), pad(mp["desc"], (32,), np.uint8)]
+        _check(lib().orbx_fuse_search_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, nn.ctypes.data, 1, cap, grids.bounds.ctypes.data, cs.ctypes.data,
+                                            ci.ctypes.data, kb.ctypes.data, pose.ctypes.data, ow.ctypes.data, *[float(v) for v in cam], sc.ctypes.data,
+                                            isg.ctypes.data, len(sc), float(log_scale_factor), *[a.ctypes.data for a in arrs], mm.ctypes.data, mcap,
+                                            float(th), best.ctypes.data, 0, None))
+        return best[:m].copy()
+
+    @staticmethod
+    def SearchBySim3(grids, desc1, desc2, kf_bounds, pose1, pose2, cam, scale_factors, log_scale_factor, xf, mp1, mp2, th=7.5):
+        """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1102-1326) for the keyframe pair (0, 1) of `grids`.  pose = (Rcw, tcw);
+        cam = (fx, fy, cx, cy) of keyframe 1; xf = sR12 (9), t12 (3), sR21 (9), t21 (3) as :1119-1122 compute them; mp1 / mp2 =
+        dict(index, xw, dmin, dmax, desc) of the taking-part map points of each keyframe.  Returns (nFound, matches12 over KF1's features)."""
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        cap = grids.cap; n1, n2 = int(grids.n[0]), int(grids.n[1])
+        mcap = max(len(mp1["index"]), len(mp2["index"]), 1)
+        def side(f, desc, pose):
+            d = np.zeros((cap, 32), np.uint8); d[:int(grids.n[f])] = desc
+            return [np.ascontiguousarray(grids.kps_un[f]), d, np.array([grids.n[f]], np.int32), np.ascontiguousarray(grids.cell_start[f]),
+                    np.ascontiguousarray(grids.cell_items[f]), f32(kf_bounds), np.concatenate([f32(pose[0]).reshape(9), f32(pose[1]).reshape(3)])]
+        def mps(mp):
+            m = len(mp["index"])
+            idx = np.full(mcap, -1, np.int32); idx[:m] = mp["index"]
+            xw = np.zeros((mcap, 3), np.float32); xw[:m] = mp["xw"]
+            lo = np.zeros(mcap, np.float32); lo[:m] = mp["dmin"]; hi = np.zeros(mcap, np.float32); hi[:m] = mp["dmax"]
+            dd = np.zeros((mcap, 32), np.uint8); dd[:m] = mp["desc"]
+            return [idx, xw, lo, hi, dd, np.array([m], np.int32)]
+        A, B, M1, M2 = side(0, desc1, pose1), side(1, desc2, pose2), mps(mp1), mps(mp2)
+        sc = f32(scale_factors); x = f32(xf).reshape(24)
+        m12 = np.zeros(cap, np.int32); nf = np.zeros(1, np.int32)
+        _check(lib().orbx_search_by_sim3_batch(*[a.ctypes.data for a in A], *[b.ctypes.data for b in B], 1, cap, grids.bounds.ctypes.data,
+                                               *[float(v) for v in cam[:4]], sc.ctypes.data, len(sc), float(log_scale_factor), x.ctypes.data,
+                                               *[a.ctypes.data for a in M1], *[a.ctypes.data for a in M2], mcap, float(th), m12.ctypes.data,
+                                               nf.ctypes.data, 0, None))
+        return int(nf[0]), m12[:n1].copy()
 
     def SearchByBoWNodes(self, sidesA, sidesB, strict=True, th=None):
         """SearchByBoW with vocabulary buckets, batched.  Each side = (desc, angles, valid, node) per pair; strict=True is

@@ -833,6 +833,124 @@ orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uin
   return ORBX_OK;
 }
 
+namespace {
+// scale tables arrive on the host or on the device; the kernels take them by value
+cudaError_t fetch_levels(float* dst, const float* src, int nlevels, int on_device, cudaStream_t st) {
+  for (int l = 0; l < kMaxLevels; ++l) dst[l] = 1.f;
+  if (!on_device) { std::memcpy(dst, src, nlevels * sizeof(float)); return cudaSuccess; }
+  cudaError_t e = cudaMemcpyAsync(dst, src, nlevels * sizeof(float), cudaMemcpyDeviceToHost, st);
+  return e != cudaSuccess ? e : cudaStreamSynchronize(st);
+}
+}  // namespace
+
+orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* desc, const float* u_right, const int* n, int n_kfs, int cap,
+                                   const float* grid_bounds, const int* cell_start, const int* cell_items, const float* kf_bounds,
+                                   const float* pose, const float* Ow, float fx, float fy, float cx, float cy, float bf,
+                                   const float* scale_factors, const float* inv_level_sigma2, int nlevels, float log_scale_factor,
+                                   const uint8_t* mp_valid, const float* mp_xw, const float* mp_normal, const float* mp_min_dist,
+                                   const float* mp_max_dist, const uint8_t* mp_desc, const int* m, int mcap, float th, int* best_idx,
+                                   int on_device, void* stream) {
+  if (!kps_un || !desc || !u_right || !n || !grid_bounds || !cell_start || !cell_items || !kf_bounds || !pose || !Ow || !scale_factors ||
+      !inv_level_sigma2 || !mp_valid || !mp_xw || !mp_normal || !mp_min_dist || !mp_max_dist || !mp_desc || !m || !best_idx)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_kfs < 1 || n_kfs > 65535 || cap < 1 || mcap < 1 || nlevels < 1 || nlevels > kMaxLevels || !(log_scale_factor > 0.f))
+    return fail(ORBX_ERR_BAD_ARG, "bad sizes (n_kfs <= 65535, nlevels <= 8, log_scale_factor > 0)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_kfs, kc = np * cap, mc = np * mcap, cells = np * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1);
+  ProjSearchArgs a;
+  CU(sg.in(kps_un, kc, on_device, &a.kps)); CU(sg.in(desc, kc * 32, on_device, &a.desc)); CU(sg.in(u_right, kc, on_device, &a.u_right));
+  CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds)); CU(sg.in(cell_start, cells, on_device, &a.cell_start)); CU(sg.in(cell_items, kc, on_device, &a.cell_items));
+  CU(sg.in(kf_bounds, np * 4, on_device, &a.kf_bounds));
+  // xf per problem: R1 t1 | R2 t2 (unused) | Ow
+  float* d_xf = nullptr;
+  CU(sg.alloc((void**)&d_xf, np * 27 * sizeof(float)));
+  CU(cudaMemsetAsync(d_xf, 0, np * 27 * sizeof(float), st));
+  const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  CU(cudaMemcpy2DAsync(d_xf, 27 * sizeof(float), pose, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
+  CU(cudaMemcpy2DAsync(d_xf + 24, 27 * sizeof(float), Ow, 3 * sizeof(float), 3 * sizeof(float), np, kind, st));
+  a.xf = d_xf;
+  CU(sg.in(mp_valid, mc, on_device, &a.valid)); CU(sg.in(mp_xw, mc * 3, on_device, &a.xw)); CU(sg.in(mp_normal, mc * 3, on_device, &a.normal));
+  CU(sg.in(mp_min_dist, mc, on_device, &a.dmin)); CU(sg.in(mp_max_dist, mc, on_device, &a.dmax)); CU(sg.in(mp_desc, mc * 32, on_device, &a.mp_desc));
+  CU(sg.in(m, np, on_device, &a.m));
+  if (on_device) a.best = best_idx; else CU(sg.alloc((void**)&a.best, mc * 4));
+  CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st)); CU(fetch_levels(a.inv_sigma2, inv_level_sigma2, nlevels, on_device, st));
+  a.n_problems = n_kfs; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.mode = 2 | 4 | 8; a.th_dist = 50;   // TH_LOW
+  a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = bf; a.log_scale = log_scale_factor; a.th = th;
+  g_launches += launch_project_search(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) { CU(cudaMemcpyAsync(best_idx, a.best, mc * 4, cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+  return ORBX_OK;
+}
+
+orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const int* n1, const int* cell_start1, const int* cell_items1,
+                                      const float* kf_bounds1, const float* pose1, const orbx_keypoint* kps2, const uint8_t* desc2, const int* n2,
+                                      const int* cell_start2, const int* cell_items2, const float* kf_bounds2, const float* pose2, int n_pairs,
+                                      int cap, const float* grid_bounds, float fx, float fy, float cx, float cy, const float* scale_factors,
+                                      int nlevels, float log_scale_factor, const float* xf, const int* mp1_index, const float* mp1_xw,
+                                      const float* mp1_min_dist, const float* mp1_max_dist, const uint8_t* mp1_desc, const int* m1,
+                                      const int* mp2_index, const float* mp2_xw, const float* mp2_min_dist, const float* mp2_max_dist,
+                                      const uint8_t* mp2_desc, const int* m2, int mcap, float th, int* matches12, int* n_found, int on_device,
+                                      void* stream) {
+  if (!kps1 || !desc1 || !n1 || !cell_start1 || !cell_items1 || !kf_bounds1 || !pose1 || !kps2 || !desc2 || !n2 || !cell_start2 || !cell_items2 ||
+      !kf_bounds2 || !pose2 || !grid_bounds || !scale_factors || !xf || !mp1_index || !mp1_xw || !mp1_min_dist || !mp1_max_dist || !mp1_desc || !m1 ||
+      !mp2_index || !mp2_xw || !mp2_min_dist || !mp2_max_dist || !mp2_desc || !m2 || !matches12 || !n_found)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_pairs < 1 || n_pairs > 65535 || cap < 1 || mcap < 1 || nlevels < 1 || nlevels > kMaxLevels || !(log_scale_factor > 0.f))
+    return fail(ORBX_ERR_BAD_ARG, "bad sizes (n_pairs <= 65535, nlevels <= 8, log_scale_factor > 0)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_pairs, kc = np * cap, mc = np * mcap, cells = np * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1);
+  const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  const float* d_gb; CU(sg.in(grid_bounds, 6, on_device, &d_gb));
+  uint8_t* d_valid = nullptr; CU(sg.alloc((void**)&d_valid, mc)); CU(cudaMemsetAsync(d_valid, 1, mc, st));
+  float* d_zero = nullptr; CU(sg.alloc((void**)&d_zero, mc * 3 * sizeof(float))); CU(cudaMemsetAsync(d_zero, 0, mc * 3 * sizeof(float), st));
+  int* d_vn[2]; int* d_best[2]; const int* d_idx[2]; const int* d_m[2];
+  const int* d_n1; CU(sg.in(n1, np, on_device, &d_n1));
+  // pass 0: map points of keyframe 1 into keyframe 2 (R1w, t1w then sR21, t21); pass 1: the other way (R2w, t2w then sR12, t12)
+  for (int pass = 0; pass < 2; ++pass) {
+    ProjSearchArgs a;
+    const bool fwd = pass == 0;
+    CU(sg.in(fwd ? kps2 : kps1, kc, on_device, &a.kps)); CU(sg.in(fwd ? desc2 : desc1, kc * 32, on_device, &a.desc));
+    a.u_right = nullptr; a.grid_bounds = d_gb;
+    CU(sg.in(fwd ? cell_start2 : cell_start1, cells, on_device, &a.cell_start)); CU(sg.in(fwd ? cell_items2 : cell_items1, kc, on_device, &a.cell_items));
+    CU(sg.in(fwd ? kf_bounds2 : kf_bounds1, np * 4, on_device, &a.kf_bounds));
+    float* d_xf = nullptr;
+    CU(sg.alloc((void**)&d_xf, np * 27 * sizeof(float)));
+    CU(cudaMemsetAsync(d_xf, 0, np * 27 * sizeof(float), st));
+    CU(cudaMemcpy2DAsync(d_xf, 27 * sizeof(float), fwd ? pose1 : pose2, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
+    CU(cudaMemcpy2DAsync(d_xf + 12, 27 * sizeof(float), xf + (fwd ? 12 : 0), 24 * sizeof(float), 12 * sizeof(float), np, kind, st));
+    a.xf = d_xf;
+    a.valid = d_valid; a.normal = d_zero;
+    CU(sg.in(fwd ? mp1_xw : mp2_xw, mc * 3, on_device, &a.xw)); CU(sg.in(fwd ? mp1_min_dist : mp2_min_dist, mc, on_device, &a.dmin));
+    CU(sg.in(fwd ? mp1_max_dist : mp2_max_dist, mc, on_device, &a.dmax)); CU(sg.in(fwd ? mp1_desc : mp2_desc, mc * 32, on_device, &a.mp_desc));
+    CU(sg.in(fwd ? m1 : m2, np, on_device, &d_m[pass])); a.m = d_m[pass];
+    CU(sg.in(fwd ? mp1_index : mp2_index, mc, on_device, &d_idx[pass]));
+    CU(sg.alloc((void**)&d_best[pass], mc * 4)); a.best = d_best[pass];
+    CU(sg.alloc((void**)&d_vn[pass], kc * 4)); CU(cudaMemsetAsync(d_vn[pass], 0xFF, kc * 4, st));
+    CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st));
+    for (int l = 0; l < kMaxLevels; ++l) a.inv_sigma2[l] = 1.f;
+    a.n_problems = n_pairs; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.mode = 1 | 16; a.th_dist = 100;   // TH_HIGH
+    a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = 0.f; a.log_scale = log_scale_factor; a.th = th;
+    g_launches += launch_project_search(a, st);
+    g_launches += launch_scatter_matches(d_best[pass], d_idx[pass], d_m[pass], mcap, cap, n_pairs, d_vn[pass], st);
+  }
+  Sim3AgreeArgs g;
+  g.match1 = d_vn[0]; g.match2 = d_vn[1]; g.n1 = d_n1; g.cap = cap;
+  if (on_device) { g.matches12 = matches12; g.nfound = n_found; }
+  else { CU(sg.alloc((void**)&g.matches12, kc * 4)); CU(sg.alloc((void**)&g.nfound, np * 4)); }
+  CU(cudaMemsetAsync(g.nfound, 0, np * 4, st));
+  g_launches += launch_sim3_agree(g, n_pairs, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(matches12, g.matches12, kc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_found, g.nfound, np * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  (void)n2;
+  return ORBX_OK;
+}
+
 orbx_status orbx_distinctive_descriptors_batch(const uint8_t* desc, const int* counts, int n_points, int kcap, int* best_idx,
                                                uint8_t* best_desc, int on_device, void* stream) {
   if (!desc || !counts || !best_idx) return fail(ORBX_ERR_BAD_ARG, "null argument");

@@ -155,6 +155,21 @@ struct BowTrArgs {
 };
 int launch_bow_transform(const BowTrArgs& a, cudaStream_t st);
 
+struct ProjSearchArgs {
+  const orbx_keypoint* kps; const uint8_t* desc; const float* u_right;                 // target keyframes, [P][cap]
+  const float* grid_bounds; const int* cell_start; const int* cell_items; const float* kf_bounds; const float* xf;
+  const uint8_t* valid; const float* xw; const float* normal; const float* dmin; const float* dmax; const uint8_t* mp_desc;   // [P][mcap]
+  const int* m;
+  int n_problems, cap, mcap, nlevels, mode, th_dist;
+  float fx, fy, cx, cy, bf, log_scale, th;
+  float scale[kMaxLevels], inv_sigma2[kMaxLevels];
+  int* best;
+};
+int launch_project_search(const ProjSearchArgs& a, cudaStream_t st);
+int launch_scatter_matches(const int* best, const int* mp_index, const int* m, int mcap, int cap, int n_problems, int* vn, cudaStream_t st);
+struct Sim3AgreeArgs { const int* match1; const int* match2; const int* n1; int cap; int* matches12; int* nfound; };
+int launch_sim3_agree(const Sim3AgreeArgs& a, int n_problems, cudaStream_t st);
+
 struct TriArgs {
   const orbx_keypoint* k1; const uint8_t* d1; const uint8_t* hasMp1; const float* uR1; const int* node1; const int* n1;
   const orbx_keypoint* k2; const uint8_t* d2; const uint8_t* hasMp2; const float* uR2; const int* node2; const int* n2;

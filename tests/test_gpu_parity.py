@@ -719,3 +719,34 @@ def test_cuda_keyframe_searches_reproduce_reference(gx):
     lists = gs.distinct_lists(kc.GOLD["distinct"]["seed"])
     best, out = gx.ComputeDistinctiveDescriptors(lists)
     assert hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest() == kc.GOLD["distinct"]["chosen_sha256"]
+
+
+def test_cuda_fuse_and_sim3_reproduce_reference(gx):
+    """K16 against ORBmatcher::Fuse (search) and ORBmatcher::SearchBySim3 of the REFERENCE on real KeyFrames and MapPoints
+    (tests/golden/ref_kf_*.npz): frames, stereo, the feature grid (K10) come from the CUDA path, MapPoint fields from the fixture."""
+    import importlib.util, os
+    spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
+    kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
+    gs = kc.gs
+    cfg = synth.KITTI
+    w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
+    for case in kc.GOLD["kf"]:
+        ims, V, T1, T2, F12 = gs.kf_case_inputs(case["seed"], case["L"])
+        fx = np.load(os.path.join(kc.HERE, "golden", case["fixture"]))
+        G = _ext(gx, w, h, nf, batch=4)
+        G.extract_batch(np.stack([ims[0], ims[2], ims[1], ims[3]]))
+        ur, dp, _ = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=2, slotL0=0, slotR0=2)
+        (k1, d1), (k2, d2) = G.fetch(0, 2)
+        scale = np.asarray(G.GetScaleFactors(), np.float32)
+        FG = gx.FrameGrids([k1, k2], gs.KITTI_CAM, w, h)
+        mp1, mp2 = fx["mps1"], fx["mps2"]
+        R2, t2 = T2[:3, :3], T2[:3, 3]
+        cam = gs.KITTI_CAM + (cfg["bf"],)
+        mpd = dict(valid=np.ones(len(mp1), np.uint8), xw=mp1["xw"], normal=mp1["normal"], dmin=mp1["dmin"], dmax=mp1["dmax"], desc=mp1["desc"])
+        best = gx.ORBmatcher.FuseSearch(FG, 1, ur[1, :len(k2)], d2, fx["kf_bounds"], R2, t2, (-R2.T @ t2).astype(np.float32), cam, scale, fx["inv_sigma2"],
+                                        float(fx["log_scale"]), mpd, 3.0)
+        assert int((best >= 0).sum()) == case["n_fuse"] and np.array_equal(best, fx["fuse"])
+        side = lambda mp: dict(index=mp["idx"], xw=mp["xw"], dmin=mp["dmin"], dmax=mp["dmax"], desc=mp["desc"])
+        n, m12 = gx.ORBmatcher.SearchBySim3(FG, d1, d2, fx["kf_bounds"], (T1[:3, :3], T1[:3, 3]), (R2, t2), gs.KITTI_CAM, scale, float(fx["log_scale"]), fx["sim3_xf"],
+                                            side(mp1), side(mp2), 7.5)
+        assert n == case["n_sim3"] and np.array_equal(m12, fx["sim3"])

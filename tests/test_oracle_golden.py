@@ -275,3 +275,43 @@ def test_oracle_distinctive_descriptors_match_reference(oracle):
     assert _sha(chosen) == GOLD_SLAM["distinct"]["chosen_sha256"]
     if oracle.ref_slam_available():
         assert np.array_equal(oracle.ref_slam_distinct(lists, synth.mono_frame(1, 1241, 376)), chosen)
+
+
+@pytest.mark.parametrize("case", GOLD_SLAM["kf"], ids=lambda c: f"kf{c['seed']}-L{c['L']}")
+def test_oracle_fuse_and_sim3_match_reference(oracle, case):
+    """ORBmatcher::Fuse (search) and SearchBySim3 of the reference on the same real KeyFrames / MapPoints."""
+    c = _kc.build(oracle, case)
+    F1, F2, fx = c["F1"], c["F2"], c["fx"]
+    cam, bf, T2 = c["cam"], c["cfg"]["bf"], c["T2"]
+    kfv = (cam[0], cam[1], cam[2], cam[3], bf, float(fx["log_scale"]), *fx["kf_bounds"])
+    mp1, mp2 = fx["mps1"], fx["mps2"]
+    R2, t2 = T2[:3, :3], T2[:3, 3]
+    mpd = dict(valid=np.ones(len(mp1), np.uint8), xw=mp1["xw"], normal=mp1["normal"], dmin=mp1["dmin"], dmax=mp1["dmax"], desc=mp1["desc"])
+    best = oracle.project_search(F2["keys"], F2["desc"], F2["u_right"], kfv, c["scale"], fx["inv_sigma2"], dict(R1=R2, t1=t2, Ow=(-R2.T @ t2).astype(np.float32)),
+                                 mpd, 3.0, oracle.FUSE_MODE, 50)
+    assert int((best >= 0).sum()) == case["n_fuse"] and np.array_equal(best, fx["fuse"])
+    x = fx["sim3_xf"]
+    sR12, t12, sR21, t21 = x[:9].reshape(3, 3), x[9:12], x[12:21].reshape(3, 3), x[21:24]
+    one = lambda mp: dict(valid=np.ones(len(mp), np.uint8), xw=mp["xw"], normal=mp["normal"], dmin=mp["dmin"], dmax=mp["dmax"], desc=mp["desc"])
+    b1 = oracle.project_search(F2["keys"], F2["desc"], F2["u_right"], kfv, c["scale"], fx["inv_sigma2"], dict(R1=np.eye(3), t1=np.zeros(3), R2=sR21, t2=t21), one(mp1), 7.5,
+                               oracle.SIM3_MODE, 100)
+    b2 = oracle.project_search(F1["keys"], F1["desc"], F1["u_right"], kfv, c["scale"], fx["inv_sigma2"], dict(R1=R2, t1=t2, R2=sR12, t2=t12), one(mp2), 7.5,
+                               oracle.SIM3_MODE, 100)
+    n1, n2 = len(F1["keys"]), len(F2["keys"])
+    vn1 = np.full(n1, -1, np.int32); vn1[mp1["idx"]] = b1
+    vn2 = np.full(n2, -1, np.int32); vn2[mp2["idx"]] = b2
+    m12 = np.array([vn1[i] if vn1[i] >= 0 and vn2[vn1[i]] == i else -1 for i in range(n1)], np.int32)
+    assert int((m12 >= 0).sum()) == case["n_sim3"] and np.array_equal(m12, fx["sim3"])
+    assert case["n_fuse"] > 50 and case["n_sim3"] > 50
+
+
+def test_logf_restatement(oracle):
+    """glibc logf restated (MapPoint::PredictScale calls the float overload of log): sampled against the host libm here,
+    exhaustively by tools/sweep_logf.c."""
+    import ctypes, math
+    L = oracle.lib(); L.orbo_logf.restype = ctypes.c_float; L.orbo_logf.argtypes = [ctypes.c_float]
+    libm = ctypes.CDLL("libm.so.6"); libm.logf.restype = ctypes.c_float; libm.logf.argtypes = [ctypes.c_float]
+    rng = np.random.default_rng(3)
+    xs = np.concatenate([rng.uniform(0.01, 100, 20000), np.exp(rng.uniform(-80, 80, 20000)), [1.0, 1.2, 0.5, 2.0]]).astype(np.float32)
+    for x in xs:
+        assert np.float32(L.orbo_logf(float(x))).tobytes() == np.float32(libm.logf(float(x))).tobytes(), x
