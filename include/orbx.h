@@ -266,7 +266,10 @@ orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uin
  * mp_max_dist = mfMinDistance / mfMaxDistance (what Get{Min,Max}DistanceInvariance() return divided by 0.8 / 1.2),
  * mp_desc = GetDescriptor(); m[p] candidates.  best_idx[p*mcap + k] receives bestIdx when bestDist <= TH_LOW, else -1.
  * The map update of :944-966 (Replace / AddObservation + AddMapPoint, nFused++) stays with the caller, in candidate
- * order: the search of one candidate does not depend on the updates of the others. */
+ * order: the search of one candidate does not depend on the updates of the others.
+ * sim3_variant = 1 selects the search of Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:977-1100, loop
+ * closing): pose / Ow are then Rcw = sRcw/scw, tcw = Scw.col(3)/scw and Ow = -Rcw.t()*tcw as :986-991 compute them, mp_valid
+ * = (!isBad() && !spAlreadyFound.count(pMP)), and there is no reprojection-error gate (u_right, inv_level_sigma2 unused). */
 orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* desc, const float* u_right, const int* n,
                                    int n_kfs, int cap, const float* grid_bounds, const int* cell_start,
                                    const int* cell_items, const float* kf_bounds, const float* pose, const float* Ow,
@@ -274,7 +277,8 @@ orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* d
                                    const float* inv_level_sigma2, int nlevels, float log_scale_factor,
                                    const uint8_t* mp_valid, const float* mp_xw, const float* mp_normal,
                                    const float* mp_min_dist, const float* mp_max_dist, const uint8_t* mp_desc,
-                                   const int* m, int mcap, float th, int* best_idx, int on_device, void* stream);
+                                   const int* m, int mcap, float th, int sim3_variant, int* best_idx, int on_device,
+                                   void* stream);
 
 /* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1102-1326; src/LoopClosing.cc:328)
  * for n_pairs independent keyframe pairs.  Keyframe 1 of pair p at index p*cap (kps1 = mvKeysUn, desc1, n1, its grid
@@ -295,6 +299,29 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
                                       const int* mp2_index, const float* mp2_xw, const float* mp2_min_dist,
                                       const float* mp2_max_dist, const uint8_t* mp2_desc, const int* m2, int mcap,
                                       float th, int* matches12, int* n_found, int on_device, void* stream);
+
+/* The two SearchByProjection members that claim keypoints as they go, for n_problems independent (target, map point list)
+ * problems:
+ *   relocalisation = 0: SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:290-403, src/LoopClosing.cc:389):
+ *     target = the keyframe, target_bounds = its mnMinX.. (ints), pose / Ow = Rcw, tcw, Ow as :298-303 compute them from Scw,
+ *     occupied[i] = (vpMatched[i] != NULL), mp_valid = (!isBad() && !spAlreadyFound.count(pMP)), max_dist = TH_LOW;
+ *   relocalisation = 1: SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (:1472-1599, src/Tracking.cc:1397,1412):
+ *     target = the current frame, target_bounds = Frame::mnMinX.., pose = CurrentFrame.mTcw, Ow = -Rcw.t()*tcw, occupied[i] =
+ *     (CurrentFrame.mvpMapPoints[i] != NULL), the list = pKF's map points in feature order with mp_valid = (pMP && !isBad() &&
+ *     !sAlreadyFound.count(pMP)), mp_src_angle = pKF->mvKeysUn[i].angle, max_dist = ORBdist, rotation check per check_orientation.
+ * Target p at index p*cap with its grid (orbx_undistort_grid_batch); map point k of problem p at index p*mcap + k: world position,
+ * normal (relocalisation = 0 only), mfMinDistance / mfMaxDistance, descriptor.  Map points are taken in list order; assigned[p*cap + i]
+ * receives the list position of the map point given to keypoint i by this call (-1 otherwise), n_matches[p] the return value. */
+orbx_status orbx_search_projection_ordered_batch(const orbx_keypoint* kps_un, const uint8_t* desc, const int* n, int n_problems,
+                                                 int cap, const float* grid_bounds, const int* cell_start, const int* cell_items,
+                                                 const float* target_bounds, const float* pose, const float* Ow, float fx, float fy,
+                                                 float cx, float cy, const float* scale_factors, int nlevels,
+                                                 float log_scale_factor, const uint8_t* occupied, const uint8_t* mp_valid,
+                                                 const float* mp_xw, const float* mp_normal, const float* mp_min_dist,
+                                                 const float* mp_max_dist, const uint8_t* mp_desc, const float* mp_src_angle,
+                                                 const int* m, int mcap, float th, int max_dist, int relocalisation,
+                                                 int check_orientation, int* assigned, int* n_matches, int on_device,
+                                                 void* stream);
 
 /* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305) for n_points map points.  Map point m:
  * counts[m] observed descriptors (those of the keyframes that are not bad, in mObservations order) at

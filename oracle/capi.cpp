@@ -104,6 +104,15 @@ void orbo_project_search(const KeyPt* k, const uint8_t* d, const float* uRight, 
                        : -1;
 }
 float orbo_logf(float x) { return libm_logf(x); }
+// kf as in orbo_project_search; gridBounds = the Frame's {minX, maxX, minY, maxY}; xf = Rcw (9), tcw (3), Ow (3)
+int orbo_project_match_ordered(const KeyPt* k, const uint8_t* d, int n, const float* kf, const float* gridBounds, const float* scale, int nlevels,
+                               int reloc, const float* xf, const uint8_t* valid, const float* xw, const float* normal, const float* dmin,
+                               const float* dmax, const uint8_t* mpDesc, const float* srcAngle, int m, float th, int thDist, int checkOri,
+                               uint8_t* occupied, int* assigned) {
+  KFSearchView K{k, d, nullptr, n, {kf[6], kf[7], kf[8], kf[9]}, scale, nullptr, nlevels, kf[5], kf[0], kf[1], kf[2], kf[3], kf[4]};
+  return project_match_ordered(K, gridBounds, reloc != 0, xf, xf + 9, xf + 12, valid, xw, normal, dmin, dmax, mpDesc, srcAngle, m, th, thDist,
+                               checkOri != 0, occupied, assigned);
+}
 
 int orbo_distinctive_descriptor(const uint8_t* d, int n) { return distinctive_descriptor(d, n); }
 

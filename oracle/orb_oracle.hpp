@@ -993,6 +993,78 @@ inline int project_search_one(const KFSearchView& K, const FrameGrid& grid, cons
   return bestDist <= M.th_dist ? bestIdx : -1;
 }
 
+// The two remaining SearchByProjection members, which claim keypoints as they go (hazard H6):
+//   SearchByProjection(pKF, Scw, vpPoints, vpMatched, th)                         src/ORBmatcher.cc:290-403   (reloc = false)
+//   SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)             src/ORBmatcher.cc:1472-1599 (reloc = true)
+// Map points are visited in list order; occupied[i] != 0 marks a keypoint that already holds a map point (vpMatched[i] /
+// CurrentFrame.mvpMapPoints[i]); an accepted match occupies its keypoint.  assigned[i] = position of the map point given to
+// keypoint i by this call, or -1.  The two differ in how the projection is written, in the image test, the viewing-angle
+// test, the level window ([pred-1, pred] vs [pred-1, pred+1]) and the rotation histogram (reloc only).
+inline int project_match_ordered(const KFSearchView& K, const float* gridBounds, bool reloc, const float* Rcw, const float* tcw,
+                                 const float* Ow, const uint8_t* valid, const float* xw, const float* normal, const float* dminA,
+                                 const float* dmaxA, const uint8_t* desc, const float* srcAngle, int m, float th, int thDist,
+                                 bool checkOri, uint8_t* occupied, int* assigned) {
+  FrameGrid grid(K.k, K.n, gridBounds);
+  // the query window uses the target's own bounds (KeyFrame: ints, Frame: floats); cells were assigned with the Frame's
+  grid.minX = K.bounds[0]; grid.minY = K.bounds[2];
+  for (int i = 0; i < K.n; ++i) assigned[i] = -1;
+  std::vector<int> hist[kHisto];
+  int nm = 0;
+  std::vector<int> cand;
+  for (int iMP = 0; iMP < m; ++iMP) {
+    if (!valid[iMP]) continue;
+    const float* X = xw + 3 * iMP;
+    float p[3];
+    for (int r = 0; r < 3; ++r) p[r] = ((Rcw[3 * r] * X[0] + Rcw[3 * r + 1] * X[1]) + Rcw[3 * r + 2] * X[2]) + tcw[r];
+    float u, v;
+    if (!reloc) {
+      if (p[2] < 0.0f) continue;
+      const float invz = 1 / p[2];
+      const float x = p[0] * invz, y = p[1] * invz;
+      u = K.fx * x + K.cx; v = K.fy * y + K.cy;
+      if (!(u >= K.bounds[0] && u < K.bounds[1] && v >= K.bounds[2] && v < K.bounds[3])) continue;
+    } else {
+      const float invzc = (float)(1.0 / (double)p[2]);
+      u = K.fx * p[0] * invzc + K.cx; v = K.fy * p[1] * invzc + K.cy;
+      if (u < K.bounds[0] || u > K.bounds[1]) continue;
+      if (v < K.bounds[2] || v > K.bounds[3]) continue;
+    }
+    const float PO[3] = {X[0] - Ow[0], X[1] - Ow[1], X[2] - Ow[2]};
+    const float dist3D = (float)std::sqrt((double)PO[0] * PO[0] + (double)PO[1] * PO[1] + (double)PO[2] * PO[2]);
+    if (dist3D < 0.8f * dminA[iMP] || dist3D > 1.2f * dmaxA[iMP]) continue;
+    if (!reloc) {
+      const float* nn = normal + 3 * iMP;
+      const double dot = (double)PO[0] * nn[0] + (double)PO[1] * nn[1] + (double)PO[2] * nn[2];
+      if (dot < 0.5 * dist3D) continue;
+    }
+    int level = (int)std::ceil(libm_logf(dmaxA[iMP] / dist3D) / K.logScale);
+    if (level < 0) level = 0; else if (level >= K.nlevels) level = K.nlevels - 1;
+    const float radius = th * K.scale[level];
+    grid.in_area(K.k, u, v, radius, -1, -1, cand);
+    int bestDist = 256, bestIdx = -1;
+    for (int idx : cand) {
+      if (occupied[idx]) continue;
+      const int oct = K.k[idx].octave;
+      if (oct < level - 1 || oct > (reloc ? level + 1 : level)) continue;
+      const int dist = hamming256(desc + 32 * (size_t)iMP, K.d + 32 * (size_t)idx);
+      if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+    }
+    if (bestDist <= thDist) {
+      occupied[bestIdx] = 1; assigned[bestIdx] = iMP; ++nm;
+      if (reloc && checkOri) hist[rot_bin(srcAngle[iMP], K.k[bestIdx].angle)].push_back(bestIdx);
+    }
+  }
+  if (reloc && checkOri) {
+    int a = -1, b = -1, c = -1;
+    three_maxima(hist, kHisto, a, b, c);
+    for (int i = 0; i < kHisto; ++i) {
+      if (i == a || i == b || i == c) continue;
+      for (int idx : hist[i]) { assigned[idx] = -1; --nm; }
+    }
+  }
+  return nm;
+}
+
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305): among the N observed descriptors, the one
 // whose median distance to all of them (itself included, sorted row element [0.5*(N-1)]) is least; first on ties.
 inline int distinctive_descriptor(const uint8_t* d, int N) {

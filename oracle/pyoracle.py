@@ -236,7 +236,7 @@ def kf_rule(i, salt, pct):
 
 
 def ref_slam_kf(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, pct1=60, pct2=50, ratio_kk=0.75, ratio_kf=0.7,
-                th_proj=3.0, th_last=15.0, check_ori=True, only_stereo=False, mono=False):
+                th_proj=3.0, th_last=15.0, check_ori=True, only_stereo=False, mono=False, fuse_scw=False):
     """Two real KeyFrames with real MapPoints and DBoW2 feature vectors, and the REFERENCE's SearchByBoW (both forms),
     SearchForTriangulation and SearchByProjection (both forms) on them.  voc = flat vocabulary dict (written out in the
     reference's text format, L1_NORM + TF_IDF).  Returns a dict of everything the restatements need and the results."""
@@ -249,7 +249,7 @@ def ref_slam_kf(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, pct1=60, p
         pb = vp.encode()
         pay = (np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, bf) + np.array([pct1, pct2], np.int32).tobytes() +
                np.array([ratio_kk, ratio_kf, th_proj, th_last], np.float32).tobytes() +
-               np.array([int(check_ori), int(only_stereo), int(mono)], np.int32).tobytes() +
+               np.array([int(check_ori), int(only_stereo), int(mono), int(fuse_scw)], np.int32).tobytes() +
                np.asarray(T1, np.float32).reshape(16).tobytes() + np.asarray(T2, np.float32).reshape(16).tobytes() +
                np.asarray(F12, np.float32).reshape(9).tobytes() + np.int32(len(pb)).tobytes() + pb + b"".join(x.tobytes() for x in ims))
         rd = _Rd(_run_ref_slam("kf", pay))
@@ -280,6 +280,10 @@ def ref_slam_kf(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, pct1=60, p
     o["log_scale"] = float(rd.arr(np.float32, 1)[0]); o["kf_bounds"] = rd.arr(np.float32, 4); o["inv_sigma2"] = rd.arr(np.float32, 8)
     o["sim3_xf"] = dict(sR12=rd.arr(np.float32, 9, (3, 3)), t12=rd.arr(np.float32, 3), sR21=rd.arr(np.float32, 9, (3, 3)), t21=rd.arr(np.float32, 3))
     o["sim3"] = (rd.i32(), rd.arr(np.int32, n1))
+    o["scw_xf"] = dict(Rcw=rd.arr(np.float32, 9, (3, 3)), tcw=rd.arr(np.float32, 3), Ow=rd.arr(np.float32, 3))
+    o["proj_scw"] = (rd.i32(), rd.arr(np.int32, n2))
+    o["reloc_Ow"] = rd.arr(np.float32, 3)
+    o["proj_kf"] = (rd.i32(), rd.arr(np.int32, n2))
     o["fuse"] = (rd.i32(), rd.arr(np.int32, m))
     return o
 
@@ -375,6 +379,20 @@ def project_search(k, d, uright, kf, scale, inv_sigma2, xf, mp, th, mode, th_dis
                           _p(np.ascontiguousarray(mp["valid"], np.uint8)), _p(f32(mp["xw"])), _p(f32(mp["normal"])), _p(f32(mp["dmin"])),
                           _p(f32(mp["dmax"])), _p(np.ascontiguousarray(mp["desc"], np.uint8)), m, C.c_float(th), int(mode), int(th_dist), _p(best))
     return best[:m]
+
+
+def project_match_ordered(k, d, kf, grid_bounds, scale, reloc, Rcw, tcw, Ow, mp, th, th_dist, check_ori, occupied):
+    """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (reloc=False) / SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th,
+    ORBdist) (reloc=True).  mp = dict(valid, xw, normal, dmin, dmax, desc, angle).  Returns (assigned per keypoint, nmatches)."""
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    k = np.ascontiguousarray(k); d = np.ascontiguousarray(d, np.uint8); m = len(mp["dmin"])
+    xf = np.concatenate([f32(Rcw).reshape(9), f32(tcw).reshape(3), f32(Ow).reshape(3)])
+    occ = np.ascontiguousarray(occupied, np.uint8).copy(); assigned = np.zeros(max(len(k), 1), np.int32)
+    n = lib().orbo_project_match_ordered(_p(k), _p(d), len(k), _p(f32(kf)), _p(f32(grid_bounds)), _p(f32(scale)), len(scale), int(reloc), _p(xf),
+                                         _p(np.ascontiguousarray(mp["valid"], np.uint8)), _p(f32(mp["xw"])), _p(f32(mp["normal"])), _p(f32(mp["dmin"])),
+                                         _p(f32(mp["dmax"])), _p(np.ascontiguousarray(mp["desc"], np.uint8)), _p(f32(mp["angle"])), m, C.c_float(th),
+                                         int(th_dist), int(check_ori), _p(occ), _p(assigned))
+    return assigned[:len(k)], n
 
 
 def distinctive_descriptor(desc):

@@ -101,9 +101,11 @@ def lib():
         L.orbx_vocabulary_destroy.restype = None
         L.orbx_bow_transform_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p]
         L.orbx_fuse_search_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_float] * 5 + [C.c_void_p, C.c_void_p, C.c_int, C.c_float] +
-                                             [C.c_void_p] * 7 + [C.c_int, C.c_float, C.c_void_p, C.c_int, C.c_void_p])
+                                             [C.c_void_p] * 7 + [C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_int, C.c_void_p])
         L.orbx_search_by_sim3_batch.argtypes = ([C.c_void_p] * 14 + [C.c_int, C.c_int, C.c_void_p] + [C.c_float] * 4 + [C.c_void_p, C.c_int, C.c_float, C.c_void_p] +
                                                 [C.c_void_p] * 12 + [C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p])
+        L.orbx_search_projection_ordered_batch.argtypes = ([C.c_void_p] * 3 + [C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_float] * 4 + [C.c_void_p, C.c_int, C.c_float] +
+                                                           [C.c_void_p] * 9 + [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p])
         L.orbx_distinctive_descriptors_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_undistort_grid_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
         L.orbx_features_in_area_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9 + [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -523,8 +525,8 @@ class ORBmatcher:
         return [int(v) for v in nm], [m12[p, :A[5][p]].copy() for p in range(npairs)]
 
     @staticmethod
-    def FuseSearch(grids, f, u_right, desc, kf_bounds, Rcw, tcw, Ow, cam, scale_factors, inv_level_sigma2, log_scale_factor, mp, th=3.0):
-        """The search of ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975) for keyframe f of `grids` (a FrameGrids):
+    def FuseSearch(grids, f, u_right, desc, kf_bounds, Rcw, tcw, Ow, cam, scale_factors, inv_level_sigma2, log_scale_factor, mp, th=3.0, sim3_variant=False):
+        """The search of ORBmatcher::Fuse(pKF, vpMapPoints, th) (or, with sim3_variant, of Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)) (src/ORBmatcher.cc:825-975) for keyframe f of `grids` (a FrameGrids):
         cam = (fx, fy, cx, cy, bf); mp = dict(valid, xw, normal, dmin, dmax, desc) with dmin / dmax = mfMinDistance / mfMaxDistance.
         Returns bestIdx per candidate (-1 = no keypoint within TH_LOW)."""
         f32 = lambda a: np.ascontiguousarray(a, np.float32)
@@ -542,8 +544,32 @@ class ORBmatcher:
         _check(lib().orbx_fuse_search_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, nn.ctypes.data, 1, cap, grids.bounds.ctypes.data, cs.ctypes.data,
                                             ci.ctypes.data, kb.ctypes.data, pose.ctypes.data, ow.ctypes.data, *[float(v) for v in cam], sc.ctypes.data,
                                             isg.ctypes.data, len(sc), float(log_scale_factor), *[a.ctypes.data for a in arrs], mm.ctypes.data, mcap,
-                                            float(th), best.ctypes.data, 0, None))
+                                            float(th), int(sim3_variant), best.ctypes.data, 0, None))
         return best[:m].copy()
+
+    def SearchByProjectionOrdered(self, grids, f, desc, target_bounds, Rcw, tcw, Ow, cam, scale_factors, log_scale_factor, occupied, mp, th, max_dist,
+                                  relocalisation):
+        """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (relocalisation=False, src/ORBmatcher.cc:290) or
+        SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (relocalisation=True, :1472) on target f of `grids`.
+        mp = dict(valid, xw, normal, dmin, dmax, desc, angle).  Returns (nmatches, assigned per keypoint of the target)."""
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        cap = grids.cap; n = int(grids.n[f]); m = len(mp["dmin"]); mcap = max(m, 1)
+        d = np.zeros((cap, 32), np.uint8); d[:n] = desc
+        occ = np.zeros(cap, np.uint8); occ[:n] = occupied
+        pose = np.concatenate([f32(Rcw).reshape(9), f32(tcw).reshape(3)]); ow = f32(Ow); tb = f32(target_bounds); sc = f32(scale_factors)
+        def pad(a, shape, dt):
+            o = np.zeros((mcap,) + shape, dt); o[:m] = np.asarray(a, dt).reshape((m,) + shape); return o
+        arrs = [pad(mp["valid"], (), np.uint8), pad(mp["xw"], (3,), np.float32), pad(mp["normal"], (3,), np.float32), pad(mp["dmin"], (), np.float32),
+                pad(mp["dmax"], (), np.float32), pad(mp["desc"], (32,), np.uint8), pad(mp["angle"], (), np.float32)]
+        k = np.ascontiguousarray(grids.kps_un[f]); cs = np.ascontiguousarray(grids.cell_start[f]); ci = np.ascontiguousarray(grids.cell_items[f])
+        nn = np.array([n], np.int32); mm = np.array([m], np.int32)
+        assigned = np.zeros(cap, np.int32); nm = np.zeros(1, np.int32)
+        _check(lib().orbx_search_projection_ordered_batch(k.ctypes.data, d.ctypes.data, nn.ctypes.data, 1, cap, grids.bounds.ctypes.data, cs.ctypes.data,
+                                                          ci.ctypes.data, tb.ctypes.data, pose.ctypes.data, ow.ctypes.data, *[float(v) for v in cam[:4]],
+                                                          sc.ctypes.data, len(sc), float(log_scale_factor), occ.ctypes.data, *[a.ctypes.data for a in arrs],
+                                                          mm.ctypes.data, mcap, float(th), int(max_dist), int(relocalisation),
+                                                          int(self.mbCheckOrientation), assigned.ctypes.data, nm.ctypes.data, 0, None))
+        return int(nm[0]), assigned[:n].copy()
 
     @staticmethod
     def SearchBySim3(grids, desc1, desc2, kf_bounds, pose1, pose2, cam, scale_factors, log_scale_factor, xf, mp1, mp2, th=7.5):

@@ -152,6 +152,134 @@ __global__ void __launch_bounds__(128) k_scatter_matches(const int* __restrict__
   if (kpi >= 0 && kpi < cap) vn[(size_t)p * cap + kpi] = best[(size_t)p * mcap + i];
 }
 
+// K17: the two SearchByProjection members that claim keypoints as they go (hazard H6), one warp per problem:
+//   SearchByProjection(pKF, Scw, vpPoints, vpMatched, th)              src/ORBmatcher.cc:290-403   (reloc = 0)
+//   SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)  src/ORBmatcher.cc:1472-1599 (reloc = 1)
+// Map points are taken in list order; every lane evaluates the (cheap) projection of the current one, the lanes then share
+// the candidates of the window, cell column by cell column.  The winner is the least (distance, cell column, position in
+// the column's CSR run), i.e. the first least distance in the reference's enumeration order, among free keypoints.
+__device__ __forceinline__ int rot_bin30(float a1, float a2) {
+  float rot = __fsub_rn(a1, a2);
+  if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+  int bin = (int)roundf(__fmul_rn(rot, 1.0f / 30));
+  return bin == 30 ? 0 : bin;
+}
+
+__global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint32_t* occ = reinterpret_cast<uint32_t*>(smem);            // bit i: keypoint i holds a map point
+  __shared__ int s_hist[30];
+  const int p = blockIdx.x, lane = threadIdx.x;
+  const int n = min(a.n[p], a.cap), m = min(a.m[p], a.mcap);
+  const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
+  const orbx_keypoint* kps = a.kps + ko;
+  const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
+  const int* items = a.cell_items + ko;
+  const float* xf = a.xf + (size_t)p * 15;                      // Rcw (9) tcw (3) Ow (3)
+  const float* kb = a.tgt_bounds + (size_t)p * 4;
+  const float* gb = a.grid_bounds;
+  int* assigned = a.assigned + ko;
+  for (int w = lane; w < (a.cap + 31) / 32; w += 32) {
+    uint32_t bits = 0u;
+    for (int b = 0; b < 32; ++b) { const int i = w * 32 + b; if (i < n && a.occupied[ko + i]) bits |= 1u << b; }
+    occ[w] = bits;
+  }
+  for (int i = lane; i < a.cap; i += 32) assigned[i] = -1;
+  if (lane < 30) s_hist[lane] = 0;
+  __syncwarp();
+  int nm = 0;
+  for (int iMP = 0; iMP < m; ++iMP) {
+    if (!a.valid[mo + iMP]) continue;
+    const float xw[3] = {a.xw[(mo + iMP) * 3], a.xw[(mo + iMP) * 3 + 1], a.xw[(mo + iMP) * 3 + 2]};
+    float pc[3];
+    gemm3(xf, xf + 9, xw, pc);
+    float u, v;
+    if (!a.reloc) {
+      if (pc[2] < 0.0f) continue;
+      const float invz = __fdiv_rn(1.0f, pc[2]);
+      u = __fadd_rn(__fmul_rn(a.fx, __fmul_rn(pc[0], invz)), a.cx); v = __fadd_rn(__fmul_rn(a.fy, __fmul_rn(pc[1], invz)), a.cy);
+      if (!(u >= kb[0] && u < kb[1] && v >= kb[2] && v < kb[3])) continue;
+    } else {
+      const float invzc = (float)__ddiv_rn(1.0, (double)pc[2]);
+      u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, pc[0]), invzc), a.cx); v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, pc[1]), invzc), a.cy);
+      if (u < kb[0] || u > kb[1] || v < kb[2] || v > kb[3]) continue;
+    }
+    const float PO[3] = {__fsub_rn(xw[0], xf[12]), __fsub_rn(xw[1], xf[13]), __fsub_rn(xw[2], xf[14])};
+    const double s2 = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)PO[0]), __dmul_rn((double)PO[1], (double)PO[1])), __dmul_rn((double)PO[2], (double)PO[2]));
+    const float dist3D = (float)__dsqrt_rn(s2);
+    const float dmin = a.dmin[mo + iMP], dmax = a.dmax[mo + iMP];
+    if (dist3D < __fmul_rn(0.8f, dmin) || dist3D > __fmul_rn(1.2f, dmax)) continue;
+    if (!a.reloc) {
+      const float* nn = a.normal + (mo + iMP) * 3;
+      const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)nn[0]), __dmul_rn((double)PO[1], (double)nn[1])), __dmul_rn((double)PO[2], (double)nn[2]));
+      if (dot < __dmul_rn(0.5, (double)dist3D)) continue;
+    }
+    int level = (int)ceilf(__fdiv_rn(libm_logf(__fdiv_rn(dmax, dist3D)), a.log_scale));
+    level = level < 0 ? 0 : (level >= a.nlevels ? a.nlevels - 1 : level);
+    const int lvl_hi = a.reloc ? level + 1 : level;
+    const float radius = __fmul_rn(a.th, a.scale[level]);
+    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
+    const int cx1 = min(kPGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
+    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
+    const int cy1 = min(kPGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
+    if (cx0 >= kPGridCols || cx1 < 0 || cy0 >= kPGridRows || cy1 < 0) continue;
+    uint32_t qd[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) qd[w] = __ldg(reinterpret_cast<const uint32_t*>(a.mp_desc + (mo + iMP) * 32) + w);
+    unsigned hi = 0xffffffffu, lo = 0xffffffffu;                // (distance << 8 | cell column), CSR position
+    for (int ix = cx0; ix <= cx1; ++ix) {
+      const int e_hi = cs[ix * kPGridRows + cy1 + 1];
+      for (int e = cs[ix * kPGridRows + cy0] + lane; e < e_hi; e += 32) {
+        const int idx = items[e];
+        if ((occ[idx >> 5] >> (idx & 31)) & 1u) continue;
+        const orbx_keypoint kp = kps[idx];
+        if (!(fabsf(__fsub_rn(kp.x, u)) < radius && fabsf(__fsub_rn(kp.y, v)) < radius)) continue;
+        if (kp.octave < level - 1 || kp.octave > lvl_hi) continue;
+        const unsigned h = ((unsigned)ham8p(qd, reinterpret_cast<const uint32_t*>(a.desc + (ko + idx) * 32)) << 8) | (unsigned)ix;
+        if (h < hi || (h == hi && (unsigned)e < lo)) { hi = h; lo = (unsigned)e; }
+      }
+    }
+    const unsigned whi = __reduce_min_sync(0xffffffffu, hi);
+    if (whi == 0xffffffffu || (int)(whi >> 8) > a.th_dist) continue;      // no candidate (distance starts at 256) or too far
+    const unsigned wlo = __reduce_min_sync(0xffffffffu, hi == whi ? lo : 0xffffffffu);
+    const int bestIdx = items[wlo];
+    if (lane == 0) {
+      occ[bestIdx >> 5] |= 1u << (bestIdx & 31);
+      assigned[bestIdx] = iMP;
+      if (a.reloc && a.checkOri) atomicAdd(&s_hist[rot_bin30(a.src_angle[mo + iMP], kps[bestIdx].angle)], 1);
+    }
+    ++nm;
+    __syncwarp();
+  }
+  __syncwarp();
+  if (a.reloc && a.checkOri) {                                  // rotation consistency, src/ORBmatcher.cc:1577-1596
+    int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;      // ORBmatcher::ComputeThreeMaxima :1601-1642
+    for (int i = 0; i < 30; ++i) {
+      const int sc = s_hist[i];
+      if (sc > m1) { m3 = m2; m2 = m1; m1 = sc; i3 = i2; i2 = i1; i1 = i; }
+      else if (sc > m2) { m3 = m2; m2 = sc; i3 = i2; i2 = i; }
+      else if (sc > m3) { m3 = sc; i3 = i; }
+    }
+    if ((float)m2 < __fmul_rn(0.1f, (float)m1)) { i2 = -1; i3 = -1; }
+    else if ((float)m3 < __fmul_rn(0.1f, (float)m1)) i3 = -1;
+    int drop = 0;
+    for (int i = lane; i < n; i += 32) {
+      const int mp = assigned[i];
+      if (mp >= 0) {
+        const int b = rot_bin30(a.src_angle[mo + mp], kps[i].angle);
+        if (b != i1 && b != i2 && b != i3) { assigned[i] = -1; ++drop; }
+      }
+    }
+    nm -= __reduce_add_sync(0xffffffffu, drop);
+  }
+  if (lane == 0) a.nm[p] = nm;
+}
+
+int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
+  k_project_match_ordered<<<a.n_problems, 32, (size_t)((a.cap + 31) / 32) * 4, st>>>(a);
+  return 1;
+}
+
 int launch_project_search(const ProjSearchArgs& a, cudaStream_t st) {
   k_project_search<<<dim3((unsigned)((a.mcap + 127) / 128), (unsigned)a.n_problems), 128, 0, st>>>(a);
   return 1;

@@ -848,8 +848,8 @@ orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* d
                                    const float* pose, const float* Ow, float fx, float fy, float cx, float cy, float bf,
                                    const float* scale_factors, const float* inv_level_sigma2, int nlevels, float log_scale_factor,
                                    const uint8_t* mp_valid, const float* mp_xw, const float* mp_normal, const float* mp_min_dist,
-                                   const float* mp_max_dist, const uint8_t* mp_desc, const int* m, int mcap, float th, int* best_idx,
-                                   int on_device, void* stream) {
+                                   const float* mp_max_dist, const uint8_t* mp_desc, const int* m, int mcap, float th, int sim3_variant,
+                                   int* best_idx, int on_device, void* stream) {
   if (!kps_un || !desc || !u_right || !n || !grid_bounds || !cell_start || !cell_items || !kf_bounds || !pose || !Ow || !scale_factors ||
       !inv_level_sigma2 || !mp_valid || !mp_xw || !mp_normal || !mp_min_dist || !mp_max_dist || !mp_desc || !m || !best_idx)
     return fail(ORBX_ERR_BAD_ARG, "null argument");
@@ -875,7 +875,7 @@ orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* d
   CU(sg.in(m, np, on_device, &a.m));
   if (on_device) a.best = best_idx; else CU(sg.alloc((void**)&a.best, mc * 4));
   CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st)); CU(fetch_levels(a.inv_sigma2, inv_level_sigma2, nlevels, on_device, st));
-  a.n_problems = n_kfs; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.mode = 2 | 4 | 8; a.th_dist = 50;   // TH_LOW
+  a.n_problems = n_kfs; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.mode = sim3_variant ? (2 | 4 | 16) : (2 | 4 | 8); a.th_dist = 50;   // TH_LOW; :1019 divides 1.0 by z in double, :862 in float
   a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = bf; a.log_scale = log_scale_factor; a.th = th;
   g_launches += launch_project_search(a, st);
   CU(cudaGetLastError());
@@ -948,6 +948,51 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
     CU(cudaStreamSynchronize(st));
   }
   (void)n2;
+  return ORBX_OK;
+}
+
+orbx_status orbx_search_projection_ordered_batch(const orbx_keypoint* kps_un, const uint8_t* desc, const int* n, int n_problems, int cap,
+                                                 const float* grid_bounds, const int* cell_start, const int* cell_items,
+                                                 const float* target_bounds, const float* pose, const float* Ow, float fx, float fy, float cx,
+                                                 float cy, const float* scale_factors, int nlevels, float log_scale_factor,
+                                                 const uint8_t* occupied, const uint8_t* mp_valid, const float* mp_xw, const float* mp_normal,
+                                                 const float* mp_min_dist, const float* mp_max_dist, const uint8_t* mp_desc,
+                                                 const float* mp_src_angle, const int* m, int mcap, float th, int max_dist, int relocalisation,
+                                                 int check_orientation, int* assigned, int* n_matches, int on_device, void* stream) {
+  if (!kps_un || !desc || !n || !grid_bounds || !cell_start || !cell_items || !target_bounds || !pose || !Ow || !scale_factors || !occupied ||
+      !mp_valid || !mp_xw || !mp_normal || !mp_min_dist || !mp_max_dist || !mp_desc || !mp_src_angle || !m || !assigned || !n_matches)
+    return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (n_problems < 1 || cap < 1 || mcap < 1 || nlevels < 1 || nlevels > kMaxLevels || !(log_scale_factor > 0.f) || max_dist < 0 || max_dist > 255)
+    return fail(ORBX_ERR_BAD_ARG, "bad sizes (nlevels <= 8, log_scale_factor > 0, max_dist 0..255)");
+  cudaStream_t st = (cudaStream_t)stream;
+  Staged sg(st);
+  const size_t np = (size_t)n_problems, kc = np * cap, mc = np * mcap, cells = np * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1);
+  const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  ProjOrderedArgs a;
+  CU(sg.in(kps_un, kc, on_device, &a.kps)); CU(sg.in(desc, kc * 32, on_device, &a.desc)); CU(sg.in(n, np, on_device, &a.n));
+  CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds)); CU(sg.in(cell_start, cells, on_device, &a.cell_start)); CU(sg.in(cell_items, kc, on_device, &a.cell_items));
+  CU(sg.in(target_bounds, np * 4, on_device, &a.tgt_bounds));
+  float* d_xf = nullptr;
+  CU(sg.alloc((void**)&d_xf, np * 15 * sizeof(float)));
+  CU(cudaMemcpy2DAsync(d_xf, 15 * sizeof(float), pose, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
+  CU(cudaMemcpy2DAsync(d_xf + 12, 15 * sizeof(float), Ow, 3 * sizeof(float), 3 * sizeof(float), np, kind, st));
+  a.xf = d_xf;
+  CU(sg.in(occupied, kc, on_device, &a.occupied));
+  CU(sg.in(mp_valid, mc, on_device, &a.valid)); CU(sg.in(mp_xw, mc * 3, on_device, &a.xw)); CU(sg.in(mp_normal, mc * 3, on_device, &a.normal));
+  CU(sg.in(mp_min_dist, mc, on_device, &a.dmin)); CU(sg.in(mp_max_dist, mc, on_device, &a.dmax)); CU(sg.in(mp_desc, mc * 32, on_device, &a.mp_desc));
+  CU(sg.in(mp_src_angle, mc, on_device, &a.src_angle)); CU(sg.in(m, np, on_device, &a.m));
+  if (on_device) { a.assigned = assigned; a.nm = n_matches; }
+  else { CU(sg.alloc((void**)&a.assigned, kc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
+  CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st));
+  a.n_problems = n_problems; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.reloc = relocalisation ? 1 : 0; a.th_dist = max_dist;
+  a.checkOri = check_orientation ? 1 : 0; a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.log_scale = log_scale_factor; a.th = th;
+  g_launches += launch_project_match_ordered(a, st);
+  CU(cudaGetLastError());
+  if (!on_device) {
+    CU(cudaMemcpyAsync(assigned, a.assigned, kc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
   return ORBX_OK;
 }
 

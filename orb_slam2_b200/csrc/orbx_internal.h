@@ -170,6 +170,19 @@ int launch_scatter_matches(const int* best, const int* mp_index, const int* m, i
 struct Sim3AgreeArgs { const int* match1; const int* match2; const int* n1; int cap; int* matches12; int* nfound; };
 int launch_sim3_agree(const Sim3AgreeArgs& a, int n_problems, cudaStream_t st);
 
+struct ProjOrderedArgs {
+  const orbx_keypoint* kps; const uint8_t* desc; const int* n;                          // targets, [P][cap]
+  const float* grid_bounds; const int* cell_start; const int* cell_items; const float* tgt_bounds; const float* xf;
+  const uint8_t* occupied;
+  const uint8_t* valid; const float* xw; const float* normal; const float* dmin; const float* dmax; const uint8_t* mp_desc;
+  const float* src_angle; const int* m;
+  int n_problems, cap, mcap, nlevels, reloc, th_dist, checkOri;
+  float fx, fy, cx, cy, log_scale, th;
+  float scale[kMaxLevels];
+  int* assigned; int* nm;
+};
+int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st);
+
 struct TriArgs {
   const orbx_keypoint* k1; const uint8_t* d1; const uint8_t* hasMp1; const float* uR1; const int* node1; const int* n1;
   const orbx_keypoint* k2; const uint8_t* d2; const uint8_t* hasMp2; const float* uR2; const int* node2; const int* n2;

@@ -750,3 +750,19 @@ def test_cuda_fuse_and_sim3_reproduce_reference(gx):
         n, m12 = gx.ORBmatcher.SearchBySim3(FG, d1, d2, fx["kf_bounds"], (T1[:3, :3], T1[:3, 3]), (R2, t2), gs.KITTI_CAM, scale, float(fx["log_scale"]), fx["sim3_xf"],
                                             side(mp1), side(mp2), 7.5)
         assert n == case["n_sim3"] and np.array_equal(m12, fx["sim3"])
+        # K16 with the Sim3 variant of Fuse (:977) and K17: SearchByProjection(pKF, Scw, ...) :290 / SearchByProjection(Frame, pKF, ...) :1472
+        from oracle.pyoracle import kf_rule                   # index rule only
+        x = fx["scw_xf"]; Rcw, tcw, Ow = x[:9].reshape(3, 3), x[9:12], x[12:15]
+        best = gx.ORBmatcher.FuseSearch(FG, 1, ur[1, :len(k2)], d2, fx["kf_bounds"], Rcw, tcw, Ow, cam, scale, fx["inv_sigma2"], float(fx["log_scale"]), mpd, 4.0,
+                                        sim3_variant=True)
+        assert int((best >= 0).sum()) == case["n_fuse_scw"] and np.array_equal(best, fx["fuse_scw"])
+        n2 = len(k2); has2 = fx["has2"]
+        mpo = dict(mpd, angle=k1["angle"][mp1["idx"]])
+        occ = np.array([has2[i] and kf_rule(i, 7, 30) for i in range(n2)], np.uint8)
+        n, a = gx.ORBmatcher(0.75, True).SearchByProjectionOrdered(FG, 1, d2, fx["kf_bounds"], Rcw, tcw, Ow, gs.KITTI_CAM, scale, float(fx["log_scale"]), occ, mpo, 10.0, 50, False)
+        assert n == case["n_proj_scw"] and np.array_equal(a, np.where(fx["proj_scw"] >= 0, fx["proj_scw"], -1))
+        occ = np.array([has2[i] and kf_rule(i, 11, 20) for i in range(n2)], np.uint8)
+        mpr = dict(mpo, valid=np.array([not kf_rule(k, 9, 25) for k in range(len(mp1))], np.uint8))
+        n, a = gx.ORBmatcher(0.9, case["check_ori"]).SearchByProjectionOrdered(FG, 1, d2, (0.0, float(w), 0.0, float(h)), R2, t2, fx["reloc_Ow"], gs.KITTI_CAM, scale,
+                                                                                 float(fx["log_scale"]), occ, mpr, 10.0, 100, True)
+        assert n == case["n_proj_kf"] and np.array_equal(a, np.where(fx["proj_kf"] >= 0, fx["proj_kf"], -1))

@@ -315,3 +315,34 @@ def test_logf_restatement(oracle):
     xs = np.concatenate([rng.uniform(0.01, 100, 20000), np.exp(rng.uniform(-80, 80, 20000)), [1.0, 1.2, 0.5, 2.0]]).astype(np.float32)
     for x in xs:
         assert np.float32(L.orbo_logf(float(x))).tobytes() == np.float32(libm.logf(float(x))).tobytes(), x
+
+
+@pytest.mark.parametrize("case", GOLD_SLAM["kf"], ids=lambda c: f"kf{c['seed']}-L{c['L']}")
+def test_oracle_remaining_matcher_members_match_reference(oracle, case):
+    """SearchByProjection(pKF, Scw, ...) :290, SearchByProjection(CurrentFrame, pKF, sAlreadyFound, ...) :1472 and
+    Fuse(pKF, Scw, ...) :977 of the reference on the same real KeyFrames / MapPoints."""
+    c = _kc.build(oracle, case)
+    F1, F2, fx = c["F1"], c["F2"], c["fx"]
+    cam, bf, T2 = c["cam"], c["cfg"]["bf"], c["T2"]
+    w, h = c["cfg"]["w"], c["cfg"]["h"]
+    mp1 = fx["mps1"]; n2 = len(F2["keys"])
+    fb = (0.0, float(w), 0.0, float(h))
+    kfv = (cam[0], cam[1], cam[2], cam[3], bf, float(fx["log_scale"]), *fx["kf_bounds"])
+    mpd = dict(valid=np.ones(len(mp1), np.uint8), xw=mp1["xw"], normal=mp1["normal"], dmin=mp1["dmin"], dmax=mp1["dmax"], desc=mp1["desc"],
+               angle=F1["keys"]["angle"][mp1["idx"]])
+    x = fx["scw_xf"]; Rcw, tcw, Ow = x[:9].reshape(3, 3), x[9:12], x[12:15]
+    occ = np.array([c["has2"][i] and oracle.kf_rule(i, 7, 30) for i in range(n2)], np.uint8)
+    a, n = oracle.project_match_ordered(F2["keys"], F2["desc"], kfv, fb, c["scale"], False, Rcw, tcw, Ow, mpd, 10.0, 50, False, occ)
+    ref = fx["proj_scw"]
+    assert n == case["n_proj_scw"] and np.array_equal(a, np.where(ref >= 0, ref, -1)) and np.array_equal(ref == -2, occ.astype(bool))
+    occ = np.array([c["has2"][i] and oracle.kf_rule(i, 11, 20) for i in range(n2)], np.uint8)
+    mpd2 = dict(mpd); mpd2["valid"] = np.array([not oracle.kf_rule(k, 9, 25) for k in range(len(mp1))], np.uint8)
+    kfv2 = (cam[0], cam[1], cam[2], cam[3], bf, float(fx["log_scale"]), *fb)
+    a, n = oracle.project_match_ordered(F2["keys"], F2["desc"], kfv2, fb, c["scale"], True, T2[:3, :3], T2[:3, 3], fx["reloc_Ow"], mpd2, 10.0, 100,
+                                        case["check_ori"], occ)
+    ref = fx["proj_kf"]
+    assert n == case["n_proj_kf"] and np.array_equal(a, np.where(ref >= 0, ref, -1))
+    best = oracle.project_search(F2["keys"], F2["desc"], F2["u_right"], kfv, c["scale"], fx["inv_sigma2"], dict(R1=Rcw, t1=tcw, Ow=Ow),
+                                 dict(valid=mpd["valid"], xw=mp1["xw"], normal=mp1["normal"], dmin=mp1["dmin"], dmax=mp1["dmax"], desc=mp1["desc"]), 4.0, 2 | 4 | 16, 50)
+    assert int((best >= 0).sum()) == case["n_fuse_scw"] and np.array_equal(best, fx["fuse_scw"])
+    assert min(case["n_proj_scw"], case["n_proj_kf"], case["n_fuse_scw"]) > 50

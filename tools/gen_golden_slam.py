@@ -91,16 +91,18 @@ if __name__ == "__main__":
     for seed, L, only_stereo, mono, ori in KF_CASES:
         ims, V, T1, T2, F12 = kf_case_inputs(seed, L)
         o = O.ref_slam_kf(*ims, cfg["nfeatures"], KITTI_CAM, cfg["bf"], V, T1, T2, F12, check_ori=ori, only_stereo=only_stereo, mono=mono, **KF_PARAMS)
+        o2 = O.ref_slam_kf(*ims, cfg["nfeatures"], KITTI_CAM, cfg["bf"], V, T1, T2, F12, check_ori=ori, only_stereo=only_stereo, mono=mono, fuse_scw=True, **KF_PARAMS)
         name = f"ref_kf_{seed}.npz"
         np.savez_compressed(os.path.join(ROOT, "tests/golden", name), mps1=o["mps1"], track=o["track"], Ow1=o["Ow1"],
                             node1=o["node1"], node2=o["node2"], nodec=o["nodec"], has1=o["has1"], has2=o["has2"],
                             bow_kk=o["bow_kk"][1], bow_kf=o["bow_kf"][1], tri=o["tri"][1], proj=o["proj"][1], proj_last=o["proj_last"][1],
                             mps2=o["mps2"], log_scale=np.float32(o["log_scale"]), kf_bounds=o["kf_bounds"], inv_sigma2=o["inv_sigma2"],
                             sim3_xf=np.concatenate([o["sim3_xf"][k].reshape(-1) for k in ("sR12", "t12", "sR21", "t21")]).astype(np.float32),
-                            sim3=o["sim3"][1], fuse=o["fuse"][1])
+                            sim3=o["sim3"][1], fuse=o["fuse"][1], proj_scw=o["proj_scw"][1], proj_kf=o["proj_kf"][1], reloc_Ow=o["reloc_Ow"],
+                            scw_xf=np.concatenate([o["scw_xf"][k].reshape(-1) for k in ("Rcw", "tcw", "Ow")]).astype(np.float32), fuse_scw=o2["fuse"][1])
         out["kf"].append(dict(seed=seed, L=L, only_stereo=only_stereo, mono=mono, check_ori=ori, fixture=name, n1=len(o["F1"]["keys"]),
                               n2=len(o["F2"]["keys"]), map_points=len(o["mps1"]), keys1_sha256=sha(o["F1"]["keys"]), u_right2_sha256=sha(o["F2"]["u_right"]),
-                              n_bow_kk=o["bow_kk"][0], n_bow_kf=o["bow_kf"][0], n_tri=o["tri"][0], n_proj=o["proj"][0], n_proj_last=o["proj_last"][0], n_sim3=o["sim3"][0], n_fuse=o["fuse"][0]))
+                              n_bow_kk=o["bow_kk"][0], n_bow_kf=o["bow_kf"][0], n_tri=o["tri"][0], n_proj=o["proj"][0], n_proj_last=o["proj_last"][0], n_sim3=o["sim3"][0], n_fuse=o["fuse"][0], n_proj_scw=o["proj_scw"][0], n_proj_kf=o["proj_kf"][0], n_fuse_scw=o2["fuse"][0]))
     lists = distinct_lists()
     chosen = O.ref_slam_distinct(lists, synth.mono_frame(1, 1241, 376))
     out["distinct"] = dict(seed=21, n=len(lists), chosen_sha256=sha(chosen))
