@@ -73,6 +73,12 @@ void orbx_extractor_destroy(orbx_extractor* ext);
 orbx_status orbx_get_tables(const orbx_extractor* ext, int* nlevels, float* scale, float* inv_scale,
                             float* sigma2, float* inv_sigma2, int* quota);
 
+/* The same tables from the constructor arguments alone, without an extractor handle or a device: the reference's
+ * constructor fills them (src/ORBextractor.cc:414-446) and every Frame constructor reads them BEFORE the first
+ * extraction (src/Frame.cc:69-75), so a stand-in class must be able to answer at once.  Any output may be NULL. */
+orbx_status orbx_compute_tables(const orbx_params* params, int* nlevels, float* scale_factors, float* inv_scale_factors,
+                                float* level_sigma2, float* inv_level_sigma2, int* features_per_level);
+
 /* Upper bound on keypoints one image can return (nfeatures plus up to 3 per level, because the
  * quad-tree's last split may overshoot, src/ORBextractor.cc:730). Size caller buffers with it. */
 int orbx_max_keypoints(const orbx_extractor* ext);

@@ -97,8 +97,7 @@ class ORBextractor {
  private:
   std::vector<float> Table(int which) {
     float t[4][8]; int n = 0;
-    if (!handle_) throw std::runtime_error("orbx: extractor tables need Ensure(w,h) or a first extraction");
-    orbx_check(orbx_get_tables(handle_, &n, t[0], t[1], t[2], t[3], nullptr));
+    orbx_check(orbx_compute_tables(&params_, &n, t[0], t[1], t[2], t[3], nullptr));   // no handle needed: Frame reads these first
     return std::vector<float>(t[which], t[which] + n);
   }
   orbx_params params_;

@@ -393,6 +393,18 @@ orbx_status orbx_get_tables(const orbx_extractor* e, int* nlevels, float* scale,
   return ORBX_OK;
 }
 
+orbx_status orbx_compute_tables(const orbx_params* params, int* nlevels, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                                int* quota) {
+  if (!params) return fail(ORBX_ERR_BAD_ARG, "null params");
+  if (params->nlevels < 1 || params->nlevels > kMaxLevels || !(params->scale_factor > 1.0f) || params->nfeatures < 1)
+    return fail(ORBX_ERR_BAD_ARG, "nlevels must be 1..8, scale_factor > 1, nfeatures >= 1");
+  orbx_extractor tmp;                       // host tables only: no device is touched
+  tmp.P = *params; tmp.nlevels = params->nlevels;
+  make_tables(&tmp);
+  return orbx_get_tables(&tmp, nlevels, scale, inv_scale, sigma2, inv_sigma2, quota);
+}
+
+
 int orbx_max_keypoints(const orbx_extractor* e) { return e ? e->kp_cap : 0; }
 
 orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, int w, int h, int stride,

@@ -49,6 +49,24 @@ def test_host_helpers_without_gpu():
     assert (ORBmatcher.TH_LOW, ORBmatcher.TH_HIGH, ORBmatcher.HISTO_LENGTH) == (50, 100, 30)
 
 
+def test_tables_without_a_device(oracle):
+    """orbx_compute_tables: the constructor tables (src/ORBextractor.cc:414-446) from the parameters alone - what every Frame
+    constructor reads before the first extraction (src/Frame.cc:69-75).  Checked against the oracle (itself pinned to the reference)."""
+    import numpy as np
+    from orb_slam2_b200 import api
+    L = api.lib()
+    for nf, sf, nl in [(2000, 1.2, 8), (1000, 1.2, 8), (1200, 1.2, 8), (500, 1.5, 5)]:
+        p = api._Params(nf, sf, nl, 20, 7)
+        n = ctypes.c_int(); t = [np.zeros(8, np.float32) for _ in range(4)]; q = np.zeros(8, np.int32)
+        assert L.orbx_compute_tables(ctypes.byref(p), ctypes.byref(n), *[a.ctypes.data_as(ctypes.c_void_p) for a in t], q.ctypes.data_as(ctypes.c_void_p)) == 0
+        ref = oracle.Extractor(nf, sf, nl).tables()
+        assert n.value == nl
+        for a, key in zip(t, ("scale", "inv", "sigma2", "invsigma2")):
+            assert np.array_equal(a[:nl].view(np.uint32), ref[key].view(np.uint32)), key
+        assert np.array_equal(q[:nl], ref["quota"])
+    assert L.orbx_compute_tables(ctypes.byref(api._Params(1000, 1.2, 9, 20, 7)), None, None, None, None, None, None) == api.ERR_BAD_ARG
+
+
 def test_bad_arguments_rejected_before_touching_the_gpu():
     from orb_slam2_b200 import api
     L = api.lib()
