@@ -65,6 +65,9 @@ class ORBextractor {
     _descriptors.create(n, 32, CV_8U);
     cv::Mat out = _descriptors.getMat();
     for (int i = 0; i < n; ++i) std::copy(desc.begin() + (size_t)i * 32, desc.begin() + (size_t)(i + 1) * 32, out.ptr(i));
+#ifdef ORBX_DROPIN_HOST_PYRAMID
+    DownloadPyramid();   // for callers that still read mvImagePyramid on the host (unmodified Frame::ComputeStereoMatches)
+#endif
   }
 
   int GetLevels() { return params_.nlevels; }
