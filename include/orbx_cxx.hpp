@@ -155,6 +155,7 @@ struct FrameGridGPU {
   }
 };
 
+#ifndef ORBX_CXX_EXTRACTOR_ONLY   // dropin/ORBextractor.h: inside the reference tree include/ORBmatcher.h declares the class
 class ORBmatcher {
  public:
   static const int TH_LOW = 50, TH_HIGH = 100, HISTO_LENGTH = 30;   // src/ORBmatcher.cc:37-39
@@ -187,6 +188,8 @@ class ORBmatcher {
   float mfNNratio;
   bool mbCheckOrientation;
 };
+
+#endif  // ORBX_CXX_EXTRACTOR_ONLY
 
 }  // namespace ORB_SLAM2
 #endif  // ORBX_CXX_HPP_

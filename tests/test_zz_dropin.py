@@ -1,0 +1,87 @@
+"""The drop-in boundary, end to end: oracle/_ref/orbref_slam is the reference's own Frame / KeyFrame / MapPoint / Map / ORBmatcher /
+ORBextractor sources behind a small driver; oracle/_ref/orbref_slam_gpu is the SAME driver and the SAME reference sources with only
+src/ORBextractor.cc and src/ORBmatcher.cc swapped for dropin/ORBextractor.h + dropin/ORBmatcher.cc, i.e. for the orbx library.
+Both run here on the same inputs (real stereo / monocular Frame constructors, real KeyFrames and MapPoints, every ORBmatcher
+member) and must write the same bytes.  The binaries are built where /root/reference exists (make -C oracle ref) and travel with
+the snapshot; nothing here reads the reference tree."""
+import os
+
+import numpy as np
+import pytest
+
+from orb_slam2_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _same(a, b, path=""):
+    if isinstance(a, dict):
+        assert a.keys() == b.keys(), path
+        for k in a:
+            _same(a[k], b[k], f"{path}/{k}")
+    elif isinstance(a, (tuple, list)):
+        assert len(a) == len(b), path
+        for i, (x, y) in enumerate(zip(a, b)):
+            _same(x, y, f"{path}[{i}]")
+    elif isinstance(a, np.ndarray):
+        assert a.dtype == b.dtype and a.shape == b.shape and a.tobytes() == b.tobytes(), path
+    else:
+        assert a == b, path
+
+
+@pytest.fixture(scope="module")
+def both(oracle):
+    gpu_bin = os.path.join(os.path.dirname(oracle.REF_SLAM_BIN), "orbref_slam_gpu")
+    if not (oracle.ref_slam_available() and os.path.exists(gpu_bin)):
+        pytest.skip("oracle/_ref/orbref_slam(_gpu) not built (make -C oracle ref, needs /root/reference)")
+    ref_bin = oracle.REF_SLAM_BIN
+
+    def run(fn, *args, **kw):
+        out = []
+        for b in (ref_bin, gpu_bin):
+            oracle.REF_SLAM_BIN = b
+            try:
+                out.append(fn(*args, **kw))
+            finally:
+                oracle.REF_SLAM_BIN = ref_bin
+        return out
+    return run
+
+
+def test_stereo_frame_constructor(oracle, both):
+    cfg = synth.KITTI
+    for seed in (5, 43):
+        L, R, _ = synth.stereo_pair(seed, cfg["w"], cfg["h"])
+        ref, gpu = both(oracle.ref_slam_stereo, L, R, cfg["nfeatures"], (718.856, 718.856, 607.1928, 185.2157), cfg["bf"])
+        _same(ref, gpu)
+        assert (ref["u_right"] >= 0).sum() > 300
+
+
+def test_monocular_frames_and_initialisation(oracle, both):
+    a, b, _ = synth.mono_pair(60, 640, 480)
+    ref, gpu = both(oracle.ref_slam_init, a, b, 1000, (517.3, 516.5, 318.6, 255.3), 0.9, 100, True)
+    _same(ref, gpu)
+    assert ref[2] > 50
+
+
+def test_distorted_camera_grid(oracle, both):
+    tum1 = (517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+    rng = np.random.default_rng(2)
+    qs = [(float(rng.uniform(0, 640)), float(rng.uniform(0, 480)), float(rng.uniform(5, 100)), -1, -1) for _ in range(50)]
+    ref, gpu = both(oracle.ref_slam_grid, synth.mono_frame(300, 640, 480), 1000, tum1, qs)
+    _same(ref, gpu)
+
+
+@pytest.mark.parametrize("fuse_scw", [False, True])
+def test_keyframes_mappoints_and_every_matcher_member(oracle, both, fuse_scw):
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
+    kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
+    gs = kc.gs
+    cfg = synth.KITTI
+    for seed, L, only_stereo, mono, ori in gs.KF_CASES[:2]:
+        ims, V, T1, T2, F12 = gs.kf_case_inputs(seed, L)
+        ref, gpu = both(oracle.ref_slam_kf, *ims, cfg["nfeatures"], gs.KITTI_CAM, cfg["bf"], V, T1, T2, F12, check_ori=ori, only_stereo=only_stereo,
+                        mono=mono, fuse_scw=fuse_scw, **gs.KF_PARAMS)
+        _same(ref, gpu)
+        assert ref["bow_kk"][0] > 20 and ref["fuse"][0] > 50 and ref["sim3"][0] > 50
