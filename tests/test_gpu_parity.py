@@ -234,6 +234,37 @@ def test_stereo_two_handles_like_the_reference(gx, oracle):
     assert int(nm[0]) == 0
 
 
+def test_stereo_saturated_strips_take_the_scalar_sad(gx, oracle):
+    """K5 evaluates the centre-subtracted SAD on packed bytes when right pixel + (cl - cr) stays within a byte
+    over the whole 11x21 strip and falls back to a scalar form otherwise.  A right image that is 40 grey levels
+    darker (or 35 brighter) with 1 % salt (255) and pepper (0) pixels puts a saturated pixel into most strips,
+    so most accepted matches go through the scalar form and the rest through the packed one: both must equal
+    the oracle bit for bit."""
+    cfg = synth.EUROC
+    w, h, nf, bf, fx = cfg["w"], cfg["h"], cfg["nfeatures"], cfg["bf"], cfg["fx"]
+    rng = np.random.default_rng(5)
+    pairs = []
+    for seed, off in [(41, 40), (42, -35)]:
+        L, R, _ = synth.stereo_pair(seed, w, h)
+        R2 = np.clip(R.astype(np.int32) - off, 0, 255).astype(np.uint8)
+        m = rng.random(R2.shape)
+        R2[m < 0.005] = 255
+        R2[m > 0.995] = 0
+        pairs.append((L, R2))
+    n = len(pairs)
+    G = _ext(gx, w, h, nf, batch=2 * n)
+    G.extract_batch(np.stack([p[0] for p in pairs] + [p[1] for p in pairs]))
+    ur, dp, nm = gx.ComputeStereoMatches(G, G, bf, fx, n=n, slotL0=0, slotR0=n)
+    for i in range(n):
+        EL, ER = oracle.Extractor(nf), oracle.Extractor(nf)
+        kl, dl = EL.extract(pairs[i][0]); kr, dr = ER.extract(pairs[i][1])
+        rur, rdp, _, rm = oracle.stereo(EL, ER, kl, dl, kr, dr, bf, fx)
+        cnt = len(kl)
+        assert int(nm[i]) == rm and rm > 100
+        assert np.array_equal(ur[i, :cnt].view(np.uint32), rur.view(np.uint32))
+        assert np.array_equal(dp[i, :cnt].view(np.uint32), rdp.view(np.uint32))
+
+
 @pytest.mark.parametrize("nf", [1000, 2000])
 def test_search_for_initialization(gx, oracle, nf):
     w, h = 640, 480

@@ -1,5 +1,5 @@
 import sys, numpy as np, torch, time
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, '.')
 import orb_slam2_b200 as gx
 from orb_slam2_b200 import synth
 cfg = synth.KITTI; w, h = cfg['w'], cfg['h']
