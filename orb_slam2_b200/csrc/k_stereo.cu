@@ -21,7 +21,6 @@
 namespace orbx {
 
 constexpr int kStWarps = 8;
-constexpr int kStPerCta = 64;   // left keypoints per CTA (the bin sort of the right keypoints is redone per CTA)
 
 __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4* __restrict__ b) {
   const uint4 b0 = __ldg(b), b1 = __ldg(b + 1);
@@ -39,109 +38,125 @@ __device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t c)
   return d;
 }
 
-constexpr int kRowBinShift = 3;          // right keypoints are binned by (int)y >> 3
-constexpr int kMaxBins = 520;            // images up to 4160 rows
-
-__global__ void __launch_bounds__(kStWarps * 32) k_stereo_match(StereoArgs a, int chunks) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  const int capR = a.R.kp_cap;
-  float* s_x = reinterpret_cast<float*>(smem);
-  int* s_bin = reinterpret_cast<int*>(s_x + capR);                 // [kMaxBins+1] start offsets, then as many cursors
-  short* s_min = reinterpret_cast<short*>(s_bin + 2 * (kMaxBins + 1));
-  short* s_max = s_min + capR;
-  unsigned short* s_idx = reinterpret_cast<unsigned short*>(s_max + capR);
-  int8_t* s_oct = reinterpret_cast<int8_t*>(s_idx + capR);
-  uint8_t* s_patch = reinterpret_cast<uint8_t*>(s_oct) + ((capR + 15) & ~15);
-
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int img = blockIdx.x / chunks, chunk = blockIdx.x - img * chunks;
-  const int slotL = a.slotL0 + img, slotR = a.slotR0 + img;
-  const int nL = a.L.nkp[slotL], nR = a.R.nkp[slotR];
-  if (chunk * kStPerCta >= nL) return;
-  const orbx_keypoint* kL = a.L.kps + (size_t)slotL * a.L.kp_cap;
+// K5a: the right keypoints of one pair, counting-sorted by (octave, (int)y) into 16-byte records
+// {x, floor(y-r) | ceil(y+r) << 16, iR, 0} (r = 2 * scale[octave], src/Frame.cc:483-493) plus the table of bin
+// starts T[octave * H + row].  This is the reference's vRowIndices turned inside out: a left keypoint on row v
+// of level l reads, for each octave l-1 .. l+1, the one contiguous run of rows that can reach v.  The order
+// inside a bin is irrelevant because the winner is the lexicographic minimum of (distance, iR).
+constexpr int kRowThreads = 1024;
+__global__ void __launch_bounds__(kRowThreads) k_stereo_rows(StereoArgs a) {
+  __shared__ int s_part[kRowThreads / 32];
+  const int img = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int slotR = a.slotR0 + img;
+  const int nR = a.R.nkp[slotR];
+  const int H = a.R.geom[0].h, nb = a.R.nlevels * H;
+  int* T = a.tab + (size_t)img * a.tab_stride;           // nb + 2 entries; T[b] = start of bin b when the kernel ends
+  uint4* rec = a.rec + (size_t)img * a.R.kp_cap;
   const orbx_keypoint* kR = a.R.kps + (size_t)slotR * a.R.kp_cap;
+  for (int i = tid; i < nb + 2; i += kRowThreads) T[i] = 0;
+  __syncthreads();
+  for (int i = tid; i < nR; i += kRowThreads) {
+    const int b = kR[i].octave * H + min(max((int)kR[i].y, 0), H - 1);
+    atomicAdd(&T[b + 2], 1);
+  }
+  __syncthreads();
+  // inclusive scan of T[1 .. nb+1]: T[b+1] becomes the start of bin b, advanced to its end by the scatter below
+  const int len = nb + 1, per = (len + kRowThreads - 1) / kRowThreads;
+  const int lo = 1 + tid * per, hi = min(lo + per, 1 + len);
+  int sum = 0;
+  for (int i = lo; i < hi; ++i) sum += T[i];
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_part[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int v = s_part[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += t;
+    }
+    s_part[lane] = v;
+  }
+  __syncthreads();
+  int run = incl - sum + (warp ? s_part[warp - 1] : 0);
+  for (int i = lo; i < hi; ++i) { run += T[i]; T[i] = run; }
+  __syncthreads();
+  for (int i = tid; i < nR; i += kRowThreads) {
+    const orbx_keypoint kp = kR[i];
+    const int b = kp.octave * H + min(max((int)kp.y, 0), H - 1);
+    const int pos = atomicAdd(&T[b + 1], 1);
+    const float r = __fmul_rn(2.0f, a.L.geom[kp.octave].scale);                     // :487
+    const int ymax = (int)ceilf(__fadd_rn(kp.y, r)), ymin = (int)floorf(__fsub_rn(kp.y, r));
+    rec[pos] = make_uint4(__float_as_uint(kp.x), ((unsigned)ymin & 0xffffu) | ((unsigned)ymax << 16), (unsigned)i, 0u);
+  }
+}
+
+// K5b: one warp per left keypoint, no block-level step.
+__global__ void __launch_bounds__(kStWarps * 32, 6) k_stereo_match(StereoArgs a, int ctas_per_img) {
+  __shared__ __align__(16) uint8_t s_patch[kStWarps * 384];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int img = blockIdx.x / ctas_per_img;
+  const int iL = (blockIdx.x - img * ctas_per_img) * kStWarps + warp;
+  const int slotL = a.slotL0 + img, slotR = a.slotR0 + img;
+  if (iL >= a.L.nkp[slotL]) return;
+  const orbx_keypoint* kL = a.L.kps + (size_t)slotL * a.L.kp_cap;
   const uint8_t* dL = a.L.desc + (size_t)slotL * a.L.kp_cap * 32;
   const uint8_t* dR = a.R.desc + (size_t)slotR * a.R.kp_cap * 32;
-
-  // Right keypoints, counting-sorted into 8-row bins (the reference's vRowIndices table,
-  // src/Frame.cc:476-493, coarsened): a left keypoint on row v only has to look at the bins that
-  // can hold a right keypoint with floor(y-r) <= v <= ceil(y+r).  The order inside a bin is
-  // irrelevant because the winner is the lexicographic minimum of (distance, iR).
-  const int nbins = min(kMaxBins, (a.L.geom[0].h >> kRowBinShift) + 1);
-  int* s_cur = s_bin + kMaxBins + 1;
-  for (int i = tid; i <= nbins; i += kStWarps * 32) { s_bin[i] = 0; s_cur[i] = 0; }
-  __syncthreads();
-  for (int i = tid; i < nR; i += kStWarps * 32) {
-    const int b = min(max((int)kR[i].y >> kRowBinShift, 0), nbins - 1);
-    atomicAdd(&s_bin[b + 1], 1);
-  }
-  __syncthreads();
-  if (warp == 0) {           // inclusive scan of the counts -> bin start offsets
-    int carry = 0;
-    for (int base = 0; base <= nbins; base += 32) {
-      const int i = base + lane;
-      int v = i <= nbins ? s_bin[i] : 0;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, v, o);
-        if (lane >= o) v += t;
-      }
-      if (i <= nbins) s_bin[i] = v + carry;
-      carry += __shfl_sync(0xffffffffu, v, 31);
-    }
-  }
-  __syncthreads();
-  for (int i = tid; i < nR; i += kStWarps * 32) {
-    const orbx_keypoint kp = kR[i];
-    const int b = min(max((int)kp.y >> kRowBinShift, 0), nbins - 1);
-    const int pos = s_bin[b] + atomicAdd(&s_cur[b], 1);
-    const float r = __fmul_rn(2.0f, a.L.geom[kp.octave].scale);                     // :487
-    s_max[pos] = (short)(int)ceilf(__fadd_rn(kp.y, r));
-    s_min[pos] = (short)(int)floorf(__fsub_rn(kp.y, r));
-    s_oct[pos] = (int8_t)kp.octave;
-    s_x[pos] = kp.x;
-    s_idx[pos] = (unsigned short)i;
-  }
-  __syncthreads();
-  const int reach = (int)ceilf(__fmul_rn(2.0f, a.L.geom[a.L.nlevels - 1].scale)) + 2;   // max |(int)yR - row| of a candidate
-
-  uint8_t* lp = s_patch + warp * 384;   // 11x11 left patch
+  const int* T = a.tab + (size_t)img * a.tab_stride;
+  const uint4* rec = a.rec + (size_t)img * a.R.kp_cap;
+  uint8_t* lp = s_patch + warp * 384;   // 11x11 left patch   (scalar SAD form only)
   uint8_t* rp = lp + 128;               // 11x21 right strip
-  for (int t = 0; t < kStPerCta / kStWarps; ++t) {
-    const int iL = chunk * kStPerCta + t * kStWarps + warp;
-    if (iL >= nL) break;
+  do {                                  // one pass; "continue" = this keypoint has no stereo match
     const size_t oi = (size_t)img * a.cap + iL;
     if (lane == 0) { a.uRight[oi] = -1.f; a.depth[oi] = -1.f; a.sad[oi] = -1; }
-    const orbx_keypoint kl = kL[iL];
-    const int lvl = kl.octave;
-    const float uL = kl.x, vL = kl.y;
+    const float uL = kL[iL].x, vL = kL[iL].y;
+    const int lvl = kL[iL].octave;
     const int row = (int)vL;
     const float minU = __fsub_rn(uL, a.maxD), maxU = uL;
     if (maxU < 0) continue;
     const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32));
     const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32) + 1);
-    unsigned best = 100u << 16;                                                      // TH_HIGH
-    const int b_lo = min(max((row - reach) >> kRowBinShift, 0), nbins - 1), b_hi = min(max((row + reach) >> kRowBinShift, 0), nbins - 1);
-    const int e_end = s_bin[b_hi + 1];
-    for (int e = s_bin[b_lo] + lane; e < e_end; e += 32) {
-      if (row < s_min[e] || row > s_max[e]) continue;
-      const int oc = s_oct[e];
-      if (oc < lvl - 1 || oc > lvl + 1) continue;
-      const float uR = s_x[e];
-      if (uR >= minU && uR <= maxU) {
-        const unsigned iR = s_idx[e];
-        const unsigned d = (unsigned)hamming256(a0, a1, reinterpret_cast<const uint4*>(dR + (size_t)iR * 32));
-        best = min(best, (d << 16) | iR);
+    // the three runs (octaves lvl-1, lvl, lvl+1): lanes 0..5 fetch their bounds from the table.
+    // floor(y-r) <= row <= ceil(y+r)  =>  |(int)y - row| <= ceil(r) + 1
+    const int H = a.R.geom[0].h;
+    int tv = 0;
+    if (lane < 6) {
+      const int o = lvl - 1 + (lane >> 1);
+      if (o >= 0 && o < a.R.nlevels) {
+        const int reach = (int)ceilf(__fmul_rn(2.0f, a.L.geom[o].scale)) + 1;
+        const int rr = (lane & 1) ? min(max(row + reach, 0), H - 1) + 1 : min(max(row - reach, 0), H - 1);
+        tv = T[o * H + rr];
       }
     }
+    const int s0 = __shfl_sync(0xffffffffu, tv, 0), n0 = __shfl_sync(0xffffffffu, tv, 1) - s0;
+    const int s1 = __shfl_sync(0xffffffffu, tv, 2), n1 = __shfl_sync(0xffffffffu, tv, 3) - s1;
+    const int s2 = __shfl_sync(0xffffffffu, tv, 4), n2 = __shfl_sync(0xffffffffu, tv, 5) - s2;
+    const int total = n0 + n1 + n2;
+    unsigned best = 100u << 16;                                                      // TH_HIGH
+    float bestU = 0.f;
+    for (int j = lane; j < total; j += 32) {
+      const int pos = j < n0 ? s0 + j : j < n0 + n1 ? s1 + (j - n0) : s2 + (j - n0 - n1);
+      const uint4 rc = __ldg(rec + pos);
+      const int ymin = (int)(short)(rc.y & 0xffffu), ymax = (int)rc.y >> 16;
+      const float uR = __uint_as_float(rc.x);
+      if (row >= ymin && row <= ymax && uR >= minU && uR <= maxU) {
+        const unsigned key = ((unsigned)hamming256(a0, a1, reinterpret_cast<const uint4*>(dR + (size_t)rc.z * 32)) << 16) | rc.z;
+        if (key < best) { best = key; bestU = uR; }
+      }
+    }
+    const unsigned mykey = best;
     best = __reduce_min_sync(0xffffffffu, best);
     if ((best >> 16) >= 75u) continue;                                               // (TH_HIGH+TH_LOW)/2
-    const int bestR = best & 0xFFFF;
-    const float uR0 = kR[bestR].x;
+    const float uR0 = __shfl_sync(0xffffffffu, bestU, __ffs((int)__ballot_sync(0xffffffffu, mykey == best)) - 1);
     const LevelGeom& gl = a.L.geom[lvl];
     const LevelGeom& gr = a.R.geom[lvl];
     const float inv = gl.inv_scale;
-    const float su = roundf(__fmul_rn(kl.x, inv)), sv = roundf(__fmul_rn(kl.y, inv)), sr = roundf(__fmul_rn(uR0, inv));
+    const float su = roundf(__fmul_rn(uL, inv)), sv = roundf(__fmul_rn(vL, inv)), sr = roundf(__fmul_rn(uR0, inv));
     if (sr < 0.f || __fadd_rn(sr, 11.f) >= (float)gr.w) continue;                    // :573-575
     const int cy = (int)sv, cxl = (int)su, cxr = (int)sr;
     const uint8_t* pl = a.L.pyr + gl.plane_off + (size_t)slotL * gl.plane_stride + (size_t)(kEdge + cy - 5) * gl.pitch + kEdge + cxl - 5;
@@ -243,7 +258,7 @@ __global__ void __launch_bounds__(kStWarps * 32) k_stereo_match(StereoArgs a, in
       if (disp <= 0.f) { disp = 0.01f; bestu = (float)((double)uL - 0.01); }
       if (lane == 0) { a.depth[oi] = __fdiv_rn(a.bf, disp); a.uRight[oi] = bestu; a.sad[oi] = bestSad; }
     }
-  }
+  } while (false);
 }
 
 constexpr int kMedThreads = 1024;
@@ -304,15 +319,12 @@ __global__ void __launch_bounds__(kMedThreads) k_stereo_median(StereoArgs a) {
 }
 
 int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid) {
-  const int capR = a.R.kp_cap, capL = a.L.kp_cap;
-  const int chunks = (capL + kStPerCta - 1) / kStPerCta;
-  const size_t smem1 = (size_t)capR * 10 + ((capR + 15) & ~15) + kStWarps * 384 + 2 * (kMaxBins + 1) * sizeof(int);
-  if (smem1 > 48 * 1024) cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
-  k_stereo_match<<<a.n * chunks, kStWarps * 32, smem1, st>>>(a, chunks);
+  const int ctas_per_img = (a.L.kp_cap + kStWarps - 1) / kStWarps;
+  k_stereo_rows<<<a.n, kRowThreads, 0, st>>>(a);
+  k_stereo_match<<<a.n * ctas_per_img, kStWarps * 32, 0, st>>>(a, ctas_per_img);
   if (ev_mid) cudaEventRecord(ev_mid, st);
-  (void)capL;
   k_stereo_median<<<a.n, kMedThreads, 0, st>>>(a);
-  return 2;
+  return 3;
 }
 
 }  // namespace orbx

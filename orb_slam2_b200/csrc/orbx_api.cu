@@ -80,6 +80,7 @@ struct orbx_extractor {
   LevelGeom* d_geom = nullptr; ResizeTap* d_taps = nullptr; int* d_umax = nullptr; char4* d_pattern = nullptr;
   uint8_t* d_in = nullptr;
   float* d_uright = nullptr; float* d_depth = nullptr; int* d_sad = nullptr; int* d_nmatch = nullptr;
+  uint4* d_strec = nullptr; int* d_sttab = nullptr; int st_tab_stride = 0;   // K5a scratch (sorted right keypoints, bin starts)
   int slots_valid = 0;
   // optional per-stage timing: a ring of event sets, 5 boundaries per extract pass, 3 per stereo pass
   bool profiling = false;
@@ -351,6 +352,9 @@ orbx_status orbx_extractor_create(const orbx_params* params, int max_w, int max_
   ALLOC(e->d_depth, nb * e->kp_cap);
   ALLOC(e->d_sad, nb * e->kp_cap);
   ALLOC(e->d_nmatch, nb);
+  e->st_tab_stride = e->nlevels * max_h + 2;
+  ALLOC(e->d_strec, nb * e->kp_cap);
+  ALLOC(e->d_sttab, nb * e->st_tab_stride);
 #undef ALLOC
   L.geom = e->d_geom; L.taps = e->d_taps;
   cudaError_t ce = cudaMemcpy(e->d_umax, e->umax, sizeof(e->umax), cudaMemcpyHostToDevice);
@@ -369,7 +373,7 @@ void orbx_extractor_destroy(orbx_extractor* e) {
   DeviceLayout& L = e->L;
   void* ptrs[] = {e->d_geom, e->d_taps, e->d_umax, e->d_pattern, e->d_in, L.pyr, L.celltab, L.poolcnt, L.pool, L.okeys,
                   L.knode, L.lvlkp, L.lvlcnt, L.nkeys, L.kps, L.desc, L.nkp, L.err, e->d_uright, e->d_depth, e->d_sad,
-                  e->d_nmatch};
+                  e->d_nmatch, e->d_strec, e->d_sttab};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (e->ev_ext[0][0])
     for (int i = 0; i < orbx_extractor::kRing; ++i) {
@@ -561,6 +565,7 @@ orbx_status orbx_stereo_match_batch(orbx_extractor* eL, int slotL0, orbx_extract
   a.depth = direct ? depth : eL->d_depth;
   a.nMatches = direct ? n_matches : eL->d_nmatch;
   a.sad = eL->d_sad;
+  a.rec = eR->d_strec; a.tab = eR->d_sttab; a.tab_stride = eR->st_tab_stride;   // indexed by the right handle's kp_cap
   a.cap = direct ? cap : eL->kp_cap;
   cudaEvent_t* ev = (eL->profiling && eL->n_st < orbx_extractor::kRing) ? eL->ev_st[eL->n_st++] : nullptr;
   if (ev) cudaEventRecord(ev[0], st);

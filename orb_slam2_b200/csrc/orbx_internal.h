@@ -91,6 +91,7 @@ struct StereoArgs {
   float bf, maxD;
   float* uRight; float* depth; int* nMatches; int* sad;  // device, [n][cap]
   int cap;
+  uint4* rec; int* tab; int tab_stride;   // K5a output: sorted right-keypoint records [n][R.kp_cap], bin starts [n][tab_stride]
 };
 int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid);
 
