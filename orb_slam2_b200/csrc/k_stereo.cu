@@ -31,12 +31,7 @@ __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const 
   return __popcll(x0) + __popcll(x1) + __popcll(x2) + __popcll(x3);
 }
 
-// c + sum of the absolute differences of the four byte pairs of a and b (VABSDIFF4.U8.ACC)
-__device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t c) {
-  uint32_t d;
-  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-  return d;
-}
+constexpr int kLP = 12, kRP = 24;       // row pitch of the left patch / right strip in shared memory (words per row: 3 / 6)
 
 // K5a: the right keypoints of one pair, counting-sorted by (octave, (int)y) into 16-byte records
 // {x, floor(y-r) | ceil(y+r) << 16, iR, 0} (r = 2 * scale[octave], src/Frame.cc:483-493) plus the table of bin
@@ -98,7 +93,7 @@ __global__ void __launch_bounds__(kRowThreads) k_stereo_rows(StereoArgs a) {
 
 // K5b: one warp per left keypoint, no block-level step.
 __global__ void __launch_bounds__(kStWarps * 32, 6) k_stereo_match(StereoArgs a, int ctas_per_img) {
-  __shared__ __align__(16) uint8_t s_patch[kStWarps * 384];
+  __shared__ __align__(16) uint8_t s_patch[kStWarps * 416];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int img = blockIdx.x / ctas_per_img;
   const int iL = (blockIdx.x - img * ctas_per_img) * kStWarps + warp;
@@ -109,8 +104,8 @@ __global__ void __launch_bounds__(kStWarps * 32, 6) k_stereo_match(StereoArgs a,
   const uint8_t* dR = a.R.desc + (size_t)slotR * a.R.kp_cap * 32;
   const int* T = a.tab + (size_t)img * a.tab_stride;
   const uint4* rec = a.rec + (size_t)img * a.R.kp_cap;
-  uint8_t* lp = s_patch + warp * 384;   // 11x11 left patch   (scalar SAD form only)
-  uint8_t* rp = lp + 128;               // 11x21 right strip
+  uint8_t* lp = s_patch + warp * 416;   // 11x11 left patch, pitch 12
+  uint8_t* rp = lp + 144;               // 11x21 right strip, pitch 24
   do {                                  // one pass; "continue" = this keypoint has no stereo match
     const size_t oi = (size_t)img * a.cap + iL;
     if (lane == 0) { a.uRight[oi] = -1.f; a.depth[oi] = -1.f; a.sad[oi] = -1; }
@@ -161,88 +156,57 @@ __global__ void __launch_bounds__(kStWarps * 32, 6) k_stereo_match(StereoArgs a,
     const int cy = (int)sv, cxl = (int)su, cxr = (int)sr;
     const uint8_t* pl = a.L.pyr + gl.plane_off + (size_t)slotL * gl.plane_stride + (size_t)(kEdge + cy - 5) * gl.pitch + kEdge + cxl - 5;
     const uint8_t* pr = a.R.pyr + gr.plane_off + (size_t)slotR * gr.plane_stride + (size_t)(kEdge + cy - 5) * gr.pitch + kEdge + cxr - 10;
-    // SAD of the centre-subtracted 11x11 patches over the 11 shifts (:578-592).  sum |(L - cl) - (R - cr)| =
-    // sum |L - (R + delta)| with delta = cl - cr.  Packed form: lane = patch row (lanes 0..10); the row's 11 left
-    // bytes and 21 right bytes come straight from the planes as aligned words, the shifted windows are funnel
-    // shifts of those registers, delta is added to the packed right bytes (one 32-bit add per word) and three
-    // VABSDIFF4.ACC give the row's 11 absolute differences.  That is exact as long as R + delta stays within a
-    // byte for every pixel of the strip; the min / max of the strip decide (warp-uniform), and a pair that
-    // fails the test takes the scalar form below.  Either way lane s ends up holding the sum of shift s.
+    // SAD of the centre-subtracted 11x11 patches over the 11 shifts (:578-592), in integers.
+    // Lanes 0..10 fetch one patch row each as aligned words (11 left bytes, 21 right bytes), byte-align them with
+    // funnel shifts and park them in shared memory; then every lane owns 4 of the 121 pixels and evaluates
+    // |(L - cl) - (R - cr)| = |(L - cl + cr) - R| with one VABSDIFF per pixel and shift.  Lane s ends up holding
+    // the sum of shift s.  (A packed-byte VABSDIFF4 form is not exact here: R + cl - cr leaves a byte for most
+    // shifts of a corner patch.)
     int mine = 0x7fffffff;
     {
-      const int prow = min(lane, 10);
-      const uint8_t* al = pl + (size_t)prow * gl.pitch;
-      const uint8_t* ar = pr + (size_t)prow * gr.pitch;
-      const uint32_t* wl = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(al) & ~(uintptr_t)3);
-      const uint32_t* wr = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(ar) & ~(uintptr_t)3);
-      const int shl = (int)(reinterpret_cast<uintptr_t>(al) & 3) * 8, shr = (int)(reinterpret_cast<uintptr_t>(ar) & 3) * 8;
-      const uint32_t L0 = __ldg(wl), L1 = __ldg(wl + 1), L2 = __ldg(wl + 2), L3 = __ldg(wl + 3);
-      uint32_t W[7];
+      __syncwarp();
+      if (lane < 11) {
+        const uint8_t* al = pl + (size_t)lane * gl.pitch;
+        const uint8_t* ar = pr + (size_t)lane * gr.pitch;
+        const uint32_t* wl = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(al) & ~(uintptr_t)3);
+        const uint32_t* wr = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(ar) & ~(uintptr_t)3);
+        const int shl = (int)(reinterpret_cast<uintptr_t>(al) & 3) * 8, shr = (int)(reinterpret_cast<uintptr_t>(ar) & 3) * 8;
+        const uint32_t L0 = __ldg(wl), L1 = __ldg(wl + 1), L2 = __ldg(wl + 2), L3 = __ldg(wl + 3);
+        uint32_t W[7];
 #pragma unroll
-      for (int k = 0; k < 6; ++k) W[k] = __ldg(wr + k);
-      W[6] = 0u;
-      const uint32_t l0 = __funnelshift_r(L0, L1, shl), l1 = __funnelshift_r(L1, L2, shl), l2 = __funnelshift_r(L2, L3, shl) & 0x00ffffffu;
-      uint32_t r[6];                                   // right row bytes 0..20 (r[5] holds byte 20 only)
+        for (int k = 0; k < 6; ++k) W[k] = __ldg(wr + k);
+        W[6] = 0u;
+        uint32_t* lrow = reinterpret_cast<uint32_t*>(lp) + lane * (kLP / 4);
+        uint32_t* rrow = reinterpret_cast<uint32_t*>(rp) + lane * (kRP / 4);
+        lrow[0] = __funnelshift_r(L0, L1, shl); lrow[1] = __funnelshift_r(L1, L2, shl); lrow[2] = __funnelshift_r(L2, L3, shl);
 #pragma unroll
-      for (int k = 0; k < 6; ++k) r[k] = __funnelshift_r(W[k], W[k + 1], shr);
-      const uint32_t r5 = (r[5] & 0xffu) * 0x01010101u;   // the one valid byte, replicated so that min / max ignore the rest
-      // min / max of the 21 bytes of this row as u16 pairs: odd bytes ride in the high byte of each half, even bytes after << 8;
-      // for the minimum the low bytes are forced to 0xff so that only the high bytes decide
-      const uint32_t lo = 0x00ff00ffu;
-      uint32_t mx = __vimax3_u16x2(r[0], r[1], r[2]), mn = __vimin3_u16x2(r[0] | lo, r[1] | lo, r[2] | lo);
-      mx = __vimax3_u16x2(mx, r[3], r[4]); mn = __vimin3_u16x2(mn, r[3] | lo, r[4] | lo);
-      uint32_t mxe = __vimax3_u16x2(r[0] << 8, r[1] << 8, r[2] << 8), mne = __vimin3_u16x2((r[0] << 8) | lo, (r[1] << 8) | lo, (r[2] << 8) | lo);
-      mxe = __vimax3_u16x2(mxe, r[3] << 8, r[4] << 8); mne = __vimin3_u16x2(mne, (r[3] << 8) | lo, (r[4] << 8) | lo);
-      mx = __vimax3_u16x2(mx, mxe, r5); mn = __vimin3_u16x2(mn, mne, r5 | lo);
-      const int maxR = __reduce_max_sync(0xffffffffu, (int)(max(mx & 0xffffu, mx >> 16) >> 8));
-      const int minR = __reduce_min_sync(0xffffffffu, (int)(min(mn & 0xffffu, mn >> 16) >> 8));
-      // centres: cl = left (5, 5); cr(s) = right (5, 5 + s), i.e. bytes 5..15 of row 5
-      const int cl = (int)((__shfl_sync(0xffffffffu, l1, 5) >> 8) & 0xffu);
-      const uint32_t c1 = __shfl_sync(0xffffffffu, r[1], 5), c2 = __shfl_sync(0xffffffffu, r[2], 5), c3 = __shfl_sync(0xffffffffu, r[3], 5);
-      int dlt[11];
-#pragma unroll
-      for (int s = 0; s < 11; ++s) {
-        const int b = 5 + s;
-        const uint32_t cw = b < 8 ? c1 : b < 12 ? c2 : c3;
-        dlt[s] = cl - (int)((cw >> (8 * (b & 3))) & 0xffu);
+        for (int k = 0; k < 6; ++k) rrow[k] = __funnelshift_r(W[k], W[k + 1], shr);
       }
-      int dmin = dlt[0], dmax = dlt[0];
+      __syncwarp();
+      // pixel q of this lane: row 3q + lane/11, column lane%11; lanes 22..24 use their idle fourth slot for the
+      // three pixels (2,10), (5,10), (8,10) that this cut leaves out
+      const int lr = lane >= 22 ? 2 : lane >= 11 ? 1 : 0, lc = lane - 11 * lr;
+      const bool v3 = lr < 2 || lane < 25;
+      const int row3 = lr < 2 ? 9 + lr : 2 + 3 * (lane - 22), col3 = lr < 2 ? lc : 10;
+      const int cl = lp[5 * kLP + 5];
+      int la[4];
+      const uint8_t* rq[4];
 #pragma unroll
-      for (int s = 1; s < 11; s += 2) { dmin = __vimin3_s32(dmin, dlt[s], dlt[s + 1]); dmax = __vimax3_s32(dmax, dlt[s], dlt[s + 1]); }
-      if (minR + dmin >= 0 && maxR + dmax <= 255) {    // warp-uniform
+      for (int q = 0; q < 3; ++q) {
+        la[q] = (int)lp[(3 * q + lr) * kLP + lc] - cl;
+        rq[q] = rp + (3 * q + lr) * kRP + lc + 10;       // right pixel of shift 0 is column +5, centre of the strip at +10: index by inc below
+      }
+      la[3] = v3 ? (int)lp[row3 * kLP + col3] - cl : 0;
+      rq[3] = rp + (v3 ? row3 * kRP + col3 + 10 : 10);
 #pragma unroll
-        for (int s = 0; s < 11; ++s) {
-          const int k = s >> 2, sh = (s & 3) * 8;
-          const uint32_t d4 = (uint32_t)dlt[s] * 0x01010101u;
-          const uint32_t w0 = __funnelshift_r(r[k], r[k + 1], sh) + d4, w1 = __funnelshift_r(r[k + 1], r[k + 2], sh) + d4;
-          const uint32_t w2 = (__funnelshift_r(r[k + 2], r[k + 3], sh) + d4) & 0x00ffffffu;
-          int sum = (int)sad4_acc(l0, w0, sad4_acc(l1, w1, sad4_acc(l2, w2, 0u)));
-          sum = __reduce_add_sync(0xffffffffu, lane < 11 ? sum : 0);
-          if (lane == s) mine = sum;
-        }
-      } else {
-        __syncwarp();
-        for (int idx = lane; idx < 121; idx += 32) { const int dy = idx / 11, dx = idx - dy * 11; lp[idx] = __ldg(pl + (size_t)dy * gl.pitch + dx); }
-        for (int idx = lane; idx < 231; idx += 32) { const int dy = idx / 21, dx = idx - dy * 21; rp[idx] = __ldg(pr + (size_t)dy * gr.pitch + dx); }
-        __syncwarp();
-        int la[4], off[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int idx = lane + 32 * q;
-          const int dy = idx / 11, dx = idx - dy * 11;
-          la[q] = idx < 121 ? (int)lp[idx] - cl : 0;
-          off[q] = idx < 121 ? dy * 21 + dx + 5 : -1;
-        }
-#pragma unroll
-        for (int inc = -5; inc <= 5; ++inc) {
-          const int cr = rp[5 * 21 + 10 + inc];
-          int sum = 0;
-#pragma unroll
-          for (int q = 0; q < 4; ++q)
-            if (off[q] >= 0) sum += abs(la[q] - ((int)rp[off[q] + inc] - cr));
-          sum = __reduce_add_sync(0xffffffffu, sum);
-          if (lane == inc + 5) mine = sum;
-        }
+      for (int inc = -5; inc <= 5; ++inc) {
+        const int cr = rp[5 * kRP + 10 + inc];
+        unsigned sum = __sad(la[0] + cr, (int)rq[0][inc - 5], 0u);
+        sum = __sad(la[1] + cr, (int)rq[1][inc - 5], sum);
+        sum = __sad(la[2] + cr, (int)rq[2][inc - 5], sum);
+        if (v3) sum = __sad(la[3] + cr, (int)rq[3][inc - 5], sum);
+        sum = __reduce_add_sync(0xffffffffu, sum);
+        if (lane == inc + 5) mine = (int)sum;
       }
     }
     // first minimum over the shifts (:587-591): least (sum, shift)

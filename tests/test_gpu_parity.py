@@ -234,12 +234,10 @@ def test_stereo_two_handles_like_the_reference(gx, oracle):
     assert int(nm[0]) == 0
 
 
-def test_stereo_saturated_strips_take_the_scalar_sad(gx, oracle):
-    """K5 evaluates the centre-subtracted SAD on packed bytes when right pixel + (cl - cr) stays within a byte
-    over the whole 11x21 strip and falls back to a scalar form otherwise.  A right image that is 40 grey levels
-    darker (or 35 brighter) with 1 % salt (255) and pepper (0) pixels puts a saturated pixel into most strips,
-    so most accepted matches go through the scalar form and the rest through the packed one: both must equal
-    the oracle bit for bit."""
+def test_stereo_saturated_and_offset_right_images(gx, oracle):
+    """The SAD of K5 is centre-subtracted, so right pixel + (cl - cr) spans 9 bits.  A right image that is 40 grey
+    levels darker (or 35 brighter) with 1 % salt (255) and pepper (0) pixels drives those sums to their extremes;
+    uRight / depth must still equal the oracle bit for bit."""
     cfg = synth.EUROC
     w, h, nf, bf, fx = cfg["w"], cfg["h"], cfg["nfeatures"], cfg["bf"], cfg["fx"]
     rng = np.random.default_rng(5)
