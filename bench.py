@@ -413,18 +413,19 @@ def main():
     sets = make_inputs(rank, B)
     host = [torch.from_numpy(s).pin_memory() for s in sets]
     dev = [t.cuda(non_blocking=True) for t in host]
-    G = [gx.ORBextractor(*PARAMS, max_w=w, max_h=h, max_batch=2 * B, device=local) for _ in range(2)]
+    NPIPE = max(2, int(os.environ.get("ORBX_BENCH_PIPE", "3")))   # handles / streams / pinned result sets in flight in the end-to-end leg
+    G = [gx.ORBextractor(*PARAMS, max_w=w, max_h=h, max_batch=2 * B, device=local) for _ in range(NPIPE)]
     cap = G[0].kp_cap
     d_ur = torch.empty((B, cap), dtype=torch.float32, device="cuda"); d_dp = torch.empty_like(d_ur)
     d_nm = torch.empty(B, dtype=torch.int32, device="cuda")
-    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    streams = [torch.cuda.Stream() for _ in range(NPIPE)]
     # pinned result buffers for the end-to-end leg, one set per pipeline stage
     h_out = [dict(kps=torch.empty((2 * B, cap, 28), dtype=torch.uint8).pin_memory(),
                   desc=torch.empty((2 * B, cap, 32), dtype=torch.uint8).pin_memory(),
                   cnt=torch.empty(2 * B, dtype=torch.int32).pin_memory(),
                   ur=torch.empty((B, cap), dtype=torch.float32).pin_memory(),
                   dp=torch.empty((B, cap), dtype=torch.float32).pin_memory(),
-                  nm=torch.empty(B, dtype=torch.int32).pin_memory()) for _ in range(2)]
+                  nm=torch.empty(B, dtype=torch.int32).pin_memory()) for _ in range(NPIPE)]
     torch.cuda.synchronize()
 
     def barrier():
@@ -468,19 +469,23 @@ def main():
     checksum = int(np.bitwise_xor.reduce(np.frombuffer(res[0][1].tobytes(), np.uint64))) if len(res[0][1]) else 0
 
     # ---- end to end through the C ABI with host buffers, two handles/streams ping-pong ----
-    for i in range(args.warmup):
-        step_e2e(i, G[i & 1], streams[i & 1], h_out[i & 1])
+    for i in range(max(args.warmup, NPIPE)):
+        step_e2e(i, G[i % NPIPE], streams[i % NPIPE], h_out[i % NPIPE])
     torch.cuda.synchronize(); barrier()
     ee0 = torch.cuda.Event(enable_timing=True); ee1 = torch.cuda.Event(enable_timing=True)
     ee0.record(streams[0])
+    for k in range(1, NPIPE):
+        streams[k].wait_stream(streams[0])               # nothing of the timed steps starts before ee0
     for i in range(args.steps):
-        step_e2e(i, G[i & 1], streams[i & 1], h_out[i & 1])
-    streams[0].wait_stream(streams[1])
+        step_e2e(i, G[i % NPIPE], streams[i % NPIPE], h_out[i % NPIPE])
+    for k in range(1, NPIPE):
+        streams[0].wait_stream(streams[k])
     ee1.record(streams[0])
     torch.cuda.synchronize(); barrier()
     ms_e2e = ee0.elapsed_time(ee1)
     clocks = sampler.stop()
-    assert int(h_out[(args.steps - 1) & 1]["cnt"].sum()) > 0 and int(h_out[(args.steps - 1) & 1]["nm"].sum()) > 0
+    last = h_out[(args.steps - 1) % NPIPE]
+    assert int(last["cnt"].sum()) > 0 and int(last["nm"].sum()) > 0
 
     # ---- max over ranks, totals over ranks ----
     from orb_slam2_b200 import sharding
@@ -509,7 +514,7 @@ def main():
                        "l2": f"inputs rotate over {NSETS} sets of {2 * B * w * h / 1e6:.0f} MB (> {L2_MB} MB L2 in total); per-step intermediates {2 * B * 1.8:.0f} MB",
                        "bf": bf, "fx": fx},
             "e2e": {"value": e2e_val, "unit": "stereo frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "pipeline": "2 handles x 2 streams, pinned host buffers", "cpu_affinity": affinity},
+                    "ms_per_step": ms_e2e / args.steps, "pipeline": f"{NPIPE} handles x {NPIPE} streams, pinned host buffers", "cpu_affinity": affinity},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
