@@ -214,16 +214,25 @@ __global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int firs
       if (nd < C && cnt[cur][nd] > 1) atomicAdd(&cc[4 * nd + quadrant(okeys[k], box[cur][nd])], 1);
     }
     __syncthreads();
-    // rank by (size desc, list position asc) == the reference's sort() walked from the back
+    // rank by (size desc, list position asc) == the reference's sort() walked from the back.
+    // One packed key per open node, size << 16 | (0xFFFF - position) (0 for the others; a level holds far fewer
+    // than 65536 keys and nodes): rank = number of larger keys, read two at a time
+    unsigned* rkey = reinterpret_cast<unsigned*>(a5);            // a5 is free until the survivor scan below
+    for (int i = tid; i < ((C + 1) & ~1); i += kOctThreads) {   // padded to an even count
+      const int ci = i < C ? cnt[cur][i] : 0;
+      rkey[i] = ci > 1 ? ((unsigned)ci << 16) | (unsigned)(0xFFFF - i) : 0u;
+    }
+    __syncthreads();
     int my_m = 0;
     for (int i = tid; i < C; i += kOctThreads) {
       const int ci = cnt[cur][i];
       int rank = -1;
       if (ci > 1) {
         rank = 0;
-        for (int j = 0; j < C; ++j) {
-          const int cj = cnt[cur][j];
-          rank += (cj > 1) && (cj > ci || (cj == ci && j < i));
+        const unsigned mk = rkey[i];
+        for (int j = 0; j < C; j += 2) {
+          const uint2 kj = *reinterpret_cast<const uint2*>(rkey + j);
+          rank += (kj.x > mk) + (kj.y > mk);
         }
         int nch = 0;
         for (int q = 0; q < 4; ++q) nch += cc[4 * i + q] > 0;
