@@ -181,7 +181,10 @@ __global__ void __launch_bounds__(kDescWarps * 32, 6) k_describe(DeviceLayout L,
 #pragma unroll
     for (int v = 1; v <= kHalfPatch; ++v) {
       const int a = colp[v * kTileP], b = colp[-v * kTileP];   // always inside the tile: load first, then decide
-      if (v <= vlim) { s_all += a + b; s_v += v * (a - b); }
+      // if (v <= vlim) { s_all += a + b; s_v += v * (a - b); } with the predication spelled out: left to itself
+      // the compiler turns these 15 rows into branches or predicates depending on unrelated code (7 % of the kernel)
+      asm("{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %2, %3;\n\t@p add.s32 %0, %0, %4;\n\t@p mad.lo.s32 %1, %5, %3, %1;\n\t}"
+          : "+r"(s_all), "+r"(s_v) : "r"(vlim), "r"(v), "r"(a + b), "r"(a - b));
     }
     m10 = u * s_all;
     m01 = s_v;
@@ -229,8 +232,6 @@ __global__ void __launch_bounds__(kDescWarps * 32, 6) k_describe(DeviceLayout L,
   // Vertical pass: one task = one column and a run of row pairs, walking down two output rows per
   // step with a 4-word sliding window and 8 dp2a (u16 x u8); the rounding constant rides in the
   // accumulator and the two result bytes leave as one 16-bit store into the transposed patch.
-  // 37 columns x rows 0..37: two sweeps of 10-step tasks (columns x {rows 0-19, rows 18-37}), and the
-  // last 10 half-columns cut in three 4-step pieces so that the third sweep keeps 30 lanes busy.
   {
     const unsigned E0 = pk4(18, 34, 0, 0), E1 = pk4(48, 56, 0, 0), E2 = pk4(48, 34, 0, 0), E3 = pk4(18, 0, 0, 0);
     const unsigned F0 = pk4(0, 18, 0, 0), F1 = pk4(34, 48, 0, 0), F2 = pk4(56, 48, 0, 0), F3 = pk4(34, 18, 0, 0);
@@ -247,14 +248,15 @@ __global__ void __launch_bounds__(kDescWarps * 32, 6) k_describe(DeviceLayout L,
         W0 = W1; W1 = W2; W2 = W3;
       }
     };
-    vrun(phase + lane, 0, IntC<10>{});
+    // Sweeps 1 and 2: lane = absolute column 0..31 (the pitches 23 and 11 words are odd, so 32 consecutive
+    // columns at one row offset never share a bank; columns below `phase` are computed for nothing, which is
+    // cheaper than the conflicts a phase-relative cut runs into at the skewed columns), rows 0-19 and 18-37.
+    // Sweep 3: the 8 skewed columns 32..39 in four 5-step pieces (rows 0-9, 10-19, 18-27, 28-37).
+    vrun(lane, 0, IntC<10>{});
+    vrun(lane, 18, IntC<10>{});
     {
-      const int t = 32 + lane, half = t >= 37;
-      vrun(phase + (half ? t - 37 : t), half ? 18 : 0, IntC<10>{});
-    }
-    if (lane < 30) {
-      const int q = lane / 3, part = lane - 3 * q;
-      vrun(phase + 27 + q, 18 + 6 * part, IntC<4>{});
+      const int piece = lane & 3;
+      vrun(32 + (lane >> 2), piece == 0 ? 0 : piece == 1 ? 10 : piece == 2 ? 18 : 28, IntC<5>{});
     }
   }
   __syncwarp();
