@@ -22,13 +22,13 @@ namespace orbx {
 constexpr int kDescWarps = 4;
 constexpr int kKpPerWarp = 4;             // keypoints per warp: the next tile is in flight while this one is processed
 constexpr int kTileR = kDescTileH, kTileP = kDescTileW;   // raw tile rows / pitch (TMA box); the keypoint sits at (21, phase16+21)
-constexpr int kHtC = 40, kHtP = 46;       // horizontal pass, TRANSPOSED: [column][row] uint16, 46-entry pitch (bank-conflict free reads)
+constexpr int kHtC = 40, kHtP = 50;       // horizontal pass, TRANSPOSED: [column][row] uint16, 50-entry pitch = 25 words: odd, so 32 columns never share a bank, and (unlike 23) the four row pieces of the skewed columns collide only two-way
 constexpr int kHtSkew = 4;                // columns 32+ sit two words further: the 10 four-column groups of a store sweep then hit 10 distinct banks
 constexpr int kBlC = 40, kBlP = 44;       // blurred patch, TRANSPOSED: [column][row] bytes, rows 0..37 (row 37 is scratch), centre (18,18)
 // per-warp shared memory: raw tile | Ht | blurred | mbarrier.  The raw tile is dead once the moments and
 // the horizontal pass have read it, so the NEXT keypoint's tile is requested right then and lands while
 // the vertical pass and the descriptor of this one run.  
-constexpr int kOffHt = 2816, kOffBl = 6528, kOffBar = 8288, kWarpSmem = 8320;
+constexpr int kOffHt = 2816, kOffBl = 6832, kOffBar = 8592, kWarpSmem = 8704;
 static_assert(kTileR * kTileP <= kOffHt && kOffHt + (kHtC * kHtP + kHtSkew) * 2 <= kOffBl && kOffBl + kBlC * kBlP <= kOffBar, "smem carve-up");
 static_assert(kWarpSmem % 128 == 0 && kOffBar % 8 == 0, "TMA destinations must be 128-byte aligned");
 
