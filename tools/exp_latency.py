@@ -1,6 +1,6 @@
 """Single-frame latency of the drop-in calls (host image in, host keypoints/descriptors out)."""
 import sys, time, numpy as np
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, '.')
 import orb_slam2_b200 as gx
 from orb_slam2_b200 import synth
 cfg = synth.KITTI; w, h = cfg['w'], cfg['h']
