@@ -20,7 +20,10 @@
 namespace orbx {
 
 constexpr int kDescWarps = 2;             // 2-warp CTAs: 12 per SM; measured 0.7 % faster than 6 x 4 warps (finer tail)
-constexpr int kKpPerWarp = 4;             // keypoints per warp: the next tile is in flight while this one is processed
+// keypoints per warp (launch argument): the next tile is in flight while this one is processed.  16 for large batches
+// (fewer warp prologues: 1.426 -> 1.386 ms per 256 KITTI pairs; 4 / 8 / 12 / 16 / 32 were measured), 4 when the whole
+// launch is small, so that a single image still spreads over the SMs
+constexpr int kKpPerWarpBatch = 16, kKpPerWarpSmall = 4;
 constexpr int kTileR = kDescTileH, kTileP = kDescTileW;   // raw tile rows / pitch (TMA box); the keypoint sits at (21, phase16+21)
 constexpr int kHtC = 40, kHtP = 50;       // horizontal pass, TRANSPOSED: [column][row] uint16, 50-entry pitch = 25 words: odd, so 32 columns never share a bank, and (unlike 23) the four row pieces of the skewed columns collide only two-way
 constexpr int kHtSkew = 4;                // columns 32+ sit two words further: the 10 four-column groups of a store sweep then hit 10 distinct banks
@@ -116,7 +119,7 @@ __device__ __forceinline__ KpRef locate_kp(const DeviceLayout& L, int slot, int 
 }
 
 __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
-                                                              int n_img, int ctas_per_img, const int* __restrict__ umax,
+                                                              int n_img, int ctas_per_img, int kp_per_warp, const int* __restrict__ umax,
                                                               const char4* __restrict__ pattern) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -128,7 +131,7 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe(DeviceLayout L
   const int img = blockIdx.x / ctas_per_img;
   if (img >= n_img) return;
   const int slot = first_slot + img;
-  const int j0 = ((blockIdx.x - img * ctas_per_img) * kDescWarps + warp) * kKpPerWarp;   // first output keypoint of this warp
+  const int j0 = ((blockIdx.x - img * ctas_per_img) * kDescWarps + warp) * kp_per_warp;   // first output keypoint of this warp
 
   const int myc = lane < L.nlevels ? L.lvlcnt[slot * kMaxLevels + lane] : 0;
   int incl = myc;
@@ -140,7 +143,7 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe(DeviceLayout L
   const int total = min(__shfl_sync(0xffffffffu, incl, 31), L.kp_cap);
   if (j0 == 0 && lane == 0) L.nkp[slot] = total;
   if (j0 >= total) return;
-  const int nk = min(kKpPerWarp, total - j0);
+  const int nk = min(kp_per_warp, total - j0);
 
   if (lane == 0) { mbar_init(bar, 1); fence_barrier_init(); }
   __syncwarp();
@@ -298,10 +301,11 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe(DeviceLayout L
 }
 
 int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st) {
-  const int per_cta = kDescWarps * kKpPerWarp;
+  const int kp_per_warp = (long long)n * L.kp_cap >= 148LL * 24 * kKpPerWarpBatch ? kKpPerWarpBatch : kKpPerWarpSmall;
+  const int per_cta = kDescWarps * kp_per_warp;
   const int ctas_per_img = (L.kp_cap + per_cta - 1) / per_cta;
   const size_t smem = (size_t)kDescWarps * kWarpSmem;
-  k_describe<<<n * ctas_per_img, kDescWarps * 32, smem, st>>>(L, maps, first_slot, n, ctas_per_img, d_umax, d_pattern);
+  k_describe<<<n * ctas_per_img, kDescWarps * 32, smem, st>>>(L, maps, first_slot, n, ctas_per_img, kp_per_warp, d_umax, d_pattern);
   return 1;
 }
 
