@@ -234,6 +234,25 @@ def test_stereo_two_handles_like_the_reference(gx, oracle):
     assert int(nm[0]) == 0
 
 
+def test_stereo_handles_with_different_feature_budgets(gx, oracle):
+    """Left and right extractor with different nFeatures (different keypoint capacity per slot): the sorted
+    right-keypoint records of K5 live in the right handle's scratch and are indexed by its capacity."""
+    cfg = synth.EUROC
+    w, h = cfg["w"], cfg["h"]
+    L, R, _ = synth.stereo_pair(52, w, h)
+    for nl, nr in [(1200, 700), (600, 1500)]:
+        GL, GR = _ext(gx, w, h, nl), _ext(gx, w, h, nr)
+        kl, dl = GL(L); kr, dr = GR(R)
+        ur, dp, nm = gx.ComputeStereoMatches(GL, GR, cfg["bf"], cfg["fx"])
+        EL, ER = oracle.Extractor(nl), oracle.Extractor(nr)
+        okl, odl = EL.extract(L); okr, odr = ER.extract(R)
+        assert kl.tobytes() == okl.tobytes() and kr.tobytes() == okr.tobytes()
+        rur, rdp, _, rm = oracle.stereo(EL, ER, okl, odl, okr, odr, cfg["bf"], cfg["fx"])
+        assert int(nm[0]) == rm and rm > 50
+        assert np.array_equal(ur[0, :len(kl)].view(np.uint32), rur.view(np.uint32))
+        assert np.array_equal(dp[0, :len(kl)].view(np.uint32), rdp.view(np.uint32))
+
+
 def test_stereo_saturated_and_offset_right_images(gx, oracle):
     """The SAD of K5 is centre-subtracted, so right pixel + (cl - cr) spans 9 bits.  A right image that is 40 grey
     levels darker (or 35 brighter) with 1 % salt (255) and pepper (0) pixels drives those sums to their extremes;
