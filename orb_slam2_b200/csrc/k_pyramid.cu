@@ -109,46 +109,38 @@ __global__ void __launch_bounds__(256) k_resize_level(DeviceLayout L, int level,
 //   2. horizontal pass once per SOURCE row (1.2x fewer than two per output row), (h >> 4) as uint16
 //   3. vertical pass, 4 pixels per thread, (b*H) >> 16 as one multiply-high with the +2 rounding
 //      riding in the accumulator; one aligned 32-bit store per thread, a warp writes 128 B
-constexpr int kRtTH = 32, kRtTW = 128, kRtSH = kResizeBoxH, kRtSWP = kResizeBoxW;
+constexpr int kRtTH = kResizeTileH, kRtTW = kResizeTileW, kRtSH = kResizeBoxH, kRtSWP = kResizeBoxW;
 
 __global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __grid_constant__ TmaMaps maps, int level, int first_slot) {
   __shared__ __align__(128) uint8_t s_src[kRtSH * kRtSWP];
   __shared__ __align__(16) uint32_t s_h[kRtSH * kRtTW];
   __shared__ int4 s_ty[kRtTH];          // {row offset into s_h, a0 << 16, a1 << 16, -}
-  __shared__ int s_lim[4];   // sx_lo, sx_hi, sy_lo, sy_hi (inclusive, source ROI coordinates)
   __shared__ __align__(8) uint64_t s_bar;
   const LevelGeom& g = L.geom[level];
   const int t = threadIdx.x;
   const int txi = blockIdx.x, tyi = blockIdx.y, img = blockIdx.z;   // grid = (tiles_x, tiles_y, images)
   const int bx0 = txi * kRtTW, by0 = tyi * kRtTH;
   const int tw = min(kRtTW, g.pitch - bx0), th = min(kRtTH, g.rows - by0);
-  if (t == 0) {
-    s_lim[0] = 1 << 30; s_lim[1] = -1; s_lim[2] = 1 << 30; s_lim[3] = -1;
-    mbar_init(&s_bar, 1);
-    fence_barrier_init();
-  }
-  __syncthreads();
-  const int c = t & (kRtTW - 1);
-  ResizeTap tx; tx.ofs = 0; tx.a0 = 0; tx.a1 = 0;
-  if (c < tw) {
-    tx = L.taps[g.xtab_off + bx0 + c];
-    if (t < kRtTW) { atomicMin(&s_lim[0], tx.ofs); atomicMax(&s_lim[1], tx.ofs + 1); }
-  }
-  ResizeTap tyr; tyr.ofs = 0; tyr.a0 = 0; tyr.a1 = 0;
-  if (t < th) {
-    tyr = L.taps[g.ytab_off + by0 + t];
-    atomicMin(&s_lim[2], tyr.ofs); atomicMax(&s_lim[3], tyr.ofs + 1);
-  }
-  __syncthreads();
-  const int sx_lo = s_lim[0], sy_lo = s_lim[2];
-  const int SH = s_lim[3] - sy_lo + 1;
+  // source footprint of this tile from the host-made tile table: first source column / row, row count
+  const int sx_lo = L.taps[g.xtile_off + txi].ofs;
+  const ResizeTap ytile = L.taps[g.ytile_off + tyi];
+  const int sy_lo = ytile.ofs, SH = ytile.a0;
   const int phase = (kEdge + sx_lo) & 15;            // smem column of source column sx_lo
   if (t == 0) {
+    mbar_init(&s_bar, 1);
+    fence_barrier_init();
     mbar_expect_tx(&s_bar, kRtSH * kRtSWP);
     tma_load_3d(s_src, &maps.m[level - 1], (kEdge + sx_lo) & ~15, kEdge + sy_lo, first_slot + img, &s_bar);
   }
+  const int c = t & (kRtTW - 1);
+  ResizeTap tx; tx.ofs = 0; tx.a0 = 0; tx.a1 = 0;
+  if (c < tw) tx = L.taps[g.xtab_off + bx0 + c];
   // mulhi(b << 16, H) == (b * H) >> 16: the vertical weights are kept pre-shifted
-  if (t < th) s_ty[t] = make_int4((tyr.ofs - sy_lo) * kRtTW, tyr.a0 << 16, tyr.a1 << 16, 0);
+  if (t < th) {
+    const ResizeTap tyr = L.taps[g.ytab_off + by0 + t];
+    s_ty[t] = make_int4((tyr.ofs - sy_lo) * kRtTW, tyr.a0 << 16, tyr.a1 << 16, 0);
+  }
+  __syncthreads();                                   // barrier initialised, s_ty visible
   mbar_wait(&s_bar, 0);
   if (c < tw) {
     const int a0 = tx.a0, a1 = tx.a1;

@@ -173,6 +173,28 @@ orbx_status geometry(const orbx_extractor* e, int w, int h, int nslots, LevelGeo
         for (int by = 0; by < (int)align_up(q.rows, 4); ++by)
           (*taps)[q.ytab_off + by] = by < q.rows ? ty[reflect101(by - kEdge, q.h)] : pady;
       }
+      // source footprint of every output tile of the tiled kernel (it used to be found by shared-memory
+      // atomics in every CTA): the TMA box can be requested before the CTA has read a single tap
+      const int tiles_x = (q.pitch + kResizeTileW - 1) / kResizeTileW, tiles_y = (q.rows + kResizeTileH - 1) / kResizeTileH;
+      q.xtile_off = t->taps; q.ytile_off = t->taps + tiles_x;
+      t->taps += (int)align_up(tiles_x + tiles_y, 4);
+      if (taps) {
+        taps->resize(t->taps);
+        for (int i = 0; i < tiles_x; ++i) {
+          int lo = 1 << 30;
+          for (int c = i * kResizeTileW; c < std::min((i + 1) * kResizeTileW, q.pitch); ++c) lo = std::min(lo, (*taps)[q.xtab_off + c].ofs);
+          ResizeTap e; e.ofs = lo; e.a0 = 0; e.a1 = 0;
+          (*taps)[q.xtile_off + i] = e;
+        }
+        for (int i = 0; i < tiles_y; ++i) {
+          int lo = 1 << 30, hi = -1;
+          for (int r = i * kResizeTileH; r < std::min((i + 1) * kResizeTileH, q.rows); ++r) {
+            lo = std::min(lo, (*taps)[q.ytab_off + r].ofs); hi = std::max(hi, (*taps)[q.ytab_off + r].ofs + 1);
+          }
+          ResizeTap e; e.ofs = lo; e.a0 = (short)(hi - lo + 1); e.a1 = 0;
+          (*taps)[q.ytile_off + i] = e;
+        }
+      }
     }
     // FAST cells
     q.maxBX = q.w - kEdge + 3; q.maxBY = q.h - kEdge + 3;

@@ -32,6 +32,7 @@ struct LevelGeom {
   size_t plane_off;      // byte offset of slot 0's plane of this level inside the pyramid arena
   size_t plane_stride;   // bytes between consecutive slots' planes of this level
   int xtab_off, ytab_off;  // offsets (in ResizeTap) of this level's resize tables
+  int xtile_off, ytile_off;  // per 128-column / 32-row output tile of the tiled resize: first source column {ofs}, first source row and row count {ofs, a0}
   // FAST cell grid (src/ORBextractor.cc:773-806)
   int maxBX, maxBY, nCols, nRows, wCell, hCell;
   int cell_base;         // index of this level's first cell in the per-slot cell table
@@ -73,6 +74,7 @@ __host__ __device__ inline int reflect101(int i, int n) {
 
 // one TMA tensor map per pyramid level (passed to kernels as a __grid_constant__ parameter)
 struct TmaMaps { CUtensorMap m[kMaxLevels]; };
+constexpr int kResizeTileW = 128, kResizeTileH = 32;   // output tile of k_resize_tiled (bordered pixels)
 constexpr int kResizeBoxW = 192, kResizeBoxH = 48;  // K1 tiled resize: source footprint box
 constexpr int kDescTileW = 64, kDescTileH = 43;   // K4 tile box: TMA needs a 16-byte aligned start, so 43+15 columns -> 64
 
