@@ -95,8 +95,11 @@ __device__ __forceinline__ int arc_score(const uint8_t* c, const int wp) {
 // maxima / emission stages.
 constexpr int kCellsPerWarp = 4;
 
+// the fields of LevelGeom this kernel reads, per level, as a kernel parameter (constant bank instead of global loads)
+struct FastGeom { int wCell[kMaxLevels], hCell[kMaxLevels], maxBX[kMaxLevels], maxBY[kMaxLevels], nCols[kMaxLevels], cell_base[kMaxLevels], cand_off[kMaxLevels], cand_cap[kMaxLevels]; };
+
 template <int WP>
-__global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, int first_slot,
+__global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, const __grid_constant__ FastGeom G, int first_slot,
                                                                 int n, int win_rows, int iw_max) {
   constexpr int SP = WP - 16;                 // S-map pitch: 48 (cells up to 36 tested columns) or 80
   extern __shared__ __align__(128) uint8_t smem[];
@@ -118,10 +121,10 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
 
   struct Cell { int slot, c, level, col, row, x0, y0, ww, hh; bool skip; };
   auto finish = [&](Cell& k) {                // window of cell (col, row) of its level
-    const LevelGeom& g = L.geom[k.level];
-    k.x0 = kFastBorder + k.col * g.wCell; k.y0 = kFastBorder + k.row * g.hCell;
-    k.ww = min(k.x0 + g.wCell + 6, g.maxBX) - k.x0; k.hh = min(k.y0 + g.hCell + 6, g.maxBY) - k.y0;
-    k.skip = k.y0 >= g.maxBY - 3 || k.x0 >= g.maxBX - 6 || k.ww < 7 || k.hh < 7;   // src/ORBextractor.cc:794,802
+    const int l = k.level, wCell = G.wCell[l], hCell = G.hCell[l], maxBX = G.maxBX[l], maxBY = G.maxBY[l];
+    k.x0 = kFastBorder + k.col * wCell; k.y0 = kFastBorder + k.row * hCell;
+    k.ww = min(k.x0 + wCell + 6, maxBX) - k.x0; k.hh = min(k.y0 + hCell + 6, maxBY) - k.y0;
+    k.skip = k.y0 >= maxBY - 3 || k.x0 >= maxBX - 6 || k.ww < 7 || k.hh < 7;   // src/ORBextractor.cc:794,802
   };
   auto locate = [&](long long gcell) {
     Cell k;
@@ -130,10 +133,9 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
     k.slot = first_slot + img;
     k.level = 0;
     for (int l = 1; l < L.nlevels; ++l)
-      if (k.c >= L.geom[l].cell_base) k.level = l;
-    const LevelGeom& g = L.geom[k.level];
-    const int ci = k.c - g.cell_base;
-    k.row = ci / g.nCols; k.col = ci - k.row * g.nCols;
+      if (k.c >= G.cell_base[l]) k.level = l;
+    const int ci = k.c - G.cell_base[k.level], nCols = G.nCols[k.level];
+    k.row = ci / nCols; k.col = ci - k.row * nCols;
     finish(k);
     return k;
   };
@@ -141,11 +143,11 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
     Cell k = p;
     ++k.c; ++k.col;
     if (k.c == L.cells_per_slot) { k.c = 0; ++k.slot; k.level = 0; k.col = 0; k.row = 0; }
-    else if (k.col == L.geom[k.level].nCols) {
+    else if (k.col == G.nCols[k.level]) {
       k.col = 0; ++k.row;
-      if (k.level + 1 < L.nlevels && k.c >= L.geom[k.level + 1].cell_base) {
+      if (k.level + 1 < L.nlevels && k.c >= G.cell_base[k.level + 1]) {
         k.row = 0;
-        do ++k.level; while (k.level + 1 < L.nlevels && k.c >= L.geom[k.level + 1].cell_base);
+        do ++k.level; while (k.level + 1 < L.nlevels && k.c >= G.cell_base[k.level + 1]);
       }
     }
     finish(k);
@@ -165,7 +167,6 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
   for (int kc = 0; kc < ncell; ++kc) {
     const Cell cur = nxt;
     if (kc + 1 < ncell) nxt = advance(cur);
-    const LevelGeom& g = L.geom[cur.level];
     uint2* cell_out = L.celltab + (size_t)cur.slot * L.cells_per_slot + cur.c;
     if (cur.skip) {
       if (lane == 0) *cell_out = make_uint2(0u, 0u);
@@ -273,7 +274,8 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
       base = __shfl_sync(0xffffffffu, base, 0);
       // emit in pixel row-major order: lane r owns tested rows r and r+32; when iniTh found corners only
       // those are emitted (second mask set)
-      uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
+      uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + G.cand_off[level];
+      const int cand_cap = G.cand_cap[level];
       const uint32_t* km = rows + (use_ini ? (m_words >> 1) : 0);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
@@ -294,7 +296,7 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
           const int xx = __ffsll((long long)m) - 1;
           m &= m - 1;
           const int resp = (int)srow[xx] - 1;
-          if (pos < g.cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
+          if (pos < cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
           ++pos;
         }
       }
@@ -304,7 +306,7 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
 }
 
 template <int WP>
-static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
+static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, const FastGeom& G, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
   constexpr int SP = WP - 16;
   const int iw_max = win_w - 6;
   const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + ((2 * (win_h - 6) * iw_max + 7) & ~7) + 16 * (win_h - 6) + 16 + 127) & ~(size_t)127;
@@ -312,15 +314,20 @@ static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, int first_
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const long long cells = (long long)n * L.cells_per_slot;
   const long long per_cta = (long long)kFastWarps * kCellsPerWarp;
-  k_fast_cells<WP><<<(unsigned)((cells + per_cta - 1) / per_cta), kFastWarps * 32, smem, st>>>(L, maps, first_slot, n, win_h, iw_max);
+  k_fast_cells<WP><<<(unsigned)((cells + per_cta - 1) / per_cta), kFastWarps * 32, smem, st>>>(L, maps, G, first_slot, n, win_h, iw_max);
 }
 
 int fast_window_pitch(int win_w) { return win_w + 15 <= 64 ? 64 : 96; }
 
-int launch_fast(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
+int launch_fast(const DeviceLayout& L, const LevelGeom* hg, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
+  FastGeom G{};
+  for (int l = 0; l < L.nlevels; ++l) {
+    G.wCell[l] = hg[l].wCell; G.hCell[l] = hg[l].hCell; G.maxBX[l] = hg[l].maxBX; G.maxBY[l] = hg[l].maxBY;
+    G.nCols[l] = hg[l].nCols; G.cell_base[l] = hg[l].cell_base; G.cand_off[l] = hg[l].cand_off; G.cand_cap[l] = hg[l].cand_cap;
+  }
   // the TMA box starts at the 16-byte boundary below the window: phase (<= 15) + width must fit the pitch
-  if (fast_window_pitch(win_w) == 64) launch_fast_t<64>(L, maps, first_slot, n, win_w, win_h, st);
-  else launch_fast_t<96>(L, maps, first_slot, n, win_w, win_h, st);
+  if (fast_window_pitch(win_w) == 64) launch_fast_t<64>(L, maps, G, first_slot, n, win_w, win_h, st);
+  else launch_fast_t<96>(L, maps, G, first_slot, n, win_w, win_h, st);
   return 1;
 }
 

@@ -111,13 +111,12 @@ __global__ void __launch_bounds__(256) k_resize_level(DeviceLayout L, int level,
 //      riding in the accumulator; one aligned 32-bit store per thread, a warp writes 128 B
 constexpr int kRtTH = kResizeTileH, kRtTW = kResizeTileW, kRtSH = kResizeBoxH, kRtSWP = kResizeBoxW;
 
-__global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __grid_constant__ TmaMaps maps, int level, int first_slot) {
+__global__ void __launch_bounds__(256) k_resize_tiled(DeviceLayout L, const __grid_constant__ TmaMaps maps, const __grid_constant__ LevelGeom g, int level, int first_slot) {
   __shared__ __align__(128) uint8_t s_src[kRtSH * kRtSWP];
   __shared__ __align__(16) uint32_t s_h[kRtSH * kRtTW];
   __shared__ int4 s_ty[kRtTH];          // {row offset into s_h, a0 << 16, a1 << 16, -}
   __shared__ __align__(8) uint64_t s_bar;
-  const LevelGeom& g = L.geom[level];
-  const int t = threadIdx.x;
+  const int t = threadIdx.x;                         // g: this level's geometry as a kernel parameter (no global load ahead of the TMA request)
   const int txi = blockIdx.x, tyi = blockIdx.y, img = blockIdx.z;   // grid = (tiles_x, tiles_y, images)
   const int bx0 = txi * kRtTW, by0 = tyi * kRtTH;
   const int tw = min(kRtTW, g.pitch - bx0), th = min(kRtTH, g.rows - by0);
@@ -205,7 +204,7 @@ int launch_pyramid(const DeviceLayout& L, const LevelGeom* hg, const uint8_t* sr
   for (int l = 1; l < L.nlevels; ++l) {
     if (tiled_mask & (1u << l)) {
       const int tiles_x = (hg[l].pitch + kRtTW - 1) / kRtTW, tiles_y = (hg[l].rows + kRtTH - 1) / kRtTH;
-      k_resize_tiled<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)n), 256, 0, st>>>(L, *resize_maps, l, first_slot);
+      k_resize_tiled<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)n), 256, 0, st>>>(L, *resize_maps, hg[l], l, first_slot);
     } else {
       long long total = (long long)(hg[l].pitch >> 2) * hg[l].rows * n;
       k_resize_level<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, l, first_slot, n);

@@ -461,7 +461,7 @@ orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, in
   if (ev) cudaEventRecord(ev[0], st);
   launches += launch_pyramid(e->L, e->hg, src, src_pitch, src_istride, first_slot, n, e->tiled_mask, &e->resize_maps, st);
   if (ev) cudaEventRecord(ev[1], st);
-  launches += launch_fast(e->L, e->fast_maps, first_slot, n, e->cur.win_w, e->cur.win_h, st);
+  launches += launch_fast(e->L, e->hg, e->fast_maps, first_slot, n, e->cur.win_w, e->cur.win_h, st);
   if (ev) cudaEventRecord(ev[2], st);
   launches += launch_octree(e->L, first_slot, n, e->cur.node_cap, st);
   if (ev) cudaEventRecord(ev[3], st);

@@ -82,7 +82,7 @@ constexpr int kDescTileW = 64, kDescTileH = 43;   // K4 tile box: TMA needs a 16
 int launch_pyramid(const DeviceLayout& L, const LevelGeom* hgeom, const uint8_t* src, int src_pitch,
                    size_t src_img_stride, int first_slot, int n, unsigned tiled_mask, const TmaMaps* resize_maps, cudaStream_t st);
 bool resize_tiled_fits(const LevelGeom& g, const ResizeTap* taps);
-int launch_fast(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st);
+int launch_fast(const DeviceLayout& L, const LevelGeom* hg, const TmaMaps& maps, int first_slot, int n, int win_w, int win_h, cudaStream_t st);
 int fast_window_pitch(int win_w);   // TMA box width of the FAST window (64 or 96)
 int launch_octree(const DeviceLayout& L, int first_slot, int n, int node_cap, cudaStream_t st);
 int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st);
