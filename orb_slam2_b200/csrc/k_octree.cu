@@ -83,7 +83,7 @@ __device__ __forceinline__ int block_sum(int v, int* sw) {
   return tot;
 }
 
-__global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int first_slot, int n_img, int NC) {
+__global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int first_slot, int n_img, int NC, int KC) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   Box* box0 = reinterpret_cast<Box*>(smem_raw);
   Box* box1 = box0 + NC;
@@ -97,6 +97,10 @@ __global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int firs
   int* a5 = a4 + NC;
   int* sw = a5 + NC;          // [34] scan scratch
   int* s_misc = sw + 34;      // [2]
+  // the level's ordered keys and their node ids, kept in shared memory when there are at most KC of them (every
+  // pass reads both; from global memory those loads were 35 % of the kernel's stall samples)
+  uint32_t* s_keys = reinterpret_cast<uint32_t*>(s_misc + 2);
+  uint16_t* s_node = reinterpret_cast<uint16_t*>(s_keys + KC);
 
   const int tid = threadIdx.x;
   const int img = blockIdx.x / L.nlevels, level = blockIdx.x - img * L.nlevels;
@@ -106,8 +110,8 @@ __global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int firs
   const int N = g.quota;
   const uint2* tab = L.celltab + (size_t)slot * L.cells_per_slot + g.cell_base;
   const uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + g.cand_off;
-  uint32_t* okeys = L.okeys + (size_t)slot * L.pool_per_slot + g.cand_off;
-  uint16_t* knode = L.knode + (size_t)slot * L.pool_per_slot + g.cand_off;
+  uint32_t* gkeys = L.okeys + (size_t)slot * L.pool_per_slot + g.cand_off;   // global copy: debug API, and the working set when it exceeds KC
+  uint16_t* gnode = L.knode + (size_t)slot * L.pool_per_slot + g.cand_off;
 
   // ---- A. candidates in reference order: cells row-major, pixels row-major inside a cell ----
   const int ncells = g.nCols * g.nRows;
@@ -118,10 +122,18 @@ __global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int firs
     if (c < ncells) e = tab[c];
     int tot;
     const int ex = block_scan_excl((int)e.y, sw, &tot);
-    for (uint32_t j = 0; j < e.y; ++j) okeys[nkeys + ex + j] = pool[e.x + j];
+    for (uint32_t j = 0; j < e.y; ++j) {
+      const uint32_t key = pool[e.x + j];
+      const int k = nkeys + ex + (int)j;
+      gkeys[k] = key;
+      if (k < KC) s_keys[k] = key;
+    }
     nkeys += tot;
   }
   if (tid == 0) L.nkeys[slot * kMaxLevels + level] = nkeys;
+  const bool in_smem = nkeys <= KC;                  // CTA-uniform
+  const uint32_t* okeys = in_smem ? s_keys : gkeys;
+  uint16_t* knode = in_smem ? s_node : gnode;
 
   // ---- B. root nodes (src/ORBextractor.cc:543-585) ----
   Box* box[2] = {box0, box1};
@@ -306,12 +318,13 @@ __global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int firs
   if (tid == 0) L.lvlcnt[slot * kMaxLevels + level] = n;
 }
 
-size_t octree_smem_bytes(int NC) { return (size_t)NC * (2 * sizeof(Box) + 2 * 4 + 16 + 5 * 4) + 36 * 4; }
+constexpr int kOctKeyCap = 3072;   // keys per (image, level) held in shared memory (6 bytes each); beyond that the kernel works from global memory
+size_t octree_smem_bytes(int NC) { return (size_t)NC * (2 * sizeof(Box) + 2 * 4 + 16 + 5 * 4) + 36 * 4 + (size_t)kOctKeyCap * 6; }
 
 int launch_octree(const DeviceLayout& L, int first_slot, int n, int node_cap, cudaStream_t st) {
   const size_t smem = octree_smem_bytes(node_cap);
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_octree<<<n * L.nlevels, kOctThreads, smem, st>>>(L, first_slot, n, node_cap);
+  k_octree<<<n * L.nlevels, kOctThreads, smem, st>>>(L, first_slot, n, node_cap, kOctKeyCap);
   return 1;
 }
 
