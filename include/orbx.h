@@ -129,7 +129,9 @@ orbx_status orbx_debug_level_keys(orbx_extractor* ext, int slot, int level, uint
  * extR).  bf and fx are Frame::mbf and Frame::fx; the search range is maxD = bf/(bf/fx)
  * (Frame::mb is read before it is assigned in the reference, src/Frame.cc:90 vs :114; it is
  * defined here as bf/fx).  Outputs per pair i, at [i*cap ..): mvuRight and mvDepth (-1 = no
- * match), n_matches[i] = surviving matches.  Asynchronous on `stream`. */
+ * match), n_matches[i] = surviving matches.  Asynchronous on `stream`.  Nothing is allocated:
+ * the call works in scratch both handles own since create (SAD values in extL, the right keypoints
+ * sorted by (octave, row) in extR), so calls that share a handle must not overlap on the GPU. */
 orbx_status orbx_stereo_match_batch(orbx_extractor* extL, int slotL0, orbx_extractor* extR, int slotR0,
                                     int n, float bf, float fx, float* u_right, float* depth,
                                     int* n_matches, int cap, int dst_on_device, void* stream);
