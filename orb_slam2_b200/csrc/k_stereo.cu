@@ -1,21 +1,20 @@
 // K5 — stereo matching for rectified pairs, batched over frames.
 //
 // Replaces Frame::ComputeStereoMatches (src/Frame.cc:466-640).
-//   k_stereo_match : one warp per left keypoint.
-//     (i)  descriptor search.  The reference buckets right keypoints into a per-row table
-//          (:476-493) and scans the left keypoint's row in ascending iR with a strict "<"
-//          (:522-548).  Equivalent without the table: among all iR with
-//          floor(yR-r) <= (int)vL <= ceil(yR+r), |octave difference| <= 1 and uL-maxD <= uR <= uL,
-//          take the minimum of (distance, iR) lexicographically.  Lanes stride over iR, 4x
-//          __popcll per candidate, one REDUX min over the packed key.
+//   k_stereo_rows  : one CTA per pair sorts the right keypoints by (octave, row) into 16-byte records and a
+//                    table of bin starts (the reference's per-row table vRowIndices, :476-493, turned inside out).
+//   k_stereo_match : one warp per left keypoint, no block-level step.
+//     (i)  descriptor search.  The reference scans the left keypoint's row of vRowIndices in ascending iR
+//          with a strict "<" (:522-548).  Equivalent: among all iR with floor(yR-r) <= (int)vL <= ceil(yR+r),
+//          |octave difference| <= 1 and uL-maxD <= uR <= uL, take the minimum of (distance, iR)
+//          lexicographically.  The candidates are the three contiguous runs (one per octave) of rows that can
+//          reach the keypoint's row; one record per lane, 4x __popcll, one REDUX min over the packed key.
 //     (ii) 11x11 SAD over 11 shifts on the pyramid level of the left keypoint (:552-592), integer
 //          arithmetic (the reference's float L1 norm of integer-valued patches is exact),
 //          first minimum wins; parabola refinement in the reference's float operation order
 //          with un-fused intrinsics (:597-622).
 //   k_stereo_median: one CTA per frame; the median SAD (element size/2 of the sorted list, :627)
 //     by bisection over the value range, then the 1.5*1.4*median cut (:628-639).
-#include <climits>
-
 #include "orbx_internal.h"
 
 namespace orbx {
