@@ -177,7 +177,6 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
     const int phase = (kEdge + x0) & 15;
 
     for (int i = lane; i < ((ih + 2) * SP) >> 4; i += 32) reinterpret_cast<uint4*>(smap)[i] = make_uint4(0u, 0u, 0u, 0u);   // SP % 16 == 0
-    for (int i = lane; i < m_words; i += 32) rows[i] = 0u;
     mbar_wait(bar, waited & 1);
     ++waited;
 
@@ -245,59 +244,112 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
     // the window is dead: fetch the next cell's while the maxima / emission stages run
     if (kc + 1 < ncell && !nxt.skip && lane == 0) { fence_proxy_async(); request(nxt); }
 
-    // stage 3: strict 3x3 maxima among the hot pixels (neighbours that are not hot read as 0)
-    int cnt_ini = 0, cnt_min = 0;
-    for (int i = 0; i < nhot; i += 32) {
-      const bool valid = i + lane < nhot;
-      const int e = valid ? queue[i + lane] : 0;
-      const int yy = e >> 6, xx = e & 63;
-      const uint8_t* p = smap + (yy + 1) * SP + xx + 1;
-      const int sc = p[0];
-      const int m1 = __vimax3_s32(p[-SP - 1], p[-SP], p[-SP + 1]), m2 = __vimax3_s32(p[-1], p[1], p[SP - 1]);
-      const int m3 = __vimax3_s32(p[SP], p[SP + 1], m1);
-      const bool kept = valid && sc > max(m2, m3);
-      const bool kept_ini = kept && sc > ini_th;
-      if (kept) atomicOr(&rows[yy * 2 + (xx >> 5)], 1u << (xx & 31));
-      if (kept_ini) atomicOr(&rows[(m_words >> 1) + yy * 2 + (xx >> 5)], 1u << (xx & 31));
-      cnt_min += __popc(__ballot_sync(0xffffffffu, kept));
-      cnt_ini += __popc(__ballot_sync(0xffffffffu, kept_ini));
-    }
-    __syncwarp();
-    const bool use_ini = cnt_ini > 0;                    // src/ORBextractor.cc:812: retry at minTh iff empty
-    const int total = use_ini ? cnt_ini : cnt_min;
-    int base = 0;
-    if (lane == 0) {
-      if (total > 0) base = atomicAdd(L.poolcnt + slot * kMaxLevels + level, total);
-      *cell_out = make_uint2((uint32_t)base, (uint32_t)total);
-    }
-    if (total > 0) {                                     // warp-uniform
-      base = __shfl_sync(0xffffffffu, base, 0);
-      // emit in pixel row-major order: lane r owns tested rows r and r+32; when iniTh found corners only
-      // those are emitted (second mask set)
-      uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + G.cand_off[level];
-      const int cand_cap = G.cand_cap[level];
-      const uint32_t* km = rows + (use_ini ? (m_words >> 1) : 0);
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        if (half * 32 >= ih) break;                        // warp-uniform: most cells have at most 32 tested rows
-        const int yy = half * 32 + lane;
-        unsigned long long m = yy < ih ? (((unsigned long long)km[yy * 2 + 1] << 32) | km[yy * 2]) : 0ull;
-        const uint8_t* srow = smap + (yy + 1) * SP + 1;
-        const int mine = __popcll(m);
-        int incl = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int t = __shfl_up_sync(0xffffffffu, incl, o);
-          if (lane >= o) incl += t;
+    const uint32_t lt = (1u << lane) - 1u;
+    if (iw <= 32) {                                      // warp-uniform; the usual case
+      // One column chunk: the queue, and with it the hot list, is in pixel row-major order, which is the order
+      // the candidates must leave in.  Stage 3: strict 3x3 maxima among the hot pixels (neighbours that are not
+      // hot read as 0); the kept ones are compacted in place at the front of the queue, bit 15 = also above iniTh.
+      int nkept = 0, cnt_ini = 0;
+      for (int i = 0; i < nhot; i += 32) {
+        const bool valid = i + lane < nhot;
+        const int e = valid ? queue[i + lane] : 0;
+        const int yy = e >> 6, xx = e & 63;
+        const uint8_t* p = smap + (yy + 1) * SP + xx + 1;
+        const int sc = p[0];
+        const int m1 = __vimax3_s32(p[-SP - 1], p[-SP], p[-SP + 1]), m2 = __vimax3_s32(p[-1], p[1], p[SP - 1]);
+        const int m3 = __vimax3_s32(p[SP], p[SP + 1], m1);
+        const bool kept = valid && sc > max(m2, m3);
+        const bool kept_ini = kept && sc > ini_th;
+        const uint32_t bk = __ballot_sync(0xffffffffu, kept), bi = __ballot_sync(0xffffffffu, kept_ini);
+        if (kept) queue[nkept + __popc(bk & lt)] = (uint16_t)(e | (kept_ini ? 0x8000 : 0));
+        nkept += __popc(bk);
+        cnt_ini += __popc(bi);
+      }
+      __syncwarp();
+      const bool use_ini = cnt_ini > 0;                  // src/ORBextractor.cc:812: retry at minTh iff empty
+      const int total = use_ini ? cnt_ini : nkept;
+      int base = 0;
+      if (lane == 0) {
+        if (total > 0) base = atomicAdd(L.poolcnt + slot * kMaxLevels + level, total);
+        *cell_out = make_uint2((uint32_t)base, (uint32_t)total);
+      }
+      if (total > 0) {                                   // warp-uniform
+        base = __shfl_sync(0xffffffffu, base, 0);
+        uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + G.cand_off[level];
+        const int cand_cap = G.cand_cap[level];
+        for (int i = 0; i < nkept; i += 32) {
+          const bool valid = i + lane < nkept;
+          const int e = valid ? queue[i + lane] : 0;
+          const bool sel = valid && (!use_ini || (e & 0x8000));
+          const uint32_t bs = __ballot_sync(0xffffffffu, sel);
+          if (sel) {
+            const int yy = (e >> 6) & 63, xx = e & 63;
+            const int resp = (int)smap[(yy + 1) * SP + xx + 1] - 1;
+            const int pos = base + __popc(bs & lt);
+            if (pos < cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
+          }
+          base += __popc(bs);
         }
-        int pos = base + incl - mine;
-        base += __shfl_sync(0xffffffffu, incl, 31);
-        while (m) {
-          const int xx = __ffsll((long long)m) - 1;
-          m &= m - 1;
-          const int resp = (int)srow[xx] - 1;
-          if (pos < cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
-          ++pos;
+      }
+    } else {
+      // Two column chunks (cells wider than 32 tested columns): the hot list is chunk-major, so the kept corners
+      // go through per-row bit masks and leave row by row.
+      for (int i = lane; i < m_words; i += 32) rows[i] = 0u;
+      __syncwarp();
+      // stage 3: strict 3x3 maxima among the hot pixels (neighbours that are not hot read as 0)
+      int cnt_ini = 0, cnt_min = 0;
+      for (int i = 0; i < nhot; i += 32) {
+        const bool valid = i + lane < nhot;
+        const int e = valid ? queue[i + lane] : 0;
+        const int yy = e >> 6, xx = e & 63;
+        const uint8_t* p = smap + (yy + 1) * SP + xx + 1;
+        const int sc = p[0];
+        const int m1 = __vimax3_s32(p[-SP - 1], p[-SP], p[-SP + 1]), m2 = __vimax3_s32(p[-1], p[1], p[SP - 1]);
+        const int m3 = __vimax3_s32(p[SP], p[SP + 1], m1);
+        const bool kept = valid && sc > max(m2, m3);
+        const bool kept_ini = kept && sc > ini_th;
+        if (kept) atomicOr(&rows[yy * 2 + (xx >> 5)], 1u << (xx & 31));
+        if (kept_ini) atomicOr(&rows[(m_words >> 1) + yy * 2 + (xx >> 5)], 1u << (xx & 31));
+        cnt_min += __popc(__ballot_sync(0xffffffffu, kept));
+        cnt_ini += __popc(__ballot_sync(0xffffffffu, kept_ini));
+      }
+      __syncwarp();
+      const bool use_ini = cnt_ini > 0;                    // src/ORBextractor.cc:812: retry at minTh iff empty
+      const int total = use_ini ? cnt_ini : cnt_min;
+      int base = 0;
+      if (lane == 0) {
+        if (total > 0) base = atomicAdd(L.poolcnt + slot * kMaxLevels + level, total);
+        *cell_out = make_uint2((uint32_t)base, (uint32_t)total);
+      }
+      if (total > 0) {                                     // warp-uniform
+        base = __shfl_sync(0xffffffffu, base, 0);
+        // emit in pixel row-major order: lane r owns tested rows r and r+32; when iniTh found corners only
+        // those are emitted (second mask set)
+        uint32_t* pool = L.pool + (size_t)slot * L.pool_per_slot + G.cand_off[level];
+        const int cand_cap = G.cand_cap[level];
+        const uint32_t* km = rows + (use_ini ? (m_words >> 1) : 0);
+  #pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          if (half * 32 >= ih) break;                        // warp-uniform: most cells have at most 32 tested rows
+          const int yy = half * 32 + lane;
+          unsigned long long m = yy < ih ? (((unsigned long long)km[yy * 2 + 1] << 32) | km[yy * 2]) : 0ull;
+          const uint8_t* srow = smap + (yy + 1) * SP + 1;
+          const int mine = __popcll(m);
+          int incl = mine;
+  #pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+          }
+          int pos = base + incl - mine;
+          base += __shfl_sync(0xffffffffu, incl, 31);
+          while (m) {
+            const int xx = __ffsll((long long)m) - 1;
+            m &= m - 1;
+            const int resp = (int)srow[xx] - 1;
+            if (pos < cand_cap) pool[pos] = pack_xyr(x0 + 3 + xx - kFastBorder, y0 + 3 + yy - kFastBorder, resp);
+            ++pos;
+          }
         }
       }
     }
