@@ -98,14 +98,16 @@ constexpr int kCellsPerWarp = 4;
 // the fields of LevelGeom this kernel reads, per level, as a kernel parameter (constant bank instead of global loads)
 struct FastGeom { int wCell[kMaxLevels], hCell[kMaxLevels], maxBX[kMaxLevels], maxBY[kMaxLevels], nCols[kMaxLevels], cell_base[kMaxLevels], cand_off[kMaxLevels], cand_cap[kMaxLevels]; };
 
-template <int WP>
-__global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, const __grid_constant__ FastGeom G, int first_slot,
+// NARROW: no cell of the launch has more than 32 tested columns (one column chunk everywhere): the per-row masks are
+// not needed and the S map shrinks to a 40-byte pitch - 7.2 KB instead of 8 KB per warp, 10 CTAs per SM instead of 9
+template <int WP, bool NARROW>
+__global__ void __launch_bounds__(kFastWarps * 32, NARROW ? 10 : 9) k_fast_cells(DeviceLayout L, const __grid_constant__ TmaMaps maps, const __grid_constant__ FastGeom G, int first_slot,
                                                                 int n, int win_rows, int iw_max) {
-  constexpr int SP = WP - 16;                 // S-map pitch: 48 (cells up to 36 tested columns) or 80
+  constexpr int SP = NARROW ? 40 : WP - 16;   // S-map pitch: 40 (up to 32 tested columns), 48 (up to 36) or 80
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int win_bytes = WP * win_rows, s_bytes = SP * (win_rows - 4), q_bytes = (2 * (win_rows - 6) * iw_max + 7) & ~7;
-  const int m_words = 4 * (win_rows - 6);      // two mask sets (kept above minTh / above iniTh), two words per tested row
+  const int m_words = NARROW ? 0 : 4 * (win_rows - 6);      // two mask sets (kept above minTh / above iniTh), two words per tested row
   const int per_warp = (win_bytes + s_bytes + q_bytes + 4 * m_words + 16 + 127) & ~127;
   uint8_t* win = smem + (size_t)warp * per_warp;
   uint8_t* smap = win + win_bytes;
@@ -176,7 +178,8 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
     const int x0 = cur.x0, y0 = cur.y0, iw = cur.ww - 6, ih = cur.hh - 6, slot = cur.slot, level = cur.level;
     const int phase = (kEdge + x0) & 15;
 
-    for (int i = lane; i < ((ih + 2) * SP) >> 4; i += 32) reinterpret_cast<uint4*>(smap)[i] = make_uint4(0u, 0u, 0u, 0u);   // SP % 16 == 0
+    if (NARROW) { for (int i = lane; i < ((ih + 2) * SP) >> 3; i += 32) reinterpret_cast<uint2*>(smap)[i] = make_uint2(0u, 0u); }   // SP % 8 == 0
+    else { for (int i = lane; i < ((ih + 2) * SP) >> 4; i += 32) reinterpret_cast<uint4*>(smap)[i] = make_uint4(0u, 0u, 0u, 0u); }   // SP % 16 == 0
     mbar_wait(bar, waited & 1);
     ++waited;
 
@@ -245,7 +248,7 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
     if (kc + 1 < ncell && !nxt.skip && lane == 0) { fence_proxy_async(); request(nxt); }
 
     const uint32_t lt = (1u << lane) - 1u;
-    if (iw <= 32) {                                      // warp-uniform; the usual case
+    if (NARROW || iw <= 32) {                            // warp-uniform; the usual case
       // One column chunk: the queue, and with it the hot list, is in pixel row-major order, which is the order
       // the candidates must leave in.  Stage 3: strict 3x3 maxima among the hot pixels (neighbours that are not
       // hot read as 0); the kept ones are compacted in place at the front of the queue, bit 15 = also above iniTh.
@@ -291,7 +294,7 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
           base += __popc(bs);
         }
       }
-    } else {
+    } else if (!NARROW) {
       // Two column chunks (cells wider than 32 tested columns): the hot list is chunk-major, so the kept corners
       // go through per-row bit masks and leave row by row.
       for (int i = lane; i < m_words; i += 32) rows[i] = 0u;
@@ -357,16 +360,16 @@ __global__ void __launch_bounds__(kFastWarps * 32, 9) k_fast_cells(DeviceLayout 
   }
 }
 
-template <int WP>
+template <int WP, bool NARROW>
 static void launch_fast_t(const DeviceLayout& L, const TmaMaps& maps, const FastGeom& G, int first_slot, int n, int win_w, int win_h, cudaStream_t st) {
-  constexpr int SP = WP - 16;
+  constexpr int SP = NARROW ? 40 : WP - 16;
   const int iw_max = win_w - 6;
-  const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + ((2 * (win_h - 6) * iw_max + 7) & ~7) + 16 * (win_h - 6) + 16 + 127) & ~(size_t)127;
+  const size_t per_warp = ((size_t)WP * win_h + SP * (win_h - 4) + ((2 * (win_h - 6) * iw_max + 7) & ~7) + (NARROW ? 0 : 16 * (win_h - 6)) + 16 + 127) & ~(size_t)127;
   const size_t smem = kFastWarps * per_warp;
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<WP, NARROW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const long long cells = (long long)n * L.cells_per_slot;
   const long long per_cta = (long long)kFastWarps * kCellsPerWarp;
-  k_fast_cells<WP><<<(unsigned)((cells + per_cta - 1) / per_cta), kFastWarps * 32, smem, st>>>(L, maps, G, first_slot, n, win_h, iw_max);
+  k_fast_cells<WP, NARROW><<<(unsigned)((cells + per_cta - 1) / per_cta), kFastWarps * 32, smem, st>>>(L, maps, G, first_slot, n, win_h, iw_max);
 }
 
 int fast_window_pitch(int win_w) { return win_w + 15 <= 64 ? 64 : 96; }
@@ -378,8 +381,9 @@ int launch_fast(const DeviceLayout& L, const LevelGeom* hg, const TmaMaps& maps,
     G.nCols[l] = hg[l].nCols; G.cell_base[l] = hg[l].cell_base; G.cand_off[l] = hg[l].cand_off; G.cand_cap[l] = hg[l].cand_cap;
   }
   // the TMA box starts at the 16-byte boundary below the window: phase (<= 15) + width must fit the pitch
-  if (fast_window_pitch(win_w) == 64) launch_fast_t<64>(L, maps, G, first_slot, n, win_w, win_h, st);
-  else launch_fast_t<96>(L, maps, G, first_slot, n, win_w, win_h, st);
+  if (win_w - 6 <= 32) launch_fast_t<64, true>(L, maps, G, first_slot, n, win_w, win_h, st);
+  else if (fast_window_pitch(win_w) == 64) launch_fast_t<64, false>(L, maps, G, first_slot, n, win_w, win_h, st);
+  else launch_fast_t<96, false>(L, maps, G, first_slot, n, win_w, win_h, st);
   return 1;
 }
 
