@@ -260,10 +260,11 @@ def secondary_workloads(gx, torch, local):
     prev0 = kps.view(torch.float32).reshape(2 * P, cap, 7)[:P, :, :2].contiguous()
     m12 = torch.empty((P, cap), dtype=torch.int32, device="cuda"); nmm = torch.empty(P, dtype=torch.int32, device="cuda")
     L = gx.lib()
+    gb = torch.tensor([0, w, 0, h, 64.0 / w, 48.0 / h], dtype=torch.float32, device="cuda")     # undistorted camera: Frame's bounds = the image
     def init_step():
         prev = prev0.clone()
         rc = L.orbx_search_init_batch(kps.data_ptr(), desc.data_ptr(), cnt.data_ptr(), kps[P:].data_ptr(), desc[P:].data_ptr(), cnt[P:].data_ptr(),
-                                      P, cap, w, h, prev.data_ptr(), 0.9, 100, 1, m12.data_ptr(), nmm.data_ptr(), 1, st)
+                                      P, cap, gb.data_ptr(), prev.data_ptr(), 0.9, 100, 1, m12.data_ptr(), nmm.data_ptr(), 1, st)
         assert rc == 0, L.orbx_last_error_string()
     for _ in range(2):
         init_step()

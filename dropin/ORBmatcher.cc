@@ -7,9 +7,10 @@
 // Frame / KeyFrame / MapPoint / Map sources linked with this file and dropin/ORBextractor.h instead of src/ORBmatcher.cc
 // and src/ORBextractor.cc; tests/test_zz_dropin.py checks that it writes the same bytes as the all-reference binary.
 //
-// Two things the reference keeps private are needed: MapPoint::mfMinDistance / mfMaxDistance (only their 0.8x / 1.2x
-// products are public, and the division is not exact in float).  A maintainer adds two getters to MapPoint; this file
-// lifts the access check for its own translation unit instead, which does not change any layout.
+// Two things the reference keeps protected are needed: MapPoint::mfMinDistance / mfMaxDistance (only their 0.8x / 1.2x
+// products are public, and dividing those back is not exact in float).  A maintainer adds the two getters shown in
+// INTEGRATION.md; so that this file also compiles against an unpatched tree it reads them through pointers to members
+// named via a derived class (MapPointFields below), which is plain C++ and touches no declaration of the reference.
 #include <algorithm>
 #include <cmath>
 #include <list>
@@ -22,9 +23,7 @@
 #include <vector>
 
 #include <opencv2/core/core.hpp>
-#define protected public
 #include "MapPoint.h"
-#undef protected
 #include "Frame.h"
 #include "KeyFrame.h"
 #include "ORBmatcher.h"
@@ -39,6 +38,21 @@ const int ORBmatcher::TH_LOW = 50;
 const int ORBmatcher::HISTO_LENGTH = 30;
 
 namespace {
+
+// &Derived::member for a protected member of the base has type `float MapPoint::*` and passes the access check
+struct MapPointFields : MapPoint {
+  static float MinDistance(MapPoint* p) { return p->*(&MapPointFields::mfMinDistance); }
+  static float MaxDistance(MapPoint* p) { return p->*(&MapPointFields::mfMaxDistance); }
+};
+
+// Frame's static image bounds and inverse cell sizes (src/Frame.cc:207-213) as the C ABI's grid_bounds[6]
+struct FrameBounds {
+  float v[6];
+  FrameBounds() {
+    v[0] = Frame::mnMinX; v[1] = Frame::mnMaxX; v[2] = Frame::mnMinY; v[3] = Frame::mnMaxY;
+    v[4] = Frame::mfGridElementWidthInv; v[5] = Frame::mfGridElementHeightInv;
+  }
+};
 
 void check(orbx_status s) {
   if (s != ORBX_OK) throw std::runtime_error(std::string("orbx: ") + orbx_last_error_string());
@@ -103,7 +117,7 @@ struct MPs {
     const cv::Mat X = mp->GetWorldPos(), Nn = mp->GetNormal(), d = mp->GetDescriptor();
     for (int a = 0; a < 3; ++a) { xw[3 * k + a] = X.at<float>(a); normal[3 * k + a] = Nn.at<float>(a); }
     std::copy(d.ptr(0), d.ptr(0) + 32, &desc[(size_t)k * 32]);
-    dmin[k] = mp->mfMinDistance; dmax[k] = mp->mfMaxDistance;
+    dmin[k] = MapPointFields::MinDistance(mp); dmax[k] = MapPointFields::MaxDistance(mp);
     obs[k] = mp->Observations();
   }
 };
@@ -137,8 +151,8 @@ int ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoint
   std::vector<int> frame_obs(f.cap, -1), assigned(f.cap, -1);
   for (int i = 0; i < f.n; ++i) if (F.mvpMapPoints[i]) frame_obs[i] = F.mvpMapPoints[i]->Observations();
   int nm = 0;
-  check(orbx_search_projection_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, (int)(Frame::mnMaxX - Frame::mnMinX),
-                                     (int)(Frame::mnMaxY - Frame::mnMinY), F.mvScaleFactors.data(), F.mnScaleLevels, inview.data(), px.data(), py.data(),
+  const FrameBounds gb;
+  check(orbx_search_projection_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, gb.v, F.mvScaleFactors.data(), F.mnScaleLevels, inview.data(), px.data(), py.data(),
                                      pxr.data(), level.data(), vcos.data(), desc.data(), obs.data(), &m, mcap, th, mfNNratio, frame_obs.data(),
                                      assigned.data(), &nm, 0, nullptr));
   for (int i = 0; i < f.n; ++i) if (assigned[i] >= 0) F.mvpMapPoints[i] = vpMapPoints[assigned[i]];
@@ -173,8 +187,8 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, 
   std::vector<int> frame_obs(f.cap, -1), assigned(f.cap, -1);
   for (int i = 0; i < f.n; ++i) if (CurrentFrame.mvpMapPoints[i]) frame_obs[i] = CurrentFrame.mvpMapPoints[i]->Observations();
   int nm = 0;
-  check(orbx_search_projection_frame_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, (int)(Frame::mnMaxX - Frame::mnMinX),
-                                           (int)(Frame::mnMaxY - Frame::mnMinY), CurrentFrame.mvScaleFactors.data(), CurrentFrame.mnScaleLevels, pose, &mode,
+  const FrameBounds gb;
+  check(orbx_search_projection_frame_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, gb.v, CurrentFrame.mvScaleFactors.data(), CurrentFrame.mnScaleLevels, pose, &mode,
                                            CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx, CurrentFrame.cy, CurrentFrame.mbf, valid.data(), xw.data(),
                                            octave.data(), angle.data(), desc.data(), obs.data(), &nl, lcap, th, mbCheckOrientation ? 1 : 0,
                                            frame_obs.data(), assigned.data(), &nm, 0, nullptr));
@@ -292,8 +306,8 @@ int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f
   for (int i = 0; i < F1.N; ++i) { prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
   vnMatches12.assign(cap, -1);
   int nm = 0;
-  check(orbx_search_init_batch(a.kps.data(), a.desc.data(), &a.n, b.kps.data(), b.desc.data(), &b.n, 1, cap, (int)(Frame::mnMaxX - Frame::mnMinX),
-                               (int)(Frame::mnMaxY - Frame::mnMinY), prev.data(), mfNNratio, windowSize, mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nm, 0,
+  const FrameBounds gb;
+  check(orbx_search_init_batch(a.kps.data(), a.desc.data(), &a.n, b.kps.data(), b.desc.data(), &b.n, 1, cap, gb.v, prev.data(), mfNNratio, windowSize, mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nm, 0,
                                nullptr));
   vnMatches12.resize(F1.N);
   for (int i = 0; i < F1.N; ++i) { vbPrevMatched[i].x = prev[2 * i]; vbPrevMatched[i].y = prev[2 * i + 1]; }

@@ -144,11 +144,15 @@ int orbx_hamming256(const uint8_t* a, const uint8_t* b);
 /* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520) for n_pairs independent frame
  * pairs.  Pair p: frame 1 has n1[p] keypoints at kps1 + p*cap (desc1 likewise), frame 2 n2[p].
  * prev_xy (in/out) is vbPrevMatched as x,y pairs; matches12 receives vnMatches12 (-1 = none),
- * n_matches the return value.  cols/rows are the image bounds used by the 64x48 feature grid
- * (src/Frame.cc:230-245, undistorted camera).  All pointers host or all device per on_device. */
+ * n_matches the return value.  grid_bounds[6] = frame 2's mnMinX, mnMaxX, mnMinY, mnMaxY,
+ * mfGridElementWidthInv, mfGridElementHeightInv (src/Frame.cc:207-213; what orbx_undistort_grid_batch
+ * returns as `bounds`; {0, cols, 0, rows, 64/cols, 48/rows} for an undistorted camera): a distorted
+ * camera's undistorted keypoints may lie left of / above 0 and the 64x48 grid is laid over
+ * [mnMinX, mnMaxX) x [mnMinY, mnMaxY) (PosInGrid :382-392, GetFeaturesInArea :327-380).
+ * All pointers host or all device per on_device. */
 orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const int* n1,
                                    const orbx_keypoint* kps2, const uint8_t* desc2, const int* n2,
-                                   int n_pairs, int cap, int cols, int rows, float* prev_xy,
+                                   int n_pairs, int cap, const float* grid_bounds, float* prev_xy,
                                    float nnratio, int window, int check_orientation,
                                    int* matches12, int* n_matches, int on_device, void* stream);
 
@@ -166,7 +170,8 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
 /* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:45-129; the
  * local-map search of every tracked frame, called from src/Tracking.cc:1192) for n_frames independent
  * frames.  Frame f: n[f] keypoints at kps + f*cap (undistorted keypoints, descriptors, mvuRight),
- * image bounds cols x rows for the 64x48 feature grid, scale_factors = mvScaleFactors.  Its m[f] map
+ * grid_bounds[6] as in orbx_search_init_batch (the Frame's static bounds and inverse cell sizes),
+ * scale_factors = mvScaleFactors.  Its m[f] map
  * points at index f*mcap carry what Frame::isInFrustum left in each MapPoint (src/Frame.cc:316-322):
  * mp_in_view (mbTrackInView && !isBad()), mp_proj_x/y/xr (mTrackProjX/Y/XR), mp_level
  * (mnTrackScaleLevel), mp_view_cos (mTrackViewCos), mp_desc (GetDescriptor()), mp_obs (Observations()).
@@ -175,7 +180,7 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
  * call (-1 = none), n_matches[f] the return value.  nnratio/th as in the reference (0.8 and 1 or 3 at
  * src/Tracking.cc:1185-1192).  All pointers host or all device per on_device. */
 orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right,
-                                         const int* n, int n_frames, int cap, int cols, int rows,
+                                         const int* n, int n_frames, int cap, const float* grid_bounds,
                                          const float* scale_factors, int nlevels, const uint8_t* mp_in_view,
                                          const float* mp_proj_x, const float* mp_proj_y, const float* mp_proj_xr,
                                          const int* mp_level, const float* mp_view_cos, const uint8_t* mp_desc,
@@ -185,7 +190,8 @@ orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t
 
 /* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono) (src/ORBmatcher.cc:1328-1470;
  * the motion-model search, called from src/Tracking.cc:886,892) for n_frames independent frame pairs.
- * Current frame f as in orbx_search_projection_batch (kps/desc/u_right/n, cols x rows, scale_factors).
+ * Current frame f as in orbx_search_projection_batch (kps/desc/u_right/n, grid_bounds, scale_factors); a
+ * projection outside [mnMinX, mnMaxX] x [mnMinY, mnMaxY] is skipped (:1373-1376).
  * Last frame f: n_last[f] entries at index f*lcap: last_valid (mvpMapPoints[i] && !mvbOutlier[i]),
  * last_xw (the map point's world position, 3 floats), last_octave / last_angle (mvKeys[i].octave,
  * mvKeysUn[i].angle), mp_desc (GetDescriptor()), mp_obs (Observations()).  pose[f*12..] is
@@ -194,7 +200,7 @@ orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t
  * frame_obs / assigned / n_matches as in orbx_search_projection_batch (assigned = index into the last
  * frame).  All pointers host or all device per on_device. */
 orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right,
-                                               const int* n, int n_frames, int cap, int cols, int rows,
+                                               const int* n, int n_frames, int cap, const float* grid_bounds,
                                                const float* scale_factors, int nlevels, const float* pose,
                                                const int* mode, float fx, float fy, float cx, float cy, float bf,
                                                const uint8_t* last_valid, const float* last_xw,
@@ -383,7 +389,8 @@ orbx_status orbx_features_in_area_batch(const orbx_keypoint* kps_un, const int* 
  * is part of the library image: every GPU that loads liborbx.so holds it until the process exits.
  *   - all pointers are DEVICE pointers (inputs descA/angA/descB/angB, outputs matches12[nA] and
  *     n_matches[1]); the call is asynchronous on `stream`
- *   - at most ORBX_NOALLOC_MAX_FEATURES features per side, otherwise ORBX_ERR_CAPACITY
+ *   - at most ORBX_NOALLOC_MAX_FEATURES features per side, otherwise ORBX_ERR_CAPACITY; th is 0..255 as in
+ *     orbx_knn_ratio_batch, otherwise ORBX_ERR_BAD_ARG; device indices 0..63
  *   - the first call on each device looks up the array's device address and raises the kernel's
  *     shared-memory limit; make that first call outside any stream capture
  *   - all calls on one GPU share the array (it keeps the last call's contents; the kernel

@@ -163,11 +163,13 @@ class ORBmatcher {
 
   static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return orbx_hamming256(a.ptr(), b.ptr()); }
 
-  // SearchForInitialization on the arrays Frame holds (mvKeysUn, mDescriptors of F1 and F2, image
-  // bounds); vbPrevMatched and vnMatches12 as in include/ORBmatcher.h:69.
+  // SearchForInitialization on the arrays Frame holds (mvKeysUn, mDescriptors of F1 and F2) and Frame's static
+  // bounds {mnMinX, mnMaxX, mnMinY, mnMaxY} ({0, cols, 0, rows} without distortion); vbPrevMatched and vnMatches12
+  // as in include/ORBmatcher.h:69.
   int SearchForInitialization(const std::vector<cv::KeyPoint>& keys1, const cv::Mat& desc1,
-                              const std::vector<cv::KeyPoint>& keys2, const cv::Mat& desc2, int cols, int rows,
+                              const std::vector<cv::KeyPoint>& keys2, const cv::Mat& desc2, const float bounds[4],
                               std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10) {
+    const float gb[6] = {bounds[0], bounds[1], bounds[2], bounds[3], 64.0f / (bounds[1] - bounds[0]), 48.0f / (bounds[3] - bounds[2])};   // src/Frame.cc:212-213
     const int n1 = (int)keys1.size(), n2 = (int)keys2.size(), cap = std::max(std::max(n1, n2), 1);
     std::vector<orbx_keypoint> k1(cap), k2(cap);
     std::vector<unsigned char> d1((size_t)cap * 32), d2((size_t)cap * 32);
@@ -177,7 +179,7 @@ class ORBmatcher {
     for (int i = 0; i < n2; ++i) { k2[i] = reinterpret_cast<const orbx_keypoint&>(keys2[i]); std::copy(desc2.ptr(i), desc2.ptr(i) + 32, &d2[(size_t)i * 32]); }
     vnMatches12.assign(cap, -1);
     int nm = 0;
-    orbx_check(orbx_search_init_batch(k1.data(), d1.data(), &n1, k2.data(), d2.data(), &n2, 1, cap, cols, rows, prev.data(), mfNNratio,
+    orbx_check(orbx_search_init_batch(k1.data(), d1.data(), &n1, k2.data(), d2.data(), &n2, 1, cap, gb, prev.data(), mfNNratio,
                                       windowSize, mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nm, 0, nullptr));
     vnMatches12.resize(n1);
     for (int i = 0; i < n1; ++i) { vbPrevMatched[i].x = prev[2 * i]; vbPrevMatched[i].y = prev[2 * i + 1]; }

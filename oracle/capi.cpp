@@ -58,9 +58,9 @@ int orbo_stereo(void* eL, void* eR, const KeyPt* kL, const uint8_t* dL, int nL, 
 }
 
 int orbo_search_init(const KeyPt* k1, const uint8_t* d1, int n1, const KeyPt* k2, const uint8_t* d2,
-                     int n2, int cols, int rows, float* prev, float ratio, int window, int checkOri,
+                     int n2, const float* bounds, float* prev, float ratio, int window, int checkOri,
                      int* m12) {
-  return search_for_init(k1, d1, n1, k2, d2, n2, cols, rows, prev, ratio, window, checkOri != 0, m12);
+  return search_for_init(k1, d1, n1, k2, d2, n2, bounds, prev, ratio, window, checkOri != 0, m12);
 }
 
 int orbo_knn_ratio(const uint8_t* dA, const float* angA, int nA, const uint8_t* dB, const float* angB,
@@ -116,20 +116,20 @@ int orbo_project_match_ordered(const KeyPt* k, const uint8_t* d, int n, const fl
 
 int orbo_distinctive_descriptor(const uint8_t* d, int n) { return distinctive_descriptor(d, n); }
 
-int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,
+int orbo_search_projection(const KeyPt* k, const uint8_t* d, const float* uRight, int n, const float* bounds, const float* scale,
                             const uint8_t* inView, const float* projX, const float* projY, const float* projXR, const int* level,
                             const float* viewCos, const uint8_t* mpDesc, const int* mpObs, int m, float th, float nnratio,
                             int* frameObs, int* assigned) {
-  return search_by_projection_points(k, d, uRight, n, cols, rows, scale, inView, projX, projY, projXR, level, viewCos, mpDesc,
+  return search_by_projection_points(k, d, uRight, n, bounds, scale, inView, projX, projY, projXR, level, viewCos, mpDesc,
                                      mpObs, m, th, nnratio, frameObs, assigned);
 }
 
-int orbo_search_projection_frame(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols, int rows, const float* scale,
+int orbo_search_projection_frame(const KeyPt* k, const uint8_t* d, const float* uRight, int n, const float* bounds, const float* scale,
                                   const float* Rcw, const float* tcw, float fx, float fy, float cx, float cy, float bf,
                                   const uint8_t* lastValid, const float* lastXw, const int* lastOctave, const float* lastAngle,
                                   const uint8_t* mpDesc, const int* mpObs, int nLast, float th, int mode, int checkOri, int* frameObs,
                                   int* assigned) {
-  return search_by_projection_frame(k, d, uRight, n, cols, rows, scale, Rcw, tcw, fx, fy, cx, cy, bf, lastValid, lastXw, lastOctave,
+  return search_by_projection_frame(k, d, uRight, n, bounds, scale, Rcw, tcw, fx, fy, cx, cy, bf, lastValid, lastXw, lastOctave,
                                     lastAngle, mpDesc, mpObs, nLast, th, mode, checkOri != 0, frameObs, assigned);
 }
 

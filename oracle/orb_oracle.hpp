@@ -540,13 +540,13 @@ static inline int rot_bin(float a1, float a2) {
 
 // ORBmatcher::SearchForInitialization.  prev is vbPrevMatched (in/out, xy pairs).
 inline int search_for_init(const KeyPt* k1, const uint8_t* d1, int n1, const KeyPt* k2,
-                           const uint8_t* d2, int n2, int cols, int rows, float* prev, float ratio,
-                           int window, bool checkOri, int* m12) {
+                           const uint8_t* d2, int n2, const float* bounds, float* prev, float ratio,
+                           int window, bool checkOri, int* m12) {   // bounds = frame 2's {mnMinX, mnMaxX, mnMinY, mnMaxY}
   int nm = 0;
   for (int i = 0; i < n1; ++i) m12[i] = -1;
   std::vector<int> hist[kHisto];
   std::vector<int> dist2(n2, INT_MAX), m21(n2, -1);
-  FrameGrid grid(k2, n2, cols, rows);
+  FrameGrid grid(k2, n2, bounds);
   std::vector<int> cand;
   for (int i1 = 0; i1 < n1; ++i1) {
     if (k1[i1].octave > 0) continue;
@@ -586,13 +586,13 @@ inline int search_for_init(const KeyPt* k1, const uint8_t* d1, int n1, const Key
 // point's descriptor and Observations().  frameObs[i] is the state of F.mvpMapPoints[i] on entry:
 // -1 = none, else that point's Observations(); assigned[i] receives the index of the map point
 // matched to keypoint i by this call (-1 = none).  Returns nmatches.
-inline int search_by_projection_points(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols,
-                                       int rows, const float* scale, const uint8_t* inView, const float* projX,
+inline int search_by_projection_points(const KeyPt* k, const uint8_t* d, const float* uRight, int n,
+                                       const float* bounds, const float* scale, const uint8_t* inView, const float* projX,
                                        const float* projY, const float* projXR, const int* level,
                                        const float* viewCos, const uint8_t* mpDesc, const int* mpObs, int m,
                                        float th, float nnratio, int* frameObs, int* assigned) {
   for (int i = 0; i < n; ++i) assigned[i] = -1;
-  FrameGrid grid(k, n, cols, rows);
+  FrameGrid grid(k, n, bounds);
   const bool bFactor = th != 1.0;
   int nm = 0;
   std::vector<int> cand;
@@ -631,14 +631,14 @@ inline int search_by_projection_points(const KeyPt* k, const uint8_t* d, const f
 // (row-major 3x3 and 3x1).  mode: 0 = neither, 1 = bForward, 2 = bBackward (the caller evaluates
 // :1347-1348 from tlc and mb).  Camera-frame coordinates use OpenCV's small-matrix gemm arithmetic,
 // which tests/test_oracle_cv2.py pins against cv2.gemm: float products and sums, left to right.
-inline int search_by_projection_frame(const KeyPt* k, const uint8_t* d, const float* uRight, int n, int cols,
-                                      int rows, const float* scale, const float* Rcw, const float* tcw, float fx,
+inline int search_by_projection_frame(const KeyPt* k, const uint8_t* d, const float* uRight, int n,
+                                      const float* bounds, const float* scale, const float* Rcw, const float* tcw, float fx,
                                       float fy, float cx, float cy, float bf, const uint8_t* lastValid,
                                       const float* lastXw, const int* lastOctave, const float* lastAngle,
                                       const uint8_t* mpDesc, const int* mpObs, int nLast, float th, int mode,
                                       bool checkOri, int* frameObs, int* assigned) {
   for (int i = 0; i < n; ++i) assigned[i] = -1;
-  FrameGrid grid(k, n, cols, rows);
+  FrameGrid grid(k, n, bounds);
   std::vector<int> hist[kHisto];
   std::vector<int> cand;
   int nm = 0;
@@ -651,8 +651,8 @@ inline int search_by_projection_frame(const KeyPt* k, const uint8_t* d, const fl
     const float invzc = (float)(1.0 / c3[2]);
     if (invzc < 0) continue;
     const float u = fx * xc * invzc + cx, v = fy * yc * invzc + cy;
-    if (u < 0.f || u > (float)cols) continue;
-    if (v < 0.f || v > (float)rows) continue;
+    if (u < bounds[0] || u > bounds[1]) continue;      // CurrentFrame.mnMinX / mnMaxX, :1373
+    if (v < bounds[2] || v > bounds[3]) continue;
     const int oct = lastOctave[i];
     const float radius = th * scale[oct];
     if (mode == 1) grid.in_area(k, u, v, radius, oct, -1, cand);

@@ -94,12 +94,18 @@ def stereo(eL, eR, kL, dL, kR, dR, bf, fx):
     return ur, dp, sad, m
 
 
-def search_init(k1, d1, k2, d2, cols, rows, prev, ratio=0.9, window=100, check_ori=True):
+def _bounds4(cols, rows, bounds):
+    """Frame::mnMinX, mnMaxX, mnMinY, mnMaxY: [0, cols] x [0, rows] for an undistorted camera."""
+    return np.array([0, cols, 0, rows] if bounds is None else list(bounds)[:4], np.float32)
+
+
+def search_init(k1, d1, k2, d2, cols, rows, prev, ratio=0.9, window=100, check_ori=True, bounds=None):
     k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
     d1 = np.ascontiguousarray(d1); d2 = np.ascontiguousarray(d2)
     prev = np.ascontiguousarray(prev, np.float32).copy()
     m12 = np.zeros(len(k1), np.int32)
-    n = lib().orbo_search_init(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), cols, rows, _p(prev),
+    b = _bounds4(cols, rows, bounds)
+    n = lib().orbo_search_init(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), _p(b), _p(prev),
                                C.c_float(ratio), window, int(check_ori), _p(m12))
     return m12, n, prev
 
@@ -432,7 +438,7 @@ def features_in_area(kun, bounds, x, y, r, min_level=-1, max_level=-1):
     return out[:n].copy()
 
 
-def search_projection(k, d, uright, cols, rows, scale, mp, th=1.0, nnratio=0.8, frame_obs=None):
+def search_projection(k, d, uright, cols, rows, scale, mp, th=1.0, nnratio=0.8, frame_obs=None, bounds=None):
     """mp: dict of arrays inview(u8), projx, projy, projxr (f32), level (i32), viewcos (f32), desc (m,32), obs (i32)."""
     k = np.ascontiguousarray(k); d = np.ascontiguousarray(d); n = len(k); m = len(mp["level"])
     uright = np.ascontiguousarray(uright, np.float32); scale = np.ascontiguousarray(scale, np.float32)
@@ -440,13 +446,14 @@ def search_projection(k, d, uright, cols, rows, scale, mp, th=1.0, nnratio=0.8, 
     assigned = np.zeros(n, np.int32)
     a = {key: np.ascontiguousarray(mp[key], dt) for key, dt in [("inview", np.uint8), ("projx", np.float32), ("projy", np.float32),
          ("projxr", np.float32), ("level", np.int32), ("viewcos", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
-    nm = lib().orbo_search_projection(_p(k), _p(d), _p(uright), n, cols, rows, _p(scale), _p(a["inview"]), _p(a["projx"]), _p(a["projy"]),
+    b = _bounds4(cols, rows, bounds)
+    nm = lib().orbo_search_projection(_p(k), _p(d), _p(uright), n, _p(b), _p(scale), _p(a["inview"]), _p(a["projx"]), _p(a["projy"]),
                                       _p(a["projxr"]), _p(a["level"]), _p(a["viewcos"]), _p(a["desc"]), _p(a["obs"]), m,
                                       C.c_float(th), C.c_float(nnratio), _p(fo), _p(assigned))
     return assigned, nm, fo
 
 
-def search_projection_frame(k, d, uright, cols, rows, scale, Rcw, tcw, cam, last, th=15.0, mode=0, check_ori=True, frame_obs=None):
+def search_projection_frame(k, d, uright, cols, rows, scale, Rcw, tcw, cam, last, th=15.0, mode=0, check_ori=True, frame_obs=None, bounds=None):
     """cam = (fx, fy, cx, cy, bf); last: dict valid(u8), xw (n,3 f32), octave (i32), angle (f32), desc (n,32), obs (i32)."""
     k = np.ascontiguousarray(k); d = np.ascontiguousarray(d); n = len(k); nl = len(last["octave"])
     uright = np.ascontiguousarray(uright, np.float32); scale = np.ascontiguousarray(scale, np.float32)
@@ -456,7 +463,8 @@ def search_projection_frame(k, d, uright, cols, rows, scale, Rcw, tcw, cam, last
     a = {key: np.ascontiguousarray(last[key], dt) for key, dt in [("valid", np.uint8), ("xw", np.float32), ("octave", np.int32),
          ("angle", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
     fx, fy, cx, cy, bf = (C.c_float(v) for v in cam)
-    nm = lib().orbo_search_projection_frame(_p(k), _p(d), _p(uright), n, cols, rows, _p(scale), _p(Rcw), _p(tcw), fx, fy, cx, cy, bf,
+    b = _bounds4(cols, rows, bounds)
+    nm = lib().orbo_search_projection_frame(_p(k), _p(d), _p(uright), n, _p(b), _p(scale), _p(Rcw), _p(tcw), fx, fy, cx, cy, bf,
                                             _p(a["valid"]), _p(a["xw"]), _p(a["octave"]), _p(a["angle"]), _p(a["desc"]), _p(a["obs"]), nl,
                                             C.c_float(th), mode, int(check_ori), _p(fo), _p(assigned))
     return assigned, nm, fo

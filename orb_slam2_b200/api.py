@@ -76,7 +76,7 @@ def lib():
                                    C.c_void_p, C.c_void_p]
         L.orbx_stereo_match_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
-        L.orbx_search_init_batch.argtypes = [C.c_void_p] * 6 + [C.c_int] * 4 + [C.c_void_p, C.c_float, C.c_int, C.c_int,
+        L.orbx_search_init_batch.argtypes = [C.c_void_p] * 6 + [C.c_int] * 2 + [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int,
                                                                              C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_knn_ratio_batch.argtypes = [C.c_void_p] * 6 + [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
                                                               C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -87,10 +87,10 @@ def lib():
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_stream_synchronize.argtypes = [C.c_void_p]
-        L.orbx_search_projection_frame_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 4 + [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] +
+        L.orbx_search_projection_frame_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 2 + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] +
                                                          [C.c_float] * 5 + [C.c_void_p] * 7 + [C.c_int, C.c_float, C.c_int] +
                                                          [C.c_void_p] * 3 + [C.c_int, C.c_void_p])
-        L.orbx_search_projection_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 9 +
+        L.orbx_search_projection_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 2 + [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 9 +
                                                    [C.c_int, C.c_float, C.c_float] + [C.c_void_p] * 3 + [C.c_int, C.c_void_p])
         L.orbx_knn_ratio_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                              C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -307,8 +307,13 @@ def ComputeStereoMatches(extL, extR, bf, fx, n=1, slotL0=0, slotR0=0, out=None, 
 class Frame:
     """The slice of ORB_SLAM2::Frame the matchers read: undistorted keypoints, descriptors, image bounds."""
 
-    def __init__(self, keypoints, descriptors, cols, rows):
+    def __init__(self, keypoints, descriptors, cols, rows, bounds=None):
+        """bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY) of a distorted camera (Frame::ComputeImageBounds, src/Frame.cc:436-464;
+        FrameGrids.bounds[:4]); None = undistorted camera, [0, cols] x [0, rows]."""
         self.mvKeysUn, self.mDescriptors, self.cols, self.rows = keypoints, descriptors, cols, rows
+        b = np.array([0, cols, 0, rows] if bounds is None else list(bounds)[:4], np.float32)
+        # mfGridElementWidthInv / HeightInv, src/Frame.cc:212-213 (float division)
+        self.grid_bounds = np.array([b[0], b[1], b[2], b[3], np.float32(GRID_COLS) / (b[1] - b[0]), np.float32(GRID_ROWS) / (b[3] - b[2])], np.float32)
 
 
 class ORBVocabulary:
@@ -446,7 +451,7 @@ class ORBmatcher:
             pv[p, :n1[p]] = pr
         m12 = np.zeros((npairs, cap), np.int32); nm = np.zeros(npairs, np.int32)
         _check(lib().orbx_search_init_batch(k1.ctypes.data, d1.ctypes.data, n1.ctypes.data, k2.ctypes.data, d2.ctypes.data,
-                                            n2.ctypes.data, npairs, cap, F2s[0].cols, F2s[0].rows, pv.ctypes.data,
+                                            n2.ctypes.data, npairs, cap, F2s[0].grid_bounds.ctypes.data, pv.ctypes.data,
                                             self.mfNNratio, int(windowSize), int(self.mbCheckOrientation),
                                             m12.ctypes.data, nm.ctypes.data, 0, None))
         for p, pr in enumerate(prevs):
@@ -465,7 +470,7 @@ class ORBmatcher:
              ("projxr", np.float32), ("level", np.int32), ("viewcos", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
         cn = np.array([n], np.int32); cm = np.array([m], np.int32)
         assigned = np.zeros(cap, np.int32); nm = np.zeros(1, np.int32)
-        _check(lib().orbx_search_projection_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, cn.ctypes.data, 1, cap, F.cols, F.rows,
+        _check(lib().orbx_search_projection_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, cn.ctypes.data, 1, cap, F.grid_bounds.ctypes.data,
                                                   sc.ctypes.data, len(sc), a["inview"].ctypes.data, a["projx"].ctypes.data,
                                                   a["projy"].ctypes.data, a["projxr"].ctypes.data, a["level"].ctypes.data,
                                                   a["viewcos"].ctypes.data, a["desc"].ctypes.data, a["obs"].ctypes.data, cm.ctypes.data,
@@ -486,7 +491,7 @@ class ORBmatcher:
         cn = np.array([n], np.int32); cl = np.array([nl], np.int32); md = np.array([mode], np.int32)
         assigned = np.zeros(cap, np.int32); nm = np.zeros(1, np.int32)
         fx, fy, cx, cy, bf = cam
-        _check(lib().orbx_search_projection_frame_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, cn.ctypes.data, 1, cap, F.cols, F.rows,
+        _check(lib().orbx_search_projection_frame_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, cn.ctypes.data, 1, cap, F.grid_bounds.ctypes.data,
                                                         sc.ctypes.data, len(sc), pose.ctypes.data, md.ctypes.data, fx, fy, cx, cy, bf,
                                                         a["valid"].ctypes.data, a["xw"].ctypes.data, a["octave"].ctypes.data,
                                                         a["angle"].ctypes.data, a["desc"].ctypes.data, a["obs"].ctypes.data, cl.ctypes.data,

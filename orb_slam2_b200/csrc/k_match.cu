@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(32) k_search_init(InitMatchArgs a) {
   __shared__ int s_hist[kHisto];
   const int p = blockIdx.x, lane = threadIdx.x;
   const int n1 = a.n1[p], n2 = a.n2[p];
+  const float minX = a.gb[0], minY = a.gb[2], invW = a.gb[4], invH = a.gb[5];   // Frame::mnMinX, mnMinY, mfGridElement{Width,Height}Inv
   const orbx_keypoint* k1 = a.k1 + (size_t)p * a.cap;
   const orbx_keypoint* k2 = a.k2 + (size_t)p * a.cap;
   const uint32_t* d1 = reinterpret_cast<const uint32_t*>(a.d1 + (size_t)p * a.cap * 32);
@@ -85,7 +86,7 @@ __global__ void __launch_bounds__(32) k_search_init(InitMatchArgs a) {
     int cell = 0;
     if (i < n2) {
       const orbx_keypoint kp = k2[i];
-      const int gx = (int)roundf(__fmul_rn(kp.x, a.invW)), gy = (int)roundf(__fmul_rn(kp.y, a.invH));   // PosInGrid
+      const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));   // PosInGrid, src/Frame.cc:382-392
       ok = kp.octave == 0 && gx >= 0 && gx < 64 && gy >= 0 && gy < 48;
       cell = gx * 48 + gy;
     }
@@ -360,12 +361,12 @@ constexpr int kGridCells = 64 * 48;
 // src/Frame.cc:230-245,382-392), one warp.  On return cell c occupies [soff[c+1], soff[c+2]) of
 // sxy / smeta (the last cell ends at the returned count); keypoints outside the grid are dropped,
 // as the reference does.  smeta = octave<<28 | cell<<16 | keypoint index.
-__device__ __forceinline__ int grid_sort(const orbx_keypoint* k, int n, float invW, float invH, float2* sxy, uint32_t* smeta,
+__device__ __forceinline__ int grid_sort(const orbx_keypoint* k, int n, float minX, float minY, float invW, float invH, float2* sxy, uint32_t* smeta,
                                          int* soff, int lane) {
   for (int i = lane; i <= kGridCells; i += 32) soff[i] = 0;
   __syncwarp();
   for (int i = lane; i < n; i += 32) {
-    const int gx = (int)roundf(__fmul_rn(k[i].x, invW)), gy = (int)roundf(__fmul_rn(k[i].y, invH));
+    const int gx = (int)roundf(__fmul_rn(__fsub_rn(k[i].x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(k[i].y, minY), invH));
     if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) atomicAdd(&soff[gx * 48 + gy + 1], 1);
   }
   __syncwarp();
@@ -385,7 +386,7 @@ __device__ __forceinline__ int grid_sort(const orbx_keypoint* k, int n, float in
   // fill each cell from its end downwards: afterwards soff[c+1] = start of cell c
   for (int i = lane; i < n; i += 32) {
     const orbx_keypoint kp = k[i];
-    const int gx = (int)roundf(__fmul_rn(kp.x, invW)), gy = (int)roundf(__fmul_rn(kp.y, invH));
+    const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));
     if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) {
       const int c = gx * 48 + gy;
       const int pos = atomicSub(&soff[c + 1], 1) - 1;
@@ -412,7 +413,8 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
   const size_t mo = (size_t)p * a.mcap;
 
   for (int i = lane; i < n; i += 32) assigned[i] = -1;
-  const int n_in_grid = grid_sort(k, n, a.invW, a.invH, sxy, smeta, soff, lane);
+  const float minX = a.gb[0], minY = a.gb[2], invW = a.gb[4], invH = a.gb[5];
+  const int n_in_grid = grid_sort(k, n, minX, minY, invW, invH, sxy, smeta, soff, lane);
   const int* cstart = soff + 1;                                         // cell c = [cstart[c], cstart[c+1]); the last cell ends at n_in_grid
 
   int nm = 0;
@@ -423,13 +425,14 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
     if (a.th != 1.0f) r = __fmul_rn(r, a.th);
     const float R = __fmul_rn(r, a.scale[lvl]);
     const float x = a.projX[mo + iMP], y = a.projY[mo + iMP];
-    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(x, R), a.invW)));
+    // GetFeaturesInArea's cell window, src/Frame.cc:332-346: (x - mnMinX -+ r) * inv, left to right
+    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, minX), R), invW)));
     if (cx0 >= 64) continue;
-    const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(x, R), a.invW)));
+    const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, minX), R), invW)));
     if (cx1 < 0) continue;
-    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(y, R), a.invH)));
+    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, minY), R), invH)));
     if (cy0 >= 48) continue;
-    const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(y, R), a.invH)));
+    const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, minY), R), invH)));
     if (cy1 < 0) continue;
     const float xr = a.projXR[mo + iMP];
     uint32_t q[8];
@@ -509,7 +512,8 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
 
   for (int i = lane; i < n; i += 32) assigned[i] = -1;
   if (lane < kHisto) s_hist[lane] = 0;
-  const int n_in_grid = grid_sort(k, n, a.invW, a.invH, sxy, smeta, soff, lane);
+  const float minX = a.gb[0], maxX = a.gb[1], minY = a.gb[2], maxY = a.gb[3], invW = a.gb[4], invH = a.gb[5];
+  const int n_in_grid = grid_sort(k, n, minX, minY, invW, invH, sxy, smeta, soff, lane);
   const int* cstart = soff + 1;
 
   int nm = 0;
@@ -523,18 +527,18 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
     const float invzc = (float)(1.0 / (double)c3[2]);
     if (invzc < 0.f) continue;
     const float u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, c3[0]), invzc), a.cx), v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, c3[1]), invzc), a.cy);
-    if (u < 0.f || u > a.cols || v < 0.f || v > a.rows) continue;
+    if (u < minX || u > maxX || v < minY || v > maxY) continue;                        // src/ORBmatcher.cc:1373-1376
     if (!(u == u) || !(v == v)) continue;                                              // NaN never passes the reference's window either
     const int oct = min(max(a.lastOctave[lo + i], 0), a.nlevels - 1);
     const float R = __fmul_rn(a.th, a.scale[oct]);
     const int l_lo = mode == 1 ? oct : (mode == 2 ? 0 : oct - 1), l_hi = mode == 1 ? 99 : (mode == 2 ? oct : oct + 1);
-    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(u, R), a.invW)));
+    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, minX), R), invW)));
     if (cx0 >= 64) continue;
-    const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(u, R), a.invW)));
+    const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, minX), R), invW)));
     if (cx1 < 0) continue;
-    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(v, R), a.invH)));
+    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, minY), R), invH)));
     if (cy0 >= 48) continue;
-    const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(v, R), a.invH)));
+    const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, minY), R), invH)));
     if (cy1 < 0) continue;
     const float ur_pred = __fsub_rn(u, __fmul_rn(a.bf, invzc));
     uint32_t q[8];
@@ -1037,10 +1041,13 @@ extern "C" orbx_status orbx_knn_ratio_noalloc(const uint8_t* descA, const float*
   using namespace orbx;
   if (!descA || !angA || !descB || !angB || !matches12 || !n_matches) return set_error(ORBX_ERR_BAD_ARG, "null argument");
   if (nA < 0 || nB < 0) return set_error(ORBX_ERR_BAD_ARG, "negative feature count");
+  // a best distance of 256 is the "no candidate" value of the scan and must never pass the threshold
+  if (th < 0 || th > 255) return set_error(ORBX_ERR_BAD_ARG, "th must be 0..255 (the reference passes TH_LOW = 50)");
   if (nA > kNoAllocMax || nB > kNoAllocMax)
     return set_error(ORBX_ERR_CAPACITY, "orbx_knn_ratio_noalloc handles at most 4096 features per side (fixed static scratch)");
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return set_error(ORBX_ERR_CUDA, "cudaGetDevice failed");
+  if (cudaGetDevice(&dev) != cudaSuccess) return set_error(ORBX_ERR_CUDA, "cudaGetDevice failed");
+  if (dev < 0 || dev >= 64) return set_error(ORBX_ERR_CAPACITY, "orbx_knn_ratio_noalloc keeps its per-device set-up for device indices 0..63 only");
   const int capPad = (kNoAllocMax + 31) & ~31;
   const size_t smem = (size_t)capPad * 32;
   if (!g_knn_static_addr[dev]) {   // one-time set-up for this device: allocates nothing, but must precede stream capture

@@ -227,12 +227,15 @@ __global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int firs
     }
     __syncthreads();
     // rank by (size desc, list position asc) == the reference's sort() walked from the back.
-    // One packed key per open node, size << 16 | (0xFFFF - position) (0 for the others; a level holds far fewer
-    // than 65536 keys and nodes): rank = number of larger keys, read two at a time
+    // One packed key per open node, size << 16 | (0xFFFF - position) (0 for the others): rank = number of larger
+    // keys, read two at a time.  Positions are < node_cap <= 3072; a node's size fits 16 bits whenever the level
+    // has fewer than 65536 candidates (`packed`, CTA-uniform).  A level with more (a multi-megapixel image of
+    // dense texture) ranks on the unpacked sizes with the position as the tie-break: slower, same order.
+    const bool packed = nkeys < 65536;
     unsigned* rkey = reinterpret_cast<unsigned*>(a5);            // a5 is free until the survivor scan below
     for (int i = tid; i < ((C + 1) & ~1); i += kOctThreads) {   // padded to an even count
       const int ci = i < C ? cnt[cur][i] : 0;
-      rkey[i] = ci > 1 ? ((unsigned)ci << 16) | (unsigned)(0xFFFF - i) : 0u;
+      rkey[i] = ci > 1 ? (packed ? ((unsigned)ci << 16) | (unsigned)(0xFFFF - i) : (unsigned)ci) : 0u;
     }
     __syncthreads();
     int my_m = 0;
@@ -242,9 +245,13 @@ __global__ void __launch_bounds__(kOctThreads) k_octree(DeviceLayout L, int firs
       if (ci > 1) {
         rank = 0;
         const unsigned mk = rkey[i];
-        for (int j = 0; j < C; j += 2) {
-          const uint2 kj = *reinterpret_cast<const uint2*>(rkey + j);
-          rank += (kj.x > mk) + (kj.y > mk);
+        if (packed) {
+          for (int j = 0; j < C; j += 2) {
+            const uint2 kj = *reinterpret_cast<const uint2*>(rkey + j);
+            rank += (kj.x > mk) + (kj.y > mk);
+          }
+        } else {
+          for (int j = 0; j < C; ++j) rank += (rkey[j] > mk) || (rkey[j] == mk && j < i);
         }
         int nch = 0;
         for (int q = 0; q < 4; ++q) nch += cc[4 * i + q] > 0;

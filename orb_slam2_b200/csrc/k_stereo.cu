@@ -107,7 +107,8 @@ __global__ void __launch_bounds__(kStWarps * 32, 24) k_stereo_match(StereoArgs a
   uint8_t* rp = lp + 144;               // 11x21 right strip, pitch 24
   do {                                  // one pass; "continue" = this keypoint has no stereo match
     const size_t oi = (size_t)img * a.cap + iL;
-    if (lane == 0) { a.uRight[oi] = -1.f; a.depth[oi] = -1.f; a.sad[oi] = -1; }
+    const size_t si = (size_t)img * a.L.kp_cap + iL;      // the SAD scratch belongs to the left handle: its own pitch, not the caller's
+    if (lane == 0) { a.uRight[oi] = -1.f; a.depth[oi] = -1.f; a.sad[si] = -1; }
     const float uL = kL[iL].x, vL = kL[iL].y;
     const int lvl = kL[iL].octave;
     const int row = (int)vL;
@@ -219,7 +220,7 @@ __global__ void __launch_bounds__(kStWarps * 32, 24) k_stereo_match(StereoArgs a
     float disp = __fsub_rn(uL, bestu);
     if (disp >= 0.f && disp < a.maxD) {
       if (disp <= 0.f) { disp = 0.01f; bestu = (float)((double)uL - 0.01); }
-      if (lane == 0) { a.depth[oi] = __fdiv_rn(a.bf, disp); a.uRight[oi] = bestu; a.sad[oi] = bestSad; }
+      if (lane == 0) { a.depth[oi] = __fdiv_rn(a.bf, disp); a.uRight[oi] = bestu; a.sad[si] = bestSad; }
     }
   } while (false);
 }
@@ -233,17 +234,17 @@ __global__ void __launch_bounds__(kMedThreads) k_stereo_median(StereoArgs a) {
   __shared__ int s_tot;
   const int img = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nL = a.L.nkp[a.slotL0 + img];
-  const size_t base = (size_t)img * a.cap;
+  const size_t base = (size_t)img * a.cap, sbase = (size_t)img * a.L.kp_cap;
   // up to 4 values per thread in registers (kp_cap <= 4096 for any accepted configuration is not
   // guaranteed, so the tail is re-read from memory in the rare larger case)
   int v[4];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) { const int i = tid + q * kMedThreads; v[q] = i < nL ? a.sad[base + i] : -1; }
+  for (int q = 0; q < 4; ++q) { const int i = tid + q * kMedThreads; v[q] = i < nL ? a.sad[sbase + i] : -1; }
   auto block_count = [&](int limit) {      // #(0 <= SAD <= limit) over the whole frame
     int c = 0;
 #pragma unroll
     for (int q = 0; q < 4; ++q) c += (v[q] >= 0 && v[q] <= limit);
-    for (int i = tid + 4 * kMedThreads; i < nL; i += kMedThreads) { const int s = a.sad[base + i]; c += (s >= 0 && s <= limit); }
+    for (int i = tid + 4 * kMedThreads; i < nL; i += kMedThreads) { const int s = a.sad[sbase + i]; c += (s >= 0 && s <= limit); }
     c = __reduce_add_sync(0xffffffffu, c);
     if (lane == 0) s_part[warp] = c;
     __syncthreads();
@@ -267,7 +268,7 @@ __global__ void __launch_bounds__(kMedThreads) k_stereo_median(StereoArgs a) {
   const float th = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)lo);
   int kept = 0;
   for (int i = tid; i < nL; i += kMedThreads) {
-    const int s = a.sad[base + i];
+    const int s = a.sad[sbase + i];
     if (s < 0) continue;
     if ((float)s < th) ++kept;
     else { a.uRight[base + i] = -1.f; a.depth[base + i] = -1.f; }

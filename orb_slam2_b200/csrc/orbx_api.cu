@@ -644,12 +644,12 @@ struct Staged {
 extern "C" {
 
 orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* desc1, const int* n1, const orbx_keypoint* kps2,
-                                   const uint8_t* desc2, const int* n2, int n_pairs, int cap, int cols, int rows, float* prev_xy,
+                                   const uint8_t* desc2, const int* n2, int n_pairs, int cap, const float* grid_bounds, float* prev_xy,
                                    float nnratio, int window, int check_orientation, int* matches12, int* n_matches,
                                    int on_device, void* stream) {
-  if (!kps1 || !desc1 || !n1 || !kps2 || !desc2 || !n2 || !prev_xy || !matches12 || !n_matches)
+  if (!kps1 || !desc1 || !n1 || !kps2 || !desc2 || !n2 || !grid_bounds || !prev_xy || !matches12 || !n_matches)
     return fail(ORBX_ERR_BAD_ARG, "null argument");
-  if (n_pairs < 1 || cap < 1 || cap > 65535 || cols < 1 || rows < 1 || window < 0) return fail(ORBX_ERR_BAD_ARG, "bad sizes");
+  if (n_pairs < 1 || cap < 1 || cap > 65535 || window < 0) return fail(ORBX_ERR_BAD_ARG, "bad sizes");
   cudaStream_t st = (cudaStream_t)stream;
   Staged sg(st);
   const size_t np = (size_t)n_pairs, pc = np * cap;
@@ -663,7 +663,7 @@ orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* des
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
   CU(sg.alloc((void**)&a.scratch, pc * 4 * sizeof(int)));
   a.n_pairs = n_pairs; a.cap = cap;
-  a.invW = 64.0f / (float)cols; a.invH = 48.0f / (float)rows;   // src/Frame.cc:212-213 (mnMinX = 0, mnMaxX = cols)
+  CU(sg.in(grid_bounds, 6, on_device, &a.gb));                  // Frame 2's bounds and inverse cell sizes, src/Frame.cc:207-213
   a.ratio = nnratio; a.window = (float)window; a.checkOri = check_orientation;
   g_launches += launch_search_init(a, st);
   CU(cudaGetLastError());
@@ -1123,16 +1123,16 @@ orbx_status orbx_features_in_area_batch(const orbx_keypoint* kps_un, const int* 
 }
 
 orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right, const int* n,
-                                         int n_frames, int cap, int cols, int rows, const float* scale_factors, int nlevels,
+                                         int n_frames, int cap, const float* grid_bounds, const float* scale_factors, int nlevels,
                                          const uint8_t* mp_in_view, const float* mp_proj_x, const float* mp_proj_y,
                                          const float* mp_proj_xr, const int* mp_level, const float* mp_view_cos,
                                          const uint8_t* mp_desc, const int* mp_obs, const int* m, int mcap, float th,
                                          float nnratio, int* frame_obs, int* assigned, int* n_matches, int on_device,
                                          void* stream) {
-  if (!kps || !desc || !u_right || !n || !scale_factors || !mp_in_view || !mp_proj_x || !mp_proj_y || !mp_proj_xr || !mp_level ||
+  if (!kps || !desc || !u_right || !n || !grid_bounds || !scale_factors || !mp_in_view || !mp_proj_x || !mp_proj_y || !mp_proj_xr || !mp_level ||
       !mp_view_cos || !mp_desc || !mp_obs || !m || !frame_obs || !assigned || !n_matches)
     return fail(ORBX_ERR_BAD_ARG, "null argument");
-  if (n_frames < 1 || cap < 1 || cap > 8192 || mcap < 1 || cols < 1 || rows < 1 || nlevels < 1 || nlevels > kMaxLevels)
+  if (n_frames < 1 || cap < 1 || cap > 8192 || mcap < 1 || nlevels < 1 || nlevels > kMaxLevels)
     return fail(ORBX_ERR_BAD_ARG, "bad sizes (cap <= 8192, nlevels <= 8)");
   cudaStream_t st = (cudaStream_t)stream;
   Staged sg(st);
@@ -1149,7 +1149,7 @@ orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t
   if (on_device) { a.assigned = assigned; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.assigned, fc * 4)); CU(sg.alloc((void**)&a.nm, nf * 4)); }
   a.n_pairs = n_frames; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels;
-  a.invW = 64.0f / (float)cols; a.invH = 48.0f / (float)rows; a.th = th; a.ratio = nnratio;
+  CU(sg.in(grid_bounds, 6, on_device, &a.gb)); a.th = th; a.ratio = nnratio;
   for (int i = 0; i < kMaxLevels; ++i) a.scale[i] = 1.f;
   if (on_device) CU(cudaMemcpyAsync(a.scale, scale_factors, sizeof(float) * nlevels, cudaMemcpyDeviceToHost, st));
   else std::memcpy(a.scale, scale_factors, sizeof(float) * nlevels);
@@ -1166,16 +1166,16 @@ orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t
 }
 
 orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const uint8_t* desc, const float* u_right, const int* n,
-                                               int n_frames, int cap, int cols, int rows, const float* scale_factors, int nlevels,
+                                               int n_frames, int cap, const float* grid_bounds, const float* scale_factors, int nlevels,
                                                const float* pose, const int* mode, float fx, float fy, float cx, float cy, float bf,
                                                const uint8_t* last_valid, const float* last_xw, const int* last_octave,
                                                const float* last_angle, const uint8_t* mp_desc, const int* mp_obs, const int* n_last,
                                                int lcap, float th, int check_orientation, int* frame_obs, int* assigned,
                                                int* n_matches, int on_device, void* stream) {
-  if (!kps || !desc || !u_right || !n || !scale_factors || !pose || !mode || !last_valid || !last_xw || !last_octave || !last_angle ||
+  if (!kps || !desc || !u_right || !n || !grid_bounds || !scale_factors || !pose || !mode || !last_valid || !last_xw || !last_octave || !last_angle ||
       !mp_desc || !mp_obs || !n_last || !frame_obs || !assigned || !n_matches)
     return fail(ORBX_ERR_BAD_ARG, "null argument");
-  if (n_frames < 1 || cap < 1 || cap > 8192 || lcap < 1 || cols < 1 || rows < 1 || nlevels < 1 || nlevels > kMaxLevels)
+  if (n_frames < 1 || cap < 1 || cap > 8192 || lcap < 1 || nlevels < 1 || nlevels > kMaxLevels)
     return fail(ORBX_ERR_BAD_ARG, "bad sizes (cap <= 8192, nlevels <= 8)");
   cudaStream_t st = (cudaStream_t)stream;
   Staged sg(st);
@@ -1193,7 +1193,7 @@ orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const u
   else { CU(sg.alloc((void**)&a.assigned, fc * 4)); CU(sg.alloc((void**)&a.nm, nf * 4)); }
   CU(sg.alloc((void**)&a.events, fl * 4));
   a.n_pairs = n_frames; a.cap = cap; a.lcap = lcap; a.nlevels = nlevels; a.checkOri = check_orientation;
-  a.invW = 64.0f / (float)cols; a.invH = 48.0f / (float)rows; a.cols = (float)cols; a.rows = (float)rows;
+  CU(sg.in(grid_bounds, 6, on_device, &a.gb));
   a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = bf; a.th = th;
   for (int i = 0; i < kMaxLevels; ++i) a.scale[i] = 1.f;
   if (on_device) { CU(cudaMemcpyAsync(a.scale, scale_factors, sizeof(float) * nlevels, cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }

@@ -100,7 +100,7 @@ int launch_stereo(const StereoArgs& a, cudaStream_t st, cudaEvent_t ev_mid);
 struct InitMatchArgs {
   const orbx_keypoint* k1; const uint8_t* d1; const int* n1;
   const orbx_keypoint* k2; const uint8_t* d2; const int* n2;
-  int n_pairs, cap; float invW, invH; float* prev; float ratio; float window; int checkOri;
+  int n_pairs, cap; const float* gb; float* prev; float ratio; float window; int checkOri;   // gb: device, Frame 2's {mnMinX, mnMaxX, mnMinY, mnMaxY, invW, invH}
   int* m12; int* nm;
   int* scratch;  // per pair: cap ints (matched distance) + cap ints (matches21) + cap ints (grid order)
 };
@@ -120,7 +120,8 @@ struct ProjArgs {
   const uint8_t* inView; const float* projX; const float* projY; const float* projXR;  // map-point side, [P][mcap]
   const int* level; const float* viewCos; const uint8_t* mpDesc; const int* mpObs; const int* m;
   int n_pairs, cap, mcap, nlevels;
-  float invW, invH, th, ratio;
+  const float* gb;            // device: the Frame's {mnMinX, mnMaxX, mnMinY, mnMaxY, invW, invH}
+  float th, ratio;
   float scale[kMaxLevels];
   int* frameObs; int* assigned; int* nm;
 };
@@ -133,7 +134,8 @@ struct ProjFrameArgs {
   const float* pose;          // [P][12]: Rcw row-major (9) then tcw (3)
   const int* mode;            // [P]: 0 neither, 1 forward, 2 backward
   int n_pairs, cap, lcap, nlevels, checkOri;
-  float invW, invH, cols, rows, fx, fy, cx, cy, bf, th;
+  const float* gb;            // device: the current Frame's {mnMinX, mnMaxX, mnMinY, mnMaxY, invW, invH}
+  float fx, fy, cx, cy, bf, th;
   float scale[kMaxLevels];
   int* frameObs; int* assigned; int* nm;
   int* events;                // scratch [P][lcap]: bin<<16 | keypoint index per accepted match

@@ -32,3 +32,27 @@ def build(oracle, case):
            for f, s, p in ((frames[0], 0, gs.KF_PARAMS["pct1"]), (frames[1], 1, gs.KF_PARAMS["pct2"]))]
     return dict(cfg=cfg, F1=frames[0], F2=frames[1], node1=node[0], node2=node[1], has1=has[0], has2=has[1], fx=fx, T2=T2, F12=F12,
                 scale=tb["scale"], sigma2=tb["sigma2"], cam=gs.KITTI_CAM)
+
+
+GOLD_DIST = json.load(open(os.path.join(HERE, "golden", "ref_dist.json")))
+
+
+def build_dist(extract_stereo, undistort, case):
+    """Inputs of a tests/golden/ref_kfd_*.npz case (a DISTORTED stereo camera: Frame::mnMinX / mnMinY < 0).
+    extract_stereo(L, R) -> dict(keys, desc, u_right, depth); undistort(cam, keys, w, h) -> (keys_un, bounds6).
+    Returns what SearchByProjection(Frame, MapPoints) and SearchByProjection(Current, Last) read."""
+    cfg = synth.KITTI
+    w, h = cfg["w"], cfg["h"]
+    ims, _, _, T2, _ = gs.kf_case_inputs(case["seed"], case["L"])
+    fx = np.load(os.path.join(HERE, "golden", case["fixture"]))
+    F1, F2 = extract_stereo(ims[0], ims[1]), extract_stereo(ims[2], ims[3])
+    for F in (F1, F2):
+        F["keys_un"], F["bounds"] = undistort(case["cam"], F["keys"], w, h)
+    mp, tr = fx["mps1"], fx["track"]
+    mpd = dict(inview=tr["inview"].astype(np.uint8), projx=tr["projx"], projy=tr["projy"], projxr=tr["projxr"], level=tr["level"], viewcos=tr["viewcos"],
+               desc=mp["desc"], obs=mp["obs"])
+    n1 = len(F1["keys"])
+    last = dict(valid=fx["has1"], xw=np.zeros((n1, 3), np.float32), octave=F1["keys"]["octave"], angle=F1["keys_un"]["angle"], desc=np.zeros((n1, 32), np.uint8),
+                obs=np.zeros(n1, np.int32))
+    last["xw"][mp["idx"]] = mp["xw"]; last["desc"][mp["idx"]] = mp["desc"]; last["obs"][mp["idx"]] = mp["obs"]
+    return dict(cfg=cfg, F1=F1, F2=F2, fx=fx, T2=T2, mpd=mpd, last=last, cam=tuple(case["cam"][:4]))

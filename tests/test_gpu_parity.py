@@ -814,3 +814,78 @@ def test_cuda_fuse_and_sim3_reproduce_reference(gx):
         n, a = gx.ORBmatcher(0.9, case["check_ori"]).SearchByProjectionOrdered(FG, 1, d2, (0.0, float(w), 0.0, float(h)), R2, t2, fx["reloc_Ow"], gs.KITTI_CAM, scale,
                                                                                  float(fx["log_scale"]), occ, mpr, 10.0, 100, True)
         assert n == case["n_proj_kf"] and np.array_equal(a, np.where(fx["proj_kf"] >= 0, fx["proj_kf"], -1))
+
+
+def test_stereo_direct_device_outputs_wider_than_kp_cap(gx, oracle):
+    """Two handles (n == max_batch) writing uRight / depth straight into DEVICE buffers whose row pitch is larger than
+    orbx_max_keypoints() (a caller rounding 2024 up to 2048): the SAD scratch of the left handle keeps its own pitch."""
+    import torch
+    cfg = synth.EUROC
+    w, h, nf, n = cfg["w"], cfg["h"], cfg["nfeatures"], 3
+    pairs = [synth.stereo_pair(70 + i, w, h) for i in range(n)]
+    GL, GR = _ext(gx, w, h, nf, batch=n), _ext(gx, w, h, nf, batch=n)
+    GL.extract_batch(np.stack([p[0] for p in pairs])); GR.extract_batch(np.stack([p[1] for p in pairs]))
+    cap = GL.kp_cap + 24
+    guard = 4096
+    buf = torch.full((3, n * cap + guard), -7.0, dtype=torch.float32, device="cuda")      # guard floats behind each output
+    ur, dp = buf[0, :n * cap].view(n, cap), buf[1, :n * cap].view(n, cap)
+    nm = torch.zeros(n, dtype=torch.int32, device="cuda")
+    gx.ComputeStereoMatches(GL, GR, cfg["bf"], cfg["fx"], n=n, out=(ur, dp, nm))
+    torch.cuda.synchronize()
+    assert bool((buf[:, n * cap:] == -7.0).all()), "wrote past the caller's buffers"
+    ur, dp, nm = ur.cpu().numpy(), dp.cpu().numpy(), nm.cpu().numpy()
+    resL = GL.fetch(0, n)
+    for i in range(n):
+        EL, ER = oracle.Extractor(nf), oracle.Extractor(nf)
+        kl, dl = EL.extract(pairs[i][0]); kr, dr = ER.extract(pairs[i][1])
+        assert resL[i][0].tobytes() == kl.tobytes()
+        rur, rdp, _, rm = oracle.stereo(EL, ER, kl, dl, kr, dr, cfg["bf"], cfg["fx"])
+        assert int(nm[i]) == rm and rm > 50
+        assert np.array_equal(ur[i, :len(kl)].view(np.uint32), rur.view(np.uint32)) and np.array_equal(dp[i, :len(kl)].view(np.uint32), rdp.view(np.uint32))
+
+
+def test_cuda_searches_on_distorted_cameras_reproduce_reference(gx):
+    """K6 / K8 / K9 on cameras WITH distortion (Frame::mnMinX / mnMinY != 0) against tests/golden/ref_dist.json and
+    ref_kfd_*.npz, which the reference's own Frame.cc / ORBmatcher.cc wrote (tools/gen_golden_dist.py): undistorted keypoints
+    (K10), SearchForInitialization, SearchByProjection(Frame, MapPoints), SearchByProjection(Current, Last)."""
+    import importlib.util
+    here = os.path.dirname(__file__)
+    spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(here, "kf_cases.py"))
+    kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    for case in kc.GOLD_DIST["init"]:
+        a, b, _ = synth.mono_pair(case["seed"], 640, 480)
+        G = _ext(gx, 640, 480, 1000)
+        k1, d1 = G(a); k2, d2 = G(b)
+        FG = gx.FrameGrids([k1, k2], case["cam"], 640, 480)
+        ku1, ku2 = FG.mvKeysUn
+        assert sha(ku2) == case["keys_un2_sha256"] and FG.bounds[0] != 0.0
+        prev = np.stack([ku1["x"], ku1["y"]], 1).astype(np.float32)
+        n, m12 = gx.ORBmatcher(case["ratio"], case["check_ori"]).SearchForInitialization(gx.Frame(ku1, d1, 640, 480, FG.bounds), gx.Frame(ku2, d2, 640, 480, FG.bounds),
+                                                                                         prev, case["window"])
+        assert n == case["nmatches"] and sha(m12.astype(np.int32)) == case["matches12_sha256"] and sha(prev) == case["prev_sha256"]
+    cfg = synth.KITTI
+    w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
+    for case in kc.GOLD_DIST["kf"]:
+        def extract_stereo(L, R):
+            G = _ext(gx, w, h, nf, batch=2)
+            G.extract_batch(np.stack([L, R]))
+            ur, dp, _ = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=1, slotL0=0, slotR0=1)
+            (kl, dl), _ = G.fetch(0, 2)
+            return dict(keys=kl, desc=dl, u_right=ur[0, :len(kl)].copy(), depth=dp[0, :len(kl)].copy())
+
+        def undistort(cam, k, w_, h_):
+            FG = gx.FrameGrids([k], cam, w_, h_)
+            return FG.mvKeysUn[0], FG.bounds.copy()
+
+        c = kc.build_dist(extract_stereo, undistort, case)
+        F1, F2, fx, T2 = c["F1"], c["F2"], c["fx"], c["T2"]
+        assert sha(F1["keys_un"]) == case["keys_un1_sha256"] and sha(F2["keys_un"]) == case["keys_un2_sha256"] and sha(F2["u_right"]) == case["u_right2_sha256"]
+        scale = np.asarray(_ext(gx, w, h, nf).GetScaleFactors(), np.float32)
+        Fc = gx.Frame(F2["keys_un"], F2["desc"], w, h, F2["bounds"])
+        P = kc.gs.KF_PARAMS
+        n, a, _ = gx.ORBmatcher(0.8, True).SearchByProjection(Fc, F2["u_right"], scale, c["mpd"], P["th_proj"])
+        assert n == case["n_proj"] and np.array_equal(a, fx["proj"])
+        n, a, _ = gx.ORBmatcher(0.9, case["check_ori"]).SearchByProjectionFrame(Fc, F2["u_right"], scale, T2[:3, :3], T2[:3, 3], c["cam"] + (cfg["bf"],), c["last"],
+                                                                               P["th_last"], 0)
+        assert n == case["n_proj_last"] and np.array_equal(a, fx["proj_last"])

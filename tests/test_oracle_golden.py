@@ -9,6 +9,8 @@ import os
 import numpy as np
 import pytest
 
+from conftest import missing_reference_binary
+
 from orb_slam2_b200 import synth
 
 GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "ref_extract.json")))
@@ -28,7 +30,7 @@ def test_oracle_matches_reference_golden(oracle, case):
 
 def test_oracle_matches_reference_binary(oracle):
     if not oracle.ref_available():
-        pytest.skip("oracle/_ref/orbref not built (needs /root/reference: make -C oracle ref)")
+        missing_reference_binary("oracle/_ref/orbref")
     for w, h, nf in [(1241, 376, 2000), (640, 480, 1000)]:
         imgs = np.stack([synth.synth_image(900 + i, w, h) for i in range(2)])
         ref, _ = oracle.ref_extract(imgs, nf)
@@ -141,7 +143,7 @@ def test_oracle_bow_transform_matches_reference_golden(oracle, case):
 
 def test_oracle_bow_transform_matches_reference_binary(oracle):
     if not oracle.ref_dbow_available():
-        pytest.skip("oracle/_ref/orbref_dbow not built (needs /root/reference: make -C oracle ref)")
+        missing_reference_binary("oracle/_ref/orbref_dbow")
     for seed, k, L, levelsup, scoring, weighting, norm in [(31, 10, 3, 2, 0, 0, 1), (32, 7, 4, 4, 1, 1, 2), (33, 9, 3, 1, 5, 2, 0)]:
         V = synth.vocabulary(seed, k, L, stop_fraction=0.1)
         D = _gb.descriptors(seed, V, 900)
@@ -199,7 +201,7 @@ def test_oracle_frame_grid_matches_reference_golden(oracle, case):
 
 def test_oracle_matches_reference_slam_binary(oracle):
     if not oracle.ref_slam_available():
-        pytest.skip("oracle/_ref/orbref_slam not built (needs /root/reference: make -C oracle ref)")
+        missing_reference_binary("oracle/_ref/orbref_slam")
     cfg = synth.KITTI
     L, R, _ = synth.stereo_pair(41, cfg["w"], cfg["h"])
     F = oracle.ref_slam_stereo(L, R, cfg["nfeatures"], _gs.KITTI_CAM, cfg["bf"])
@@ -346,3 +348,46 @@ def test_oracle_remaining_matcher_members_match_reference(oracle, case):
                                  dict(valid=mpd["valid"], xw=mp1["xw"], normal=mp1["normal"], dmin=mp1["dmin"], dmax=mp1["dmax"], desc=mp1["desc"]), 4.0, 2 | 4 | 16, 50)
     assert int((best >= 0).sum()) == case["n_fuse_scw"] and np.array_equal(best, fx["fuse_scw"])
     assert min(case["n_proj_scw"], case["n_proj_kf"], case["n_fuse_scw"]) > 50
+
+
+# ---- distorted cameras: Frame::mnMinX / mnMinY != 0 (tests/golden/ref_dist.json, written by the reference compiled in place) ----
+@pytest.mark.parametrize("case", _kc.GOLD_DIST["init"], ids=lambda c: f"init{c['seed']}")
+def test_oracle_search_init_distorted_camera(oracle, case):
+    """SearchForInitialization on TUM1 WITH its distortion: the grid of frame 2 is laid over the undistorted image bounds."""
+    a, b, _ = synth.mono_pair(case["seed"], 640, 480)
+    E = oracle.Extractor(1000)
+    (k1, d1), (k2, d2) = E.extract(a), E.extract(b)
+    ku1, bnd, _, _ = oracle.undistort_grid(case["cam"], k1, 640, 480)
+    ku2 = oracle.undistort_grid(case["cam"], k2, 640, 480)[0]
+    assert bnd[0] != 0.0 and bnd[2] != 0.0 and _sha(ku2) == case["keys_un2_sha256"]
+    prev = np.stack([ku1["x"], ku1["y"]], 1).astype(np.float32)
+    m12, n, prev = oracle.search_init(ku1, d1, ku2, d2, 640, 480, prev, case["ratio"], case["window"], case["check_ori"], bounds=bnd)
+    assert n == case["nmatches"] and _sha(m12) == case["matches12_sha256"] and _sha(prev) == case["prev_sha256"]
+    assert n > 50
+
+
+@pytest.mark.parametrize("case", _kc.GOLD_DIST["kf"], ids=lambda c: f"kfd{c['seed']}")
+def test_oracle_projection_searches_distorted_camera(oracle, case):
+    """SearchByProjection(Frame, MapPoints) :45 and SearchByProjection(Current, Last) :1328 of the reference on a distorted
+    stereo camera (mnMinX = -64, mnMinY = -22: 35 keypoints have negative undistorted x)."""
+    cfg = synth.KITTI
+
+    def extract_stereo(L, R):
+        EL, ER = oracle.Extractor(cfg["nfeatures"]), oracle.Extractor(cfg["nfeatures"])
+        kl, dl = EL.extract(L); kr, dr = ER.extract(R)
+        ur, dp, _, _ = oracle.stereo(EL, ER, kl, dl, kr, dr, cfg["bf"], cfg["fx"])
+        return dict(keys=kl, desc=dl, u_right=ur, depth=dp)
+
+    c = _kc.build_dist(extract_stereo, lambda cam, k, w, h: oracle.undistort_grid(cam, k, w, h)[:2], case)
+    F1, F2, fx, T2 = c["F1"], c["F2"], c["fx"], c["T2"]
+    w, h = cfg["w"], cfg["h"]
+    assert _sha(F1["keys_un"]) == case["keys_un1_sha256"] and _sha(F2["keys_un"]) == case["keys_un2_sha256"] and _sha(F2["u_right"]) == case["u_right2_sha256"]
+    b = F2["bounds"]
+    assert [float(int(v)) for v in b[:4]] == fx["kf_bounds"].tolist() and int((F2["keys_un"]["x"] < 0).sum()) == case["negative_x"] > 0
+    scale = oracle.Extractor(cfg["nfeatures"]).tables()["scale"]
+    P = _kc.gs.KF_PARAMS
+    a, n, _ = oracle.search_projection(F2["keys_un"], F2["desc"], F2["u_right"], w, h, scale, c["mpd"], P["th_proj"], 0.8, bounds=b)
+    assert n == case["n_proj"] and np.array_equal(a, fx["proj"])
+    a, n, _ = oracle.search_projection_frame(F2["keys_un"], F2["desc"], F2["u_right"], w, h, scale, T2[:3, :3], T2[:3, 3], c["cam"] + (cfg["bf"],), c["last"],
+                                             P["th_last"], 0, case["check_ori"], bounds=b)
+    assert n == case["n_proj_last"] and np.array_equal(a, fx["proj_last"])

@@ -9,6 +9,8 @@ import os
 import numpy as np
 import pytest
 
+from conftest import missing_reference_binary
+
 from orb_slam2_b200 import synth
 
 pytestmark = pytest.mark.gpu
@@ -33,7 +35,7 @@ def _same(a, b, path=""):
 def both(oracle):
     gpu_bin = os.path.join(os.path.dirname(oracle.REF_SLAM_BIN), "orbref_slam_gpu")
     if not (oracle.ref_slam_available() and os.path.exists(gpu_bin)):
-        pytest.skip("oracle/_ref/orbref_slam(_gpu) not built (make -C oracle ref, needs /root/reference)")
+        missing_reference_binary("oracle/_ref/orbref_slam(_gpu)")
     ref_bin = oracle.REF_SLAM_BIN
 
     def run(fn, *args, **kw):

@@ -1,5 +1,7 @@
 """The allocation-free brute-force matcher (orbx_knn_ratio_noalloc) against the regular batched
-entry point (orbx_knn_ratio_batch), both called through the C ABI.
+entry point (orbx_knn_ratio_batch), both called through the C ABI, and against the CPU oracle's
+restatement of the reference loop (oracle.knn_ratio), so that a fault the two kernels shared would
+still show.
 
 Some users of this library may not allocate device memory while matching: a tracking thread on a
 frame deadline cannot risk the device-wide lock behind cudaMalloc/cudaFree, and a process that
@@ -65,7 +67,7 @@ def _noalloc(lib, torch, dA, angA, dB, angB, th, ratio, ori, strict):
     return m12.cpu().numpy()[:nA], int(nm.cpu()[0])
 
 
-def test_noalloc_matches_regular_entry_point_twice_in_a_row():
+def test_noalloc_matches_regular_entry_point_twice_in_a_row(oracle):
     import torch
     assert torch.cuda.is_available()
     from orb_slam2_b200 import api
@@ -79,6 +81,8 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
         got_m, got_n = _noalloc(lib, torch, dA, angA, dB, angB, th, ratio, ori, strict)
         assert got_n == ref_n
         assert np.array_equal(got_m, ref_m)
+        cpu_m, cpu_n = oracle.knn_ratio(dA, angA, dB, angB, th, ratio, ori, strict)      # src/ORBmatcher.cc:522-655, one bucket
+        assert got_n == cpu_n and np.array_equal(got_m, cpu_m)
         assert ref_n > 50                      # the comparison is not vacuous
     # same input again: identical output although the scratch now holds its own stale state
     (dA, angA, dB, angB), th, ratio, ori, strict = cases[0]
@@ -96,6 +100,10 @@ def test_noalloc_rejects_oversize_and_handles_empty():
     st = lib.orbx_knn_ratio_noalloc(big.data_ptr(), ang.data_ptr(), 4097, big.data_ptr(), ang.data_ptr(), 10, 50, 0.75, 1, 1,
                                     out.data_ptr(), nm.data_ptr(), None)
     assert st == api.ERR_CAPACITY and b"4096" in lib.orbx_last_error_string()
+    for bad_th in (-1, 256, 1000):              # 256 is the scan's "no candidate" distance: it must not pass as a threshold
+        st = lib.orbx_knn_ratio_noalloc(big.data_ptr(), ang.data_ptr(), 5, big.data_ptr(), ang.data_ptr(), 0, bad_th, 1.5, 1, 0,
+                                        out.data_ptr(), nm.data_ptr(), None)
+        assert st == api.ERR_BAD_ARG
     st = lib.orbx_knn_ratio_noalloc(big.data_ptr(), ang.data_ptr(), 5, big.data_ptr(), ang.data_ptr(), 0, 50, 0.75, 1, 1,
                                     out.data_ptr(), nm.data_ptr(), None)
     assert st == 0
