@@ -416,6 +416,11 @@ orbx_status orbx_get_profile(orbx_extractor* ext, float* ms, int* calls);
 
 /* cudaStreamSynchronize for callers that do not link the CUDA runtime themselves. */
 orbx_status orbx_stream_synchronize(void* stream);
+/* A non-blocking stream on `device` for such callers (no counterpart in the reference, which has no device).  The reference
+ * runs its left and right extractor on two host threads (src/Frame.cc:78-81); two handles on two such streams run
+ * concurrently on the GPU, whereas the legacy default stream (NULL) would serialise them. */
+orbx_status orbx_stream_create(int device, void** stream);
+void orbx_stream_destroy(void* stream);
 
 /* Message of the last failing call on the calling thread ("" if none). */
 const char* orbx_last_error_string(void);

@@ -37,12 +37,12 @@ class ORBextractor {
   enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
 
   ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0)
-      : device_(device), handle_(nullptr) {
+      : device_(device), handle_(nullptr), stream_(nullptr), max_w_(0), max_h_(0) {
     params_.nfeatures = nfeatures; params_.scale_factor = scaleFactor; params_.nlevels = nlevels;
     params_.ini_th_fast = iniThFAST; params_.min_th_fast = minThFAST;
     mvImagePyramid.resize(nlevels);
   }
-  ~ORBextractor() { orbx_extractor_destroy(handle_); }
+  ~ORBextractor() { orbx_extractor_destroy(handle_); orbx_stream_destroy(stream_); }
   ORBextractor(const ORBextractor&) = delete;
   ORBextractor& operator=(const ORBextractor&) = delete;
 
@@ -59,7 +59,7 @@ class ORBextractor {
     std::vector<unsigned char> desc((size_t)cap * 32);
     int n = 0;
     orbx_check(orbx_extract(handle_, image.data, image.cols, image.rows, (int)image.step,
-                            reinterpret_cast<orbx_keypoint*>(keypoints.data()), desc.data(), cap, &n, nullptr));
+                            reinterpret_cast<orbx_keypoint*>(keypoints.data()), desc.data(), cap, &n, stream_));
     keypoints.resize(n);
     if (n == 0) { _descriptors.release(); return; }
     _descriptors.create(n, 32, CV_8U);
@@ -91,10 +91,17 @@ class ORBextractor {
   }
 
   orbx_extractor* handle() { return handle_; }
-  // Sizes the device arenas; called lazily by operator() with the first image's size.
+  void* stream() { return stream_; }
+  // Sizes the device arenas; called by operator() with every image's size.  The reference accepts any image size on
+  // any call (it reallocates mvImagePyramid, src/ORBextractor.cc:1115), so a later image that is larger than the
+  // arenas were sized for gets a new handle.  Each stand-in owns a non-blocking stream: the reference's two extractor
+  // threads (src/Frame.cc:78-81) then overlap on the GPU instead of queueing on the legacy default stream.
   void Ensure(int w, int h, int max_batch = 1) {
-    if (handle_) return;
-    orbx_check(orbx_extractor_create(&params_, w, h, max_batch, device_, &handle_));
+    if (!stream_) orbx_check(orbx_stream_create(device_, &stream_));
+    if (handle_ && w <= max_w_ && h <= max_h_) return;
+    if (handle_) { orbx_extractor_destroy(handle_); handle_ = nullptr; }
+    max_w_ = std::max(max_w_, w); max_h_ = std::max(max_h_, h);
+    orbx_check(orbx_extractor_create(&params_, max_w_, max_h_, max_batch, device_, &handle_));
   }
 
  private:
@@ -106,17 +113,21 @@ class ORBextractor {
   orbx_params params_;
   int device_;
   orbx_extractor* handle_;
+  void* stream_;
+  int max_w_, max_h_;
 };
 
 // Body of Frame::ComputeStereoMatches (src/Frame.cc:466-640): call right after both ExtractORB
-// threads joined (src/Frame.cc:78-81).  N = mvKeys.size().
+// threads joined (src/Frame.cc:78-81; operator() returns with its stream drained, so both slots are complete).
+// N = mvKeys.size(); fx = mK.at<float>(0,0) - the static Frame::fx is still unset when the FIRST stereo frame gets
+// here (src/Frame.cc:90 runs before :105).
 inline void ComputeStereoMatchesGPU(ORBextractor& left, ORBextractor& right, int N, float mbf, float fx,
                                     std::vector<float>& mvuRight, std::vector<float>& mvDepth) {
   const int cap = orbx_max_keypoints(left.handle());
   std::vector<float> ur(cap, -1.f), dp(cap, -1.f);
   int nmatches = 0;
-  orbx_check(orbx_stereo_match_batch(left.handle(), 0, right.handle(), 0, 1, mbf, fx, ur.data(), dp.data(), &nmatches, cap, 0, nullptr));
-  orbx_check(orbx_stream_synchronize(nullptr));
+  orbx_check(orbx_stereo_match_batch(left.handle(), 0, right.handle(), 0, 1, mbf, fx, ur.data(), dp.data(), &nmatches, cap, 0, left.stream()));
+  orbx_check(orbx_stream_synchronize(left.stream()));
   mvuRight.assign(ur.begin(), ur.begin() + N);
   mvDepth.assign(dp.begin(), dp.begin() + N);
 }

@@ -87,6 +87,9 @@ def lib():
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_stream_synchronize.argtypes = [C.c_void_p]
+        L.orbx_stream_create.argtypes = [C.c_int, C.c_void_p]
+        L.orbx_stream_destroy.argtypes = [C.c_void_p]
+        L.orbx_stream_destroy.restype = None
         L.orbx_search_projection_frame_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int] * 2 + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] +
                                                          [C.c_float] * 5 + [C.c_void_p] * 7 + [C.c_int, C.c_float, C.c_int] +
                                                          [C.c_void_p] * 3 + [C.c_int, C.c_void_p])

@@ -84,7 +84,7 @@ struct orbx_extractor {
   int slots_valid = 0;
   // optional per-stage timing: a ring of event sets, 5 boundaries per extract pass, 3 per stereo pass
   bool profiling = false;
-  static constexpr int kRing = 64;
+  static constexpr int kRing = 256;
   cudaEvent_t ev_ext[kRing][5] = {}; int n_ext = 0;
   cudaEvent_t ev_st[kRing][3] = {}; int n_st = 0;
 };
@@ -1247,6 +1247,23 @@ orbx_status orbx_get_profile(orbx_extractor* e, float* ms, int* calls) {
 orbx_status orbx_stream_synchronize(void* stream) {
   CU(cudaStreamSynchronize((cudaStream_t)stream));
   return ORBX_OK;
+}
+
+orbx_status orbx_stream_create(int device, void** stream) {
+  if (!stream) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  *stream = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(ORBX_ERR_CUDA, "no CUDA device: orbx has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(ORBX_ERR_BAD_ARG, "device index out of range");
+  DeviceGuard guard(device);
+  cudaStream_t st;
+  CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  *stream = (void*)st;
+  return ORBX_OK;
+}
+
+void orbx_stream_destroy(void* stream) {
+  if (stream) cudaStreamDestroy((cudaStream_t)stream);
 }
 
 const char* orbx_last_error_string(void) { return g_err.c_str(); }

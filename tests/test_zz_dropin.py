@@ -31,16 +31,17 @@ def _same(a, b, path=""):
         assert a == b, path
 
 
-@pytest.fixture(scope="module")
-def both(oracle):
-    gpu_bin = os.path.join(os.path.dirname(oracle.REF_SLAM_BIN), "orbref_slam_gpu")
-    if not (oracle.ref_slam_available() and os.path.exists(gpu_bin)):
-        missing_reference_binary("oracle/_ref/orbref_slam(_gpu)")
+def _runner(oracle, names):
+    """Runs an oracle.ref_slam_* call once per binary of oracle/_ref (the all-reference one first)."""
+    d = os.path.dirname(oracle.REF_SLAM_BIN)
+    bins = [os.path.join(d, n) for n in names]
+    if not all(os.path.exists(b) for b in bins):
+        missing_reference_binary("oracle/_ref/{" + ",".join(names) + "}")
     ref_bin = oracle.REF_SLAM_BIN
 
     def run(fn, *args, **kw):
         out = []
-        for b in (ref_bin, gpu_bin):
+        for b in bins:
             oracle.REF_SLAM_BIN = b
             try:
                 out.append(fn(*args, **kw))
@@ -50,13 +51,44 @@ def both(oracle):
     return run
 
 
-def test_stereo_frame_constructor(oracle, both):
+@pytest.fixture(scope="module")
+def both(oracle):
+    return _runner(oracle, ["orbref_slam", "orbref_slam_gpu"])
+
+
+@pytest.fixture(scope="module")
+def all_three(oracle):
+    """reference | drop-in extractor + matcher with the reference's CPU ComputeStereoMatches on a downloaded pyramid |
+    the same with dropin/FrameStereo.cc: Frame::ComputeStereoMatches on the GPU, nothing copied back but the results."""
+    return _runner(oracle, ["orbref_slam", "orbref_slam_gpu", "orbref_slam_gpustereo"])
+
+
+def test_stereo_frame_constructor(oracle, all_three):
+    """The reference's own stereo Frame constructor (src/Frame.cc:61-117) in all three builds: mvKeys, mvKeysUn, descriptors,
+    mvuRight and mvDepth must be the same bytes (KITTI and EuRoC shapes)."""
+    for cfg, cam, seeds in ((synth.KITTI, (718.856, 718.856, 607.1928, 185.2157), (5, 43)),
+                            (synth.EUROC, (435.2047, 435.2047, 367.4517, 252.2008), (6,))):
+        for seed in seeds:
+            L, R, _ = synth.stereo_pair(seed, cfg["w"], cfg["h"])
+            ref, gpu, gpu_stereo = all_three(oracle.ref_slam_stereo, L, R, cfg["nfeatures"], cam, cfg["bf"])
+            _same(ref, gpu)
+            _same(ref, gpu_stereo, "gpustereo")
+            assert (ref["u_right"] >= 0).sum() > 200
+
+
+def test_keyframe_searches_with_gpu_stereo_frames(oracle, all_three):
+    """One keyframe case through the third binary as well: every Frame it builds gets its depth from the GPU stereo body."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
+    kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
+    gs = kc.gs
     cfg = synth.KITTI
-    for seed in (5, 43):
-        L, R, _ = synth.stereo_pair(seed, cfg["w"], cfg["h"])
-        ref, gpu = both(oracle.ref_slam_stereo, L, R, cfg["nfeatures"], (718.856, 718.856, 607.1928, 185.2157), cfg["bf"])
-        _same(ref, gpu)
-        assert (ref["u_right"] >= 0).sum() > 300
+    seed, L, only_stereo, mono, ori = gs.KF_CASES[2]
+    ims, V, T1, T2, F12 = gs.kf_case_inputs(seed, L)
+    ref, gpu, gpu_stereo = all_three(oracle.ref_slam_kf, *ims, cfg["nfeatures"], gs.KITTI_CAM, cfg["bf"], V, T1, T2, F12, check_ori=ori,
+                                     only_stereo=only_stereo, mono=mono, **gs.KF_PARAMS)
+    _same(ref, gpu_stereo, "gpustereo")
+    _same(ref, gpu)
 
 
 def test_monocular_frames_and_initialisation(oracle, both):
