@@ -231,6 +231,38 @@ double orbo_bench_stereo(const uint8_t* imgsL, const uint8_t* imgsR, int nframes
   if (totalMatches) *totalMatches = m;
   return s;
 }
+// Full results for a batch of frames on `threads` std::threads (soak tests, bench.py's self-check): frame f goes to
+// rows f (left) and nframes + f (right, when imgsR is given) of kps [.][cap] / desc [.][cap][32] / counts [.];
+// uRight / depth [nframes][cap] and nMatches [nframes] for stereo.  Untouched entries keep the caller's fill.
+// Returns 0, or the first negative extract() status / -100 when cap is too small.
+int orbo_batch_stereo(const uint8_t* imgsL, const uint8_t* imgsR, int nframes, int w, int h, int nf, float sf, int nl,
+                      int ini, int mn, float bf, float fx, int threads, int cap, KeyPt* kps, uint8_t* desc, int* counts,
+                      float* uRight, float* depth, int* nMatches) {
+  std::vector<int> status(threads, 0);
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      Extractor L(nf, sf, nl, ini, mn), R(nf, sf, nl, ini, mn);
+      std::vector<KeyPt> kl, kr; std::vector<uint8_t> dl, dr;
+      for (int f = t; f < nframes && status[t] == 0; f += threads) {
+        const int a = L.extract(imgsL + (size_t)f * w * h, w, h, w, kl, dl);
+        if (a < 0 || a > cap) { status[t] = a < 0 ? a : -100; break; }
+        counts[f] = a;
+        if (a) { std::memcpy(kps + (size_t)f * cap, kl.data(), sizeof(KeyPt) * a); std::memcpy(desc + (size_t)f * cap * 32, dl.data(), 32 * (size_t)a); }
+        if (!imgsR) continue;
+        const int b = R.extract(imgsR + (size_t)f * w * h, w, h, w, kr, dr);
+        if (b < 0 || b > cap) { status[t] = b < 0 ? b : -100; break; }
+        const size_t fr = (size_t)nframes + f;
+        counts[fr] = b;
+        if (b) { std::memcpy(kps + fr * cap, kr.data(), sizeof(KeyPt) * b); std::memcpy(desc + fr * cap * 32, dr.data(), 32 * (size_t)b); }
+        nMatches[f] = (a > 0 && b > 0) ? stereo_match(L, R, kl, dl.data(), kr, dr.data(), bf, fx, uRight + (size_t)f * cap, depth + (size_t)f * cap) : 0;
+      }
+    });
+  for (auto& th : pool) th.join();
+  for (int t = 0; t < threads; ++t) if (status[t]) return status[t];
+  return 0;
+}
+
 int orbo_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

@@ -311,20 +311,33 @@ def ref_slam_distinct(descriptor_lists, image, nfeatures=2000, cam=(700.0, 700.0
     return out
 
 
-def ref_slam_bench(imgsL, imgsR, nfeatures, cam, bf, threads, reps=1):
-    """Times the REFERENCE's stereo Frame constructor (extraction of both eyes in two threads + ComputeStereoMatches) on
-    `threads` std::threads, one stereo frame per thread at a time.  Returns (seconds, keypoints, stereo matches)."""
+REF_BENCH_MODES = {"stereo": 0, "mono": 1, "init": 2, "bow": 3}
+
+
+def ref_slam_bench(imgsL, imgsR, nfeatures, cam, bf, threads, reps=1, mode="stereo", ratio=0.9, window=100, check_ori=True, binary=None,
+                   detail=False):
+    """Times the REFERENCE's own code on `threads` std::threads, one unit per thread at a time (oracle/ref_slam_cmds.inc:cmd_bench):
+    mode "stereo" = the stereo Frame constructor (two extractor threads + ComputeStereoMatches), "mono" = the monocular Frame
+    constructor (imgsR None), "init" = ORBmatcher::SearchForInitialization on (imgsL[i], imgsR[i]) frame pairs, "bow" =
+    ORBmatcher::SearchByBoW(KF,KF) with one vocabulary bucket on such pairs.  binary: another build of the driver (the drop-in
+    ones).  Returns (seconds, keypoints, matches), with detail=True also (p50_ms, p99_ms) of one call."""
     import tempfile
-    imgsL = np.ascontiguousarray(imgsL, np.uint8); imgsR = np.ascontiguousarray(imgsR, np.uint8)
+    imgsL = np.ascontiguousarray(imgsL, np.uint8)
     n, h, w = imgsL.shape
+    m = REF_BENCH_MODES[mode]
     with tempfile.TemporaryDirectory() as td:
         fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
         with open(fin, "wb") as f:
-            f.write(np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, bf) + np.array([n, threads, reps], np.int32).tobytes())
-            f.write(imgsL.tobytes()); f.write(imgsR.tobytes())
-        res = subprocess.run([REF_SLAM_BIN, "bench", fin, fout], check=True, capture_output=True, text=True)
-    secs, keys, matches = res.stdout.strip().splitlines()[-1].split()
-    return float(secs), int(keys), int(matches)
+            f.write(np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, bf) + np.array([n, threads, reps, m], np.int32).tobytes())
+            if m >= 2:
+                f.write(np.float32(ratio).tobytes() + np.array([window, int(check_ori)], np.int32).tobytes())
+            f.write(imgsL.tobytes())
+            if m != 1:
+                f.write(np.ascontiguousarray(imgsR, np.uint8).tobytes())
+        res = subprocess.run([binary or REF_SLAM_BIN, "bench", fin, fout], check=True, capture_output=True, text=True)
+    tok = res.stdout.strip().splitlines()[-1].split()
+    out = (float(tok[0]), int(tok[1]), int(tok[2]))
+    return out + ((float(tok[3]), float(tok[4])),) if detail else out
 
 
 def ref_dbow_available():
@@ -546,6 +559,25 @@ def bench_stereo(imgsL, imgsR, params, bf, fx, threads, reps=1):
     s = lib().orbo_bench_stereo(_p(imgsL), _p(imgsR), n, w, h, nf, C.c_float(sf), nl, ini, mn, C.c_float(bf),
                                 C.c_float(fx), threads, reps, C.byref(k), C.byref(m))
     return s, k.value, m.value
+
+
+def batch_stereo(imgsL, imgsR, params, bf, fx, cap, threads=0):
+    """Extraction (+ stereo matching when imgsR is given) of a batch on all host threads, full results in the layout of the
+    CUDA path's batched fetch: kps [(1 or 2) * n][cap] (left eyes, then right eyes), desc, counts; uRight / depth [n][cap]
+    (-1 filled), n_matches [n]."""
+    imgsL = np.ascontiguousarray(imgsL, np.uint8)
+    n, h, w = imgsL.shape
+    eyes = 1 if imgsR is None else 2
+    if imgsR is not None:
+        imgsR = np.ascontiguousarray(imgsR, np.uint8)
+    kps = np.zeros((eyes * n, cap), KP_DTYPE); desc = np.zeros((eyes * n, cap, 32), np.uint8); counts = np.zeros(eyes * n, np.int32)
+    ur = np.full((n, cap), -1, np.float32); dp = np.full((n, cap), -1, np.float32); nm = np.zeros(n, np.int32)
+    nf, sf, nl, ini, mn = params
+    rc = lib().orbo_batch_stereo(_p(imgsL), _p(imgsR), n, w, h, nf, C.c_float(sf), nl, ini, mn, C.c_float(bf), C.c_float(fx),
+                                 threads or hardware_threads(), cap, _p(kps), _p(desc), _p(counts), _p(ur), _p(dp), _p(nm))
+    if rc != 0:
+        raise RuntimeError(f"orbo_batch_stereo failed: {rc}")
+    return kps, desc, counts, ur, dp, nm
 
 
 def hardware_threads():

@@ -204,8 +204,9 @@ class ORBextractor:
         n, _, q = self._tables(); return q[:n].copy()
 
     # --- operator() ---
-    def __call__(self, image, mask=None):
-        """(keypoints, descriptors) for one host image; mask is ignored as in the reference."""
+    def __call__(self, image, mask=None, stream=None):
+        """(keypoints, descriptors) for one host image; mask is ignored as in the reference.  stream: a cudaStream_t
+        (e.g. from orbx_stream_create) so that two extractors on two host threads overlap on the GPU."""
         if image is None or image.size == 0:
             return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
         if image.dtype != np.uint8 or image.ndim != 2:
@@ -218,7 +219,7 @@ class ORBextractor:
         cap = self.kp_cap
         kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8); n = C.c_int()
         _check(lib().orbx_extract(self._h, image.ctypes.data, w, h, image.strides[0], kps.ctypes.data, desc.ctypes.data,
-                                  cap, C.byref(n), None))
+                                  cap, C.byref(n), stream))
         self.shape = (h, w)
         return kps[:n.value].copy(), desc[:n.value].copy()
 

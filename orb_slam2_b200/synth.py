@@ -108,6 +108,23 @@ def mono_pair(frame_idx, w, h, maxshift=40):
     return a, _add_noise(b, seed + 1), (dx, dy)
 
 
+def variant(img, v):
+    """Distinct frame number v derived from a seeded base frame at almost no cost (large soaks and batches need thousands
+    of different images; painting each from scratch costs 50 ms): the columns are rolled by 37 * v (a new alignment with the
+    FAST cell grid and the quad-tree boxes, and a vertical seam), every other variant is turned upside down.  Applied alike
+    to both eyes of a stereo pair it keeps the planted horizontal disparities.  v = 0 is the base frame."""
+    out = np.roll(img, (37 * v) % img.shape[1], axis=1) if v else img
+    return np.ascontiguousarray(out[::-1] if (v & 1) else out)
+
+
+def stereo_set(first_seed, n_base, count, w, h):
+    """count distinct stereo pairs as two arrays (count, h, w): n_base painted pairs (seeds first_seed ..) and their variants."""
+    base = [stereo_pair(first_seed + i, w, h)[:2] for i in range(n_base)]
+    L = np.stack([variant(base[i % n_base][0], i // n_base) for i in range(count)])
+    R = np.stack([variant(base[i % n_base][1], i // n_base) for i in range(count)])
+    return L, R
+
+
 def mono_frame(frame_idx, w, h):
     return synth_image(BASE_SEED + 16 * frame_idx + 12, w, h)
 
