@@ -46,9 +46,13 @@ struct Totals {
   int cells = 0, pool = 0, lvlkp = 0, taps = 0, win_w = 0, win_h = 0, node_cap = 0;
 };
 
+// Makes `dev` current for the scope.  cudaSetDevice is called even when the runtime already reports `dev`: on a host thread
+// that has made no runtime call yet it is what binds the primary context to the thread, and configure() goes to the driver
+// API directly (cuTensorMapEncodeTiled), which fails with CUDA_ERROR_INVALID_CONTEXT on a thread without one - the
+// reference's pattern of constructing the extractors on one thread and calling them on two others (src/Frame.cc:78-81).
 struct DeviceGuard {
   int prev = -1;
-  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); if (prev == dev) prev = -1; }
   ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 

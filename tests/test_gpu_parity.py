@@ -889,3 +889,34 @@ def test_cuda_searches_on_distorted_cameras_reproduce_reference(gx):
         n, a, _ = gx.ORBmatcher(0.9, case["check_ori"]).SearchByProjectionFrame(Fc, F2["u_right"], scale, T2[:3, :3], T2[:3, 3], c["cam"] + (cfg["bf"],), c["last"],
                                                                                P["th_last"], 0)
         assert n == case["n_proj_last"] and np.array_equal(a, fx["proj_last"])
+
+
+def test_first_extract_on_another_host_thread(gx, oracle):
+    """The reference constructs its extractors on the tracking thread and calls them on two fresh std::threads
+    (src/Tracking.cc:120-126, src/Frame.cc:78-81).  A handle created here and first used on threads that never touched CUDA
+    must work (the geometry set-up reaches the driver API, which needs a context bound to the calling thread)."""
+    import ctypes as C
+    import threading
+    cfg = synth.EUROC
+    w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
+    L, R, _ = synth.stereo_pair(81, w, h)
+    GL, GR = _ext(gx, w, h, nf), _ext(gx, w, h, nf)
+    lib = gx.lib()
+    sL, sR = C.c_void_p(), C.c_void_p()
+    assert lib.orbx_stream_create(0, C.byref(sL)) == 0 and lib.orbx_stream_create(0, C.byref(sR)) == 0
+    out, err = {}, []
+    def run(name, G, im, st):
+        try:
+            out[name] = G(im, stream=st)
+        except Exception as exc:
+            err.append(exc)
+    ts = [threading.Thread(target=run, args=("L", GL, L, sL)), threading.Thread(target=run, args=("R", GR, R, sR))]
+    [t.start() for t in ts]; [t.join() for t in ts]
+    assert not err, err
+    ur, dp, nm = gx.ComputeStereoMatches(GL, GR, cfg["bf"], cfg["fx"])
+    EL, ER = oracle.Extractor(nf), oracle.Extractor(nf)
+    okl, odl = EL.extract(L); okr, odr = ER.extract(R)
+    assert out["L"][0].tobytes() == okl.tobytes() and out["R"][0].tobytes() == okr.tobytes() and np.array_equal(out["R"][1], odr)
+    rur, rdp, _, rm = oracle.stereo(EL, ER, okl, odl, okr, odr, cfg["bf"], cfg["fx"])
+    assert int(nm[0]) == rm and np.array_equal(ur[0, :len(okl)].view(np.uint32), rur.view(np.uint32))
+    lib.orbx_stream_destroy(sL); lib.orbx_stream_destroy(sR)
