@@ -74,7 +74,8 @@ def algorithmic_bytes(w, h, nf, cands_per_eye, kps_per_eye):
         "pyramid": 2 * (w * h + bordered),
         "fast": 2 * (raw + 4 * cands_per_eye),
         "quadtree": 2 * (4 * cands_per_eye + 4 * kps_per_eye),
-        "describe": 2 * kps_per_eye * (43 * 43 + 60),
+        "blur": 2 * (bordered + raw),                                  # K4a reads the bordered planes, writes the blurred ROIs
+        "describe": 2 * kps_per_eye * (48 * 31 + 64 * 37 + 60),        # K4b: raw moments box + blurred tap box per keypoint, 60 B out
         "stereo_match": 2 * kps_per_eye * 60 + kps_per_eye * (11 * 32 + 8),
         "stereo_median": kps_per_eye * 12,
     }

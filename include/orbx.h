@@ -408,9 +408,9 @@ orbx_status orbx_knn_ratio_noalloc(const uint8_t* descA, const float* angA, int 
  * and stereo_match_batch bracket each stage with CUDA events on the launching stream.
  * orbx_get_profile synchronises the device, adds up what was recorded since the last call and
  * resets: ms[s] = total milliseconds of stage s, calls[s] = number of recorded passes.
- * Stages: 0 pyramid (all level launches), 1 FAST cells, 2 quad-tree, 3 orientation+blur+rBRIEF,
- * 4 stereo search+SAD, 5 stereo median cut. */
-#define ORBX_N_STAGES 6
+ * Stages: 0 pyramid (all level launches), 1 FAST cells, 2 quad-tree, 3 orientation + rBRIEF,
+ * 4 stereo search+SAD, 5 stereo median cut, 6 Gaussian blur of the level planes. */
+#define ORBX_N_STAGES 7
 orbx_status orbx_set_profiling(orbx_extractor* ext, int enable);
 orbx_status orbx_get_profile(orbx_extractor* ext, float* ms, int* calls);
 

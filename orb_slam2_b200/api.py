@@ -46,7 +46,7 @@ EXPORTS = ["orbx_extractor_create", "orbx_extractor_destroy", "orbx_get_tables",
            "orbx_get_profile", "orbx_stream_synchronize", "orbx_knn_ratio_noalloc",
            "orbx_search_projection_batch", "orbx_search_projection_frame_batch"]
 
-STAGES = ["pyramid", "fast", "quadtree", "describe", "stereo_match", "stereo_median"]
+STAGES = ["pyramid", "fast", "quadtree", "describe", "stereo_match", "stereo_median", "blur"]
 
 
 def library_path():

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "liborbx.so")
-SOURCES = ["orbx_api.cu", "k_pyramid.cu", "k_fast.cu", "k_octree.cu", "k_describe.cu", "k_stereo.cu", "k_match.cu", "k_frame.cu", "k_bow.cu", "k_project.cu"]
+SOURCES = ["orbx_api.cu", "k_pyramid.cu", "k_fast.cu", "k_octree.cu", "k_describe.cu", "k_blur.cu", "k_stereo.cu", "k_match.cu", "k_frame.cu", "k_bow.cu", "k_project.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--fmad=false", "-prec-div=true", "-prec-sqrt=true",
               "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-Wall", "-shared", "-cudart", "static"]

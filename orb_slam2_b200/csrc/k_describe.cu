@@ -300,6 +300,143 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe(DeviceLayout L
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// K4b — the same stage on top of the blurred level planes of K4a (k_blur.cu): no blur work per keypoint.
+//
+// The fused kernel above blurs a 43 x 40 / 38 x 40 region around every keypoint: 3.2 k pixels x ~2000 keypoints = 4.5x the
+// pixels of the level planes themselves, and those two passes were three quarters of its shared-memory traffic.  Here a
+// keypoint costs two TMA boxes - 48 x 31 raw bytes for the orientation moments (IC_Angle reads the UNBLURRED level,
+// src/ORBextractor.cc:77-104) and 64 x 37 blurred bytes for the 512 taps (:108-147) - the moments, fastAtan2, sinf / cosf
+// and the 16 rotated taps per lane.  Two stages per warp: the boxes of keypoint t + 1 are requested before keypoint t is
+// touched.  Arithmetic, rounding and output are those of k_describe, line for line.
+constexpr int kMomBytes = kMomBoxW * kMomBoxH, kTapBytes = kTapBoxW * kTapBoxH;       // 1488, 2368
+constexpr int kOffTap = 1536, kStageBytes = 3968, kOffBar2 = 2 * kStageBytes, kWarpSmem2 = 8064;
+static_assert(kMomBytes <= kOffTap && kOffTap + kTapBytes <= kStageBytes && kOffBar2 + 16 <= kWarpSmem2, "smem carve-up");
+static_assert(kOffTap % 128 == 0 && kStageBytes % 128 == 0 && kWarpSmem2 % 128 == 0, "TMA destinations must be 128-byte aligned");
+
+__global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe_planes(DeviceLayout L, const __grid_constant__ TmaMaps mom_maps,
+                                                                         const __grid_constant__ TmaMaps tap_maps, int first_slot, int n_img,
+                                                                         int ctas_per_img, int kp_per_warp, const char4* __restrict__ pattern) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* wbase = smem + (size_t)warp * kWarpSmem2;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(wbase + kOffBar2);     // bar[0], bar[1]: one per stage
+
+  const int img = blockIdx.x / ctas_per_img;
+  if (img >= n_img) return;
+  const int slot = first_slot + img;
+  const int j0 = ((blockIdx.x - img * ctas_per_img) * kDescWarps + warp) * kp_per_warp;   // first output keypoint of this warp
+
+  const int myc = lane < L.nlevels ? L.lvlcnt[slot * kMaxLevels + lane] : 0;
+  int incl = myc;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  const int total = min(__shfl_sync(0xffffffffu, incl, 31), L.kp_cap);
+  if (j0 == 0 && lane == 0) L.nkp[slot] = total;
+  if (j0 >= total) return;
+  const int nk = min(kp_per_warp, total - j0);
+
+  if (lane == 0) { mbar_init(bar, 1); mbar_init(bar + 1, 1); fence_barrier_init(); }
+  __syncwarp();
+  auto request = [&](const KpRef& k, int stage) {            // lane 0: both boxes of one keypoint on the stage's barrier
+    uint8_t* dst = wbase + stage * kStageBytes;
+    mbar_expect_tx(bar + stage, kMomBytes + kTapBytes);
+    tma_load_3d(dst, &mom_maps.m[k.level], (k.px + kEdge - 15) & ~15, k.py + kEdge - 15, slot, bar + stage);
+    tma_load_3d(dst + kOffTap, &tap_maps.m[k.level], (k.px + kEdge - 18) & ~15, k.py + kEdge - 18, slot, bar + stage);
+  };
+  KpRef nxt = locate_kp(L, slot, j0, incl, myc, lane);
+  if (lane == 0) request(nxt, 0);
+
+  float4 pat[8];                                              // this lane's 8 tests {x0, y0, x1, y1}
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    const char4 q = __ldg(pattern + lane * 8 + t);
+    pat[t] = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
+  }
+
+  for (int t = 0; t < nk; ++t) {
+    const KpRef cur = nxt;
+    const int j = j0 + t, stage = t & 1;
+    if (t + 1 < nk) {                                         // warp-uniform: the other stage was released at the end of the last iteration
+      nxt = locate_kp(L, slot, j + 1, incl, myc, lane);
+      if (lane == 0) { fence_proxy_async(); request(nxt, stage ^ 1); }
+    }
+    const int level = cur.level, px = cur.px, py = cur.py;
+    const LevelGeom& g = L.geom[level];
+    const uint8_t* raw = wbase + stage * kStageBytes;
+    const uint8_t* bl = raw + kOffTap;
+    mbar_wait(bar + stage, (t >> 1) & 1);
+
+    // intensity-centroid moments over the radius-15 disc (see k_describe): lane = column u, predicated rows
+    int m10, m01;
+    {
+      const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+      const int vlim = lane < 31 ? (int)((kUmaxNibbles >> (4 * (au & 15))) & 15ull) : -1;
+      const uint8_t* colp = raw + 15 * kMomBoxW + ((px + kEdge - 15) & 15) + 15 + (lane < 31 ? u : 0);
+      int s_all = lane < 31 ? (int)colp[0] : 0, s_v = 0;
+#pragma unroll
+      for (int v = 1; v <= kHalfPatch; ++v) {
+        const int a = colp[v * kMomBoxW], b = colp[-v * kMomBoxW];
+        asm("{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %2, %3;\n\t@p add.s32 %0, %0, %4;\n\t@p mad.lo.s32 %1, %5, %3, %1;\n\t}"
+            : "+r"(s_all), "+r"(s_v) : "r"(vlim), "r"(v), "r"(a + b), "r"(a - b));
+      }
+      m10 = u * s_all;
+      m01 = s_v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+      m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // steered BRIEF on the blurred box: lane i produces descriptor byte i; tap (row r, column c) = ctr[r * 64 + c]
+    const float rad = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
+    const float ca = libm_sincos(rad, 1), sb = libm_sincos(rad, 0);
+    const float kMagic = 12582912.0f;                         // cvRound by the 1.5 * 2^23 trick, see k_describe
+    const uint32_t kBias = 0x4B400000u * (uint32_t)(kTapBoxW + 1);
+    const uint8_t* ctr = bl + 18 * kTapBoxW + ((px + kEdge - 18) & 15) + 18;
+    uint32_t byte = 0;
+#pragma unroll
+    for (int q8 = 0; q8 < 8; ++q8) {
+      const float4 q = pat[q8];
+      const uint32_t r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(q.x, sb), __fmul_rn(q.y, ca)), kMagic));
+      const uint32_t c0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(q.x, ca), __fmul_rn(q.y, sb)), kMagic));
+      const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(q.z, sb), __fmul_rn(q.w, ca)), kMagic));
+      const uint32_t c1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(q.z, ca), __fmul_rn(q.w, sb)), kMagic));
+      const int v0 = ctr[(int)(r0 * kTapBoxW + c0 - kBias)], v1 = ctr[(int)(r1 * kTapBoxW + c1 - kBias)];
+      byte |= (uint32_t)(v0 < v1) << q8;
+    }
+    const size_t oi = (size_t)slot * L.kp_cap + j;
+    L.desc[oi * 32 + lane] = (uint8_t)byte;
+    if (lane == 0) {
+      orbx_keypoint kp;
+      kp.x = level ? __fmul_rn((float)px, g.scale) : (float)px;
+      kp.y = level ? __fmul_rn((float)py, g.scale) : (float)py;
+      kp.size = (float)g.patch_size;
+      kp.angle = angle;
+      kp.response = (float)cur.resp;
+      kp.octave = level;
+      kp.class_id = -1;
+      L.kps[oi] = kp;
+    }
+    __syncwarp();                                             // every lane is done with this stage
+  }
+}
+
+int launch_describe_planes(const DeviceLayout& L, const TmaMaps& mom_maps, const TmaMaps& tap_maps, int first_slot, int n, const char4* d_pattern,
+                           cudaStream_t st) {
+  const int kp_per_warp = (long long)n * L.kp_cap >= 148LL * 24 * kKpPerWarpBatch ? kKpPerWarpBatch : kKpPerWarpSmall;
+  const int per_cta = kDescWarps * kp_per_warp;
+  const int ctas_per_img = (L.kp_cap + per_cta - 1) / per_cta;
+  const size_t smem = (size_t)kDescWarps * kWarpSmem2;
+  k_describe_planes<<<n * ctas_per_img, kDescWarps * 32, smem, st>>>(L, mom_maps, tap_maps, first_slot, n, ctas_per_img, kp_per_warp, d_pattern);
+  return 1;
+}
+
 int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st) {
   const int kp_per_warp = (long long)n * L.kp_cap >= 148LL * 24 * kKpPerWarpBatch ? kKpPerWarpBatch : kKpPerWarpSmall;
   const int per_cta = kDescWarps * kp_per_warp;

@@ -10,6 +10,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <type_traits>
 #include <string>
@@ -77,6 +78,10 @@ struct orbx_extractor {
   std::vector<ResizeTap> htaps;
   DeviceLayout L{};
   TmaMaps desc_maps{};       // per-level tensor maps with the K4 tile box
+  TmaMaps blur_src_maps{};   // K4a: source box of the whole-plane blur (raw pyramid)
+  TmaMaps mom_maps{};        // K4b: raw box for the orientation moments
+  TmaMaps tap_maps{};        // K4b: blurred box for the descriptor taps (blur arena)
+  bool fused_describe = false;   // ORBX_DESCRIBE=fused at create: the blur-on-demand kernel instead of K4a + K4b (kept for A/B measurements)
   TmaMaps resize_maps{};     // per-level tensor maps with the K1 source-footprint box
   TmaMaps fast_maps{};       // per-level tensor maps with the K2 cell-window box
   unsigned tiled_mask = 0;   // levels whose resize runs through the shared-memory tiled kernel
@@ -89,7 +94,7 @@ struct orbx_extractor {
   // optional per-stage timing: a ring of event sets, 5 boundaries per extract pass, 3 per stereo pass
   bool profiling = false;
   static constexpr int kRing = 256;
-  cudaEvent_t ev_ext[kRing][5] = {}; int n_ext = 0;
+  cudaEvent_t ev_ext[kRing][6] = {}; int n_ext = 0;
   cudaEvent_t ev_st[kRing][3] = {}; int n_st = 0;
 };
 
@@ -247,7 +252,8 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-orbx_status encode_level_maps(const orbx_extractor* e, const LevelGeom* g, int box_w, int box_h, TmaMaps* out) {
+orbx_status encode_level_maps(const orbx_extractor* e, const LevelGeom* g, int box_w, int box_h, TmaMaps* out, uint8_t* base = nullptr) {
+  if (!base) base = e->L.pyr;
   static EncodeTiledFn fn = nullptr;
   if (!fn) {
     void* p = nullptr;
@@ -261,7 +267,7 @@ orbx_status encode_level_maps(const orbx_extractor* e, const LevelGeom* g, int b
     const cuuint64_t strides[2] = {(cuuint64_t)g[l].pitch, (cuuint64_t)g[l].plane_stride};
     const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
     const cuuint32_t estr[3] = {1u, 1u, 1u};
-    const CUresult r = fn(&out->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, e->L.pyr + g[l].plane_off, dims, strides, box, estr,
+    const CUresult r = fn(&out->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base + g[l].plane_off, dims, strides, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for level " + std::to_string(l) + " (CUresult " + std::to_string((int)r) + ")");
@@ -280,7 +286,13 @@ orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
   if (t.pyr_bytes > e->capy.pyr_bytes || t.cells > e->capy.cells || t.pool > e->capy.pool || t.taps > e->capy.taps ||
       t.lvlkp > e->capy.lvlkp || t.node_cap > e->capy.node_cap || t.win_w > e->capy.win_w || t.win_h > e->capy.win_h)
     return fail(ORBX_ERR_CAPACITY, "image geometry needs more device memory than reserved at create");
-  TmaMaps maps, rmaps, fmaps;
+  TmaMaps maps, rmaps, fmaps, bmaps, mmaps, tmaps;
+  s = encode_level_maps(e, g, kBlurBoxW, kBlurBoxH, &bmaps);
+  if (s != ORBX_OK) return s;
+  s = encode_level_maps(e, g, kMomBoxW, kMomBoxH, &mmaps);
+  if (s != ORBX_OK) return s;
+  s = encode_level_maps(e, g, kTapBoxW, kTapBoxH, &tmaps, e->L.blur);
+  if (s != ORBX_OK) return s;
   s = encode_level_maps(e, g, fast_window_pitch(t.win_w), t.win_h, &fmaps);
   if (s != ORBX_OK) return s;
   s = encode_level_maps(e, g, kDescTileW, kDescTileH, &maps);
@@ -292,6 +304,7 @@ orbx_status configure(orbx_extractor* e, int w, int h, cudaStream_t st) {
   e->desc_maps = maps;
   e->resize_maps = rmaps;
   e->fast_maps = fmaps;
+  e->blur_src_maps = bmaps; e->mom_maps = mmaps; e->tap_maps = tmaps;
   e->tiled_mask = 0;
   for (int l = 1; l < e->nlevels; ++l)
     if (resize_tiled_fits(g[l], taps.data())) e->tiled_mask |= 1u << l;
@@ -362,6 +375,11 @@ orbx_status orbx_extractor_create(const orbx_params* params, int max_w, int max_
   ALLOC(e->d_pattern, 256);
   ALLOC(e->d_in, nb * max_w * max_h);
   ALLOC(L.pyr, e->capy.pyr_bytes);
+  {
+    const char* mode = std::getenv("ORBX_DESCRIBE");
+    e->fused_describe = mode && std::strcmp(mode, "fused") == 0;
+  }
+  ALLOC(L.blur, e->fused_describe ? 1 : e->capy.pyr_bytes);
   ALLOC(L.celltab, nb * e->capy.cells);
   ALLOC(L.poolcnt, nb * kMaxLevels);
   ALLOC(L.pool, nb * e->capy.pool);
@@ -397,13 +415,13 @@ void orbx_extractor_destroy(orbx_extractor* e) {
   DeviceGuard guard(e->device);
   cudaDeviceSynchronize();
   DeviceLayout& L = e->L;
-  void* ptrs[] = {e->d_geom, e->d_taps, e->d_umax, e->d_pattern, e->d_in, L.pyr, L.celltab, L.poolcnt, L.pool, L.okeys,
+  void* ptrs[] = {e->d_geom, e->d_taps, e->d_umax, e->d_pattern, e->d_in, L.pyr, L.blur, L.celltab, L.poolcnt, L.pool, L.okeys,
                   L.knode, L.lvlkp, L.lvlcnt, L.nkeys, L.kps, L.desc, L.nkp, L.err, e->d_uright, e->d_depth, e->d_sad,
                   e->d_nmatch, e->d_strec, e->d_sttab};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (e->ev_ext[0][0])
     for (int i = 0; i < orbx_extractor::kRing; ++i) {
-      for (int j = 0; j < 5; ++j) cudaEventDestroy(e->ev_ext[i][j]);
+      for (int j = 0; j < 6; ++j) cudaEventDestroy(e->ev_ext[i][j]);
       for (int j = 0; j < 3; ++j) cudaEventDestroy(e->ev_st[i][j]);
     }
   delete e;
@@ -469,8 +487,11 @@ orbx_status orbx_extract_batch(orbx_extractor* e, const uint8_t* imgs, int n, in
   if (ev) cudaEventRecord(ev[2], st);
   launches += launch_octree(e->L, first_slot, n, e->cur.node_cap, st);
   if (ev) cudaEventRecord(ev[3], st);
-  launches += launch_describe(e->L, e->desc_maps, first_slot, n, e->d_umax, e->d_pattern, st);
+  if (!e->fused_describe) launches += launch_blur(e->L, e->hg, e->blur_src_maps, first_slot, n, st);
   if (ev) cudaEventRecord(ev[4], st);
+  if (e->fused_describe) launches += launch_describe(e->L, e->desc_maps, first_slot, n, e->d_umax, e->d_pattern, st);
+  else launches += launch_describe_planes(e->L, e->mom_maps, e->tap_maps, first_slot, n, e->d_pattern, st);
+  if (ev) cudaEventRecord(ev[5], st);
   g_launches += launches;
   CU(cudaGetLastError());
   e->slots_valid = std::max(e->slots_valid, first_slot + n);
@@ -1218,7 +1239,7 @@ orbx_status orbx_set_profiling(orbx_extractor* e, int enable) {
   DeviceGuard guard(e->device);
   if (enable && !e->ev_ext[0][0]) {
     for (int i = 0; i < orbx_extractor::kRing; ++i) {
-      for (int j = 0; j < 5; ++j) CU(cudaEventCreate(&e->ev_ext[i][j]));
+      for (int j = 0; j < 6; ++j) CU(cudaEventCreate(&e->ev_ext[i][j]));
       for (int j = 0; j < 3; ++j) CU(cudaEventCreate(&e->ev_st[i][j]));
     }
   }
@@ -1232,11 +1253,12 @@ orbx_status orbx_get_profile(orbx_extractor* e, float* ms, int* calls) {
   DeviceGuard guard(e->device);
   CU(cudaDeviceSynchronize());
   for (int s = 0; s < ORBX_N_STAGES; ++s) { ms[s] = 0.f; calls[s] = 0; }
+  static const int kExtStage[5] = {0, 1, 2, 6, 3};   // event intervals in launch order: pyramid, FAST, quad-tree, blur, describe
   for (int i = 0; i < e->n_ext; ++i)
-    for (int s = 0; s < 4; ++s) {
+    for (int s = 0; s < 5; ++s) {
       float t = 0.f;
       CU(cudaEventElapsedTime(&t, e->ev_ext[i][s], e->ev_ext[i][s + 1]));
-      ms[s] += t; calls[s] += 1;
+      ms[kExtStage[s]] += t; calls[kExtStage[s]] += 1;
     }
   for (int i = 0; i < e->n_st; ++i)
     for (int s = 0; s < 2; ++s) {

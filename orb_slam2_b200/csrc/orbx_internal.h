@@ -52,6 +52,7 @@ struct DeviceLayout {    // per-handle pointers handed to kernels by value
   const LevelGeom* geom;     // [nlevels]
   const ResizeTap* taps;
   uint8_t* pyr;
+  uint8_t* blur;             // 7x7 sigma-2 blurred level planes, same layout as pyr (K4a); only the ROI part is written / read
   uint2* celltab;            // [nslots][cells_per_slot] {pool offset, count}
   int* poolcnt;              // [nslots][kMaxLevels]
   uint32_t* pool;            // [nslots][pool_per_slot]
@@ -77,6 +78,15 @@ struct TmaMaps { CUtensorMap m[kMaxLevels]; };
 constexpr int kResizeTileW = 128, kResizeTileH = 32;   // output tile of k_resize_tiled (bordered pixels)
 constexpr int kResizeBoxW = 192, kResizeBoxH = 48;  // K1 tiled resize: source footprint box
 constexpr int kDescTileW = 64, kDescTileH = 43;   // K4 tile box: TMA needs a 16-byte aligned start, so 43+15 columns -> 64
+constexpr int kBlurBoxW = 160, kBlurBoxH = 38;    // K4a source box of a 128 x 32 output tile: 3-px halo, 16-byte aligned start
+constexpr int kMomBoxW = 48, kMomBoxH = 31;       // K4b raw box for the orientation moments: 31 + 15 columns -> 48
+constexpr int kTapBoxW = 64, kTapBoxH = 37;       // K4b blurred box for the descriptor taps: 37 + 15 columns -> 64
+
+// per-level fields the blur kernel reads, as a kernel parameter
+struct BlurGeom {
+  int nlevels, tile_start[kMaxLevels], tiles_x[kMaxLevels], pitch[kMaxLevels], rows[kMaxLevels];
+  size_t plane_off[kMaxLevels], plane_stride[kMaxLevels];
+};
 
 // kernel launchers (each returns the number of kernel launches it made)
 int launch_pyramid(const DeviceLayout& L, const LevelGeom* hgeom, const uint8_t* src, int src_pitch,
@@ -86,6 +96,9 @@ int launch_fast(const DeviceLayout& L, const LevelGeom* hg, const TmaMaps& maps,
 int fast_window_pitch(int win_w);   // TMA box width of the FAST window (64 or 96)
 int launch_octree(const DeviceLayout& L, int first_slot, int n, int node_cap, cudaStream_t st);
 int launch_describe(const DeviceLayout& L, const TmaMaps& maps, int first_slot, int n, const int* d_umax, const char4* d_pattern, cudaStream_t st);
+// K4a + K4b: whole-plane blur, then orientation + descriptors from a raw moments box and a blurred tap box per keypoint
+int launch_blur(const DeviceLayout& L, const LevelGeom* hg, const TmaMaps& blur_src_maps, int first_slot, int n, cudaStream_t st);
+int launch_describe_planes(const DeviceLayout& L, const TmaMaps& mom_maps, const TmaMaps& tap_maps, int first_slot, int n, const char4* d_pattern, cudaStream_t st);
 
 struct StereoArgs {
   DeviceLayout L, R;
