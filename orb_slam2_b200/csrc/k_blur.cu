@@ -38,13 +38,11 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur_levels(const __grid_const
   __shared__ __align__(128) uint8_t s_src[kBsH * kBsW];                  // 6080 B
   __shared__ __align__(16) uint32_t s_h[(kBsH / 2) * kBtW];             // [row pair][column]: H(2r) | H(2r+1) << 16, 9728 B
   __shared__ __align__(8) uint64_t s_bar;
-  const int t = threadIdx.x, slot = first_slot + blockIdx.y;
-  int level = 0;
-#pragma unroll
-  for (int l = 1; l < kMaxLevels; ++l)
-    if (l < G.nlevels && (int)blockIdx.x >= G.tile_start[l]) level = l;
-  const int ti = blockIdx.x - G.tile_start[level], tiles_x = G.tiles_x[level];
-  const int ty = ti / tiles_x, tx = ti - ty * tiles_x;
+  // grid = (tile columns of level 0, tile rows of all levels stacked, slots): the level and the tile row of a CTA come from one
+  // table entry (no division, no search); levels narrower than level 0 leave their surplus CTAs at once
+  const int t = threadIdx.x, slot = first_slot + blockIdx.z;
+  const int rowinfo = G.row_info[blockIdx.y], level = rowinfo & 15, ty = rowinfo >> 4, tx = blockIdx.x;
+  if (tx >= G.tiles_x[level]) return;
   const int X0 = kBlurOrigin + tx * kBtW, Y0 = kBlurOrigin + ty * kBtH;
   if (t == 0) {
     mbar_init(&s_bar, 1);
@@ -69,11 +67,11 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur_levels(const __grid_const
       const uint32_t* p = src + (2 * r) * (kBsW / 4);
       const uint32_t a0 = p[0], a1 = p[1], a2 = p[2];
       const uint32_t b0 = p[kBsW / 4], b1 = p[kBsW / 4 + 1], b2 = p[kBsW / 4 + 2];
-      uint4 o;
-      o.x = __dp4a(a1, B1, __dp4a(a0, B0, 0u)) | (__dp4a(b1, B1, __dp4a(b0, B0, 0u)) << 16);
-      o.y = __dp4a(a2, C2, __dp4a(a1, C1, __dp4a(a0, C0, 0u))) | (__dp4a(b2, C2, __dp4a(b1, C1, __dp4a(b0, C0, 0u))) << 16);
-      o.z = __dp4a(a2, D2, __dp4a(a1, D1, __dp4a(a0, D0, 0u))) | (__dp4a(b2, D2, __dp4a(b1, D1, __dp4a(b0, D0, 0u))) << 16);
-      o.w = __dp4a(a2, A1, __dp4a(a1, A0, 0u)) | (__dp4a(b2, A1, __dp4a(b1, A0, 0u)) << 16);
+      uint4 o;                                                            // the sums fit 16 bits: one PRMT packs a row pair
+      o.x = __byte_perm(__dp4a(a1, B1, __dp4a(a0, B0, 0u)), __dp4a(b1, B1, __dp4a(b0, B0, 0u)), 0x5410);
+      o.y = __byte_perm(__dp4a(a2, C2, __dp4a(a1, C1, __dp4a(a0, C0, 0u))), __dp4a(b2, C2, __dp4a(b1, C1, __dp4a(b0, C0, 0u))), 0x5410);
+      o.z = __byte_perm(__dp4a(a2, D2, __dp4a(a1, D1, __dp4a(a0, D0, 0u))), __dp4a(b2, D2, __dp4a(b1, D1, __dp4a(b0, D0, 0u))), 0x5410);
+      o.w = __byte_perm(__dp4a(a2, A1, __dp4a(a1, A0, 0u)), __dp4a(b2, A1, __dp4a(b1, A0, 0u)), 0x5410);
       *reinterpret_cast<uint4*>(s_h + r * kBtW + 4 * g) = o;
     }
   }
@@ -87,9 +85,11 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur_levels(const __grid_const
     const int g = t & 31, s = t >> 5;
     const int col = X0 + 4 * g, pitch = G.pitch[level], rows = G.rows[level];
     const uint4* hp = reinterpret_cast<const uint4*>(s_h + (4 * s) * kBtW + 4 * g);
-    uint8_t* dst = blur + G.plane_off[level] + (size_t)slot * G.plane_stride[level] + (size_t)(Y0 + 8 * s) * pitch + col;
+    // a level plane is far below 2 GB: 32-bit offsets inside it
+    uint8_t* dst = blur + G.plane_off[level] + (size_t)slot * G.plane_stride[level] + (unsigned)((Y0 + 8 * s) * pitch + col);
     uint4 W0 = hp[0], W1 = hp[kBtW / 4], W2 = hp[2 * (kBtW / 4)];
-    const bool col_ok = col < pitch;
+    // rows this thread may write: all 8 in an interior tile (CTA-uniform test first), fewer at the bottom edge; none right of the plane
+    const int nrow = (X0 + kBtW <= pitch && Y0 + kBtH <= rows) ? 8 : (col < pitch ? min(8, rows - (Y0 + 8 * s)) : 0);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const uint4 W3 = hp[(k + 3) * (kBtW / 4)];
@@ -102,9 +102,9 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur_levels(const __grid_const
       // byte 2 of each sum is the pixel; four of them make one word of the output row
       const unsigned re = __byte_perm(__byte_perm(e[0], e[1], 0x0062), __byte_perm(e[2], e[3], 0x0062), 0x5410);
       const unsigned rf = __byte_perm(__byte_perm(f[0], f[1], 0x0062), __byte_perm(f[2], f[3], 0x0062), 0x5410);
-      const int y = Y0 + 8 * s + 2 * k;
-      if (col_ok && y < rows) *reinterpret_cast<uint32_t*>(dst + (size_t)(2 * k) * pitch) = re;
-      if (col_ok && y + 1 < rows) *reinterpret_cast<uint32_t*>(dst + (size_t)(2 * k + 1) * pitch) = rf;
+      if (2 * k < nrow) *reinterpret_cast<uint32_t*>(dst) = re;
+      if (2 * k + 1 < nrow) *reinterpret_cast<uint32_t*>(dst + pitch) = rf;
+      dst += 2 * pitch;
       W0 = W1; W1 = W2; W2 = W3;
     }
   }
@@ -112,17 +112,15 @@ __global__ void __launch_bounds__(kBlurThreads) k_blur_levels(const __grid_const
 
 int launch_blur(const DeviceLayout& L, const LevelGeom* hg, const TmaMaps& maps, int first_slot, int n, cudaStream_t st) {
   BlurGeom G{};
-  G.nlevels = L.nlevels;
-  int tiles = 0;
+  int rows_total = 0;
   for (int l = 0; l < L.nlevels; ++l) {
     // the ROI is columns 19 .. 19 + w - 1 of the bordered plane; tiles start at column / row 16
     G.tiles_x[l] = (hg[l].w + 3 + kBtW - 1) / kBtW;
     const int tiles_y = (hg[l].h + 3 + kBtH - 1) / kBtH;
-    G.tile_start[l] = tiles;
-    tiles += G.tiles_x[l] * tiles_y;
+    for (int ty = 0; ty < tiles_y && rows_total < kBlurMaxRows; ++ty) G.row_info[rows_total++] = l | (ty << 4);
     G.pitch[l] = hg[l].pitch; G.rows[l] = hg[l].rows; G.plane_off[l] = hg[l].plane_off; G.plane_stride[l] = hg[l].plane_stride;
   }
-  k_blur_levels<<<dim3((unsigned)tiles, (unsigned)n), kBlurThreads, 0, st>>>(maps, G, L.blur, first_slot);
+  k_blur_levels<<<dim3((unsigned)G.tiles_x[0], (unsigned)rows_total, (unsigned)n), kBlurThreads, 0, st>>>(maps, G, L.blur, first_slot);
   return 1;
 }
 

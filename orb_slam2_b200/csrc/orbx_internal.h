@@ -83,9 +83,11 @@ constexpr int kMomBoxW = 48, kMomBoxH = 31;       // K4b raw box for the orienta
 constexpr int kTapBoxW = 64, kTapBoxH = 37;       // K4b blurred box for the descriptor taps: 37 + 15 columns -> 64
 
 // per-level fields the blur kernel reads, as a kernel parameter
+constexpr int kBlurMaxRows = 8 * ((4096 + 3 + 31) / 32);   // tile rows of all levels stacked: at most 8 levels of a 4096-px high image
 struct BlurGeom {
-  int nlevels, tile_start[kMaxLevels], tiles_x[kMaxLevels], pitch[kMaxLevels], rows[kMaxLevels];
+  int tiles_x[kMaxLevels], pitch[kMaxLevels], rows[kMaxLevels];
   size_t plane_off[kMaxLevels], plane_stride[kMaxLevels];
+  uint16_t row_info[kBlurMaxRows];   // per stacked tile row: level | tile row inside the level << 4
 };
 
 // kernel launchers (each returns the number of kernel launches it made)
