@@ -609,6 +609,20 @@ def latency_block(gx, torch, local):
             s, _, m2, lat = O.ref_slam_bench(Ls, Rs, nf, KITTI_CAM, CFG["bf"], 1, reps=13, detail=True, binary=gpu_bin)
             out["frame_constructor_dropin_gpu"] = {"p50_ms": lat[0], "p99_ms": lat[1], "calls": 208,
                                                    "what": "the same constructor, unmodified src/Frame.cc, with dropin/ORBextractor.h + dropin/FrameStereo.cc over liborbx.so"}
+        # per-call latency of the ORBmatcher members on real KeyFrames / MapPoints (the kf case of the parity tests): the same driver
+        # source compiled with the reference's src/ORBmatcher.cc (CPU) and with dropin/ORBmatcher.cc over liborbx.so
+        drop_bin = os.path.join(os.path.dirname(O.REF_SLAM_BIN), "orbref_slam_gpu")
+        if O.ref_slam_available() and os.path.exists(drop_bin):
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import gen_golden_slam as gs
+            ims, V, T1, T2, F12 = gs.kf_case_inputs(5, 5)
+            kw = dict(reps=40, check_ori=True, **gs.KF_PARAMS)
+            ref, sizes = O.ref_slam_kfbench(*ims, nf, KITTI_CAM, CFG["bf"], V, T1, T2, F12, **kw)
+            gpu, _ = O.ref_slam_kfbench(*ims, nf, KITTI_CAM, CFG["bf"], V, T1, T2, F12, binary=drop_bin, **kw)
+            out["matcher_members"] = {"what": "p50 / p99 ms of one call on the kf case (2004-feature KITTI-shaped keyframes, %d / %d map points), 40 calls each; "
+                                              "reference = src/ORBmatcher.cc on the CPU, dropin = dropin/ORBmatcher.cc (flatten + one C-ABI call + write-back)" % sizes[2:],
+                                      "members": {k: {"reference_cpu_p50_ms": ref[k][0], "reference_cpu_p99_ms": ref[k][1], "dropin_gpu_p50_ms": gpu[k][0],
+                                                      "dropin_gpu_p99_ms": gpu[k][1], "matches": [ref[k][2], gpu[k][2]]} for k in ref if k in gpu}}
     except Exception as exc:
         out["frame_constructor_error"] = repr(exc)
     return out

@@ -294,6 +294,36 @@ def ref_slam_kf(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, pct1=60, p
     return o
 
 
+def ref_slam_kfbench(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, reps=30, pct1=60, pct2=50, ratio_kk=0.75, ratio_kf=0.7,
+                     th_proj=3.0, th_last=15.0, check_ori=True, only_stereo=False, mono=False, binary=None):
+    """Per-call latency of the ORBmatcher members on the kf case (oracle/ref_slam_cmds.inc:cmd_kfbench) in the given build of the
+    driver.  Returns ({member: (p50_ms, p99_ms, result)}, (n1, n2, map points 1, map points 2))."""
+    import tempfile
+    ims = [np.ascontiguousarray(x, np.uint8) for x in (L1, R1, L2, R2)]
+    h, w = ims[0].shape
+    with tempfile.TemporaryDirectory() as td:
+        vp = os.path.join(td, "voc.txt")
+        write_vocabulary_text(voc, vp, 0, 0)
+        pb = vp.encode()
+        pay = (np.array([w, h, nfeatures], np.int32).tobytes() + _calib_bytes(cam, bf) + np.array([pct1, pct2], np.int32).tobytes() +
+               np.array([ratio_kk, ratio_kf, th_proj, th_last], np.float32).tobytes() +
+               np.array([int(check_ori), int(only_stereo), int(mono), int(reps)], np.int32).tobytes() +
+               np.asarray(T1, np.float32).reshape(16).tobytes() + np.asarray(T2, np.float32).reshape(16).tobytes() +
+               np.asarray(F12, np.float32).reshape(9).tobytes() + np.int32(len(pb)).tobytes() + pb + b"".join(x.tobytes() for x in ims))
+        fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        with open(fin, "wb") as f:
+            f.write(pay)
+        res = subprocess.run([binary or REF_SLAM_BIN, "kfbench", fin, fout], check=True, capture_output=True, text=True)
+    out, sizes = {}, None
+    for ln in res.stdout.strip().splitlines():
+        t = ln.split()
+        if t[0] == "sizes":
+            sizes = tuple(int(v) for v in t[1:])
+        elif len(t) == 4:
+            out[t[0]] = (float(t[1]), float(t[2]), int(t[3]))
+    return out, sizes
+
+
 def ref_slam_distinct(descriptor_lists, image, nfeatures=2000, cam=(700.0, 700.0, 600.0, 180.0)):
     """The REFERENCE's MapPoint::ComputeDistinctiveDescriptors on real MapPoints / KeyFrames: descriptor_lists[m] = (N_m, 32)
     observed descriptors of map point m (N_m >= 1).  Returns the (M, 32) chosen descriptors."""
