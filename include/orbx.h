@@ -14,6 +14,10 @@
  *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream)
  *   - an extractor handle owns all device memory it needs (allocated once in create);
  *     extract/match calls allocate nothing
+ *   - the ORBmatcher / Frame entry points take their arrays from host or from device memory (`on_device`).  Host arrays are
+ *     staged through a pinned buffer and a device scratch buffer owned by the CALLING THREAD: they grow to the largest call
+ *     that thread has made and are reused, so in steady state a call allocates nothing, uploads all inputs in one copy
+ *     and returns when the results are in the caller's arrays.  With device arrays only kernel scratch comes from that buffer
  *   - a handle is a single-stream object: calls on one handle must not overlap; distinct
  *     handles may be used from different host threads (the reference runs its left and right
  *     extractor on two threads, src/Frame.cc:78-81)

@@ -97,7 +97,10 @@ __global__ void __launch_bounds__(kStWarps * 32, 24) k_stereo_match(StereoArgs a
   const int img = blockIdx.x / ctas_per_img;
   const int iL = (blockIdx.x - img * ctas_per_img) * kStWarps + warp;
   const int slotL = a.slotL0 + img, slotR = a.slotR0 + img;
-  if (iL >= a.L.nkp[slotL]) return;
+  if (iL >= a.L.nkp[slotL]) {            // rows are kp_cap long: the entries behind the last keypoint read "no match" as well
+    if (lane == 0 && iL < a.L.kp_cap) { a.uRight[(size_t)img * a.cap + iL] = -1.f; a.depth[(size_t)img * a.cap + iL] = -1.f; }
+    return;
+  }
   const orbx_keypoint* kL = a.L.kps + (size_t)slotL * a.L.kp_cap;
   const uint8_t* dL = a.L.desc + (size_t)slotL * a.L.kp_cap * 32;
   const uint8_t* dR = a.R.desc + (size_t)slotR * a.R.kp_cap * 32;

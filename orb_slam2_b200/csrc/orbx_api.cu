@@ -642,26 +642,121 @@ int orbx_hamming256(const uint8_t* a, const uint8_t* b) {
 
 }  // extern "C"
 
-// Stages host arrays through stream-ordered device allocations when on_device == 0.
+// Staging for the matcher entry points called with HOST arrays (on_device == 0): every input is packed into one pinned host
+// buffer and reaches the device in ONE copy, scratch and outputs come out of a device buffer with a pinned mirror, results
+// return through that mirror.  Both buffers belong to the calling thread, grow to the largest call it has made and are
+// then reused: in steady state a call allocates nothing and issues one H2D copy, the kernels, and one small D2H copy per
+// output array.  (A SLAM thread calls these members once per frame on a few hundred KB; per-array cudaMallocAsync +
+// pageable copies cost more than the kernels.)  With device arrays (on_device == 1) inputs and outputs are used in place
+// and only scratch comes from the buffer.
 namespace {
+struct Arena {                       // a list of blocks: pointers handed out stay valid when more space is needed mid-call
+  struct Block { uint8_t* h = nullptr; uint8_t* d = nullptr; size_t cap = 0, used = 0, sent = 0; };
+  std::vector<Block> blocks;
+  int device = -1;
+  void release() {
+    for (Block& b : blocks) { if (b.h) cudaFreeHost(b.h); if (b.d) cudaFree(b.d); }
+    blocks.clear();
+  }
+  ~Arena() { release(); }
+  // bytes from the current block (a new one when it is full); returns false on allocation failure
+  bool take(size_t bytes, uint8_t** h, uint8_t** d, size_t* block_index) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    if (blocks.empty() || blocks.back().used + bytes > blocks.back().cap) {
+      Block b;
+      size_t total = 0;
+      for (const Block& x : blocks) total += x.cap;
+      b.cap = std::max<size_t>(std::max<size_t>(bytes, total), (size_t)1 << 20);      // at least doubles the arena
+      if (cudaMallocHost((void**)&b.h, b.cap) != cudaSuccess) return false;
+      if (cudaMalloc((void**)&b.d, b.cap) != cudaSuccess) { cudaFreeHost(b.h); return false; }
+      blocks.push_back(b);
+    }
+    Block& b = blocks.back();
+    *h = b.h + b.used; *d = b.d + b.used; *block_index = blocks.size() - 1;
+    b.used += bytes;
+    return true;
+  }
+  // after a call: one block as large as everything the call needed, so that the next call of this size finds room at once
+  void reset() {
+    if (blocks.size() > 1) {
+      size_t total = 0;
+      for (const Block& x : blocks) total += x.cap;
+      release();
+      Block b; b.cap = total;
+      if (cudaMallocHost((void**)&b.h, b.cap) == cudaSuccess) {
+        if (cudaMalloc((void**)&b.d, b.cap) == cudaSuccess) blocks.push_back(b); else cudaFreeHost(b.h);
+      }
+    }
+    for (Block& b : blocks) b.used = b.sent = 0;
+  }
+};
+thread_local Arena g_in_arena, g_out_arena;
+// With device arrays a call returns before its kernels have run; the next call of this thread hands out the same scratch.
+// An event recorded at the end of every call and waited for at the start of the next orders the two, whatever their streams.
+thread_local cudaEvent_t g_arena_event = nullptr;
+
 struct Staged {
   cudaStream_t st;
-  std::vector<void*> bufs;
-  explicit Staged(cudaStream_t s) : st(s) {}
-  ~Staged() { for (void* p : bufs) cudaFreeAsync(p, st); }
+  struct Pending { void* user; const uint8_t* mirror; size_t bytes; };
+  std::vector<Pending> pending;
+  explicit Staged(cudaStream_t s) : st(s) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (g_in_arena.device != dev && g_arena_event) { cudaEventDestroy(g_arena_event); g_arena_event = nullptr; }
+    for (Arena* a : {&g_in_arena, &g_out_arena}) {
+      if (a->device != dev) { a->release(); a->device = dev; }
+      a->reset();
+    }
+    if (g_arena_event) cudaStreamWaitEvent(st, g_arena_event, 0);
+  }
+  ~Staged() {
+    if (!g_arena_event) cudaEventCreateWithFlags(&g_arena_event, cudaEventDisableTiming);
+    if (g_arena_event) cudaEventRecord(g_arena_event, st);
+  }
+  // device scratch / output space
   cudaError_t alloc(void** p, size_t bytes) {
-    cudaError_t e = cudaMallocAsync(p, std::max<size_t>(bytes, 16), st);
-    if (e == cudaSuccess) bufs.push_back(*p);
-    return e;
+    uint8_t *h, *d; size_t bi;
+    if (!g_out_arena.take(std::max<size_t>(bytes, 16), &h, &d, &bi)) return cudaErrorMemoryAllocation;
+    *p = d;
+    return cudaSuccess;
   }
   template <typename T>
   cudaError_t in(const T* host, size_t count, int on_device, const T** out) {
     if (on_device) { *out = host; return cudaSuccess; }
-    void* d = nullptr;
-    cudaError_t e = alloc(&d, count * sizeof(T));
+    uint8_t *h, *d; size_t bi;
+    if (!g_in_arena.take(std::max<size_t>(count * sizeof(T), 16), &h, &d, &bi)) return cudaErrorMemoryAllocation;
+    std::memcpy(h, host, count * sizeof(T));
+    *out = reinterpret_cast<const T*>(d);
+    return cudaSuccess;
+  }
+  // the inputs staged since the last upload go to the device: one copy (per arena block).  Called before every launch.
+  cudaError_t upload() {
+    for (Arena::Block& b : g_in_arena.blocks)
+      if (b.used > b.sent) {
+        const cudaError_t e = cudaMemcpyAsync(b.d + b.sent, b.h + b.sent, b.used - b.sent, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return e;
+        b.sent = b.used;
+      }
+    return cudaSuccess;
+  }
+  // device -> caller's host array: through the pinned mirror when `dev` lies in one of this thread's buffers
+  // (asynchronous; the bytes reach `user` in sync()), else a plain copy
+  cudaError_t d2h(void* user, const void* dev, size_t bytes) {
+    for (Arena* a : {&g_out_arena, &g_in_arena})
+      for (const Arena::Block& b : a->blocks)
+        if ((const uint8_t*)dev >= b.d && (const uint8_t*)dev + bytes <= b.d + b.cap) {
+          uint8_t* m = b.h + ((const uint8_t*)dev - b.d);
+          pending.push_back({user, m, bytes});
+          return cudaMemcpyAsync(m, dev, bytes, cudaMemcpyDeviceToHost, st);
+        }
+    return cudaMemcpyAsync(user, dev, bytes, cudaMemcpyDeviceToHost, st);
+  }
+  cudaError_t sync() {
+    const cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) return e;
-    *out = (const T*)d;
-    return cudaMemcpyAsync(d, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
+    for (const Pending& p : pending) std::memcpy(p.user, p.mirror, p.bytes);
+    pending.clear();
+    return cudaSuccess;
   }
 };
 }  // namespace
@@ -690,13 +785,14 @@ orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* des
   a.n_pairs = n_pairs; a.cap = cap;
   CU(sg.in(grid_bounds, 6, on_device, &a.gb));                  // Frame 2's bounds and inverse cell sizes, src/Frame.cc:207-213
   a.ratio = nnratio; a.window = (float)window; a.checkOri = check_orientation;
+  CU(sg.upload());
   g_launches += launch_search_init(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(prev_xy, a.prev, pc * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(matches12, a.m12, pc * 4));
+    CU(sg.d2h(n_matches, a.nm, np * 4));
+    CU(sg.d2h(prev_xy, a.prev, pc * 8));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -719,12 +815,13 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
   CU(sg.alloc((void**)&a.topk, pc * 8 * sizeof(uint32_t)));
   a.n_pairs = n_pairs; a.cap = cap; a.th = th; a.ratio = nnratio; a.checkOri = check_orientation; a.strict = strict_lt;
+  CU(sg.upload());
   g_launches += launch_knn_ratio(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(matches12, a.m12, pc * 4));
+    CU(sg.d2h(n_matches, a.nm, np * 4));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -748,12 +845,13 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
   if (on_device) { a.m12 = matches12; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
   a.n_pairs = n_pairs; a.cap = cap; a.th = th; a.ratio = nnratio; a.checkOri = check_orientation; a.strict = strict_lt;
+  CU(sg.upload());
   g_launches += launch_search_by_bow(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(matches12, a.m12, pc * 4));
+    CU(sg.d2h(n_matches, a.nm, np * 4));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -845,13 +943,14 @@ orbx_status orbx_bow_transform_batch(const orbx_vocabulary* voc, const uint8_t* 
     CU(sg.alloc((void**)&a.bow_val, fc * 8)); CU(sg.alloc((void**)&a.bow_count, nf * 4));
   }
   a.n_frames = n_frames; a.cap = cap;
+  CU(sg.upload());
   g_launches += launch_bow_transform(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(word_of, a.word_of, fc * 4, cudaMemcpyDeviceToHost, st)); CU(cudaMemcpyAsync(node_of, a.node_of, fc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(bow_word, a.bow_word, fc * 4, cudaMemcpyDeviceToHost, st)); CU(cudaMemcpyAsync(bow_val, a.bow_val, fc * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(bow_count, a.bow_count, nf * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(word_of, a.word_of, fc * 4)); CU(sg.d2h(node_of, a.node_of, fc * 4));
+    CU(sg.d2h(bow_word, a.bow_word, fc * 4)); CU(sg.d2h(bow_val, a.bow_val, fc * 8));
+    CU(sg.d2h(bow_count, a.bow_count, nf * 4));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -877,9 +976,9 @@ orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uin
   CU(sg.in(F12, np * 9, on_device, &a.F12)); CU(sg.in(pose2, np * 12, on_device, &a.pose2)); CU(sg.in(Cw, np * 3, on_device, &a.Cw));
   CU(sg.in(cam2, np * 4, on_device, &a.cam2));
   if (on_device) {
-    CU(cudaMemcpyAsync(a.scale2, scale_factors2, nlevels * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(a.sigma2_2, level_sigma2_2, nlevels * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(a.scale2, scale_factors2, nlevels * sizeof(float)));
+    CU(sg.d2h(a.sigma2_2, level_sigma2_2, nlevels * sizeof(float)));
+    CU(sg.sync());
   } else {
     std::memcpy(a.scale2, scale_factors2, nlevels * sizeof(float)); std::memcpy(a.sigma2_2, level_sigma2_2, nlevels * sizeof(float));
   }
@@ -887,12 +986,13 @@ orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uin
   if (on_device) { a.m12 = matches12; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
   a.n_pairs = n_pairs; a.cap = cap; a.onlyStereo = only_stereo; a.checkOri = check_orientation;
+  CU(sg.upload());
   g_launches += launch_search_triangulation(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(matches12, a.m12, pc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(matches12, a.m12, pc * 4));
+    CU(sg.d2h(n_matches, a.nm, np * 4));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -941,9 +1041,10 @@ orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* d
   CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st)); CU(fetch_levels(a.inv_sigma2, inv_level_sigma2, nlevels, on_device, st));
   a.n_problems = n_kfs; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.mode = sim3_variant ? (2 | 4 | 16) : (2 | 4 | 8); a.th_dist = 50;   // TH_LOW; :1019 divides 1.0 by z in double, :862 in float
   a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = bf; a.log_scale = log_scale_factor; a.th = th;
+  CU(sg.upload());
   g_launches += launch_project_search(a, st);
   CU(cudaGetLastError());
-  if (!on_device) { CU(cudaMemcpyAsync(best_idx, a.best, mc * 4, cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+  if (!on_device) { CU(sg.d2h(best_idx, a.best, mc * 4)); CU(sg.sync()); }
   return ORBX_OK;
 }
 
@@ -996,7 +1097,9 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
     for (int l = 0; l < kMaxLevels; ++l) a.inv_sigma2[l] = 1.f;
     a.n_problems = n_pairs; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.mode = 1 | 16; a.th_dist = 100;   // TH_HIGH
     a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = 0.f; a.log_scale = log_scale_factor; a.th = th;
+    CU(sg.upload());
     g_launches += launch_project_search(a, st);
+    CU(sg.upload());
     g_launches += launch_scatter_matches(d_best[pass], d_idx[pass], d_m[pass], mcap, cap, n_pairs, d_vn[pass], st);
   }
   Sim3AgreeArgs g;
@@ -1004,12 +1107,13 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
   if (on_device) { g.matches12 = matches12; g.nfound = n_found; }
   else { CU(sg.alloc((void**)&g.matches12, kc * 4)); CU(sg.alloc((void**)&g.nfound, np * 4)); }
   CU(cudaMemsetAsync(g.nfound, 0, np * 4, st));
+  CU(sg.upload());
   g_launches += launch_sim3_agree(g, n_pairs, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(matches12, g.matches12, kc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_found, g.nfound, np * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(matches12, g.matches12, kc * 4));
+    CU(sg.d2h(n_found, g.nfound, np * 4));
+    CU(sg.sync());
   }
   (void)n2;
   return ORBX_OK;
@@ -1050,12 +1154,13 @@ orbx_status orbx_search_projection_ordered_batch(const orbx_keypoint* kps_un, co
   CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st));
   a.n_problems = n_problems; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.reloc = relocalisation ? 1 : 0; a.th_dist = max_dist;
   a.checkOri = check_orientation ? 1 : 0; a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.log_scale = log_scale_factor; a.th = th;
+  CU(sg.upload());
   g_launches += launch_project_match_ordered(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(assigned, a.assigned, kc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_matches, a.nm, np * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(assigned, a.assigned, kc * 4));
+    CU(sg.d2h(n_matches, a.nm, np * 4));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -1076,12 +1181,13 @@ orbx_status orbx_distinctive_descriptors_batch(const uint8_t* desc, const int* c
     if (best_desc) { CU(sg.alloc((void**)&a.best_desc, np * 32)); CU(cudaMemcpyAsync(a.best_desc, best_desc, np * 32, cudaMemcpyHostToDevice, st)); }
   }
   a.n_points = n_points; a.kcap = kcap;
+  CU(sg.upload());
   g_launches += launch_distinctive(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(best_idx, a.best_idx, np * 4, cudaMemcpyDeviceToHost, st));
-    if (best_desc) CU(cudaMemcpyAsync(best_desc, a.best_desc, np * 32, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(best_idx, a.best_idx, np * 4));
+    if (best_desc) CU(sg.d2h(best_desc, a.best_desc, np * 32));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -1103,14 +1209,15 @@ orbx_status orbx_undistort_grid_batch(const orbx_keypoint* kps, const int* n, in
     CU(sg.alloc((void**)&a.cell_start, cells * sizeof(int))); CU(sg.alloc((void**)&a.items, fc * sizeof(int)));
   }
   a.n_frames = n_frames; a.cap = cap; a.cols = cols; a.rows = rows; a.cam = *camera;
+  CU(sg.upload());
   g_launches += launch_undistort_grid(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(kps_un, a.kun, fc * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(bounds, a.bounds, 6 * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(cell_start, a.cell_start, cells * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(cell_items, a.items, fc * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(kps_un, a.kun, fc * sizeof(orbx_keypoint)));
+    CU(sg.d2h(bounds, a.bounds, 6 * sizeof(float)));
+    CU(sg.d2h(cell_start, a.cell_start, cells * sizeof(int)));
+    CU(sg.d2h(cell_items, a.items, fc * sizeof(int)));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -1137,12 +1244,13 @@ orbx_status orbx_features_in_area_batch(const orbx_keypoint* kps_un, const int* 
   if (on_device) { a.out_idx = out_idx; a.out_cnt = out_cnt; }
   else { CU(sg.alloc((void**)&a.out_idx, nq * qcap * sizeof(int))); CU(sg.alloc((void**)&a.out_cnt, nq * sizeof(int))); }
   a.cap = cap; a.n_queries = n_queries; a.qcap = qcap;
+  CU(sg.upload());
   g_launches += launch_features_in_area(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(out_idx, a.out_idx, nq * qcap * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(out_cnt, a.out_cnt, nq * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(out_idx, a.out_idx, nq * qcap * sizeof(int)));
+    CU(sg.d2h(out_cnt, a.out_cnt, nq * sizeof(int)));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -1176,16 +1284,17 @@ orbx_status orbx_search_projection_batch(const orbx_keypoint* kps, const uint8_t
   a.n_pairs = n_frames; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels;
   CU(sg.in(grid_bounds, 6, on_device, &a.gb)); a.th = th; a.ratio = nnratio;
   for (int i = 0; i < kMaxLevels; ++i) a.scale[i] = 1.f;
-  if (on_device) CU(cudaMemcpyAsync(a.scale, scale_factors, sizeof(float) * nlevels, cudaMemcpyDeviceToHost, st));
+  if (on_device) CU(sg.d2h(a.scale, scale_factors, sizeof(float) * nlevels));
   else std::memcpy(a.scale, scale_factors, sizeof(float) * nlevels);
-  if (on_device) CU(cudaStreamSynchronize(st));
+  if (on_device) CU(sg.sync());
+  CU(sg.upload());
   g_launches += launch_search_projection(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(assigned, a.assigned, fc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_matches, a.nm, nf * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(frame_obs, a.frameObs, fc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(assigned, a.assigned, fc * 4));
+    CU(sg.d2h(n_matches, a.nm, nf * 4));
+    CU(sg.d2h(frame_obs, a.frameObs, fc * 4));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
@@ -1221,15 +1330,16 @@ orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const u
   CU(sg.in(grid_bounds, 6, on_device, &a.gb));
   a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = bf; a.th = th;
   for (int i = 0; i < kMaxLevels; ++i) a.scale[i] = 1.f;
-  if (on_device) { CU(cudaMemcpyAsync(a.scale, scale_factors, sizeof(float) * nlevels, cudaMemcpyDeviceToHost, st)); CU(cudaStreamSynchronize(st)); }
+  if (on_device) { CU(sg.d2h(a.scale, scale_factors, sizeof(float) * nlevels)); CU(sg.sync()); }
   else std::memcpy(a.scale, scale_factors, sizeof(float) * nlevels);
+  CU(sg.upload());
   g_launches += launch_search_projection_frame(a, st);
   CU(cudaGetLastError());
   if (!on_device) {
-    CU(cudaMemcpyAsync(assigned, a.assigned, fc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(n_matches, a.nm, nf * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(frame_obs, a.frameObs, fc * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sg.d2h(assigned, a.assigned, fc * 4));
+    CU(sg.d2h(n_matches, a.nm, nf * 4));
+    CU(sg.d2h(frame_obs, a.frameObs, fc * 4));
+    CU(sg.sync());
   }
   return ORBX_OK;
 }
