@@ -462,9 +462,13 @@ class ORBmatcher:
             pr[:] = pv[p, :n1[p]]
         return [int(v) for v in nm], [m12[p, :n1[p]].copy() for p in range(npairs)]
 
-    def SearchByProjection(self, F, uRight, scale_factors, mp, th=1.0, frame_obs=None):
+    def SearchByProjection(self, F, uRight, scale_factors, mp, th=1.0, frame_obs=None, replicas=1):
         """SearchByProjection(Frame&, const vector<MapPoint*>&, th): mp is a dict of per-map-point arrays
-        inview, projx, projy, projxr, level, viewcos, desc (m x 32), obs.  Returns (nmatches, assigned, frame_obs)."""
+        inview, projx, projy, projxr, level, viewcos, desc (m x 32), obs.  Returns (nmatches, assigned, frame_obs).
+        replicas > 1 submits the same problem that many times in one call (the many-frames-per-launch form) and returns
+        the lists of all results."""
+        if replicas > 1:
+            return self._projection_replicas(F, uRight, scale_factors, mp, th, frame_obs, replicas)
         k = np.ascontiguousarray(F.mvKeysUn); d = np.ascontiguousarray(F.mDescriptors, np.uint8)
         n, m = len(k), len(mp["level"])
         cap, mcap = max(n, 1), max(m, 1)
@@ -480,6 +484,25 @@ class ORBmatcher:
                                                   a["viewcos"].ctypes.data, a["desc"].ctypes.data, a["obs"].ctypes.data, cm.ctypes.data,
                                                   mcap, th, self.mfNNratio, fo.ctypes.data, assigned.ctypes.data, nm.ctypes.data, 0, None))
         return int(nm[0]), assigned[:n].copy(), fo[:n].copy()
+
+    def _projection_replicas(self, F, uRight, scale_factors, mp, th, frame_obs, P):
+        k = np.ascontiguousarray(F.mvKeysUn); d = np.ascontiguousarray(F.mDescriptors, np.uint8)
+        n, m = len(k), len(mp["level"])
+        cap, mcap = max(n, 1), max(m, 1)
+        rep = lambda a: np.ascontiguousarray(np.broadcast_to(a, (P,) + a.shape))
+        ur = rep(np.ascontiguousarray(uRight, np.float32)); sc = np.ascontiguousarray(scale_factors, np.float32)
+        fo = rep(np.full(cap, -1, np.int32) if frame_obs is None else np.ascontiguousarray(frame_obs, np.int32)).copy()
+        a = {key: rep(np.ascontiguousarray(mp[key], dt)) for key, dt in [("inview", np.uint8), ("projx", np.float32), ("projy", np.float32),
+             ("projxr", np.float32), ("level", np.int32), ("viewcos", np.float32), ("desc", np.uint8), ("obs", np.int32)]}
+        kk, dd = rep(k), rep(d)
+        cn = np.full(P, n, np.int32); cm = np.full(P, m, np.int32)
+        assigned = np.zeros((P, cap), np.int32); nm = np.zeros(P, np.int32)
+        _check(lib().orbx_search_projection_batch(kk.ctypes.data, dd.ctypes.data, ur.ctypes.data, cn.ctypes.data, P, cap, F.grid_bounds.ctypes.data,
+                                                  sc.ctypes.data, len(sc), a["inview"].ctypes.data, a["projx"].ctypes.data,
+                                                  a["projy"].ctypes.data, a["projxr"].ctypes.data, a["level"].ctypes.data,
+                                                  a["viewcos"].ctypes.data, a["desc"].ctypes.data, a["obs"].ctypes.data, cm.ctypes.data,
+                                                  mcap, th, self.mfNNratio, fo.ctypes.data, assigned.ctypes.data, nm.ctypes.data, 0, None))
+        return [int(v) for v in nm], [assigned[p, :n].copy() for p in range(P)], [fo[p, :n].copy() for p in range(P)]
 
     def SearchByProjectionFrame(self, F, uRight, scale_factors, Rcw, tcw, cam, last, th=15.0, mode=0, frame_obs=None):
         """SearchByProjection(Frame& Current, const Frame& Last, th, bMono).  cam = (fx, fy, cx, cy, bf); last is a dict

@@ -398,33 +398,59 @@ __device__ __forceinline__ int grid_sort(const orbx_keypoint* k, int n, float mi
   return carry;
 }
 
+// DSM: the frame's descriptors are copied to shared memory first (they fit for the usual 1000-2000 features); a candidate's
+// descriptor then costs a shared-memory read instead of a dependent L2 round trip per map point - with ONE frame per call
+// (the SLAM loop's pattern) the kernel is a single warp walking the map points in order and those round trips were its time.
+// The fields of map point i + 1 are fetched while point i is processed.
+template <bool DSM>
 __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
   float2* sxy = reinterpret_cast<float2*>(smem);                       // [cap] sorted by cell
   uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);          // [cap] octave<<28 | cell<<16 | index
-  int* soff = reinterpret_cast<int*>(smeta + a.cap);                   // [kGridCells + 1] cell c = [soff[c], soff[c+1])
+  int* soff = reinterpret_cast<int*>(smeta + a.cap);                   // [kGridCells + 2] cell c = [soff[c+1], soff[c+2])
+  uint32_t* sdesc = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(soff + kGridCells + 2) + 15) & ~(uintptr_t)15);  // DSM: [cap][8]
   const int p = blockIdx.x, lane = threadIdx.x;
   const int n = a.n[p], m = a.m[p];
   const orbx_keypoint* k = a.k + (size_t)p * a.cap;
-  const uint32_t* d = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
+  const uint32_t* dg = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
   const float* uRight = a.uRight + (size_t)p * a.cap;
   int* frameObs = a.frameObs + (size_t)p * a.cap;
   int* assigned = a.assigned + (size_t)p * a.cap;
   const size_t mo = (size_t)p * a.mcap;
 
   for (int i = lane; i < n; i += 32) assigned[i] = -1;
+  if (DSM) {
+    const uint4* src = reinterpret_cast<const uint4*>(dg);
+    uint4* dst = reinterpret_cast<uint4*>(sdesc);
+    for (int i = lane; i < n * 2; i += 32) dst[i] = __ldg(src + i);
+  }
+  const uint32_t* d = DSM ? sdesc : dg;
   const float minX = a.gb[0], minY = a.gb[2], invW = a.gb[4], invH = a.gb[5];
   const int n_in_grid = grid_sort(k, n, minX, minY, invW, invH, sxy, smeta, soff, lane);
   const int* cstart = soff + 1;                                         // cell c = [cstart[c], cstart[c+1]); the last cell ends at n_in_grid
 
+  // fields of one map point: lanes 0..7 hold one descriptor word each, every lane the scalars
+  struct MP { int inView, level; float viewCos, x, y, xr; uint32_t dw; };
+  auto fetch = [&](int i) {
+    MP q;
+    q.inView = i < m ? a.inView[mo + i] : 0;
+    q.level = i < m ? a.level[mo + i] : 0;
+    q.viewCos = i < m ? a.viewCos[mo + i] : 0.f;
+    q.x = i < m ? a.projX[mo + i] : 0.f; q.y = i < m ? a.projY[mo + i] : 0.f; q.xr = i < m ? a.projXR[mo + i] : 0.f;
+    q.dw = (i < m && lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (mo + i) * 32) + lane) : 0u;
+    return q;
+  };
   int nm = 0;
+  MP nx = fetch(0);
   for (int iMP = 0; iMP < m; ++iMP) {
-    if (!a.inView[mo + iMP]) continue;
-    const int lvl = min(max(a.level[mo + iMP], 0), a.nlevels - 1);
-    float r = ((double)a.viewCos[mo + iMP] > 0.998) ? 2.5f : 4.0f;
+    const MP c = nx;
+    nx = fetch(iMP + 1);
+    if (!c.inView) continue;
+    const int lvl = min(max(c.level, 0), a.nlevels - 1);
+    float r = ((double)c.viewCos > 0.998) ? 2.5f : 4.0f;
     if (a.th != 1.0f) r = __fmul_rn(r, a.th);
     const float R = __fmul_rn(r, a.scale[lvl]);
-    const float x = a.projX[mo + iMP], y = a.projY[mo + iMP];
+    const float x = c.x, y = c.y;
     // GetFeaturesInArea's cell window, src/Frame.cc:332-346: (x - mnMinX -+ r) * inv, left to right
     const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, minX), R), invW)));
     if (cx0 >= 64) continue;
@@ -434,10 +460,10 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
     if (cy0 >= 48) continue;
     const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, minY), R), invH)));
     if (cy1 < 0) continue;
-    const float xr = a.projXR[mo + iMP];
+    const float xr = c.xr;
     uint32_t q[8];
 #pragma unroll
-    for (int w = 0; w < 8; ++w) q[w] = __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (mo + iMP) * 32) + w);
+    for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
     unsigned long long k1 = ~0ull, k2 = ~0ull;
     for (int ix = cx0; ix <= cx1; ++ix) {
       const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
@@ -481,9 +507,17 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
 }
 
 int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
-  const size_t smem = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_search_projection<<<a.n_pairs, 32, smem, st>>>(a);
+  const size_t base = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
+  const size_t with_desc = ((base + 15) & ~(size_t)15) + (size_t)a.cap * 32;
+  // latency mode (a few frames per call): one warp per SM anyway, so spend the shared memory on the descriptors;
+  // throughput mode keeps the small footprint (6 CTAs per SM)
+  if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
+    cudaFuncSetAttribute(k_search_projection<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)with_desc);
+    k_search_projection<true><<<a.n_pairs, 32, with_desc, st>>>(a);
+  } else {
+    if (base > 48 * 1024) cudaFuncSetAttribute(k_search_projection<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)base);
+    k_search_projection<false><<<a.n_pairs, 32, base, st>>>(a);
+  }
   return 1;
 }
 
@@ -493,16 +527,18 @@ int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
 // Same structure as K8.  Camera-frame coordinates follow OpenCV's small-matrix gemm (float products
 // and sums, left to right, + t; pinned against cv2.gemm in tests/test_oracle_cv2.py).  The rotation
 // histogram is applied after the ordered pass from a per-match event list.
+template <bool DSM>
 __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
   float2* sxy = reinterpret_cast<float2*>(smem);
   uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);
   int* soff = reinterpret_cast<int*>(smeta + a.cap);
+  uint32_t* sdesc = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(soff + kGridCells + 2) + 15) & ~(uintptr_t)15);   // DSM: [cap][8], see K8
   __shared__ int s_hist[kHisto];
   const int p = blockIdx.x, lane = threadIdx.x;
   const int n = a.n[p], nLast = a.nLast[p], mode = a.mode[p];
   const orbx_keypoint* k = a.k + (size_t)p * a.cap;
-  const uint32_t* d = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
+  const uint32_t* dg = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
   const float* uRight = a.uRight + (size_t)p * a.cap;
   int* frameObs = a.frameObs + (size_t)p * a.cap;
   int* assigned = a.assigned + (size_t)p * a.cap;
@@ -512,24 +548,65 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
 
   for (int i = lane; i < n; i += 32) assigned[i] = -1;
   if (lane < kHisto) s_hist[lane] = 0;
+  if (DSM) {
+    const uint4* src = reinterpret_cast<const uint4*>(dg);
+    uint4* dst = reinterpret_cast<uint4*>(sdesc);
+    for (int i = lane; i < n * 2; i += 32) dst[i] = __ldg(src + i);
+  }
+  const uint32_t* d = DSM ? sdesc : dg;
   const float minX = a.gb[0], maxX = a.gb[1], minY = a.gb[2], maxY = a.gb[3], invW = a.gb[4], invH = a.gb[5];
   const int n_in_grid = grid_sort(k, n, minX, minY, invW, invH, sxy, smeta, soff, lane);
   const int* cstart = soff + 1;
+  float Tr[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) Tr[i] = T[i];
 
+  // The last frame's keypoints that carry a map point are a minority (a few hundred of ~2000): their indices come from
+  // ballots over 32 validity flags at a time (the next block's flags are loaded one block ahead), and the fields of the
+  // next valid one are fetched while the current one is processed.  Lanes 0..7 hold one descriptor word each.
+  struct LP { int octave; float X0, X1, X2; uint32_t dw; };
+  auto fetch = [&](int i) {
+    LP q;
+    const bool ok = i >= 0;
+    q.octave = ok ? a.lastOctave[lo + i] : 0;
+    q.X0 = ok ? a.lastXw[(lo + i) * 3] : 0.f; q.X1 = ok ? a.lastXw[(lo + i) * 3 + 1] : 0.f; q.X2 = ok ? a.lastXw[(lo + i) * 3 + 2] : 0.f;
+    q.dw = (ok && lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (lo + i) * 32) + lane) : 0u;
+    return q;
+  };
+  int vbase = 0;
+  uint32_t vmask = __ballot_sync(0xffffffffu, lane < nLast && a.lastValid[lo + lane]);
+  uint32_t vnext = __ballot_sync(0xffffffffu, 32 + lane < nLast && a.lastValid[lo + 32 + lane]);
+  auto pop = [&]() {                                   // next valid index in ascending order, -1 at the end (warp-uniform)
+    while (vmask == 0u) {
+      vbase += 32;
+      if (vbase >= nLast) return -1;
+      vmask = vnext;
+      vnext = __ballot_sync(0xffffffffu, vbase + 32 + lane < nLast && a.lastValid[lo + vbase + 32 + lane]);
+    }
+    const int b = __ffs((int)vmask) - 1;
+    vmask &= vmask - 1u;
+    return vbase + b;
+  };
   int nm = 0;
-  for (int i = 0; i < nLast; ++i) {
-    if (!a.lastValid[lo + i]) continue;
-    const float X0 = a.lastXw[(lo + i) * 3], X1 = a.lastXw[(lo + i) * 3 + 1], X2 = a.lastXw[(lo + i) * 3 + 2];
+  int i = pop();
+  LP nx = fetch(i);
+  while (i >= 0) {
+    const LP c = nx;
+    const int inext = pop();
+    nx = fetch(inext);
+    const int icur = i;
+    i = inext;
+    const float X0 = c.X0, X1 = c.X1, X2 = c.X2;
     float c3[3];
 #pragma unroll
     for (int r = 0; r < 3; ++r)
-      c3[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[3 * r], X0), __fmul_rn(T[3 * r + 1], X1)), __fmul_rn(T[3 * r + 2], X2)), T[9 + r]);
+      c3[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(Tr[3 * r], X0), __fmul_rn(Tr[3 * r + 1], X1)), __fmul_rn(Tr[3 * r + 2], X2)), Tr[9 + r]);
     const float invzc = (float)(1.0 / (double)c3[2]);
     if (invzc < 0.f) continue;
     const float u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, c3[0]), invzc), a.cx), v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, c3[1]), invzc), a.cy);
     if (u < minX || u > maxX || v < minY || v > maxY) continue;                        // src/ORBmatcher.cc:1373-1376
     if (!(u == u) || !(v == v)) continue;                                              // NaN never passes the reference's window either
-    const int oct = min(max(a.lastOctave[lo + i], 0), a.nlevels - 1);
+    const int oct = min(max(c.octave, 0), a.nlevels - 1);
     const float R = __fmul_rn(a.th, a.scale[oct]);
     const int l_lo = mode == 1 ? oct : (mode == 2 ? 0 : oct - 1), l_hi = mode == 1 ? 99 : (mode == 2 ? oct : oct + 1);
     const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, minX), R), invW)));
@@ -543,7 +620,7 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
     const float ur_pred = __fsub_rn(u, __fmul_rn(a.bf, invzc));
     uint32_t q[8];
 #pragma unroll
-    for (int w = 0; w < 8; ++w) q[w] = __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (lo + i) * 32) + w);
+    for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
     unsigned long long best = ~0ull;
     for (int ix = cx0; ix <= cx1; ++ix) {
       const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
@@ -567,10 +644,10 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
     const unsigned glo = __reduce_min_sync(0xffffffffu, hi1 == ghi ? lo1 : 0xffffffffu);
     const int bestIdx = (int)(glo & 0xFFFF);
     if (lane == 0) {
-      assigned[bestIdx] = i;
-      frameObs[bestIdx] = a.mpObs[lo + i];
+      assigned[bestIdx] = icur;
+      frameObs[bestIdx] = a.mpObs[lo + icur];
       int bin = 0;
-      if (a.checkOri) { bin = rot_bin(a.lastAngle[lo + i], k[bestIdx].angle); s_hist[bin] += 1; }
+      if (a.checkOri) { bin = rot_bin(a.lastAngle[lo + icur], k[bestIdx].angle); s_hist[bin] += 1; }
       events[nm] = (bin << 16) | bestIdx;
     }
     ++nm;
@@ -591,9 +668,15 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
 }
 
 int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st) {
-  const size_t smem = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_projection_frame, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_search_projection_frame<<<a.n_pairs, 32, smem, st>>>(a);
+  const size_t base = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
+  const size_t with_desc = ((base + 15) & ~(size_t)15) + (size_t)a.cap * 32;
+  if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {    // latency mode, see launch_search_projection
+    cudaFuncSetAttribute(k_search_projection_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)with_desc);
+    k_search_projection_frame<true><<<a.n_pairs, 32, with_desc, st>>>(a);
+  } else {
+    if (base > 48 * 1024) cudaFuncSetAttribute(k_search_projection_frame<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)base);
+    k_search_projection_frame<false><<<a.n_pairs, 32, base, st>>>(a);
+  }
   return 1;
 }
 

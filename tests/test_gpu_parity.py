@@ -405,6 +405,9 @@ def test_search_by_projection_local_map(gx, oracle, th):
     gn, gas, gfo = gx.ORBmatcher(0.8, True).SearchByProjection(gx.Frame(kf, df, w, h), ur[0, :n], scale, mp, th, frame_obs)
     assert gn == rn and np.array_equal(gas, ras) and np.array_equal(gfo, rfo)
     assert rn > 300
+    if th == 1.0:       # the many-frames-per-launch instantiation (descriptors stay in global memory): 160 copies in one call
+        ns, ass, fos = gx.ORBmatcher(0.8, True).SearchByProjection(gx.Frame(kf, df, w, h), ur[0, :n], scale, mp, th, frame_obs, replicas=160)
+        assert all(v == rn for v in ns) and all(np.array_equal(x, ras) for x in ass) and all(np.array_equal(x, rfo) for x in fos)
 
 
 @pytest.mark.parametrize("mode,th,ori", [(0, 15.0, True), (1, 7.0, True), (2, 15.0, False)])
