@@ -111,6 +111,17 @@ orbx_status orbx_extract_batch(orbx_extractor* ext, const uint8_t* imgs, int n, 
 orbx_status orbx_fetch_results(orbx_extractor* ext, int first_slot, int n, orbx_keypoint* kps,
                                uint8_t* desc, int* counts, int cap, int dst_on_device, void* stream);
 
+/* Where the results of slots first_slot, first_slot + 1, ... live ON THE DEVICE, so that the matcher / Frame entry points
+ * below can read them in place (on_device = 1) instead of being handed a copy: what operator() returned for a slot
+ * (src/ORBextractor.cc:1043-1105) is kps_dev[(slot - first_slot) * cap + i], desc_dev[((slot - first_slot) * cap + i) * 32],
+ * i < counts_dev[slot - first_slot], with *cap = orbx_max_keypoints().  Consecutive slots are a ready-made batch: e.g. the two
+ * frames of ORBmatcher::SearchForInitialization extracted into slots 0 and 1 go to orbx_search_init_batch as
+ * (kps_dev, desc_dev, counts_dev) and (kps_dev + cap, desc_dev + cap * 32, counts_dev + 1); orbx_undistort_grid_batch takes
+ * kps_dev / counts_dev as they are.  The pointers stay valid until the handle is destroyed; their contents are those of
+ * the last extraction into the slot (order your calls on one stream, or synchronise).  Any output may be NULL. */
+orbx_status orbx_slot_results(const orbx_extractor* ext, int first_slot, const orbx_keypoint** kps_dev,
+                              const uint8_t** desc_dev, const int** counts_dev, int* cap);
+
 /* ORBextractor::mvImagePyramid[level] (public member, include/ORBextractor.h:85; read by
  * src/Frame.cc:473,563,575,580): device pointer to the level's inner ROI (w x h, rows `stride`
  * bytes apart; the 19-px reflect-101 border lies around it). */
@@ -425,6 +436,13 @@ orbx_status orbx_stream_synchronize(void* stream);
  * concurrently on the GPU, whereas the legacy default stream (NULL) would serialise them. */
 orbx_status orbx_stream_create(int device, void** stream);
 void orbx_stream_destroy(void* stream);
+
+/* Page-locked host memory for callers that do not link the CUDA runtime (no counterpart in the reference): images handed
+ * to orbx_extract_batch from such a buffer are copied asynchronously at full PCIe rate (pageable memory is staged by the
+ * driver and blocks the call).  write_combined = 1 asks for write-combined pages: faster for the GPU to read on some
+ * hosts, very slow for the CPU to READ - only for upload buffers the CPU just fills. */
+orbx_status orbx_host_alloc(size_t bytes, int write_combined, void** out);
+void orbx_host_free(void* p);
 
 /* Message of the last failing call on the calling thread ("" if none). */
 const char* orbx_last_error_string(void);

@@ -87,6 +87,10 @@ def lib():
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_stream_synchronize.argtypes = [C.c_void_p]
+        L.orbx_host_alloc.argtypes = [C.c_size_t, C.c_int, C.c_void_p]
+        L.orbx_host_free.argtypes = [C.c_void_p]
+        L.orbx_host_free.restype = None
+        L.orbx_slot_results.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_stream_create.argtypes = [C.c_int, C.c_void_p]
         L.orbx_stream_destroy.argtypes = [C.c_void_p]
         L.orbx_stream_destroy.restype = None
@@ -134,6 +138,26 @@ def _ptr(a):
 
 def _on_device(a):
     return 0 if isinstance(a, np.ndarray) else int(a.is_cuda)
+
+
+class HostBuffer:
+    """Page-locked host memory from orbx_host_alloc as a numpy uint8 array (`.array`); write_combined for upload-only buffers."""
+
+    def __init__(self, nbytes, write_combined=False):
+        self.ptr = C.c_void_p()
+        _check(lib().orbx_host_alloc(int(nbytes), int(write_combined), C.byref(self.ptr)))
+        self.array = np.ctypeslib.as_array((C.c_uint8 * int(nbytes)).from_address(self.ptr.value))
+
+    def close(self):
+        if self.ptr:
+            self.array = None
+            lib().orbx_host_free(self.ptr); self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def kernel_launch_count():
@@ -250,6 +274,13 @@ class ORBextractor:
         self.fetch_into(first_slot, n, kps, desc, cnt)
         _sync(self.device)
         return [(kps[i, :cnt[i]].copy(), desc[i, :cnt[i]].copy()) for i in range(n)]
+
+    def slot_results(self, first_slot=0):
+        """Device addresses (ints) of the keypoints, descriptors and counts of slots first_slot.., and the row capacity:
+        the in-place route into the matcher entry points (on_device = 1), no copy."""
+        k, d, c, cap = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_int()
+        _check(lib().orbx_slot_results(self._h, first_slot, C.byref(k), C.byref(d), C.byref(c), C.byref(cap)))
+        return k.value, d.value, c.value, cap.value
 
     def set_profiling(self, enable=True):
         _check(lib().orbx_set_profiling(self._h, int(enable)))

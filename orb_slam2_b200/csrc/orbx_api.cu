@@ -537,6 +537,18 @@ orbx_status orbx_extract(orbx_extractor* e, const uint8_t* img, int w, int h, in
   return ORBX_OK;
 }
 
+orbx_status orbx_slot_results(const orbx_extractor* e, int first_slot, const orbx_keypoint** kps_dev, const uint8_t** desc_dev,
+                              const int** counts_dev, int* cap) {
+  if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
+  if (first_slot < 0 || first_slot >= e->max_batch) return fail(ORBX_ERR_BAD_ARG, "slot out of range");
+  const size_t kc = (size_t)e->kp_cap;
+  if (kps_dev) *kps_dev = e->L.kps + first_slot * kc;
+  if (desc_dev) *desc_dev = e->L.desc + first_slot * kc * 32;
+  if (counts_dev) *counts_dev = e->L.nkp + first_slot;
+  if (cap) *cap = e->kp_cap;
+  return ORBX_OK;
+}
+
 orbx_status orbx_pyramid_level(const orbx_extractor* e, int slot, int level, const uint8_t** dev_ptr, int* w, int* h, int* stride) {
   if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
   if (e->cur_w == 0) return fail(ORBX_ERR_STATE, "no image extracted yet");
@@ -1400,6 +1412,17 @@ orbx_status orbx_stream_create(int device, void** stream) {
 
 void orbx_stream_destroy(void* stream) {
   if (stream) cudaStreamDestroy((cudaStream_t)stream);
+}
+
+orbx_status orbx_host_alloc(size_t bytes, int write_combined, void** out) {
+  if (!out || bytes == 0) return fail(ORBX_ERR_BAD_ARG, "null argument or zero size");
+  *out = nullptr;
+  CU(cudaHostAlloc(out, bytes, write_combined ? cudaHostAllocWriteCombined : cudaHostAllocDefault));
+  return ORBX_OK;
+}
+
+void orbx_host_free(void* p) {
+  if (p) cudaFreeHost(p);
 }
 
 const char* orbx_last_error_string(void) { return g_err.c_str(); }

@@ -18,8 +18,15 @@ def probe(torch, h2d_bytes, d2h_bytes, streams=(1, 3), reps=6, dist=None, write_
     """Returns {"h2d_gbs": {nstreams: GB/s}, "d2h_gbs": {...}, "duplex_gbs": {nstreams: (h2d GB/s, d2h GB/s)}} for THIS rank,
     every figure taken while all ranks run the same copy.  Buffers are split evenly over the streams."""
     dev = torch.device("cuda", torch.cuda.current_device())
-    up_h = torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory()
-    up_h.fill_(7)
+    wc = None
+    if write_combined:                                  # upload buffer in write-combined pinned memory (orbx_host_alloc)
+        from . import api
+        wc = api.HostBuffer(h2d_bytes, write_combined=True)
+        wc.array[:] = 7
+        up_h = torch.from_numpy(wc.array)
+    else:
+        up_h = torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory()
+        up_h.fill_(7)
     up_d = torch.empty(h2d_bytes, dtype=torch.uint8, device=dev)
     dn_d = torch.zeros(d2h_bytes, dtype=torch.uint8, device=dev)
     dn_h = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
@@ -51,6 +58,9 @@ def probe(torch, h2d_bytes, d2h_bytes, streams=(1, 3), reps=6, dist=None, write_
         out["d2h_gbs"][ns] = d2h_bytes * reps / run(ns, False, True) / 1e9
         dt = run(ns, True, True)
         out["duplex_gbs"][ns] = (h2d_bytes * reps / dt / 1e9, d2h_bytes * reps / dt / 1e9)
+    del up_h
+    if wc is not None:
+        wc.close()
     return out
 
 

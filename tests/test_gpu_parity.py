@@ -923,3 +923,36 @@ def test_first_extract_on_another_host_thread(gx, oracle):
     rur, rdp, _, rm = oracle.stereo(EL, ER, okl, odl, okr, odr, cfg["bf"], cfg["fx"])
     assert int(nm[0]) == rm and np.array_equal(ur[0, :len(okl)].view(np.uint32), rur.view(np.uint32))
     lib.orbx_stream_destroy(sL); lib.orbx_stream_destroy(sR)
+
+
+def test_matchers_read_extractor_slots_in_place(gx, oracle):
+    """orbx_slot_results: the frames stay where the extractor left them on the device; UndistortKeyPoints + grid (K10) and
+    SearchForInitialization (K6) read the slots in place (on_device = 1) - no fetch, no re-upload - and give what the host route
+    and the oracle give."""
+    import ctypes as C
+    import torch
+    w, h = 640, 480
+    a, b, _ = synth.mono_pair(66, w, h)
+    G = _ext(gx, w, h, 1000, batch=2)
+    G.extract_batch(np.stack([a, b]))
+    kd, dd, cd, cap = G.slot_results(0)
+    lib = gx.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    # K10 on the slots (undistorted camera: a copy, bounds = the image) -> device outputs
+    kun = torch.empty((2, cap, 28), dtype=torch.uint8, device="cuda"); bounds = torch.empty(6, dtype=torch.float32, device="cuda")
+    cs = torch.empty((2, 64 * 48 + 1), dtype=torch.int32, device="cuda"); ci = torch.empty((2, cap), dtype=torch.int32, device="cuda")
+    cam = (C.c_float * 9)(517.3, 516.5, 318.6, 255.3, 0, 0, 0, 0, 0)
+    assert lib.orbx_undistort_grid_batch(kd, cd, 2, cap, cam, w, h, kun.data_ptr(), bounds.data_ptr(), cs.data_ptr(), ci.data_ptr(), 1, st) == 0
+    # K6: frame 1 = slot 0, frame 2 = slot 1, all device pointers
+    prev = kun.view(torch.float32).reshape(2, cap, 7)[0, :, :2].contiguous()
+    m12 = torch.empty(cap, dtype=torch.int32, device="cuda"); nm = torch.empty(1, dtype=torch.int32, device="cuda")
+    rc = lib.orbx_search_init_batch(kd, dd, cd, kd + cap * 28, dd + cap * 32, cd + 4, 1, cap, bounds.data_ptr(), prev.data_ptr(), 0.9, 100, 1,
+                                    m12.data_ptr(), nm.data_ptr(), 1, st)
+    assert rc == 0, lib.orbx_last_error_string()
+    torch.cuda.synchronize()
+    (k1, d1), (k2, d2) = G.fetch(0, 2)
+    p0 = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    rm12, rn, rprev = oracle.search_init(k1, d1, k2, d2, w, h, p0, 0.9, 100, True)
+    assert int(nm.cpu()[0]) == rn and np.array_equal(m12.cpu().numpy()[:len(k1)], rm12) and rn > 50
+    assert np.array_equal(prev.cpu().numpy()[:len(k1)], rprev)
+    assert bounds.cpu().tolist()[:4] == [0.0, float(w), 0.0, float(h)]

@@ -30,13 +30,14 @@ def main():
     B, w, h, cap = 256, 1241, 376, 2024
     h2d = 2 * B * w * h
     d2h = 2 * B * cap * 60 + 2 * B * 4 + 2 * B * cap * 4 + B * 4
-    res = hostfeed.probe(torch, h2d, d2h, streams=(1, 3), reps=8, dist=dist if world > 1 else None)
+    wc = "--wc" in sys.argv
+    res = hostfeed.probe(torch, h2d, d2h, streams=(1, 3), reps=8, dist=dist if world > 1 else None, write_combined=wc)
     flat = [res["h2d_gbs"][1], res["h2d_gbs"][3], res["d2h_gbs"][1], res["d2h_gbs"][3], *res["duplex_gbs"][1], *res["duplex_gbs"][3]]
     allv = hostfeed.gather(torch, dist if world > 1 else None, flat)
     if rank == 0:
         names = ["h2d_1stream", "h2d_3streams", "d2h_1stream", "d2h_3streams", "duplex1_h2d", "duplex1_d2h", "duplex3_h2d", "duplex3_d2h"]
         per_gpu = {n: [round(v[i], 2) for v in allv] for i, n in enumerate(names)}
-        line = {"probe": "bare cudaMemcpyAsync, pinned host memory, all ranks concurrently", "n_gpus": world, "h2d_bytes": h2d, "d2h_bytes": d2h,
+        line = {"probe": "bare cudaMemcpyAsync, pinned host memory%s, all ranks concurrently" % (" (upload buffer write-combined)" if wc else ""), "n_gpus": world, "h2d_bytes": h2d, "d2h_bytes": d2h,
                 "per_gpu_gbs": per_gpu, "aggregate_gbs": {n: round(sum(v), 1) for n, v in per_gpu.items()},
                 "min_per_gpu_gbs": {n: min(v) for n, v in per_gpu.items()}}
         try:
