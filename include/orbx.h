@@ -111,6 +111,17 @@ orbx_status orbx_extract_batch(orbx_extractor* ext, const uint8_t* imgs, int n, 
 orbx_status orbx_fetch_results(orbx_extractor* ext, int first_slot, int n, orbx_keypoint* kps,
                                uint8_t* desc, int* counts, int cap, int dst_on_device, void* stream);
 
+/* orbx_fetch_results with the keypoints in 8 bytes instead of the 28 of cv::KeyPoint, for callers that fetch many frames
+ * per call and are bound by the device -> host copy: packed[i*cap + j] = {x | y << 12 | response << 24 in level coordinates,
+ * angle bits << 32} of keypoint j of slot first_slot + i, level_counts[i*8 + l] = keypoints of level l (the output is
+ * level-major, src/ORBextractor.cc:1073-1103), descriptors as in orbx_fetch_results.  orbx_unpack_keypoints (host code, no
+ * device needed) rebuilds the cv::KeyPoint records - pt scaled by mvScaleFactor[level] in float, size, octave, class_id -
+ * byte for byte what orbx_fetch_results returns, plus counts[i] = the keypoint count of frame i. */
+orbx_status orbx_fetch_results_packed(orbx_extractor* ext, int first_slot, int n, uint64_t* packed, uint8_t* desc,
+                                      int* level_counts, int cap, int dst_on_device, void* stream);
+orbx_status orbx_unpack_keypoints(const orbx_params* params, const uint64_t* packed, const int* level_counts, int n_frames,
+                                  int cap, orbx_keypoint* kps, int kps_cap, int* counts);
+
 /* Where the results of slots first_slot, first_slot + 1, ... live ON THE DEVICE, so that the matcher / Frame entry points
  * below can read them in place (on_device = 1) instead of being handed a copy: what operator() returned for a slot
  * (src/ORBextractor.cc:1043-1105) is kps_dev[(slot - first_slot) * cap + i], desc_dev[((slot - first_slot) * cap + i) * 32],

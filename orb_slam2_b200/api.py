@@ -87,6 +87,8 @@ def lib():
         L.orbx_get_tables.argtypes = [C.c_void_p] * 7
         L.orbx_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_stream_synchronize.argtypes = [C.c_void_p]
+        L.orbx_fetch_results_packed.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orbx_unpack_keypoints.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_host_alloc.argtypes = [C.c_size_t, C.c_int, C.c_void_p]
         L.orbx_host_free.argtypes = [C.c_void_p]
         L.orbx_host_free.restype = None
@@ -266,6 +268,21 @@ class ORBextractor:
         cap = ref.shape[1] if ref is not None else self.kp_cap
         dev = _on_device(ref if ref is not None else counts)
         _check(lib().orbx_fetch_results(self._h, first_slot, n, _ptr(kps), _ptr(desc), _ptr(counts), cap, dev, stream))
+
+    def fetch_packed_into(self, first_slot, n, packed, desc, level_counts, stream=None):
+        """The 8-byte keypoint form: packed [n][cap] uint64, desc [n][cap][32], level_counts [n][8] (arrays / tensors, host or device)."""
+        ref = packed if packed is not None else desc
+        cap = ref.shape[1] if ref is not None else self.kp_cap
+        dev = _on_device(ref if ref is not None else level_counts)
+        _check(lib().orbx_fetch_results_packed(self._h, first_slot, n, _ptr(packed), _ptr(desc), _ptr(level_counts), cap, dev, stream))
+
+    def unpack_keypoints(self, packed, level_counts, out=None, counts=None):
+        """Host arrays from fetch_packed_into -> (keypoints [n][cap] KP_DTYPE, counts [n]): the cv::KeyPoint records."""
+        n, cap = packed.shape
+        out = np.zeros((n, cap), KP_DTYPE) if out is None else out
+        counts = np.zeros(n, np.int32) if counts is None else counts
+        _check(lib().orbx_unpack_keypoints(C.byref(self.params), _ptr(packed), _ptr(level_counts), n, cap, _ptr(out), out.shape[1], _ptr(counts)))
+        return out, counts
 
     def fetch(self, first_slot=0, n=1):
         """Synchronous convenience: list of (keypoints, descriptors) per slot."""

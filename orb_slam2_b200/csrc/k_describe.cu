@@ -295,6 +295,7 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe(DeviceLayout L
     kp.octave = level;
     kp.class_id = -1;
     L.kps[oi] = kp;
+    L.kpk[oi] = make_uint2(pack_xyr(px, py, resp), __float_as_uint(angle));
   }
   __syncwarp();                                       // every lane is done with this tile, Ht and the blurred patch
   }
@@ -318,6 +319,7 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe_planes(DeviceL
                                                                          const __grid_constant__ TmaMaps tap_maps, int first_slot, int n_img,
                                                                          int ctas_per_img, int kp_per_warp, const char4* __restrict__ pattern) {
   extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint32_t s_mask[8][32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* wbase = smem + (size_t)warp * kWarpSmem2;
   uint64_t* bar = reinterpret_cast<uint64_t*>(wbase + kOffBar2);     // bar[0], bar[1]: one per stage
@@ -340,6 +342,19 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe_planes(DeviceL
   const int nk = min(kp_per_warp, total - j0);
 
   if (lane == 0) { mbar_init(bar, 1); mbar_init(bar + 1, 1); fence_barrier_init(); }
+  // byte masks of the orientation disc, per row (= lane) and word: byte b of word k is column u = -15 + 4k + b, inside the
+  // disc iff |u| <= umax[|v|]; lane 31 (no row) masks everything.  Each warp fills the table with the same values.
+  {
+    const int v = lane - kHalfPatch, av = v < 0 ? -v : v;
+    const int half = lane < 31 ? (int)((kUmaxNibbles >> (4 * (av & 15))) & 15ull) : -1;
+#pragma unroll
+    for (int k2 = 0; k2 < 8; ++k2) {
+      uint32_t mk = 0u;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) { const int u = -15 + 4 * k2 + b; if ((u < 0 ? -u : u) <= half) mk |= 0xffu << (8 * b); }
+      s_mask[k2][lane] = mk;
+    }
+  }
   __syncwarp();
   auto request = [&](const KpRef& k, int stage) {            // lane 0: both boxes of one keypoint on the stage's barrier
     uint8_t* dst = wbase + stage * kStageBytes;
@@ -370,21 +385,30 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe_planes(DeviceL
     const uint8_t* bl = raw + kOffTap;
     mbar_wait(bar + stage, (t >> 1) & 1);
 
-    // intensity-centroid moments over the radius-15 disc (see k_describe): lane = column u, predicated rows
+    // intensity-centroid moments over the radius-15 disc (src/ORBextractor.cc:77-104).  lane = ROW v of the 31 x 31 patch: its
+    // 31 bytes come as 9 aligned words, byte-aligned by funnel shifts, masked to the row's half-width umax[|v|] (s_mask, made
+    // once per CTA); two dp4a per word then give the row's sum of pixels and its sum of u * pixel (u = -15..15 as signed-byte
+    // coefficients).  m10 = sum of the latter, m01 = sum of v * row sum: ~45 instructions per keypoint instead of ~105 with
+    // one column per lane and one load per pixel.
     int m10, m01;
     {
-      const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
-      const int vlim = lane < 31 ? (int)((kUmaxNibbles >> (4 * (au & 15))) & 15ull) : -1;
-      const uint8_t* colp = raw + 15 * kMomBoxW + ((px + kEdge - 15) & 15) + 15 + (lane < 31 ? u : 0);
-      int s_all = lane < 31 ? (int)colp[0] : 0, s_v = 0;
+      const int phM = (px + kEdge - 15) & 15, sh = (phM & 3) * 8;
+      const uint32_t* rowp = reinterpret_cast<const uint32_t*>(raw + (lane < 31 ? lane : 0) * kMomBoxW + (phM & ~3));
+      uint32_t W[9];
 #pragma unroll
-      for (int v = 1; v <= kHalfPatch; ++v) {
-        const int a = colp[v * kMomBoxW], b = colp[-v * kMomBoxW];
-        asm("{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %2, %3;\n\t@p add.s32 %0, %0, %4;\n\t@p mad.lo.s32 %1, %5, %3, %1;\n\t}"
-            : "+r"(s_all), "+r"(s_v) : "r"(vlim), "r"(v), "r"(a + b), "r"(a - b));
+      for (int k2 = 0; k2 < 9; ++k2) W[k2] = rowp[k2];
+      int rsum = 0, usum = 0;
+#pragma unroll
+      for (int k2 = 0; k2 < 8; ++k2) {
+        const uint32_t dmask = __funnelshift_r(W[k2], W[k2 + 1], sh) & s_mask[k2][lane];
+        // u of the four bytes: -15 + 4 k2 + {0, 1, 2, 3}, as signed bytes (the 32nd byte, u = 16, is always masked out)
+        const int u0 = -15 + 4 * k2;
+        const uint32_t ucoef = (uint32_t)(u0 & 0xff) | ((uint32_t)((u0 + 1) & 0xff) << 8) | ((uint32_t)((u0 + 2) & 0xff) << 16) | ((uint32_t)((u0 + 3) & 0xff) << 24);
+        rsum = (int)__dp4a(dmask, 0x01010101u, (uint32_t)rsum);
+        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(usum) : "r"(dmask), "r"(ucoef));
       }
-      m10 = u * s_all;
-      m01 = s_v;
+      m10 = usum;
+      m01 = (lane - kHalfPatch) * rsum;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -422,6 +446,7 @@ __global__ void __launch_bounds__(kDescWarps * 32, 12) k_describe_planes(DeviceL
       kp.octave = level;
       kp.class_id = -1;
       L.kps[oi] = kp;
+      L.kpk[oi] = make_uint2(pack_xyr(px, py, cur.resp), __float_as_uint(angle));
     }
     __syncwarp();                                             // every lane is done with this stage
   }

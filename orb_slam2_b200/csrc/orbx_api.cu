@@ -389,6 +389,7 @@ orbx_status orbx_extractor_create(const orbx_params* params, int max_w, int max_
   ALLOC(L.lvlcnt, nb * kMaxLevels);
   ALLOC(L.nkeys, nb * kMaxLevels);
   ALLOC(L.kps, nb * e->kp_cap);
+  ALLOC(L.kpk, nb * e->kp_cap);
   ALLOC(L.desc, nb * e->kp_cap * 32);
   ALLOC(L.nkp, nb);
   ALLOC(L.err, nb);
@@ -416,7 +417,7 @@ void orbx_extractor_destroy(orbx_extractor* e) {
   cudaDeviceSynchronize();
   DeviceLayout& L = e->L;
   void* ptrs[] = {e->d_geom, e->d_taps, e->d_umax, e->d_pattern, e->d_in, L.pyr, L.blur, L.celltab, L.poolcnt, L.pool, L.okeys,
-                  L.knode, L.lvlkp, L.lvlcnt, L.nkeys, L.kps, L.desc, L.nkp, L.err, e->d_uright, e->d_depth, e->d_sad,
+                  L.knode, L.lvlkp, L.lvlcnt, L.nkeys, L.kps, L.kpk, L.desc, L.nkp, L.err, e->d_uright, e->d_depth, e->d_sad,
                   e->d_nmatch, e->d_strec, e->d_sttab};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (e->ev_ext[0][0])
@@ -511,6 +512,55 @@ orbx_status orbx_fetch_results(orbx_extractor* e, int first_slot, int n, orbx_ke
   if (kps) CU(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_keypoint), e->L.kps + first_slot * kc, kc * sizeof(orbx_keypoint),
                                 kc * sizeof(orbx_keypoint), n, kind, st));
   if (desc) CU(cudaMemcpy2DAsync(desc, (size_t)cap * 32, e->L.desc + first_slot * kc * 32, kc * 32, kc * 32, n, kind, st));
+  return ORBX_OK;
+}
+
+orbx_status orbx_fetch_results_packed(orbx_extractor* e, int first_slot, int n, uint64_t* packed, uint8_t* desc, int* level_counts, int cap,
+                                      int dst_on_device, void* stream) {
+  if (!e) return fail(ORBX_ERR_BAD_ARG, "null extractor");
+  if (n < 1 || first_slot < 0 || first_slot + n > e->max_batch) return fail(ORBX_ERR_CAPACITY, "slots exceed max_batch");
+  if ((packed || desc) && cap < e->kp_cap) return fail(ORBX_ERR_CAPACITY, "cap smaller than orbx_max_keypoints()");
+  cudaStream_t st = (cudaStream_t)stream;
+  DeviceGuard guard(e->device);
+  const cudaMemcpyKind kind = dst_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  const size_t kc = (size_t)e->kp_cap;
+  if (level_counts) CU(cudaMemcpyAsync(level_counts, e->L.lvlcnt + (size_t)first_slot * kMaxLevels, (size_t)n * kMaxLevels * sizeof(int), kind, st));
+  if (packed) CU(cudaMemcpy2DAsync(packed, (size_t)cap * 8, e->L.kpk + first_slot * kc, kc * 8, kc * 8, n, kind, st));
+  if (desc) CU(cudaMemcpy2DAsync(desc, (size_t)cap * 32, e->L.desc + first_slot * kc * 32, kc * 32, kc * 32, n, kind, st));
+  return ORBX_OK;
+}
+
+orbx_status orbx_unpack_keypoints(const orbx_params* params, const uint64_t* packed, const int* level_counts, int n_frames, int cap,
+                                  orbx_keypoint* kps, int kps_cap, int* counts) {
+  if (!params || !packed || !level_counts || !kps) return fail(ORBX_ERR_BAD_ARG, "null argument");
+  if (params->nlevels < 1 || params->nlevels > kMaxLevels || !(params->scale_factor > 1.0f) || params->nfeatures < 1 || n_frames < 1 || cap < 1 || kps_cap < 1)
+    return fail(ORBX_ERR_BAD_ARG, "bad sizes");
+  orbx_extractor tmp;                       // host tables only (scale factors exactly as the kernels use them)
+  tmp.P = *params; tmp.nlevels = params->nlevels;
+  make_tables(&tmp);
+  for (int f = 0; f < n_frames; ++f) {
+    const uint64_t* src = packed + (size_t)f * cap;
+    orbx_keypoint* dst = kps + (size_t)f * kps_cap;
+    int j = 0;
+    for (int l = 0; l < tmp.nlevels; ++l) {
+      const float scale = tmp.scale[l], size = (float)(int)(31 * tmp.scale[l]);      // src/ORBextractor.cc:845, :1095-1101
+      const int cnt = level_counts[(size_t)f * kMaxLevels + l];
+      for (int i = 0; i < cnt && j < cap; ++i, ++j) {
+        if (j >= kps_cap) return fail(ORBX_ERR_CAPACITY, "keypoint buffer too small");
+        const uint32_t key = (uint32_t)src[j], ab = (uint32_t)(src[j] >> 32);
+        orbx_keypoint kp;
+        const float px = (float)unpack_x(key), py = (float)unpack_y(key);
+        kp.x = l ? px * scale : px;
+        kp.y = l ? py * scale : py;
+        kp.size = size;
+        std::memcpy(&kp.angle, &ab, 4);
+        kp.response = (float)unpack_r(key);
+        kp.octave = l; kp.class_id = -1;
+        dst[j] = kp;
+      }
+    }
+    if (counts) counts[f] = j;
+  }
   return ORBX_OK;
 }
 

@@ -62,6 +62,7 @@ struct DeviceLayout {    // per-handle pointers handed to kernels by value
   int* lvlcnt;               // [nslots][kMaxLevels]
   int* nkeys;                // [nslots][kMaxLevels] ordered candidate count
   orbx_keypoint* kps;        // [nslots][kp_cap]
+  uint2* kpk;                // [nslots][kp_cap] the same keypoints in 8 bytes: {x | y<<12 | response<<24 (level coordinates), angle bits}; level from lvlcnt
   uint8_t* desc;             // [nslots][kp_cap][32]
   int* nkp;                  // [nslots]
   int* err;                  // [nslots]

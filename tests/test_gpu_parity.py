@@ -956,3 +956,24 @@ def test_matchers_read_extractor_slots_in_place(gx, oracle):
     assert int(nm.cpu()[0]) == rn and np.array_equal(m12.cpu().numpy()[:len(k1)], rm12) and rn > 50
     assert np.array_equal(prev.cpu().numpy()[:len(k1)], rprev)
     assert bounds.cpu().tolist()[:4] == [0.0, float(w), 0.0, float(h)]
+
+
+def test_packed_fetch_and_host_unpack_equal_the_full_records(gx):
+    """orbx_fetch_results_packed + orbx_unpack_keypoints (8 bytes per keypoint over the bus, cv::KeyPoint rebuilt on the host)
+    against orbx_fetch_results, byte for byte, on frames of all three shapes (different level geometries and counts)."""
+    for name, w, h, nf in CONFIGS:
+        imgs = np.stack([synth.mono_frame(400 + i, w, h) for i in range(3)] + [np.full((h, w), 77, np.uint8)])   # the last one: no keypoints
+        G = _ext(gx, w, h, nf, batch=4)
+        G.extract_batch(imgs)
+        full = G.fetch(0, 4)
+        cap = G.kp_cap
+        packed = np.zeros((4, cap), np.uint64); desc = np.zeros((4, cap, 32), np.uint8); lc = np.zeros((4, 8), np.int32)
+        G.fetch_packed_into(0, 4, packed, desc, lc)
+        import torch
+        torch.cuda.synchronize()
+        kps, cnt = G.unpack_keypoints(packed, lc)
+        for i in range(4):
+            assert cnt[i] == len(full[i][0]) == lc[i].sum(), (name, i)
+            assert kps[i, :cnt[i]].tobytes() == full[i][0].tobytes(), (name, i)
+            assert np.array_equal(desc[i, :cnt[i]], full[i][1])
+        assert cnt[3] == 0 and cnt[0] >= nf

@@ -4,7 +4,7 @@
     python tools/h2d_probe.py                                                         # one GPU
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/h2d_probe.py
 
-Per rank: pinned buffers of bench.py's sizes (239 MB up, 66 MB down per step of 256 KITTI-shaped stereo pairs), plain
+Per rank: pinned buffers of bench.py's sizes (239 MB up, 46 MB down per step of 256 KITTI-shaped stereo pairs), plain
 cudaMemcpyAsync on 1 and on 3 streams, H2D alone / D2H alone / both at once, all ranks at the same time
 (orb_slam2_b200/hostfeed.py).  Rank 0 prints one JSON line with per-GPU and aggregate GB/s and the GPU <-> PCIe / NUMA map
 (`nvidia-smi topo -m`).  Output of this script is kept under profiles/.
@@ -29,7 +29,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B, w, h, cap = 256, 1241, 376, 2024
     h2d = 2 * B * w * h
-    d2h = 2 * B * cap * 60 + 2 * B * 4 + 2 * B * cap * 4 + B * 4
+    d2h = 2 * B * cap * 40 + 2 * B * 32 + 2 * B * cap * 4 + B * 4       # bench.py: 8-byte keypoints + descriptors, uRight + depth, counts
     wc = "--wc" in sys.argv
     res = hostfeed.probe(torch, h2d, d2h, streams=(1, 3), reps=8, dist=dist if world > 1 else None, write_combined=wc)
     flat = [res["h2d_gbs"][1], res["h2d_gbs"][3], res["d2h_gbs"][1], res["d2h_gbs"][3], *res["duplex_gbs"][1], *res["duplex_gbs"][3]]
