@@ -628,6 +628,20 @@ def latency_block(gx, torch, local):
     return out
 
 
+def spread_device(torch, local, world):
+    """The GPU of local rank `local`.  When the job sees more GPUs than it has ranks, the ranks are spread evenly over them
+    (rank r -> device r * ndev / world) instead of taking the first `world`: on this pool's 8-GPU boxes GPUs 0-3 and 4-7
+    hang off two host bridges with separate upload ceilings (profiles/: host-feed probe - four uploads through one bridge get
+    29 GB/s each, two get 55), and the end-to-end leg is bound by exactly that.  With as many GPUs as ranks: the identity."""
+    try:
+        ndev = torch.cuda.device_count()
+        if os.environ.get("ORBX_BENCH_SPREAD", "1") != "0" and ndev > world and ndev % world == 0:
+            return local * (ndev // world)
+    except Exception:
+        pass
+    return local
+
+
 def bind_near_gpu(torch, local):
     """Pins this rank's threads to the CPU cores NVML reports as local to its GPU, so that the pinned host
     buffers of the end-to-end leg are allocated (first touched) on the GPU's own NUMA node.  Best effort."""
@@ -673,6 +687,7 @@ def main():
     from orb_slam2_b200.api import KP_DTYPE
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the CUDA path has no CPU fallback")
+    local = spread_device(torch, local, world)
     torch.cuda.set_device(local)
     all_cpus = os.sched_getaffinity(0)
     affinity = bind_near_gpu(torch, local)      # before any pinned allocation: first touch decides the NUMA node
@@ -881,6 +896,7 @@ def main():
                                 "d2h_3streams": [round(v[2], 2) for v in feed_all], "duplex3_h2d": [round(v[3], 2) for v in feed_all],
                                 "duplex3_d2h": [round(v[4], 2) for v in feed_all]}},
             "gpu_launches": int(launches),
+            "devices": {"rank0_device": local, "visible": torch.cuda.device_count(), "placement": "ranks spread evenly over the visible GPUs (spread_device)"},
             "clocks": clocks,
             "verified": {"pairs": int(ver_all[:, 0].sum()), "mismatches": int(ver_all[:, 1].sum()), "per_rank": ver_all[:, :2].tolist(),
                          "what": "after each timed region every rank re-computes a seeded choice of the pairs of its last step with the CPU oracle: keypoint bytes, "

@@ -977,3 +977,18 @@ def test_packed_fetch_and_host_unpack_equal_the_full_records(gx):
             assert kps[i, :cnt[i]].tobytes() == full[i][0].tobytes(), (name, i)
             assert np.array_equal(desc[i, :cnt[i]], full[i][1])
         assert cnt[3] == 0 and cnt[0] >= nf
+
+
+def test_fused_describe_kernel_kept_for_ab_gives_the_same_bytes(gx, oracle):
+    """ORBX_DESCRIBE=fused (read at create) selects round 1's blur-on-demand kernel instead of K4a + K4b: same keypoints,
+    angles and descriptors, and both equal the oracle."""
+    w, h, nf = 752, 480, 1200
+    img = synth.mono_frame(500, w, h)
+    k0, d0 = _ext(gx, w, h, nf)(img)
+    os.environ["ORBX_DESCRIBE"] = "fused"
+    try:
+        k1, d1 = _ext(gx, w, h, nf)(img)
+    finally:
+        del os.environ["ORBX_DESCRIBE"]
+    ok, od = oracle.Extractor(nf).extract(img)
+    assert k0.tobytes() == k1.tobytes() == ok.tobytes() and np.array_equal(d0, d1) and np.array_equal(d0, od)

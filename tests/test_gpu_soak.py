@@ -16,13 +16,16 @@ from orb_slam2_b200 import synth
 pytestmark = pytest.mark.gpu
 
 CHUNK = 256
-SHAPES = [("kitti", synth.KITTI["w"], synth.KITTI["h"], synth.KITTI["nfeatures"], synth.KITTI["bf"], synth.KITTI["fx"], True, 2048),
-          ("euroc", synth.EUROC["w"], synth.EUROC["h"], synth.EUROC["nfeatures"], synth.EUROC["bf"], synth.EUROC["fx"], True, 2048),
-          ("tum-ini", 640, 480, 2000, 0.0, 0.0, False, 2048)]
+DEFAULT = (1.2, 8, 20, 7)            # scaleFactor, nLevels, iniThFAST, minThFAST of every dataset YAML
+SHAPES = [("kitti", synth.KITTI["w"], synth.KITTI["h"], synth.KITTI["nfeatures"], synth.KITTI["bf"], synth.KITTI["fx"], True, 2048, DEFAULT),
+          ("euroc", synth.EUROC["w"], synth.EUROC["h"], synth.EUROC["nfeatures"], synth.EUROC["bf"], synth.EUROC["fx"], True, 2048, DEFAULT),
+          ("tum-ini", 640, 480, 2000, 0.0, 0.0, False, 2048, DEFAULT),
+          # other constructor arguments: different level geometry, cell grid, quotas and both FAST thresholds (stereo, 512 pairs)
+          ("svga-1.3x6", 800, 600, 1500, 60.0, 500.0, True, 512, (1.3, 6, 12, 5))]
 
 
-@pytest.mark.parametrize("name,w,h,nf,bf,fx,stereo,count", SHAPES, ids=[s[0] for s in SHAPES])
-def test_soak_every_result_byte_equals_the_oracle(oracle, name, w, h, nf, bf, fx, stereo, count):
+@pytest.mark.parametrize("name,w,h,nf,bf,fx,stereo,count,ctor", SHAPES, ids=[s[0] for s in SHAPES])
+def test_soak_every_result_byte_equals_the_oracle(oracle, name, w, h, nf, bf, fx, stereo, count, ctor):
     import torch
     assert torch.cuda.is_available()
     import orb_slam2_b200 as gx
@@ -33,9 +36,9 @@ def test_soak_every_result_byte_equals_the_oracle(oracle, name, w, h, nf, bf, fx
     else:
         base = [(synth.mono_frame(20000 + i, w, h), None) for i in range(nbase)]
     eyes = 2 if stereo else 1
-    G = gx.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=eyes * CHUNK)
+    G = gx.ORBextractor(nf, *ctor, max_w=w, max_h=h, max_batch=eyes * CHUNK)
     cap = G.kp_cap
-    params = (nf, 1.2, 8, 20, 7)
+    params = (nf,) + ctor
     kps = np.zeros((eyes * CHUNK, cap), KP_DTYPE); desc = np.zeros((eyes * CHUNK, cap, 32), np.uint8); cnt = np.zeros(eyes * CHUNK, np.int32)
     seen = set()
     total_kp = total_m = frames_bad = 0

@@ -23,6 +23,8 @@ def main():
     import torch.distributed as dist
     from orb_slam2_b200 import hostfeed
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if "--spread" in sys.argv and torch.cuda.device_count() > world and torch.cuda.device_count() % world == 0:
+        local = local * (torch.cuda.device_count() // world)          # bench.py's placement: ranks spread over the visible GPUs
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -37,7 +39,7 @@ def main():
     if rank == 0:
         names = ["h2d_1stream", "h2d_3streams", "d2h_1stream", "d2h_3streams", "duplex1_h2d", "duplex1_d2h", "duplex3_h2d", "duplex3_d2h"]
         per_gpu = {n: [round(v[i], 2) for v in allv] for i, n in enumerate(names)}
-        line = {"probe": "bare cudaMemcpyAsync, pinned host memory%s, all ranks concurrently" % (" (upload buffer write-combined)" if wc else ""), "n_gpus": world, "h2d_bytes": h2d, "d2h_bytes": d2h,
+        line = {"probe": "bare cudaMemcpyAsync, pinned host memory%s, all ranks concurrently" % (" (upload buffer write-combined)" if wc else ""), "n_gpus": world, "spread_over_visible_gpus": "--spread" in sys.argv, "h2d_bytes": h2d, "d2h_bytes": d2h,
                 "per_gpu_gbs": per_gpu, "aggregate_gbs": {n: round(sum(v), 1) for n, v in per_gpu.items()},
                 "min_per_gpu_gbs": {n: min(v) for n, v in per_gpu.items()}}
         try:

@@ -14,7 +14,7 @@ for r in rows[hdr + 1:]:
     a = agg.setdefault(r[ki].split('(')[0].replace('void ', ''), [0, 0.0]); a[0] += 1; a[1] += v
 tot = sum(a[1] for a in agg.values())
 with open(f'profiles/{tag}_launch_shares.csv', 'w') as f:
-    f.write(f"# {desc}\n# ncu --metrics gpu__time_duration.sum --clock-control none -c 400 over `python bench.py --steps 2 --warmup 3 --no-cpu-baseline`\n")
+    f.write(f"# {desc}\n# ncu --metrics gpu__time_duration.sum --clock-control none -c 400 over `python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-secondary --no-verify`\n")
     f.write("# per-launch times under ncu are cold-cache and serialised: compare SHARES with bench.py's stage_ms_per_step, not absolutes\n")
     f.write("kernel,launches,total_us,avg_us,share_pct\n")
     for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
@@ -29,7 +29,7 @@ want = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'launch__registers_per_thread', 'launch__grid_size', 'launch__block_size']
 idx = [H.index(w) for w in want]; ki = H.index('Kernel Name')
 with open(f'profiles/{tag}_ncu_full_one_step.csv', 'w') as f:
-    f.write(f"# {desc}\n# ncu --set full --clock-control none --import-source on -k regex:k_ --launch-skip 42 --launch-count 14 (all launches of one step)\n")
+    f.write(f"# {desc}\n# ncu --set full --clock-control none --import-source on -k regex:k_ --launch-skip 45 --launch-count 15 (all launches of one step)\n")
     f.write("kernel," + ",".join(f"{w} [{U[i]}]" for w, i in zip(want, idx)) + "\n")
     for r in rows[2:]:
         f.write(r[ki].split('(')[0].replace('void ', '') + "," + ",".join(r[i].replace(',', '') for i in idx) + "\n")
@@ -37,7 +37,7 @@ print(open(f'profiles/{tag}_launch_shares.csv').read())
 
 # ---- profiles/traffic.json: per-stage DRAM bytes per step and issue / pipe utilisation, read by bench.py ----
 import json
-STAGE = [('k_border_level0', 'pyramid'), ('k_resize', 'pyramid'), ('k_fast_cells', 'fast'), ('k_octree', 'quadtree'), ('k_describe', 'describe'),
+STAGE = [('k_border_level0', 'pyramid'), ('k_resize', 'pyramid'), ('k_fast_cells', 'fast'), ('k_octree', 'quadtree'), ('k_blur', 'blur'), ('k_describe', 'describe'),
          ('k_stereo_rows', 'stereo_match'), ('k_stereo_match', 'stereo_match'), ('k_stereo_median', 'stereo_median')]
 def col(name): return H.index(name)
 dram = collections.OrderedDict(); acc = {}
@@ -47,9 +47,8 @@ for r in rows[2:]:
     if st is None:
         continue
     f = lambda n: float(r[col(n)].replace(',', ''))
-    unit = U[col('dram__bytes_read.sum')]
-    mul = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[unit]
-    dram[st] = dram.get(st, 0) + int((f('dram__bytes_read.sum') + f('dram__bytes_write.sum')) * mul)
+    mul = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    dram[st] = dram.get(st, 0) + int(f('dram__bytes_read.sum') * mul[U[col('dram__bytes_read.sum')]] + f('dram__bytes_write.sum') * mul[U[col('dram__bytes_write.sum')]])
     t = f('gpu__time_duration.sum')
     a = acc.setdefault(st, [0.0, 0.0, 0.0, 0.0])
     a[0] += t; a[1] += t * f('smsp__issue_active.avg.pct_of_peak_sustained_active')
