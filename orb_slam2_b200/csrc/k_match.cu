@@ -18,6 +18,8 @@
 #include <algorithm>
 #include <climits>
 
+#include <cstdlib>
+
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -506,12 +508,179 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
   if (lane == 0) a.nm[p] = nm;
 }
 
+// ------------------------------------------------------------------------------------------
+// K8, latency form: ONE frame per call is the SLAM loop's pattern (src/Tracking.cc:1192), and one warp walking a few hundred
+// map points in order is then all the GPU does.  Here a CTA of 8 warps serves the frame in two phases.
+//   A (parallel, map points strided over the warps): the two smallest candidate keys of every map point against the
+//     frame as it is ON ENTRY (frameObs is not written in this phase);
+//   B (warp 0, in map-point order, hazard H6): a map point's phase-A answer is what the ordered walk would have found
+//     unless one of its two keypoints was claimed meanwhile by an earlier map point of this call (claimed = given a map
+//     point with Observations() > 0, the only way a candidate disappears); only then is the point scanned again, against
+//     the live frameObs.  Then the reference's acceptance rules, the claim, the output.
+// Removing a candidate that is neither the smallest nor the second smallest key changes neither, so B reproduces the
+// sequential result exactly (same tests as the one-warp kernel: parity tests run both).
+constexpr int kProjParWarps = 8;
+
+struct ProjMP { int inView, level; float viewCos, x, y, xr; uint32_t dw; };
+
+// the two smallest keys dist<<32 | cell<<16 | idx among map point c's candidates (warp-wide; every lane returns them)
+__device__ __forceinline__ void proj_scan(const ProjArgs& a, const ProjMP& c, const int* cstart, int n_in_grid, const float2* sxy, const uint32_t* smeta,
+                                          const uint32_t* d, const float* uRight, const int* frameObs, float minX, float minY, float invW, float invH,
+                                          int lane, unsigned long long& o1, unsigned long long& o2) {
+  o1 = o2 = ~0ull;
+  if (!c.inView) return;
+  const int lvl = min(max(c.level, 0), a.nlevels - 1);
+  float r = ((double)c.viewCos > 0.998) ? 2.5f : 4.0f;
+  if (a.th != 1.0f) r = __fmul_rn(r, a.th);
+  const float R = __fmul_rn(r, a.scale[lvl]);
+  const float x = c.x, y = c.y;
+  const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, minX), R), invW)));
+  if (cx0 >= 64) return;
+  const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, minX), R), invW)));
+  if (cx1 < 0) return;
+  const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, minY), R), invH)));
+  if (cy0 >= 48) return;
+  const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, minY), R), invH)));
+  if (cy1 < 0) return;
+  uint32_t q[8];
+#pragma unroll
+  for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
+  unsigned long long k1 = ~0ull, k2 = ~0ull;
+  for (int ix = cx0; ix <= cx1; ++ix) {
+    const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
+    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : n_in_grid;
+    for (int e = e_lo + lane; e < e_hi; e += 32) {
+      const uint32_t meta = smeta[e];
+      const int oct = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
+      if (oct < lvl - 1 || oct > lvl) continue;
+      const float2 pt = sxy[e];
+      if (!(fabsf(__fsub_rn(pt.x, x)) < R && fabsf(__fsub_rn(pt.y, y)) < R)) continue;
+      if (frameObs[idx] > 0) continue;
+      const float ur = uRight[idx];
+      if (ur > 0.f && fabsf(__fsub_rn(c.xr, ur)) > R) continue;
+      const unsigned long long key = ((unsigned long long)ham8(q, d + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
+      if (key < k1) { k2 = k1; k1 = key; }
+      else if (key < k2) k2 = key;
+    }
+  }
+  const unsigned hi1 = (unsigned)(k1 >> 32), lo1 = (unsigned)k1;
+  const unsigned ghi = __reduce_min_sync(0xffffffffu, hi1);
+  if (ghi == 0xffffffffu) return;
+  const unsigned glo = __reduce_min_sync(0xffffffffu, hi1 == ghi ? lo1 : 0xffffffffu);
+  const bool owner = hi1 == ghi && lo1 == glo;
+  const unsigned long long mine2 = owner ? k2 : k1;
+  const unsigned hi2 = (unsigned)(mine2 >> 32), lo2 = (unsigned)mine2;
+  const unsigned shi = __reduce_min_sync(0xffffffffu, hi2);
+  const unsigned slo = __reduce_min_sync(0xffffffffu, hi2 == shi ? lo2 : 0xffffffffu);
+  o1 = ((unsigned long long)ghi << 32) | glo;
+  o2 = shi == 0xffffffffu ? ~0ull : (((unsigned long long)shi << 32) | slo);
+}
+
+__global__ void __launch_bounds__(kProjParWarps * 32) k_search_projection_par(ProjArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float2* sxy = reinterpret_cast<float2*>(smem);
+  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);
+  int* soff = reinterpret_cast<int*>(smeta + a.cap);
+  uint32_t* sdesc = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(soff + kGridCells + 2) + 15) & ~(uintptr_t)15);   // [cap][8]
+  uint32_t* claim = sdesc + (size_t)a.cap * 8;                          // [(cap + 31) / 32] keypoints claimed by this call
+  uint8_t* soct = reinterpret_cast<uint8_t*>(claim + (a.cap + 31) / 32);  // [cap] octave per keypoint
+  __shared__ int s_ngrid;
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n = a.n[p], m = a.m[p];
+  const orbx_keypoint* k = a.k + (size_t)p * a.cap;
+  const uint32_t* dg = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
+  const float* uRight = a.uRight + (size_t)p * a.cap;
+  int* frameObs = a.frameObs + (size_t)p * a.cap;
+  int* assigned = a.assigned + (size_t)p * a.cap;
+  const size_t mo = (size_t)p * a.mcap;
+  uint4* spec = a.spec + mo;
+
+  for (int i = tid; i < n; i += kProjParWarps * 32) { assigned[i] = -1; soct[i] = (uint8_t)k[i].octave; }
+  for (int i = tid; i < (a.cap + 31) / 32; i += kProjParWarps * 32) claim[i] = 0u;
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(dg);
+    uint4* dst = reinterpret_cast<uint4*>(sdesc);
+    for (int i = tid; i < n * 2; i += kProjParWarps * 32) dst[i] = __ldg(src + i);
+  }
+  const float minX = a.gb[0], minY = a.gb[2], invW = a.gb[4], invH = a.gb[5];
+  if (warp == 0) {
+    const int ng = grid_sort(k, n, minX, minY, invW, invH, sxy, smeta, soff, lane);
+    if (lane == 0) s_ngrid = ng;
+  }
+  __syncthreads();
+  const int n_in_grid = s_ngrid;
+  const int* cstart = soff + 1;
+  auto fetch = [&](int i) {
+    ProjMP q;
+    q.inView = i < m ? a.inView[mo + i] : 0;
+    q.level = i < m ? a.level[mo + i] : 0;
+    q.viewCos = i < m ? a.viewCos[mo + i] : 0.f;
+    q.x = i < m ? a.projX[mo + i] : 0.f; q.y = i < m ? a.projY[mo + i] : 0.f; q.xr = i < m ? a.projXR[mo + i] : 0.f;
+    q.dw = (i < m && lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (mo + i) * 32) + lane) : 0u;
+    return q;
+  };
+  // phase A
+  {
+    ProjMP nx = fetch(warp);
+    for (int iMP = warp; iMP < m; iMP += kProjParWarps) {
+      const ProjMP c = nx;
+      nx = fetch(iMP + kProjParWarps);
+      unsigned long long k1, k2;
+      proj_scan(a, c, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, minX, minY, invW, invH, lane, k1, k2);
+      if (lane == 0) spec[iMP] = make_uint4((unsigned)(k1 >> 32), (unsigned)k1, (unsigned)(k2 >> 32), (unsigned)k2);
+    }
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  // phase B: 32 map points per round - their phase-A keys and Observations() arrive by one coalesced load each and are
+  // handed round by shuffles, the octaves come from shared memory: no dependent global load per map point
+  int nm = 0;
+  for (int base = 0; base < m; base += 32) {
+    const int mine = base + lane;
+    const uint4 my4 = mine < m ? spec[mine] : make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    const int myobs = mine < m ? a.mpObs[mo + mine] : 0;
+    const int cnt = min(32, m - base);
+    for (int j = 0; j < cnt; ++j) {
+      const int iMP = base + j;
+      const unsigned x = __shfl_sync(0xffffffffu, my4.x, j), y = __shfl_sync(0xffffffffu, my4.y, j);
+      const unsigned z = __shfl_sync(0xffffffffu, my4.z, j), w4 = __shfl_sync(0xffffffffu, my4.w, j);
+      const int obs = __shfl_sync(0xffffffffu, myobs, j);
+      unsigned long long k1 = ((unsigned long long)x << 32) | y, k2 = ((unsigned long long)z << 32) | w4;
+      if (k1 == ~0ull) continue;
+      const int i1 = (int)(y & 0xFFFF), i2 = (int)(w4 & 0xFFFF);
+      const bool stale = ((claim[i1 >> 5] >> (i1 & 31)) & 1u) || (k2 != ~0ull && ((claim[i2 >> 5] >> (i2 & 31)) & 1u));
+      if (stale) {                                                       // warp-uniform: rare
+        const ProjMP c = fetch(iMP);
+        proj_scan(a, c, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, minX, minY, invW, invH, lane, k1, k2);
+        if (k1 == ~0ull) continue;
+      }
+      const int bestDist = (int)(k1 >> 32), bestIdx = (int)(k1 & 0xFFFF);
+      if (bestDist > 100) continue;                                      // TH_HIGH
+      const int bestLvl = soct[bestIdx];
+      const int bestDist2 = k2 == ~0ull ? 256 : (int)(k2 >> 32);
+      const int bestLvl2 = k2 == ~0ull ? -1 : (int)soct[k2 & 0xFFFF];
+      if (bestLvl == bestLvl2 && (float)bestDist > __fmul_rn(a.ratio, (float)bestDist2)) continue;
+      if (lane == 0) {
+        assigned[bestIdx] = iMP; frameObs[bestIdx] = obs;
+        if (obs > 0) claim[bestIdx >> 5] |= 1u << (bestIdx & 31);
+      }
+      ++nm;
+      __syncwarp();
+    }
+  }
+  if (lane == 0) a.nm[p] = nm;
+}
+
 int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
   const size_t base = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
   const size_t with_desc = ((base + 15) & ~(size_t)15) + (size_t)a.cap * 32;
   // latency mode (a few frames per call): one warp per SM anyway, so spend the shared memory on the descriptors;
   // throughput mode keeps the small footprint (6 CTAs per SM)
-  if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
+  const size_t par = with_desc + (size_t)((a.cap + 31) / 32) * 4 + (size_t)a.cap;
+  if (a.n_pairs <= 148 && par <= 200 * 1024 && !getenv("ORBX_PROJ_SERIAL")) {
+    cudaFuncSetAttribute(k_search_projection_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
+    k_search_projection_par<<<a.n_pairs, kProjParWarps * 32, par, st>>>(a);
+  } else if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
     cudaFuncSetAttribute(k_search_projection<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)with_desc);
     k_search_projection<true><<<a.n_pairs, 32, with_desc, st>>>(a);
   } else {
@@ -667,10 +836,185 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
   if (lane == 0) a.nm[p] = nm;
 }
 
+// ------------------------------------------------------------------------------------------
+// K9, latency form (see K8's): phase A - every last-frame keypoint that carries a map point gets the smallest candidate key
+// against the current frame as it is on entry, keypoints strided over 8 warps; phase B - warp 0 walks them in index order,
+// re-scans only the ones whose keypoint was claimed meanwhile, applies TH_HIGH, claims, and records the rotation events.
+struct ProjLP { int octave; float X0, X1, X2; uint32_t dw; };
+
+__device__ __forceinline__ unsigned long long projf_scan(const ProjFrameArgs& a, const ProjLP& c, const float* Tr, int mode, const int* cstart, int n_in_grid,
+                                                         const float2* sxy, const uint32_t* smeta, const uint32_t* d, const float* uRight,
+                                                         const int* frameObs, const float* gbv, int lane) {
+  const float minX = gbv[0], maxX = gbv[1], minY = gbv[2], maxY = gbv[3], invW = gbv[4], invH = gbv[5];
+  float c3[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+    c3[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(Tr[3 * r], c.X0), __fmul_rn(Tr[3 * r + 1], c.X1)), __fmul_rn(Tr[3 * r + 2], c.X2)), Tr[9 + r]);
+  const float invzc = (float)(1.0 / (double)c3[2]);
+  if (invzc < 0.f) return ~0ull;
+  const float u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, c3[0]), invzc), a.cx), v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, c3[1]), invzc), a.cy);
+  if (u < minX || u > maxX || v < minY || v > maxY) return ~0ull;
+  if (!(u == u) || !(v == v)) return ~0ull;
+  const int oct = min(max(c.octave, 0), a.nlevels - 1);
+  const float R = __fmul_rn(a.th, a.scale[oct]);
+  const int l_lo = mode == 1 ? oct : (mode == 2 ? 0 : oct - 1), l_hi = mode == 1 ? 99 : (mode == 2 ? oct : oct + 1);
+  const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, minX), R), invW)));
+  if (cx0 >= 64) return ~0ull;
+  const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, minX), R), invW)));
+  if (cx1 < 0) return ~0ull;
+  const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, minY), R), invH)));
+  if (cy0 >= 48) return ~0ull;
+  const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, minY), R), invH)));
+  if (cy1 < 0) return ~0ull;
+  const float ur_pred = __fsub_rn(u, __fmul_rn(a.bf, invzc));
+  uint32_t q[8];
+#pragma unroll
+  for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
+  unsigned long long best = ~0ull;
+  for (int ix = cx0; ix <= cx1; ++ix) {
+    const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
+    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : n_in_grid;
+    for (int e = e_lo + lane; e < e_hi; e += 32) {
+      const uint32_t meta = smeta[e];
+      const int oct2 = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
+      if (oct2 < l_lo || oct2 > l_hi) continue;
+      const float2 pt = sxy[e];
+      if (!(fabsf(__fsub_rn(pt.x, u)) < R && fabsf(__fsub_rn(pt.y, v)) < R)) continue;
+      if (frameObs[idx] > 0) continue;
+      const float ur = uRight[idx];
+      if (ur > 0.f && fabsf(__fsub_rn(ur_pred, ur)) > R) continue;
+      const unsigned long long key = ((unsigned long long)ham8(q, d + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
+      best = min(best, key);
+    }
+  }
+  const unsigned hi1 = (unsigned)(best >> 32), lo1 = (unsigned)best;
+  const unsigned ghi = __reduce_min_sync(0xffffffffu, hi1);
+  if (ghi == 0xffffffffu) return ~0ull;
+  const unsigned glo = __reduce_min_sync(0xffffffffu, hi1 == ghi ? lo1 : 0xffffffffu);
+  return ((unsigned long long)ghi << 32) | glo;
+}
+
+__global__ void __launch_bounds__(kProjParWarps * 32) k_search_projection_frame_par(ProjFrameArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float2* sxy = reinterpret_cast<float2*>(smem);
+  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);
+  int* soff = reinterpret_cast<int*>(smeta + a.cap);
+  uint32_t* sdesc = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(soff + kGridCells + 2) + 15) & ~(uintptr_t)15);
+  uint32_t* claim = sdesc + (size_t)a.cap * 8;
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_ngrid;
+  __shared__ float s_gb[6];
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n = a.n[p], nLast = a.nLast[p], mode = a.mode[p];
+  const orbx_keypoint* k = a.k + (size_t)p * a.cap;
+  const uint32_t* dg = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
+  const float* uRight = a.uRight + (size_t)p * a.cap;
+  int* frameObs = a.frameObs + (size_t)p * a.cap;
+  int* assigned = a.assigned + (size_t)p * a.cap;
+  int* events = a.events + (size_t)p * a.lcap;
+  const size_t lo = (size_t)p * a.lcap;
+  uint2* spec = a.spec + lo;
+
+  for (int i = tid; i < n; i += kProjParWarps * 32) assigned[i] = -1;
+  for (int i = tid; i < (a.cap + 31) / 32; i += kProjParWarps * 32) claim[i] = 0u;
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (tid < 6) s_gb[tid] = a.gb[tid];
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(dg);
+    uint4* dst = reinterpret_cast<uint4*>(sdesc);
+    for (int i = tid; i < n * 2; i += kProjParWarps * 32) dst[i] = __ldg(src + i);
+  }
+  if (warp == 0) {
+    const int ng = grid_sort(k, n, a.gb[0], a.gb[2], a.gb[4], a.gb[5], sxy, smeta, soff, lane);
+    if (lane == 0) s_ngrid = ng;
+  }
+  __syncthreads();
+  const int n_in_grid = s_ngrid;
+  const int* cstart = soff + 1;
+  float Tr[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) Tr[i] = a.pose[(size_t)p * 12 + i];
+  auto fetch = [&](int i) {
+    ProjLP q;
+    const bool ok = i >= 0 && i < nLast;
+    q.octave = ok ? a.lastOctave[lo + i] : 0;
+    q.X0 = ok ? a.lastXw[(lo + i) * 3] : 0.f; q.X1 = ok ? a.lastXw[(lo + i) * 3 + 1] : 0.f; q.X2 = ok ? a.lastXw[(lo + i) * 3 + 2] : 0.f;
+    q.dw = (ok && lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (lo + i) * 32) + lane) : 0u;
+    return q;
+  };
+  // phase A: blocks of 32 last-frame keypoints strided over the warps; inside a block only the valid ones are scanned
+  for (int base = warp * 32; base < nLast; base += kProjParWarps * 32) {
+    const int mine = base + lane;
+    uint32_t vm = __ballot_sync(0xffffffffu, mine < nLast && a.lastValid[lo + mine]);
+    unsigned long long mykey = ~0ull;
+    while (vm) {
+      const int b = __ffs((int)vm) - 1;
+      vm &= vm - 1u;
+      const ProjLP c = fetch(base + b);
+      const unsigned long long key = projf_scan(a, c, Tr, mode, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, s_gb, lane);
+      if (lane == b) mykey = key;
+    }
+    if (mine < nLast) spec[mine] = make_uint2((unsigned)(mykey >> 32), (unsigned)mykey);      // invalid keypoints: ~0
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  // phase B
+  int nm = 0;
+  for (int base = 0; base < nLast; base += 32) {
+    const int mine = base + lane;
+    const uint2 my2 = mine < nLast ? spec[mine] : make_uint2(0xffffffffu, 0xffffffffu);
+    const int myobs = mine < nLast ? a.mpObs[lo + mine] : 0;
+    const float myang = mine < nLast ? a.lastAngle[lo + mine] : 0.f;
+    uint32_t vm = __ballot_sync(0xffffffffu, my2.x != 0xffffffffu);
+    while (vm) {
+      const int j = __ffs((int)vm) - 1;
+      vm &= vm - 1u;
+      const int i = base + j;
+      unsigned long long key = ((unsigned long long)__shfl_sync(0xffffffffu, my2.x, j) << 32) | __shfl_sync(0xffffffffu, my2.y, j);
+      const int obs = __shfl_sync(0xffffffffu, myobs, j);
+      const float ang = __shfl_sync(0xffffffffu, myang, j);
+      const int i1 = (int)(key & 0xFFFF);
+      if ((claim[i1 >> 5] >> (i1 & 31)) & 1u) {                          // its keypoint went to an earlier map point: scan again (rare)
+        const ProjLP c = fetch(i);
+        key = projf_scan(a, c, Tr, mode, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, s_gb, lane);
+        if (key == ~0ull) continue;
+      }
+      if ((unsigned)(key >> 32) > 100u) continue;                        // worse than TH_HIGH
+      const int bestIdx = (int)(key & 0xFFFF);
+      if (lane == 0) {
+        assigned[bestIdx] = i;
+        frameObs[bestIdx] = obs;
+        if (obs > 0) claim[bestIdx >> 5] |= 1u << (bestIdx & 31);
+        int bin = 0;
+        if (a.checkOri) { bin = rot_bin(ang, k[bestIdx].angle); s_hist[bin] += 1; }
+        events[nm] = (bin << 16) | bestIdx;
+      }
+      ++nm;
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  if (a.checkOri) {
+    int k_a, k_b, k_c;
+    three_maxima(s_hist, k_a, k_b, k_c);
+    int drop = 0;
+    for (int e = lane; e < nm; e += 32) {
+      const int bin = events[e] >> 16, idx = events[e] & 0xFFFF;
+      if (bin != k_a && bin != k_b && bin != k_c) { assigned[idx] = -1; ++drop; }
+    }
+    nm -= __reduce_add_sync(0xffffffffu, drop);
+  }
+  if (lane == 0) a.nm[p] = nm;
+}
+
 int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st) {
   const size_t base = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
   const size_t with_desc = ((base + 15) & ~(size_t)15) + (size_t)a.cap * 32;
-  if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {    // latency mode, see launch_search_projection
+  const size_t par = with_desc + (size_t)((a.cap + 31) / 32) * 4;
+  if (a.n_pairs <= 148 && par <= 200 * 1024 && !getenv("ORBX_PROJ_SERIAL")) {    // latency mode, see launch_search_projection
+    cudaFuncSetAttribute(k_search_projection_frame_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
+    k_search_projection_frame_par<<<a.n_pairs, kProjParWarps * 32, par, st>>>(a);
+  } else if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
     cudaFuncSetAttribute(k_search_projection_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)with_desc);
     k_search_projection_frame<true><<<a.n_pairs, 32, with_desc, st>>>(a);
   } else {

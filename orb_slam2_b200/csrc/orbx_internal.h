@@ -140,6 +140,7 @@ struct ProjArgs {
   float th, ratio;
   float scale[kMaxLevels];
   int* frameObs; int* assigned; int* nm;
+  uint4* spec;                // scratch [P][mcap]: the two smallest candidate keys per map point (latency mode)
 };
 int launch_search_projection(const ProjArgs& a, cudaStream_t st);
 
@@ -155,6 +156,7 @@ struct ProjFrameArgs {
   float scale[kMaxLevels];
   int* frameObs; int* assigned; int* nm;
   int* events;                // scratch [P][lcap]: bin<<16 | keypoint index per accepted match
+  uint2* spec;                // scratch [P][lcap]: the smallest candidate key per last-frame keypoint (latency mode)
 };
 int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st);
 
