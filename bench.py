@@ -728,11 +728,12 @@ def main():
         g.extract_batch(dev[i % NSETS], 0, st.cuda_stream)
         gx.ComputeStereoMatches(g, g, bf, fx, n=B, slotL0=0, slotR0=B, out=(d_ur, d_dp, d_nm), stream=st.cuda_stream)
 
-    # How the keypoints come back: "full" = the 28-byte cv::KeyPoint records by D2H copy, "packed" = 8 bytes per keypoint
-    # over the bus + orbx_unpack_keypoints on the host (inside the timed region).  With one GPU the link is full duplex and
-    # the upload is the bound, so the plain copy wins; with several GPUs on this box uploads and downloads share one
-    # half-duplex host path (profiles/: host-feed probe), and every byte not downloaded is upload time won.
-    e2e_mode = os.environ.get("ORBX_BENCH_D2H", "packed" if world > 1 else "full")
+    # How the keypoints come back: "full" = the 28-byte cv::KeyPoint records by D2H copy (default), "packed" = 8 bytes per
+    # keypoint over the bus + orbx_unpack_keypoints on the host (inside the timed region).  Measured on this pool's boxes
+    # (profiles/README.md, round 2): packed loses 3-6 % at 1 GPU and 3 % at 8 - the download is not what holds the leg, and the
+    # unpack costs 5 ms of one core per step and rank - so it is an option (ORBX_BENCH_D2H=packed) for hosts with a slow
+    # device-to-host path, not the default.
+    e2e_mode = os.environ.get("ORBX_BENCH_D2H", "full")
 
     def step_e2e(i, g, st, o):
         s = st.cuda_stream
