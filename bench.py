@@ -892,6 +892,7 @@ def main():
                                             else ": cv::KeyPoint records copied as they are"), "cpu_affinity": affinity,
                     "h2d_gbs": h2d / e2e_step_s / 1e9, "d2h_gbs": d2h / e2e_step_s / 1e9,
                     "ceiling_gbs": ceil_h2d, "ceiling_duplex_h2d_gbs": ceil_dup, "frac_of_ceiling": h2d / e2e_step_s / 1e9 / ceil_h2d,
+                    "frac_of_duplex_ceiling": h2d / e2e_step_s / 1e9 / ceil_dup,   # against uploads WITH a step's downloads running beside them: what the leg does
                     "ceiling": {"what": "bare cudaMemcpyAsync of one step's bytes from/to pinned host memory, no kernels, all ranks at once (orb_slam2_b200/hostfeed.py); per-GPU GB/s, [rank]",
                                 "h2d_1stream": [round(v[0], 2) for v in feed_all], "h2d_3streams": [round(v[1], 2) for v in feed_all],
                                 "d2h_3streams": [round(v[2], 2) for v in feed_all], "duplex3_h2d": [round(v[3], 2) for v in feed_all],
