@@ -69,3 +69,48 @@ def test_soak_every_result_byte_equals_the_oracle(oracle, name, w, h, nf, bf, fx
     assert frames_bad == 0, f"{name}: {frames_bad} of {eyes * count} frames differ from the oracle"
     assert len(seen) == count, "the soak frames are not all distinct"
     assert total_kp >= eyes * count * nf and (not stereo or total_m > 100 * count)
+
+
+def test_soak_matchers_on_many_distinct_pairs(oracle):
+    """BASELINE.json configs 4 and 5 in breadth: SearchForInitialization (ratio 0.9, window 100) on 192 distinct TUM-shaped
+    frame pairs and the one-bucket SearchByBoW (brute-force kNN + ratio 0.75, TH_LOW strict) on 96 distinct KITTI-shaped
+    pairs of ~2000 x 2000 features, every match array equal to the oracle's (which is pinned to the reference's ORBmatcher.cc)."""
+    import torch
+    assert torch.cuda.is_available()
+    import orb_slam2_b200 as gx
+    # config 4
+    w, h, npairs = 640, 480, 192
+    base = [synth.mono_pair(30000 + i, w, h)[:2] for i in range(16)]
+    A = np.stack([synth.variant(base[i % 16][0], i // 16) for i in range(npairs)])
+    B = np.stack([synth.variant(base[i % 16][1], i // 16) for i in range(npairs)])
+    G = gx.ORBextractor(1000, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=2 * npairs)
+    G.extract_batch(np.concatenate([A, B]))
+    res = G.fetch(0, 2 * npairs)
+    F1 = [gx.Frame(res[i][0], res[i][1], w, h) for i in range(npairs)]
+    F2 = [gx.Frame(res[npairs + i][0], res[npairs + i][1], w, h) for i in range(npairs)]
+    prevs = [np.stack([f.mvKeysUn["x"], f.mvKeysUn["y"]], 1).astype(np.float32) for f in F1]
+    refs = [oracle.search_init(a.mvKeysUn, a.mDescriptors, b.mvKeysUn, b.mDescriptors, w, h, p, 0.9, 100, True) for a, b, p in zip(F1, F2, prevs)]
+    nm, m12 = gx.ORBmatcher(0.9, True).SearchForInitializationBatch(F1, F2, prevs, 100)
+    bad = [i for i in range(npairs) if nm[i] != refs[i][1] or not np.array_equal(m12[i], refs[i][0]) or not np.array_equal(prevs[i], refs[i][2])]
+    assert not bad, f"SearchForInitialization differs on pairs {bad[:8]}"
+    assert sum(nm) > 20 * npairs
+    G.close()
+    # config 5
+    w, h, npairs = 1241, 376, 96
+    base = [synth.mono_pair(31000 + i, w, h)[:2] for i in range(16)]
+    A = np.stack([synth.variant(base[i % 16][0], i // 16) for i in range(npairs)])
+    B = np.stack([synth.variant(base[i % 16][1], i // 16) for i in range(npairs)])
+    G = gx.ORBextractor(2000, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=2 * npairs)
+    G.extract_batch(np.concatenate([A, B]))
+    res = G.fetch(0, 2 * npairs)
+    As = [(res[i][1], res[i][0]["angle"]) for i in range(npairs)]
+    Bs = [(res[npairs + i][1], res[npairs + i][0]["angle"]) for i in range(npairs)]
+    nm, m12 = gx.ORBmatcher(0.75, True).SearchByBoWBatch(As, Bs, strict=True)
+    bad = []
+    for i in range(npairs):
+        rm, rn = oracle.knn_ratio(As[i][0], As[i][1], Bs[i][0], Bs[i][1], 50, 0.75, True, True)
+        if rn != nm[i] or not np.array_equal(rm, m12[i]):
+            bad.append(i)
+    assert not bad, f"kNN + ratio differs on pairs {bad[:8]}"
+    assert sum(nm) > 100 * npairs
+    G.close()
