@@ -11,6 +11,8 @@
 // = ceil(logf(dmax / dist) / logScale) with glibc's logf restated in double (tools/sweep_logf.c: exhaustive, 0
 // mismatches), then the keyframe's CSR grid (orbx_undistort_grid_batch) is walked in the reference's cell order and
 // the first least descriptor distance among levels [pred-1, pred] wins.
+#include <cstdlib>
+
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -165,54 +167,42 @@ __device__ __forceinline__ int rot_bin30(float a1, float a2) {
   return bin == 30 ? 0 : bin;
 }
 
-__global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  uint32_t* occ = reinterpret_cast<uint32_t*>(smem);            // bit i: keypoint i holds a map point
-  __shared__ int s_hist[30];
-  const int p = blockIdx.x, lane = threadIdx.x;
-  const int n = min(a.n[p], a.cap), m = min(a.m[p], a.mcap);
+// The projection and candidate scan of ONE map point of K17 (warp-wide): the least (distance << 8 | cell column, CSR position)
+// among the keypoints that are free in `occ`, ~0 when the point is skipped or has no candidate.  Shared by the one-warp
+// kernel and by both phases of the latency form.
+__device__ __forceinline__ void ordered_scan(const ProjOrderedArgs& a, int p, int iMP, const uint32_t* occ, int lane, unsigned& whi, unsigned& wlo) {
+  whi = wlo = 0xffffffffu;
   const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
   const orbx_keypoint* kps = a.kps + ko;
   const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
   const int* items = a.cell_items + ko;
-  const float* xf = a.xf + (size_t)p * 15;                      // Rcw (9) tcw (3) Ow (3)
+  const float* xf = a.xf + (size_t)p * 15;
   const float* kb = a.tgt_bounds + (size_t)p * 4;
   const float* gb = a.grid_bounds;
-  int* assigned = a.assigned + ko;
-  for (int w = lane; w < (a.cap + 31) / 32; w += 32) {
-    uint32_t bits = 0u;
-    for (int b = 0; b < 32; ++b) { const int i = w * 32 + b; if (i < n && a.occupied[ko + i]) bits |= 1u << b; }
-    occ[w] = bits;
-  }
-  for (int i = lane; i < a.cap; i += 32) assigned[i] = -1;
-  if (lane < 30) s_hist[lane] = 0;
-  __syncwarp();
-  int nm = 0;
-  for (int iMP = 0; iMP < m; ++iMP) {
-    if (!a.valid[mo + iMP]) continue;
+    if (!a.valid[mo + iMP]) return;
     const float xw[3] = {a.xw[(mo + iMP) * 3], a.xw[(mo + iMP) * 3 + 1], a.xw[(mo + iMP) * 3 + 2]};
     float pc[3];
     gemm3(xf, xf + 9, xw, pc);
     float u, v;
     if (!a.reloc) {
-      if (pc[2] < 0.0f) continue;
+      if (pc[2] < 0.0f) return;
       const float invz = __fdiv_rn(1.0f, pc[2]);
       u = __fadd_rn(__fmul_rn(a.fx, __fmul_rn(pc[0], invz)), a.cx); v = __fadd_rn(__fmul_rn(a.fy, __fmul_rn(pc[1], invz)), a.cy);
-      if (!(u >= kb[0] && u < kb[1] && v >= kb[2] && v < kb[3])) continue;
+      if (!(u >= kb[0] && u < kb[1] && v >= kb[2] && v < kb[3])) return;
     } else {
       const float invzc = (float)__ddiv_rn(1.0, (double)pc[2]);
       u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, pc[0]), invzc), a.cx); v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, pc[1]), invzc), a.cy);
-      if (u < kb[0] || u > kb[1] || v < kb[2] || v > kb[3]) continue;
+      if (u < kb[0] || u > kb[1] || v < kb[2] || v > kb[3]) return;
     }
     const float PO[3] = {__fsub_rn(xw[0], xf[12]), __fsub_rn(xw[1], xf[13]), __fsub_rn(xw[2], xf[14])};
     const double s2 = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)PO[0]), __dmul_rn((double)PO[1], (double)PO[1])), __dmul_rn((double)PO[2], (double)PO[2]));
     const float dist3D = (float)__dsqrt_rn(s2);
     const float dmin = a.dmin[mo + iMP], dmax = a.dmax[mo + iMP];
-    if (dist3D < __fmul_rn(0.8f, dmin) || dist3D > __fmul_rn(1.2f, dmax)) continue;
+    if (dist3D < __fmul_rn(0.8f, dmin) || dist3D > __fmul_rn(1.2f, dmax)) return;
     if (!a.reloc) {
       const float* nn = a.normal + (mo + iMP) * 3;
       const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)nn[0]), __dmul_rn((double)PO[1], (double)nn[1])), __dmul_rn((double)PO[2], (double)nn[2]));
-      if (dot < __dmul_rn(0.5, (double)dist3D)) continue;
+      if (dot < __dmul_rn(0.5, (double)dist3D)) return;
     }
     int level = (int)ceilf(__fdiv_rn(libm_logf(__fdiv_rn(dmax, dist3D)), a.log_scale));
     level = level < 0 ? 0 : (level >= a.nlevels ? a.nlevels - 1 : level);
@@ -222,7 +212,7 @@ __global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a)
     const int cx1 = min(kPGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
     const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
     const int cy1 = min(kPGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
-    if (cx0 >= kPGridCols || cx1 < 0 || cy0 >= kPGridRows || cy1 < 0) continue;
+    if (cx0 >= kPGridCols || cx1 < 0 || cy0 >= kPGridRows || cy1 < 0) return;
     uint32_t qd[8];
 #pragma unroll
     for (int w = 0; w < 8; ++w) qd[w] = __ldg(reinterpret_cast<const uint32_t*>(a.mp_desc + (mo + iMP) * 32) + w);
@@ -239,9 +229,34 @@ __global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a)
         if (h < hi || (h == hi && (unsigned)e < lo)) { hi = h; lo = (unsigned)e; }
       }
     }
-    const unsigned whi = __reduce_min_sync(0xffffffffu, hi);
+    whi = __reduce_min_sync(0xffffffffu, hi);
+    if (whi == 0xffffffffu) return;
+    wlo = __reduce_min_sync(0xffffffffu, hi == whi ? lo : 0xffffffffu);
+}
+
+__global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint32_t* occ = reinterpret_cast<uint32_t*>(smem);            // bit i: keypoint i holds a map point
+  __shared__ int s_hist[30];
+  const int p = blockIdx.x, lane = threadIdx.x;
+  const int n = min(a.n[p], a.cap), m = min(a.m[p], a.mcap);
+  const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
+  const orbx_keypoint* kps = a.kps + ko;
+  const int* items = a.cell_items + ko;
+  int* assigned = a.assigned + ko;
+  for (int w = lane; w < (a.cap + 31) / 32; w += 32) {
+    uint32_t bits = 0u;
+    for (int b = 0; b < 32; ++b) { const int i = w * 32 + b; if (i < n && a.occupied[ko + i]) bits |= 1u << b; }
+    occ[w] = bits;
+  }
+  for (int i = lane; i < a.cap; i += 32) assigned[i] = -1;
+  if (lane < 30) s_hist[lane] = 0;
+  __syncwarp();
+  int nm = 0;
+  for (int iMP = 0; iMP < m; ++iMP) {
+    unsigned whi, wlo;
+    ordered_scan(a, p, iMP, occ, lane, whi, wlo);
     if (whi == 0xffffffffu || (int)(whi >> 8) > a.th_dist) continue;      // no candidate (distance starts at 256) or too far
-    const unsigned wlo = __reduce_min_sync(0xffffffffu, hi == whi ? lo : 0xffffffffu);
     const int bestIdx = items[wlo];
     if (lane == 0) {
       occ[bestIdx >> 5] |= 1u << (bestIdx & 31);
@@ -275,8 +290,103 @@ __global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a)
   if (lane == 0) a.nm[p] = nm;
 }
 
+// K17, latency form (one or a few problems per call: relocalisation and loop closing ask about one frame / keyframe at a
+// time).  A CTA of 8 warps per problem.  Phase A: the winner of every map point against the keypoints that are occupied ON
+// ENTRY, map points strided over the warps.  Phase B: warp 0 walks the map points in list order (hazard H6); a phase-A
+// winner stands unless its keypoint was taken meanwhile by an earlier map point of this call - only then the point is
+// scanned again against the live occupancy (taking away a keypoint that is not a point's winner cannot change its winner).
+constexpr int kOrdParWarps = 8;
+__global__ void __launch_bounds__(kOrdParWarps * 32) k_project_match_ordered_par(ProjOrderedArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint32_t* occ = reinterpret_cast<uint32_t*>(smem);            // bit i: keypoint i holds a map point
+  __shared__ int s_hist[30];
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n = min(a.n[p], a.cap), m = min(a.m[p], a.mcap);
+  const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
+  const orbx_keypoint* kps = a.kps + ko;
+  const int* items = a.cell_items + ko;
+  int* assigned = a.assigned + ko;
+  uint4* spec = a.spec + mo;
+  for (int w = tid; w < (a.cap + 31) / 32; w += kOrdParWarps * 32) {
+    uint32_t bits = 0u;
+    for (int b = 0; b < 32; ++b) { const int i = w * 32 + b; if (i < n && a.occupied[ko + i]) bits |= 1u << b; }
+    occ[w] = bits;
+  }
+  for (int i = tid; i < a.cap; i += kOrdParWarps * 32) assigned[i] = -1;
+  if (tid < 30) s_hist[tid] = 0;
+  __syncthreads();
+  // phase A (occ is only read)
+  for (int iMP = warp; iMP < m; iMP += kOrdParWarps) {
+    unsigned whi, wlo;
+    ordered_scan(a, p, iMP, occ, lane, whi, wlo);
+    if (lane == 0) {
+      int idx = 0; float ang = 0.f;
+      if (whi != 0xffffffffu) { idx = items[wlo]; ang = kps[idx].angle; }
+      spec[iMP] = make_uint4(whi, wlo, (unsigned)idx, __float_as_uint(ang));
+    }
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  // phase B
+  int nm = 0;
+  for (int base = 0; base < m; base += 32) {
+    const int mine = base + lane;
+    const uint4 my4 = mine < m ? spec[mine] : make_uint4(0xffffffffu, 0u, 0u, 0u);
+    const float mysrc = (mine < m && a.reloc && a.checkOri) ? a.src_angle[mo + mine] : 0.f;
+    uint32_t vm = __ballot_sync(0xffffffffu, my4.x != 0xffffffffu);
+    while (vm) {
+      const int j = __ffs((int)vm) - 1;
+      vm &= vm - 1u;
+      const int iMP = base + j;
+      unsigned whi = __shfl_sync(0xffffffffu, my4.x, j);
+      int bestIdx = (int)__shfl_sync(0xffffffffu, my4.z, j);
+      float ang = __uint_as_float(__shfl_sync(0xffffffffu, my4.w, j));
+      const float src = __shfl_sync(0xffffffffu, mysrc, j);
+      if ((occ[bestIdx >> 5] >> (bestIdx & 31)) & 1u) {            // taken meanwhile: scan again (warp-uniform, rare)
+        unsigned wlo;
+        ordered_scan(a, p, iMP, occ, lane, whi, wlo);
+        if (whi == 0xffffffffu) continue;
+        bestIdx = items[wlo];
+        ang = kps[bestIdx].angle;
+      }
+      if ((int)(whi >> 8) > a.th_dist) continue;
+      if (lane == 0) {
+        occ[bestIdx >> 5] |= 1u << (bestIdx & 31);
+        assigned[bestIdx] = iMP;
+        if (a.reloc && a.checkOri) s_hist[rot_bin30(src, ang)] += 1;
+      }
+      ++nm;
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  if (a.reloc && a.checkOri) {                                  // rotation consistency, src/ORBmatcher.cc:1577-1596
+    int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;      // ORBmatcher::ComputeThreeMaxima :1601-1642
+    for (int i = 0; i < 30; ++i) {
+      const int sc = s_hist[i];
+      if (sc > m1) { m3 = m2; m2 = m1; m1 = sc; i3 = i2; i2 = i1; i1 = i; }
+      else if (sc > m2) { m3 = m2; m2 = sc; i3 = i2; i2 = i; }
+      else if (sc > m3) { m3 = sc; i3 = i; }
+    }
+    if ((float)m2 < __fmul_rn(0.1f, (float)m1)) { i2 = -1; i3 = -1; }
+    else if ((float)m3 < __fmul_rn(0.1f, (float)m1)) i3 = -1;
+    int drop = 0;
+    for (int i = lane; i < n; i += 32) {
+      const int mp = assigned[i];
+      if (mp >= 0) {
+        const int b = rot_bin30(a.src_angle[mo + mp], kps[i].angle);
+        if (b != i1 && b != i2 && b != i3) { assigned[i] = -1; ++drop; }
+      }
+    }
+    nm -= __reduce_add_sync(0xffffffffu, drop);
+  }
+  if (lane == 0) a.nm[p] = nm;
+}
+
 int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
-  k_project_match_ordered<<<a.n_problems, 32, (size_t)((a.cap + 31) / 32) * 4, st>>>(a);
+  const size_t smem = (size_t)((a.cap + 31) / 32) * 4;
+  if (a.n_problems <= 148 && !getenv("ORBX_PROJ_SERIAL")) k_project_match_ordered_par<<<a.n_problems, kOrdParWarps * 32, smem, st>>>(a);
+  else k_project_match_ordered<<<a.n_problems, 32, smem, st>>>(a);
   return 1;
 }
 

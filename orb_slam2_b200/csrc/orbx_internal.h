@@ -203,6 +203,7 @@ struct ProjOrderedArgs {
   float fx, fy, cx, cy, log_scale, th;
   float scale[kMaxLevels];
   int* assigned; int* nm;
+  uint4* spec;                // scratch [P][mcap]: per map point {distance<<8 | cell column, CSR position, keypoint, its angle bits} (latency form)
 };
 int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st);
 
