@@ -907,6 +907,7 @@ orbx_status orbx_search_by_bow_batch(const uint8_t* descA, const float* angA, co
   if (on_device) { a.m12 = matches12; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
   a.n_pairs = n_pairs; a.cap = cap; a.th = th; a.ratio = nnratio; a.checkOri = check_orientation; a.strict = strict_lt;
+  CU(sg.alloc((void**)&a.spec, pc * sizeof(uint4)));
   CU(sg.upload());
   g_launches += launch_search_by_bow(a, st);
   CU(cudaGetLastError());

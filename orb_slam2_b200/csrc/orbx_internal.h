@@ -165,6 +165,7 @@ struct BowArgs {
   const uint8_t* dB; const float* angB; const uint8_t* validB; const int* nodeB; const int* nB;
   int n_pairs, cap, th; float ratio; int checkOri, strict;
   int* m12; int* nm;
+  uint4* spec;     // scratch [P][cap]: per sorted query its two nearest free B features (distance << 16 | j) and its node's B run
 };
 int launch_search_by_bow(const BowArgs& a, cudaStream_t st);
 
