@@ -108,3 +108,31 @@ def test_cxx_wrapper_header_compiles(tmp_path):
     r = subprocess.run(["g++", "-std=gnu++14", "-fsyntax-only", "-I", os.path.join(ROOT, "include"),
                         "-I", os.path.join(ROOT, "oracle", "cvshim"), str(src)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+def test_unpack_keypoints_is_host_code_and_rebuilds_the_records(oracle):
+    """orbx_unpack_keypoints needs no device: the oracle's per-level keypoints (level coordinates), packed into the 8-byte form
+    the CUDA path downloads, come back as exactly the cv::KeyPoint records the oracle's extractor returns."""
+    import numpy as np
+    from orb_slam2_b200 import api, synth
+    img = synth.mono_frame(3, 640, 480)
+    E = oracle.Extractor(1000)
+    k, _ = E.extract(img)
+    lv = [E.level_keys(l) for l in range(8)]
+    cap = 1100
+    packed = np.zeros((1, cap), np.uint64); lc = np.zeros((1, 8), np.int32)
+    j = 0
+    for l, q in enumerate(lv):
+        lc[0, l] = len(q)
+        for r in q:
+            key = int(r["x"]) | (int(r["y"]) << 12) | (int(r["response"]) << 24)
+            packed[0, j] = key | (int(np.float32(r["angle"]).view(np.uint32)) << 32)
+            j += 1
+    out = np.zeros((1, cap), api.KP_DTYPE); cnt = np.zeros(1, np.int32)
+    p = api._Params(1000, 1.2, 8, 20, 7)
+    rc = api.lib().orbx_unpack_keypoints(ctypes.byref(p), packed.ctypes.data, lc.ctypes.data, 1, cap, out.ctypes.data, cap, cnt.ctypes.data)
+    assert rc == 0 and cnt[0] == len(k) == j
+    assert out[0, :j].tobytes() == k.tobytes()
+    # a buffer that is too small is refused
+    small = np.zeros((1, 10), api.KP_DTYPE)
+    assert api.lib().orbx_unpack_keypoints(ctypes.byref(p), packed.ctypes.data, lc.ctypes.data, 1, cap, small.ctypes.data, 10, cnt.ctypes.data) == api.ERR_CAPACITY
