@@ -18,7 +18,7 @@ with open(f'profiles/{tag}_launch_shares.csv', 'w') as f:
     f.write("# per-launch times under ncu are cold-cache and serialised: compare SHARES with bench.py's stage_ms_per_step, not absolutes\n")
     f.write("kernel,launches,total_us,avg_us,share_pct\n")
     for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        f.write(f"{k},{n},{t:.1f},{t / n:.1f},{100 * t / tot:.1f}\n")
+        f.write(f"\"{k}\",{n},{t:.1f},{t / n:.1f},{100 * t / tot:.1f}\n")      # quoted: template arguments carry commas
 raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw))); H, U = rows[0], rows[1]
 want = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
@@ -32,7 +32,7 @@ with open(f'profiles/{tag}_ncu_full_one_step.csv', 'w') as f:
     f.write(f"# {desc}\n# ncu --set full --clock-control none --import-source on -k regex:k_ --launch-skip 45 --launch-count 15 (all launches of one step)\n")
     f.write("kernel," + ",".join(f"{w} [{U[i]}]" for w, i in zip(want, idx)) + "\n")
     for r in rows[2:]:
-        f.write(r[ki].split('(')[0].replace('void ', '') + "," + ",".join(r[i].replace(',', '') for i in idx) + "\n")
+        f.write('"' + r[ki].split('(')[0].replace('void ', '') + '",' + ",".join(r[i].replace(',', '') for i in idx) + "\n")
 print(open(f'profiles/{tag}_launch_shares.csv').read())
 
 # ---- profiles/traffic.json: per-stage DRAM bytes per step and issue / pipe utilisation, read by bench.py ----
