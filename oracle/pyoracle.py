@@ -4,6 +4,7 @@ Imported by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs, ne
 orb_slam2_b200 package."""
 import ctypes as C
 import os
+import sys
 import subprocess
 import numpy as np
 
@@ -295,9 +296,9 @@ def ref_slam_kf(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, pct1=60, p
 
 
 def ref_slam_kfbench(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, reps=30, pct1=60, pct2=50, ratio_kk=0.75, ratio_kf=0.7,
-                     th_proj=3.0, th_last=15.0, check_ori=True, only_stereo=False, mono=False, binary=None):
+                     th_proj=3.0, th_last=15.0, check_ori=True, only_stereo=False, mono=False, binary=None, prefix=()):
     """Per-call latency of the ORBmatcher members on the kf case (oracle/ref_slam_cmds.inc:cmd_kfbench) in the given build of the
-    driver.  Returns ({member: (p50_ms, p99_ms, result)}, (n1, n2, map points 1, map points 2))."""
+    driver (`prefix`: a command to run it under, e.g. an ncu launch list).  Returns ({member: (p50_ms, p99_ms, result)}, (n1, n2, map points 1, map points 2))."""
     import tempfile
     ims = [np.ascontiguousarray(x, np.uint8) for x in (L1, R1, L2, R2)]
     h, w = ims[0].shape
@@ -313,7 +314,9 @@ def ref_slam_kfbench(L1, R1, L2, R2, nfeatures, cam, bf, voc, T1, T2, F12, reps=
         fin, fout = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
         with open(fin, "wb") as f:
             f.write(pay)
-        res = subprocess.run([binary or REF_SLAM_BIN, "kfbench", fin, fout], check=True, capture_output=True, text=True)
+        res = subprocess.run(list(prefix) + [binary or REF_SLAM_BIN, "kfbench", fin, fout], check=True, capture_output=True, text=True)
+    if os.environ.get("ORBX_KFBENCH_STDOUT"):                       # experiments: device-side printf of an instrumented build
+        sys.stderr.write(res.stdout)
     out, sizes = {}, None
     for ln in res.stdout.strip().splitlines():
         t = ln.split()

@@ -21,6 +21,10 @@
 #include <cstdlib>
 
 #include "orbx_internal.h"
+#include "ordered.cuh"
+#ifdef ORBX_PHASE_CLOCKS
+#include <cstdio>
+#endif
 
 namespace orbx {
 
@@ -509,107 +513,211 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------
-// K8, latency form: ONE frame per call is the SLAM loop's pattern (src/Tracking.cc:1192), and one warp walking a few hundred
-// map points in order is then all the GPU does.  Here a CTA of 8 warps serves the frame in two phases.
-//   A (parallel, map points strided over the warps): the two smallest candidate keys of every map point against the
-//     frame as it is ON ENTRY (frameObs is not written in this phase);
-//   B (warp 0, in map-point order, hazard H6): a map point's phase-A answer is what the ordered walk would have found
-//     unless one of its two keypoints was claimed meanwhile by an earlier map point of this call (claimed = given a map
-//     point with Observations() > 0, the only way a candidate disappears); only then is the point scanned again, against
-//     the live frameObs.  Then the reference's acceptance rules, the claim, the output.
-// Removing a candidate that is neither the smallest nor the second smallest key changes neither, so B reproduces the
-// sequential result exactly (same tests as the one-warp kernel: parity tests run both).
-constexpr int kProjParWarps = 8;
+// Latency forms of K8 / K9: ONE frame per call is the SLAM loop's pattern (src/Tracking.cc:1192, :886), so a call is one
+// CTA on one SM and what it costs is that CTA's critical path.  Everything the candidate loops touch is therefore staged
+// in shared memory by the whole CTA first (a dependent global load per candidate column was most of the kernel: two L2
+// round trips for frameObs / uRight per column and map point), and the cell sort is done by all warps, not by one.
+constexpr int kParThreads = 1024;
 
+#ifdef ORBX_PHASE_CLOCKS
+// experiments: SM clock at phase boundaries, printed by thread 0 of CTA 0 (build with ORBX_NVCC_EXTRA=-DORBX_PHASE_CLOCKS)
+#define ORBX_CLK(v) const long long v = clock64()
+#define ORBX_CLK_PRINT(name, ...) do { if (threadIdx.x == 0 && blockIdx.x == 0) { const long long c_[] = {__VA_ARGS__}; printf("%s:", name); \
+  for (unsigned i_ = 1; i_ < sizeof(c_) / sizeof(c_[0]); ++i_) printf(" %lld", c_[i_] - c_[i_ - 1]); printf(" cycles\n"); } } while (0)
+#define ORBX_STAT(...) __VA_ARGS__
+#else
+#define ORBX_CLK(v)
+#define ORBX_CLK_PRINT(...)
+#define ORBX_STAT(...)
+#endif
+
+struct FrameStage {                // shared-memory views of one frame
+  float2* sxy;                     // [cap] positions sorted by grid cell
+  uint32_t* smeta;                 // [cap] octave<<28 | cell<<16 | keypoint index, same order
+  int* soff;                       // [kGridCells + 2] cell c = [soff[c+1], soff[c+2])
+  uint32_t* sdesc;                 // [cap][8] descriptors by keypoint index
+  float* sur;                      // [cap] uRight by keypoint index
+  uint32_t* sobs;                  // [(cap+31)/32] bit i: keypoint i holds a map point with Observations() > 0 (live)
+  uint32_t* claim;                 // [(cap+31)/32] bit i: keypoint i was given such a map point by THIS call
+  uint8_t* soct;                   // [cap] octave by keypoint index
+  int* sasg;                       // [cap] the call's output `assigned`, kept here until the ordered phase is over
+  int* stag;                       // [cap] 255, or the lowest lane that wants keypoint i in the round being resolved (order_round)
+  int n_in_grid;
+};
+
+__host__ __device__ inline size_t frame_stage_bytes(int cap) {
+  size_t b = (size_t)cap * 12 + (kGridCells + 2) * sizeof(int);
+  b = ((b + 15) & ~(size_t)15) + (size_t)cap * 32 + (size_t)cap * 12 + (size_t)((cap + 31) / 32) * 8 + (size_t)cap;
+  return (b + 15) & ~(size_t)15;
+}
+
+// All threads of the CTA.  Ends with a block barrier.
+__device__ __forceinline__ void frame_stage(FrameStage& S, uint8_t* smem, int cap, const orbx_keypoint* k, const uint32_t* dg, const float* uRight,
+                                            const int* frameObs, int n, float minX, float minY, float invW, float invH) {
+  __shared__ int s_wsum[32];
+  __shared__ int s_total;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x;
+  S.sxy = reinterpret_cast<float2*>(smem);
+  S.smeta = reinterpret_cast<uint32_t*>(S.sxy + cap);
+  S.soff = reinterpret_cast<int*>(S.smeta + cap);
+  S.sdesc = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(S.soff + kGridCells + 2) + 15) & ~(uintptr_t)15);
+  S.sur = reinterpret_cast<float*>(S.sdesc + (size_t)cap * 8);
+  S.sasg = reinterpret_cast<int*>(S.sur + cap);
+  S.stag = S.sasg + cap;
+  S.sobs = reinterpret_cast<uint32_t*>(S.stag + cap);
+  S.claim = S.sobs + (cap + 31) / 32;
+  S.soct = reinterpret_cast<uint8_t*>(S.claim + (cap + 31) / 32);
+  int* soff = S.soff;
+  ORBX_CLK(fs0);
+  for (int i = tid; i <= kGridCells + 1; i += nth) soff[i] = 0;
+  for (int base = warp * 32; base < cap; base += nth) {                 // 32 keypoints per ballot
+    const int i = base + lane;
+    const uint32_t b = __ballot_sync(0xffffffffu, i < n && frameObs[i] > 0);
+    if (lane == 0) { S.sobs[base >> 5] = b; S.claim[base >> 5] = 0u; }
+  }
+  for (int i = tid; i < n; i += nth) { S.sasg[i] = -1; S.stag[i] = 255; S.sur[i] = uRight[i]; }
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(dg);
+    uint4* dst = reinterpret_cast<uint4*>(S.sdesc);
+    for (int i = tid; i < n * 2; i += nth) dst[i] = __ldg(src + i);
+  }
+  __syncthreads();
+  ORBX_CLK(fs1);
+  for (int i = tid; i < n; i += nth) {                                  // Frame::PosInGrid, src/Frame.cc:382-392
+    const orbx_keypoint kp = k[i];
+    S.soct[i] = (uint8_t)kp.octave;
+    const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) atomicAdd(&soff[gx * 48 + gy + 1], 1);
+  }
+  __syncthreads();
+  ORBX_CLK(fs2);
+  // inclusive scan of soff[0 .. kGridCells]: a contiguous chunk per thread, warp scan of the chunk sums, scan of the warp sums
+  const int ch = (kGridCells + nth) / nth, b0 = tid * ch;
+  int sum = 0;
+  for (int j = 0; j < ch; ++j) sum += (b0 + j <= kGridCells) ? soff[b0 + j] : 0;
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_wsum[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    const int own = lane < (nth >> 5) ? s_wsum[lane] : 0;
+    int v = own;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += t;
+    }
+    s_wsum[lane] = v - own;
+    if (lane == 31) s_total = v;
+  }
+  __syncthreads();
+  int run = s_wsum[warp] + incl - sum;
+  for (int j = 0; j < ch; ++j)
+    if (b0 + j <= kGridCells) { run += soff[b0 + j]; soff[b0 + j] = run; }   // soff[c+1] = end of cell c
+  __syncthreads();
+  ORBX_CLK(fs3);
+  for (int i = tid; i < n; i += nth) {                                  // fill each cell from its end downwards: soff[c+1] = start of cell c
+    const orbx_keypoint kp = k[i];
+    const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) {
+      const int c = gx * 48 + gy;
+      const int pos = atomicSub(&soff[c + 1], 1) - 1;
+      S.sxy[pos] = make_float2(kp.x, kp.y);
+      S.smeta[pos] = ((uint32_t)kp.octave << 28) | ((uint32_t)c << 16) | (uint32_t)i;
+    }
+  }
+  __syncthreads();
+  ORBX_CLK(fs4);
+  ORBX_CLK_PRINT("frame_stage copy / histogram / scan / fill", fs0, fs1, fs2, fs3, fs4);
+  S.n_in_grid = s_total;
+}
+
+__device__ __forceinline__ bool bit_of(const uint32_t* w, int i) { return (w[i >> 5] >> (i & 31)) & 1u; }
+
+// K8, latency form.
 struct ProjMP { int inView, level; float viewCos, x, y, xr; uint32_t dw; };
 
-// the two smallest keys dist<<32 | cell<<16 | idx among map point c's candidates (warp-wide; every lane returns them)
-__device__ __forceinline__ void proj_scan(const ProjArgs& a, const ProjMP& c, const int* cstart, int n_in_grid, const float2* sxy, const uint32_t* smeta,
-                                          const uint32_t* d, const float* uRight, const int* frameObs, float minX, float minY, float invW, float invH,
-                                          int lane, unsigned long long& o1, unsigned long long& o2) {
-  o1 = o2 = ~0ull;
-  if (!c.inView) return;
+// Map point c's candidate list against S.sobs as it is now (warp-wide; every lane returns the same):
+// {l0 | complete << 31, l1, l2, l3}, l = distance << 16 | keypoint in ascending (distance, cell, keypoint) = the reference's
+// first-wins streaming over GetFeaturesInArea's order; kNoKey = none.
+__device__ __forceinline__ uint4 proj_scan(const ProjArgs& a, const ProjMP& c, const FrameStage& S, float minX, float minY, float invW, float invH, int lane) {
+  const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+  if (!c.inView) return none;
   const int lvl = min(max(c.level, 0), a.nlevels - 1);
   float r = ((double)c.viewCos > 0.998) ? 2.5f : 4.0f;
   if (a.th != 1.0f) r = __fmul_rn(r, a.th);
   const float R = __fmul_rn(r, a.scale[lvl]);
   const float x = c.x, y = c.y;
+  // GetFeaturesInArea's cell window, src/Frame.cc:332-346: (x - mnMinX -+ r) * inv, left to right
   const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, minX), R), invW)));
-  if (cx0 >= 64) return;
+  if (cx0 >= 64) return none;
   const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, minX), R), invW)));
-  if (cx1 < 0) return;
+  if (cx1 < 0) return none;
   const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, minY), R), invH)));
-  if (cy0 >= 48) return;
+  if (cy0 >= 48) return none;
   const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, minY), R), invH)));
-  if (cy1 < 0) return;
+  if (cy1 < 0) return none;
   uint32_t q[8];
 #pragma unroll
   for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
+  const int* cstart = S.soff + 1;
   unsigned long long k1 = ~0ull, k2 = ~0ull;
+  int cnt = 0;
   for (int ix = cx0; ix <= cx1; ++ix) {
     const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
-    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : n_in_grid;
+    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : S.n_in_grid;
     for (int e = e_lo + lane; e < e_hi; e += 32) {
-      const uint32_t meta = smeta[e];
+      const uint32_t meta = S.smeta[e];
       const int oct = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
-      if (oct < lvl - 1 || oct > lvl) continue;
-      const float2 pt = sxy[e];
+      if (oct < lvl - 1 || oct > lvl) continue;                                       // GetFeaturesInArea level window
+      const float2 pt = S.sxy[e];
       if (!(fabsf(__fsub_rn(pt.x, x)) < R && fabsf(__fsub_rn(pt.y, y)) < R)) continue;
-      if (frameObs[idx] > 0) continue;
-      const float ur = uRight[idx];
+      if (bit_of(S.sobs, idx)) continue;                                              // already holds an observed map point
+      const float ur = S.sur[idx];
       if (ur > 0.f && fabsf(__fsub_rn(c.xr, ur)) > R) continue;
-      const unsigned long long key = ((unsigned long long)ham8(q, d + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
+      const unsigned long long key = ((unsigned long long)ham8(q, S.sdesc + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
+      ++cnt;
       if (key < k1) { k2 = k1; k1 = key; }
       else if (key < k2) k2 = key;
     }
   }
-  const unsigned hi1 = (unsigned)(k1 >> 32), lo1 = (unsigned)k1;
-  const unsigned ghi = __reduce_min_sync(0xffffffffu, hi1);
-  if (ghi == 0xffffffffu) return;
-  const unsigned glo = __reduce_min_sync(0xffffffffu, hi1 == ghi ? lo1 : 0xffffffffu);
-  const bool owner = hi1 == ghi && lo1 == glo;
-  const unsigned long long mine2 = owner ? k2 : k1;
-  const unsigned hi2 = (unsigned)(mine2 >> 32), lo2 = (unsigned)mine2;
-  const unsigned shi = __reduce_min_sync(0xffffffffu, hi2);
-  const unsigned slo = __reduce_min_sync(0xffffffffu, hi2 == shi ? lo2 : 0xffffffffu);
-  o1 = ((unsigned long long)ghi << 32) | glo;
-  o2 = shi == 0xffffffffu ? ~0ull : (((unsigned long long)shi << 32) | slo);
+  unsigned hi[4], lo[4];
+  bool complete;
+  warp_top4(k1, k2, cnt, hi, lo, complete);
+  uint32_t l[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
+  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
 }
 
-__global__ void __launch_bounds__(kProjParWarps * 32) k_search_projection_par(ProjArgs a) {
+// the reference's acceptance of a (best, second best) pair, src/ORBmatcher.cc:108-124; keys distance << 16 | keypoint
+__device__ __forceinline__ bool proj_accept(uint32_t k1, uint32_t k2, const uint8_t* soct, float ratio) {
+  if (k1 == kNoKey) return false;
+  const int bestDist = (int)(k1 >> 16);
+  if (bestDist > 100) return false;                                                   // TH_HIGH
+  const int bestLvl = soct[k1 & 0xFFFFu];
+  const int bestDist2 = k2 == kNoKey ? 256 : (int)(k2 >> 16);
+  const int bestLvl2 = k2 == kNoKey ? -1 : (int)soct[k2 & 0xFFFFu];
+  return !(bestLvl == bestLvl2 && (float)bestDist > __fmul_rn(ratio, (float)bestDist2));
+}
+
+__global__ void __launch_bounds__(kParThreads) k_search_projection_par(ProjArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
-  float2* sxy = reinterpret_cast<float2*>(smem);
-  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);
-  int* soff = reinterpret_cast<int*>(smeta + a.cap);
-  uint32_t* sdesc = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(soff + kGridCells + 2) + 15) & ~(uintptr_t)15);   // [cap][8]
-  uint32_t* claim = sdesc + (size_t)a.cap * 8;                          // [(cap + 31) / 32] keypoints claimed by this call
-  uint8_t* soct = reinterpret_cast<uint8_t*>(claim + (a.cap + 31) / 32);  // [cap] octave per keypoint
-  __shared__ int s_ngrid;
-  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   const int n = a.n[p], m = a.m[p];
-  const orbx_keypoint* k = a.k + (size_t)p * a.cap;
-  const uint32_t* dg = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
-  const float* uRight = a.uRight + (size_t)p * a.cap;
   int* frameObs = a.frameObs + (size_t)p * a.cap;
   int* assigned = a.assigned + (size_t)p * a.cap;
   const size_t mo = (size_t)p * a.mcap;
   uint4* spec = a.spec + mo;
-
-  for (int i = tid; i < n; i += kProjParWarps * 32) { assigned[i] = -1; soct[i] = (uint8_t)k[i].octave; }
-  for (int i = tid; i < (a.cap + 31) / 32; i += kProjParWarps * 32) claim[i] = 0u;
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(dg);
-    uint4* dst = reinterpret_cast<uint4*>(sdesc);
-    for (int i = tid; i < n * 2; i += kProjParWarps * 32) dst[i] = __ldg(src + i);
-  }
   const float minX = a.gb[0], minY = a.gb[2], invW = a.gb[4], invH = a.gb[5];
-  if (warp == 0) {
-    const int ng = grid_sort(k, n, minX, minY, invW, invH, sxy, smeta, soff, lane);
-    if (lane == 0) s_ngrid = ng;
-  }
-  __syncthreads();
-  const int n_in_grid = s_ngrid;
-  const int* cstart = soff + 1;
+  FrameStage S;
+  ORBX_CLK(t0);
+  frame_stage(S, smem, a.cap, a.k + (size_t)p * a.cap, reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32), a.uRight + (size_t)p * a.cap,
+              frameObs, n, minX, minY, invW, invH);
   auto fetch = [&](int i) {
     ProjMP q;
     q.inView = i < m ? a.inView[mo + i] : 0;
@@ -620,55 +728,85 @@ __global__ void __launch_bounds__(kProjParWarps * 32) k_search_projection_par(Pr
     return q;
   };
   // phase A
+  ORBX_CLK(t1);
   {
     ProjMP nx = fetch(warp);
-    for (int iMP = warp; iMP < m; iMP += kProjParWarps) {
+    for (int iMP = warp; iMP < m; iMP += nwarps) {
       const ProjMP c = nx;
-      nx = fetch(iMP + kProjParWarps);
-      unsigned long long k1, k2;
-      proj_scan(a, c, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, minX, minY, invW, invH, lane, k1, k2);
-      if (lane == 0) spec[iMP] = make_uint4((unsigned)(k1 >> 32), (unsigned)k1, (unsigned)(k2 >> 32), (unsigned)k2);
+      nx = fetch(iMP + nwarps);
+      const uint4 l = proj_scan(a, c, S, minX, minY, invW, invH, lane);
+      if (lane == 0) spec[iMP] = l;
     }
   }
   __syncthreads();
-  if (warp != 0) return;
-  // phase B: 32 map points per round - their phase-A keys and Observations() arrive by one coalesced load each and are
-  // handed round by shuffles, the octaves come from shared memory: no dependent global load per map point
-  int nm = 0;
-  for (int base = 0; base < m; base += 32) {
-    const int mine = base + lane;
-    const uint4 my4 = mine < m ? spec[mine] : make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-    const int myobs = mine < m ? a.mpObs[mo + mine] : 0;
-    const int cnt = min(32, m - base);
-    for (int j = 0; j < cnt; ++j) {
-      const int iMP = base + j;
-      const unsigned x = __shfl_sync(0xffffffffu, my4.x, j), y = __shfl_sync(0xffffffffu, my4.y, j);
-      const unsigned z = __shfl_sync(0xffffffffu, my4.z, j), w4 = __shfl_sync(0xffffffffu, my4.w, j);
-      const int obs = __shfl_sync(0xffffffffu, myobs, j);
-      unsigned long long k1 = ((unsigned long long)x << 32) | y, k2 = ((unsigned long long)z << 32) | w4;
-      if (k1 == ~0ull) continue;
-      const int i1 = (int)(y & 0xFFFF), i2 = (int)(w4 & 0xFFFF);
-      const bool stale = ((claim[i1 >> 5] >> (i1 & 31)) & 1u) || (k2 != ~0ull && ((claim[i2 >> 5] >> (i2 & 31)) & 1u));
-      if (stale) {                                                       // warp-uniform: rare
-        const ProjMP c = fetch(iMP);
-        proj_scan(a, c, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, minX, minY, invW, invH, lane, k1, k2);
-        if (k1 == ~0ull) continue;
+  ORBX_CLK(t2);
+  // phase B
+  if (warp == 0) {
+    int nm = 0;
+    ORBX_STAT(int dbg_serial = 0;)
+    for (int base = 0; base < m; base += 32) {
+      const int iMP = base + lane;
+      const uint4 my4 = iMP < m ? spec[iMP] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+      const int obs = iMP < m ? a.mpObs[mo + iMP] : 0;
+      const bool complete = my4.x >> 31;
+      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
+      const uint32_t have = __ballot_sync(0xffffffffu, key[0] != kNoKey);
+      if (!have) continue;
+      unsigned hitP = 0u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (key[k] != kNoKey && bit_of(S.claim, (int)(key[k] & 0xFFFFu))) hitP |= 1u << k;
+      bool acc = false, starved = false;
+      int bestIdx = -1;
+      order_round(key, hitP, S.stag, lane, [&](unsigned hit) {
+        uint32_t k1 = kNoKey, k2 = kNoKey;                               // the first two keys nobody earlier has claimed
+#pragma unroll
+        for (int k = 3; k >= 0; --k)
+          if (key[k] != kNoKey && !((hit >> k) & 1u)) { k2 = k1; k1 = key[k]; }
+        starved = !complete && k2 == kNoKey && key[0] != kNoKey;         // the list ran out before two free keys were found
+        acc = proj_accept(k1, k2, S.soct, a.ratio);
+        bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
+        return (acc && obs > 0) ? bestIdx : -1;
+      });
+      if (!__any_sync(0xffffffffu, starved)) {
+        if (acc) {
+          atomicMax(&S.sasg[bestIdx], iMP);                              // a keypoint given away twice keeps the later map point
+          if (obs > 0) { atomicOr(&S.claim[bestIdx >> 5], 1u << (bestIdx & 31)); atomicOr(&S.sobs[bestIdx >> 5], 1u << (bestIdx & 31)); }
+        }
+        nm += __popc(__ballot_sync(0xffffffffu, acc));
+        __syncwarp();
+        continue;
       }
-      const int bestDist = (int)(k1 >> 32), bestIdx = (int)(k1 & 0xFFFF);
-      if (bestDist > 100) continue;                                      // TH_HIGH
-      const int bestLvl = soct[bestIdx];
-      const int bestDist2 = k2 == ~0ull ? 256 : (int)(k2 >> 32);
-      const int bestLvl2 = k2 == ~0ull ? -1 : (int)soct[k2 & 0xFFFF];
-      if (bestLvl == bestLvl2 && (float)bestDist > __fmul_rn(a.ratio, (float)bestDist2)) continue;
-      if (lane == 0) {
-        assigned[bestIdx] = iMP; frameObs[bestIdx] = obs;
-        if (obs > 0) claim[bestIdx >> 5] |= 1u << (bestIdx & 31);
+      // the rare round: one map point at a time, each scanned again against the live occupancy
+      ORBX_STAT(++dbg_serial;)
+      for (int j = 0; j < 32; ++j) {
+        if (!((have >> j) & 1u)) continue;
+        const ProjMP c = fetch(base + j);
+        const uint4 l = proj_scan(a, c, S, minX, minY, invW, invH, lane);
+        const uint32_t k1 = l.x & 0x7FFFFFFFu;
+        if (!proj_accept(k1, l.y, S.soct, a.ratio)) continue;
+        const int bi = (int)(k1 & 0xFFFFu), o = __shfl_sync(0xffffffffu, obs, j);
+        if (lane == 0) {
+          S.sasg[bi] = base + j;
+          if (o > 0) { S.claim[bi >> 5] |= 1u << (bi & 31); S.sobs[bi >> 5] |= 1u << (bi & 31); }
+        }
+        ++nm;
+        __syncwarp();
       }
-      ++nm;
-      __syncwarp();
     }
+    if (lane == 0) a.nm[p] = nm;
+    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K8 phase B: %d serial rounds, nm %d of %d\n", dbg_serial, nm, m);)
   }
-  if (lane == 0) a.nm[p] = nm;
+  __syncthreads();
+  ORBX_CLK(t3);
+  // results leave together: assigned[], and frameObs[i] = Observations() of the map point keypoint i ended up with
+  for (int i = tid; i < n; i += blockDim.x) {
+    const int v = S.sasg[i];
+    assigned[i] = v;
+    if (v >= 0) frameObs[i] = a.mpObs[mo + v];
+  }
+  ORBX_CLK(t4);
+  ORBX_CLK_PRINT("k_search_projection_par stage / A / B / flush", t0, t1, t2, t3, t4);
 }
 
 int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
@@ -676,10 +814,10 @@ int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
   const size_t with_desc = ((base + 15) & ~(size_t)15) + (size_t)a.cap * 32;
   // latency mode (a few frames per call): one warp per SM anyway, so spend the shared memory on the descriptors;
   // throughput mode keeps the small footprint (6 CTAs per SM)
-  const size_t par = with_desc + (size_t)((a.cap + 31) / 32) * 4 + (size_t)a.cap;
+  const size_t par = frame_stage_bytes(a.cap);
   if (a.n_pairs <= 148 && par <= 200 * 1024 && !getenv("ORBX_PROJ_SERIAL")) {
     cudaFuncSetAttribute(k_search_projection_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
-    k_search_projection_par<<<a.n_pairs, kProjParWarps * 32, par, st>>>(a);
+    k_search_projection_par<<<a.n_pairs, kParThreads, par, st>>>(a);
   } else if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
     cudaFuncSetAttribute(k_search_projection<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)with_desc);
     k_search_projection<true><<<a.n_pairs, 32, with_desc, st>>>(a);
@@ -837,183 +975,232 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
 }
 
 // ------------------------------------------------------------------------------------------
-// K9, latency form (see K8's): phase A - every last-frame keypoint that carries a map point gets the smallest candidate key
-// against the current frame as it is on entry, keypoints strided over 8 warps; phase B - warp 0 walks them in index order,
-// re-scans only the ones whose keypoint was claimed meanwhile, applies TH_HIGH, claims, and records the rotation events.
+// K9, latency form (see K8's): the frame side staged by frame_stage; the last-frame keypoints that carry a map point are
+// compacted (in index order) into a list in shared memory; phase A - every entry of the list gets the smallest candidate
+// key against the current frame as it is on entry, entries strided over the warps, the next entry's fields in flight;
+// phase B - warp 0 walks the list in order, re-scans only the entries whose keypoint was claimed meanwhile, applies
+// TH_HIGH, claims, and records the rotation events.
 struct ProjLP { int octave; float X0, X1, X2; uint32_t dw; };
 
-__device__ __forceinline__ unsigned long long projf_scan(const ProjFrameArgs& a, const ProjLP& c, const float* Tr, int mode, const int* cstart, int n_in_grid,
-                                                         const float2* sxy, const uint32_t* smeta, const uint32_t* d, const float* uRight,
-                                                         const int* frameObs, const float* gbv, int lane) {
+// list entry c's candidate list against S.sobs as it is now, in K8's format (proj_scan)
+__device__ __forceinline__ uint4 projf_scan(const ProjFrameArgs& a, const ProjLP& c, const float* Tr, int mode, const FrameStage& S,
+                                            const float* gbv, int lane) {
+  const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
   const float minX = gbv[0], maxX = gbv[1], minY = gbv[2], maxY = gbv[3], invW = gbv[4], invH = gbv[5];
   float c3[3];
 #pragma unroll
   for (int r = 0; r < 3; ++r)
     c3[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(Tr[3 * r], c.X0), __fmul_rn(Tr[3 * r + 1], c.X1)), __fmul_rn(Tr[3 * r + 2], c.X2)), Tr[9 + r]);
   const float invzc = (float)(1.0 / (double)c3[2]);
-  if (invzc < 0.f) return ~0ull;
+  if (invzc < 0.f) return none;
   const float u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, c3[0]), invzc), a.cx), v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, c3[1]), invzc), a.cy);
-  if (u < minX || u > maxX || v < minY || v > maxY) return ~0ull;
-  if (!(u == u) || !(v == v)) return ~0ull;
+  if (u < minX || u > maxX || v < minY || v > maxY) return none;                     // src/ORBmatcher.cc:1373-1376
+  if (!(u == u) || !(v == v)) return none;                                           // NaN never passes the reference's window either
   const int oct = min(max(c.octave, 0), a.nlevels - 1);
   const float R = __fmul_rn(a.th, a.scale[oct]);
   const int l_lo = mode == 1 ? oct : (mode == 2 ? 0 : oct - 1), l_hi = mode == 1 ? 99 : (mode == 2 ? oct : oct + 1);
   const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, minX), R), invW)));
-  if (cx0 >= 64) return ~0ull;
+  if (cx0 >= 64) return none;
   const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, minX), R), invW)));
-  if (cx1 < 0) return ~0ull;
+  if (cx1 < 0) return none;
   const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, minY), R), invH)));
-  if (cy0 >= 48) return ~0ull;
+  if (cy0 >= 48) return none;
   const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, minY), R), invH)));
-  if (cy1 < 0) return ~0ull;
+  if (cy1 < 0) return none;
   const float ur_pred = __fsub_rn(u, __fmul_rn(a.bf, invzc));
   uint32_t q[8];
 #pragma unroll
   for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
-  unsigned long long best = ~0ull;
+  const int* cstart = S.soff + 1;
+  unsigned long long k1 = ~0ull, k2 = ~0ull;
+  int cnt = 0;
   for (int ix = cx0; ix <= cx1; ++ix) {
     const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
-    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : n_in_grid;
+    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : S.n_in_grid;
     for (int e = e_lo + lane; e < e_hi; e += 32) {
-      const uint32_t meta = smeta[e];
+      const uint32_t meta = S.smeta[e];
       const int oct2 = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
       if (oct2 < l_lo || oct2 > l_hi) continue;
-      const float2 pt = sxy[e];
+      const float2 pt = S.sxy[e];
       if (!(fabsf(__fsub_rn(pt.x, u)) < R && fabsf(__fsub_rn(pt.y, v)) < R)) continue;
-      if (frameObs[idx] > 0) continue;
-      const float ur = uRight[idx];
+      if (bit_of(S.sobs, idx)) continue;
+      const float ur = S.sur[idx];
       if (ur > 0.f && fabsf(__fsub_rn(ur_pred, ur)) > R) continue;
-      const unsigned long long key = ((unsigned long long)ham8(q, d + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
-      best = min(best, key);
+      const unsigned long long key = ((unsigned long long)ham8(q, S.sdesc + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
+      ++cnt;
+      if (key < k1) { k2 = k1; k1 = key; }
+      else if (key < k2) k2 = key;
     }
   }
-  const unsigned hi1 = (unsigned)(best >> 32), lo1 = (unsigned)best;
-  const unsigned ghi = __reduce_min_sync(0xffffffffu, hi1);
-  if (ghi == 0xffffffffu) return ~0ull;
-  const unsigned glo = __reduce_min_sync(0xffffffffu, hi1 == ghi ? lo1 : 0xffffffffu);
-  return ((unsigned long long)ghi << 32) | glo;
+  unsigned hi[4], lo[4];
+  bool complete;
+  warp_top4(k1, k2, cnt, hi, lo, complete);
+  uint32_t l[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
+  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
 }
 
-__global__ void __launch_bounds__(kProjParWarps * 32) k_search_projection_frame_par(ProjFrameArgs a) {
+__global__ void __launch_bounds__(kParThreads) k_search_projection_frame_par(ProjFrameArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
-  float2* sxy = reinterpret_cast<float2*>(smem);
-  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);
-  int* soff = reinterpret_cast<int*>(smeta + a.cap);
-  uint32_t* sdesc = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(soff + kGridCells + 2) + 15) & ~(uintptr_t)15);
-  uint32_t* claim = sdesc + (size_t)a.cap * 8;
   __shared__ int s_hist[kHisto];
-  __shared__ int s_ngrid;
-  __shared__ float s_gb[6];
-  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ float s_gb[6], s_Tr[12];
+  __shared__ int s_bcnt[kParThreads / 32 + 1];
+  __shared__ int s_nm;
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
   const int n = a.n[p], nLast = a.nLast[p], mode = a.mode[p];
   const orbx_keypoint* k = a.k + (size_t)p * a.cap;
-  const uint32_t* dg = reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32);
-  const float* uRight = a.uRight + (size_t)p * a.cap;
   int* frameObs = a.frameObs + (size_t)p * a.cap;
   int* assigned = a.assigned + (size_t)p * a.cap;
-  int* events = a.events + (size_t)p * a.lcap;
   const size_t lo = (size_t)p * a.lcap;
-  uint2* spec = a.spec + lo;
-
-  for (int i = tid; i < n; i += kProjParWarps * 32) assigned[i] = -1;
-  for (int i = tid; i < (a.cap + 31) / 32; i += kProjParWarps * 32) claim[i] = 0u;
+  uint4* spec = a.spec + lo;                                             // indexed by list position
+  uint16_t* svalid = reinterpret_cast<uint16_t*>(smem + frame_stage_bytes(a.cap));   // [lcap] last-frame indices with a map point, ascending
+  int* sev = reinterpret_cast<int*>(smem + frame_stage_bytes(a.cap) + (((size_t)a.lcap * 2 + 15) & ~(size_t)15));   // [lcap] accepted matches
   if (tid < kHisto) s_hist[tid] = 0;
   if (tid < 6) s_gb[tid] = a.gb[tid];
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(dg);
-    uint4* dst = reinterpret_cast<uint4*>(sdesc);
-    for (int i = tid; i < n * 2; i += kProjParWarps * 32) dst[i] = __ldg(src + i);
+  if (tid >= 32 && tid < 44) s_Tr[tid - 32] = a.pose[(size_t)p * 12 + tid - 32];
+  // ordered compaction of the valid last-frame keypoints: rounds of blockDim.x flags
+  ORBX_CLK(t0);
+  int nvalid = 0;
+  for (int base = 0; base < nLast; base += nth) {
+    const int i = base + tid;
+    const bool ok = i < nLast && a.lastValid[lo + i];
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) s_bcnt[warp] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < nwarps; ++w) { const int c = s_bcnt[w]; before += w < warp ? c : 0; total += c; }
+    if (ok) svalid[nvalid + before + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)i;
+    nvalid += total;
+    __syncthreads();
   }
-  if (warp == 0) {
-    const int ng = grid_sort(k, n, a.gb[0], a.gb[2], a.gb[4], a.gb[5], sxy, smeta, soff, lane);
-    if (lane == 0) s_ngrid = ng;
-  }
-  __syncthreads();
-  const int n_in_grid = s_ngrid;
-  const int* cstart = soff + 1;
-  float Tr[12];
-#pragma unroll
-  for (int i = 0; i < 12; ++i) Tr[i] = a.pose[(size_t)p * 12 + i];
-  auto fetch = [&](int i) {
+  FrameStage S;
+  ORBX_CLK(t1);
+  frame_stage(S, smem, a.cap, k, reinterpret_cast<const uint32_t*>(a.d + (size_t)p * a.cap * 32), a.uRight + (size_t)p * a.cap, frameObs, n,
+              a.gb[0], a.gb[2], a.gb[4], a.gb[5]);
+  const float* Tr = s_Tr;                                                // written before frame_stage's barriers
+  auto fetch = [&](int c) {                                              // fields of list entry c
     ProjLP q;
-    const bool ok = i >= 0 && i < nLast;
+    const bool ok = c < nvalid;
+    const int i = ok ? svalid[c] : 0;
     q.octave = ok ? a.lastOctave[lo + i] : 0;
     q.X0 = ok ? a.lastXw[(lo + i) * 3] : 0.f; q.X1 = ok ? a.lastXw[(lo + i) * 3 + 1] : 0.f; q.X2 = ok ? a.lastXw[(lo + i) * 3 + 2] : 0.f;
     q.dw = (ok && lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (lo + i) * 32) + lane) : 0u;
     return q;
   };
-  // phase A: blocks of 32 last-frame keypoints strided over the warps; inside a block only the valid ones are scanned
-  for (int base = warp * 32; base < nLast; base += kProjParWarps * 32) {
-    const int mine = base + lane;
-    uint32_t vm = __ballot_sync(0xffffffffu, mine < nLast && a.lastValid[lo + mine]);
-    unsigned long long mykey = ~0ull;
-    while (vm) {
-      const int b = __ffs((int)vm) - 1;
-      vm &= vm - 1u;
-      const ProjLP c = fetch(base + b);
-      const unsigned long long key = projf_scan(a, c, Tr, mode, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, s_gb, lane);
-      if (lane == b) mykey = key;
+  // phase A
+  ORBX_CLK(t2);
+  {
+    ProjLP nx = fetch(warp);
+    for (int c = warp; c < nvalid; c += nwarps) {
+      const ProjLP cur = nx;
+      nx = fetch(c + nwarps);
+      const uint4 l = projf_scan(a, cur, Tr, mode, S, s_gb, lane);
+      if (lane == 0) spec[c] = l;
     }
-    if (mine < nLast) spec[mine] = make_uint2((unsigned)(mykey >> 32), (unsigned)mykey);      // invalid keypoints: ~0
   }
   __syncthreads();
-  if (warp != 0) return;
-  // phase B
-  int nm = 0;
-  for (int base = 0; base < nLast; base += 32) {
-    const int mine = base + lane;
-    const uint2 my2 = mine < nLast ? spec[mine] : make_uint2(0xffffffffu, 0xffffffffu);
-    const int myobs = mine < nLast ? a.mpObs[lo + mine] : 0;
-    const float myang = mine < nLast ? a.lastAngle[lo + mine] : 0.f;
-    uint32_t vm = __ballot_sync(0xffffffffu, my2.x != 0xffffffffu);
-    while (vm) {
-      const int j = __ffs((int)vm) - 1;
-      vm &= vm - 1u;
-      const int i = base + j;
-      unsigned long long key = ((unsigned long long)__shfl_sync(0xffffffffu, my2.x, j) << 32) | __shfl_sync(0xffffffffu, my2.y, j);
-      const int obs = __shfl_sync(0xffffffffu, myobs, j);
-      const float ang = __shfl_sync(0xffffffffu, myang, j);
-      const int i1 = (int)(key & 0xFFFF);
-      if ((claim[i1 >> 5] >> (i1 & 31)) & 1u) {                          // its keypoint went to an earlier map point: scan again (rare)
-        const ProjLP c = fetch(i);
-        key = projf_scan(a, c, Tr, mode, cstart, n_in_grid, sxy, smeta, sdesc, uRight, frameObs, s_gb, lane);
-        if (key == ~0ull) continue;
+  ORBX_CLK(t3);
+  // phase B (see "ordered resolution" above): one key per map point here - the first of its list nobody earlier has claimed
+  if (warp == 0) {
+    int nm = 0;
+    ORBX_STAT(int dbg_serial = 0;)
+    for (int base = 0; base < nvalid; base += 32) {
+      const int mine = base + lane;
+      const int myi = mine < nvalid ? svalid[mine] : 0;
+      const uint4 my4 = mine < nvalid ? spec[mine] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+      const int obs = mine < nvalid ? a.mpObs[lo + myi] : 0;
+      const bool complete = my4.x >> 31;
+      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
+      const uint32_t have = __ballot_sync(0xffffffffu, key[0] != kNoKey);
+      if (!have) continue;
+      unsigned hitP = 0u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (key[k] != kNoKey && bit_of(S.claim, (int)(key[k] & 0xFFFFu))) hitP |= 1u << k;
+      bool acc = false, starved = false;
+      int bestIdx = -1;
+      order_round(key, hitP, S.stag, lane, [&](unsigned hit) {
+        uint32_t k1 = kNoKey;
+#pragma unroll
+        for (int k = 3; k >= 0; --k)
+          if (key[k] != kNoKey && !((hit >> k) & 1u)) k1 = key[k];
+        starved = !complete && k1 == kNoKey && key[0] != kNoKey;
+        acc = k1 != kNoKey && (k1 >> 16) <= 100u;                        // TH_HIGH
+        bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
+        return (acc && obs > 0) ? bestIdx : -1;
+      });
+      if (!__any_sync(0xffffffffu, starved)) {
+        const uint32_t accm = __ballot_sync(0xffffffffu, acc);
+        if (acc) {
+          atomicMax(&S.sasg[bestIdx], myi);                              // a keypoint given away twice keeps the later map point
+          if (obs > 0) { atomicOr(&S.claim[bestIdx >> 5], 1u << (bestIdx & 31)); atomicOr(&S.sobs[bestIdx >> 5], 1u << (bestIdx & 31)); }
+          sev[nm + __popc(accm & ((1u << lane) - 1u))] = (mine << 16) | bestIdx;   // list position | keypoint: the rotation bin is worked out afterwards
+        }
+        nm += __popc(accm);
+        __syncwarp();
+        continue;
       }
-      if ((unsigned)(key >> 32) > 100u) continue;                        // worse than TH_HIGH
-      const int bestIdx = (int)(key & 0xFFFF);
-      if (lane == 0) {
-        assigned[bestIdx] = i;
-        frameObs[bestIdx] = obs;
-        if (obs > 0) claim[bestIdx >> 5] |= 1u << (bestIdx & 31);
-        int bin = 0;
-        if (a.checkOri) { bin = rot_bin(ang, k[bestIdx].angle); s_hist[bin] += 1; }
-        events[nm] = (bin << 16) | bestIdx;
+      ORBX_STAT(++dbg_serial;)
+      for (int j = 0; j < 32; ++j) {                                     // the rare round: one at a time, scanned again
+        if (!((have >> j) & 1u)) continue;
+        const ProjLP c = fetch(base + j);
+        const uint4 l = projf_scan(a, c, Tr, mode, S, s_gb, lane);
+        const uint32_t k1 = l.x & 0x7FFFFFFFu;
+        if (k1 == kNoKey || (k1 >> 16) > 100u) continue;
+        const int bi = (int)(k1 & 0xFFFFu), o = __shfl_sync(0xffffffffu, obs, j), i = __shfl_sync(0xffffffffu, myi, j);
+        if (lane == 0) {
+          S.sasg[bi] = i;
+          if (o > 0) { S.claim[bi >> 5] |= 1u << (bi & 31); S.sobs[bi >> 5] |= 1u << (bi & 31); }
+          sev[nm] = ((base + j) << 16) | bi;
+        }
+        ++nm;
+        __syncwarp();
       }
-      ++nm;
-      __syncwarp();
     }
+    if (lane == 0) s_nm = nm;
+    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K9 phase B: %d serial rounds, nm %d of %d\n", dbg_serial, nm, nvalid);)
   }
-  __syncwarp();
+  __syncthreads();
+  ORBX_CLK(t4);
+  // frameObs[i] = Observations() of the map point keypoint i ended up with (before the rotation check takes matches away)
+  for (int i = tid; i < n; i += nth) {
+    const int v = S.sasg[i];
+    if (v >= 0) frameObs[i] = a.mpObs[lo + v];
+  }
+  const int nm0 = s_nm;
   if (a.checkOri) {
+    // rotation histogram of the accepted matches (counts do not depend on the order), whole CTA: no angle load in the ordered loop
+    for (int e = tid; e < nm0; e += nth) {
+      const unsigned ev = (unsigned)sev[e];
+      const int idx = (int)(ev & 0xFFFF), bin = rot_bin(a.lastAngle[lo + svalid[ev >> 16]], k[idx].angle);
+      atomicAdd(&s_hist[bin], 1);
+      sev[e] = (bin << 16) | idx;
+    }
+    __syncthreads();
     int k_a, k_b, k_c;
     three_maxima(s_hist, k_a, k_b, k_c);
     int drop = 0;
-    for (int e = lane; e < nm; e += 32) {
-      const int bin = events[e] >> 16, idx = events[e] & 0xFFFF;
-      if (bin != k_a && bin != k_b && bin != k_c) { assigned[idx] = -1; ++drop; }
+    for (int e = tid; e < nm0; e += nth) {
+      const int bin = sev[e] >> 16, idx = sev[e] & 0xFFFF;
+      if (bin != k_a && bin != k_b && bin != k_c) { S.sasg[idx] = -1; ++drop; }
     }
-    nm -= __reduce_add_sync(0xffffffffu, drop);
+    if (drop) atomicSub(&s_nm, drop);
+    __syncthreads();
   }
-  if (lane == 0) a.nm[p] = nm;
+  for (int i = tid; i < n; i += nth) assigned[i] = S.sasg[i];
+  if (tid == 0) a.nm[p] = s_nm;
+  ORBX_CLK(t5);
+  ORBX_CLK_PRINT("k_search_projection_frame_par compact / stage / A / B / rotation + flush", t0, t1, t2, t3, t4, t5);
 }
 
 int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st) {
   const size_t base = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
   const size_t with_desc = ((base + 15) & ~(size_t)15) + (size_t)a.cap * 32;
-  const size_t par = with_desc + (size_t)((a.cap + 31) / 32) * 4;
-  if (a.n_pairs <= 148 && par <= 200 * 1024 && !getenv("ORBX_PROJ_SERIAL")) {    // latency mode, see launch_search_projection
+  const size_t par = frame_stage_bytes(a.cap) + (((size_t)a.lcap * 2 + 15) & ~(size_t)15) + (size_t)a.lcap * 4;
+  if (a.n_pairs <= 148 && par <= 200 * 1024 && a.lcap <= 65535 && !getenv("ORBX_PROJ_SERIAL")) {    // latency mode, see launch_search_projection
     cudaFuncSetAttribute(k_search_projection_frame_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
-    k_search_projection_frame_par<<<a.n_pairs, kProjParWarps * 32, par, st>>>(a);
+    k_search_projection_frame_par<<<a.n_pairs, kParThreads, par, st>>>(a);
   } else if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
     cudaFuncSetAttribute(k_search_projection_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)with_desc);
     k_search_projection_frame<true><<<a.n_pairs, 32, with_desc, st>>>(a);

@@ -14,6 +14,7 @@
 #include <cstdlib>
 
 #include "orbx_internal.h"
+#include "ordered.cuh"
 
 namespace orbx {
 
@@ -167,71 +168,80 @@ __device__ __forceinline__ int rot_bin30(float a1, float a2) {
   return bin == 30 ? 0 : bin;
 }
 
-// The projection and candidate scan of ONE map point of K17 (warp-wide): the least (distance << 8 | cell column, CSR position)
-// among the keypoints that are free in `occ`, ~0 when the point is skipped or has no candidate.  Shared by the one-warp
-// kernel and by both phases of the latency form.
-__device__ __forceinline__ void ordered_scan(const ProjOrderedArgs& a, int p, int iMP, const uint32_t* occ, int lane, unsigned& whi, unsigned& wlo) {
-  whi = wlo = 0xffffffffu;
-  const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
-  const orbx_keypoint* kps = a.kps + ko;
-  const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
-  const int* items = a.cell_items + ko;
+// The projection of ONE map point of K17 and its search window (every lane computes the same): false when the point is skipped.
+struct OrdWin { float u, v, radius; int level, lvl_hi, cx0, cx1, cy0, cy1; uint32_t qd[8]; };
+
+__device__ __forceinline__ bool ordered_window(const ProjOrderedArgs& a, int p, int iMP, OrdWin& w) {
+  const size_t mo = (size_t)p * a.mcap;
   const float* xf = a.xf + (size_t)p * 15;
   const float* kb = a.tgt_bounds + (size_t)p * 4;
   const float* gb = a.grid_bounds;
-    if (!a.valid[mo + iMP]) return;
-    const float xw[3] = {a.xw[(mo + iMP) * 3], a.xw[(mo + iMP) * 3 + 1], a.xw[(mo + iMP) * 3 + 2]};
-    float pc[3];
-    gemm3(xf, xf + 9, xw, pc);
-    float u, v;
-    if (!a.reloc) {
-      if (pc[2] < 0.0f) return;
-      const float invz = __fdiv_rn(1.0f, pc[2]);
-      u = __fadd_rn(__fmul_rn(a.fx, __fmul_rn(pc[0], invz)), a.cx); v = __fadd_rn(__fmul_rn(a.fy, __fmul_rn(pc[1], invz)), a.cy);
-      if (!(u >= kb[0] && u < kb[1] && v >= kb[2] && v < kb[3])) return;
-    } else {
-      const float invzc = (float)__ddiv_rn(1.0, (double)pc[2]);
-      u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, pc[0]), invzc), a.cx); v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, pc[1]), invzc), a.cy);
-      if (u < kb[0] || u > kb[1] || v < kb[2] || v > kb[3]) return;
-    }
-    const float PO[3] = {__fsub_rn(xw[0], xf[12]), __fsub_rn(xw[1], xf[13]), __fsub_rn(xw[2], xf[14])};
-    const double s2 = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)PO[0]), __dmul_rn((double)PO[1], (double)PO[1])), __dmul_rn((double)PO[2], (double)PO[2]));
-    const float dist3D = (float)__dsqrt_rn(s2);
-    const float dmin = a.dmin[mo + iMP], dmax = a.dmax[mo + iMP];
-    if (dist3D < __fmul_rn(0.8f, dmin) || dist3D > __fmul_rn(1.2f, dmax)) return;
-    if (!a.reloc) {
-      const float* nn = a.normal + (mo + iMP) * 3;
-      const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)nn[0]), __dmul_rn((double)PO[1], (double)nn[1])), __dmul_rn((double)PO[2], (double)nn[2]));
-      if (dot < __dmul_rn(0.5, (double)dist3D)) return;
-    }
-    int level = (int)ceilf(__fdiv_rn(libm_logf(__fdiv_rn(dmax, dist3D)), a.log_scale));
-    level = level < 0 ? 0 : (level >= a.nlevels ? a.nlevels - 1 : level);
-    const int lvl_hi = a.reloc ? level + 1 : level;
-    const float radius = __fmul_rn(a.th, a.scale[level]);
-    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
-    const int cx1 = min(kPGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
-    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
-    const int cy1 = min(kPGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
-    if (cx0 >= kPGridCols || cx1 < 0 || cy0 >= kPGridRows || cy1 < 0) return;
-    uint32_t qd[8];
+  if (!a.valid[mo + iMP]) return false;
+  const float xw[3] = {a.xw[(mo + iMP) * 3], a.xw[(mo + iMP) * 3 + 1], a.xw[(mo + iMP) * 3 + 2]};
+  float pc[3];
+  gemm3(xf, xf + 9, xw, pc);
+  float u, v;
+  if (!a.reloc) {
+    if (pc[2] < 0.0f) return false;
+    const float invz = __fdiv_rn(1.0f, pc[2]);
+    u = __fadd_rn(__fmul_rn(a.fx, __fmul_rn(pc[0], invz)), a.cx); v = __fadd_rn(__fmul_rn(a.fy, __fmul_rn(pc[1], invz)), a.cy);
+    if (!(u >= kb[0] && u < kb[1] && v >= kb[2] && v < kb[3])) return false;
+  } else {
+    const float invzc = (float)__ddiv_rn(1.0, (double)pc[2]);
+    u = __fadd_rn(__fmul_rn(__fmul_rn(a.fx, pc[0]), invzc), a.cx); v = __fadd_rn(__fmul_rn(__fmul_rn(a.fy, pc[1]), invzc), a.cy);
+    if (u < kb[0] || u > kb[1] || v < kb[2] || v > kb[3]) return false;
+  }
+  const float PO[3] = {__fsub_rn(xw[0], xf[12]), __fsub_rn(xw[1], xf[13]), __fsub_rn(xw[2], xf[14])};
+  const double s2 = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)PO[0]), __dmul_rn((double)PO[1], (double)PO[1])), __dmul_rn((double)PO[2], (double)PO[2]));
+  const float dist3D = (float)__dsqrt_rn(s2);
+  const float dmin = a.dmin[mo + iMP], dmax = a.dmax[mo + iMP];
+  if (dist3D < __fmul_rn(0.8f, dmin) || dist3D > __fmul_rn(1.2f, dmax)) return false;
+  if (!a.reloc) {
+    const float* nn = a.normal + (mo + iMP) * 3;
+    const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)nn[0]), __dmul_rn((double)PO[1], (double)nn[1])), __dmul_rn((double)PO[2], (double)nn[2]));
+    if (dot < __dmul_rn(0.5, (double)dist3D)) return false;
+  }
+  int level = (int)ceilf(__fdiv_rn(libm_logf(__fdiv_rn(dmax, dist3D)), a.log_scale));
+  level = level < 0 ? 0 : (level >= a.nlevels ? a.nlevels - 1 : level);
+  w.level = level; w.lvl_hi = a.reloc ? level + 1 : level;
+  const float radius = __fmul_rn(a.th, a.scale[level]);
+  w.u = u; w.v = v; w.radius = radius;
+  w.cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
+  w.cx1 = min(kPGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
+  w.cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
+  w.cy1 = min(kPGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
+  if (w.cx0 >= kPGridCols || w.cx1 < 0 || w.cy0 >= kPGridRows || w.cy1 < 0) return false;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) qd[w] = __ldg(reinterpret_cast<const uint32_t*>(a.mp_desc + (mo + iMP) * 32) + w);
-    unsigned hi = 0xffffffffu, lo = 0xffffffffu;                // (distance << 8 | cell column), CSR position
-    for (int ix = cx0; ix <= cx1; ++ix) {
-      const int e_hi = cs[ix * kPGridRows + cy1 + 1];
-      for (int e = cs[ix * kPGridRows + cy0] + lane; e < e_hi; e += 32) {
-        const int idx = items[e];
-        if ((occ[idx >> 5] >> (idx & 31)) & 1u) continue;
-        const orbx_keypoint kp = kps[idx];
-        if (!(fabsf(__fsub_rn(kp.x, u)) < radius && fabsf(__fsub_rn(kp.y, v)) < radius)) continue;
-        if (kp.octave < level - 1 || kp.octave > lvl_hi) continue;
-        const unsigned h = ((unsigned)ham8p(qd, reinterpret_cast<const uint32_t*>(a.desc + (ko + idx) * 32)) << 8) | (unsigned)ix;
-        if (h < hi || (h == hi && (unsigned)e < lo)) { hi = h; lo = (unsigned)e; }
-      }
+  for (int q = 0; q < 8; ++q) w.qd[q] = __ldg(reinterpret_cast<const uint32_t*>(a.mp_desc + (mo + iMP) * 32) + q);
+  return true;
+}
+
+// The candidate scan of ONE map point of K17 (warp-wide): the least (distance << 8 | cell column, CSR position)
+// among the keypoints that are free in `occ`, ~0 when the point is skipped or has no candidate.
+__device__ __forceinline__ void ordered_scan(const ProjOrderedArgs& a, int p, int iMP, const uint32_t* occ, int lane, unsigned& whi, unsigned& wlo) {
+  whi = wlo = 0xffffffffu;
+  OrdWin w;
+  if (!ordered_window(a, p, iMP, w)) return;
+  const size_t ko = (size_t)p * a.cap;
+  const orbx_keypoint* kps = a.kps + ko;
+  const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
+  const int* items = a.cell_items + ko;
+  unsigned hi = 0xffffffffu, lo = 0xffffffffu;                // (distance << 8 | cell column), CSR position
+  for (int ix = w.cx0; ix <= w.cx1; ++ix) {
+    const int e_hi = cs[ix * kPGridRows + w.cy1 + 1];
+    for (int e = cs[ix * kPGridRows + w.cy0] + lane; e < e_hi; e += 32) {
+      const int idx = items[e];
+      if ((occ[idx >> 5] >> (idx & 31)) & 1u) continue;
+      const orbx_keypoint kp = kps[idx];
+      if (!(fabsf(__fsub_rn(kp.x, w.u)) < w.radius && fabsf(__fsub_rn(kp.y, w.v)) < w.radius)) continue;
+      if (kp.octave < w.level - 1 || kp.octave > w.lvl_hi) continue;
+      const unsigned h = ((unsigned)ham8p(w.qd, reinterpret_cast<const uint32_t*>(a.desc + (ko + idx) * 32)) << 8) | (unsigned)ix;
+      if (h < hi || (h == hi && (unsigned)e < lo)) { hi = h; lo = (unsigned)e; }
     }
-    whi = __reduce_min_sync(0xffffffffu, hi);
-    if (whi == 0xffffffffu) return;
-    wlo = __reduce_min_sync(0xffffffffu, hi == whi ? lo : 0xffffffffu);
+  }
+  whi = __reduce_min_sync(0xffffffffu, hi);
+  if (whi == 0xffffffffu) return;
+  wlo = __reduce_min_sync(0xffffffffu, hi == whi ? lo : 0xffffffffu);
 }
 
 __global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a) {
@@ -291,76 +301,167 @@ __global__ void __launch_bounds__(32) k_project_match_ordered(ProjOrderedArgs a)
 }
 
 // K17, latency form (one or a few problems per call: relocalisation and loop closing ask about one frame / keyframe at a
-// time).  A CTA of 8 warps per problem.  Phase A: the winner of every map point against the keypoints that are occupied ON
-// ENTRY, map points strided over the warps.  Phase B: warp 0 walks the map points in list order (hazard H6); a phase-A
-// winner stands unless its keypoint was taken meanwhile by an earlier map point of this call - only then the point is
-// scanned again against the live occupancy (taking away a keypoint that is not a point's winner cannot change its winner).
-constexpr int kOrdParWarps = 8;
-__global__ void __launch_bounds__(kOrdParWarps * 32) k_project_match_ordered_par(ProjOrderedArgs a) {
+// time): a CTA of 32 warps per problem, and - as in K8's latency form - nothing in the loops leaves the SM.  The target's
+// CSR grid arrives as it is (cell starts; positions / octave / index in CSR order), descriptors and angles by keypoint
+// index, the occupancy as a bitset, the output `assigned` stays in shared memory until the end.
+//   Phase A: the winner of every map point against the keypoints that are occupied ON ENTRY, map points strided over the warps.
+//   Phase B: warp 0 walks the map points in list order (hazard H6); a phase-A winner stands unless its keypoint was taken
+//   meanwhile by an earlier map point of this call - only then the point is scanned again against the live occupancy
+//   (taking away a keypoint that is not a point's winner cannot change its winner).
+constexpr int kOrdParThreads = 1024;
+
+struct OrdStage { int* cs; float2* sxy; uint32_t* smeta; uint32_t* sdesc; float* sang; int* sasg; int* stag; uint32_t* occ; };
+
+__host__ __device__ inline size_t ord_stage_bytes(int cap) {
+  size_t b = (size_t)(kPCells + 1 + 3) / 4 * 16;            // cell starts, padded to 16 bytes
+  b += (size_t)cap * (8 + 4 + 32 + 4 + 4 + 4) + (size_t)((cap + 31) / 32) * 4;
+  return (b + 15) & ~(size_t)15;
+}
+
+// Map point iMP's candidate list against S.occ as it is now (warp-wide, every lane returns the same):
+// {l0 | complete << 31, l1, l2, l3}, l = distance << 16 | keypoint in ascending (distance, cell column, CSR position) = the
+// reference's first-least over its enumeration; kNoKey = none.
+__device__ __forceinline__ uint4 ordered_scan_staged(const ProjOrderedArgs& a, int p, int iMP, const OrdStage& S, int lane) {
+  const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+  OrdWin w;
+  if (!ordered_window(a, p, iMP, w)) return none;
+  unsigned long long k1 = ~0ull, k2 = ~0ull;                  // (distance << 8 | cell column) << 32 | CSR position
+  int cnt = 0;
+  for (int ix = w.cx0; ix <= w.cx1; ++ix) {
+    const int e_hi = S.cs[ix * kPGridRows + w.cy1 + 1];
+    for (int e = S.cs[ix * kPGridRows + w.cy0] + lane; e < e_hi; e += 32) {
+      const uint32_t meta = S.smeta[e];
+      const int idx = (int)(meta & 0xFFFFFFu), oct = (int)(meta >> 24);
+      if ((S.occ[idx >> 5] >> (idx & 31)) & 1u) continue;
+      const float2 pt = S.sxy[e];
+      if (!(fabsf(__fsub_rn(pt.x, w.u)) < w.radius && fabsf(__fsub_rn(pt.y, w.v)) < w.radius)) continue;
+      if (oct < w.level - 1 || oct > w.lvl_hi) continue;
+      const uint32_t* g = S.sdesc + (size_t)idx * 8;
+      const uint4 b0 = *reinterpret_cast<const uint4*>(g), b1 = *reinterpret_cast<const uint4*>(g + 4);
+      const int d = __popc(w.qd[0] ^ b0.x) + __popc(w.qd[1] ^ b0.y) + __popc(w.qd[2] ^ b0.z) + __popc(w.qd[3] ^ b0.w) + __popc(w.qd[4] ^ b1.x) +
+                    __popc(w.qd[5] ^ b1.y) + __popc(w.qd[6] ^ b1.z) + __popc(w.qd[7] ^ b1.w);
+      const unsigned long long key = ((unsigned long long)(((unsigned)d << 8) | (unsigned)ix) << 32) | (unsigned)e;
+      ++cnt;
+      if (key < k1) { k2 = k1; k1 = key; }
+      else if (key < k2) k2 = key;
+    }
+  }
+  unsigned hi[4], lo[4];
+  bool complete;
+  warp_top4(k1, k2, cnt, hi, lo, complete);
+  uint32_t l[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : (((hi[k] >> 8) << 16) | (S.smeta[lo[k]] & 0xFFFFu));
+  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
+}
+
+__global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(ProjOrderedArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
-  uint32_t* occ = reinterpret_cast<uint32_t*>(smem);            // bit i: keypoint i holds a map point
   __shared__ int s_hist[30];
-  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ int s_nm;
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
   const int n = min(a.n[p], a.cap), m = min(a.m[p], a.mcap);
   const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
   const orbx_keypoint* kps = a.kps + ko;
-  const int* items = a.cell_items + ko;
   int* assigned = a.assigned + ko;
   uint4* spec = a.spec + mo;
-  for (int w = tid; w < (a.cap + 31) / 32; w += kOrdParWarps * 32) {
-    uint32_t bits = 0u;
-    for (int b = 0; b < 32; ++b) { const int i = w * 32 + b; if (i < n && a.occupied[ko + i]) bits |= 1u << b; }
-    occ[w] = bits;
+  OrdStage S;
+  S.cs = reinterpret_cast<int*>(smem);
+  S.sdesc = reinterpret_cast<uint32_t*>(smem + (size_t)(kPCells + 1 + 3) / 4 * 16);      // 16-byte aligned for any cap
+  S.sxy = reinterpret_cast<float2*>(S.sdesc + (size_t)a.cap * 8);
+  S.smeta = reinterpret_cast<uint32_t*>(S.sxy + a.cap);
+  S.sang = reinterpret_cast<float*>(S.smeta + a.cap);
+  S.sasg = reinterpret_cast<int*>(S.sang + a.cap);
+  S.stag = S.sasg + a.cap;
+  S.occ = reinterpret_cast<uint32_t*>(S.stag + a.cap);
+  {
+    const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
+    const int* items = a.cell_items + ko;
+    for (int i = tid; i <= kPCells; i += nth) S.cs[i] = cs[i];
+    const int n_items = min(cs[kPCells], a.cap);
+    for (int e = tid; e < n_items; e += nth) {
+      const int idx = items[e];
+      const orbx_keypoint kp = kps[idx];
+      S.sxy[e] = make_float2(kp.x, kp.y);
+      S.smeta[e] = ((uint32_t)kp.octave << 24) | (uint32_t)idx;
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(a.desc + ko * 32);
+    uint4* dst = reinterpret_cast<uint4*>(S.sdesc);
+    for (int i = tid; i < n * 2; i += nth) dst[i] = __ldg(src + i);
+    for (int i = tid; i < a.cap; i += nth) { S.sasg[i] = -1; S.stag[i] = 255; S.sang[i] = i < n ? kps[i].angle : 0.f; }
+    for (int base = warp * 32; base < a.cap; base += nth) {
+      const int i = base + lane;
+      const uint32_t b = __ballot_sync(0xffffffffu, i < n && a.occupied[ko + i]);
+      if (lane == 0) S.occ[base >> 5] = b;
+    }
+    if (tid < 30) s_hist[tid] = 0;
   }
-  for (int i = tid; i < a.cap; i += kOrdParWarps * 32) assigned[i] = -1;
-  if (tid < 30) s_hist[tid] = 0;
   __syncthreads();
   // phase A (occ is only read)
-  for (int iMP = warp; iMP < m; iMP += kOrdParWarps) {
-    unsigned whi, wlo;
-    ordered_scan(a, p, iMP, occ, lane, whi, wlo);
-    if (lane == 0) {
-      int idx = 0; float ang = 0.f;
-      if (whi != 0xffffffffu) { idx = items[wlo]; ang = kps[idx].angle; }
-      spec[iMP] = make_uint4(whi, wlo, (unsigned)idx, __float_as_uint(ang));
-    }
+  for (int iMP = warp; iMP < m; iMP += nwarps) {
+    const uint4 l = ordered_scan_staged(a, p, iMP, S, lane);
+    if (lane == 0) spec[iMP] = l;
   }
   __syncthreads();
-  if (warp != 0) return;
-  // phase B
-  int nm = 0;
-  for (int base = 0; base < m; base += 32) {
-    const int mine = base + lane;
-    const uint4 my4 = mine < m ? spec[mine] : make_uint4(0xffffffffu, 0u, 0u, 0u);
-    const float mysrc = (mine < m && a.reloc && a.checkOri) ? a.src_angle[mo + mine] : 0.f;
-    uint32_t vm = __ballot_sync(0xffffffffu, my4.x != 0xffffffffu);
-    while (vm) {
-      const int j = __ffs((int)vm) - 1;
-      vm &= vm - 1u;
-      const int iMP = base + j;
-      unsigned whi = __shfl_sync(0xffffffffu, my4.x, j);
-      int bestIdx = (int)__shfl_sync(0xffffffffu, my4.z, j);
-      float ang = __uint_as_float(__shfl_sync(0xffffffffu, my4.w, j));
-      const float src = __shfl_sync(0xffffffffu, mysrc, j);
-      if ((occ[bestIdx >> 5] >> (bestIdx & 31)) & 1u) {            // taken meanwhile: scan again (warp-uniform, rare)
-        unsigned wlo;
-        ordered_scan(a, p, iMP, occ, lane, whi, wlo);
-        if (whi == 0xffffffffu) continue;
-        bestIdx = items[wlo];
-        ang = kps[bestIdx].angle;
+  // phase B (see ordered.cuh): one key per map point - the first of its list no earlier map point has taken; every match claims
+  if (warp == 0) {
+    int nm = 0;
+    for (int base = 0; base < m; base += 32) {
+      const int iMP = base + lane;
+      const uint4 my4 = iMP < m ? spec[iMP] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+      const float src = (iMP < m && a.reloc && a.checkOri) ? a.src_angle[mo + iMP] : 0.f;
+      const bool complete = my4.x >> 31;
+      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
+      const uint32_t have = __ballot_sync(0xffffffffu, key[0] != kNoKey);
+      if (!have) continue;
+      unsigned hitP = 0u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int idx = (int)(key[k] & 0xFFFFu);
+        if (key[k] != kNoKey && ((S.occ[idx >> 5] >> (idx & 31)) & 1u)) hitP |= 1u << k;
       }
-      if ((int)(whi >> 8) > a.th_dist) continue;
-      if (lane == 0) {
-        occ[bestIdx >> 5] |= 1u << (bestIdx & 31);
-        assigned[bestIdx] = iMP;
-        if (a.reloc && a.checkOri) s_hist[rot_bin30(src, ang)] += 1;
+      bool acc = false, starved = false;
+      int bestIdx = -1;
+      order_round(key, hitP, S.stag, lane, [&](unsigned hit) {
+        uint32_t k1 = kNoKey;
+#pragma unroll
+        for (int k = 3; k >= 0; --k)
+          if (key[k] != kNoKey && !((hit >> k) & 1u)) k1 = key[k];
+        starved = !complete && k1 == kNoKey && key[0] != kNoKey;
+        acc = k1 != kNoKey && (int)(k1 >> 16) <= a.th_dist;
+        bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
+        return bestIdx;
+      });
+      if (!__any_sync(0xffffffffu, starved)) {
+        if (acc) {
+          S.sasg[bestIdx] = iMP;                                         // claims are exclusive here: one writer per keypoint
+          atomicOr(&S.occ[bestIdx >> 5], 1u << (bestIdx & 31));
+          if (a.reloc && a.checkOri) atomicAdd(&s_hist[rot_bin30(src, S.sang[bestIdx])], 1);
+        }
+        nm += __popc(__ballot_sync(0xffffffffu, acc));
+        __syncwarp();
+        continue;
       }
-      ++nm;
-      __syncwarp();
+      for (int j = 0; j < 32; ++j) {                                     // the rare round: one at a time, scanned again
+        if (!((have >> j) & 1u)) continue;
+        const uint4 l = ordered_scan_staged(a, p, base + j, S, lane);
+        const uint32_t k1 = l.x & 0x7FFFFFFFu;
+        if (k1 == kNoKey || (int)(k1 >> 16) > a.th_dist) continue;
+        const int bi = (int)(k1 & 0xFFFFu);
+        const float sj = __shfl_sync(0xffffffffu, src, j);
+        if (lane == 0) {
+          S.occ[bi >> 5] |= 1u << (bi & 31);
+          S.sasg[bi] = base + j;
+          if (a.reloc && a.checkOri) s_hist[rot_bin30(sj, S.sang[bi])] += 1;
+        }
+        ++nm;
+        __syncwarp();
+      }
     }
+    if (lane == 0) s_nm = nm;
   }
-  __syncwarp();
-  if (a.reloc && a.checkOri) {                                  // rotation consistency, src/ORBmatcher.cc:1577-1596
+  __syncthreads();
+  if (a.reloc && a.checkOri) {                                  // rotation consistency, src/ORBmatcher.cc:1577-1596, whole CTA
     int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;      // ORBmatcher::ComputeThreeMaxima :1601-1642
     for (int i = 0; i < 30; ++i) {
       const int sc = s_hist[i];
@@ -371,22 +472,28 @@ __global__ void __launch_bounds__(kOrdParWarps * 32) k_project_match_ordered_par
     if ((float)m2 < __fmul_rn(0.1f, (float)m1)) { i2 = -1; i3 = -1; }
     else if ((float)m3 < __fmul_rn(0.1f, (float)m1)) i3 = -1;
     int drop = 0;
-    for (int i = lane; i < n; i += 32) {
-      const int mp = assigned[i];
+    for (int i = tid; i < n; i += nth) {
+      const int mp = S.sasg[i];
       if (mp >= 0) {
-        const int b = rot_bin30(a.src_angle[mo + mp], kps[i].angle);
-        if (b != i1 && b != i2 && b != i3) { assigned[i] = -1; ++drop; }
+        const int b = rot_bin30(a.src_angle[mo + mp], S.sang[i]);
+        if (b != i1 && b != i2 && b != i3) { S.sasg[i] = -1; ++drop; }
       }
     }
-    nm -= __reduce_add_sync(0xffffffffu, drop);
+    if (drop) atomicSub(&s_nm, drop);
+    __syncthreads();
   }
-  if (lane == 0) a.nm[p] = nm;
+  for (int i = tid; i < a.cap; i += nth) assigned[i] = S.sasg[i];
+  if (tid == 0) a.nm[p] = s_nm;
 }
 
 int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
-  const size_t smem = (size_t)((a.cap + 31) / 32) * 4;
-  if (a.n_problems <= 148 && !getenv("ORBX_PROJ_SERIAL")) k_project_match_ordered_par<<<a.n_problems, kOrdParWarps * 32, smem, st>>>(a);
-  else k_project_match_ordered<<<a.n_problems, 32, smem, st>>>(a);
+  const size_t smem = (size_t)((a.cap + 31) / 32) * 4, par = ord_stage_bytes(a.cap);
+  if (a.n_problems <= 148 && par <= 200 * 1024 && a.cap <= 65536 && !getenv("ORBX_PROJ_SERIAL")) {
+    cudaFuncSetAttribute(k_project_match_ordered_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
+    k_project_match_ordered_par<<<a.n_problems, kOrdParThreads, par, st>>>(a);
+  } else {
+    k_project_match_ordered<<<a.n_problems, 32, smem, st>>>(a);
+  }
   return 1;
 }
 

@@ -1391,7 +1391,7 @@ orbx_status orbx_search_projection_frame_batch(const orbx_keypoint* kps, const u
   if (on_device) { a.assigned = assigned; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.assigned, fc * 4)); CU(sg.alloc((void**)&a.nm, nf * 4)); }
   CU(sg.alloc((void**)&a.events, fl * 4));
-  CU(sg.alloc((void**)&a.spec, fl * sizeof(uint2)));
+  CU(sg.alloc((void**)&a.spec, fl * sizeof(uint4)));
   a.n_pairs = n_frames; a.cap = cap; a.lcap = lcap; a.nlevels = nlevels; a.checkOri = check_orientation;
   CU(sg.in(grid_bounds, 6, on_device, &a.gb));
   a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = bf; a.th = th;

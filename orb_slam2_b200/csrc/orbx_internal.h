@@ -140,7 +140,7 @@ struct ProjArgs {
   float th, ratio;
   float scale[kMaxLevels];
   int* frameObs; int* assigned; int* nm;
-  uint4* spec;                // scratch [P][mcap]: the two smallest candidate keys per map point (latency mode)
+  uint4* spec;                // scratch [P][mcap]: the candidate list (four smallest keys) per map point (latency mode)
 };
 int launch_search_projection(const ProjArgs& a, cudaStream_t st);
 
@@ -156,7 +156,7 @@ struct ProjFrameArgs {
   float scale[kMaxLevels];
   int* frameObs; int* assigned; int* nm;
   int* events;                // scratch [P][lcap]: bin<<16 | keypoint index per accepted match
-  uint2* spec;                // scratch [P][lcap]: the smallest candidate key per last-frame keypoint (latency mode)
+  uint4* spec;                // scratch [P][lcap]: the candidate list per last-frame keypoint that carries a map point (latency mode)
 };
 int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st);
 
@@ -204,7 +204,7 @@ struct ProjOrderedArgs {
   float fx, fy, cx, cy, log_scale, th;
   float scale[kMaxLevels];
   int* assigned; int* nm;
-  uint4* spec;                // scratch [P][mcap]: per map point {distance<<8 | cell column, CSR position, keypoint, its angle bits} (latency form)
+  uint4* spec;                // scratch [P][mcap]: the candidate list (four smallest keys, distance << 16 | keypoint) per map point (latency form)
 };
 int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st);
 
