@@ -22,9 +22,6 @@
 
 #include "orbx_internal.h"
 #include "ordered.cuh"
-#ifdef ORBX_PHASE_CLOCKS
-#include <cstdio>
-#endif
 
 namespace orbx {
 
@@ -519,17 +516,6 @@ __global__ void __launch_bounds__(32) k_search_projection(ProjArgs a) {
 // round trips for frameObs / uRight per column and map point), and the cell sort is done by all warps, not by one.
 constexpr int kParThreads = 1024;
 
-#ifdef ORBX_PHASE_CLOCKS
-// experiments: SM clock at phase boundaries, printed by thread 0 of CTA 0 (build with ORBX_NVCC_EXTRA=-DORBX_PHASE_CLOCKS)
-#define ORBX_CLK(v) const long long v = clock64()
-#define ORBX_CLK_PRINT(name, ...) do { if (threadIdx.x == 0 && blockIdx.x == 0) { const long long c_[] = {__VA_ARGS__}; printf("%s:", name); \
-  for (unsigned i_ = 1; i_ < sizeof(c_) / sizeof(c_[0]); ++i_) printf(" %lld", c_[i_] - c_[i_ - 1]); printf(" cycles\n"); } } while (0)
-#define ORBX_STAT(...) __VA_ARGS__
-#else
-#define ORBX_CLK(v)
-#define ORBX_CLK_PRINT(...)
-#define ORBX_STAT(...)
-#endif
 
 struct FrameStage {                // shared-memory views of one frame
   float2* sxy;                     // [cap] positions sorted by grid cell
@@ -541,7 +527,7 @@ struct FrameStage {                // shared-memory views of one frame
   uint32_t* claim;                 // [(cap+31)/32] bit i: keypoint i was given such a map point by THIS call
   uint8_t* soct;                   // [cap] octave by keypoint index
   int* sasg;                       // [cap] the call's output `assigned`, kept here until the ordered phase is over
-  int* stag;                       // [cap] 255, or the lowest lane that wants keypoint i in the round being resolved (order_round)
+  int* stag;                       // [cap] who wants keypoint i in the round being resolved (order_round)
   int n_in_grid;
 };
 
@@ -575,7 +561,7 @@ __device__ __forceinline__ void frame_stage(FrameStage& S, uint8_t* smem, int ca
     const uint32_t b = __ballot_sync(0xffffffffu, i < n && frameObs[i] > 0);
     if (lane == 0) { S.sobs[base >> 5] = b; S.claim[base >> 5] = 0u; }
   }
-  for (int i = tid; i < n; i += nth) { S.sasg[i] = -1; S.stag[i] = 255; S.sur[i] = uRight[i]; }
+  for (int i = tid; i < n; i += nth) { S.sasg[i] = -1; S.stag[i] = 0; S.sur[i] = uRight[i]; }
   {
     const uint4* src = reinterpret_cast<const uint4*>(dg);
     uint4* dst = reinterpret_cast<uint4*>(S.sdesc);
@@ -639,13 +625,13 @@ __device__ __forceinline__ void frame_stage(FrameStage& S, uint8_t* smem, int ca
 __device__ __forceinline__ bool bit_of(const uint32_t* w, int i) { return (w[i >> 5] >> (i & 31)) & 1u; }
 
 // K8, latency form.
-struct ProjMP { int inView, level; float viewCos, x, y, xr; uint32_t dw; };
+struct ProjMP { int inView, level, obs; float viewCos, x, y, xr; uint32_t dw; };
 
 // Map point c's candidate list against S.sobs as it is now (warp-wide; every lane returns the same):
-// {l0 | complete << 31, l1, l2, l3}, l = distance << 16 | keypoint in ascending (distance, cell, keypoint) = the reference's
-// first-wins streaming over GetFeaturesInArea's order; kNoKey = none.
+// {l0 | complete << 31, l1 | (Observations() > 0) << 31, l2, l3}, l = distance << 16 | keypoint in ascending (distance, cell,
+// keypoint) = the reference's first-wins streaming over GetFeaturesInArea's order; kNoKey = none.
 __device__ __forceinline__ uint4 proj_scan(const ProjArgs& a, const ProjMP& c, const FrameStage& S, float minX, float minY, float invW, float invH, int lane) {
-  const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+  const uint4 none = make_uint4(0xffffffffu, kNoKey | (c.obs > 0 ? 0x80000000u : 0u), kNoKey, kNoKey);
   if (!c.inView) return none;
   const int lvl = min(max(c.level, 0), a.nlevels - 1);
   float r = ((double)c.viewCos > 0.998) ? 2.5f : 4.0f;
@@ -667,31 +653,32 @@ __device__ __forceinline__ uint4 proj_scan(const ProjArgs& a, const ProjMP& c, c
   const int* cstart = S.soff + 1;
   unsigned long long k1 = ~0ull, k2 = ~0ull;
   int cnt = 0;
-  for (int ix = cx0; ix <= cx1; ++ix) {
-    const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
-    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : S.n_in_grid;
-    for (int e = e_lo + lane; e < e_hi; e += 32) {
+  for_each_in_columns(cx0, cx1, lane,
+    [&](int ix, int& e_lo, int& e_hi) {
+      const int c_hi = ix * 48 + cy1;
+      e_lo = cstart[ix * 48 + cy0]; e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : S.n_in_grid;
+    },
+    [&](int e, int) {
       const uint32_t meta = S.smeta[e];
       const int oct = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
-      if (oct < lvl - 1 || oct > lvl) continue;                                       // GetFeaturesInArea level window
+      if (oct < lvl - 1 || oct > lvl) return;                                         // GetFeaturesInArea level window
       const float2 pt = S.sxy[e];
-      if (!(fabsf(__fsub_rn(pt.x, x)) < R && fabsf(__fsub_rn(pt.y, y)) < R)) continue;
-      if (bit_of(S.sobs, idx)) continue;                                              // already holds an observed map point
+      if (!(fabsf(__fsub_rn(pt.x, x)) < R && fabsf(__fsub_rn(pt.y, y)) < R)) return;
+      if (bit_of(S.sobs, idx)) return;                                                // already holds an observed map point
       const float ur = S.sur[idx];
-      if (ur > 0.f && fabsf(__fsub_rn(c.xr, ur)) > R) continue;
+      if (ur > 0.f && fabsf(__fsub_rn(c.xr, ur)) > R) return;
       const unsigned long long key = ((unsigned long long)ham8(q, S.sdesc + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
       ++cnt;
       if (key < k1) { k2 = k1; k1 = key; }
       else if (key < k2) k2 = key;
-    }
-  }
+    });
   unsigned hi[4], lo[4];
   bool complete;
   warp_top4(k1, k2, cnt, hi, lo, complete);
   uint32_t l[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
-  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
+  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1] | (c.obs > 0 ? 0x80000000u : 0u), l[2], l[3]);
 }
 
 // the reference's acceptance of a (best, second best) pair, src/ORBmatcher.cc:108-124; keys distance << 16 | keypoint
@@ -722,6 +709,7 @@ __global__ void __launch_bounds__(kParThreads) k_search_projection_par(ProjArgs 
     ProjMP q;
     q.inView = i < m ? a.inView[mo + i] : 0;
     q.level = i < m ? a.level[mo + i] : 0;
+    q.obs = i < m ? a.mpObs[mo + i] : 0;
     q.viewCos = i < m ? a.viewCos[mo + i] : 0.f;
     q.x = i < m ? a.projX[mo + i] : 0.f; q.y = i < m ? a.projY[mo + i] : 0.f; q.xr = i < m ? a.projXR[mo + i] : 0.f;
     q.dw = (i < m && lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (mo + i) * 32) + lane) : 0u;
@@ -743,59 +731,67 @@ __global__ void __launch_bounds__(kParThreads) k_search_projection_par(ProjArgs 
   // phase B
   if (warp == 0) {
     int nm = 0;
-    ORBX_STAT(int dbg_serial = 0;)
+    ORBX_STAT(int dbg_serial = 0; int dbg_iters = 0;)
+    int epoch = 0;
+    const uint4 nokeys = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+    uint4 nxt = lane < m ? spec[lane] : nokeys;
     for (int base = 0; base < m; base += 32) {
       const int iMP = base + lane;
-      const uint4 my4 = iMP < m ? spec[iMP] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
-      const int obs = iMP < m ? a.mpObs[mo + iMP] : 0;
-      const bool complete = my4.x >> 31;
-      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
-      const uint32_t have = __ballot_sync(0xffffffffu, key[0] != kNoKey);
-      if (!have) continue;
-      unsigned hitP = 0u;
+      const uint4 my4 = nxt;
+      nxt = iMP + 32 < m ? spec[iMP + 32] : nokeys;                       // the next round's lists are on their way while this one is resolved
+      const bool complete = my4.x >> 31, obs = my4.y >> 31;              // obs: Observations() > 0
+      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y & 0x7FFFFFFFu, my4.z, my4.w};
+      uint32_t todo = __ballot_sync(0xffffffffu, key[0] != kNoKey);      // lanes whose map point is still to be decided
+      while (todo) {
+        const bool mine = (todo >> lane) & 1u;
+        unsigned hitP = 0u;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (key[k] != kNoKey && bit_of(S.claim, (int)(key[k] & 0xFFFFu))) hitP |= 1u << k;
-      bool acc = false, starved = false;
-      int bestIdx = -1;
-      order_round(key, hitP, S.stag, lane, [&](unsigned hit) {
-        uint32_t k1 = kNoKey, k2 = kNoKey;                               // the first two keys nobody earlier has claimed
+        for (int k = 0; k < 4; ++k)
+          if (key[k] != kNoKey && bit_of(S.claim, (int)(key[k] & 0xFFFFu))) hitP |= 1u << k;
+        bool acc = false, starved = false;
+        int bestIdx = -1;
+        const int iters = order_round(key, hitP, S.stag, epoch, lane, [&](unsigned hit) {
+          uint32_t k1 = kNoKey, k2 = kNoKey;                             // the first two keys nobody earlier has claimed
 #pragma unroll
-        for (int k = 3; k >= 0; --k)
-          if (key[k] != kNoKey && !((hit >> k) & 1u)) { k2 = k1; k1 = key[k]; }
-        starved = !complete && k2 == kNoKey && key[0] != kNoKey;         // the list ran out before two free keys were found
-        acc = proj_accept(k1, k2, S.soct, a.ratio);
-        bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
-        return (acc && obs > 0) ? bestIdx : -1;
-      });
-      if (!__any_sync(0xffffffffu, starved)) {
-        if (acc) {
+          for (int k = 3; k >= 0; --k)
+            if (key[k] != kNoKey && !((hit >> k) & 1u)) { k2 = k1; k1 = key[k]; }
+          starved = mine && !complete && k2 == kNoKey;                   // the list ran out before two free keys were found
+          acc = mine && proj_accept(k1, k2, S.soct, a.ratio);
+          bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
+          return (acc && obs) ? bestIdx : -1;
+        });
+        ORBX_STAT(dbg_iters += iters;)
+        (void)iters;
+        // lanes below the first starved one are final (a lane depends on earlier lanes only): they commit together
+        const uint32_t sm = __ballot_sync(0xffffffffu, starved);
+        const int jstar = sm ? __ffs((int)sm) - 1 : 32;
+        const bool commit = acc && lane < jstar;
+        if (commit) {
           atomicMax(&S.sasg[bestIdx], iMP);                              // a keypoint given away twice keeps the later map point
-          if (obs > 0) { atomicOr(&S.claim[bestIdx >> 5], 1u << (bestIdx & 31)); atomicOr(&S.sobs[bestIdx >> 5], 1u << (bestIdx & 31)); }
+          if (obs) { atomicOr(&S.claim[bestIdx >> 5], 1u << (bestIdx & 31)); atomicOr(&S.sobs[bestIdx >> 5], 1u << (bestIdx & 31)); }
         }
-        nm += __popc(__ballot_sync(0xffffffffu, acc));
+        nm += __popc(__ballot_sync(0xffffffffu, commit));
         __syncwarp();
-        continue;
-      }
-      // the rare round: one map point at a time, each scanned again against the live occupancy
-      ORBX_STAT(++dbg_serial;)
-      for (int j = 0; j < 32; ++j) {
-        if (!((have >> j) & 1u)) continue;
-        const ProjMP c = fetch(base + j);
+        if (!sm) break;
+        // the starved map point is scanned again against the live occupancy (exact), then the lanes after it go round again
+        ORBX_STAT(++dbg_serial;)
+        const ProjMP c = fetch(base + jstar);
         const uint4 l = proj_scan(a, c, S, minX, minY, invW, invH, lane);
         const uint32_t k1 = l.x & 0x7FFFFFFFu;
-        if (!proj_accept(k1, l.y, S.soct, a.ratio)) continue;
-        const int bi = (int)(k1 & 0xFFFFu), o = __shfl_sync(0xffffffffu, obs, j);
-        if (lane == 0) {
-          S.sasg[bi] = base + j;
-          if (o > 0) { S.claim[bi >> 5] |= 1u << (bi & 31); S.sobs[bi >> 5] |= 1u << (bi & 31); }
+        if (proj_accept(k1, l.y & 0x7FFFFFFFu, S.soct, a.ratio)) {
+          const int bi = (int)(k1 & 0xFFFFu);
+          if (lane == 0) {
+            S.sasg[bi] = base + jstar;
+            if (l.y >> 31) { S.claim[bi >> 5] |= 1u << (bi & 31); S.sobs[bi >> 5] |= 1u << (bi & 31); }
+          }
+          ++nm;
         }
-        ++nm;
         __syncwarp();
+        todo &= ~((2u << jstar) - 1u);
       }
     }
     if (lane == 0) a.nm[p] = nm;
-    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K8 phase B: %d serial rounds, nm %d of %d\n", dbg_serial, nm, m);)
+    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K8 phase B: %d re-scans, %d fixpoint iterations, nm %d of %d\n", dbg_serial, dbg_iters, nm, m);)
   }
   __syncthreads();
   ORBX_CLK(t3);
@@ -980,12 +976,12 @@ __global__ void __launch_bounds__(32) k_search_projection_frame(ProjFrameArgs a)
 // key against the current frame as it is on entry, entries strided over the warps, the next entry's fields in flight;
 // phase B - warp 0 walks the list in order, re-scans only the entries whose keypoint was claimed meanwhile, applies
 // TH_HIGH, claims, and records the rotation events.
-struct ProjLP { int octave; float X0, X1, X2; uint32_t dw; };
+struct ProjLP { int octave, obs; float X0, X1, X2; uint32_t dw; };
 
 // list entry c's candidate list against S.sobs as it is now, in K8's format (proj_scan)
 __device__ __forceinline__ uint4 projf_scan(const ProjFrameArgs& a, const ProjLP& c, const float* Tr, int mode, const FrameStage& S,
                                             const float* gbv, int lane) {
-  const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+  const uint4 none = make_uint4(0xffffffffu, kNoKey | (c.obs > 0 ? 0x80000000u : 0u), kNoKey, kNoKey);
   const float minX = gbv[0], maxX = gbv[1], minY = gbv[2], maxY = gbv[3], invW = gbv[4], invH = gbv[5];
   float c3[3];
 #pragma unroll
@@ -1014,31 +1010,32 @@ __device__ __forceinline__ uint4 projf_scan(const ProjFrameArgs& a, const ProjLP
   const int* cstart = S.soff + 1;
   unsigned long long k1 = ~0ull, k2 = ~0ull;
   int cnt = 0;
-  for (int ix = cx0; ix <= cx1; ++ix) {
-    const int c_lo = ix * 48 + cy0, c_hi = ix * 48 + cy1;
-    const int e_lo = cstart[c_lo], e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : S.n_in_grid;
-    for (int e = e_lo + lane; e < e_hi; e += 32) {
+  for_each_in_columns(cx0, cx1, lane,
+    [&](int ix, int& e_lo, int& e_hi) {
+      const int c_hi = ix * 48 + cy1;
+      e_lo = cstart[ix * 48 + cy0]; e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : S.n_in_grid;
+    },
+    [&](int e, int) {
       const uint32_t meta = S.smeta[e];
       const int oct2 = (int)(meta >> 28), idx = (int)(meta & 0xFFFF);
-      if (oct2 < l_lo || oct2 > l_hi) continue;
+      if (oct2 < l_lo || oct2 > l_hi) return;
       const float2 pt = S.sxy[e];
-      if (!(fabsf(__fsub_rn(pt.x, u)) < R && fabsf(__fsub_rn(pt.y, v)) < R)) continue;
-      if (bit_of(S.sobs, idx)) continue;
+      if (!(fabsf(__fsub_rn(pt.x, u)) < R && fabsf(__fsub_rn(pt.y, v)) < R)) return;
+      if (bit_of(S.sobs, idx)) return;
       const float ur = S.sur[idx];
-      if (ur > 0.f && fabsf(__fsub_rn(ur_pred, ur)) > R) continue;
+      if (ur > 0.f && fabsf(__fsub_rn(ur_pred, ur)) > R) return;
       const unsigned long long key = ((unsigned long long)ham8(q, S.sdesc + (size_t)idx * 8) << 32) | (meta & 0x0FFFFFFFu);
       ++cnt;
       if (key < k1) { k2 = k1; k1 = key; }
       else if (key < k2) k2 = key;
-    }
-  }
+    });
   unsigned hi[4], lo[4];
   bool complete;
   warp_top4(k1, k2, cnt, hi, lo, complete);
   uint32_t l[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
-  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
+  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1] | (c.obs > 0 ? 0x80000000u : 0u), l[2], l[3]);
 }
 
 __global__ void __launch_bounds__(kParThreads) k_search_projection_frame_par(ProjFrameArgs a) {
@@ -1084,6 +1081,7 @@ __global__ void __launch_bounds__(kParThreads) k_search_projection_frame_par(Pro
     const bool ok = c < nvalid;
     const int i = ok ? svalid[c] : 0;
     q.octave = ok ? a.lastOctave[lo + i] : 0;
+    q.obs = ok ? a.mpObs[lo + i] : 0;
     q.X0 = ok ? a.lastXw[(lo + i) * 3] : 0.f; q.X1 = ok ? a.lastXw[(lo + i) * 3 + 1] : 0.f; q.X2 = ok ? a.lastXw[(lo + i) * 3 + 2] : 0.f;
     q.dw = (ok && lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(a.mpDesc + (lo + i) * 32) + lane) : 0u;
     return q;
@@ -1104,62 +1102,71 @@ __global__ void __launch_bounds__(kParThreads) k_search_projection_frame_par(Pro
   // phase B (see "ordered resolution" above): one key per map point here - the first of its list nobody earlier has claimed
   if (warp == 0) {
     int nm = 0;
-    ORBX_STAT(int dbg_serial = 0;)
+    ORBX_STAT(int dbg_serial = 0; int dbg_iters = 0;)
+    int epoch = 0;
+    const uint4 nokeys = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+    uint4 nxt = lane < nvalid ? spec[lane] : nokeys;
     for (int base = 0; base < nvalid; base += 32) {
       const int mine = base + lane;
       const int myi = mine < nvalid ? svalid[mine] : 0;
-      const uint4 my4 = mine < nvalid ? spec[mine] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
-      const int obs = mine < nvalid ? a.mpObs[lo + myi] : 0;
-      const bool complete = my4.x >> 31;
-      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
-      const uint32_t have = __ballot_sync(0xffffffffu, key[0] != kNoKey);
-      if (!have) continue;
-      unsigned hitP = 0u;
+      const uint4 my4 = nxt;
+      nxt = mine + 32 < nvalid ? spec[mine + 32] : nokeys;
+      const bool complete = my4.x >> 31, obs = my4.y >> 31;              // obs: Observations() > 0
+      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y & 0x7FFFFFFFu, my4.z, my4.w};
+      uint32_t todo = __ballot_sync(0xffffffffu, key[0] != kNoKey);      // lanes whose map point is still to be decided
+      while (todo) {
+        const bool live = (todo >> lane) & 1u;
+        unsigned hitP = 0u;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (key[k] != kNoKey && bit_of(S.claim, (int)(key[k] & 0xFFFFu))) hitP |= 1u << k;
-      bool acc = false, starved = false;
-      int bestIdx = -1;
-      order_round(key, hitP, S.stag, lane, [&](unsigned hit) {
-        uint32_t k1 = kNoKey;
+        for (int k = 0; k < 4; ++k)
+          if (key[k] != kNoKey && bit_of(S.claim, (int)(key[k] & 0xFFFFu))) hitP |= 1u << k;
+        bool acc = false, starved = false;
+        int bestIdx = -1;
+        const int iters = order_round(key, hitP, S.stag, epoch, lane, [&](unsigned hit) {
+          uint32_t k1 = kNoKey;
 #pragma unroll
-        for (int k = 3; k >= 0; --k)
-          if (key[k] != kNoKey && !((hit >> k) & 1u)) k1 = key[k];
-        starved = !complete && k1 == kNoKey && key[0] != kNoKey;
-        acc = k1 != kNoKey && (k1 >> 16) <= 100u;                        // TH_HIGH
-        bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
-        return (acc && obs > 0) ? bestIdx : -1;
-      });
-      if (!__any_sync(0xffffffffu, starved)) {
-        const uint32_t accm = __ballot_sync(0xffffffffu, acc);
-        if (acc) {
+          for (int k = 3; k >= 0; --k)
+            if (key[k] != kNoKey && !((hit >> k) & 1u)) k1 = key[k];
+          starved = live && !complete && k1 == kNoKey;                   // the list ran out of free keys
+          acc = live && k1 != kNoKey && (k1 >> 16) <= 100u;              // TH_HIGH
+          bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
+          return (acc && obs) ? bestIdx : -1;
+        });
+        ORBX_STAT(dbg_iters += iters;)
+        (void)iters;
+        // lanes below the first starved one are final (a lane depends on earlier lanes only): they commit together
+        const uint32_t sm = __ballot_sync(0xffffffffu, starved);
+        const int jstar = sm ? __ffs((int)sm) - 1 : 32;
+        const bool commit = acc && lane < jstar;
+        const uint32_t cm = __ballot_sync(0xffffffffu, commit);
+        if (commit) {
           atomicMax(&S.sasg[bestIdx], myi);                              // a keypoint given away twice keeps the later map point
-          if (obs > 0) { atomicOr(&S.claim[bestIdx >> 5], 1u << (bestIdx & 31)); atomicOr(&S.sobs[bestIdx >> 5], 1u << (bestIdx & 31)); }
-          sev[nm + __popc(accm & ((1u << lane) - 1u))] = (mine << 16) | bestIdx;   // list position | keypoint: the rotation bin is worked out afterwards
+          if (obs) { atomicOr(&S.claim[bestIdx >> 5], 1u << (bestIdx & 31)); atomicOr(&S.sobs[bestIdx >> 5], 1u << (bestIdx & 31)); }
+          sev[nm + __popc(cm & ((1u << lane) - 1u))] = (mine << 16) | bestIdx;   // list position | keypoint: the rotation bin is worked out afterwards
         }
-        nm += __popc(accm);
+        nm += __popc(cm);
         __syncwarp();
-        continue;
-      }
-      ORBX_STAT(++dbg_serial;)
-      for (int j = 0; j < 32; ++j) {                                     // the rare round: one at a time, scanned again
-        if (!((have >> j) & 1u)) continue;
-        const ProjLP c = fetch(base + j);
+        if (!sm) break;
+        // the starved entry is scanned again against the live occupancy (exact), then the lanes after it go round again
+        ORBX_STAT(++dbg_serial;)
+        const ProjLP c = fetch(base + jstar);
         const uint4 l = projf_scan(a, c, Tr, mode, S, s_gb, lane);
         const uint32_t k1 = l.x & 0x7FFFFFFFu;
-        if (k1 == kNoKey || (k1 >> 16) > 100u) continue;
-        const int bi = (int)(k1 & 0xFFFFu), o = __shfl_sync(0xffffffffu, obs, j), i = __shfl_sync(0xffffffffu, myi, j);
-        if (lane == 0) {
-          S.sasg[bi] = i;
-          if (o > 0) { S.claim[bi >> 5] |= 1u << (bi & 31); S.sobs[bi >> 5] |= 1u << (bi & 31); }
-          sev[nm] = ((base + j) << 16) | bi;
+        if (k1 != kNoKey && (k1 >> 16) <= 100u) {
+          const int bi = (int)(k1 & 0xFFFFu), i = __shfl_sync(0xffffffffu, myi, jstar);
+          if (lane == 0) {
+            S.sasg[bi] = i;
+            if (l.y >> 31) { S.claim[bi >> 5] |= 1u << (bi & 31); S.sobs[bi >> 5] |= 1u << (bi & 31); }
+            sev[nm] = ((base + jstar) << 16) | bi;
+          }
+          ++nm;
         }
-        ++nm;
         __syncwarp();
+        todo &= ~((2u << jstar) - 1u);
       }
     }
     if (lane == 0) s_nm = nm;
-    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K9 phase B: %d serial rounds, nm %d of %d\n", dbg_serial, nm, nvalid);)
+    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K9 phase B: %d re-scans, %d fixpoint iterations, nm %d of %d\n", dbg_serial, dbg_iters, nm, nvalid);)
   }
   __syncthreads();
   ORBX_CLK(t4);

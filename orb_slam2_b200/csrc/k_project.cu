@@ -169,15 +169,33 @@ __device__ __forceinline__ int rot_bin30(float a1, float a2) {
 }
 
 // The projection of ONE map point of K17 and its search window (every lane computes the same): false when the point is skipped.
-struct OrdWin { float u, v, radius; int level, lvl_hi, cx0, cx1, cy0, cy1; uint32_t qd[8]; };
+struct OrdWin { float u, v, radius; int level, lvl_hi, cx0, cx1, cy0, cy1; };
+struct OrdMP { int valid; float xw[3], dmin, dmax, nn[3]; uint32_t qd[8]; };
 
-__device__ __forceinline__ bool ordered_window(const ProjOrderedArgs& a, int p, int iMP, OrdWin& w) {
+// every field of map point iMP, requested together: one memory round trip per map point, not one per test (iMP >= m: an invalid point)
+template <bool DESC = true>
+__device__ __forceinline__ OrdMP ordered_fetch(const ProjOrderedArgs& a, int p, int iMP, int m) {
   const size_t mo = (size_t)p * a.mcap;
+  OrdMP q;
+  const bool ok = iMP < m;
+  q.valid = ok ? a.valid[mo + iMP] : 0;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) q.xw[c] = ok ? a.xw[(mo + iMP) * 3 + c] : 0.f;
+  q.dmin = ok ? a.dmin[mo + iMP] : 0.f; q.dmax = ok ? a.dmax[mo + iMP] : 0.f;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) q.nn[c] = (ok && !a.reloc) ? a.normal[(mo + iMP) * 3 + c] : 0.f;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) q.qd[c] = (DESC && ok) ? __ldg(reinterpret_cast<const uint32_t*>(a.mp_desc + (mo + iMP) * 32) + c) : 0u;
+  return q;
+}
+
+__device__ __forceinline__ bool ordered_window(const ProjOrderedArgs& a, int p, const OrdMP& q, OrdWin& w) {
   const float* xf = a.xf + (size_t)p * 15;
   const float* kb = a.tgt_bounds + (size_t)p * 4;
   const float* gb = a.grid_bounds;
-  if (!a.valid[mo + iMP]) return false;
-  const float xw[3] = {a.xw[(mo + iMP) * 3], a.xw[(mo + iMP) * 3 + 1], a.xw[(mo + iMP) * 3 + 2]};
+  const float* xw = q.xw; const float* nn = q.nn;
+  const float dmin = q.dmin, dmax = q.dmax;
+  if (!q.valid) return false;
   float pc[3];
   gemm3(xf, xf + 9, xw, pc);
   float u, v;
@@ -194,10 +212,8 @@ __device__ __forceinline__ bool ordered_window(const ProjOrderedArgs& a, int p, 
   const float PO[3] = {__fsub_rn(xw[0], xf[12]), __fsub_rn(xw[1], xf[13]), __fsub_rn(xw[2], xf[14])};
   const double s2 = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)PO[0]), __dmul_rn((double)PO[1], (double)PO[1])), __dmul_rn((double)PO[2], (double)PO[2]));
   const float dist3D = (float)__dsqrt_rn(s2);
-  const float dmin = a.dmin[mo + iMP], dmax = a.dmax[mo + iMP];
   if (dist3D < __fmul_rn(0.8f, dmin) || dist3D > __fmul_rn(1.2f, dmax)) return false;
   if (!a.reloc) {
-    const float* nn = a.normal + (mo + iMP) * 3;
     const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)nn[0]), __dmul_rn((double)PO[1], (double)nn[1])), __dmul_rn((double)PO[2], (double)nn[2]));
     if (dot < __dmul_rn(0.5, (double)dist3D)) return false;
   }
@@ -210,10 +226,7 @@ __device__ __forceinline__ bool ordered_window(const ProjOrderedArgs& a, int p, 
   w.cx1 = min(kPGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, kb[0]), radius), gb[4])));
   w.cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
   w.cy1 = min(kPGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, kb[2]), radius), gb[5])));
-  if (w.cx0 >= kPGridCols || w.cx1 < 0 || w.cy0 >= kPGridRows || w.cy1 < 0) return false;
-#pragma unroll
-  for (int q = 0; q < 8; ++q) w.qd[q] = __ldg(reinterpret_cast<const uint32_t*>(a.mp_desc + (mo + iMP) * 32) + q);
-  return true;
+  return !(w.cx0 >= kPGridCols || w.cx1 < 0 || w.cy0 >= kPGridRows || w.cy1 < 0);
 }
 
 // The candidate scan of ONE map point of K17 (warp-wide): the least (distance << 8 | cell column, CSR position)
@@ -221,7 +234,8 @@ __device__ __forceinline__ bool ordered_window(const ProjOrderedArgs& a, int p, 
 __device__ __forceinline__ void ordered_scan(const ProjOrderedArgs& a, int p, int iMP, const uint32_t* occ, int lane, unsigned& whi, unsigned& wlo) {
   whi = wlo = 0xffffffffu;
   OrdWin w;
-  if (!ordered_window(a, p, iMP, w)) return;
+  const OrdMP mp = ordered_fetch(a, p, iMP, iMP + 1);
+  if (!ordered_window(a, p, mp, w)) return;
   const size_t ko = (size_t)p * a.cap;
   const orbx_keypoint* kps = a.kps + ko;
   const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
@@ -235,7 +249,7 @@ __device__ __forceinline__ void ordered_scan(const ProjOrderedArgs& a, int p, in
       const orbx_keypoint kp = kps[idx];
       if (!(fabsf(__fsub_rn(kp.x, w.u)) < w.radius && fabsf(__fsub_rn(kp.y, w.v)) < w.radius)) continue;
       if (kp.octave < w.level - 1 || kp.octave > w.lvl_hi) continue;
-      const unsigned h = ((unsigned)ham8p(w.qd, reinterpret_cast<const uint32_t*>(a.desc + (ko + idx) * 32)) << 8) | (unsigned)ix;
+      const unsigned h = ((unsigned)ham8p(mp.qd, reinterpret_cast<const uint32_t*>(a.desc + (ko + idx) * 32)) << 8) | (unsigned)ix;
       if (h < hi || (h == hi && (unsigned)e < lo)) { hi = h; lo = (unsigned)e; }
     }
   }
@@ -318,34 +332,41 @@ __host__ __device__ inline size_t ord_stage_bytes(int cap) {
   return (b + 15) & ~(size_t)15;
 }
 
-// Map point iMP's candidate list against S.occ as it is now (warp-wide, every lane returns the same):
+// The candidate list of a map point with search window `win` ({u, v, radius, packed level / cell window}, ordered_pack) and
+// descriptor qd against S.occ as it is now (warp-wide, every lane returns the same):
 // {l0 | complete << 31, l1, l2, l3}, l = distance << 16 | keypoint in ascending (distance, cell column, CSR position) = the
 // reference's first-least over its enumeration; kNoKey = none.
-__device__ __forceinline__ uint4 ordered_scan_staged(const ProjOrderedArgs& a, int p, int iMP, const OrdStage& S, int lane) {
+__device__ __forceinline__ uint32_t ordered_pack(const OrdWin& w) {
+  return 0x80000000u | ((uint32_t)w.level << 24) | ((uint32_t)w.cx0 << 18) | ((uint32_t)w.cx1 << 12) | ((uint32_t)w.cy0 << 6) | (uint32_t)w.cy1;
+}
+
+__device__ __forceinline__ uint4 ordered_scan_staged(const ProjOrderedArgs& a, const uint4 win, const uint32_t (&qd)[8], const OrdStage& S, int lane) {
   const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+  if (!(win.w >> 31)) return none;
   OrdWin w;
-  if (!ordered_window(a, p, iMP, w)) return none;
+  w.u = __uint_as_float(win.x); w.v = __uint_as_float(win.y); w.radius = __uint_as_float(win.z);
+  w.level = (int)((win.w >> 24) & 15u); w.lvl_hi = a.reloc ? w.level + 1 : w.level;
+  w.cx0 = (int)((win.w >> 18) & 63u); w.cx1 = (int)((win.w >> 12) & 63u); w.cy0 = (int)((win.w >> 6) & 63u); w.cy1 = (int)(win.w & 63u);
   unsigned long long k1 = ~0ull, k2 = ~0ull;                  // (distance << 8 | cell column) << 32 | CSR position
   int cnt = 0;
-  for (int ix = w.cx0; ix <= w.cx1; ++ix) {
-    const int e_hi = S.cs[ix * kPGridRows + w.cy1 + 1];
-    for (int e = S.cs[ix * kPGridRows + w.cy0] + lane; e < e_hi; e += 32) {
+  for_each_in_columns(w.cx0, w.cx1, lane,
+    [&](int ix, int& e_lo, int& e_hi) { e_lo = S.cs[ix * kPGridRows + w.cy0]; e_hi = S.cs[ix * kPGridRows + w.cy1 + 1]; },
+    [&](int e, int ix) {
       const uint32_t meta = S.smeta[e];
       const int idx = (int)(meta & 0xFFFFFFu), oct = (int)(meta >> 24);
-      if ((S.occ[idx >> 5] >> (idx & 31)) & 1u) continue;
+      if ((S.occ[idx >> 5] >> (idx & 31)) & 1u) return;
       const float2 pt = S.sxy[e];
-      if (!(fabsf(__fsub_rn(pt.x, w.u)) < w.radius && fabsf(__fsub_rn(pt.y, w.v)) < w.radius)) continue;
-      if (oct < w.level - 1 || oct > w.lvl_hi) continue;
+      if (!(fabsf(__fsub_rn(pt.x, w.u)) < w.radius && fabsf(__fsub_rn(pt.y, w.v)) < w.radius)) return;
+      if (oct < w.level - 1 || oct > w.lvl_hi) return;
       const uint32_t* g = S.sdesc + (size_t)idx * 8;
       const uint4 b0 = *reinterpret_cast<const uint4*>(g), b1 = *reinterpret_cast<const uint4*>(g + 4);
-      const int d = __popc(w.qd[0] ^ b0.x) + __popc(w.qd[1] ^ b0.y) + __popc(w.qd[2] ^ b0.z) + __popc(w.qd[3] ^ b0.w) + __popc(w.qd[4] ^ b1.x) +
-                    __popc(w.qd[5] ^ b1.y) + __popc(w.qd[6] ^ b1.z) + __popc(w.qd[7] ^ b1.w);
+      const int d = __popc(qd[0] ^ b0.x) + __popc(qd[1] ^ b0.y) + __popc(qd[2] ^ b0.z) + __popc(qd[3] ^ b0.w) + __popc(qd[4] ^ b1.x) +
+                    __popc(qd[5] ^ b1.y) + __popc(qd[6] ^ b1.z) + __popc(qd[7] ^ b1.w);
       const unsigned long long key = ((unsigned long long)(((unsigned)d << 8) | (unsigned)ix) << 32) | (unsigned)e;
       ++cnt;
       if (key < k1) { k2 = k1; k1 = key; }
       else if (key < k2) k2 = key;
-    }
-  }
+    });
   unsigned hi[4], lo[4];
   bool complete;
   warp_top4(k1, k2, cnt, hi, lo, complete);
@@ -359,6 +380,7 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ int s_hist[30];
   __shared__ int s_nm;
+  __shared__ int s_bcnt[kOrdParThreads / 32];
   const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
   const int n = min(a.n[p], a.cap), m = min(a.m[p], a.mcap);
   const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
@@ -366,6 +388,7 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
   int* assigned = a.assigned + ko;
   uint4* spec = a.spec + mo;
   OrdStage S;
+  ORBX_CLK(t0);
   S.cs = reinterpret_cast<int*>(smem);
   S.sdesc = reinterpret_cast<uint32_t*>(smem + (size_t)(kPCells + 1 + 3) / 4 * 16);      // 16-byte aligned for any cap
   S.sxy = reinterpret_cast<float2*>(S.sdesc + (size_t)a.cap * 8);
@@ -374,6 +397,7 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
   S.sasg = reinterpret_cast<int*>(S.sang + a.cap);
   S.stag = S.sasg + a.cap;
   S.occ = reinterpret_cast<uint32_t*>(S.stag + a.cap);
+  uint16_t* slist = reinterpret_cast<uint16_t*>(smem + ord_stage_bytes(a.cap));   // [mcap] the map points that have a search window, in list order
   {
     const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
     const int* items = a.cell_items + ko;
@@ -388,7 +412,7 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
     const uint4* src = reinterpret_cast<const uint4*>(a.desc + ko * 32);
     uint4* dst = reinterpret_cast<uint4*>(S.sdesc);
     for (int i = tid; i < n * 2; i += nth) dst[i] = __ldg(src + i);
-    for (int i = tid; i < a.cap; i += nth) { S.sasg[i] = -1; S.stag[i] = 255; S.sang[i] = i < n ? kps[i].angle : 0.f; }
+    for (int i = tid; i < a.cap; i += nth) { S.sasg[i] = -1; S.stag[i] = 0; S.sang[i] = i < n ? kps[i].angle : 0.f; }
     for (int base = warp * 32; base < a.cap; base += nth) {
       const int i = base + lane;
       const uint32_t b = __ballot_sync(0xffffffffu, i < n && a.occupied[ko + i]);
@@ -396,71 +420,128 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
     }
     if (tid < 30) s_hist[tid] = 0;
   }
-  __syncthreads();
-  // phase A (occ is only read)
-  for (int iMP = warp; iMP < m; iMP += nwarps) {
-    const uint4 l = ordered_scan_staged(a, p, iMP, S, lane);
-    if (lane == 0) spec[iMP] = l;
+  // pre-pass, one THREAD per map point: the projection and the search window (double-precision square root, logarithm and
+  // divisions - a few thousand cycles of latency that a warp per map point would pay 32 lanes wide, once per map point in
+  // turn), left in global scratch as 16 bytes; the map points that have a window are listed in order in shared memory
+  uint4* wins = a.spec + (size_t)a.n_problems * a.mcap + mo;
+  int nlist = 0;
+  for (int base = 0; base < m; base += nth) {
+    const int i = base + tid;
+    OrdWin w;
+    const bool ok = i < m && ordered_window(a, p, ordered_fetch<false>(a, p, i, m), w);
+    if (ok) wins[i] = make_uint4(__float_as_uint(w.u), __float_as_uint(w.v), __float_as_uint(w.radius), ordered_pack(w));
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) s_bcnt[warp] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int q = 0; q < nwarps; ++q) { const int c = s_bcnt[q]; before += q < warp ? c : 0; total += c; }
+    if (ok) slist[nlist + before + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)i;
+    nlist += total;
+    __syncthreads();
+  }
+  ORBX_CLK(t1);
+  // phase A (occ is only read): a warp per listed map point, the next one's window and descriptor in flight
+  const uint32_t* mpd = reinterpret_cast<const uint32_t*>(a.mp_desc + mo * 32);
+  auto fetch = [&](int c, uint4& win, uint32_t& dw) {
+    const bool ok = c < nlist;
+    const int i = ok ? slist[c] : 0;
+    win = ok ? wins[i] : make_uint4(0u, 0u, 0u, 0u);
+    dw = (ok && lane < 8) ? __ldg(mpd + (size_t)i * 8 + lane) : 0u;
+  };
+  {
+    uint4 nwin; uint32_t ndw;
+    fetch(warp, nwin, ndw);
+    for (int c = warp; c < nlist; c += nwarps) {
+      const uint4 win = nwin; const uint32_t dw = ndw;
+      fetch(c + nwarps, nwin, ndw);
+      uint32_t qd[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) qd[q] = __shfl_sync(0xffffffffu, dw, q);
+      const uint4 l = ordered_scan_staged(a, win, qd, S, lane);
+      if (lane == 0) spec[c] = l;                                        // by list position
+    }
   }
   __syncthreads();
+  ORBX_CLK(t2);
   // phase B (see ordered.cuh): one key per map point - the first of its list no earlier map point has taken; every match claims
   if (warp == 0) {
     int nm = 0;
-    for (int base = 0; base < m; base += 32) {
-      const int iMP = base + lane;
-      const uint4 my4 = iMP < m ? spec[iMP] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
-      const float src = (iMP < m && a.reloc && a.checkOri) ? a.src_angle[mo + iMP] : 0.f;
+    int epoch = 0;
+    ORBX_STAT(int dbg_serial = 0; int dbg_iters = 0;)
+    const uint4 nokeys = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+    const bool ori = a.reloc && a.checkOri;
+    uint4 nxt = lane < nlist ? spec[lane] : nokeys;
+    float nsrc = (lane < nlist && ori) ? a.src_angle[mo + slist[lane]] : 0.f;
+    for (int base = 0; base < nlist; base += 32) {
+      const int c = base + lane;
+      const int iMP = c < nlist ? slist[c] : 0;
+      const uint4 my4 = nxt;
+      const float src = nsrc;
+      nxt = c + 32 < nlist ? spec[c + 32] : nokeys;                       // the next round's inputs are on their way while this one is resolved
+      nsrc = (c + 32 < nlist && ori) ? a.src_angle[mo + slist[c + 32]] : 0.f;
       const bool complete = my4.x >> 31;
       const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
-      const uint32_t have = __ballot_sync(0xffffffffu, key[0] != kNoKey);
-      if (!have) continue;
-      unsigned hitP = 0u;
+      uint32_t todo = __ballot_sync(0xffffffffu, key[0] != kNoKey);      // lanes whose map point is still to be decided
+      while (todo) {
+        const bool live = (todo >> lane) & 1u;
+        unsigned hitP = 0u;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int idx = (int)(key[k] & 0xFFFFu);
-        if (key[k] != kNoKey && ((S.occ[idx >> 5] >> (idx & 31)) & 1u)) hitP |= 1u << k;
-      }
-      bool acc = false, starved = false;
-      int bestIdx = -1;
-      order_round(key, hitP, S.stag, lane, [&](unsigned hit) {
-        uint32_t k1 = kNoKey;
+        for (int k = 0; k < 4; ++k) {
+          const int idx = (int)(key[k] & 0xFFFFu);
+          if (key[k] != kNoKey && ((S.occ[idx >> 5] >> (idx & 31)) & 1u)) hitP |= 1u << k;
+        }
+        bool acc = false, starved = false;
+        int bestIdx = -1;
+        ORBX_STAT(dbg_iters +=) order_round(key, hitP, S.stag, epoch, lane, [&](unsigned hit) {
+          uint32_t k1 = kNoKey;
 #pragma unroll
-        for (int k = 3; k >= 0; --k)
-          if (key[k] != kNoKey && !((hit >> k) & 1u)) k1 = key[k];
-        starved = !complete && k1 == kNoKey && key[0] != kNoKey;
-        acc = k1 != kNoKey && (int)(k1 >> 16) <= a.th_dist;
-        bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
-        return bestIdx;
-      });
-      if (!__any_sync(0xffffffffu, starved)) {
-        if (acc) {
+          for (int k = 3; k >= 0; --k)
+            if (key[k] != kNoKey && !((hit >> k) & 1u)) k1 = key[k];
+          starved = live && !complete && k1 == kNoKey;                   // the list ran out of free keys
+          acc = live && k1 != kNoKey && (int)(k1 >> 16) <= a.th_dist;
+          bestIdx = acc ? (int)(k1 & 0xFFFFu) : -1;
+          return bestIdx;
+        });
+        // lanes below the first starved one are final (a lane depends on earlier lanes only): they commit together
+        const uint32_t sm = __ballot_sync(0xffffffffu, starved);
+        const int jstar = sm ? __ffs((int)sm) - 1 : 32;
+        const bool commit = acc && lane < jstar;
+        if (commit) {
           S.sasg[bestIdx] = iMP;                                         // claims are exclusive here: one writer per keypoint
           atomicOr(&S.occ[bestIdx >> 5], 1u << (bestIdx & 31));
-          if (a.reloc && a.checkOri) atomicAdd(&s_hist[rot_bin30(src, S.sang[bestIdx])], 1);
+          if (ori) atomicAdd(&s_hist[rot_bin30(src, S.sang[bestIdx])], 1);
         }
-        nm += __popc(__ballot_sync(0xffffffffu, acc));
+        nm += __popc(__ballot_sync(0xffffffffu, commit));
         __syncwarp();
-        continue;
-      }
-      for (int j = 0; j < 32; ++j) {                                     // the rare round: one at a time, scanned again
-        if (!((have >> j) & 1u)) continue;
-        const uint4 l = ordered_scan_staged(a, p, base + j, S, lane);
+        if (!sm) break;
+        // the starved map point is scanned again against the live occupancy (exact), then the lanes after it go round again
+        ORBX_STAT(++dbg_serial;)
+        const int ij = __shfl_sync(0xffffffffu, iMP, jstar);
+        const uint32_t dwj = lane < 8 ? __ldg(mpd + (size_t)ij * 8 + lane) : 0u;
+        uint32_t qd[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) qd[q] = __shfl_sync(0xffffffffu, dwj, q);
+        const uint4 l = ordered_scan_staged(a, wins[ij], qd, S, lane);
         const uint32_t k1 = l.x & 0x7FFFFFFFu;
-        if (k1 == kNoKey || (int)(k1 >> 16) > a.th_dist) continue;
-        const int bi = (int)(k1 & 0xFFFFu);
-        const float sj = __shfl_sync(0xffffffffu, src, j);
-        if (lane == 0) {
-          S.occ[bi >> 5] |= 1u << (bi & 31);
-          S.sasg[bi] = base + j;
-          if (a.reloc && a.checkOri) s_hist[rot_bin30(sj, S.sang[bi])] += 1;
+        if (k1 != kNoKey && (int)(k1 >> 16) <= a.th_dist) {
+          const int bi = (int)(k1 & 0xFFFFu);
+          const float sj = __shfl_sync(0xffffffffu, src, jstar);
+          if (lane == 0) {
+            S.occ[bi >> 5] |= 1u << (bi & 31);
+            S.sasg[bi] = ij;
+            if (ori) s_hist[rot_bin30(sj, S.sang[bi])] += 1;
+          }
+          ++nm;
         }
-        ++nm;
         __syncwarp();
+        todo &= ~((2u << jstar) - 1u);
       }
     }
     if (lane == 0) s_nm = nm;
+    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K17 phase B: %d re-scans, %d fixpoint iterations, nm %d of %d listed of %d\n", dbg_serial, dbg_iters, nm, nlist, m);)
   }
   __syncthreads();
+  ORBX_CLK(t3);
   if (a.reloc && a.checkOri) {                                  // rotation consistency, src/ORBmatcher.cc:1577-1596, whole CTA
     int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;      // ORBmatcher::ComputeThreeMaxima :1601-1642
     for (int i = 0; i < 30; ++i) {
@@ -484,11 +565,13 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
   }
   for (int i = tid; i < a.cap; i += nth) assigned[i] = S.sasg[i];
   if (tid == 0) a.nm[p] = s_nm;
+  ORBX_CLK(t4);
+  ORBX_CLK_PRINT("k_project_match_ordered_par stage / A / B / rotation + flush", t0, t1, t2, t3, t4);
 }
 
 int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
-  const size_t smem = (size_t)((a.cap + 31) / 32) * 4, par = ord_stage_bytes(a.cap);
-  if (a.n_problems <= 148 && par <= 200 * 1024 && a.cap <= 65536 && !getenv("ORBX_PROJ_SERIAL")) {
+  const size_t smem = (size_t)((a.cap + 31) / 32) * 4, par = ord_stage_bytes(a.cap) + (size_t)a.mcap * 2;
+  if (a.n_problems <= 148 && par <= 200 * 1024 && a.cap <= 65536 && a.mcap <= 65536 && !getenv("ORBX_PROJ_SERIAL")) {
     cudaFuncSetAttribute(k_project_match_ordered_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
     k_project_match_ordered_par<<<a.n_problems, kOrdParThreads, par, st>>>(a);
   } else {

@@ -1214,7 +1214,7 @@ orbx_status orbx_search_projection_ordered_batch(const orbx_keypoint* kps_un, co
   CU(sg.in(mp_src_angle, mc, on_device, &a.src_angle)); CU(sg.in(m, np, on_device, &a.m));
   if (on_device) { a.assigned = assigned; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.assigned, kc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
-  CU(sg.alloc((void**)&a.spec, mc * sizeof(uint4)));
+  CU(sg.alloc((void**)&a.spec, 2 * mc * sizeof(uint4)));
   CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st));
   a.n_problems = n_problems; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.reloc = relocalisation ? 1 : 0; a.th_dist = max_dist;
   a.checkOri = check_orientation ? 1 : 0; a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.log_scale = log_scale_factor; a.th = th;

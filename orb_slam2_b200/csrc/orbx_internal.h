@@ -204,7 +204,7 @@ struct ProjOrderedArgs {
   float fx, fy, cx, cy, log_scale, th;
   float scale[kMaxLevels];
   int* assigned; int* nm;
-  uint4* spec;                // scratch [P][mcap]: the candidate list (four smallest keys, distance << 16 | keypoint) per map point (latency form)
+  uint4* spec;                // scratch [2][P][mcap]: candidate lists (four smallest keys, distance << 16 | keypoint) by list position, then the search windows by map point (latency form)
 };
 int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st);
 

@@ -1,6 +1,21 @@
 // Shared by the latency forms of the order-dependent matchers (K8, K9 in k_match.cu; K17 in k_project.cu).
 #pragma once
 #include <stdint.h>
+#ifdef ORBX_PHASE_CLOCKS
+#include <cstdio>
+#endif
+
+#ifdef ORBX_PHASE_CLOCKS
+// experiments: SM clock at phase boundaries, printed by thread 0 of CTA 0 (build with ORBX_NVCC_EXTRA=-DORBX_PHASE_CLOCKS)
+#define ORBX_CLK(v) const long long v = clock64()
+#define ORBX_CLK_PRINT(name, ...) do { if (threadIdx.x == 0 && blockIdx.x == 0) { const long long c_[] = {__VA_ARGS__}; printf("%s:", name); \
+  for (unsigned i_ = 1; i_ < sizeof(c_) / sizeof(c_[0]); ++i_) printf(" %lld", c_[i_] - c_[i_ - 1]); printf(" cycles\n"); } } while (0)
+#define ORBX_STAT(...) __VA_ARGS__
+#else
+#define ORBX_CLK(v)
+#define ORBX_CLK_PRINT(...)
+#define ORBX_STAT(...)
+#endif
 
 namespace orbx {
 
@@ -48,24 +63,56 @@ __device__ __forceinline__ int warp_top4(unsigned long long k1, unsigned long lo
 
 // One fixpoint round of phase B (see above).  Every lane brings the keypoints of its list (key[k] & 0xFFFF, kNoKey = none),
 // `hitP` = which of them were claimed by earlier rounds, and a functor pick(hit) -> keypoint it would claim (-1: none) that
-// also leaves the lane's decision in the caller's variables.  Returns after the iteration in which no lane changed its claim.
+// also leaves the lane's decision in the caller's variables.  Returns after the iteration in which no lane changed its claim
+// (with the number of iterations).  stag[i] = (iteration stamp << 5) | (31 - lowest lane that wants keypoint i), written
+// with atomicMax: a newer stamp beats every older entry, so nothing has to be reset; `epoch` counts the iterations of the
+// whole kernel (start it at 0 over a zeroed stag).
 template <class Pick>
-__device__ __forceinline__ void order_round(const uint32_t (&key)[4], unsigned hitP, int* stag, int lane, Pick pick) {
+__device__ __forceinline__ int order_round(const uint32_t (&key)[4], unsigned hitP, int* stag, int& epoch, int lane, Pick pick) {
   int claim = pick(hitP);
-  for (int it = 0; it < 33; ++it) {
-    if (claim >= 0) atomicMin(&stag[claim], lane);
+  int it = 0;
+  for (; it < 33; ++it) {
+    ++epoch;
+    if (claim >= 0) atomicMax(&stag[claim], (epoch << 5) | (31 - lane));
     __syncwarp();
     unsigned hitR = 0u;
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-      if (key[k] != kNoKey && stag[key[k] & 0xFFFFu] < lane) hitR |= 1u << k;
-    __syncwarp();
-    if (claim >= 0) stag[claim] = 255;
-    __syncwarp();
+    for (int k = 0; k < 4; ++k) {
+      const int t = key[k] != kNoKey ? stag[key[k] & 0xFFFFu] : 0;
+      if ((t >> 5) == epoch && 31 - (t & 31) < lane) hitR |= 1u << k;
+    }
     const int next = pick(hitP | hitR);
     const bool moved = next != claim;
     claim = next;
-    if (!__any_sync(0xffffffffu, moved)) break;
+    if (!__any_sync(0xffffffffu, moved)) break;                          // (also orders this iteration's reads before the next one's atomics)
+  }
+  return it + 1;
+}
+
+// Calls body(e, ix) once for every entry e of the runs [lo(ix), hi(ix)) of columns cx0 .. cx1, the entries dealt round-robin
+// over the lanes of the warp (a lane per column entry would leave most lanes idle and give the low lanes several
+// candidates each: one loop trip per column instead of one per 32 candidates).  bounds(ix, lo, hi) gives a column's run.
+// body must not contain warp-synchronous operations.
+template <class Bounds, class Body>
+__device__ __forceinline__ void for_each_in_columns(int cx0, int cx1, int lane, Bounds bounds, Body body) {
+  for (int cb = cx0; cb <= cx1; cb += 32) {
+    const int ix = cb + lane, nc = min(32, cx1 - cb + 1);
+    int e_lo = 0, len = 0;
+    if (ix <= cx1) { int e_hi; bounds(ix, e_lo, e_hi); len = max(e_hi - e_lo, 0); }
+    int incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31), excl = incl - len;
+    for (int fb = 0; fb < total; fb += 32) {
+      const int f = fb + lane;
+      int col = 0;                                                       // column of entry f = the number of columns that end at or before it
+      for (int c = 0; c < nc - 1; ++c) col += (__shfl_sync(0xffffffffu, incl, c) <= f) ? 1 : 0;
+      const int e0 = __shfl_sync(0xffffffffu, e_lo, col), x0 = __shfl_sync(0xffffffffu, excl, col);
+      if (f < total) body(e0 + (f - x0), cb + col);
+    }
   }
 }
 
