@@ -1231,7 +1231,7 @@ int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st) {
 //      scan the B run of the same node; the A descriptors are fetched four queries ahead.
 constexpr int kBowThreads = 128;
 
-__global__ void __launch_bounds__(kBowThreads) k_search_by_bow(BowArgs a, int capPad, int par) {
+__global__ void __launch_bounds__(kBowThreads) k_search_by_bow(BowArgs a, int capPad) {
   extern __shared__ __align__(16) uint8_t smem[];
   unsigned long long* keyA = reinterpret_cast<unsigned long long*>(smem);          // [capPad] node<<32 | index, sorted
   unsigned long long* keyB = keyA + capPad;                                         // [capPad]
@@ -1274,119 +1274,6 @@ __global__ void __launch_bounds__(kBowThreads) k_search_by_bow(BowArgs a, int ca
       }
       __syncthreads();
     }
-  if (par) {
-    // Two phases instead of one warp walking every query (hazard H6 needs the ORDER of the decisions, not of the distance
-    // work).  A: the warps take contiguous chunks of the sorted A list and find, for every valid query, its two nearest B
-    // features of the same node among those free ON ENTRY (keys distance << 16 | j).  B: warp 0 decides the queries in order;
-    // a query's phase-A keys stand unless one of its two features was matched meanwhile - only then its run is scanned
-    // again (a feature that is neither the nearest nor the second nearest can be taken away without changing either).
-    uint4* spec = a.spec + po;
-    const int warp = tid >> 5, nwarp = kBowThreads / 32, chunk = (nA + nwarp - 1) / nwarp;
-    auto scan = [&](const uint32_t (&q)[8], int rb0, int rb1, unsigned& o1, unsigned& o2) {
-      unsigned k1 = 0xffffffffu, k2 = 0xffffffffu;
-      for (int e = rb0 + lane; e < rb1; e += 32) {
-        const int j = (int)(keyB[e] & 0xffffffffu);
-        if ((used[j >> 5] >> (j & 31)) & 1u) continue;
-        const unsigned kk = ((unsigned)ham8(q, Bs + (size_t)j * 8) << 16) | (unsigned)j;
-        // first-wins on equal distances in ascending e = ascending j inside a node run: strict "<" on the DISTANCE only
-        if ((kk >> 16) < (k1 >> 16)) { k2 = k1; k1 = kk; }
-        else if ((kk >> 16) < (k2 >> 16)) k2 = kk;
-      }
-      // warp merge: least key, then the least of the rest
-      const unsigned w1 = __reduce_min_sync(0xffffffffu, k1);
-      const unsigned rest = k1 == w1 ? k2 : k1;
-      o1 = w1; o2 = __reduce_min_sync(0xffffffffu, rest);
-    };
-    auto run_of = [&](uint32_t node, int from, int& rb0, int& rb1) {         // B run of `node`, searched forwards from `from`
-      rb0 = from;
-      while (true) {
-        const int e = rb0 + lane;
-        const int c = __popc(__ballot_sync(0xffffffffu, e < nB && (uint32_t)(keyB[e] >> 32) < node));
-        rb0 += c;
-        if (c < 32) break;
-      }
-      rb1 = rb0;
-      while (true) {
-        const int e = rb1 + lane;
-        const int c = __popc(__ballot_sync(0xffffffffu, e < nB && (uint32_t)(keyB[e] >> 32) == node));
-        rb1 += c;
-        if (c < 32) break;
-      }
-    };
-    {
-      int rb0 = 0, rb1 = 0;
-      uint32_t cur = 0xffffffffu; bool have = false;
-      for (int t = warp * chunk; t < min(nA, (warp + 1) * chunk); ++t) {
-        const unsigned long long ka = keyA[t];
-        const uint32_t node = (uint32_t)(ka >> 32);
-        const int i = (int)(ka & 0xffffffffu);
-        if (!have || node != cur) { run_of(node, have ? rb1 : 0, rb0, rb1); have = true; cur = node; }
-        unsigned o1 = 0xffffffffu, o2 = 0xffffffffu;
-        if (a.validA[po + i] && rb0 != rb1) {
-          uint32_t q[8];
-          const uint32_t qw = lane < 8 ? __ldg(dA + (size_t)i * 8 + lane) : 0u;
-#pragma unroll
-          for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, qw, w);
-          scan(q, rb0, rb1, o1, o2);
-        }
-        if (lane == 0) spec[t] = make_uint4(o1, o2, (unsigned)rb0, (unsigned)rb1);    // the run bounds ride along for a re-scan
-      }
-    }
-    __syncthreads();
-    if (tid >= 32) return;
-    int nm = 0;
-    for (int base = 0; base < nA; base += 32) {
-      const int mine = base + lane;
-      const uint4 my2 = mine < nA ? spec[mine] : make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
-      uint32_t vm = __ballot_sync(0xffffffffu, my2.x != 0xffffffffu);
-      while (vm) {
-        const int jj = __ffs((int)vm) - 1;
-        vm &= vm - 1u;
-        const int t = base + jj;
-        unsigned k1 = __shfl_sync(0xffffffffu, my2.x, jj), k2 = __shfl_sync(0xffffffffu, my2.y, jj);
-        const int i = (int)(keyA[t] & 0xffffffffu);
-        const int j1 = (int)(k1 & 0xffffu), j2 = (int)(k2 & 0xffffu);
-        if (((used[j1 >> 5] >> (j1 & 31)) & 1u) || (k2 != 0xffffffffu && ((used[j2 >> 5] >> (j2 & 31)) & 1u))) {   // warp-uniform, rare
-          const int rb0 = (int)__shfl_sync(0xffffffffu, my2.z, jj), rb1 = (int)__shfl_sync(0xffffffffu, my2.w, jj);
-          uint32_t q[8];
-          const uint32_t qw = lane < 8 ? __ldg(dA + (size_t)i * 8 + lane) : 0u;
-#pragma unroll
-          for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, qw, w);
-          scan(q, rb0, rb1, k1, k2);
-          if (k1 == 0xffffffffu) continue;
-        }
-        const int best = (int)(k1 >> 16), bi = (int)(k1 & 0xffffu);
-        const int sec = k2 == 0xffffffffu ? 256 : (int)(k2 >> 16);
-        const bool pass = (a.strict ? best < a.th : best <= a.th) && (float)best < __fmul_rn(a.ratio, (float)sec);
-        if (pass) {
-          if (lane == 0) { m12[i] = bi; used[bi >> 5] |= 1u << (bi & 31); }
-          ++nm;
-          __syncwarp();
-        }
-      }
-    }
-    __syncwarp();
-    if (a.checkOri) {
-      for (int i = lane; i < nA; i += 32) {
-        const int m = m12[i];
-        if (m >= 0) atomicAdd(&s_hist[rot_bin(angA[i], angB[m])], 1);
-      }
-      __syncwarp();
-      int k_a, k_b, k_c;
-      three_maxima(s_hist, k_a, k_b, k_c);
-      int drop = 0;
-      for (int i = lane; i < nA; i += 32) {
-        const int m = m12[i];
-        if (m >= 0) {
-          const int b = rot_bin(angA[i], angB[m]);
-          if (b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
-        }
-      }
-      nm -= __reduce_add_sync(0xffffffffu, drop);
-    }
-    if (lane == 0) a.nm[p] = nm;
-    return;
-  }
   if (tid >= 32) return;
 
   int nm = 0, b0 = 0, b1 = 0;
@@ -1469,14 +1356,305 @@ __global__ void __launch_bounds__(kBowThreads) k_search_by_bow(BowArgs a, int ca
   if (lane == 0) a.nm[p] = nm;
 }
 
+// Bitonic sort of one or two shared-memory arrays of `n` (a power of two, >= 32) 64-bit keys by the whole CTA (blockDim.x a
+// multiple of 32, n a multiple of 32).  The compare-exchange steps whose partner distance is below 32 stay inside a warp: the
+// thread that owns element i keeps it in a register and trades it by shuffle - 45 of the 66 steps of a 2048-key sort, no
+// barrier, no shared-memory traffic; only the 21 wide steps go through shared memory with a barrier each.
+template <int NARR>
+__device__ __forceinline__ void cta_bitonic_sort(unsigned long long* k0, unsigned long long* k1, int n) {
+  const int tid = threadIdx.x, nth = blockDim.x;
+  auto narrow = [&](int k, int jtop) {                       // steps jj = jtop, jtop / 2, ..., 1 (jtop < 32) of merge size k, in registers
+    for (int base = 0; base < n; base += nth) {
+      const int i = base + tid;
+      if (base + (tid & ~31) >= n) break;                    // warp-uniform
+#pragma unroll
+      for (int arr = 0; arr < NARR; ++arr) {
+        unsigned long long* key = arr ? k1 : k0;
+        unsigned long long x = key[i];
+        for (int jj = jtop; jj > 0; jj >>= 1) {
+          const unsigned long long y = __shfl_xor_sync(0xffffffffu, x, jj);
+          const bool keep_min = ((i & jj) == 0) == ((i & k) == 0);
+          x = keep_min ? (x < y ? x : y) : (x < y ? y : x);
+        }
+        key[i] = x;
+      }
+    }
+  };
+  for (int k = 2; k <= 32 && k <= n; k <<= 1) narrow(k, k >> 1);     // own elements only: no barrier needed between these
+  __syncthreads();
+  for (int k = 64; k <= n; k <<= 1) {
+    for (int jj = k >> 1; jj >= 32; jj >>= 1) {
+      for (int i = tid; i < n; i += nth) {
+        const int l = i ^ jj;
+        if (l > i) {
+          const bool up = (i & k) == 0;
+#pragma unroll
+          for (int arr = 0; arr < NARR; ++arr) {
+            unsigned long long* key = arr ? k1 : k0;
+            const unsigned long long x = key[i], y = key[l];
+            if ((x > y) == up) { key[i] = y; key[l] = x; }
+          }
+        }
+      }
+      __syncthreads();
+    }
+    narrow(k, 16);
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// K12, latency form (a few pairs per call: TrackReferenceKeyFrame, Relocalization and DetectLoop ask about one keyframe at
+// a time).  One CTA of 1024 threads per pair, everything the loops touch in shared memory:
+//   1. both sides sorted by (node, index) by the whole CTA; B descriptors, `used` (= !validB on entry) and validA as bits;
+//   2. one THREAD per sorted A entry: the B run of its node by binary search, then the four nearest free B features of that
+//      run (keys distance << 16 | j; ascending j on equal distances = the reference's first-wins walk) - most runs are a
+//      handful of features, a warp per query would idle; the entries that have a candidate are listed in order;
+//   3. the ordered phase (hazard H6, ordered.cuh).  Queries of different nodes never compete for a B feature, so the list
+//      is cut at node boundaries into one piece per warp and the 32 warps resolve their pieces at the same time, each in
+//      rounds of 32 queries;
+//   4. rotation histogram and the write-back by the whole CTA.
+constexpr int kBowLatThreads = 1024;
+
+__host__ __device__ inline size_t bow_lat_bytes(int cap, int capPad) {
+  return (size_t)capPad * 16 + (size_t)cap * 32 + (size_t)((cap + 31) / 32) * 8 + (size_t)capPad * 4 + (size_t)cap * 8 + (size_t)capPad * 2 + 16;
+}
+
+__global__ void __launch_bounds__(kBowLatThreads) k_search_by_bow_lat(BowArgs a, int capPad) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  unsigned long long* keyA = reinterpret_cast<unsigned long long*>(smem);          // [capPad] node<<32 | index, sorted
+  unsigned long long* keyB = keyA + capPad;                                         // [capPad]
+  uint32_t* Bs = reinterpret_cast<uint32_t*>(keyB + capPad);                        // [cap][8] B descriptors
+  uint32_t* used = Bs + (size_t)a.cap * 8;                                          // [(cap+31)/32] B feature invalid or matched
+  uint32_t* vA = used + (a.cap + 31) / 32;                                          // [(cap+31)/32] validA
+  uint32_t* srun = vA + (a.cap + 31) / 32;                                          // [capPad] by sorted A position: B run rb0 | rb1 << 16
+  int* sasg = reinterpret_cast<int*>(srun + capPad);                                // [cap] m12 until the end
+  int* stag = sasg + a.cap;                                                         // [cap] order_round's tags, by B feature
+  uint16_t* slist = reinterpret_cast<uint16_t*>(stag + a.cap);                      // [capPad] sorted A positions that have a candidate
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_bcnt[kBowLatThreads / 32];
+  __shared__ int s_nm;
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
+  const int nA = a.nA[p], nB = a.nB[p];
+  const size_t po = (size_t)p * a.cap;
+  const uint32_t* dA = reinterpret_cast<const uint32_t*>(a.dA + po * 32);
+  const uint32_t* dB = reinterpret_cast<const uint32_t*>(a.dB + po * 32);
+  uint4* spec = a.spec + po;
+
+  ORBX_CLK(t0);
+  for (int i = tid; i < capPad; i += nth) {
+    keyA[i] = i < nA ? (((unsigned long long)(uint32_t)a.nodeA[po + i] << 32) | (unsigned)i) : ~0ull;
+    keyB[i] = i < nB ? (((unsigned long long)(uint32_t)a.nodeB[po + i] << 32) | (unsigned)i) : ~0ull;
+  }
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(dB);
+    uint4* dst = reinterpret_cast<uint4*>(Bs);
+    for (int i = tid; i < nB * 2; i += nth) dst[i] = __ldg(src + i);
+  }
+  for (int base = warp * 32; base < a.cap; base += nth) {
+    const int j = base + lane;
+    const uint32_t ub = __ballot_sync(0xffffffffu, j < nB && !a.validB[po + j]);
+    const uint32_t vb = __ballot_sync(0xffffffffu, j < nA && a.validA[po + j]);
+    if (lane == 0) { used[base >> 5] = ub; vA[base >> 5] = vb; }
+  }
+  for (int i = tid; i < a.cap; i += nth) { sasg[i] = -1; stag[i] = 0; }
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (tid == 0) s_nm = 0;
+  __syncthreads();
+  ORBX_CLK(t1);
+  cta_bitonic_sort<2>(keyA, keyB, capPad);
+  // 2a. a thread per sorted A entry: the B run of its node; the entries that are valid and have a run are listed in order
+  ORBX_CLK(t2);
+  int nlist = 0;
+  for (int base = 0; base < nA; base += nth) {
+    const int t = base + tid;
+    bool ok = false;
+    if (t < nA) {
+      const unsigned long long ka = keyA[t];
+      const uint32_t node = (uint32_t)(ka >> 32);
+      int lo = 0, hi = nB;                                                          // first B entry with node >= this node
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if ((uint32_t)(keyB[mid] >> 32) < node) lo = mid + 1; else hi = mid; }
+      const int rb0 = lo;
+      hi = nB;                                                                      // first B entry with node > this node
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if ((uint32_t)(keyB[mid] >> 32) <= node) lo = mid + 1; else hi = mid; }
+      srun[t] = (uint32_t)rb0 | ((uint32_t)lo << 16);
+      ok = bit_of(vA, (int)(ka & 0xffffffffu)) && rb0 < lo;
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) s_bcnt[warp] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < nwarps; ++w) { const int c = s_bcnt[w]; before += w < warp ? c : 0; total += c; }
+    if (ok) slist[nlist + before + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)t;
+    nlist += total;
+    __syncthreads();
+  }
+  // 2b. a thread per LISTED entry: the four nearest free features of its run.  Neighbouring entries mostly share a node, so the
+  // lanes of a warp walk the same run and a B descriptor is one broadcast read for all of them.
+  for (int c = tid; c < nlist; c += nth) {
+    const int t = slist[c];
+    const int i = (int)(keyA[t] & 0xffffffffu);
+    const uint32_t rr = srun[t];
+    uint32_t l0 = kNoKey, l1 = kNoKey, l2 = kNoKey, l3 = kNoKey;
+    int cnt = 0;
+    const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8) + 1);
+    for (int e = (int)(rr & 0xFFFFu); e < (int)(rr >> 16); ++e) {
+      const int j = (int)(keyB[e] & 0xffffffffu);
+      if (bit_of(used, j)) continue;
+      const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
+      const int d = __popc(q0.x ^ b0.x) + __popc(q0.y ^ b0.y) + __popc(q0.z ^ b0.z) + __popc(q0.w ^ b0.w) + __popc(q1.x ^ b1.x) +
+                    __popc(q1.y ^ b1.y) + __popc(q1.z ^ b1.z) + __popc(q1.w ^ b1.w);
+      uint32_t kk = ((uint32_t)d << 16) | (uint32_t)j;                              // sorted insertion into (l0 <= l1 <= l2 <= l3)
+      ++cnt;
+      if (kk < l0) { const uint32_t sw = l0; l0 = kk; kk = sw; }
+      if (kk < l1) { const uint32_t sw = l1; l1 = kk; kk = sw; }
+      if (kk < l2) { const uint32_t sw = l2; l2 = kk; kk = sw; }
+      if (kk < l3) l3 = kk;
+    }
+    spec[c] = make_uint4(l0 | (cnt <= 4 ? 0x80000000u : 0u), l1, l2, l3);          // no candidate: every key kNoKey, nothing to decide
+  }
+  __syncthreads();
+  // 3. ordered phase, a piece of the list per warp, cut at node boundaries
+  ORBX_CLK(t3);
+  {
+    auto node_at = [&](int c) { return (uint32_t)(keyA[slist[c]] >> 32); };
+    auto cut = [&](int w) {                                                          // first list position of warp w's piece (warp-uniform)
+      int c = (int)(((long long)nlist * w) / nwarps);
+      if (w <= 0) return 0;
+      if (w >= nwarps) return nlist;
+      while (c < nlist) {                                                           // forwards to the next node change
+        const int cc = c + lane;
+        const uint32_t same = __ballot_sync(0xffffffffu, cc < nlist && cc > 0 && node_at(cc) == node_at(cc - 1));
+        const int run = __ffs((int)~same) - 1;                                      // lanes before the first change
+        if (run < 0) { c += 32; continue; }
+        c += run;
+        break;
+      }
+      return min(c, nlist);
+    };
+    const int c_lo = cut(warp), c_hi = cut(warp + 1);
+    auto pass_of = [&](uint32_t k1, uint32_t k2) {
+      if (k1 == kNoKey) return false;
+      const int best = (int)(k1 >> 16), sec = k2 == kNoKey ? 256 : (int)(k2 >> 16);
+      return (a.strict ? best < a.th : best <= a.th) && (float)best < __fmul_rn(a.ratio, (float)sec);
+    };
+    int nm = 0, epoch = 0;
+    for (int base = c_lo; base < c_hi; base += 32) {
+      const int c = base + lane;
+      const bool in = c < c_hi;
+      const int t = in ? slist[c] : 0;
+      const uint4 my4 = in ? spec[c] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+      const int iA = (int)(keyA[t] & 0xffffffffu);
+      const bool complete = my4.x >> 31;
+      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
+      uint32_t todo = __ballot_sync(0xffffffffu, key[0] != kNoKey);
+      while (todo) {
+        const bool live = (todo >> lane) & 1u;
+        unsigned hitP = 0u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (key[k] != kNoKey && bit_of(used, (int)(key[k] & 0xFFFFu))) hitP |= 1u << k;
+        bool acc = false, starved = false;
+        int bi = -1;
+        order_round(key, hitP, stag, epoch, lane, [&](unsigned hit) {
+          uint32_t k1 = kNoKey, k2 = kNoKey;                             // the two nearest features nobody earlier has matched
+#pragma unroll
+          for (int k = 3; k >= 0; --k)
+            if (key[k] != kNoKey && !((hit >> k) & 1u)) { k2 = k1; k1 = key[k]; }
+          starved = live && !complete && k2 == kNoKey;
+          acc = live && pass_of(k1, k2);
+          bi = acc ? (int)(k1 & 0xFFFFu) : -1;
+          return bi;
+        });
+        const uint32_t sm = __ballot_sync(0xffffffffu, starved);
+        const int jstar = sm ? __ffs((int)sm) - 1 : 32;
+        const bool commit = acc && lane < jstar;
+        if (commit) { sasg[iA] = bi; atomicOr(&used[bi >> 5], 1u << (bi & 31)); }
+        nm += __popc(__ballot_sync(0xffffffffu, commit));
+        __syncwarp();
+        if (!sm) break;
+        // the starved query: its whole run again, against the live `used` (warp-wide, exact)
+        const int ts = __shfl_sync(0xffffffffu, t, jstar), is = __shfl_sync(0xffffffffu, iA, jstar);
+        const uint32_t rr = srun[ts];
+        const uint32_t qw = lane < 8 ? __ldg(dA + (size_t)is * 8 + lane) : 0u;
+        uint32_t q[8];
+#pragma unroll
+        for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, qw, w);
+        uint32_t k1 = 0xffffffffu, k2 = 0xffffffffu;
+        for (int e = (int)(rr & 0xFFFFu) + lane; e < (int)(rr >> 16); e += 32) {
+          const int j = (int)(keyB[e] & 0xffffffffu);
+          if (bit_of(used, j)) continue;
+          const uint32_t kk = ((uint32_t)ham8(q, Bs + (size_t)j * 8) << 16) | (uint32_t)j;
+          if (kk < k1) { k2 = k1; k1 = kk; }
+          else if (kk < k2) k2 = kk;
+        }
+        const uint32_t w1 = __reduce_min_sync(0xffffffffu, k1);
+        const uint32_t w2 = __reduce_min_sync(0xffffffffu, k1 == w1 ? k2 : k1);
+        if (pass_of(w1 == 0xffffffffu ? kNoKey : w1, w2 == 0xffffffffu ? kNoKey : w2)) {
+          const int bj = (int)(w1 & 0xFFFFu);
+          if (lane == 0) { sasg[is] = bj; atomicOr(&used[bj >> 5], 1u << (bj & 31)); }   // other warps own other bits of the same word
+          ++nm;
+        }
+        __syncwarp();
+        todo &= ~((2u << jstar) - 1u);
+      }
+    }
+    if (lane == 0 && nm) atomicAdd(&s_nm, nm);
+  }
+  __syncthreads();
+  ORBX_CLK(t4);
+  // 4. rotation consistency (src/ORBmatcher.cc:270-285, :636-652) and the write-back, whole CTA
+  const float* angA = a.angA + po;
+  const float* angB = a.angB + po;
+  if (a.checkOri) {
+    int mybin[(4096 + kBowLatThreads - 1) / kBowLatThreads];
+    int r = 0;
+    for (int base = 0; base < nA; base += nth, ++r) {
+      const int i = base + tid;
+      const int m = i < nA ? sasg[i] : -1;
+      mybin[r] = -1;
+      const unsigned act = __ballot_sync(0xffffffffu, m >= 0);
+      if (m >= 0) {                                                    // one atomic per distinct bin of the warp
+        const int b = rot_bin(angA[i], angB[m]);
+        mybin[r] = b;
+        const unsigned peers = __match_any_sync(act, b);
+        if (lane == __ffs((int)peers) - 1) atomicAdd(&s_hist[b], __popc(peers));
+      }
+    }
+    __syncthreads();
+    int k_a, k_b, k_c;
+    three_maxima(s_hist, k_a, k_b, k_c);
+    int drop = 0;
+    r = 0;
+    for (int i = tid; i < nA; i += nth, ++r) {
+      const int b = mybin[r];
+      if (b >= 0 && b != k_a && b != k_b && b != k_c) { sasg[i] = -1; ++drop; }
+    }
+    if (drop) atomicSub(&s_nm, drop);
+    __syncthreads();
+  }
+  int* m12 = a.m12 + po;
+  for (int i = tid; i < nA; i += nth) m12[i] = sasg[i];
+  if (tid == 0) a.nm[p] = s_nm;
+  ORBX_CLK(t5);
+  ORBX_CLK_PRINT("k_search_by_bow_lat stage / sort / lists / ordered / rotation + flush", t0, t1, t2, t3, t4, t5);
+  ORBX_STAT(if (tid == 0 && blockIdx.x == 0) printf("  K12: nA %d nB %d listed %d\n", nA, nB, nlist);)
+}
+
 int launch_search_by_bow(const BowArgs& a, cudaStream_t st) {
   int capPad = 32;
   while (capPad < a.cap) capPad <<= 1;
+  const size_t lat = bow_lat_bytes(a.cap, capPad);
+  // the latency form pays when the GPU has a few pairs (the SLAM call pattern); with a hundred pairs per call every SM is
+  // busy with other pairs' walks anyway, and the small CTAs of the throughput form pack six to an SM
+  if (a.n_pairs <= 64 && lat <= 200 * 1024 && !getenv("ORBX_BOW_SERIAL")) {
+    cudaFuncSetAttribute(k_search_by_bow_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
+    k_search_by_bow_lat<<<a.n_pairs, kBowLatThreads, lat, st>>>(a, capPad);
+    return 1;
+  }
   const size_t smem = (size_t)capPad * 16 + (size_t)a.cap * 32 + (size_t)((a.cap + 31) / 32) * 4;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_by_bow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  // the two-phase form pays when the GPU has a few pairs (the SLAM call pattern: 1.06 -> 0.65 ms per call); with a hundred
-  // pairs per call every SM is busy with other pairs' walks anyway and the re-scans only add work (107 k against 112 k pairs/s)
-  k_search_by_bow<<<a.n_pairs, kBowThreads, smem, st>>>(a, capPad, (a.n_pairs <= 64 && !getenv("ORBX_BOW_SERIAL")) ? 1 : 0);
+  k_search_by_bow<<<a.n_pairs, kBowThreads, smem, st>>>(a, capPad);
   return 1;
 }
 
@@ -1590,9 +1768,149 @@ __global__ void __launch_bounds__(kBowThreads) k_search_triangulation(TriArgs a,
   if (tid == 0) a.nm[p] = s_nm;
 }
 
+// K14, latency form (one keyframe pair per call is how LocalMapping::CreateNewMapPoints asks): the same walk, 1024 threads
+// instead of 128, the KF2 side sorted by the whole CTA, and everything the per-candidate tests read - position, octave,
+// "has a map point", "is stereo" - staged in shared memory beside the descriptors, so that a candidate costs no global
+// round trip (the 128-thread form spends its time on three dependent ones per candidate that survives the distance test).
+constexpr int kTriLatThreads = 1024;
+
+__host__ __device__ inline size_t tri_lat_bytes(int cap, int capPad) {
+  return (size_t)capPad * 16 + (size_t)cap * 32 + (size_t)cap * 8 + (size_t)((cap + 31) / 32) * 8 + (size_t)cap + 16;
+}
+
+__global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(TriArgs a, int capPad) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  unsigned long long* keyB = reinterpret_cast<unsigned long long*>(smem);          // [capPad] KF2 node<<32 | index, sorted
+  unsigned long long* keyA = keyB + capPad;                                         // [capPad] KF1 the same: neighbouring threads then walk the same run (broadcast reads)
+  uint32_t* Bs = reinterpret_cast<uint32_t*>(keyA + capPad);                        // [cap][8]
+  float2* sxy = reinterpret_cast<float2*>(Bs + (size_t)a.cap * 8);                  // [cap] KF2 keypoint positions
+  uint32_t* hasb = reinterpret_cast<uint32_t*>(sxy + a.cap);                        // [(cap+31)/32] KF2 feature has a map point
+  uint32_t* stb = hasb + (a.cap + 31) / 32;                                         // [(cap+31)/32] KF2 feature is stereo
+  uint8_t* soct = reinterpret_cast<uint8_t*>(stb + (a.cap + 31) / 32);              // [cap] KF2 octave
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_nm;
+  __shared__ float s_epi[2], s_F[9];
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x;
+  const int n1 = a.n1[p], n2 = a.n2[p];
+  const size_t po = (size_t)p * a.cap;
+  const orbx_keypoint* k1 = a.k1 + po; const orbx_keypoint* k2 = a.k2 + po;
+  const uint32_t* d1 = reinterpret_cast<const uint32_t*>(a.d1 + po * 32);
+  const uint32_t* d2 = reinterpret_cast<const uint32_t*>(a.d2 + po * 32);
+  int* m12 = a.m12 + po;
+  ORBX_CLK(t0);
+  for (int i = tid; i < capPad; i += nth) {
+    keyB[i] = i < n2 ? (((unsigned long long)(uint32_t)a.node2[po + i] << 32) | (unsigned)i) : ~0ull;
+    keyA[i] = i < n1 ? (((unsigned long long)(uint32_t)a.node1[po + i] << 32) | (unsigned)i) : ~0ull;
+  }
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(d2);
+    uint4* dst = reinterpret_cast<uint4*>(Bs);
+    for (int i = tid; i < n2 * 2; i += nth) dst[i] = __ldg(src + i);
+  }
+  for (int j = tid; j < n2; j += nth) { const orbx_keypoint kp = k2[j]; sxy[j] = make_float2(kp.x, kp.y); soct[j] = (uint8_t)kp.octave; }
+  for (int base = warp * 32; base < a.cap; base += nth) {
+    const int j = base + lane;
+    const uint32_t hb = __ballot_sync(0xffffffffu, j < n2 && a.hasMp2[po + j]);
+    const uint32_t sb = __ballot_sync(0xffffffffu, j < n2 && a.uR2[po + j] >= 0.f);
+    if (lane == 0) { hasb[base >> 5] = hb; stb[base >> 5] = sb; }
+  }
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (tid >= 32 && tid < 41) s_F[tid - 32] = a.F12[(size_t)p * 9 + tid - 32];
+  if (tid == 0) {
+    s_nm = 0;
+    const float* T = a.pose2 + (size_t)p * 12; const float* C = a.Cw + (size_t)p * 3; const float* K = a.cam2 + (size_t)p * 4;
+    float C2[3];
+    for (int r = 0; r < 3; ++r)                                                     // R2w*Cw + t2w, cv::gemm arithmetic (src/ORBmatcher.cc:667)
+      C2[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[3 * r], C[0]), __fmul_rn(T[3 * r + 1], C[1])), __fmul_rn(T[3 * r + 2], C[2])), T[9 + r]);
+    const float invz = __fdiv_rn(1.0f, C2[2]);
+    s_epi[0] = __fadd_rn(__fmul_rn(__fmul_rn(K[0], C2[0]), invz), K[2]);
+    s_epi[1] = __fadd_rn(__fmul_rn(__fmul_rn(K[1], C2[1]), invz), K[3]);
+  }
+  __syncthreads();
+  ORBX_CLK(t1);
+  cta_bitonic_sort<2>(keyB, keyA, capPad);
+  ORBX_CLK(t2);
+  const float ex = s_epi[0], ey = s_epi[1];
+  int nm = 0;
+  ORBX_STAT(int dbg_cand = 0;)
+  int mine[(4096 + kTriLatThreads - 1) / kTriLatThreads], mybin[(4096 + kTriLatThreads - 1) / kTriLatThreads];
+  int r = 0;
+  for (int t = tid; t < n1; t += nth, ++r) {
+    int best2 = -1;
+    const unsigned long long ka = keyA[t];
+    const int i = (int)(ka & 0xffffffffu);
+    const uint32_t node = (uint32_t)(ka >> 32);
+    // every field of the KF1 feature is requested before the first test
+    const bool st1 = a.uR1[po + i] >= 0.f;
+    const int has1 = a.hasMp1[po + i];
+    const orbx_keypoint kp1 = k1[i];
+    const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8) + 1);
+    if (!has1 && !(a.onlyStereo && !st1)) {
+      int lo = 0, hi = n2;                                                          // first entry with node2 >= node
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if ((uint32_t)(keyB[mid] >> 32) < node) lo = mid + 1; else hi = mid; }
+      const float la = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[0]), __fmul_rn(kp1.y, s_F[3])), s_F[6]);
+      const float lb = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[1]), __fmul_rn(kp1.y, s_F[4])), s_F[7]);
+      const float lc = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[2]), __fmul_rn(kp1.y, s_F[5])), s_F[8]);
+      const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+      int bestDist = 50;                                                            // TH_LOW
+      for (int e = lo; e < n2 && (uint32_t)(keyB[e] >> 32) == node; ++e) {
+        ORBX_STAT(++dbg_cand;)
+        const int j = (int)(keyB[e] & 0xffffffffu);
+        const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
+        const int dist = __popc(q0.x ^ b0.x) + __popc(q0.y ^ b0.y) + __popc(q0.z ^ b0.z) + __popc(q0.w ^ b0.w) + __popc(q1.x ^ b1.x) +
+                         __popc(q1.y ^ b1.y) + __popc(q1.z ^ b1.z) + __popc(q1.w ^ b1.w);
+        if (dist > 50 || dist > bestDist) continue;
+        if (bit_of(hasb, j)) continue;
+        const bool st2 = bit_of(stb, j);
+        if (a.onlyStereo && !st2) continue;
+        const float2 p2 = sxy[j];
+        const int o2 = soct[j];
+        if (!st1 && !st2) {
+          const float dx = __fsub_rn(ex, p2.x), dy = __fsub_rn(ey, p2.y);
+          if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, a.scale2[o2])) continue;
+        }
+        if (den == 0.f) continue;
+        const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, p2.x), __fmul_rn(lb, p2.y)), lc);
+        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+        if ((double)dsqr < __dmul_rn(3.84, (double)a.sigma2_2[o2])) { best2 = j; bestDist = dist; }
+      }
+    }
+    mine[r] = best2; mybin[r] = -1;
+    if (best2 >= 0) {
+      ++nm;
+      if (a.checkOri) { mybin[r] = rot_bin(kp1.angle, k2[best2].angle); atomicAdd(&s_hist[mybin[r]], 1); }
+    }
+  }
+  ORBX_CLK(t3w);
+  if (nm) atomicAdd(&s_nm, nm);
+  __syncthreads();
+  ORBX_CLK(t3);
+  int k_a = -1, k_b = -1, k_c = -1;
+  if (a.checkOri) three_maxima(s_hist, k_a, k_b, k_c);
+  int drop = 0;
+  r = 0;
+  for (int t = tid; t < n1; t += nth, ++r) {
+    int m = mine[r];
+    if (a.checkOri && m >= 0) { const int b = mybin[r]; if (b != k_a && b != k_b && b != k_c) { m = -1; ++drop; } }
+    m12[(int)(keyA[t] & 0xffffffffu)] = m;
+  }
+  if (drop) atomicSub(&s_nm, drop);
+  __syncthreads();
+  if (tid == 0) a.nm[p] = s_nm;
+  ORBX_CLK(t4);
+  ORBX_CLK_PRINT("k_search_triangulation_lat stage / sort / walk (thread 0) / walk (all) / rotation + flush", t0, t1, t2, t3w, t3, t4);
+  ORBX_STAT(if (tid == 0 && blockIdx.x == 0) printf("  K14: thread 0 walked %d candidates\n", dbg_cand);)
+}
+
 int launch_search_triangulation(const TriArgs& a, cudaStream_t st) {
   int capPad = 32;
   while (capPad < a.cap) capPad <<= 1;
+  const size_t lat = tri_lat_bytes(a.cap, capPad);
+  if (a.n_pairs <= 64 && lat <= 200 * 1024 && !getenv("ORBX_BOW_SERIAL")) {
+    cudaFuncSetAttribute(k_search_triangulation_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
+    k_search_triangulation_lat<<<a.n_pairs, kTriLatThreads, lat, st>>>(a, capPad);
+    return 1;
+  }
   const size_t smem = (size_t)capPad * 8 + (size_t)a.cap * 32;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_search_triangulation, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   k_search_triangulation<<<a.n_pairs, kBowThreads, smem, st>>>(a, capPad);

@@ -589,6 +589,10 @@ def test_search_by_bow_with_vocabulary_buckets(gx, oracle, strict, ratio, ori):
     for p in range(4):
         assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), (p, nm[p], refs[p][1])
     assert refs[0][1] > 50 and refs[2][1] > 50
+    # the same pairs 17 times over in one call: above 64 pairs the throughput form of the kernel runs instead of the latency form
+    nm2, m2 = gx.ORBmatcher(ratio, ori).SearchByBoWNodes(sidesA * 17, sidesB * 17, strict=strict)
+    for q in range(68):
+        assert nm2[q] == refs[q % 4][1] and np.array_equal(m2[q], refs[q % 4][0]), (q, nm2[q], refs[q % 4][1])
     # matches never cross nodes and never use an invalid feature
     m = m12[0]; ok = m >= 0
     assert np.array_equal(sidesA[0][3][ok], sidesB[0][3][m[ok]]) and sidesA[0][2][ok].all() and sidesB[0][2][m[ok]].all()
@@ -644,6 +648,10 @@ def test_search_for_triangulation(gx, oracle, only_stereo, ori):
     for p in range(3):
         assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), (p, nm[p], refs[p][1])
     assert refs[0][1] > (5 if only_stereo else 30)
+    # 66 pairs in one call: above 64 the throughput form (128 threads per pair) runs instead of the latency form
+    nm2, m2 = gx.ORBmatcher(0.6, ori).SearchForTriangulation(kf1 * 22, kf2 * 22, F12 * 22, poses * 22, Cws * 22, cams * 22, scale, sigma2, bOnlyStereo=only_stereo)
+    for q in range(66):
+        assert nm2[q] == refs[q % 3][1] and np.array_equal(m2[q], refs[q % 3][0]), (q, nm2[q], refs[q % 3][1])
 
 
 @pytest.mark.parametrize("k,L,levelsup,weighting,norm", [(10, 4, 2, 0, 1), (10, 3, 4, 0, 1), (6, 5, 3, 1, 2), (10, 4, 2, 2, 1), (8, 3, 1, 3, 0), (10, 4, 2, 1, 0)])
