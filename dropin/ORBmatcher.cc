@@ -39,10 +39,23 @@ const int ORBmatcher::HISTO_LENGTH = 30;
 
 namespace {
 
-// &Derived::member for a protected member of the base has type `float MapPoint::*` and passes the access check
+// &Derived::member for a protected member of the base has type `T MapPoint::*` and passes the access check.  Position, normal
+// and descriptor are read in place under the reference's own mutexes (what GetWorldPos / GetNormal / GetDescriptor do, minus
+// the three cv::Mat clones - heap allocations - per map point, which were most of the cost of flattening a few hundred points).
 struct MapPointFields : MapPoint {
   static float MinDistance(MapPoint* p) { return p->*(&MapPointFields::mfMinDistance); }
   static float MaxDistance(MapPoint* p) { return p->*(&MapPointFields::mfMaxDistance); }
+  static void PosNormal(MapPoint* p, float* xw, float* nn) {
+    std::unique_lock<std::mutex> lock(p->*(&MapPointFields::mMutexPos));
+    const cv::Mat& X = p->*(&MapPointFields::mWorldPos);
+    const cv::Mat& N = p->*(&MapPointFields::mNormalVector);
+    for (int a = 0; a < 3; ++a) { xw[a] = X.at<float>(a); if (nn) nn[a] = N.at<float>(a); }
+  }
+  static void Descriptor(MapPoint* p, unsigned char* out) {
+    std::unique_lock<std::mutex> lock(p->*(&MapPointFields::mMutexFeatures));
+    const cv::Mat& d = p->*(&MapPointFields::mDescriptor);
+    std::copy(d.ptr(0), d.ptr(0) + 32, out);
+  }
 };
 
 // Frame's static image bounds and inverse cell sizes (src/Frame.cc:207-213) as the C ABI's grid_bounds[6]
@@ -58,19 +71,32 @@ void check(orbx_status s) {
   if (s != ORBX_OK) throw std::runtime_error(std::string("orbx: ") + orbx_last_error_string());
 }
 
-// mvKeysUn / mDescriptors / mvuRight of a Frame or KeyFrame as the flat arrays the C ABI takes
+// mvKeysUn / mDescriptors / mvuRight of a Frame or KeyFrame as the flat arrays the C ABI takes.  cv::KeyPoint and
+// orbx_keypoint have the same layout and the descriptor matrix is N contiguous rows of 32 bytes, so when no padding is asked
+// for (cap == N, the usual case) the three arrays are the object's own storage: nothing is copied.
+template <class T> struct View {
+  const T* p = nullptr; std::vector<T> own;
+  const T* data() const { return p; }
+  const T& operator[](size_t i) const { return p[i]; }
+};
 struct Flat {
   int n = 0, cap = 1;
-  std::vector<orbx_keypoint> kps; std::vector<unsigned char> desc; std::vector<float> uright;
+  View<orbx_keypoint> kps; View<unsigned char> desc; View<float> uright;
   template <class F> explicit Flat(const F& f, int cap_ = 0) {
     n = f.N; cap = std::max(std::max(n, cap_), 1);
-    kps.resize(cap); desc.assign((size_t)cap * 32, 0); uright.assign(cap, -1.f);
     static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint layout");
-    for (int i = 0; i < n; ++i) {
-      kps[i] = reinterpret_cast<const orbx_keypoint&>(f.mvKeysUn[i]);
-      std::copy(f.mDescriptors.ptr(i), f.mDescriptors.ptr(i) + 32, &desc[(size_t)i * 32]);
-      uright[i] = f.mvuRight[i];
+    if (n > 0 && cap == n && f.mDescriptors.isContinuous() && f.mDescriptors.rows >= n && f.mDescriptors.cols == 32 && f.mDescriptors.type() == CV_8UC1 &&
+        (int)f.mvKeysUn.size() >= n && (int)f.mvuRight.size() >= n) {
+      kps.p = reinterpret_cast<const orbx_keypoint*>(f.mvKeysUn.data()); desc.p = f.mDescriptors.ptr(0); uright.p = f.mvuRight.data();
+      return;
     }
+    kps.own.resize(cap); desc.own.assign((size_t)cap * 32, 0); uright.own.assign(cap, -1.f);
+    for (int i = 0; i < n; ++i) {
+      kps.own[i] = reinterpret_cast<const orbx_keypoint&>(f.mvKeysUn[i]);
+      std::copy(f.mDescriptors.ptr(i), f.mDescriptors.ptr(i) + 32, &desc.own[(size_t)i * 32]);
+      uright.own[i] = f.mvuRight[i];
+    }
+    kps.p = kps.own.data(); desc.p = desc.own.data(); uright.p = uright.own.data();
   }
 };
 
@@ -114,9 +140,8 @@ struct MPs {
   }
   void set(int k, MapPoint* mp) {
     valid[k] = 1;
-    const cv::Mat X = mp->GetWorldPos(), Nn = mp->GetNormal(), d = mp->GetDescriptor();
-    for (int a = 0; a < 3; ++a) { xw[3 * k + a] = X.at<float>(a); normal[3 * k + a] = Nn.at<float>(a); }
-    std::copy(d.ptr(0), d.ptr(0) + 32, &desc[(size_t)k * 32]);
+    MapPointFields::PosNormal(mp, &xw[3 * k], &normal[3 * k]);
+    MapPointFields::Descriptor(mp, &desc[(size_t)k * 32]);
     dmin[k] = MapPointFields::MinDistance(mp); dmax[k] = MapPointFields::MaxDistance(mp);
     obs[k] = mp->Observations();
   }
@@ -145,8 +170,7 @@ int ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoint
     if (!mp->mbTrackInView || mp->isBad()) continue;
     inview[k] = 1; px[k] = mp->mTrackProjX; py[k] = mp->mTrackProjY; pxr[k] = mp->mTrackProjXR;
     level[k] = mp->mnTrackScaleLevel; vcos[k] = mp->mTrackViewCos; obs[k] = mp->Observations();
-    const cv::Mat d = mp->GetDescriptor();
-    std::copy(d.ptr(0), d.ptr(0) + 32, &desc[(size_t)k * 32]);
+    MapPointFields::Descriptor(mp, &desc[(size_t)k * 32]);
   }
   std::vector<int> frame_obs(f.cap, -1), assigned(f.cap, -1);
   for (int i = 0; i < f.n; ++i) if (F.mvpMapPoints[i]) frame_obs[i] = F.mvpMapPoints[i]->Observations();
@@ -177,9 +201,8 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, 
     MapPoint* mp = LastFrame.mvpMapPoints[i];
     if (!mp || LastFrame.mvbOutlier[i]) continue;
     valid[i] = 1;
-    const cv::Mat X = mp->GetWorldPos(), d = mp->GetDescriptor();
-    for (int a = 0; a < 3; ++a) xw[3 * i + a] = X.at<float>(a);
-    std::copy(d.ptr(0), d.ptr(0) + 32, &desc[(size_t)i * 32]);
+    MapPointFields::PosNormal(mp, &xw[3 * i], nullptr);
+    MapPointFields::Descriptor(mp, &desc[(size_t)i * 32]);
     octave[i] = LastFrame.mvKeys[i].octave; angle[i] = LastFrame.mvKeysUn[i].angle; obs[i] = mp->Observations();
   }
   float pose[12];
@@ -255,16 +278,12 @@ int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapP
 static int bow_search(const Flat& a, const std::vector<unsigned char>& validA, const DBoW2::FeatureVector& fvA, const std::vector<float>& angA, const Flat& b,
                       const std::vector<unsigned char>& validB, const DBoW2::FeatureVector& fvB, const std::vector<float>& angB, float ratio, bool ori,
                       bool strict, std::vector<int>& m12) {
-  const int cap = std::max(a.cap, b.cap);
-  auto grow = [cap](std::vector<unsigned char> v, size_t per) { v.resize((size_t)cap * per, 0); return v; };
-  auto growf = [cap](std::vector<float> v) { v.resize(cap, 0.f); return v; };
-  const std::vector<unsigned char> dA = grow(a.desc, 32), dB = grow(b.desc, 32), vA = grow(validA, 1), vB = grow(validB, 1);
-  const std::vector<float> aA = growf(angA), aB = growf(angB);
+  const int cap = a.cap;                                                    // both sides were flattened with the common capacity
   const std::vector<int> nA = nodes_of(fvA, cap), nB = nodes_of(fvB, cap);
   m12.assign(cap, -1);
   int nm = 0;
-  check(orbx_search_by_bow_batch(dA.data(), aA.data(), vA.data(), nA.data(), &a.n, dB.data(), aB.data(), vB.data(), nB.data(), &b.n, 1, cap, 50, ratio, ori ? 1 : 0,
-                                 strict ? 1 : 0, m12.data(), &nm, 0, nullptr));
+  check(orbx_search_by_bow_batch(a.desc.data(), angA.data(), validA.data(), nA.data(), &a.n, b.desc.data(), angB.data(), validB.data(), nB.data(), &b.n, 1, cap, 50, ratio,
+                                 ori ? 1 : 0, strict ? 1 : 0, m12.data(), &nm, 0, nullptr));
   return nm;
 }
 
@@ -272,7 +291,8 @@ static int bow_search(const Flat& a, const std::vector<unsigned char>& validA, c
 int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches) {
   const vector<MapPoint*> vpMapPointsKF = pKF->GetMapPointMatches();
   vpMapPointMatches = vector<MapPoint*>(F.N, static_cast<MapPoint*>(NULL));
-  const Flat a(*pKF), b(F);
+  const int cap = std::max(pKF->N, F.N);
+  const Flat a(*pKF, cap), b(F, cap);
   std::vector<unsigned char> vA(a.cap, 0), vB(b.cap, 1);
   std::vector<float> angA(a.cap, 0.f), angB(b.cap, 0.f);
   for (int i = 0; i < a.n; ++i) { vA[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad(); angA[i] = pKF->mvKeysUn[i].angle; }
@@ -287,7 +307,8 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPoi
 int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12) {
   const vector<MapPoint*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
   vpMatches12 = vector<MapPoint*>(vpMapPoints1.size(), static_cast<MapPoint*>(NULL));
-  const Flat a(*pKF1), b(*pKF2);
+  const int cap = std::max(pKF1->N, pKF2->N);
+  const Flat a(*pKF1, cap), b(*pKF2, cap);
   std::vector<unsigned char> vA(a.cap, 0), vB(b.cap, 0);
   std::vector<float> angA(a.cap, 0.f), angB(b.cap, 0.f);
   for (int i = 0; i < a.n; ++i) { vA[i] = vpMapPoints1[i] && !vpMapPoints1[i]->isBad(); angA[i] = pKF1->mvKeysUn[i].angle; }

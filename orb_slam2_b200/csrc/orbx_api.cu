@@ -759,8 +759,6 @@ thread_local cudaEvent_t g_arena_event = nullptr;
 
 struct Staged {
   cudaStream_t st;
-  struct Pending { void* user; const uint8_t* mirror; size_t bytes; };
-  std::vector<Pending> pending;
   explicit Staged(cudaStream_t s) : st(s) {
     int dev = 0;
     cudaGetDevice(&dev);
@@ -801,19 +799,43 @@ struct Staged {
       }
     return cudaSuccess;
   }
-  // device -> caller's host array: through the pinned mirror when `dev` lies in one of this thread's buffers
-  // (asynchronous; the bytes reach `user` in sync()), else a plain copy
+  // device -> caller's host array: through the pinned mirror when `dev` lies in one of this thread's buffers (the copy is
+  // issued by sync(), merged with the call's other downloads from the same block: results that sit side by side in the
+  // arena come back in ONE copy; the bytes reach `user` in sync()), else a plain asynchronous copy
+  struct Pending { void* user; const uint8_t* mirror; size_t bytes; const Arena::Block* block; size_t off; };
+  std::vector<Pending> pending;
   cudaError_t d2h(void* user, const void* dev, size_t bytes) {
     for (Arena* a : {&g_out_arena, &g_in_arena})
       for (const Arena::Block& b : a->blocks)
         if ((const uint8_t*)dev >= b.d && (const uint8_t*)dev + bytes <= b.d + b.cap) {
-          uint8_t* m = b.h + ((const uint8_t*)dev - b.d);
-          pending.push_back({user, m, bytes});
-          return cudaMemcpyAsync(m, dev, bytes, cudaMemcpyDeviceToHost, st);
+          const size_t off = (size_t)((const uint8_t*)dev - b.d);
+          pending.push_back({user, b.h + off, bytes, &b, off});
+          return cudaSuccess;
         }
     return cudaMemcpyAsync(user, dev, bytes, cudaMemcpyDeviceToHost, st);
   }
   cudaError_t sync() {
+    // one copy per arena block that has downloads pending: the span from the first to the last wanted byte, unless the
+    // span is mostly bytes nobody asked for
+    for (size_t i = 0; i < pending.size(); ++i) {
+      const Arena::Block* b = pending[i].block;
+      bool first = true;
+      for (size_t k = 0; k < i; ++k) first = first && pending[k].block != b;
+      if (!first) continue;
+      size_t lo = (size_t)-1, hi = 0, want = 0;
+      for (const Pending& q : pending)
+        if (q.block == b) { lo = std::min(lo, q.off); hi = std::max(hi, q.off + q.bytes); want += q.bytes; }
+      if (hi - lo <= 2 * want + (64u << 10)) {
+        const cudaError_t e = cudaMemcpyAsync(b->h + lo, b->d + lo, hi - lo, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return e;
+      } else {
+        for (const Pending& q : pending)
+          if (q.block == b) {
+            const cudaError_t e = cudaMemcpyAsync(b->h + q.off, b->d + q.off, q.bytes, cudaMemcpyDeviceToHost, st);
+            if (e != cudaSuccess) return e;
+          }
+      }
+    }
     const cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) return e;
     for (const Pending& p : pending) std::memcpy(p.user, p.mirror, p.bytes);
