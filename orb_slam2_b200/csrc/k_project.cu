@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(128) k_project_search(ProjSearchArgs a) {
   if (i >= m) return;
   const size_t mo = (size_t)p * a.mcap + i, ko = (size_t)p * a.cap;
   int* out = a.best + mo;
-  if (!a.valid[mo]) { *out = -1; return; }
+  if (a.valid && !a.valid[mo]) { *out = -1; return; }
   const float* xf = a.xf + (size_t)p * 27;                      // R1 (9) t1 (3) R2 (9) t2 (3) Ow (3)
   const float* kfb = a.kf_bounds + (size_t)p * 4;               // KeyFrame::mnMinX, mnMaxX, mnMinY, mnMaxY
   const float* gb = a.grid_bounds;                              // Frame's mnMinX, mnMaxX, mnMinY, mnMaxY, invW, invH
@@ -130,6 +130,155 @@ __global__ void __launch_bounds__(128) k_project_search(ProjSearchArgs a) {
     }
   }
   if (bestDist <= a.th_dist) *out = bestIdx;
+}
+
+// K16, latency form (one keyframe per call: LoopClosing::ComputeSim3 asks about one candidate pair, SearchInNeighbors fuses
+// into one neighbour at a time).  A CTA of 1024 threads per problem; the target's CSR grid, positions, octaves, descriptors
+// (and uRight for Fuse's chi-square gate) staged in shared memory.  Map points go through in blocks of 1024: a THREAD per
+// map point works out its projection and search window (the double-precision part), the ones that have a window are listed,
+// then a WARP per listed map point shares the window's candidates (for_each_in_columns) and keeps the least
+// (distance, CSR position) - the reference's first least distance in its enumeration order.
+constexpr int kPsLatThreads = 1024;
+
+__host__ __device__ inline size_t ps_lat_bytes(int cap, bool with_ur) {
+  size_t b = (size_t)(kPCells + 1 + 3) / 4 * 16 + (size_t)cap * (32 + 8 + 4) + (with_ur ? (size_t)cap * 4 : 0);
+  b = (b + 15) & ~(size_t)15;
+  return b + (size_t)kPsLatThreads * (20 + 2);              // the block's windows {u, v, ur, radius, packed} and its list
+}
+
+__global__ void __launch_bounds__(kPsLatThreads) k_project_search_lat(ProjSearchArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ int s_bcnt[kPsLatThreads / 32];
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
+  const int m = min(a.m[p], a.mcap);
+  const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
+  const bool gate = (a.mode & 8) != 0;
+  int* cs = reinterpret_cast<int*>(smem);
+  uint32_t* sdesc = reinterpret_cast<uint32_t*>(smem + (size_t)(kPCells + 1 + 3) / 4 * 16);     // [cap][8] by keypoint
+  float2* sxy = reinterpret_cast<float2*>(sdesc + (size_t)a.cap * 8);                           // [cap] in CSR order
+  uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);                                   // [cap] octave << 24 | keypoint, CSR order
+  float* sur = reinterpret_cast<float*>(smeta + a.cap);                                         // [cap] uRight by keypoint (Fuse only)
+  uint8_t* tail = smem + ((((size_t)(kPCells + 1 + 3) / 4 * 16 + (size_t)a.cap * (32 + 8 + 4) + (gate ? (size_t)a.cap * 4 : 0)) + 15) & ~(size_t)15);
+  float4* swin = reinterpret_cast<float4*>(tail);                                               // [1024] u, v, ur, radius
+  uint32_t* spack = reinterpret_cast<uint32_t*>(swin + kPsLatThreads);                          // [1024] level << 24 | cx0 << 18 | cx1 << 12 | cy0 << 6 | cy1
+  uint16_t* slist = reinterpret_cast<uint16_t*>(spack + kPsLatThreads);                         // [1024] block-relative indices that have a window
+  {
+    const orbx_keypoint* kps = a.kps + ko;
+    const int* gcs = a.cell_start + (size_t)p * (kPCells + 1);
+    const int* items = a.cell_items + ko;
+    for (int i = tid; i <= kPCells; i += nth) cs[i] = gcs[i];
+    const int n_items = min(gcs[kPCells], a.cap);
+    for (int e = tid; e < n_items; e += nth) {
+      const int idx = items[e];
+      const orbx_keypoint kp = kps[idx];
+      sxy[e] = make_float2(kp.x, kp.y);
+      smeta[e] = ((uint32_t)kp.octave << 24) | (uint32_t)idx;
+      if (gate) sur[idx] = a.u_right[ko + idx];
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(a.desc + ko * 32);
+    uint4* dst = reinterpret_cast<uint4*>(sdesc);
+    for (int i = tid; i < a.cap * 2; i += nth) dst[i] = __ldg(src + i);
+  }
+  const float* xf = a.xf + (size_t)p * 27;                      // R1 (9) t1 (3) R2 (9) t2 (3) Ow (3)
+  const float* kfb = a.kf_bounds + (size_t)p * 4;               // KeyFrame::mnMinX, mnMaxX, mnMinY, mnMaxY
+  const float* gb = a.grid_bounds;                              // Frame's mnMinX, mnMaxX, mnMinY, mnMaxY, invW, invH
+  const uint32_t* mpd = reinterpret_cast<const uint32_t*>(a.mp_desc + mo * 32);
+  for (int base = 0; base < m; base += nth) {
+    // a thread per map point of the block: projection, tests, window (the arithmetic of k_project_search, statement by statement)
+    const int i = base + tid;
+    bool ok = false;
+    if (i < m && (!a.valid || a.valid[mo + i])) {
+      const float xw[3] = {a.xw[(mo + i) * 3], a.xw[(mo + i) * 3 + 1], a.xw[(mo + i) * 3 + 2]};
+      const float dmin = a.dmin[mo + i], dmax = a.dmax[mo + i];
+      float nn[3] = {0.f, 0.f, 0.f};
+      if (a.mode & 4) { nn[0] = a.normal[(mo + i) * 3]; nn[1] = a.normal[(mo + i) * 3 + 1]; nn[2] = a.normal[(mo + i) * 3 + 2]; }
+      float pc[3], q[3];
+      gemm3(xf, xf + 9, xw, pc);
+      if (a.mode & 1) gemm3(xf + 12, xf + 21, pc, q); else { q[0] = pc[0]; q[1] = pc[1]; q[2] = pc[2]; }
+      do {
+        if (q[2] < 0.0f) break;
+        const float invz = (a.mode & 16) ? (float)__ddiv_rn(1.0, (double)q[2]) : __fdiv_rn(1.0f, q[2]);
+        const float x = __fmul_rn(q[0], invz), y = __fmul_rn(q[1], invz);
+        const float u = __fadd_rn(__fmul_rn(a.fx, x), a.cx), v = __fadd_rn(__fmul_rn(a.fy, y), a.cy);
+        if (!(u >= kfb[0] && u < kfb[1] && v >= kfb[2] && v < kfb[3])) break;
+        const float ur = __fsub_rn(u, __fmul_rn(a.bf, invz));
+        float PO[3] = {q[0], q[1], q[2]};
+        if (a.mode & 2) { PO[0] = __fsub_rn(xw[0], xf[24]); PO[1] = __fsub_rn(xw[1], xf[25]); PO[2] = __fsub_rn(xw[2], xf[26]); }
+        const double s2 = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)PO[0]), __dmul_rn((double)PO[1], (double)PO[1])), __dmul_rn((double)PO[2], (double)PO[2]));
+        const float dist3D = (float)__dsqrt_rn(s2);
+        if (dist3D < __fmul_rn(0.8f, dmin) || dist3D > __fmul_rn(1.2f, dmax)) break;
+        if (a.mode & 4) {
+          const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)PO[0], (double)nn[0]), __dmul_rn((double)PO[1], (double)nn[1])), __dmul_rn((double)PO[2], (double)nn[2]));
+          if (dot < __dmul_rn(0.5, (double)dist3D)) break;
+        }
+        int level = (int)ceilf(__fdiv_rn(libm_logf(__fdiv_rn(dmax, dist3D)), a.log_scale));
+        level = level < 0 ? 0 : (level >= a.nlevels ? a.nlevels - 1 : level);
+        const float radius = __fmul_rn(a.th, a.scale[level]);
+        const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, kfb[0]), radius), gb[4])));
+        const int cx1 = min(kPGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, kfb[0]), radius), gb[4])));
+        const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, kfb[2]), radius), gb[5])));
+        const int cy1 = min(kPGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, kfb[2]), radius), gb[5])));
+        if (cx0 >= kPGridCols || cx1 < 0 || cy0 >= kPGridRows || cy1 < 0) break;
+        swin[tid] = make_float4(u, v, ur, radius);
+        spack[tid] = ((uint32_t)level << 24) | ((uint32_t)cx0 << 18) | ((uint32_t)cx1 << 12) | ((uint32_t)cy0 << 6) | (uint32_t)cy1;
+        ok = true;
+      } while (false);
+    }
+    if (i < m && !ok) a.best[mo + i] = -1;
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) s_bcnt[warp] = __popc(bal);
+    __syncthreads();                                            // (also: the staging above is complete)
+    int before = 0, nlist = 0;
+    for (int w = 0; w < nwarps; ++w) { const int c = s_bcnt[w]; before += w < warp ? c : 0; nlist += c; }
+    if (ok) slist[before + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)tid;
+    __syncthreads();
+    // a warp per listed map point, the next one's descriptor in flight
+    auto dword = [&](int c) { return (c < nlist && lane < 8) ? __ldg(mpd + (size_t)(base + slist[c]) * 8 + lane) : 0u; };
+    uint32_t ndw = dword(warp);
+    for (int c = warp; c < nlist; c += nwarps) {
+      const uint32_t dw = ndw;
+      ndw = dword(c + nwarps);
+      const int r = slist[c];
+      const float4 win = swin[r];
+      const uint32_t pk = spack[r];
+      const float u = win.x, v = win.y, ur = win.z, radius = win.w;
+      const int level = (int)(pk >> 24), cx0 = (int)((pk >> 18) & 63u), cx1 = (int)((pk >> 12) & 63u), cy0 = (int)((pk >> 6) & 63u), cy1 = (int)(pk & 63u);
+      uint32_t qd[8];
+#pragma unroll
+      for (int w = 0; w < 8; ++w) qd[w] = __shfl_sync(0xffffffffu, dw, w);
+      unsigned bd = 0xffffffffu, be = 0xffffffffu;             // least (distance, CSR position)
+      for_each_in_columns(cx0, cx1, lane,
+        [&](int ix, int& e_lo, int& e_hi) { e_lo = cs[ix * kPGridRows + cy0]; e_hi = cs[ix * kPGridRows + cy1 + 1]; },
+        [&](int e, int) {
+          const uint32_t meta = smeta[e];
+          const int idx = (int)(meta & 0xFFFFFFu), oct = (int)(meta >> 24);
+          const float2 pt = sxy[e];
+          if (!(fabsf(__fsub_rn(pt.x, u)) < radius && fabsf(__fsub_rn(pt.y, v)) < radius)) return;
+          if (oct < level - 1 || oct > level) return;
+          if (gate) {
+            const float ex = __fsub_rn(u, pt.x), ey = __fsub_rn(v, pt.y);
+            const float kr = sur[idx];
+            if (kr >= 0.f) {
+              const float er = __fsub_rn(ur, kr);
+              const float e2 = __fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(er, er));
+              if ((double)__fmul_rn(e2, a.inv_sigma2[oct]) > 7.8) return;
+            } else {
+              const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+              if ((double)__fmul_rn(e2, a.inv_sigma2[oct]) > 5.99) return;
+            }
+          }
+          const uint32_t* g = sdesc + (size_t)idx * 8;
+          const uint4 b0 = *reinterpret_cast<const uint4*>(g), b1 = *reinterpret_cast<const uint4*>(g + 4);
+          const unsigned d = __popc(qd[0] ^ b0.x) + __popc(qd[1] ^ b0.y) + __popc(qd[2] ^ b0.z) + __popc(qd[3] ^ b0.w) + __popc(qd[4] ^ b1.x) +
+                             __popc(qd[5] ^ b1.y) + __popc(qd[6] ^ b1.z) + __popc(qd[7] ^ b1.w);
+          if (d < bd || (d == bd && (unsigned)e < be)) { bd = d; be = (unsigned)e; }
+        });
+      const unsigned wd = __reduce_min_sync(0xffffffffu, bd);
+      const unsigned we = __reduce_min_sync(0xffffffffu, bd == wd ? be : 0xffffffffu);
+      if (lane == 0) a.best[mo + base + r] = (wd != 0xffffffffu && (int)wd <= a.th_dist) ? (int)(smeta[we] & 0xFFFFFFu) : -1;
+    }
+    __syncthreads();                                            // the block's windows are free again
+  }
 }
 
 // SearchBySim3's agreement check (src/ORBmatcher.cc:1303-1323): vnMatch1 / vnMatch2 are indexed by keypoint
@@ -581,7 +730,13 @@ int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
 }
 
 int launch_project_search(const ProjSearchArgs& a, cudaStream_t st) {
-  k_project_search<<<dim3((unsigned)((a.mcap + 127) / 128), (unsigned)a.n_problems), 128, 0, st>>>(a);
+  const size_t lat = ps_lat_bytes(a.cap, (a.mode & 8) != 0);
+  if (a.n_problems <= 148 && lat <= 200 * 1024 && a.cap < (1 << 24) && !getenv("ORBX_PROJ_SERIAL")) {
+    cudaFuncSetAttribute(k_project_search_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
+    k_project_search_lat<<<a.n_problems, kPsLatThreads, lat, st>>>(a);
+  } else {
+    k_project_search<<<dim3((unsigned)((a.mcap + 127) / 128), (unsigned)a.n_problems), 128, 0, st>>>(a);
+  }
   return 1;
 }
 int launch_scatter_matches(const int* best, const int* mp_index, const int* m, int mcap, int cap, int n_problems, int* vn, cudaStream_t st) {

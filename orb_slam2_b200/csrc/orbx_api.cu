@@ -1112,13 +1112,18 @@ orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* d
   CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds)); CU(sg.in(cell_start, cells, on_device, &a.cell_start)); CU(sg.in(cell_items, kc, on_device, &a.cell_items));
   CU(sg.in(kf_bounds, np * 4, on_device, &a.kf_bounds));
   // xf per problem: R1 t1 | R2 t2 (unused) | Ow
-  float* d_xf = nullptr;
-  CU(sg.alloc((void**)&d_xf, np * 27 * sizeof(float)));
-  CU(cudaMemsetAsync(d_xf, 0, np * 27 * sizeof(float), st));
-  const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-  CU(cudaMemcpy2DAsync(d_xf, 27 * sizeof(float), pose, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
-  CU(cudaMemcpy2DAsync(d_xf + 24, 27 * sizeof(float), Ow, 3 * sizeof(float), 3 * sizeof(float), np, kind, st));
-  a.xf = d_xf;
+  if (on_device) {
+    float* d_xf = nullptr;
+    CU(sg.alloc((void**)&d_xf, np * 27 * sizeof(float)));
+    CU(cudaMemsetAsync(d_xf, 0, np * 27 * sizeof(float), st));
+    CU(cudaMemcpy2DAsync(d_xf, 27 * sizeof(float), pose, 12 * sizeof(float), 12 * sizeof(float), np, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpy2DAsync(d_xf + 24, 27 * sizeof(float), Ow, 3 * sizeof(float), 3 * sizeof(float), np, cudaMemcpyDeviceToDevice, st));
+    a.xf = d_xf;
+  } else {                                                               // put together on the host: it rides in the call's one upload
+    std::vector<float> hx(np * 27, 0.f);
+    for (size_t q = 0; q < np; ++q) { std::memcpy(&hx[q * 27], pose + q * 12, 12 * sizeof(float)); std::memcpy(&hx[q * 27 + 24], Ow + q * 3, 3 * sizeof(float)); }
+    CU(sg.in(hx.data(), np * 27, 0, &a.xf));
+  }
   CU(sg.in(mp_valid, mc, on_device, &a.valid)); CU(sg.in(mp_xw, mc * 3, on_device, &a.xw)); CU(sg.in(mp_normal, mc * 3, on_device, &a.normal));
   CU(sg.in(mp_min_dist, mc, on_device, &a.dmin)); CU(sg.in(mp_max_dist, mc, on_device, &a.dmax)); CU(sg.in(mp_desc, mc * 32, on_device, &a.mp_desc));
   CU(sg.in(m, np, on_device, &a.m));
@@ -1153,39 +1158,46 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
   const size_t np = (size_t)n_pairs, kc = np * cap, mc = np * mcap, cells = np * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1);
   const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   const float* d_gb; CU(sg.in(grid_bounds, 6, on_device, &d_gb));
-  uint8_t* d_valid = nullptr; CU(sg.alloc((void**)&d_valid, mc)); CU(cudaMemsetAsync(d_valid, 1, mc, st));
-  float* d_zero = nullptr; CU(sg.alloc((void**)&d_zero, mc * 3 * sizeof(float))); CU(cudaMemsetAsync(d_zero, 0, mc * 3 * sizeof(float), st));
   int* d_vn[2]; int* d_best[2]; const int* d_idx[2]; const int* d_m[2];
   const int* d_n1; CU(sg.in(n1, np, on_device, &d_n1));
-  // pass 0: map points of keyframe 1 into keyframe 2 (R1w, t1w then sR21, t21); pass 1: the other way (R2w, t2w then sR12, t12)
+  CU(sg.alloc((void**)&d_vn[0], 2 * kc * 4)); d_vn[1] = d_vn[0] + kc;
+  CU(cudaMemsetAsync(d_vn[0], 0xFF, 2 * kc * 4, st));
+  // pass 0: map points of keyframe 1 into keyframe 2 (R1w, t1w then sR21, t21); pass 1: the other way (R2w, t2w then sR12, t12).
+  // Everything both passes read is staged first and goes up in one copy; then the five launches.
+  ProjSearchArgs pa[2];
   for (int pass = 0; pass < 2; ++pass) {
-    ProjSearchArgs a;
+    ProjSearchArgs& a = pa[pass];
     const bool fwd = pass == 0;
     CU(sg.in(fwd ? kps2 : kps1, kc, on_device, &a.kps)); CU(sg.in(fwd ? desc2 : desc1, kc * 32, on_device, &a.desc));
     a.u_right = nullptr; a.grid_bounds = d_gb;
     CU(sg.in(fwd ? cell_start2 : cell_start1, cells, on_device, &a.cell_start)); CU(sg.in(fwd ? cell_items2 : cell_items1, kc, on_device, &a.cell_items));
     CU(sg.in(fwd ? kf_bounds2 : kf_bounds1, np * 4, on_device, &a.kf_bounds));
-    float* d_xf = nullptr;
-    CU(sg.alloc((void**)&d_xf, np * 27 * sizeof(float)));
-    CU(cudaMemsetAsync(d_xf, 0, np * 27 * sizeof(float), st));
-    CU(cudaMemcpy2DAsync(d_xf, 27 * sizeof(float), fwd ? pose1 : pose2, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
-    CU(cudaMemcpy2DAsync(d_xf + 12, 27 * sizeof(float), xf + (fwd ? 12 : 0), 24 * sizeof(float), 12 * sizeof(float), np, kind, st));
-    a.xf = d_xf;
-    a.valid = d_valid; a.normal = d_zero;
+    if (on_device) {
+      float* d_xf = nullptr;
+      CU(sg.alloc((void**)&d_xf, np * 27 * sizeof(float)));
+      CU(cudaMemsetAsync(d_xf, 0, np * 27 * sizeof(float), st));
+      CU(cudaMemcpy2DAsync(d_xf, 27 * sizeof(float), fwd ? pose1 : pose2, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
+      CU(cudaMemcpy2DAsync(d_xf + 12, 27 * sizeof(float), xf + (fwd ? 12 : 0), 24 * sizeof(float), 12 * sizeof(float), np, kind, st));
+      a.xf = d_xf;
+    } else {                                                             // the 27 floats per pair put together on the host
+      std::vector<float> hx(np * 27, 0.f);
+      for (size_t q = 0; q < np; ++q) {
+        std::memcpy(&hx[q * 27], (fwd ? pose1 : pose2) + q * 12, 12 * sizeof(float));
+        std::memcpy(&hx[q * 27 + 12], xf + q * 24 + (fwd ? 12 : 0), 12 * sizeof(float));
+      }
+      CU(sg.in(hx.data(), np * 27, 0, &a.xf));
+    }
+    a.valid = nullptr; a.normal = nullptr;                               // every listed map point is valid; no viewing-angle test in this member
     CU(sg.in(fwd ? mp1_xw : mp2_xw, mc * 3, on_device, &a.xw)); CU(sg.in(fwd ? mp1_min_dist : mp2_min_dist, mc, on_device, &a.dmin));
     CU(sg.in(fwd ? mp1_max_dist : mp2_max_dist, mc, on_device, &a.dmax)); CU(sg.in(fwd ? mp1_desc : mp2_desc, mc * 32, on_device, &a.mp_desc));
     CU(sg.in(fwd ? m1 : m2, np, on_device, &d_m[pass])); a.m = d_m[pass];
     CU(sg.in(fwd ? mp1_index : mp2_index, mc, on_device, &d_idx[pass]));
     CU(sg.alloc((void**)&d_best[pass], mc * 4)); a.best = d_best[pass];
-    CU(sg.alloc((void**)&d_vn[pass], kc * 4)); CU(cudaMemsetAsync(d_vn[pass], 0xFF, kc * 4, st));
-    CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st));
+    if (pass == 0) CU(fetch_levels(a.scale, scale_factors, nlevels, on_device, st));
+    else std::memcpy(a.scale, pa[0].scale, sizeof(a.scale));
     for (int l = 0; l < kMaxLevels; ++l) a.inv_sigma2[l] = 1.f;
     a.n_problems = n_pairs; a.cap = cap; a.mcap = mcap; a.nlevels = nlevels; a.mode = 1 | 16; a.th_dist = 100;   // TH_HIGH
     a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy; a.bf = 0.f; a.log_scale = log_scale_factor; a.th = th;
-    CU(sg.upload());
-    g_launches += launch_project_search(a, st);
-    CU(sg.upload());
-    g_launches += launch_scatter_matches(d_best[pass], d_idx[pass], d_m[pass], mcap, cap, n_pairs, d_vn[pass], st);
   }
   Sim3AgreeArgs g;
   g.match1 = d_vn[0]; g.match2 = d_vn[1]; g.n1 = d_n1; g.cap = cap;
@@ -1193,6 +1205,10 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
   else { CU(sg.alloc((void**)&g.matches12, kc * 4)); CU(sg.alloc((void**)&g.nfound, np * 4)); }
   CU(cudaMemsetAsync(g.nfound, 0, np * 4, st));
   CU(sg.upload());
+  for (int pass = 0; pass < 2; ++pass) {
+    g_launches += launch_project_search(pa[pass], st);
+    g_launches += launch_scatter_matches(d_best[pass], d_idx[pass], d_m[pass], mcap, cap, n_pairs, d_vn[pass], st);
+  }
   g_launches += launch_sim3_agree(g, n_pairs, st);
   CU(cudaGetLastError());
   if (!on_device) {
@@ -1225,11 +1241,17 @@ orbx_status orbx_search_projection_ordered_batch(const orbx_keypoint* kps_un, co
   CU(sg.in(kps_un, kc, on_device, &a.kps)); CU(sg.in(desc, kc * 32, on_device, &a.desc)); CU(sg.in(n, np, on_device, &a.n));
   CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds)); CU(sg.in(cell_start, cells, on_device, &a.cell_start)); CU(sg.in(cell_items, kc, on_device, &a.cell_items));
   CU(sg.in(target_bounds, np * 4, on_device, &a.tgt_bounds));
-  float* d_xf = nullptr;
-  CU(sg.alloc((void**)&d_xf, np * 15 * sizeof(float)));
-  CU(cudaMemcpy2DAsync(d_xf, 15 * sizeof(float), pose, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
-  CU(cudaMemcpy2DAsync(d_xf + 12, 15 * sizeof(float), Ow, 3 * sizeof(float), 3 * sizeof(float), np, kind, st));
-  a.xf = d_xf;
+  if (on_device) {
+    float* d_xf = nullptr;
+    CU(sg.alloc((void**)&d_xf, np * 15 * sizeof(float)));
+    CU(cudaMemcpy2DAsync(d_xf, 15 * sizeof(float), pose, 12 * sizeof(float), 12 * sizeof(float), np, kind, st));
+    CU(cudaMemcpy2DAsync(d_xf + 12, 15 * sizeof(float), Ow, 3 * sizeof(float), 3 * sizeof(float), np, kind, st));
+    a.xf = d_xf;
+  } else {                                                               // put together on the host: it rides in the call's one upload
+    std::vector<float> hx(np * 15, 0.f);
+    for (size_t q = 0; q < np; ++q) { std::memcpy(&hx[q * 15], pose + q * 12, 12 * sizeof(float)); std::memcpy(&hx[q * 15 + 12], Ow + q * 3, 3 * sizeof(float)); }
+    CU(sg.in(hx.data(), np * 15, 0, &a.xf));
+  }
   CU(sg.in(occupied, kc, on_device, &a.occupied));
   CU(sg.in(mp_valid, mc, on_device, &a.valid)); CU(sg.in(mp_xw, mc * 3, on_device, &a.xw)); CU(sg.in(mp_normal, mc * 3, on_device, &a.normal));
   CU(sg.in(mp_min_dist, mc, on_device, &a.dmin)); CU(sg.in(mp_max_dist, mc, on_device, &a.dmax)); CU(sg.in(mp_desc, mc * 32, on_device, &a.mp_desc));

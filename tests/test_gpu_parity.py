@@ -368,11 +368,26 @@ def test_knn_ratio_crowded_neighbourhoods(gx, oracle, th, ratio, strict):
         assert n1 == r[1] and np.array_equal(g, r[0]), nb
 
 
+FORMS = pytest.mark.parametrize("form", ["latency", "throughput"])
+
+
+def _pick_form(monkeypatch, form):
+    """The order-dependent matchers have two device forms: the latency form (a 1024-thread CTA per problem, a few problems per
+    call - what these single-problem cases take by default) and the throughput form (a warp or a small CTA per problem, chosen
+    above ~100 problems per call).  ORBX_PROJ_SERIAL / ORBX_BOW_SERIAL make a small call take the throughput form."""
+    if form == "throughput":
+        monkeypatch.setenv("ORBX_PROJ_SERIAL", "1"); monkeypatch.setenv("ORBX_BOW_SERIAL", "1")
+    else:
+        monkeypatch.delenv("ORBX_PROJ_SERIAL", raising=False); monkeypatch.delenv("ORBX_BOW_SERIAL", raising=False)
+
+
+@FORMS
 @pytest.mark.parametrize("th", [1.0, 3.0])
-def test_search_by_projection_local_map(gx, oracle, th):
+def test_search_by_projection_local_map(gx, oracle, th, monkeypatch, form):
     """SearchByProjection(Frame, MapPoints): map points come from a second, shifted view of the scene
     (their descriptors, octaves and noisy predicted positions), some already-occupied keypoints, some
     points out of view, stereo uRight checks on."""
+    _pick_form(monkeypatch, form)
     cfg = synth.KITTI
     w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
     G = _ext(gx, w, h, nf, batch=2)
@@ -410,10 +425,12 @@ def test_search_by_projection_local_map(gx, oracle, th):
         assert all(v == rn for v in ns) and all(np.array_equal(x, ras) for x in ass) and all(np.array_equal(x, rfo) for x in fos)
 
 
+@FORMS
 @pytest.mark.parametrize("mode,th,ori", [(0, 15.0, True), (1, 7.0, True), (2, 15.0, False)])
-def test_search_by_projection_motion_model(gx, oracle, mode, th, ori):
+def test_search_by_projection_motion_model(gx, oracle, mode, th, ori, monkeypatch, form):
     """SearchByProjection(Current, Last): last-frame stereo points are back-projected to 3-D, moved by a
     small pose change and searched for in a noisy copy of the same view."""
+    _pick_form(monkeypatch, form)
     cfg = synth.KITTI
     w, h, nf, bf, fx = cfg["w"], cfg["h"], cfg["nfeatures"], cfg["bf"], cfg["fx"]
     fy, cx, cy = fx, 607.19, 185.22                              # Examples/Stereo/KITTI00-02.yaml
@@ -716,10 +733,12 @@ def test_cuda_path_reproduces_reference_goldens(gx):
         assert sha(np.concatenate([np.array([len(x)], np.int32) for x in hits] + hits)) == case["hits_sha256"]
 
 
-def test_cuda_keyframe_searches_reproduce_reference(gx):
+@FORMS
+def test_cuda_keyframe_searches_reproduce_reference(gx, monkeypatch, form):
     """K7 / K8 / K9 / K12 / K13 / K14 / K15 against what the REFERENCE's ORBmatcher.cc / MapPoint.cc produced on real KeyFrames
     and MapPoints (tests/golden/ref_kf_*.npz, ref_slam.json written by oracle/_ref/orbref_slam): frames, stereo depth and
     feature-vector nodes come from the CUDA path itself, only the MapPoint / isInFrustum fields come from the fixture."""
+    _pick_form(monkeypatch, form)
     import hashlib, importlib.util, os
     spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
     kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
@@ -780,9 +799,11 @@ def test_cuda_keyframe_searches_reproduce_reference(gx):
     assert hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest() == kc.GOLD["distinct"]["chosen_sha256"]
 
 
-def test_cuda_fuse_and_sim3_reproduce_reference(gx):
+@FORMS
+def test_cuda_fuse_and_sim3_reproduce_reference(gx, monkeypatch, form):
     """K16 against ORBmatcher::Fuse (search) and ORBmatcher::SearchBySim3 of the REFERENCE on real KeyFrames and MapPoints
     (tests/golden/ref_kf_*.npz): frames, stereo, the feature grid (K10) come from the CUDA path, MapPoint fields from the fixture."""
+    _pick_form(monkeypatch, form)
     import importlib.util, os
     spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
     kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
