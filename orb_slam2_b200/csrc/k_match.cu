@@ -811,7 +811,7 @@ int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
   // latency mode (a few frames per call): one warp per SM anyway, so spend the shared memory on the descriptors;
   // throughput mode keeps the small footprint (6 CTAs per SM)
   const size_t par = frame_stage_bytes(a.cap);
-  if (a.n_pairs <= 148 && par <= 200 * 1024 && !getenv("ORBX_PROJ_SERIAL")) {
+  if (par <= 200 * 1024 && !getenv("ORBX_PROJ_SERIAL")) {               // also for batches: 57 us of one SM per frame against 850 us of one warp
     cudaFuncSetAttribute(k_search_projection_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
     k_search_projection_par<<<a.n_pairs, kParThreads, par, st>>>(a);
   } else if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
@@ -1205,7 +1205,7 @@ int launch_search_projection_frame(const ProjFrameArgs& a, cudaStream_t st) {
   const size_t base = (size_t)a.cap * 12 + (kGridCells + 2) * sizeof(int);
   const size_t with_desc = ((base + 15) & ~(size_t)15) + (size_t)a.cap * 32;
   const size_t par = frame_stage_bytes(a.cap) + (((size_t)a.lcap * 2 + 15) & ~(size_t)15) + (size_t)a.lcap * 4;
-  if (a.n_pairs <= 148 && par <= 200 * 1024 && a.lcap <= 65535 && !getenv("ORBX_PROJ_SERIAL")) {    // latency mode, see launch_search_projection
+  if (par <= 200 * 1024 && a.lcap <= 65535 && !getenv("ORBX_PROJ_SERIAL")) {    // see launch_search_projection
     cudaFuncSetAttribute(k_search_projection_frame_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
     k_search_projection_frame_par<<<a.n_pairs, kParThreads, par, st>>>(a);
   } else if (a.n_pairs <= 148 && with_desc <= 200 * 1024) {
@@ -1645,9 +1645,9 @@ int launch_search_by_bow(const BowArgs& a, cudaStream_t st) {
   int capPad = 32;
   while (capPad < a.cap) capPad <<= 1;
   const size_t lat = bow_lat_bytes(a.cap, capPad);
-  // the latency form pays when the GPU has a few pairs (the SLAM call pattern); with a hundred pairs per call every SM is
-  // busy with other pairs' walks anyway, and the small CTAs of the throughput form pack six to an SM
-  if (a.n_pairs <= 64 && lat <= 200 * 1024 && !getenv("ORBX_BOW_SERIAL")) {
+  // the 1024-thread form whenever its shared memory fits: it finishes a pair in a fifteenth of the small-CTA form's time, which
+  // is worth more than the two small CTAs an SM could hold instead (the small form stays for cap > ~3300 and for A/B tests)
+  if (lat <= 200 * 1024 && !getenv("ORBX_BOW_SERIAL")) {
     cudaFuncSetAttribute(k_search_by_bow_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
     k_search_by_bow_lat<<<a.n_pairs, kBowLatThreads, lat, st>>>(a, capPad);
     return 1;
@@ -1906,7 +1906,7 @@ int launch_search_triangulation(const TriArgs& a, cudaStream_t st) {
   int capPad = 32;
   while (capPad < a.cap) capPad <<= 1;
   const size_t lat = tri_lat_bytes(a.cap, capPad);
-  if (a.n_pairs <= 64 && lat <= 200 * 1024 && !getenv("ORBX_BOW_SERIAL")) {
+  if (lat <= 200 * 1024 && !getenv("ORBX_BOW_SERIAL")) {
     cudaFuncSetAttribute(k_search_triangulation_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
     k_search_triangulation_lat<<<a.n_pairs, kTriLatThreads, lat, st>>>(a, capPad);
     return 1;

@@ -720,7 +720,7 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
 
 int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
   const size_t smem = (size_t)((a.cap + 31) / 32) * 4, par = ord_stage_bytes(a.cap) + (size_t)a.mcap * 2;
-  if (a.n_problems <= 148 && par <= 200 * 1024 && a.cap <= 65536 && a.mcap <= 65536 && !getenv("ORBX_PROJ_SERIAL")) {
+  if (par <= 200 * 1024 && a.cap <= 65536 && a.mcap <= 65536 && !getenv("ORBX_PROJ_SERIAL")) {
     cudaFuncSetAttribute(k_project_match_ordered_par, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par);
     k_project_match_ordered_par<<<a.n_problems, kOrdParThreads, par, st>>>(a);
   } else {
@@ -731,7 +731,7 @@ int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
 
 int launch_project_search(const ProjSearchArgs& a, cudaStream_t st) {
   const size_t lat = ps_lat_bytes(a.cap, (a.mode & 8) != 0);
-  if (a.n_problems <= 148 && lat <= 200 * 1024 && a.cap < (1 << 24) && !getenv("ORBX_PROJ_SERIAL")) {
+  if (lat <= 200 * 1024 && a.cap < (1 << 24) && !getenv("ORBX_PROJ_SERIAL")) {
     cudaFuncSetAttribute(k_project_search_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
     k_project_search_lat<<<a.n_problems, kPsLatThreads, lat, st>>>(a);
   } else {

@@ -373,8 +373,8 @@ FORMS = pytest.mark.parametrize("form", ["latency", "throughput"])
 
 def _pick_form(monkeypatch, form):
     """The order-dependent matchers have two device forms: the latency form (a 1024-thread CTA per problem, a few problems per
-    call - what these single-problem cases take by default) and the throughput form (a warp or a small CTA per problem, chosen
-    above ~100 problems per call).  ORBX_PROJ_SERIAL / ORBX_BOW_SERIAL make a small call take the throughput form."""
+    call or many) and the small form (a warp or a 128-thread CTA per problem, taken
+    when a problem's arrays do not fit the 1024-thread form's shared memory).  ORBX_PROJ_SERIAL / ORBX_BOW_SERIAL select it."""
     if form == "throughput":
         monkeypatch.setenv("ORBX_PROJ_SERIAL", "1"); monkeypatch.setenv("ORBX_BOW_SERIAL", "1")
     else:
@@ -579,10 +579,12 @@ def _vocab_nodes(desc, words):
     return (d.argmin(1) * 37 + 5).astype(np.int32)
 
 
+@FORMS
 @pytest.mark.parametrize("strict,ratio,ori", [(True, 0.75, True), (False, 0.7, True), (False, 0.9, False)])
-def test_search_by_bow_with_vocabulary_buckets(gx, oracle, strict, ratio, ori):
+def test_search_by_bow_with_vocabulary_buckets(gx, oracle, strict, ratio, ori, monkeypatch, form):
     """K12: SearchByBoW(KF,KF) / (KF,Frame) over per-node buckets, in the reference's node / index
     order, with invalid map points on both sides, nodes present on one side only, ragged pairs and an empty side."""
+    _pick_form(monkeypatch, form)
     w, h, nf = 1241, 376, 2000
     G = _ext(gx, w, h, nf)
     rng = np.random.default_rng(99)
@@ -606,7 +608,7 @@ def test_search_by_bow_with_vocabulary_buckets(gx, oracle, strict, ratio, ori):
     for p in range(4):
         assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), (p, nm[p], refs[p][1])
     assert refs[0][1] > 50 and refs[2][1] > 50
-    # the same pairs 17 times over in one call: above 64 pairs the throughput form of the kernel runs instead of the latency form
+    # the same pairs 17 times over in one call (more CTAs than one wave of the 1024-thread form)
     nm2, m2 = gx.ORBmatcher(ratio, ori).SearchByBoWNodes(sidesA * 17, sidesB * 17, strict=strict)
     for q in range(68):
         assert nm2[q] == refs[q % 4][1] and np.array_equal(m2[q], refs[q % 4][0]), (q, nm2[q], refs[q % 4][1])
@@ -636,11 +638,13 @@ def test_distinctive_descriptors(gx, oracle):
     assert best[-2] == -1 and best[-3] == 0
 
 
+@FORMS
 @pytest.mark.parametrize("only_stereo,ori", [(False, True), (True, True), (False, False)])
-def test_search_for_triangulation(gx, oracle, only_stereo, ori):
+def test_search_for_triangulation(gx, oracle, only_stereo, ori, monkeypatch, form):
     """K14: SearchForTriangulation + CheckDistEpipolarLine.  The second keyframe is a translated
     view, so F12 = [t]x of the image translation makes true matches lie on their epipolar lines; the epipole is put
     inside the image so that the mono-mono exclusion zone fires; stereo / mono features and existing map points mixed."""
+    _pick_form(monkeypatch, form)
     w, h, nf = 1241, 376, 2000
     G = _ext(gx, w, h, nf)
     scale, sigma2 = np.asarray(G.GetScaleFactors(), np.float32), np.asarray(G.GetScaleSigmaSquares(), np.float32)
@@ -665,7 +669,7 @@ def test_search_for_triangulation(gx, oracle, only_stereo, ori):
     for p in range(3):
         assert nm[p] == refs[p][1] and np.array_equal(m12[p], refs[p][0]), (p, nm[p], refs[p][1])
     assert refs[0][1] > (5 if only_stereo else 30)
-    # 66 pairs in one call: above 64 the throughput form (128 threads per pair) runs instead of the latency form
+    # 66 pairs in one call
     nm2, m2 = gx.ORBmatcher(0.6, ori).SearchForTriangulation(kf1 * 22, kf2 * 22, F12 * 22, poses * 22, Cws * 22, cams * 22, scale, sigma2, bOnlyStereo=only_stereo)
     for q in range(66):
         assert nm2[q] == refs[q % 3][1] and np.array_equal(m2[q], refs[q % 3][0]), (q, nm2[q], refs[q % 3][1])
