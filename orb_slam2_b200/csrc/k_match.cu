@@ -186,50 +186,73 @@ __device__ __forceinline__ int ham256_csa(const uint32_t (&q)[8], const uint4 b0
   return (__popc(s2) + __popc(x7)) + 2 * __popc(t0) + 4 * __popc(f0);
 }
 
+// FUSED: the query block that finishes a pair's lists last goes on to resolve the pair (its B descriptors are already in this
+// CTA's shared memory), so the ordered part of one pair runs beside the distance work of the others instead of after all of it.
+template <bool FUSED> __device__ __forceinline__ void knn_resolve_tail(const KnnArgs& a, uint32_t sentinel, int p, uint8_t* smem);
+
+template <bool FUSED>
 __global__ void __launch_bounds__(kKnnThreads) k_knn_topk(KnnArgs a, int qblocks, uint32_t sentinel) {
   extern __shared__ __align__(16) uint8_t smem[];
   uint4* Bs = reinterpret_cast<uint4*>(smem);                  // [nB][2]
+  __shared__ int s_last;
   const int p = blockIdx.x / qblocks, qb = blockIdx.x - p * qblocks, tid = threadIdx.x;
   const int nA = a.nA[p], nB = a.nB[p];
-  if (qb * kKnnThreads >= nA) return;
+  if (qb * kKnnThreads >= nA) {
+    if (FUSED && nA == 0 && qb == 0 && tid == 0) a.nm[p] = 0;  // nothing to resolve
+    return;
+  }
   const uint4* dB = reinterpret_cast<const uint4*>(a.dB + (size_t)p * a.cap * 32);
   for (int idx = tid; idx < nB * 2; idx += kKnnThreads) Bs[idx] = __ldg(dB + idx);
   __syncthreads();
   const int i = qb * kKnnThreads + tid;
-  if (i >= nA) return;
-  uint32_t q[8];
-  {
-    const uint4* dA = reinterpret_cast<const uint4*>(a.dA + ((size_t)p * a.cap + i) * 32);
-    const uint4 q0 = __ldg(dA), q1 = __ldg(dA + 1);
-    q[0] = q0.x; q[1] = q0.y; q[2] = q0.z; q[3] = q0.w; q[4] = q1.x; q[5] = q1.y; q[6] = q1.z; q[7] = q1.w;
-  }
-  uint32_t top[kTopK];
+  if (i < nA) {
+    uint32_t q[8];
+    {
+      const uint4* dA = reinterpret_cast<const uint4*>(a.dA + ((size_t)p * a.cap + i) * 32);
+      const uint4 q0 = __ldg(dA), q1 = __ldg(dA + 1);
+      q[0] = q0.x; q[1] = q0.y; q[2] = q0.z; q[3] = q0.w; q[4] = q1.x; q[5] = q1.y; q[6] = q1.z; q[7] = q1.w;
+    }
+    uint32_t top[kTopK];
 #pragma unroll
-  for (int k = 0; k < kTopK; ++k) top[k] = sentinel;
+    for (int k = 0; k < kTopK; ++k) top[k] = sentinel;
 #pragma unroll 2
-  for (int j = 0; j < nB; ++j) {
-    const uint32_t key = ((uint32_t)ham256_csa(q, Bs[2 * j], Bs[2 * j + 1]) << 16) + (uint32_t)j;
-    if (key < top[kTopK - 1]) {                                // rare: only neighbours closer than the sentinel
-      top[kTopK - 1] = key;
+    for (int j = 0; j < nB; ++j) {
+      const uint32_t key = ((uint32_t)ham256_csa(q, Bs[2 * j], Bs[2 * j + 1]) << 16) + (uint32_t)j;
+      if (key < top[kTopK - 1]) {                              // rare: only neighbours closer than the sentinel
+        top[kTopK - 1] = key;
 #pragma unroll
-      for (int k = kTopK - 1; k > 0; --k) {
-        const uint32_t lo = min(top[k - 1], top[k]), hi = max(top[k - 1], top[k]);
-        top[k - 1] = lo; top[k] = hi;
+        for (int k = kTopK - 1; k > 0; --k) {
+          const uint32_t lo = min(top[k - 1], top[k]), hi = max(top[k - 1], top[k]);
+          top[k - 1] = lo; top[k] = hi;
+        }
       }
     }
+    uint4* out = reinterpret_cast<uint4*>(a.topk + ((size_t)p * a.cap + i) * kTopK);
+    out[0] = make_uint4(top[0], top[1], top[2], top[3]);
+    out[1] = make_uint4(top[4], top[5], top[6], top[7]);
   }
-  uint4* out = reinterpret_cast<uint4*>(a.topk + ((size_t)p * a.cap + i) * kTopK);
-  out[0] = make_uint4(top[0], top[1], top[2], top[3]);
-  out[1] = make_uint4(top[4], top[5], top[6], top[7]);
+  if (!FUSED) return;
+  __threadfence();                                             // this block's lists are visible device-wide before its ticket
+  __syncthreads();
+  if (tid == 0) s_last = atomicAdd(a.done + p, 1) == (nA + kKnnThreads - 1) / kKnnThreads - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  knn_resolve_tail<FUSED>(a, sentinel, p, smem);
 }
 
-__global__ void __launch_bounds__(32) k_knn_resolve(KnnArgs a, uint32_t sentinel) {
-  extern __shared__ __align__(16) uint8_t smem[];
+constexpr int kKnnResolveThreads = 128;
+// The ordered part of K7 for pair p, by the whole CTA (any size >= 32).  BSM: the pair's B descriptors are at the start of the
+// dynamic shared memory ([nB][2] uint4) - the exact re-scans then cost no global round trip.
+template <bool BSM>
+__device__ __forceinline__ void knn_resolve_pair(const KnnArgs& a, uint32_t sentinel, int p, uint8_t* smem, bool stage_b) {
   const int uwords = (a.cap + 31) / 32;
-  uint32_t* used = reinterpret_cast<uint32_t*>(smem);          // bit j: B feature j already matched (vbMatched2)
-  int* claim = reinterpret_cast<int*>(used + uwords);          // [cap] lowest lane of the current group that wants B feature j
+  uint4* Bsm = reinterpret_cast<uint4*>(smem);                 // BSM: [nB][2] B descriptors for the exact re-scans
+  uint32_t* used = reinterpret_cast<uint32_t*>(smem + (BSM ? (size_t)a.cap * 32 : 0));   // bit j: B feature j already matched (vbMatched2)
+  int* claim = reinterpret_cast<int*>(used + uwords);          // [cap] order_round's tags: who wants B feature j in the round being resolved
   __shared__ int s_hist[kHisto];
-  const int p = blockIdx.x, lane = threadIdx.x;
+  __shared__ int s_nm;
+  const int tid = threadIdx.x, lane = tid & 31, nthr = blockDim.x;
   const int nA = a.nA[p], nB = a.nB[p];
   const uint32_t* dA = reinterpret_cast<const uint32_t*>(a.dA + (size_t)p * a.cap * 32);
   const uint32_t* dB = reinterpret_cast<const uint32_t*>(a.dB + (size_t)p * a.cap * 32);
@@ -237,115 +260,170 @@ __global__ void __launch_bounds__(32) k_knn_resolve(KnnArgs a, uint32_t sentinel
   const float* angB = a.angB + (size_t)p * a.cap;
   const uint4* tk = reinterpret_cast<const uint4*>(a.topk + (size_t)p * a.cap * kTopK);
   int* m12 = a.m12 + (size_t)p * a.cap;
-  for (int w = lane; w < uwords; w += 32) used[w] = 0u;
-  for (int j = lane; j < a.cap; j += 32) claim[j] = 32;
-  if (lane < kHisto) s_hist[lane] = 0;
-  __syncwarp();
+  // the whole CTA sets up (and, at the end, does the rotation check); the ordered part in between belongs to warp 0
+  ORBX_CLK(c0);
+  for (int w = tid; w < uwords; w += nthr) used[w] = 0u;
+  for (int j = tid; j < a.cap; j += nthr) claim[j] = 0;                                // order_round's tags
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (BSM && stage_b) {
+    const uint4* src = reinterpret_cast<const uint4*>(dB);
+    for (int i = tid; i < nB * 2; i += nthr) Bsm[i] = __ldg(src + i);
+  }
+  __syncthreads();
+  if (tid < 32) {
   const int far = min((int)(sentinel >> 16), 256);             // stands for "at least the sentinel distance, or none"
-  int nm = 0;
-  // Queries are taken 32 at a time, one per lane, and decided together; a lane's decision stands if no
-  // earlier lane of the group took a B feature that is on its list.  The group commits up to the first lane
-  // for which that fails (or whose list is exhausted), repairs that lane, and goes on from there, so the
-  // outcome is the one of the index-ordered loop of the reference.
+  int nm = 0, epoch = 0;
+  ORBX_STAT(int dbg_it = 0; int dbg_rs = 0; long long dbg_rc = 0;)
+  ORBX_CLK(c1);
+  // Queries are taken 32 at a time, one per lane, and decided together (ordered.cuh): a lane's best and second best are the
+  // first two entries of its list that no earlier query has matched; the lanes iterate to the fixpoint of that rule, commit
+  // together, and a lane whose full list has fewer than two free entries left is re-scanned exactly, alone, before the
+  // lanes after it go round again - the outcome is the one of the index-ordered loop of the reference.
   uint4 n0 = make_uint4(sentinel, sentinel, sentinel, sentinel), n1 = n0;
-  if (lane < nA) { n0 = __ldg(tk + 2 * lane); n1 = __ldg(tk + 2 * lane + 1); }
+  if (lane < nA) { n0 = __ldcg(tk + 2 * lane); n1 = __ldcg(tk + 2 * lane + 1); }      // written by other CTAs of this launch: L2, not the read-only path
   for (int i0 = 0; i0 < nA; i0 += 32) {
     const int i = i0 + lane;
     const bool active = i < nA;
-    const uint32_t key[kTopK] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
-    if (i + 32 < nA) { n0 = __ldg(tk + 2 * (i + 32)); n1 = __ldg(tk + 2 * (i + 32) + 1); }
-    const bool full = key[kTopK - 1] < sentinel;               // sorted: the last entry is valid iff all are
-    int start = 0;
-    while (true) {
-      const bool eval = active && lane >= start;
-      int cnt = 0, best = 256, bi = 0, sec = 256;
-      uint32_t freem = 0u;
-      if (eval) {
+    const uint32_t raw[kTopK] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+    if (i + 32 < nA) { n0 = __ldcg(tk + 2 * (i + 32)); n1 = __ldcg(tk + 2 * (i + 32) + 1); }
+    const bool full = raw[kTopK - 1] < sentinel;               // sorted: the last entry is valid iff all are
+    uint32_t key[kTopK];
 #pragma unroll
-        for (int k = 0; k < kTopK; ++k) {
-          const uint32_t j = key[k] & 0xffffu;
-          if (key[k] < sentinel && ((used[j >> 5] >> (j & 31)) & 1u) == 0u) {
-            freem |= 1u << k;
-            if (cnt == 0) { best = (int)(key[k] >> 16); bi = (int)j; }
+    for (int k = 0; k < kTopK; ++k) key[k] = (active && raw[k] < sentinel) ? raw[k] : kNoKey;
+    uint32_t todo = __ballot_sync(0xffffffffu, active);
+    int mine = -1;                                             // this lane's m12 entry
+    while (todo) {
+      const bool live = (todo >> lane) & 1u;
+      unsigned hitP = 0u;
+#pragma unroll
+      for (int k = 0; k < kTopK; ++k)
+        if (key[k] != kNoKey && ((used[(key[k] & 0xffffu) >> 5] >> (key[k] & 31u)) & 1u)) hitP |= 1u << k;
+      bool pass = false, starved = false;
+      int bi = -1;
+      ORBX_STAT(dbg_it +=) order_round(key, hitP, claim, epoch, lane, [&](unsigned hit) {
+        int cnt = 0, best = 256, sec = 256;
+        bi = -1;
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k)
+          if (key[k] != kNoKey && !((hit >> k) & 1u)) {
+            if (cnt == 0) { best = (int)(key[k] >> 16); bi = (int)(key[k] & 0xffffu); }
             else if (cnt == 1) sec = (int)(key[k] >> 16);
             ++cnt;
           }
-        }
-      }
-      const bool rescan = eval && cnt < 2 && full;              // the list cannot tell best and second best any more
-      if (cnt == 1 && !full) sec = far;                         // every B below the sentinel distance was on the list
-      const bool pass = eval && !rescan && cnt > 0 && (a.strict ? best < a.th : best <= a.th) &&
-                        (float)best < __fmul_rn(a.ratio, (float)sec);
-      if (pass) atomicMin(&claim[bi], lane);
-      __syncwarp();
-      bool conflict = false;
-      if (eval) {
-#pragma unroll
-        for (int k = 0; k < kTopK; ++k)
-          if (((freem >> k) & 1u) && claim[key[k] & 0xffffu] < lane) conflict = true;
-      }
-      const uint32_t stop = __ballot_sync(0xffffffffu, conflict || rescan);
-      const int first = stop ? __ffs((int)stop) - 1 : 32;
-      __syncwarp();
-      if (pass) claim[bi] = 32;
-      if (eval && lane < first) {
-        m12[i] = pass ? bi : -1;
+        starved = live && cnt < 2 && full;                      // the list cannot tell best and second best any more
+        if (cnt == 1 && !full) sec = far;                       // every B below the sentinel distance was on the list
+        pass = live && !starved && cnt > 0 && (a.strict ? best < a.th : best <= a.th) && (float)best < __fmul_rn(a.ratio, (float)sec);
+        return pass ? bi : -1;
+      });
+      const uint32_t sm = __ballot_sync(0xffffffffu, starved);
+      const int jstar = sm ? __ffs((int)sm) - 1 : 32;
+      if (live && lane < jstar) {
+        mine = pass ? bi : -1;
         if (pass) { atomicOr(&used[bi >> 5], 1u << (bi & 31)); ++nm; }
       }
       __syncwarp();
-      if (first == 32) break;
-      start = first;
-      if (__shfl_sync(0xffffffffu, (int)rescan, first)) {       // exact rescan of query i0 + first (src/ORBmatcher.cc:574-594)
-        const int iq = i0 + first;
+      if (!sm) break;
+      {                                                         // exact rescan of query i0 + jstar (src/ORBmatcher.cc:574-594)
+        ORBX_STAT(++dbg_rs;)
+        ORBX_CLK(r0);
+        const int iq = i0 + jstar;
         uint32_t qd[8];
 #pragma unroll
         for (int w = 0; w < 8; ++w) qd[w] = __ldg(dA + (size_t)iq * 8 + w);
         unsigned b1 = 256u << 16;
         int b2 = 256;
-        for (int jj = lane; jj < nB; jj += 32) {
-          if ((used[jj >> 5] >> (jj & 31)) & 1u) continue;
-          uint32_t bd[8];
-#pragma unroll
-          for (int w = 0; w < 8; ++w) bd[w] = __ldg(dB + (size_t)jj * 8 + w);
-          const int d = ham8(qd, bd);
+        auto take = [&](int d, int jj) {                        // first least distance wins (ascending jj per lane, lanes merged by key)
           const unsigned kk = ((unsigned)d << 16) | (unsigned)jj;
           if (d < (int)(b1 >> 16)) { b2 = (int)(b1 >> 16); b1 = kk; }
           else if (d < b2) b2 = d;
+        };
+        if (BSM) {
+          // four B features per lane and trip, their loads issued together: the walk is one warp's latency chain
+          for (int j0 = lane; j0 < nB; j0 += 128) {
+            int d[4]; bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int jj = j0 + 32 * u;
+              ok[u] = jj < nB && !((used[jj >> 5] >> (jj & 31)) & 1u);
+              const int js = jj < nB ? jj : 0;
+              d[u] = ham256_csa(qd, Bsm[2 * js], Bsm[2 * js + 1]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) if (ok[u]) take(d[u], j0 + 32 * u);
+          }
+        } else {
+          for (int jj = lane; jj < nB; jj += 32) {
+            if ((used[jj >> 5] >> (jj & 31)) & 1u) continue;
+            uint32_t bd[8];
+#pragma unroll
+            for (int w = 0; w < 8; ++w) bd[w] = __ldg(dB + (size_t)jj * 8 + w);
+            take(ham8(qd, bd), jj);
+          }
         }
         const unsigned wmin = __reduce_min_sync(0xffffffffu, b1);
         const int rsec = (int)__reduce_min_sync(0xffffffffu, (unsigned)(b1 == wmin ? b2 : (int)(b1 >> 16)));
         const int rbest = (int)(wmin >> 16), rbi = (int)(wmin & 0xffffu);
         const bool rpass = (a.strict ? rbest < a.th : rbest <= a.th) && (float)rbest < __fmul_rn(a.ratio, (float)rsec);
-        if (lane == first) {
-          m12[iq] = rpass ? rbi : -1;
-          if (rpass) { used[rbi >> 5] |= 1u << (rbi & 31); ++nm; }
+        if (lane == jstar) {
+          mine = rpass ? rbi : -1;
+          if (rpass) { atomicOr(&used[rbi >> 5], 1u << (rbi & 31)); ++nm; }
         }
         __syncwarp();
-        start = first + 1;
+        ORBX_CLK(r1);
+        ORBX_STAT(dbg_rc += r1 - r0;)
       }
+      todo &= ~((2u << jstar) - 1u);
     }
+    if (active) m12[i] = mine;                                  // one coalesced store per group
   }
   nm = __reduce_add_sync(0xffffffffu, nm);
-  __syncwarp();
-  if (a.checkOri) {                                            // rotation consistency, src/ORBmatcher.cc:607-652
-    for (int i = lane; i < nA; i += 32) {
-      const int m = m12[i];
-      if (m >= 0) atomicAdd(&s_hist[rot_bin(angA[i], angB[m])], 1);
+  if (lane == 0) s_nm = nm;
+  ORBX_CLK(c2);
+  ORBX_STAT(if (lane == 0 && p == 0) printf("K7 resolve pair 0: setup %lld, ordered %lld cycles: %d queries, %d fixpoint iterations, %d re-scans in %lld cycles\n", c1 - c0, c2 - c1, nA, dbg_it, dbg_rs, dbg_rc);)
+  }   // warp 0
+  __syncthreads();
+  if (a.checkOri) {                                            // rotation consistency, src/ORBmatcher.cc:607-652, whole CTA
+    int mybin[64];
+    const bool keep = nA <= 64 * nthr;            // bins remembered in registers for the usual sizes, recomputed otherwise
+    int r = 0;
+    for (int base = 0; base < nA; base += nthr, ++r) {
+      const int i = base + tid;
+      const int m = i < nA ? m12[i] : -1;
+      const unsigned act = __ballot_sync(0xffffffffu, m >= 0);
+      int b = -1;
+      if (m >= 0) {                                            // one atomic per distinct bin of the warp
+        b = rot_bin(angA[i], angB[m]);
+        const unsigned peers = __match_any_sync(act, b);
+        if (lane == __ffs((int)peers) - 1) atomicAdd(&s_hist[b], __popc(peers));
+      }
+      if (keep) mybin[r] = b;
     }
-    __syncwarp();
+    __syncthreads();
     int k_a, k_b, k_c;
     three_maxima(s_hist, k_a, k_b, k_c);
     int drop = 0;
-    for (int i = lane; i < nA; i += 32) {
-      const int m = m12[i];
-      if (m >= 0) {
-        const int b = rot_bin(angA[i], angB[m]);
-        if (b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
-      }
+    r = 0;
+    for (int i = tid; i < nA; i += nthr, ++r) {
+      int b;
+      if (keep) b = mybin[r];
+      else { const int m = m12[i]; b = m >= 0 ? rot_bin(angA[i], angB[m]) : -1; }
+      if (b >= 0 && b != k_a && b != k_b && b != k_c) { m12[i] = -1; ++drop; }
     }
-    nm -= __reduce_add_sync(0xffffffffu, drop);
+    if (drop) atomicSub(&s_nm, drop);
+    __syncthreads();
   }
-  if (lane == 0) a.nm[p] = nm;
+  if (tid == 0) a.nm[p] = s_nm;
+}
+
+template <bool FUSED> __device__ __forceinline__ void knn_resolve_tail(const KnnArgs& a, uint32_t sentinel, int p, uint8_t* smem) {
+  if (FUSED) knn_resolve_pair<true>(a, sentinel, p, smem, false);
+}
+
+// stand-alone form (a pair whose B side does not fit the fused kernel's shared memory, or ORBX_KNN_SPLIT for A/B runs)
+template <bool BSM>
+__global__ void __launch_bounds__(kKnnResolveThreads) k_knn_resolve(KnnArgs a, uint32_t sentinel) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  knn_resolve_pair<BSM>(a, sentinel, blockIdx.x, smem, true);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1986,9 +2064,21 @@ int launch_knn_ratio(const KnnArgs& a, cudaStream_t st) {
   const uint32_t sentinel = (uint32_t)dstar << 16;
   const int qblocks = (a.cap + kKnnThreads - 1) / kKnnThreads;
   const size_t smem = (size_t)a.cap * 32;
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_knn_topk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_knn_topk<<<a.n_pairs * qblocks, kKnnThreads, smem, st>>>(a, qblocks, sentinel);
-  k_knn_resolve<<<a.n_pairs, 32, (size_t)((a.cap + 31) / 32) * 4 + (size_t)a.cap * 4, st>>>(a, sentinel);
+  const size_t rs = (size_t)((a.cap + 31) / 32) * 4 + (size_t)a.cap * 4;
+  if (rs + smem <= 200 * 1024 && !getenv("ORBX_KNN_SPLIT")) {
+    cudaFuncSetAttribute(k_knn_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(rs + smem));
+    k_knn_topk<true><<<a.n_pairs * qblocks, kKnnThreads, rs + smem, st>>>(a, qblocks, sentinel);
+    return 1;
+  }
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_knn_topk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_knn_topk<false><<<a.n_pairs * qblocks, kKnnThreads, smem, st>>>(a, qblocks, sentinel);
+  if (rs + smem <= 200 * 1024) {
+    cudaFuncSetAttribute(k_knn_resolve<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(rs + smem));
+    k_knn_resolve<true><<<a.n_pairs, kKnnResolveThreads, rs + smem, st>>>(a, sentinel);
+  } else {
+    if (rs > 48 * 1024) cudaFuncSetAttribute(k_knn_resolve<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs);
+    k_knn_resolve<false><<<a.n_pairs, kKnnResolveThreads, rs, st>>>(a, sentinel);
+  }
   return 2;
 }
 

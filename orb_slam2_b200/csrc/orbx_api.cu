@@ -898,6 +898,7 @@ orbx_status orbx_knn_ratio_batch(const uint8_t* descA, const float* angA, const 
   if (on_device) { a.m12 = matches12; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
   CU(sg.alloc((void**)&a.topk, pc * 8 * sizeof(uint32_t)));
+  CU(sg.alloc((void**)&a.done, np * sizeof(int))); CU(cudaMemsetAsync(a.done, 0, np * sizeof(int), st));
   a.n_pairs = n_pairs; a.cap = cap; a.th = th; a.ratio = nnratio; a.checkOri = check_orientation; a.strict = strict_lt;
   CU(sg.upload());
   g_launches += launch_knn_ratio(a, st);

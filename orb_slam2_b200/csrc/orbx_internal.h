@@ -128,6 +128,7 @@ struct KnnArgs {
   int n_pairs, cap, th; float ratio; int checkOri, strict;
   int* m12; int* nm;
   uint32_t* topk;  // per pair: cap x 8 sorted keys distance<<16 | j (nearest B features of every A feature)
+  int* done;       // [n_pairs], zero on entry: how many query blocks of the pair have written their lists (the last one resolves the pair)
 };
 int launch_knn_ratio(const KnnArgs& a, cudaStream_t st);
 

@@ -67,8 +67,8 @@ __device__ __forceinline__ int warp_top4(unsigned long long k1, unsigned long lo
 // (with the number of iterations).  stag[i] = (iteration stamp << 5) | (31 - lowest lane that wants keypoint i), written
 // with atomicMax: a newer stamp beats every older entry, so nothing has to be reset; `epoch` counts the iterations of the
 // whole kernel (start it at 0 over a zeroed stag).
-template <class Pick>
-__device__ __forceinline__ int order_round(const uint32_t (&key)[4], unsigned hitP, int* stag, int& epoch, int lane, Pick pick) {
+template <int NK, class Pick>
+__device__ __forceinline__ int order_round(const uint32_t (&key)[NK], unsigned hitP, int* stag, int& epoch, int lane, Pick pick) {
   int claim = pick(hitP);
   int it = 0;
   for (; it < 33; ++it) {
@@ -77,7 +77,7 @@ __device__ __forceinline__ int order_round(const uint32_t (&key)[4], unsigned hi
     __syncwarp();
     unsigned hitR = 0u;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < NK; ++k) {
       const int t = key[k] != kNoKey ? stag[key[k] & 0xFFFFu] : 0;
       if ((t >> 5) == epoch && 31 - (t & 31) < lane) hitR |= 1u << k;
     }
