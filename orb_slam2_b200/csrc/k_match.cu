@@ -615,9 +615,9 @@ __host__ __device__ inline size_t frame_stage_bytes(int cap) {
   return (b + 15) & ~(size_t)15;
 }
 
-// All threads of the CTA.  Ends with a block barrier.
+// All threads of the CTA.  Ends with a block barrier.  Keypoints above `max_octave` stay out of the grid (K6 searches level 0 only).
 __device__ __forceinline__ void frame_stage(FrameStage& S, uint8_t* smem, int cap, const orbx_keypoint* k, const uint32_t* dg, const float* uRight,
-                                            const int* frameObs, int n, float minX, float minY, float invW, float invH) {
+                                            const int* frameObs, int n, float minX, float minY, float invW, float invH, int max_octave = 255) {
   __shared__ int s_wsum[32];
   __shared__ int s_total;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x;
@@ -636,10 +636,10 @@ __device__ __forceinline__ void frame_stage(FrameStage& S, uint8_t* smem, int ca
   for (int i = tid; i <= kGridCells + 1; i += nth) soff[i] = 0;
   for (int base = warp * 32; base < cap; base += nth) {                 // 32 keypoints per ballot
     const int i = base + lane;
-    const uint32_t b = __ballot_sync(0xffffffffu, i < n && frameObs[i] > 0);
+    const uint32_t b = __ballot_sync(0xffffffffu, frameObs != nullptr && i < n && frameObs[i] > 0);
     if (lane == 0) { S.sobs[base >> 5] = b; S.claim[base >> 5] = 0u; }
   }
-  for (int i = tid; i < n; i += nth) { S.sasg[i] = -1; S.stag[i] = 0; S.sur[i] = uRight[i]; }
+  for (int i = tid; i < n; i += nth) { S.sasg[i] = -1; S.stag[i] = 0; S.sur[i] = uRight ? uRight[i] : -1.f; }
   {
     const uint4* src = reinterpret_cast<const uint4*>(dg);
     uint4* dst = reinterpret_cast<uint4*>(S.sdesc);
@@ -651,7 +651,7 @@ __device__ __forceinline__ void frame_stage(FrameStage& S, uint8_t* smem, int ca
     const orbx_keypoint kp = k[i];
     S.soct[i] = (uint8_t)kp.octave;
     const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));
-    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) atomicAdd(&soff[gx * 48 + gy + 1], 1);
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48 && kp.octave <= max_octave) atomicAdd(&soff[gx * 48 + gy + 1], 1);
   }
   __syncthreads();
   ORBX_CLK(fs2);
@@ -687,7 +687,7 @@ __device__ __forceinline__ void frame_stage(FrameStage& S, uint8_t* smem, int ca
   for (int i = tid; i < n; i += nth) {                                  // fill each cell from its end downwards: soff[c+1] = start of cell c
     const orbx_keypoint kp = k[i];
     const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));
-    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) {
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48 && kp.octave <= max_octave) {
       const int c = gx * 48 + gy;
       const int pos = atomicSub(&soff[c + 1], 1) - 1;
       S.sxy[pos] = make_float2(kp.x, kp.y);
@@ -881,6 +881,219 @@ __global__ void __launch_bounds__(kParThreads) k_search_projection_par(ProjArgs 
   }
   ORBX_CLK(t4);
   ORBX_CLK_PRINT("k_search_projection_par stage / A / B / flush", t0, t1, t2, t3, t4);
+}
+
+// ------------------------------------------------------------------------------------------
+// K6, 1024-thread form (the monocular initialiser asks about one frame pair per call; batches take it too).  Frame 2 is staged
+// in shared memory in grid-cell order (frame_stage), so a query touches the cells of its window instead of every level-0
+// keypoint, and the walk over the queries - order matters: a query skips a frame-2 feature whose recorded match distance is
+// not above its own (vMatchedDistance), and may take a feature away from an earlier query - is split in two:
+//   A (all warps, no state): every level-0 keypoint of frame 1 gets its four nearest window candidates, sorted by
+//     (distance, cell, index) = the reference's first-wins order, and whether that is all of them;
+//   B (warp 0), 32 queries per pass, one per lane: each lane judges its list against the recorded distances as they stand;
+//     the lanes up to the first one whose list contains a feature an earlier lane of the pass is about to take commit
+//     together (their features are distinct), the pass resumes from that lane.  A lane whose truncated list has fewer than two
+//     survivors is re-scanned exactly, alone.  Every decision is therefore taken against exactly the state the reference's
+//     loop would have at that query.
+__host__ __device__ inline size_t init_lat_bytes(int cap) { return frame_stage_bytes(cap) + (size_t)cap * (4 + 4 + 4 + 2 + 1) + 16; }
+
+struct InitQ { float x, y; uint32_t dw; };
+
+// frame-1 query (prev position x, y; descriptor q): its candidates in frame 2, level 0, |dx| < r and |dy| < r, whose recorded
+// match distance is above their own when `live`; the list format of proj_scan.
+__device__ __forceinline__ uint4 init_scan(const InitMatchArgs& a, const InitQ& c, const FrameStage& S, const int* smd, bool live, const float* gbv, int lane) {
+  const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+  const float minX = gbv[0], minY = gbv[2], invW = gbv[4], invH = gbv[5], r = a.window, x = c.x, y = c.y;
+  // GetFeaturesInArea's cell window, src/Frame.cc:332-346
+  const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, minX), r), invW)));
+  if (cx0 >= 64) return none;
+  const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, minX), r), invW)));
+  if (cx1 < 0) return none;
+  const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, minY), r), invH)));
+  if (cy0 >= 48) return none;
+  const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, minY), r), invH)));
+  if (cy1 < 0) return none;
+  uint32_t q[8];
+#pragma unroll
+  for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
+  const int* cstart = S.soff + 1;
+  unsigned long long k1 = ~0ull, k2 = ~0ull;
+  int cnt = 0;
+  for_each_in_columns(cx0, cx1, lane,
+    [&](int ix, int& e_lo, int& e_hi) {
+      const int c_hi = ix * 48 + cy1;
+      e_lo = cstart[ix * 48 + cy0]; e_hi = (c_hi + 1 < kGridCells) ? cstart[c_hi + 1] : S.n_in_grid;
+    },
+    [&](int e, int) {
+      const uint32_t meta = S.smeta[e];
+      if (meta >> 28) return;                                                         // level 0 only (minLevel = maxLevel = 0)
+      const int idx = (int)(meta & 0xFFFF);
+      const float2 pt = S.sxy[e];
+      if (!(fabsf(__fsub_rn(pt.x, x)) < r && fabsf(__fsub_rn(pt.y, y)) < r)) return;
+      const int d = ham8(q, S.sdesc + (size_t)idx * 8);
+      if (live && smd[idx] <= d) return;                                              // vMatchedDistance[i2] <= dist, src/ORBmatcher.cc:436
+      const unsigned long long key = ((unsigned long long)d << 32) | (meta & 0x0FFFFFFFu);
+      ++cnt;
+      if (key < k1) { k2 = k1; k1 = key; }
+      else if (key < k2) k2 = key;
+    });
+  unsigned hi[4], lo[4];
+  bool complete;
+  warp_top4(k1, k2, cnt, hi, lo, complete);
+  uint32_t l[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
+  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
+}
+
+__global__ void __launch_bounds__(kParThreads) k_search_init_lat(InitMatchArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_bcnt[kParThreads / 32];
+  __shared__ int s_nm;
+  __shared__ float s_gb[6];
+  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
+  const int n1 = a.n1[p], n2 = a.n2[p];
+  const orbx_keypoint* k1 = a.k1 + (size_t)p * a.cap;
+  const orbx_keypoint* k2 = a.k2 + (size_t)p * a.cap;
+  const uint32_t* d1 = reinterpret_cast<const uint32_t*>(a.d1 + (size_t)p * a.cap * 32);
+  float* prev = a.prev + (size_t)p * a.cap * 2;
+  int* m12 = a.m12 + (size_t)p * a.cap;
+  uint4* spec = reinterpret_cast<uint4*>(a.scratch + (size_t)p * a.cap * 4);           // candidate lists by query-list position
+  uint8_t* tail = smem + frame_stage_bytes(a.cap);
+  int* sm12 = reinterpret_cast<int*>(tail);                    // [cap] vnMatches12
+  int* sm21 = sm12 + a.cap;                                    // [cap] vnMatches21
+  int* smd = sm21 + a.cap;                                     // [cap] vMatchedDistance
+  uint16_t* sq = reinterpret_cast<uint16_t*>(smd + a.cap);     // [cap] the level-0 keypoints of frame 1, in order
+  uint8_t* sbin = reinterpret_cast<uint8_t*>(sq + a.cap);      // [cap] rotation bin of a frame-1 keypoint's latest match
+  ORBX_CLK(t0);
+  for (int i = tid; i < a.cap; i += nth) { sm12[i] = -1; sm21[i] = -1; smd[i] = INT_MAX; sbin[i] = 255; }
+  if (tid < kHisto) s_hist[tid] = 0;
+  if (tid < 6) s_gb[tid] = a.gb[tid];
+  int nq = 0;
+  for (int base = 0; base < n1; base += nth) {                 // ordered list of the queries
+    const int i = base + tid;
+    const bool ok = i < n1 && k1[i].octave <= 0;
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) s_bcnt[warp] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < nwarps; ++w) { const int c = s_bcnt[w]; before += w < warp ? c : 0; total += c; }
+    if (ok) sq[nq + before + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)i;
+    nq += total;
+    __syncthreads();
+  }
+  FrameStage S;
+  frame_stage(S, smem, a.cap, k2, reinterpret_cast<const uint32_t*>(a.d2 + (size_t)p * a.cap * 32), nullptr, nullptr, n2, a.gb[0], a.gb[2], a.gb[4], a.gb[5], 0);
+  ORBX_CLK(t1);
+  auto fetch = [&](int c) {
+    InitQ q;
+    const bool ok = c < nq;
+    const int i = ok ? sq[c] : 0;
+    q.x = ok ? prev[2 * i] : 0.f; q.y = ok ? prev[2 * i + 1] : 0.f;
+    q.dw = (ok && lane < 8) ? __ldg(d1 + (size_t)i * 8 + lane) : 0u;
+    return q;
+  };
+  // phase A
+  {
+    InitQ nx = fetch(warp);
+    for (int c = warp; c < nq; c += nwarps) {
+      const InitQ cur = nx;
+      nx = fetch(c + nwarps);
+      const uint4 l = init_scan(a, cur, S, smd, false, s_gb, lane);
+      if (lane == 0) spec[c] = l;
+    }
+  }
+  __syncthreads();
+  ORBX_CLK(t2);
+  // phase B
+  if (warp == 0) {
+    int epoch = 0;
+    ORBX_STAT(int dbg_pass = 0; int dbg_rs = 0;)
+    const uint4 nokeys = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+    uint4 nxt = lane < nq ? spec[lane] : nokeys;
+    for (int base = 0; base < nq; base += 32) {
+      const int c = base + lane;
+      const int i1 = c < nq ? sq[c] : 0;
+      const uint4 my4 = nxt;
+      nxt = c + 32 < nq ? spec[c + 32] : nokeys;
+      const float ang1 = (c < nq && a.checkOri) ? k1[i1].angle : 0.f;
+      const bool complete = my4.x >> 31;
+      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
+      uint32_t todo = __ballot_sync(0xffffffffu, key[0] != kNoKey);
+      while (todo) {
+        const bool live = (todo >> lane) & 1u;
+        // the first two entries whose recorded distance is above their own
+        uint32_t f1 = kNoKey, f2 = kNoKey;
+#pragma unroll
+        for (int k = 3; k >= 0; --k)
+          if (key[k] != kNoKey && !(smd[key[k] & 0xFFFFu] <= (int)(key[k] >> 16))) { f2 = f1; f1 = key[k]; }
+        const bool starved = live && !complete && f2 == kNoKey;
+        const int best = (int)(f1 >> 16), bi = (int)(f1 & 0xFFFFu);
+        // bestDist2 stays INT_MAX without a second candidate: the product is then far above any distance
+        const bool pass = live && !starved && f1 != kNoKey && best <= 50 && (float)best < __fmul_rn(f2 == kNoKey ? (float)INT_MAX : (float)(int)(f2 >> 16), a.ratio);
+        ++epoch;
+        ORBX_STAT(++dbg_pass;)
+        if (pass) atomicMax(&S.stag[bi], (epoch << 5) | (31 - lane));
+        __syncwarp();
+        bool conflict = false;                                  // a feature on my list is about to be taken by an earlier lane
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int t = key[k] != kNoKey ? S.stag[key[k] & 0xFFFFu] : 0;
+          if ((t >> 5) == epoch && 31 - (t & 31) < lane) conflict = true;
+        }
+        const uint32_t stop = __ballot_sync(0xffffffffu, live && (conflict || starved));
+        const int first = stop ? __ffs((int)stop) - 1 : 32;
+        if (pass && lane < first) {                             // src/ORBmatcher.cc:449-466; the features of the committing lanes are distinct
+          const int old = sm21[bi];
+          if (old >= 0) sm12[old] = -1;
+          sm12[i1] = bi; sm21[bi] = i1; smd[bi] = best;
+          if (a.checkOri) { const int bin = rot_bin(ang1, k2[bi].angle); sbin[i1] = (uint8_t)bin; atomicAdd(&s_hist[bin], 1); }
+        }
+        __syncwarp();
+        if (first == 32) break;
+        if (__shfl_sync(0xffffffffu, (int)starved, first)) {    // exact re-scan against the recorded distances as they stand
+          ORBX_STAT(++dbg_rs;)
+          const int cs = base + first, is = __shfl_sync(0xffffffffu, i1, first);
+          const uint4 l = init_scan(a, fetch(cs), S, smd, true, s_gb, lane);
+          const uint32_t g1 = l.x & 0x7FFFFFFFu, g2 = l.y;
+          const int rb = (int)(g1 >> 16), rbi = (int)(g1 & 0xFFFFu);
+          if (g1 != kNoKey && rb <= 50 && (float)rb < __fmul_rn(g2 == kNoKey ? (float)INT_MAX : (float)(int)(g2 >> 16), a.ratio)) {
+            if (lane == 0) {
+              const int old = sm21[rbi];
+              if (old >= 0) sm12[old] = -1;
+              sm12[is] = rbi; sm21[rbi] = is; smd[rbi] = rb;
+              if (a.checkOri) { const int bin = rot_bin(k1[is].angle, k2[rbi].angle); sbin[is] = (uint8_t)bin; s_hist[bin] += 1; }
+            }
+          }
+          __syncwarp();
+          todo &= ~((2u << first) - 1u);
+        } else {
+          todo &= ~((1u << first) - 1u);                       // lane `first` judges again, now against the committed state
+        }
+      }
+    }
+    ORBX_STAT(if (lane == 0 && blockIdx.x == 0) printf("K6 phase B: %d queries, %d passes, %d re-scans\n", nq, dbg_pass, dbg_rs);)
+  }
+  __syncthreads();
+  ORBX_CLK(t3);
+  // rotation consistency (src/ORBmatcher.cc:474-492), vbPrevMatched update (:495-497), write-back: whole CTA
+  if (tid == 0) s_nm = 0;
+  int k_a = -1, k_b = -1, k_c = -1;
+  if (a.checkOri) three_maxima(s_hist, k_a, k_b, k_c);
+  __syncthreads();
+  int nm = 0;
+  for (int i = tid; i < n1; i += nth) {
+    int m = sm12[i];
+    if (a.checkOri && m >= 0) { const int b = sbin[i]; if (b != k_a && b != k_b && b != k_c) m = -1; }
+    m12[i] = m;
+    if (m >= 0) { prev[2 * i] = k2[m].x; prev[2 * i + 1] = k2[m].y; ++nm; }
+  }
+  if (nm) atomicAdd(&s_nm, nm);
+  __syncthreads();
+  if (tid == 0) a.nm[p] = s_nm;
+  ORBX_CLK(t4);
+  ORBX_CLK_PRINT("k_search_init_lat list + stage / A / B / rotation + flush", t0, t1, t2, t3, t4);
 }
 
 int launch_search_projection(const ProjArgs& a, cudaStream_t st) {
@@ -1576,12 +1789,12 @@ __global__ void __launch_bounds__(kBowLatThreads) k_search_by_bow_lat(BowArgs a,
     uint32_t l0 = kNoKey, l1 = kNoKey, l2 = kNoKey, l3 = kNoKey;
     int cnt = 0;
     const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8) + 1);
+    const uint32_t q[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
     for (int e = (int)(rr & 0xFFFFu); e < (int)(rr >> 16); ++e) {
       const int j = (int)(keyB[e] & 0xffffffffu);
       if (bit_of(used, j)) continue;
       const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
-      const int d = __popc(q0.x ^ b0.x) + __popc(q0.y ^ b0.y) + __popc(q0.z ^ b0.z) + __popc(q0.w ^ b0.w) + __popc(q1.x ^ b1.x) +
-                    __popc(q1.y ^ b1.y) + __popc(q1.z ^ b1.z) + __popc(q1.w ^ b1.w);
+      const int d = ham256_csa(q, b0, b1);                                          // 4 POPC per distance instead of 8: POPC is the slow pipe
       uint32_t kk = ((uint32_t)d << 16) | (uint32_t)j;                              // sorted insertion into (l0 <= l1 <= l2 <= l3)
       ++cnt;
       if (kk < l0) { const uint32_t sw = l0; l0 = kk; kk = sw; }
@@ -1923,6 +2136,7 @@ __global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(Tri
     const int has1 = a.hasMp1[po + i];
     const orbx_keypoint kp1 = k1[i];
     const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8) + 1);
+    const uint32_t qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
     if (!has1 && !(a.onlyStereo && !st1)) {
       int lo = 0, hi = n2;                                                          // first entry with node2 >= node
       while (lo < hi) { const int mid = (lo + hi) >> 1; if ((uint32_t)(keyB[mid] >> 32) < node) lo = mid + 1; else hi = mid; }
@@ -1935,8 +2149,7 @@ __global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(Tri
         ORBX_STAT(++dbg_cand;)
         const int j = (int)(keyB[e] & 0xffffffffu);
         const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
-        const int dist = __popc(q0.x ^ b0.x) + __popc(q0.y ^ b0.y) + __popc(q0.z ^ b0.z) + __popc(q0.w ^ b0.w) + __popc(q1.x ^ b1.x) +
-                         __popc(q1.y ^ b1.y) + __popc(q1.z ^ b1.z) + __popc(q1.w ^ b1.w);
+        const int dist = ham256_csa(qv, b0, b1);                                    // 4 POPC per distance instead of 8: POPC is the slow pipe
         if (dist > 50 || dist > bestDist) continue;
         if (bit_of(hasb, j)) continue;
         const bool st2 = bit_of(stb, j);
@@ -2050,7 +2263,13 @@ int launch_distinctive(const DistinctArgs& a, cudaStream_t st) {
 }
 
 int launch_search_init(const InitMatchArgs& a, cudaStream_t st) {
-  k_search_init<<<a.n_pairs, 32, 0, st>>>(a);
+  const size_t lat = init_lat_bytes(a.cap);
+  if (lat <= 200 * 1024 && a.cap <= 65535 && !getenv("ORBX_PROJ_SERIAL")) {
+    cudaFuncSetAttribute(k_search_init_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
+    k_search_init_lat<<<a.n_pairs, kParThreads, lat, st>>>(a);
+  } else {
+    k_search_init<<<a.n_pairs, 32, 0, st>>>(a);
+  }
   return 1;
 }
 

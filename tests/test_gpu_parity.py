@@ -282,8 +282,23 @@ def test_stereo_saturated_and_offset_right_images(gx, oracle):
         assert np.array_equal(dp[i, :cnt].view(np.uint32), rdp.view(np.uint32))
 
 
+FORMS = pytest.mark.parametrize("form", ["latency", "throughput"])
+
+
+def _pick_form(monkeypatch, form):
+    """The order-dependent matchers have two device forms: the latency form (a 1024-thread CTA per problem, a few problems per
+    call or many) and the small form (a warp or a 128-thread CTA per problem, taken
+    when a problem's arrays do not fit the 1024-thread form's shared memory).  ORBX_PROJ_SERIAL / ORBX_BOW_SERIAL select it."""
+    if form == "throughput":
+        monkeypatch.setenv("ORBX_PROJ_SERIAL", "1"); monkeypatch.setenv("ORBX_BOW_SERIAL", "1")
+    else:
+        monkeypatch.delenv("ORBX_PROJ_SERIAL", raising=False); monkeypatch.delenv("ORBX_BOW_SERIAL", raising=False)
+
+
+@FORMS
 @pytest.mark.parametrize("nf", [1000, 2000])
-def test_search_for_initialization(gx, oracle, nf):
+def test_search_for_initialization(gx, oracle, nf, monkeypatch, form):
+    _pick_form(monkeypatch, form)
     w, h = 640, 480
     G = _ext(gx, w, h, nf)
     F1s, F2s, prevs, refs = [], [], [], []
@@ -366,19 +381,6 @@ def test_knn_ratio_crowded_neighbourhoods(gx, oracle, th, ratio, strict):
         r = oracle.knn_ratio(A[:50], angA[:50], B[:nb], angB[:nb], th, ratio, False, strict)
         n1, g = gx.ORBmatcher(ratio, False).SearchByBoW(A[:50], angA[:50], B[:nb], angB[:nb], th=th, strict=strict)
         assert n1 == r[1] and np.array_equal(g, r[0]), nb
-
-
-FORMS = pytest.mark.parametrize("form", ["latency", "throughput"])
-
-
-def _pick_form(monkeypatch, form):
-    """The order-dependent matchers have two device forms: the latency form (a 1024-thread CTA per problem, a few problems per
-    call or many) and the small form (a warp or a 128-thread CTA per problem, taken
-    when a problem's arrays do not fit the 1024-thread form's shared memory).  ORBX_PROJ_SERIAL / ORBX_BOW_SERIAL select it."""
-    if form == "throughput":
-        monkeypatch.setenv("ORBX_PROJ_SERIAL", "1"); monkeypatch.setenv("ORBX_BOW_SERIAL", "1")
-    else:
-        monkeypatch.delenv("ORBX_PROJ_SERIAL", raising=False); monkeypatch.delenv("ORBX_BOW_SERIAL", raising=False)
 
 
 @FORMS
