@@ -2069,7 +2069,7 @@ __host__ __device__ inline size_t tri_lat_bytes(int cap, int capPad) {
   return (size_t)capPad * 16 + (size_t)cap * 32 + (size_t)cap * 8 + (size_t)((cap + 31) / 32) * 8 + (size_t)cap + 16;
 }
 
-__global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(TriArgs a, int capPad) {
+__global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(TriArgs a, int capPad, int G) {
   extern __shared__ __align__(16) uint8_t smem[];
   unsigned long long* keyB = reinterpret_cast<unsigned long long*>(smem);          // [capPad] KF2 node<<32 | index, sorted
   unsigned long long* keyA = keyB + capPad;                                         // [capPad] KF1 the same: neighbouring threads then walk the same run (broadcast reads)
@@ -2081,7 +2081,7 @@ __global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(Tri
   __shared__ int s_hist[kHisto];
   __shared__ int s_nm;
   __shared__ float s_epi[2], s_F[9];
-  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x;
+  const int p = blockIdx.x / G, g = blockIdx.x - p * G, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x;
   const int n1 = a.n1[p], n2 = a.n2[p];
   const size_t po = (size_t)p * a.cap;
   const orbx_keypoint* k1 = a.k1 + po; const orbx_keypoint* k2 = a.k2 + po;
@@ -2124,9 +2124,9 @@ __global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(Tri
   const float ex = s_epi[0], ey = s_epi[1];
   int nm = 0;
   ORBX_STAT(int dbg_cand = 0;)
-  int mine[(4096 + kTriLatThreads - 1) / kTriLatThreads], mybin[(4096 + kTriLatThreads - 1) / kTriLatThreads];
-  int r = 0;
-  for (int t = tid; t < n1; t += nth, ++r) {
+  // this CTA's share of the sorted KF1 features: a contiguous piece (neighbouring threads keep walking the same runs)
+  const int piece = (((n1 + G - 1) / G) + 31) & ~31, t_lo = g * piece, t_hi = min(n1, t_lo + piece);
+  for (int t = t_lo + tid; t < t_hi; t += nth) {
     int best2 = -1;
     const unsigned long long ka = keyA[t];
     const int i = (int)(ka & 0xffffffffu);
@@ -2166,31 +2166,41 @@ __global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(Tri
         if ((double)dsqr < __dmul_rn(3.84, (double)a.sigma2_2[o2])) { best2 = j; bestDist = dist; }
       }
     }
-    mine[r] = best2; mybin[r] = -1;
+    m12[i] = best2;
     if (best2 >= 0) {
       ++nm;
-      if (a.checkOri) { mybin[r] = rot_bin(kp1.angle, k2[best2].angle); atomicAdd(&s_hist[mybin[r]], 1); }
+      if (a.checkOri) { const int bin = rot_bin(kp1.angle, k2[best2].angle); a.bins[po + i] = (uint8_t)bin; atomicAdd(&s_hist[bin], 1); }
     }
   }
   ORBX_CLK(t3w);
   if (nm) atomicAdd(&s_nm, nm);
   __syncthreads();
   ORBX_CLK(t3);
-  int k_a = -1, k_b = -1, k_c = -1;
-  if (a.checkOri) three_maxima(s_hist, k_a, k_b, k_c);
-  int drop = 0;
-  r = 0;
-  for (int t = tid; t < n1; t += nth, ++r) {
-    int m = mine[r];
-    if (a.checkOri && m >= 0) { const int b = mybin[r]; if (b != k_a && b != k_b && b != k_c) { m = -1; ++drop; } }
-    m12[(int)(keyA[t] & 0xffffffffu)] = m;
-  }
-  if (drop) atomicSub(&s_nm, drop);
-  __syncthreads();
-  if (tid == 0) a.nm[p] = s_nm;
+  // this CTA's counts join the pair's; the rotation check is k_triangulation_finish's once every CTA of the pair is done
+  if (a.checkOri && tid < kHisto && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 32 + tid], s_hist[tid]);
+  if (tid == 0 && s_nm) atomicAdd(&a.nm[p], s_nm);
   ORBX_CLK(t4);
-  ORBX_CLK_PRINT("k_search_triangulation_lat stage / sort / walk (thread 0) / walk (all) / rotation + flush", t0, t1, t2, t3w, t3, t4);
-  ORBX_STAT(if (tid == 0 && blockIdx.x == 0) printf("  K14: thread 0 walked %d candidates\n", dbg_cand);)
+  ORBX_CLK_PRINT("k_search_triangulation_lat stage / sort / walk (thread 0) / walk (all) / totals", t0, t1, t2, t3w, t3, t4);
+}
+
+// rotation consistency of K14's 1024-thread form (src/ORBmatcher.cc:792-808): one CTA per pair, after all walk CTAs
+__global__ void __launch_bounds__(256) k_triangulation_finish(TriArgs a) {
+  __shared__ int s_hist[kHisto];
+  __shared__ int s_drop;
+  const int p = blockIdx.x, tid = threadIdx.x;
+  const size_t po = (size_t)p * a.cap;
+  if (tid < kHisto) s_hist[tid] = a.hist[(size_t)p * 32 + tid];
+  if (tid == 0) s_drop = 0;
+  __syncthreads();
+  int k_a, k_b, k_c;
+  three_maxima(s_hist, k_a, k_b, k_c);
+  int* m12 = a.m12 + po;
+  int drop = 0;
+  for (int i = tid; i < a.n1[p]; i += 256)
+    if (m12[i] >= 0) { const int bn = a.bins[po + i]; if (bn != k_a && bn != k_b && bn != k_c) { m12[i] = -1; ++drop; } }
+  if (drop) atomicAdd(&s_drop, drop);
+  __syncthreads();
+  if (tid == 0 && s_drop) a.nm[p] -= s_drop;
 }
 
 int launch_search_triangulation(const TriArgs& a, cudaStream_t st) {
@@ -2198,8 +2208,12 @@ int launch_search_triangulation(const TriArgs& a, cudaStream_t st) {
   while (capPad < a.cap) capPad <<= 1;
   const size_t lat = tri_lat_bytes(a.cap, capPad);
   if (lat <= 200 * 1024 && !getenv("ORBX_BOW_SERIAL")) {
+    // KF1 features are independent, so a pair is spread over up to 8 CTAs while the GPU has SMs to spare (each sorts the KF2
+    // side for itself: ~20 us, against a walk that is ~90 us on one SM when the runs are long)
+    const int G = std::max(1, std::min(8, 148 / std::max(a.n_pairs, 1)));
     cudaFuncSetAttribute(k_search_triangulation_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
-    k_search_triangulation_lat<<<a.n_pairs, kTriLatThreads, lat, st>>>(a, capPad);
+    k_search_triangulation_lat<<<a.n_pairs * G, kTriLatThreads, lat, st>>>(a, capPad, G);
+    if (a.checkOri) { k_triangulation_finish<<<a.n_pairs, 256, 0, st>>>(a); return 2; }
     return 1;
   }
   const size_t smem = (size_t)capPad * 8 + (size_t)a.cap * 32;

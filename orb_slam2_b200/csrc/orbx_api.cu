@@ -1072,6 +1072,8 @@ orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uin
   if (on_device) { a.m12 = matches12; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
   a.n_pairs = n_pairs; a.cap = cap; a.onlyStereo = only_stereo; a.checkOri = check_orientation;
+  CU(sg.alloc((void**)&a.hist, np * 32 * sizeof(int))); CU(sg.alloc((void**)&a.bins, pc));
+  CU(cudaMemsetAsync(a.hist, 0, np * 32 * sizeof(int), st)); CU(cudaMemsetAsync(a.nm, 0, np * sizeof(int), st));
   CU(sg.upload());
   g_launches += launch_search_triangulation(a, st);
   CU(cudaGetLastError());

@@ -216,6 +216,8 @@ struct TriArgs {
   float scale2[kMaxLevels], sigma2_2[kMaxLevels];
   int n_pairs, cap, onlyStereo, checkOri;
   int* m12; int* nm;
+  int* hist;       // scratch [P][32], zero on entry: the pair's rotation histogram, summed over its CTAs (1024-thread form)
+  uint8_t* bins;   // scratch [P][cap]: rotation bin of every KF1 feature's match
 };
 int launch_search_triangulation(const TriArgs& a, cudaStream_t st);
 
