@@ -888,31 +888,37 @@ __global__ void __launch_bounds__(kParThreads) k_search_projection_par(ProjArgs 
 // in shared memory in grid-cell order (frame_stage), so a query touches the cells of its window instead of every level-0
 // keypoint, and the walk over the queries - order matters: a query skips a frame-2 feature whose recorded match distance is
 // not above its own (vMatchedDistance), and may take a feature away from an earlier query - is split in two:
-//   A (all warps, no state): every level-0 keypoint of frame 1 gets its four nearest window candidates, sorted by
+//   A (all warps, no state): every level-0 keypoint of frame 1 gets its eight nearest window candidates, sorted by
 //     (distance, cell, index) = the reference's first-wins order, and whether that is all of them;
-//   B (warp 0), 32 queries per pass, one per lane: each lane judges its list against the recorded distances as they stand;
-//     the lanes up to the first one whose list contains a feature an earlier lane of the pass is about to take commit
-//     together (their features are distinct), the pass resumes from that lane.  A lane whose truncated list has fewer than two
-//     survivors is re-scanned exactly, alone.  Every decision is therefore taken against exactly the state the reference's
-//     loop would have at that query.
+//   B (warp 0), 32 queries per pass, one per lane: each lane judges its list against the recorded distances as they stand -
+//     best and second best are its first two entries whose recorded distance is above their own.  A lane is held back when
+//     an earlier lane of the pass is about to record, on one of those two features, a distance at or below the lane's own
+//     (claims of one feature by successive lanes have falling distances, so the latest earlier claimer decides); the lanes
+//     before the first held-back lane commit together - a feature claimed twice among them goes to the later lane, as in the
+//     loop - and the pass resumes from that lane.  A lane whose truncated list has fewer than two survivors is re-scanned
+//     exactly, alone.  Every decision is therefore taken against exactly the state the reference's loop would have.
 __host__ __device__ inline size_t init_lat_bytes(int cap) { return frame_stage_bytes(cap) + (size_t)cap * (4 + 4 + 4 + 2 + 1) + 16; }
 
 struct InitQ { float x, y; uint32_t dw; };
 
 // frame-1 query (prev position x, y; descriptor q): its candidates in frame 2, level 0, |dx| < r and |dy| < r, whose recorded
 // match distance is above their own when `live`; the list format of proj_scan.
-__device__ __forceinline__ uint4 init_scan(const InitMatchArgs& a, const InitQ& c, const FrameStage& S, const int* smd, bool live, const float* gbv, int lane) {
-  const uint4 none = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
+constexpr int kInitK = 8;
+__device__ __forceinline__ void init_scan(const InitMatchArgs& a, const InitQ& c, const FrameStage& S, const int* smd, bool live, const float* gbv, int lane,
+                                          uint32_t (&l)[kInitK], bool& complete) {
+#pragma unroll
+  for (int k = 0; k < kInitK; ++k) l[k] = kNoKey;
+  complete = true;
   const float minX = gbv[0], minY = gbv[2], invW = gbv[4], invH = gbv[5], r = a.window, x = c.x, y = c.y;
   // GetFeaturesInArea's cell window, src/Frame.cc:332-346
   const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, minX), r), invW)));
-  if (cx0 >= 64) return none;
+  if (cx0 >= 64) return;
   const int cx1 = min(63, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, minX), r), invW)));
-  if (cx1 < 0) return none;
+  if (cx1 < 0) return;
   const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, minY), r), invH)));
-  if (cy0 >= 48) return none;
+  if (cy0 >= 48) return;
   const int cy1 = min(47, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, minY), r), invH)));
-  if (cy1 < 0) return none;
+  if (cy1 < 0) return;
   uint32_t q[8];
 #pragma unroll
   for (int w = 0; w < 8; ++w) q[w] = __shfl_sync(0xffffffffu, c.dw, w);
@@ -937,13 +943,10 @@ __device__ __forceinline__ uint4 init_scan(const InitMatchArgs& a, const InitQ& 
       if (key < k1) { k2 = k1; k1 = key; }
       else if (key < k2) k2 = key;
     });
-  unsigned hi[4], lo[4];
-  bool complete;
-  warp_top4(k1, k2, cnt, hi, lo, complete);
-  uint32_t l[4];
+  unsigned hi[kInitK], lo[kInitK];
+  warp_topk<kInitK>(k1, k2, cnt, hi, lo, complete);
 #pragma unroll
-  for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
-  return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
+  for (int k = 0; k < kInitK; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
 }
 
 __global__ void __launch_bounds__(kParThreads) k_search_init_lat(InitMatchArgs a) {
@@ -959,7 +962,7 @@ __global__ void __launch_bounds__(kParThreads) k_search_init_lat(InitMatchArgs a
   const uint32_t* d1 = reinterpret_cast<const uint32_t*>(a.d1 + (size_t)p * a.cap * 32);
   float* prev = a.prev + (size_t)p * a.cap * 2;
   int* m12 = a.m12 + (size_t)p * a.cap;
-  uint4* spec = reinterpret_cast<uint4*>(a.scratch + (size_t)p * a.cap * 4);           // candidate lists by query-list position
+  uint4* spec = reinterpret_cast<uint4*>(a.scratch + (size_t)p * a.cap * 8);           // candidate lists by query-list position, two uint4 each
   uint8_t* tail = smem + frame_stage_bytes(a.cap);
   int* sm12 = reinterpret_cast<int*>(tail);                    // [cap] vnMatches12
   int* sm21 = sm12 + a.cap;                                    // [cap] vnMatches21
@@ -1000,63 +1003,69 @@ __global__ void __launch_bounds__(kParThreads) k_search_init_lat(InitMatchArgs a
     for (int c = warp; c < nq; c += nwarps) {
       const InitQ cur = nx;
       nx = fetch(c + nwarps);
-      const uint4 l = init_scan(a, cur, S, smd, false, s_gb, lane);
-      if (lane == 0) spec[c] = l;
+      uint32_t l[kInitK]; bool complete;
+      init_scan(a, cur, S, smd, false, s_gb, lane, l, complete);
+      if (lane == 0) { spec[2 * c] = make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]); spec[2 * c + 1] = make_uint4(l[4], l[5], l[6], l[7]); }
     }
   }
   __syncthreads();
   ORBX_CLK(t2);
   // phase B
   if (warp == 0) {
-    int epoch = 0;
     ORBX_STAT(int dbg_pass = 0; int dbg_rs = 0;)
-    const uint4 nokeys = make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey);
-    uint4 nxt = lane < nq ? spec[lane] : nokeys;
+    const uint4 nokeys = make_uint4(kNoKey, kNoKey, kNoKey, kNoKey);
+    uint4 nx0 = lane < nq ? spec[2 * lane] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey), nx1 = lane < nq ? spec[2 * lane + 1] : nokeys;
+    uint32_t* tag = reinterpret_cast<uint32_t*>(S.stag);        // [cap] zero between passes: the lanes of the pass that claim frame-2 feature i
     for (int base = 0; base < nq; base += 32) {
       const int c = base + lane;
       const int i1 = c < nq ? sq[c] : 0;
-      const uint4 my4 = nxt;
-      nxt = c + 32 < nq ? spec[c + 32] : nokeys;
+      const uint4 m0 = nx0, m1 = nx1;
+      nx0 = c + 32 < nq ? spec[2 * (c + 32)] : make_uint4(0xffffffffu, kNoKey, kNoKey, kNoKey); nx1 = c + 32 < nq ? spec[2 * (c + 32) + 1] : nokeys;
       const float ang1 = (c < nq && a.checkOri) ? k1[i1].angle : 0.f;
-      const bool complete = my4.x >> 31;
-      const uint32_t key[4] = {my4.x & 0x7FFFFFFFu, my4.y, my4.z, my4.w};
+      const bool complete = m0.x >> 31;
+      const uint32_t key[kInitK] = {m0.x & 0x7FFFFFFFu, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
       uint32_t todo = __ballot_sync(0xffffffffu, key[0] != kNoKey);
       while (todo) {
         const bool live = (todo >> lane) & 1u;
+        ORBX_STAT(++dbg_pass;)
         // the first two entries whose recorded distance is above their own
         uint32_t f1 = kNoKey, f2 = kNoKey;
 #pragma unroll
-        for (int k = 3; k >= 0; --k)
+        for (int k = kInitK - 1; k >= 0; --k)
           if (key[k] != kNoKey && !(smd[key[k] & 0xFFFFu] <= (int)(key[k] >> 16))) { f2 = f1; f1 = key[k]; }
         const bool starved = live && !complete && f2 == kNoKey;
         const int best = (int)(f1 >> 16), bi = (int)(f1 & 0xFFFFu);
         // bestDist2 stays INT_MAX without a second candidate: the product is then far above any distance
         const bool pass = live && !starved && f1 != kNoKey && best <= 50 && (float)best < __fmul_rn(f2 == kNoKey ? (float)INT_MAX : (float)(int)(f2 >> 16), a.ratio);
-        ++epoch;
-        ORBX_STAT(++dbg_pass;)
-        if (pass) atomicMax(&S.stag[bi], (epoch << 5) | (31 - lane));
+        if (pass) atomicOr(&tag[bi], 1u << lane);
         __syncwarp();
-        bool conflict = false;                                  // a feature on my list is about to be taken by an earlier lane
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int t = key[k] != kNoKey ? S.stag[key[k] & 0xFFFFu] : 0;
-          if ((t >> 5) == epoch && 31 - (t & 31) < lane) conflict = true;
-        }
-        const uint32_t stop = __ballot_sync(0xffffffffu, live && (conflict || starved));
+        // held back: an earlier lane is about to record, on my best or second best, a distance that takes it off my list
+        const uint32_t e1 = (live && f1 != kNoKey) ? tag[f1 & 0xFFFFu] & ((1u << lane) - 1u) : 0u;
+        const uint32_t e2 = (live && f2 != kNoKey) ? tag[f2 & 0xFFFFu] & ((1u << lane) - 1u) : 0u;
+        const int b1 = __shfl_sync(0xffffffffu, best, e1 ? 31 - __clz((int)e1) : lane);
+        const int b2 = __shfl_sync(0xffffffffu, best, e2 ? 31 - __clz((int)e2) : lane);
+        const bool held = (e1 && b1 <= (int)(f1 >> 16)) || (e2 && b2 <= (int)(f2 >> 16));
+        const uint32_t stop = __ballot_sync(0xffffffffu, live && (held || starved));
         const int first = stop ? __ffs((int)stop) - 1 : 32;
-        if (pass && lane < first) {                             // src/ORBmatcher.cc:449-466; the features of the committing lanes are distinct
-          const int old = sm21[bi];
-          if (old >= 0) sm12[old] = -1;
-          sm12[i1] = bi; sm21[bi] = i1; smd[bi] = best;
+        const uint32_t cm = __ballot_sync(0xffffffffu, pass && lane < first);
+        if (pass && lane < first) {                             // src/ORBmatcher.cc:449-466
           if (a.checkOri) { const int bin = rot_bin(ang1, k2[bi].angle); sbin[i1] = (uint8_t)bin; atomicAdd(&s_hist[bin], 1); }
+          if (!(tag[bi] & cm & ~((2u << lane) - 1u))) {         // not taken away again by a later lane of this commit
+            const int old = sm21[bi];
+            if (old >= 0) sm12[old] = -1;
+            sm12[i1] = bi; sm21[bi] = i1; smd[bi] = best;
+          }
         }
+        __syncwarp();
+        if (pass) tag[bi] = 0u;
         __syncwarp();
         if (first == 32) break;
         if (__shfl_sync(0xffffffffu, (int)starved, first)) {    // exact re-scan against the recorded distances as they stand
           ORBX_STAT(++dbg_rs;)
           const int cs = base + first, is = __shfl_sync(0xffffffffu, i1, first);
-          const uint4 l = init_scan(a, fetch(cs), S, smd, true, s_gb, lane);
-          const uint32_t g1 = l.x & 0x7FFFFFFFu, g2 = l.y;
+          uint32_t l[kInitK]; bool lc;
+          init_scan(a, fetch(cs), S, smd, true, s_gb, lane, l, lc);
+          const uint32_t g1 = l[0], g2 = l[1];
           const int rb = (int)(g1 >> 16), rbi = (int)(g1 & 0xFFFFu);
           if (g1 != kNoKey && rb <= 50 && (float)rb < __fmul_rn(g2 == kNoKey ? (float)INT_MAX : (float)(int)(g2 >> 16), a.ratio)) {
             if (lane == 0) {

@@ -865,7 +865,7 @@ orbx_status orbx_search_init_batch(const orbx_keypoint* kps1, const uint8_t* des
   a.prev = const_cast<float*>(prev_in);
   if (on_device) { a.m12 = matches12; a.nm = n_matches; }
   else { CU(sg.alloc((void**)&a.m12, pc * 4)); CU(sg.alloc((void**)&a.nm, np * 4)); }
-  CU(sg.alloc((void**)&a.scratch, pc * 4 * sizeof(int)));
+  CU(sg.alloc((void**)&a.scratch, pc * 8 * sizeof(int)));   // one-warp form: 4 int arrays per pair; 1024-thread form: eight list entries per query
   a.n_pairs = n_pairs; a.cap = cap;
   CU(sg.in(grid_bounds, 6, on_device, &a.gb));                  // Frame 2's bounds and inverse cell sizes, src/Frame.cc:207-213
   a.ratio = nnratio; a.window = (float)window; a.checkOri = check_orientation;

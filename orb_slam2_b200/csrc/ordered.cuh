@@ -34,14 +34,15 @@ namespace orbx {
 //     unclaimed keys (rare) is redone one map point at a time with full re-scans.
 constexpr uint32_t kNoKey = 0x7FFFFFFFu;
 
-// The four smallest 64-bit keys (hi, lo) of a warp whose lanes each kept their two smallest (k1 <= k2) of `cnt` candidates.
+// The K smallest 64-bit keys (hi, lo) of a warp whose lanes each kept their two smallest (k1 <= k2) of `cnt` candidates.
 // A lane that has given both kept keys and had more candidates ends the list there (its third key is unknown).
 // Returns the list length; `complete` = the list holds every candidate of the warp.
-__device__ __forceinline__ int warp_top4(unsigned long long k1, unsigned long long k2, int cnt, unsigned (&ohi)[4], unsigned (&olo)[4], bool& complete) {
+template <int K>
+__device__ __forceinline__ int warp_topk(unsigned long long k1, unsigned long long k2, int cnt, unsigned (&ohi)[K], unsigned (&olo)[K], bool& complete) {
   int popped = 0, len = 0;
   bool open = true;
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
+  for (int r = 0; r < K; ++r) {
     ohi[r] = olo[r] = 0xffffffffu;
     if (open) {
       if (__any_sync(0xffffffffu, k1 == ~0ull && cnt > popped)) open = false;
@@ -59,6 +60,9 @@ __device__ __forceinline__ int warp_top4(unsigned long long k1, unsigned long lo
   }
   complete = !__any_sync(0xffffffffu, cnt > popped);
   return len;
+}
+__device__ __forceinline__ int warp_top4(unsigned long long k1, unsigned long long k2, int cnt, unsigned (&ohi)[4], unsigned (&olo)[4], bool& complete) {
+  return warp_topk<4>(k1, k2, cnt, ohi, olo, complete);
 }
 
 // One fixpoint round of phase B (see above).  Every lane brings the keypoints of its list (key[k] & 0xFFFF, kNoKey = none),
