@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <type_traits>
 #include <string>
@@ -759,7 +760,11 @@ thread_local cudaEvent_t g_arena_event = nullptr;
 
 struct Staged {
   cudaStream_t st;
+  bool trace = false;                                                    // ORBX_TRACE_CALLS=1: host-side timing of the call on stderr (experiments)
+  std::chrono::steady_clock::time_point t0;
+  double since() const { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count(); }
   explicit Staged(cudaStream_t s) : st(s) {
+    if (getenv("ORBX_TRACE_CALLS")) { trace = true; t0 = std::chrono::steady_clock::now(); }
     int dev = 0;
     cudaGetDevice(&dev);
     if (g_in_arena.device != dev && g_arena_event) { cudaEventDestroy(g_arena_event); g_arena_event = nullptr; }
@@ -772,6 +777,7 @@ struct Staged {
   ~Staged() {
     if (!g_arena_event) cudaEventCreateWithFlags(&g_arena_event, cudaEventDisableTiming);
     if (g_arena_event) cudaEventRecord(g_arena_event, st);
+    if (trace) std::fprintf(stderr, "orbx call: end %.1f us\n", since());
   }
   // device scratch / output space
   cudaError_t alloc(void** p, size_t bytes) {
@@ -791,6 +797,7 @@ struct Staged {
   }
   // the inputs staged since the last upload go to the device: one copy (per arena block).  Called before every launch.
   cudaError_t upload() {
+    if (trace) std::fprintf(stderr, "orbx call: staged %.1f us", since());
     for (Arena::Block& b : g_in_arena.blocks)
       if (b.used > b.sent) {
         const cudaError_t e = cudaMemcpyAsync(b.d + b.sent, b.h + b.sent, b.used - b.sent, cudaMemcpyHostToDevice, st);
@@ -836,8 +843,10 @@ struct Staged {
           }
       }
     }
+    if (trace) std::fprintf(stderr, ", issued %.1f us", since());
     const cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) return e;
+    if (trace) std::fprintf(stderr, ", synchronised %.1f us, ", since());
     for (const Pending& p : pending) std::memcpy(p.user, p.mirror, p.bytes);
     pending.clear();
     return cudaSuccess;
