@@ -428,6 +428,46 @@ def test_search_by_projection_local_map(gx, oracle, th, monkeypatch, form):
 
 
 @FORMS
+def test_search_by_projection_contention_and_odd_sizes(gx, oracle, monkeypatch, form):
+    """K8's ordered resolution under pressure and at odd sizes: every map point repeated up to seven times (more rivals for a
+    keypoint than a candidate list has entries: lists run out and are re-scanned, rounds need several fixpoint iterations),
+    Observations() mixed (claiming and non-claiming matches on the same keypoint), and frame / map sizes of 0, 1, 31, 33, ..."""
+    _pick_form(monkeypatch, form)
+    cfg = synth.KITTI
+    w, h, nf = cfg["w"], cfg["h"], cfg["nfeatures"]
+    G = _ext(gx, w, h, nf, batch=2)
+    L, R, _ = synth.stereo_pair(93, w, h)
+    G.extract_batch(np.stack([L, R]))
+    ur, dp, nm = gx.ComputeStereoMatches(G, G, cfg["bf"], cfg["fx"], n=1, slotL0=0, slotR0=1)
+    (kf, df), _ = G.fetch(0, 2)
+    scale = G.GetScaleFactors()
+    rng = np.random.default_rng(4711)
+    total = 0
+    for case, (n_sub, m_sub, dup, th) in enumerate([(len(kf), 300, 7, 3.0), (len(kf), 600, 3, 1.0), (33, 64, 5, 3.0), (31, 1, 1, 3.0), (1, 33, 2, 3.0),
+                                                     (0, 10, 1, 3.0), (500, 0, 1, 3.0), (len(kf), 97, 6, 7.0), (777, 777, 4, 3.0)]):
+        k, d, u = kf[:n_sub], df[:n_sub], ur[0, :n_sub]
+        src = rng.choice(max(n_sub, 1), m_sub) if n_sub else np.zeros(m_sub, np.int64)
+        idx = np.repeat(src, dup)[:max(m_sub * dup, 0)]
+        m = len(idx)
+        base = kf[idx] if n_sub else np.zeros(m, kf.dtype)
+        mp = dict(inview=(rng.random(m) < 0.95).astype(np.uint8),
+                  projx=(base["x"] + rng.normal(0, 1.0, m)).astype(np.float32), projy=(base["y"] + rng.normal(0, 1.0, m)).astype(np.float32),
+                  level=np.clip(base["octave"] + rng.integers(0, 2, m), 0, 7).astype(np.int32),
+                  viewcos=rng.choice([0.9, 0.9985, 0.999], m).astype(np.float32),
+                  desc=(df[idx].copy() if n_sub else np.zeros((m, 32), np.uint8)), obs=rng.integers(0, 3, m).astype(np.int32))
+        mp["projxr"] = (mp["projx"] - rng.uniform(0, 40, m)).astype(np.float32)
+        for i in range(m):                                   # rivals differ by a few bits: equal and near-equal distances
+            for bit in rng.integers(0, 256, rng.integers(0, 6)):
+                mp["desc"][i, bit >> 3] ^= np.uint8(1 << (bit & 7))
+        frame_obs = np.where(rng.random(n_sub) < 0.1, rng.integers(0, 3, n_sub), -1).astype(np.int32)
+        ras, rn, rfo = oracle.search_projection(k, d, u, w, h, scale, mp, th, 0.8, frame_obs)
+        gn, gas, gfo = gx.ORBmatcher(0.8, True).SearchByProjection(gx.Frame(k, d, w, h), u, scale, mp, th, frame_obs)
+        assert gn == rn and np.array_equal(gas, ras) and np.array_equal(gfo, rfo), (case, gn, rn)
+        total += rn
+    assert total > 500
+
+
+@FORMS
 @pytest.mark.parametrize("mode,th,ori", [(0, 15.0, True), (1, 7.0, True), (2, 15.0, False)])
 def test_search_by_projection_motion_model(gx, oracle, mode, th, ori, monkeypatch, form):
     """SearchByProjection(Current, Last): last-frame stereo points are back-projected to 3-D, moved by a
