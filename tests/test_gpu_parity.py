@@ -506,6 +506,46 @@ def test_search_by_projection_motion_model(gx, oracle, mode, th, ori, monkeypatc
     assert rn > 100
 
 
+@FORMS
+def test_search_by_projection_frame_contention(gx, oracle, monkeypatch, form):
+    """K9 under pressure: every last-frame point present six times over (nearly equal descriptors), so six map points want
+    each current keypoint, eight-pixel to thirty-pixel windows, claiming and non-claiming Observations() mixed; and tiny frames."""
+    _pick_form(monkeypatch, form)
+    cfg = synth.KITTI
+    w, h, nf, bf, fx = cfg["w"], cfg["h"], cfg["nfeatures"], cfg["bf"], cfg["fx"]
+    fy, cx, cy = fx, 607.19, 185.22
+    L, R, _ = synth.stereo_pair(97, w, h)
+    G = _ext(gx, w, h, nf, batch=2)
+    G.extract_batch(np.stack([L, R]))
+    ur, dp, nm = gx.ComputeStereoMatches(G, G, bf, fx, n=1, slotL0=0, slotR0=1)
+    (kl, dl), _ = G.fetch(0, 2)
+    z = dp[0, :len(kl)]
+    good = np.nonzero(z > 0)[0]
+    scale = G.GetScaleFactors()
+    cam = (fx, fy, cx, cy, bf)
+    Rcw = np.eye(3, dtype=np.float32); tcw = np.array([0.02, 0.0, -0.1], np.float32)
+    total = 0
+    for case, (n_cur, n_src, dup, th, mode) in enumerate([(len(kl), 330, 6, 15.0, 0), (len(kl), 200, 6, 7.0, 1), (40, 30, 5, 15.0, 2), (1, 8, 2, 15.0, 0), (700, 1, 1, 15.0, 0)]):
+        rng = np.random.default_rng(100 + case)
+        src = np.repeat(rng.choice(good, n_src), dup)
+        nl = len(src)
+        desc = dl[src].copy()
+        for i in range(nl):
+            for bit in rng.integers(0, 256, rng.integers(0, 5)):
+                desc[i, bit >> 3] ^= np.uint8(1 << (bit & 7))
+        last = dict(valid=(rng.random(nl) < 0.9).astype(np.uint8),
+                    xw=np.stack([(kl["x"][src] - cx) * z[src] / fx, (kl["y"][src] - cy) * z[src] / fy, z[src]], 1).astype(np.float32),
+                    octave=kl["octave"][src].astype(np.int32), angle=kl["angle"][src].astype(np.float32), desc=desc,
+                    obs=rng.integers(0, 3, nl).astype(np.int32))
+        kc, dc, uc = kl[:n_cur], dl[:n_cur], ur[0, :n_cur]
+        frame_obs = np.where(rng.random(n_cur) < 0.05, rng.integers(0, 3, n_cur), -1).astype(np.int32)
+        ras, rn, rfo = oracle.search_projection_frame(kc, dc, uc, w, h, scale, Rcw, tcw, cam, last, th, mode, True, frame_obs)
+        gn, gas, gfo = gx.ORBmatcher(0.9, True).SearchByProjectionFrame(gx.Frame(kc, dc, w, h), uc, scale, Rcw, tcw, cam, last, th, mode, frame_obs)
+        assert gn == rn and np.array_equal(gas, ras) and np.array_equal(gfo, rfo), (case, gn, rn)
+        total += rn
+    assert total > 300
+
+
 def test_euroc_shard_of_512_frames(gx, oracle):
     """BASELINE config 3: one GPU's contiguous 512-frame shard of the 4096-frame EuRoC-shaped sequence,
     processed in 4 batches of 128 stereo pairs.  Distinct frames are checked against the oracle; the
