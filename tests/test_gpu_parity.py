@@ -343,6 +343,34 @@ def test_knn_ratio_bruteforce(gx, oracle):
     assert n1 == 0 and g.tolist() == [-1]
 
 
+@FORMS
+def test_search_for_initialization_contention(gx, oracle, monkeypatch, form):
+    """K6 under pressure: every frame-1 keypoint present five times with a few flipped descriptor bits, so rivals keep taking
+    frame-2 features from each other (vnMatches21 steals, vMatchedDistance skips) inside and across the 32-query passes;
+    windows of 100, 30 and 8 px; frames of 0, 1 and 33 keypoints."""
+    _pick_form(monkeypatch, form)
+    w, h = 640, 480
+    G = _ext(gx, w, h, 1000)
+    a, b, _ = synth.mono_pair(64, w, h)
+    k1, d1 = G(a); k2, d2 = G(b)
+    rng = np.random.default_rng(77)
+    total = 0
+    for case, (n1, dup, n2, win) in enumerate([(len(k1), 5, len(k2), 100), (300, 5, len(k2), 30), (len(k1), 3, 400, 8), (33, 2, 1, 100), (1, 1, 33, 100), (0, 1, 50, 100), (50, 1, 0, 100)]):
+        src = np.repeat(np.arange(n1), dup)
+        ka, da = k1[src].copy(), d1[src].copy()
+        for i in range(len(src)):
+            for bit in rng.integers(0, 256, rng.integers(0, 4)):
+                da[i, bit >> 3] ^= np.uint8(1 << (bit & 7))
+        kb, db = k2[:n2], d2[:n2]
+        prev = np.stack([ka["x"], ka["y"]], 1).astype(np.float32)
+        rm12, rn, rprev = oracle.search_init(ka, da, kb, db, w, h, prev.copy(), 0.9, win, True)
+        p2 = prev.copy()
+        gn, g12 = gx.ORBmatcher(0.9, True).SearchForInitialization(gx.Frame(ka, da, w, h), gx.Frame(kb, db, w, h), p2, win)
+        assert gn == rn and np.array_equal(g12, rm12) and np.array_equal(p2, rprev), (case, gn, rn)
+        total += rn
+    assert total > 50
+
+
 @pytest.mark.parametrize("th,ratio,strict", [(50, 0.75, True), (50, 0.95, False), (100, 0.9, False), (255, 0.999, False), (30, 0.2, True), (255, 1.5, False)])
 def test_knn_ratio_crowded_neighbourhoods(gx, oracle, th, ratio, strict):
     """K7's ordered resolve under pressure: groups of identical queries facing ladders of near-copies in B
