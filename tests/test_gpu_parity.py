@@ -914,7 +914,7 @@ def test_cuda_keyframe_searches_reproduce_reference(gx, monkeypatch, form):
 
 
 @FORMS
-def test_cuda_fuse_and_sim3_reproduce_reference(gx, monkeypatch, form):
+def test_cuda_fuse_and_sim3_reproduce_reference(gx, oracle, monkeypatch, form):
     """K16 against ORBmatcher::Fuse (search) and ORBmatcher::SearchBySim3 of the REFERENCE on real KeyFrames and MapPoints
     (tests/golden/ref_kf_*.npz): frames, stereo, the feature grid (K10) come from the CUDA path, MapPoint fields from the fixture."""
     _pick_form(monkeypatch, form)
@@ -960,6 +960,21 @@ def test_cuda_fuse_and_sim3_reproduce_reference(gx, monkeypatch, form):
         n, a = gx.ORBmatcher(0.9, case["check_ori"]).SearchByProjectionOrdered(FG, 1, d2, (0.0, float(w), 0.0, float(h)), R2, t2, fx["reloc_Ow"], gs.KITTI_CAM, scale,
                                                                                  float(fx["log_scale"]), occ, mpr, 10.0, 100, True)
         assert n == case["n_proj_kf"] and np.array_equal(a, np.where(fx["proj_kf"] >= 0, fx["proj_kf"], -1))
+        # K17 under contention: every map point six times over with a few flipped bits, so six rivals want each keypoint - more than
+        # a candidate list holds (re-scans) and several per 32-point round (fixpoint iterations); against the CPU oracle
+        rng = np.random.default_rng(5)
+        dup = {key: np.repeat(np.asarray(v), 6, axis=0) for key, v in mpr.items()}
+        dup["desc"] = dup["desc"].copy()
+        for i in range(len(dup["desc"])):
+            for bit in rng.integers(0, 256, rng.integers(0, 5)):
+                dup["desc"][i, bit >> 3] ^= np.uint8(1 << (bit & 7))
+        fb = (0.0, float(w), 0.0, float(h))
+        for reloc, Rm, tm, Om, kb, thd in [(False, Rcw, tcw, Ow, tuple(fx["kf_bounds"]), 50), (True, R2, t2, fx["reloc_Ow"], fb, 100)]:
+            kfv = (*gs.KITTI_CAM, cfg["bf"], float(fx["log_scale"]), *kb)
+            ra, rn = oracle.project_match_ordered(FG.mvKeysUn[1], d2, kfv, fb, scale, reloc, Rm, tm, Om, dup, 10.0, thd, case["check_ori"], occ)
+            n, a = gx.ORBmatcher(0.9, case["check_ori"]).SearchByProjectionOrdered(FG, 1, d2, kb, Rm, tm, Om, gs.KITTI_CAM, scale, float(fx["log_scale"]), occ, dup, 10.0, thd, reloc)
+            assert n == rn and np.array_equal(a, ra), (reloc, n, rn)
+            assert rn > 100
 
 
 def test_stereo_direct_device_outputs_wider_than_kp_cap(gx, oracle):
