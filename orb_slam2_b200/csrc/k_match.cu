@@ -1789,29 +1789,50 @@ __global__ void __launch_bounds__(kBowLatThreads) k_search_by_bow_lat(BowArgs a,
     nlist += total;
     __syncthreads();
   }
-  // 2b. a thread per LISTED entry: the four nearest free features of its run.  Neighbouring entries mostly share a node, so the
-  // lanes of a warp walk the same run and a B descriptor is one broadcast read for all of them.
-  for (int c = tid; c < nlist; c += nth) {
-    const int t = slist[c];
-    const int i = (int)(keyA[t] & 0xffffffffu);
-    const uint32_t rr = srun[t];
+  // 2b. FOUR threads per LISTED entry, each walking every fourth feature of the run (a walk is a chain of dependent
+  // shared-memory reads, ~400 cycles per feature: splitting it four ways is worth more than the merge costs), then the four
+  // sorted lists of a quad are merged by shuffles.  Neighbouring entries mostly share a node, so the lanes of a warp read
+  // the same few B descriptors.
+  for (int c0 = 0; c0 < nlist; c0 += nth / 4) {
+    const int c = c0 + (tid >> 2), sub = tid & 3;
     uint32_t l0 = kNoKey, l1 = kNoKey, l2 = kNoKey, l3 = kNoKey;
     int cnt = 0;
-    const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8) + 1);
-    const uint32_t q[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-    for (int e = (int)(rr & 0xFFFFu); e < (int)(rr >> 16); ++e) {
-      const int j = (int)(keyB[e] & 0xffffffffu);
-      if (bit_of(used, j)) continue;
-      const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
-      const int d = ham256_csa(q, b0, b1);                                          // 4 POPC per distance instead of 8: POPC is the slow pipe
-      uint32_t kk = ((uint32_t)d << 16) | (uint32_t)j;                              // sorted insertion into (l0 <= l1 <= l2 <= l3)
-      ++cnt;
-      if (kk < l0) { const uint32_t sw = l0; l0 = kk; kk = sw; }
-      if (kk < l1) { const uint32_t sw = l1; l1 = kk; kk = sw; }
-      if (kk < l2) { const uint32_t sw = l2; l2 = kk; kk = sw; }
-      if (kk < l3) l3 = kk;
+    if (c < nlist) {
+      const int t = slist[c];
+      const int i = (int)(keyA[t] & 0xffffffffu);
+      const uint32_t rr = srun[t];
+      const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(dA + (size_t)i * 8) + 1);
+      const uint32_t q[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+      for (int e = (int)(rr & 0xFFFFu) + sub; e < (int)(rr >> 16); e += 4) {
+        const int j = (int)(keyB[e] & 0xffffffffu);
+        if (bit_of(used, j)) continue;
+        const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
+        const int d = ham256_csa(q, b0, b1);                                        // 4 POPC per distance instead of 8: POPC is the slow pipe
+        uint32_t kk = ((uint32_t)d << 16) | (uint32_t)j;                            // sorted insertion into (l0 <= l1 <= l2 <= l3)
+        ++cnt;
+        if (kk < l0) { const uint32_t sw = l0; l0 = kk; kk = sw; }
+        if (kk < l1) { const uint32_t sw = l1; l1 = kk; kk = sw; }
+        if (kk < l2) { const uint32_t sw = l2; l2 = kk; kk = sw; }
+        if (kk < l3) l3 = kk;
+      }
     }
-    spec[c] = make_uint4(l0 | (cnt <= 4 ? 0x80000000u : 0u), l1, l2, l3);          // no candidate: every key kNoKey, nothing to decide
+    // merge within the quad (lanes 4q .. 4q+3): after two exchange steps every lane holds the four smallest keys of the entry
+#pragma unroll
+    for (int step = 1; step <= 2; step <<= 1) {
+      const uint32_t p0 = __shfl_xor_sync(0xffffffffu, l0, step), p1 = __shfl_xor_sync(0xffffffffu, l1, step);
+      const uint32_t p2 = __shfl_xor_sync(0xffffffffu, l2, step), p3 = __shfl_xor_sync(0xffffffffu, l3, step);
+      cnt += __shfl_xor_sync(0xffffffffu, cnt, step);
+      const uint32_t in[4] = {p0, p1, p2, p3};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        uint32_t kk = in[u];
+        if (kk < l0) { const uint32_t sw = l0; l0 = kk; kk = sw; }
+        if (kk < l1) { const uint32_t sw = l1; l1 = kk; kk = sw; }
+        if (kk < l2) { const uint32_t sw = l2; l2 = kk; kk = sw; }
+        if (kk < l3) l3 = kk;
+      }
+    }
+    if (c < nlist && sub == 0) spec[c] = make_uint4(l0 | (cnt <= 4 ? 0x80000000u : 0u), l1, l2, l3);   // no candidate: every key kNoKey, nothing to decide
   }
   __syncthreads();
   // 3. ordered phase, a piece of the list per warp, cut at node boundaries
@@ -2135,50 +2156,64 @@ __global__ void __launch_bounds__(kTriLatThreads) k_search_triangulation_lat(Tri
   ORBX_STAT(int dbg_cand = 0;)
   // this CTA's share of the sorted KF1 features: a contiguous piece (neighbouring threads keep walking the same runs)
   const int piece = (((n1 + G - 1) / G) + 31) & ~31, t_lo = g * piece, t_hi = min(n1, t_lo + piece);
-  for (int t = t_lo + tid; t < t_hi; t += nth) {
-    int best2 = -1;
-    const unsigned long long ka = keyA[t];
-    const int i = (int)(ka & 0xffffffffu);
-    const uint32_t node = (uint32_t)(ka >> 32);
-    // every field of the KF1 feature is requested before the first test
-    const bool st1 = a.uR1[po + i] >= 0.f;
-    const int has1 = a.hasMp1[po + i];
-    const orbx_keypoint kp1 = k1[i];
-    const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8) + 1);
-    const uint32_t qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-    if (!has1 && !(a.onlyStereo && !st1)) {
-      int lo = 0, hi = n2;                                                          // first entry with node2 >= node
-      while (lo < hi) { const int mid = (lo + hi) >> 1; if ((uint32_t)(keyB[mid] >> 32) < node) lo = mid + 1; else hi = mid; }
-      const float la = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[0]), __fmul_rn(kp1.y, s_F[3])), s_F[6]);
-      const float lb = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[1]), __fmul_rn(kp1.y, s_F[4])), s_F[7]);
-      const float lc = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[2]), __fmul_rn(kp1.y, s_F[5])), s_F[8]);
-      const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
-      int bestDist = 50;                                                            // TH_LOW
-      for (int e = lo; e < n2 && (uint32_t)(keyB[e] >> 32) == node; ++e) {
-        ORBX_STAT(++dbg_cand;)
-        const int j = (int)(keyB[e] & 0xffffffffu);
-        const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
-        const int dist = ham256_csa(qv, b0, b1);                                    // 4 POPC per distance instead of 8: POPC is the slow pipe
-        if (dist > 50 || dist > bestDist) continue;
-        if (bit_of(hasb, j)) continue;
-        const bool st2 = bit_of(stb, j);
-        if (a.onlyStereo && !st2) continue;
-        const float2 p2 = sxy[j];
-        const int o2 = soct[j];
-        if (!st1 && !st2) {
-          const float dx = __fsub_rn(ex, p2.x), dy = __fsub_rn(ey, p2.y);
-          if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, a.scale2[o2])) continue;
+  // FOUR threads per KF1 feature, each walking every fourth KF2 feature of the run (the walk is a chain of dependent
+  // shared-memory reads); the winner - least distance, the LAST such candidate in index order - is order-independent, so the
+  // four partial winners are merged by the key  distance << 16 | (65535 - j).
+  for (int t0 = t_lo; t0 < t_hi; t0 += nth / 4) {
+    const int t = t0 + (tid >> 2), sub = tid & 3;
+    uint32_t win = 0xffffffffu;
+    int i = 0;
+    float ang1 = 0.f;
+    if (t < t_hi) {
+      const unsigned long long ka = keyA[t];
+      i = (int)(ka & 0xffffffffu);
+      const uint32_t node = (uint32_t)(ka >> 32);
+      // every field of the KF1 feature is requested before the first test
+      const bool st1 = a.uR1[po + i] >= 0.f;
+      const int has1 = a.hasMp1[po + i];
+      const orbx_keypoint kp1 = k1[i];
+      ang1 = kp1.angle;
+      const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8)), q1 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i * 8) + 1);
+      const uint32_t qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+      if (!has1 && !(a.onlyStereo && !st1)) {
+        int lo = 0, hi = n2;                                                        // first entry with node2 >= node
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if ((uint32_t)(keyB[mid] >> 32) < node) lo = mid + 1; else hi = mid; }
+        const float la = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[0]), __fmul_rn(kp1.y, s_F[3])), s_F[6]);
+        const float lb = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[1]), __fmul_rn(kp1.y, s_F[4])), s_F[7]);
+        const float lc = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, s_F[2]), __fmul_rn(kp1.y, s_F[5])), s_F[8]);
+        const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+        int bestDist = 50;                                                          // TH_LOW
+        for (int e = lo + sub; e < n2 && (uint32_t)(keyB[e] >> 32) == node; e += 4) {
+          ORBX_STAT(++dbg_cand;)
+          const int j = (int)(keyB[e] & 0xffffffffu);
+          const uint4 b0 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8), b1 = *reinterpret_cast<const uint4*>(Bs + (size_t)j * 8 + 4);
+          const int dist = ham256_csa(qv, b0, b1);                                  // 4 POPC per distance instead of 8: POPC is the slow pipe
+          if (dist > 50 || dist > bestDist) continue;
+          if (bit_of(hasb, j)) continue;
+          const bool st2 = bit_of(stb, j);
+          if (a.onlyStereo && !st2) continue;
+          const float2 p2 = sxy[j];
+          const int o2 = soct[j];
+          if (!st1 && !st2) {
+            const float dx = __fsub_rn(ex, p2.x), dy = __fsub_rn(ey, p2.y);
+            if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, a.scale2[o2])) continue;
+          }
+          if (den == 0.f) continue;
+          const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, p2.x), __fmul_rn(lb, p2.y)), lc);
+          const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+          if ((double)dsqr < __dmul_rn(3.84, (double)a.sigma2_2[o2])) { win = ((uint32_t)dist << 16) | (uint32_t)(65535 - j); bestDist = dist; }
         }
-        if (den == 0.f) continue;
-        const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, p2.x), __fmul_rn(lb, p2.y)), lc);
-        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
-        if ((double)dsqr < __dmul_rn(3.84, (double)a.sigma2_2[o2])) { best2 = j; bestDist = dist; }
       }
     }
-    m12[i] = best2;
-    if (best2 >= 0) {
-      ++nm;
-      if (a.checkOri) { const int bin = rot_bin(kp1.angle, k2[best2].angle); a.bins[po + i] = (uint8_t)bin; atomicAdd(&s_hist[bin], 1); }
+    win = min(win, __shfl_xor_sync(0xffffffffu, win, 1));
+    win = min(win, __shfl_xor_sync(0xffffffffu, win, 2));
+    if (t < t_hi && sub == 0) {
+      const int best2 = win == 0xffffffffu ? -1 : 65535 - (int)(win & 0xFFFFu);
+      m12[i] = best2;
+      if (best2 >= 0) {
+        ++nm;
+        if (a.checkOri) { const int bin = rot_bin(ang1, k2[best2].angle); a.bins[po + i] = (uint8_t)bin; atomicAdd(&s_hist[bin], 1); }
+      }
     }
   }
   ORBX_CLK(t3w);
