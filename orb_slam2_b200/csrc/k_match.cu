@@ -1684,16 +1684,14 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long* k0, unsigne
   __syncthreads();
   for (int k = 64; k <= n; k <<= 1) {
     for (int jj = k >> 1; jj >= 32; jj >>= 1) {
-      for (int i = tid; i < n; i += nth) {
-        const int l = i ^ jj;
-        if (l > i) {
-          const bool up = (i & k) == 0;
+      for (int q = tid; q < (n >> 1); q += nth) {             // one compare-exchange PAIR per thread and trip: nobody idles
+        const int i = ((q & ~(jj - 1)) << 1) | (q & (jj - 1)), l = i | jj;
+        const bool up = (i & k) == 0;
 #pragma unroll
-          for (int arr = 0; arr < NARR; ++arr) {
-            unsigned long long* key = arr ? k1 : k0;
-            const unsigned long long x = key[i], y = key[l];
-            if ((x > y) == up) { key[i] = y; key[l] = x; }
-          }
+        for (int arr = 0; arr < NARR; ++arr) {
+          unsigned long long* key = arr ? k1 : k0;
+          const unsigned long long x = key[i], y = key[l];
+          if ((x > y) == up) { key[i] = y; key[l] = x; }
         }
       }
       __syncthreads();
