@@ -146,10 +146,9 @@ __host__ __device__ inline size_t ps_lat_bytes(int cap, bool with_ur) {
   return b + (size_t)kPsLatThreads * (20 + 2);              // the block's windows {u, v, ur, radius, packed} and its list
 }
 
-__global__ void __launch_bounds__(kPsLatThreads) k_project_search_lat(ProjSearchArgs a) {
-  extern __shared__ __align__(16) uint8_t smem[];
+__device__ __forceinline__ void project_search_problem(const ProjSearchArgs& a, const int p, uint8_t* smem) {
   __shared__ int s_bcnt[kPsLatThreads / 32];
-  const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x, nwarps = nth >> 5;
   const int m = min(a.m[p], a.mcap);
   const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
   const bool gate = (a.mode & 8) != 0;
@@ -279,6 +278,59 @@ __global__ void __launch_bounds__(kPsLatThreads) k_project_search_lat(ProjSearch
     }
     __syncthreads();                                            // the block's windows are free again
   }
+}
+
+__global__ void __launch_bounds__(kPsLatThreads) k_project_search_lat(ProjSearchArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  project_search_problem(a, blockIdx.x, smem);
+}
+
+// SearchBySim3 in ONE launch: CTA 2p searches keyframe pair p's map points 1 -> 2, CTA 2p + 1 the other way; each scatters its
+// winners to the per-keypoint table vnMatch (src/ORBmatcher.cc:1215,1295), and the CTA of a pair that finishes second does the
+// agreement check (:1303-1323).  ticket[p] starts at -1 (it shares the 0xFF memset of the vnMatch tables).
+struct Sim3LatArgs { ProjSearchArgs pass[2]; const int* mp_index[2]; int* vn[2]; int* ticket; const int* n1; int* matches12; int* nfound; };
+
+__global__ void __launch_bounds__(kPsLatThreads) k_sim3_lat(const __grid_constant__ Sim3LatArgs A) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ int s_last, s_cnt;
+  const int p = blockIdx.x >> 1, dir = blockIdx.x & 1, tid = threadIdx.x;
+  const ProjSearchArgs& a = A.pass[dir];
+  project_search_problem(a, p, smem);                          // ends with a block barrier: a.best of this problem is complete (written by this CTA)
+  const int m = min(a.m[p], a.mcap), cap = a.cap;
+  int* vn = A.vn[dir] + (size_t)p * cap;
+  for (int i = tid; i < m; i += blockDim.x) {
+    const int kpi = A.mp_index[dir][(size_t)p * a.mcap + i];
+    if (kpi >= 0 && kpi < cap) vn[kpi] = a.best[(size_t)p * a.mcap + i];
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) { s_last = atomicAdd(A.ticket + p, 1) == 0; s_cnt = 0; }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int* v1 = A.vn[0] + (size_t)p * cap; const int* v2 = A.vn[1] + (size_t)p * cap;
+  int found = 0;
+  for (int i1 = tid; i1 < cap; i1 += blockDim.x) {
+    const int idx2 = __ldcg(v1 + i1);
+    int res = -1;
+    if (i1 < A.n1[p] && idx2 >= 0 && idx2 < cap && __ldcg(v2 + idx2) == i1) { res = idx2; ++found; }
+    A.matches12[(size_t)p * cap + i1] = res;
+  }
+  if (found) atomicAdd(&s_cnt, found);
+  __syncthreads();
+  if (tid == 0) A.nfound[p] = s_cnt;
+}
+
+int launch_sim3_lat(const ProjSearchArgs& a0, const ProjSearchArgs& a1, const int* idx0, const int* idx1, int* vn0, int* vn1, int* ticket, const int* n1,
+                    int* matches12, int* nfound, cudaStream_t st) {
+  const size_t lat = ps_lat_bytes(a0.cap, false);
+  if (!(lat <= 200 * 1024 && a0.cap < (1 << 24)) || getenv("ORBX_PROJ_SERIAL")) return 0;      // the caller takes the five-launch route
+  Sim3LatArgs A;
+  A.pass[0] = a0; A.pass[1] = a1; A.mp_index[0] = idx0; A.mp_index[1] = idx1; A.vn[0] = vn0; A.vn[1] = vn1; A.ticket = ticket; A.n1 = n1;
+  A.matches12 = matches12; A.nfound = nfound;
+  cudaFuncSetAttribute(k_sim3_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
+  k_sim3_lat<<<a0.n_problems * 2, kPsLatThreads, lat, st>>>(A);
+  return 1;
 }
 
 // SearchBySim3's agreement check (src/ORBmatcher.cc:1303-1323): vnMatch1 / vnMatch2 are indexed by keypoint

@@ -1172,8 +1172,9 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
   const float* d_gb; CU(sg.in(grid_bounds, 6, on_device, &d_gb));
   int* d_vn[2]; int* d_best[2]; const int* d_idx[2]; const int* d_m[2];
   const int* d_n1; CU(sg.in(n1, np, on_device, &d_n1));
-  CU(sg.alloc((void**)&d_vn[0], 2 * kc * 4)); d_vn[1] = d_vn[0] + kc;
-  CU(cudaMemsetAsync(d_vn[0], 0xFF, 2 * kc * 4, st));
+  CU(sg.alloc((void**)&d_vn[0], (2 * kc + np) * 4)); d_vn[1] = d_vn[0] + kc;
+  int* d_ticket = d_vn[0] + 2 * kc;                                      // -1 per pair: shares the 0xFF fill of the two vnMatch tables
+  CU(cudaMemsetAsync(d_vn[0], 0xFF, (2 * kc + np) * 4, st));
   // pass 0: map points of keyframe 1 into keyframe 2 (R1w, t1w then sR21, t21); pass 1: the other way (R2w, t2w then sR12, t12).
   // Everything both passes read is staged first and goes up in one copy; then the five launches.
   ProjSearchArgs pa[2];
@@ -1215,13 +1216,17 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
   g.match1 = d_vn[0]; g.match2 = d_vn[1]; g.n1 = d_n1; g.cap = cap;
   if (on_device) { g.matches12 = matches12; g.nfound = n_found; }
   else { CU(sg.alloc((void**)&g.matches12, kc * 4)); CU(sg.alloc((void**)&g.nfound, np * 4)); }
-  CU(cudaMemsetAsync(g.nfound, 0, np * 4, st));
   CU(sg.upload());
-  for (int pass = 0; pass < 2; ++pass) {
-    g_launches += launch_project_search(pa[pass], st);
-    g_launches += launch_scatter_matches(d_best[pass], d_idx[pass], d_m[pass], mcap, cap, n_pairs, d_vn[pass], st);
+  const int fused = launch_sim3_lat(pa[0], pa[1], d_idx[0], d_idx[1], d_vn[0], d_vn[1], d_ticket, d_n1, g.matches12, g.nfound, st);
+  g_launches += fused;
+  if (!fused) {
+    CU(cudaMemsetAsync(g.nfound, 0, np * 4, st));
+    for (int pass = 0; pass < 2; ++pass) {
+      g_launches += launch_project_search(pa[pass], st);
+      g_launches += launch_scatter_matches(d_best[pass], d_idx[pass], d_m[pass], mcap, cap, n_pairs, d_vn[pass], st);
+    }
+    g_launches += launch_sim3_agree(g, n_pairs, st);
   }
-  g_launches += launch_sim3_agree(g, n_pairs, st);
   CU(cudaGetLastError());
   if (!on_device) {
     CU(sg.d2h(matches12, g.matches12, kc * 4));

@@ -194,6 +194,9 @@ int launch_project_search(const ProjSearchArgs& a, cudaStream_t st);
 int launch_scatter_matches(const int* best, const int* mp_index, const int* m, int mcap, int cap, int n_problems, int* vn, cudaStream_t st);
 struct Sim3AgreeArgs { const int* match1; const int* match2; const int* n1; int cap; int* matches12; int* nfound; };
 int launch_sim3_agree(const Sim3AgreeArgs& a, int n_problems, cudaStream_t st);
+// SearchBySim3 in one launch (both passes, scatter, agreement); returns 0 when the 1024-thread form does not fit: use the five launches
+int launch_sim3_lat(const ProjSearchArgs& a0, const ProjSearchArgs& a1, const int* idx0, const int* idx1, int* vn0, int* vn1, int* ticket, const int* n1,
+                    int* matches12, int* nfound, cudaStream_t st);
 
 struct ProjOrderedArgs {
   const orbx_keypoint* kps; const uint8_t* desc; const int* n;                          // targets, [P][cap]
