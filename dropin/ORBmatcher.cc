@@ -100,24 +100,14 @@ struct Flat {
   }
 };
 
-// mGrid as CSR, rebuilt from mvKeysUn with Frame::PosInGrid's rule and the static bounds every Frame shares
-// (src/Frame.cc:230-245, 382-392): cell = ix*48 + iy, features in index order.
+// The projection searches walk mGrid.  The library rebuilds it from mvKeysUn with Frame::PosInGrid's rule and the static bounds
+// every Frame shares (src/Frame.cc:230-245, 382-392) inside the kernel, so no grid is flattened here: NULL is passed for it.
 struct Grid {
-  std::vector<int> cell_start, cell_items;
   float bounds[6];
-  explicit Grid(const Flat& f) : cell_start(ORBX_GRID_COLS * ORBX_GRID_ROWS + 1, 0), cell_items(f.cap, 0) {
+  const int* cell_start = nullptr; const int* cell_items = nullptr;
+  explicit Grid(const Flat&) {
     bounds[0] = Frame::mnMinX; bounds[1] = Frame::mnMaxX; bounds[2] = Frame::mnMinY; bounds[3] = Frame::mnMaxY;
     bounds[4] = Frame::mfGridElementWidthInv; bounds[5] = Frame::mfGridElementHeightInv;
-    std::vector<int> cell(f.n, -1);
-    for (int i = 0; i < f.n; ++i) {
-      const int gx = (int)round((f.kps[i].x - bounds[0]) * bounds[4]), gy = (int)round((f.kps[i].y - bounds[2]) * bounds[5]);
-      if (gx < 0 || gx >= ORBX_GRID_COLS || gy < 0 || gy >= ORBX_GRID_ROWS) continue;
-      cell[i] = gx * ORBX_GRID_ROWS + gy;
-      ++cell_start[cell[i] + 1];
-    }
-    for (size_t c = 1; c < cell_start.size(); ++c) cell_start[c] += cell_start[c - 1];
-    std::vector<int> cur(cell_start.begin(), cell_start.end() - 1);
-    for (int i = 0; i < f.n; ++i) if (cell[i] >= 0) cell_items[cur[cell[i]]++] = i;
   }
 };
 
@@ -239,7 +229,7 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set
   pose12(Rcw, tcw, pose);
   std::vector<int> assigned(f.cap, -1);
   int nm = 0;
-  check(orbx_search_projection_ordered_batch(f.kps.data(), f.desc.data(), &f.n, 1, f.cap, g.bounds, g.cell_start.data(), g.cell_items.data(), g.bounds, pose, ow,
+  check(orbx_search_projection_ordered_batch(f.kps.data(), f.desc.data(), &f.n, 1, f.cap, g.bounds, g.cell_start, g.cell_items, g.bounds, pose, ow,
                                              CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx, CurrentFrame.cy, CurrentFrame.mvScaleFactors.data(),
                                              CurrentFrame.mnScaleLevels, CurrentFrame.mfLogScaleFactor, occupied.data(), mps.valid.data(), mps.xw.data(),
                                              mps.normal.data(), mps.dmin.data(), mps.dmax.data(), mps.desc.data(), mps.angle.data(), &mps.m, mps.cap, th,
@@ -266,7 +256,7 @@ int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapP
   pose12(Rcw, tcw, pose);
   std::vector<int> assigned(f.cap, -1);
   int nm = 0;
-  check(orbx_search_projection_ordered_batch(f.kps.data(), f.desc.data(), &f.n, 1, f.cap, g.bounds, g.cell_start.data(), g.cell_items.data(), kfb, pose, ow, pKF->fx,
+  check(orbx_search_projection_ordered_batch(f.kps.data(), f.desc.data(), &f.n, 1, f.cap, g.bounds, g.cell_start, g.cell_items, kfb, pose, ow, pKF->fx,
                                              pKF->fy, pKF->cx, pKF->cy, pKF->mvScaleFactors.data(), pKF->mnScaleLevels, pKF->mfLogScaleFactor, occupied.data(),
                                              mps.valid.data(), mps.xw.data(), mps.normal.data(), mps.dmin.data(), mps.dmax.data(), mps.desc.data(),
                                              mps.angle.data(), &mps.m, mps.cap, (float)th, TH_LOW, 0, 0, assigned.data(), &nm, 0, nullptr));
@@ -395,8 +385,8 @@ int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& 
   const float kb2[4] = {(float)pKF2->mnMinX, (float)pKF2->mnMaxX, (float)pKF2->mnMinY, (float)pKF2->mnMaxY};
   std::vector<int> m12(cap, -1);
   int nfound = 0;
-  check(orbx_search_by_sim3_batch(a.kps.data(), a.desc.data(), &a.n, g1.cell_start.data(), g1.cell_items.data(), kb1, pose1, b.kps.data(), b.desc.data(), &b.n,
-                                  g2.cell_start.data(), g2.cell_items.data(), kb2, pose2, 1, cap, g1.bounds, pKF1->fx, pKF1->fy, pKF1->cx, pKF1->cy,
+  check(orbx_search_by_sim3_batch(a.kps.data(), a.desc.data(), &a.n, g1.cell_start, g1.cell_items, kb1, pose1, b.kps.data(), b.desc.data(), &b.n,
+                                  g2.cell_start, g2.cell_items, kb2, pose2, 1, cap, g1.bounds, pKF1->fx, pKF1->fy, pKF1->cx, pKF1->cy,
                                   pKF2->mvScaleFactors.data(), pKF2->mnScaleLevels, pKF2->mfLogScaleFactor, xf, i1.data(), m1.xw.data(), m1.dmin.data(),
                                   m1.dmax.data(), m1.desc.data(), &m1.m, i2.data(), m2.xw.data(), m2.dmin.data(), m2.dmax.data(), m2.desc.data(), &m2.m, mcap, th,
                                   m12.data(), &nfound, 0, nullptr));
@@ -419,7 +409,7 @@ int ORBmatcher::Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const 
   const float ow[3] = {Ow.at<float>(0), Ow.at<float>(1), Ow.at<float>(2)};
   const float kfb[4] = {(float)pKF->mnMinX, (float)pKF->mnMaxX, (float)pKF->mnMinY, (float)pKF->mnMaxY};
   std::vector<int> best(mps.cap, -1);
-  check(orbx_fuse_search_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, g.bounds, g.cell_start.data(), g.cell_items.data(), kfb, pose, ow, pKF->fx,
+  check(orbx_fuse_search_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, g.bounds, g.cell_start, g.cell_items, kfb, pose, ow, pKF->fx,
                                pKF->fy, pKF->cx, pKF->cy, pKF->mbf, pKF->mvScaleFactors.data(), pKF->mvInvLevelSigma2.data(), pKF->mnScaleLevels,
                                pKF->mfLogScaleFactor, mps.valid.data(), mps.xw.data(), mps.normal.data(), mps.dmin.data(), mps.dmax.data(), mps.desc.data(), &mps.m,
                                mps.cap, th, 0, best.data(), 0, nullptr));
@@ -457,7 +447,7 @@ int ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoin
   const float ow[3] = {Ow.at<float>(0), Ow.at<float>(1), Ow.at<float>(2)};
   const float kfb[4] = {(float)pKF->mnMinX, (float)pKF->mnMaxX, (float)pKF->mnMinY, (float)pKF->mnMaxY};
   std::vector<int> best(mps.cap, -1);
-  check(orbx_fuse_search_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, g.bounds, g.cell_start.data(), g.cell_items.data(), kfb, pose, ow, pKF->fx,
+  check(orbx_fuse_search_batch(f.kps.data(), f.desc.data(), f.uright.data(), &f.n, 1, f.cap, g.bounds, g.cell_start, g.cell_items, kfb, pose, ow, pKF->fx,
                                pKF->fy, pKF->cx, pKF->cy, pKF->mbf, pKF->mvScaleFactors.data(), pKF->mvInvLevelSigma2.data(), pKF->mnScaleLevels,
                                pKF->mfLogScaleFactor, mps.valid.data(), mps.xw.data(), mps.normal.data(), mps.dmin.data(), mps.dmax.data(), mps.desc.data(), &mps.m,
                                mps.cap, th, 1, best.data(), 0, nullptr));

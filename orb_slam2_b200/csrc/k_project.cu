@@ -152,7 +152,7 @@ __device__ __forceinline__ void project_search_problem(const ProjSearchArgs& a, 
   const int m = min(a.m[p], a.mcap);
   const size_t ko = (size_t)p * a.cap, mo = (size_t)p * a.mcap;
   const bool gate = (a.mode & 8) != 0;
-  int* cs = reinterpret_cast<int*>(smem);
+  int* cs = reinterpret_cast<int*>(smem);                       // cell starts (a copy of the caller's, or built here: then shifted by one)
   uint32_t* sdesc = reinterpret_cast<uint32_t*>(smem + (size_t)(kPCells + 1 + 3) / 4 * 16);     // [cap][8] by keypoint
   float2* sxy = reinterpret_cast<float2*>(sdesc + (size_t)a.cap * 8);                           // [cap] in CSR order
   uint32_t* smeta = reinterpret_cast<uint32_t*>(sxy + a.cap);                                   // [cap] octave << 24 | keypoint, CSR order
@@ -163,17 +163,24 @@ __device__ __forceinline__ void project_search_problem(const ProjSearchArgs& a, 
   uint16_t* slist = reinterpret_cast<uint16_t*>(spack + kPsLatThreads);                         // [1024] block-relative indices that have a window
   {
     const orbx_keypoint* kps = a.kps + ko;
-    const int* gcs = a.cell_start + (size_t)p * (kPCells + 1);
-    const int* items = a.cell_items + ko;
-    for (int i = tid; i <= kPCells; i += nth) cs[i] = gcs[i];
-    const int n_items = min(gcs[kPCells], a.cap);
-    for (int e = tid; e < n_items; e += nth) {
-      const int idx = items[e];
-      const orbx_keypoint kp = kps[idx];
-      sxy[e] = make_float2(kp.x, kp.y);
-      smeta[e] = ((uint32_t)kp.octave << 24) | (uint32_t)idx;
-      if (gate) sur[idx] = a.u_right[ko + idx];
+    const float* gbs = a.grid_bounds;
+    if (a.cell_start) {                                         // the caller's CSR grid (K10's output)
+      const int* gcs = a.cell_start + (size_t)p * (kPCells + 1);
+      const int* items = a.cell_items + ko;
+      for (int i = tid; i <= kPCells; i += nth) cs[i] = gcs[i];
+      const int n_items = min(gcs[kPCells], a.cap);
+      for (int e = tid; e < n_items; e += nth) {
+        const int idx = items[e];
+        const orbx_keypoint kp = kps[idx];
+        const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, gbs[0]), gbs[4])), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, gbs[2]), gbs[5]));
+        sxy[e] = make_float2(kp.x, kp.y);
+        smeta[e] = ((uint32_t)kp.octave << 28) | ((uint32_t)(gx * kPGridRows + gy) << 16) | (uint32_t)idx;
+      }
+    } else {                                                    // no grid given: built here from all `cap` keypoint slots the caller filled (n)
+      grid_sort_cta(kps, a.n ? min(a.n[p], a.cap) : a.cap, gbs[0], gbs[2], gbs[4], gbs[5], cs, sxy, smeta);
+      cs += 1;
     }
+    if (gate) for (int i = tid; i < a.cap; i += nth) sur[i] = a.u_right[ko + i];
     const uint4* src = reinterpret_cast<const uint4*>(a.desc + ko * 32);
     uint4* dst = reinterpret_cast<uint4*>(sdesc);
     for (int i = tid; i < a.cap * 2; i += nth) dst[i] = __ldg(src + i);
@@ -245,12 +252,13 @@ __device__ __forceinline__ void project_search_problem(const ProjSearchArgs& a, 
       uint32_t qd[8];
 #pragma unroll
       for (int w = 0; w < 8; ++w) qd[w] = __shfl_sync(0xffffffffu, dw, w);
-      unsigned bd = 0xffffffffu, be = 0xffffffffu;             // least (distance, CSR position)
+      unsigned bd = 0xffffffffu, be = 0xffffffffu;             // least (distance, cell << 16 | keypoint)
       for_each_in_columns(cx0, cx1, lane,
         [&](int ix, int& e_lo, int& e_hi) { e_lo = cs[ix * kPGridRows + cy0]; e_hi = cs[ix * kPGridRows + cy1 + 1]; },
         [&](int e, int) {
           const uint32_t meta = smeta[e];
-          const int idx = (int)(meta & 0xFFFFFFu), oct = (int)(meta >> 24);
+          const int idx = (int)(meta & 0xFFFFu), oct = (int)(meta >> 28);
+          const uint32_t ck = meta & 0x0FFFFFFFu;               // cell << 16 | keypoint: the reference's enumeration order
           const float2 pt = sxy[e];
           if (!(fabsf(__fsub_rn(pt.x, u)) < radius && fabsf(__fsub_rn(pt.y, v)) < radius)) return;
           if (oct < level - 1 || oct > level) return;
@@ -270,11 +278,11 @@ __device__ __forceinline__ void project_search_problem(const ProjSearchArgs& a, 
           const uint4 b0 = *reinterpret_cast<const uint4*>(g), b1 = *reinterpret_cast<const uint4*>(g + 4);
           const unsigned d = __popc(qd[0] ^ b0.x) + __popc(qd[1] ^ b0.y) + __popc(qd[2] ^ b0.z) + __popc(qd[3] ^ b0.w) + __popc(qd[4] ^ b1.x) +
                              __popc(qd[5] ^ b1.y) + __popc(qd[6] ^ b1.z) + __popc(qd[7] ^ b1.w);
-          if (d < bd || (d == bd && (unsigned)e < be)) { bd = d; be = (unsigned)e; }
+          if (d < bd || (d == bd && ck < be)) { bd = d; be = ck; }
         });
       const unsigned wd = __reduce_min_sync(0xffffffffu, bd);
       const unsigned we = __reduce_min_sync(0xffffffffu, bd == wd ? be : 0xffffffffu);
-      if (lane == 0) a.best[mo + base + r] = (wd != 0xffffffffu && (int)wd <= a.th_dist) ? (int)(smeta[we] & 0xFFFFFFu) : -1;
+      if (lane == 0) a.best[mo + base + r] = (wd != 0xffffffffu && (int)wd <= a.th_dist) ? (int)(we & 0xFFFFu) : -1;
     }
     __syncthreads();                                            // the block's windows are free again
   }
@@ -324,7 +332,7 @@ __global__ void __launch_bounds__(kPsLatThreads) k_sim3_lat(const __grid_constan
 int launch_sim3_lat(const ProjSearchArgs& a0, const ProjSearchArgs& a1, const int* idx0, const int* idx1, int* vn0, int* vn1, int* ticket, const int* n1,
                     int* matches12, int* nfound, cudaStream_t st) {
   const size_t lat = ps_lat_bytes(a0.cap, false);
-  if (!(lat <= 200 * 1024 && a0.cap < (1 << 24)) || getenv("ORBX_PROJ_SERIAL")) return 0;      // the caller takes the five-launch route
+  if (!(lat <= 200 * 1024 && a0.cap <= 65536) || getenv("ORBX_PROJ_SERIAL")) return 0;      // the caller takes the five-launch route
   Sim3LatArgs A;
   A.pass[0] = a0; A.pass[1] = a1; A.mp_index[0] = idx0; A.mp_index[1] = idx1; A.vn[0] = vn0; A.vn[1] = vn1; A.ticket = ticket; A.n1 = n1;
   A.matches12 = matches12; A.nfound = nfound;
@@ -548,13 +556,13 @@ __device__ __forceinline__ uint4 ordered_scan_staged(const ProjOrderedArgs& a, c
   w.u = __uint_as_float(win.x); w.v = __uint_as_float(win.y); w.radius = __uint_as_float(win.z);
   w.level = (int)((win.w >> 24) & 15u); w.lvl_hi = a.reloc ? w.level + 1 : w.level;
   w.cx0 = (int)((win.w >> 18) & 63u); w.cx1 = (int)((win.w >> 12) & 63u); w.cy0 = (int)((win.w >> 6) & 63u); w.cy1 = (int)(win.w & 63u);
-  unsigned long long k1 = ~0ull, k2 = ~0ull;                  // (distance << 8 | cell column) << 32 | CSR position
+  unsigned long long k1 = ~0ull, k2 = ~0ull;                  // distance << 32 | cell << 16 | keypoint
   int cnt = 0;
   for_each_in_columns(w.cx0, w.cx1, lane,
     [&](int ix, int& e_lo, int& e_hi) { e_lo = S.cs[ix * kPGridRows + w.cy0]; e_hi = S.cs[ix * kPGridRows + w.cy1 + 1]; },
-    [&](int e, int ix) {
+    [&](int e, int) {
       const uint32_t meta = S.smeta[e];
-      const int idx = (int)(meta & 0xFFFFFFu), oct = (int)(meta >> 24);
+      const int idx = (int)(meta & 0xFFFFu), oct = (int)(meta >> 28);
       if ((S.occ[idx >> 5] >> (idx & 31)) & 1u) return;
       const float2 pt = S.sxy[e];
       if (!(fabsf(__fsub_rn(pt.x, w.u)) < w.radius && fabsf(__fsub_rn(pt.y, w.v)) < w.radius)) return;
@@ -563,7 +571,7 @@ __device__ __forceinline__ uint4 ordered_scan_staged(const ProjOrderedArgs& a, c
       const uint4 b0 = *reinterpret_cast<const uint4*>(g), b1 = *reinterpret_cast<const uint4*>(g + 4);
       const int d = __popc(qd[0] ^ b0.x) + __popc(qd[1] ^ b0.y) + __popc(qd[2] ^ b0.z) + __popc(qd[3] ^ b0.w) + __popc(qd[4] ^ b1.x) +
                     __popc(qd[5] ^ b1.y) + __popc(qd[6] ^ b1.z) + __popc(qd[7] ^ b1.w);
-      const unsigned long long key = ((unsigned long long)(((unsigned)d << 8) | (unsigned)ix) << 32) | (unsigned)e;
+      const unsigned long long key = ((unsigned long long)(unsigned)d << 32) | (meta & 0x0FFFFFFFu);   // (distance, cell, index): the reference's order
       ++cnt;
       if (key < k1) { k2 = k1; k1 = key; }
       else if (key < k2) k2 = key;
@@ -573,7 +581,7 @@ __device__ __forceinline__ uint4 ordered_scan_staged(const ProjOrderedArgs& a, c
   warp_top4(k1, k2, cnt, hi, lo, complete);
   uint32_t l[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : (((hi[k] >> 8) << 16) | (S.smeta[lo[k]] & 0xFFFFu));
+  for (int k = 0; k < 4; ++k) l[k] = hi[k] == 0xffffffffu ? kNoKey : ((hi[k] << 16) | (lo[k] & 0xFFFFu));
   return make_uint4(l[0] | (complete ? 0x80000000u : 0u), l[1], l[2], l[3]);
 }
 
@@ -599,7 +607,8 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
   S.stag = S.sasg + a.cap;
   S.occ = reinterpret_cast<uint32_t*>(S.stag + a.cap);
   uint16_t* slist = reinterpret_cast<uint16_t*>(smem + ord_stage_bytes(a.cap));   // [mcap] the map points that have a search window, in list order
-  {
+  const float* gbs = a.grid_bounds;
+  if (a.cell_start) {                                           // the caller's CSR grid (K10's output): copied in its order
     const int* cs = a.cell_start + (size_t)p * (kPCells + 1);
     const int* items = a.cell_items + ko;
     for (int i = tid; i <= kPCells; i += nth) S.cs[i] = cs[i];
@@ -607,9 +616,15 @@ __global__ void __launch_bounds__(kOrdParThreads) k_project_match_ordered_par(Pr
     for (int e = tid; e < n_items; e += nth) {
       const int idx = items[e];
       const orbx_keypoint kp = kps[idx];
+      const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, gbs[0]), gbs[4])), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, gbs[2]), gbs[5]));
       S.sxy[e] = make_float2(kp.x, kp.y);
-      S.smeta[e] = ((uint32_t)kp.octave << 24) | (uint32_t)idx;
+      S.smeta[e] = ((uint32_t)kp.octave << 28) | ((uint32_t)(gx * kPGridRows + gy) << 16) | (uint32_t)idx;
     }
+  } else {                                                      // no grid given: built here (cell = PosInGrid of the keypoint)
+    grid_sort_cta(kps, n, gbs[0], gbs[2], gbs[4], gbs[5], S.cs, S.sxy, S.smeta);
+    S.cs += 1;
+  }
+  {
     const uint4* src = reinterpret_cast<const uint4*>(a.desc + ko * 32);
     uint4* dst = reinterpret_cast<uint4*>(S.sdesc);
     for (int i = tid; i < n * 2; i += nth) dst[i] = __ldg(src + i);
@@ -781,9 +796,15 @@ int launch_project_match_ordered(const ProjOrderedArgs& a, cudaStream_t st) {
   return 1;
 }
 
+// do the launchers below take the small forms, which walk the caller's CSR grid in global memory (the 1024-thread forms can build it)?
+bool project_search_needs_grid(int cap, bool gate) { return !(ps_lat_bytes(cap, gate) <= 200 * 1024 && cap <= 65536) || getenv("ORBX_PROJ_SERIAL"); }
+bool project_ordered_needs_grid(int cap, int mcap) {
+  return !(ord_stage_bytes(cap) + (size_t)mcap * 2 <= 200 * 1024 && cap <= 65536 && mcap <= 65536) || getenv("ORBX_PROJ_SERIAL");
+}
+
 int launch_project_search(const ProjSearchArgs& a, cudaStream_t st) {
   const size_t lat = ps_lat_bytes(a.cap, (a.mode & 8) != 0);
-  if (lat <= 200 * 1024 && a.cap < (1 << 24) && !getenv("ORBX_PROJ_SERIAL")) {
+  if (lat <= 200 * 1024 && a.cap <= 65536 && !getenv("ORBX_PROJ_SERIAL")) {
     cudaFuncSetAttribute(k_project_search_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lat);
     k_project_search_lat<<<a.n_problems, kPsLatThreads, lat, st>>>(a);
   } else {

@@ -1104,6 +1104,45 @@ cudaError_t fetch_levels(float* dst, const float* src, int nlevels, int on_devic
 }
 }  // namespace
 
+}  // extern "C"
+
+// The CSR feature grid of the projection searches: the caller's (K10's output), or none - the 1024-thread kernels build it in
+// shared memory from the keypoints.  When the small kernels will run (large capacities), host callers get it built here with
+// Frame::PosInGrid's rule (src/Frame.cc:382-392); device callers must pass it then.
+template <class SG>
+static orbx_status stage_grid(SG& sg, const int* cell_start, const int* cell_items, const orbx_keypoint* kps, const int* n, size_t np, int cap, const float* grid_bounds,
+                              int on_device, bool needs_grid, const int** d_cs, const int** d_items) {
+  const size_t cells = np * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1), kc = np * cap;
+  if ((cell_start == nullptr) != (cell_items == nullptr)) return fail(ORBX_ERR_BAD_ARG, "cell_start and cell_items go together");
+  if (cell_start) {
+    if (sg.in(cell_start, cells, on_device, d_cs) != cudaSuccess || sg.in(cell_items, kc, on_device, d_items) != cudaSuccess) return fail(ORBX_ERR_CUDA, "staging the grid");
+    return ORBX_OK;
+  }
+  *d_cs = nullptr; *d_items = nullptr;
+  if (!needs_grid) return ORBX_OK;
+  if (on_device) return fail(ORBX_ERR_BAD_ARG, "cell_start / cell_items are required for device arrays of this capacity");
+  std::vector<int> cs(cells, 0), items(kc, 0);
+  const int nc = ORBX_GRID_COLS * ORBX_GRID_ROWS;
+  for (size_t p = 0; p < np; ++p) {
+    int* c0 = cs.data() + p * (nc + 1);
+    const orbx_keypoint* k = kps + p * cap;
+    const int np_ = std::min(n[p], cap);
+    std::vector<int> cell(np_, -1);
+    for (int i = 0; i < np_; ++i) {
+      const int gx = (int)roundf((k[i].x - grid_bounds[0]) * grid_bounds[4]), gy = (int)roundf((k[i].y - grid_bounds[2]) * grid_bounds[5]);
+      if (gx < 0 || gx >= ORBX_GRID_COLS || gy < 0 || gy >= ORBX_GRID_ROWS) continue;
+      cell[i] = gx * ORBX_GRID_ROWS + gy; ++c0[cell[i] + 1];
+    }
+    for (int c = 1; c <= nc; ++c) c0[c] += c0[c - 1];
+    std::vector<int> cur(c0, c0 + nc);
+    for (int i = 0; i < np_; ++i) if (cell[i] >= 0) items[p * cap + cur[cell[i]]++] = i;
+  }
+  if (sg.in(cs.data(), cells, 0, d_cs) != cudaSuccess || sg.in(items.data(), kc, 0, d_items) != cudaSuccess) return fail(ORBX_ERR_CUDA, "staging the grid");
+  return ORBX_OK;
+}
+
+extern "C" {
+
 orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* desc, const float* u_right, const int* n, int n_kfs, int cap,
                                    const float* grid_bounds, const int* cell_start, const int* cell_items, const float* kf_bounds,
                                    const float* pose, const float* Ow, float fx, float fy, float cx, float cy, float bf,
@@ -1111,7 +1150,7 @@ orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* d
                                    const uint8_t* mp_valid, const float* mp_xw, const float* mp_normal, const float* mp_min_dist,
                                    const float* mp_max_dist, const uint8_t* mp_desc, const int* m, int mcap, float th, int sim3_variant,
                                    int* best_idx, int on_device, void* stream) {
-  if (!kps_un || !desc || !u_right || !n || !grid_bounds || !cell_start || !cell_items || !kf_bounds || !pose || !Ow || !scale_factors ||
+  if (!kps_un || !desc || !u_right || !n || !grid_bounds || !kf_bounds || !pose || !Ow || !scale_factors ||
       !inv_level_sigma2 || !mp_valid || !mp_xw || !mp_normal || !mp_min_dist || !mp_max_dist || !mp_desc || !m || !best_idx)
     return fail(ORBX_ERR_BAD_ARG, "null argument");
   if (n_kfs < 1 || n_kfs > 65535 || cap < 1 || mcap < 1 || nlevels < 1 || nlevels > kMaxLevels || !(log_scale_factor > 0.f))
@@ -1121,7 +1160,9 @@ orbx_status orbx_fuse_search_batch(const orbx_keypoint* kps_un, const uint8_t* d
   const size_t np = (size_t)n_kfs, kc = np * cap, mc = np * mcap, cells = np * (ORBX_GRID_COLS * ORBX_GRID_ROWS + 1);
   ProjSearchArgs a;
   CU(sg.in(kps_un, kc, on_device, &a.kps)); CU(sg.in(desc, kc * 32, on_device, &a.desc)); CU(sg.in(u_right, kc, on_device, &a.u_right));
-  CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds)); CU(sg.in(cell_start, cells, on_device, &a.cell_start)); CU(sg.in(cell_items, kc, on_device, &a.cell_items));
+  CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds));
+  if (stage_grid(sg, cell_start, cell_items, kps_un, n, np, cap, grid_bounds, on_device, project_search_needs_grid(cap, true), &a.cell_start, &a.cell_items) != ORBX_OK) return ORBX_ERR_BAD_ARG;
+  CU(sg.in(n, np, on_device, &a.n));
   CU(sg.in(kf_bounds, np * 4, on_device, &a.kf_bounds));
   // xf per problem: R1 t1 | R2 t2 (unused) | Ow
   if (on_device) {
@@ -1159,7 +1200,7 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
                                       const int* mp2_index, const float* mp2_xw, const float* mp2_min_dist, const float* mp2_max_dist,
                                       const uint8_t* mp2_desc, const int* m2, int mcap, float th, int* matches12, int* n_found, int on_device,
                                       void* stream) {
-  if (!kps1 || !desc1 || !n1 || !cell_start1 || !cell_items1 || !kf_bounds1 || !pose1 || !kps2 || !desc2 || !n2 || !cell_start2 || !cell_items2 ||
+  if (!kps1 || !desc1 || !n1 || !kf_bounds1 || !pose1 || !kps2 || !desc2 || !n2 ||
       !kf_bounds2 || !pose2 || !grid_bounds || !scale_factors || !xf || !mp1_index || !mp1_xw || !mp1_min_dist || !mp1_max_dist || !mp1_desc || !m1 ||
       !mp2_index || !mp2_xw || !mp2_min_dist || !mp2_max_dist || !mp2_desc || !m2 || !matches12 || !n_found)
     return fail(ORBX_ERR_BAD_ARG, "null argument");
@@ -1183,7 +1224,9 @@ orbx_status orbx_search_by_sim3_batch(const orbx_keypoint* kps1, const uint8_t* 
     const bool fwd = pass == 0;
     CU(sg.in(fwd ? kps2 : kps1, kc, on_device, &a.kps)); CU(sg.in(fwd ? desc2 : desc1, kc * 32, on_device, &a.desc));
     a.u_right = nullptr; a.grid_bounds = d_gb;
-    CU(sg.in(fwd ? cell_start2 : cell_start1, cells, on_device, &a.cell_start)); CU(sg.in(fwd ? cell_items2 : cell_items1, kc, on_device, &a.cell_items));
+    if (stage_grid(sg, fwd ? cell_start2 : cell_start1, fwd ? cell_items2 : cell_items1, fwd ? kps2 : kps1, fwd ? n2 : n1, np, cap, grid_bounds, on_device,
+                   project_search_needs_grid(cap, false), &a.cell_start, &a.cell_items) != ORBX_OK) return ORBX_ERR_BAD_ARG;
+    CU(sg.in(fwd ? n2 : n1, np, on_device, &a.n));
     CU(sg.in(fwd ? kf_bounds2 : kf_bounds1, np * 4, on_device, &a.kf_bounds));
     if (on_device) {
       float* d_xf = nullptr;
@@ -1245,7 +1288,7 @@ orbx_status orbx_search_projection_ordered_batch(const orbx_keypoint* kps_un, co
                                                  const float* mp_min_dist, const float* mp_max_dist, const uint8_t* mp_desc,
                                                  const float* mp_src_angle, const int* m, int mcap, float th, int max_dist, int relocalisation,
                                                  int check_orientation, int* assigned, int* n_matches, int on_device, void* stream) {
-  if (!kps_un || !desc || !n || !grid_bounds || !cell_start || !cell_items || !target_bounds || !pose || !Ow || !scale_factors || !occupied ||
+  if (!kps_un || !desc || !n || !grid_bounds || !target_bounds || !pose || !Ow || !scale_factors || !occupied ||
       !mp_valid || !mp_xw || !mp_normal || !mp_min_dist || !mp_max_dist || !mp_desc || !mp_src_angle || !m || !assigned || !n_matches)
     return fail(ORBX_ERR_BAD_ARG, "null argument");
   if (n_problems < 1 || cap < 1 || mcap < 1 || nlevels < 1 || nlevels > kMaxLevels || !(log_scale_factor > 0.f) || max_dist < 0 || max_dist > 255)
@@ -1256,7 +1299,8 @@ orbx_status orbx_search_projection_ordered_batch(const orbx_keypoint* kps_un, co
   const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   ProjOrderedArgs a;
   CU(sg.in(kps_un, kc, on_device, &a.kps)); CU(sg.in(desc, kc * 32, on_device, &a.desc)); CU(sg.in(n, np, on_device, &a.n));
-  CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds)); CU(sg.in(cell_start, cells, on_device, &a.cell_start)); CU(sg.in(cell_items, kc, on_device, &a.cell_items));
+  CU(sg.in(grid_bounds, 6, on_device, &a.grid_bounds));
+  if (stage_grid(sg, cell_start, cell_items, kps_un, n, np, cap, grid_bounds, on_device, project_ordered_needs_grid(cap, mcap), &a.cell_start, &a.cell_items) != ORBX_OK) return ORBX_ERR_BAD_ARG;
   CU(sg.in(target_bounds, np * 4, on_device, &a.tgt_bounds));
   if (on_device) {
     float* d_xf = nullptr;

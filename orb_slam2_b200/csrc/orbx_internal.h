@@ -185,12 +185,15 @@ struct ProjSearchArgs {
   const float* grid_bounds; const int* cell_start; const int* cell_items; const float* kf_bounds; const float* xf;
   const uint8_t* valid; const float* xw; const float* normal; const float* dmin; const float* dmax; const uint8_t* mp_desc;   // [P][mcap]
   const int* m;
+  const int* n;               // [P] keypoints per target (used when cell_start is null: the 1024-thread form then builds the grid itself)
   int n_problems, cap, mcap, nlevels, mode, th_dist;
   float fx, fy, cx, cy, bf, log_scale, th;
   float scale[kMaxLevels], inv_sigma2[kMaxLevels];
   int* best;
 };
 int launch_project_search(const ProjSearchArgs& a, cudaStream_t st);
+bool project_search_needs_grid(int cap, bool gate);          // true: the small form will run, which needs the caller's CSR grid
+bool project_ordered_needs_grid(int cap, int mcap);
 int launch_scatter_matches(const int* best, const int* mp_index, const int* m, int mcap, int cap, int n_problems, int* vn, cudaStream_t st);
 struct Sim3AgreeArgs { const int* match1; const int* match2; const int* n1; int cap; int* matches12; int* nfound; };
 int launch_sim3_agree(const Sim3AgreeArgs& a, int n_problems, cudaStream_t st);

@@ -1,6 +1,8 @@
 // Shared by the latency forms of the order-dependent matchers (K8, K9 in k_match.cu; K17 in k_project.cu).
 #pragma once
 #include <stdint.h>
+
+#include "orbx_internal.h"
 #ifdef ORBX_PHASE_CLOCKS
 #include <cstdio>
 #endif
@@ -118,6 +120,68 @@ __device__ __forceinline__ void for_each_in_columns(int cx0, int cx1, int lane, 
       if (f < total) body(e0 + (f - x0), cb + col);
     }
   }
+}
+
+// Counting sort of a frame's keypoints by 64 x 48 grid cell (Frame::AssignFeaturesToGrid / PosInGrid, src/Frame.cc:230-245,
+// 382-392) by the whole CTA, into shared memory: on return soff[c + 1] = first position of cell c (c = gx * 48 + gy) and
+// soff[kOrdGridCells + 1] = the number of keypoints in the grid; sxy / smeta hold position and  octave << 28 | cell << 16 | index
+// per position.  The order inside a cell is arbitrary - callers rank candidates by (distance, cell, index), which is the
+// reference's enumeration order whatever the storage order.  soff needs kOrdGridCells + 2 ints.  Ends with a block barrier.
+constexpr int kOrdGridCells = 64 * 48;
+__device__ __forceinline__ int grid_sort_cta(const orbx_keypoint* k, int n, float minX, float minY, float invW, float invH, int* soff, float2* sxy,
+                                             uint32_t* smeta) {
+  __shared__ int s_gw[32];
+  __shared__ int s_gt;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nth = blockDim.x;
+  for (int i = tid; i <= kOrdGridCells + 1; i += nth) soff[i] = 0;
+  __syncthreads();
+  for (int i = tid; i < n; i += nth) {
+    const orbx_keypoint kp = k[i];
+    const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) atomicAdd(&soff[gx * 48 + gy + 1], 1);
+  }
+  __syncthreads();
+  const int ch = (kOrdGridCells + nth) / nth, b0 = tid * ch;    // inclusive scan of soff[0 .. kOrdGridCells]
+  int sum = 0;
+  for (int j = 0; j < ch; ++j) sum += (b0 + j <= kOrdGridCells) ? soff[b0 + j] : 0;
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_gw[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    const int own = lane < (nth >> 5) ? s_gw[lane] : 0;
+    int v = own;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += t;
+    }
+    s_gw[lane] = v - own;
+    if (lane == 31) s_gt = v;
+  }
+  __syncthreads();
+  int run = s_gw[warp] + incl - sum;
+  for (int j = 0; j < ch; ++j)
+    if (b0 + j <= kOrdGridCells) { run += soff[b0 + j]; soff[b0 + j] = run; }   // soff[c + 1] = end of cell c
+  __syncthreads();
+  for (int i = tid; i < n; i += nth) {                           // fill each cell from its end downwards: soff[c + 1] = start of cell c
+    const orbx_keypoint kp = k[i];
+    const int gx = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), invW)), gy = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), invH));
+    if (gx >= 0 && gx < 64 && gy >= 0 && gy < 48) {
+      const int c = gx * 48 + gy;
+      const int pos = atomicSub(&soff[c + 1], 1) - 1;
+      sxy[pos] = make_float2(kp.x, kp.y);
+      smeta[pos] = ((uint32_t)kp.octave << 28) | ((uint32_t)c << 16) | (uint32_t)i;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) soff[kOrdGridCells + 1] = s_gt;
+  __syncthreads();
+  return s_gt;
 }
 
 }  // namespace orbx
