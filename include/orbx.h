@@ -298,7 +298,10 @@ orbx_status orbx_search_triangulation_batch(const orbx_keypoint* kps1, const uin
 
 /* The search of ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975; src/LocalMapping.cc:483-534) for n_kfs
  * independent (keyframe, candidate list) problems.  Keyframe p at index p*cap: kps_un = mvKeysUn, desc, u_right = mvuRight,
- * n[p] features; its feature grid as orbx_undistort_grid_batch returns it (grid_bounds[6], cell_start, cell_items);
+ * n[p] features; its feature grid as orbx_undistort_grid_batch returns it (grid_bounds[6], cell_start, cell_items) - or
+ * cell_start = cell_items = NULL: the library then assigns the keypoints to cells itself with Frame::PosInGrid's rule and
+ * grid_bounds (inside the kernel; on the host for capacities above ~3300 features, where device callers must pass the
+ * grid).  The same holds for orbx_search_by_sim3_batch and orbx_search_projection_ordered_batch;
  * kf_bounds + p*4 = the KeyFrame's own mnMinX, mnMaxX, mnMinY, mnMaxY (ints in the reference, include/KeyFrame.h:185-188);
  * pose + p*12 = Rcw row-major then tcw; Ow + p*3 = GetCameraCenter(); fx..bf, scale_factors, inv_level_sigma2,
  * log_scale_factor = mfLogScaleFactor are the keyframe's.  Candidate k of problem p at index p*mcap + k: mp_valid =

@@ -91,7 +91,10 @@ def test_keyframe_searches_with_gpu_stereo_frames(oracle, all_three):
     _same(ref, gpu)
 
 
-def test_monocular_frames_and_initialisation(oracle, both):
+@pytest.mark.parametrize("form", ["latency", "small"])
+def test_monocular_frames_and_initialisation(oracle, both, form, monkeypatch):
+    if form == "small":
+        monkeypatch.setenv("ORBX_PROJ_SERIAL", "1")
     a, b, _ = synth.mono_pair(60, 640, 480)
     ref, gpu = both(oracle.ref_slam_init, a, b, 1000, (517.3, 516.5, 318.6, 255.3), 0.9, 100, True)
     _same(ref, gpu)
@@ -106,8 +109,14 @@ def test_distorted_camera_grid(oracle, both):
     _same(ref, gpu)
 
 
+@pytest.mark.parametrize("form", ["latency", "small"])
 @pytest.mark.parametrize("fuse_scw", [False, True])
-def test_keyframes_mappoints_and_every_matcher_member(oracle, both, fuse_scw):
+def test_keyframes_mappoints_and_every_matcher_member(oracle, both, fuse_scw, form, monkeypatch):
+    """Every ORBmatcher member of the drop-in against the reference's, in both device forms of the matcher kernels: the 1024-thread
+    form (which builds the feature grid itself: the drop-in passes none) and, with ORBX_PROJ_SERIAL / ORBX_BOW_SERIAL in the child's
+    environment, the small form (for which the library builds the grid on the host)."""
+    if form == "small":
+        monkeypatch.setenv("ORBX_PROJ_SERIAL", "1"); monkeypatch.setenv("ORBX_BOW_SERIAL", "1")
     import importlib.util
     spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
     kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
