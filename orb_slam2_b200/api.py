@@ -474,6 +474,8 @@ class FrameGrids:
 
 class ORBmatcher:
     """ORB_SLAM2::ORBmatcher (include/ORBmatcher.h:41-89): the two searches on the hot path."""
+    PASS_GRID = True     # False: the projection searches get cell_start = cell_items = NULL and build the feature grid themselves
+
     TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30
 
     def __init__(self, nnratio=0.6, checkOri=True):
@@ -621,8 +623,8 @@ class ORBmatcher:
         kb = f32(kf_bounds); sc = f32(scale_factors); isg = f32(inv_level_sigma2); ow = f32(Ow)
         arrs = [pad(mp["valid"], (), np.uint8), pad(mp["xw"], (3,), np.float32), pad(mp["normal"], (3,), np.float32), pad(mp["dmin"], (), np.float32),
                 pad(mp["dmax"], (), np.float32), pad(mp["desc"], (32,), np.uint8)]
-        _check(lib().orbx_fuse_search_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, nn.ctypes.data, 1, cap, grids.bounds.ctypes.data, cs.ctypes.data,
-                                            ci.ctypes.data, kb.ctypes.data, pose.ctypes.data, ow.ctypes.data, *[float(v) for v in cam], sc.ctypes.data,
+        _check(lib().orbx_fuse_search_batch(k.ctypes.data, d.ctypes.data, ur.ctypes.data, nn.ctypes.data, 1, cap, grids.bounds.ctypes.data, cs.ctypes.data if ORBmatcher.PASS_GRID else None,
+                                            ci.ctypes.data if ORBmatcher.PASS_GRID else None, kb.ctypes.data, pose.ctypes.data, ow.ctypes.data, *[float(v) for v in cam], sc.ctypes.data,
                                             isg.ctypes.data, len(sc), float(log_scale_factor), *[a.ctypes.data for a in arrs], mm.ctypes.data, mcap,
                                             float(th), int(sim3_variant), best.ctypes.data, 0, None))
         return best[:m].copy()
@@ -644,8 +646,8 @@ class ORBmatcher:
         k = np.ascontiguousarray(grids.kps_un[f]); cs = np.ascontiguousarray(grids.cell_start[f]); ci = np.ascontiguousarray(grids.cell_items[f])
         nn = np.array([n], np.int32); mm = np.array([m], np.int32)
         assigned = np.zeros(cap, np.int32); nm = np.zeros(1, np.int32)
-        _check(lib().orbx_search_projection_ordered_batch(k.ctypes.data, d.ctypes.data, nn.ctypes.data, 1, cap, grids.bounds.ctypes.data, cs.ctypes.data,
-                                                          ci.ctypes.data, tb.ctypes.data, pose.ctypes.data, ow.ctypes.data, *[float(v) for v in cam[:4]],
+        _check(lib().orbx_search_projection_ordered_batch(k.ctypes.data, d.ctypes.data, nn.ctypes.data, 1, cap, grids.bounds.ctypes.data, cs.ctypes.data if ORBmatcher.PASS_GRID else None,
+                                                          ci.ctypes.data if ORBmatcher.PASS_GRID else None, tb.ctypes.data, pose.ctypes.data, ow.ctypes.data, *[float(v) for v in cam[:4]],
                                                           sc.ctypes.data, len(sc), float(log_scale_factor), occ.ctypes.data, *[a.ctypes.data for a in arrs],
                                                           mm.ctypes.data, mcap, float(th), int(max_dist), int(relocalisation),
                                                           int(self.mbCheckOrientation), assigned.ctypes.data, nm.ctypes.data, 0, None))
@@ -673,7 +675,8 @@ class ORBmatcher:
         A, B, M1, M2 = side(0, desc1, pose1), side(1, desc2, pose2), mps(mp1), mps(mp2)
         sc = f32(scale_factors); x = f32(xf).reshape(24)
         m12 = np.zeros(cap, np.int32); nf = np.zeros(1, np.int32)
-        _check(lib().orbx_search_by_sim3_batch(*[a.ctypes.data for a in A], *[b.ctypes.data for b in B], 1, cap, grids.bounds.ctypes.data,
+        gp = lambda S: [(None if (q in (3, 4) and not ORBmatcher.PASS_GRID) else a.ctypes.data) for q, a in enumerate(S)]
+        _check(lib().orbx_search_by_sim3_batch(*gp(A), *gp(B), 1, cap, grids.bounds.ctypes.data,
                                                *[float(v) for v in cam[:4]], sc.ctypes.data, len(sc), float(log_scale_factor), x.ctypes.data,
                                                *[a.ctypes.data for a in M1], *[a.ctypes.data for a in M2], mcap, float(th), m12.ctypes.data,
                                                nf.ctypes.data, 0, None))

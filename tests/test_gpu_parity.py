@@ -913,11 +913,15 @@ def test_cuda_keyframe_searches_reproduce_reference(gx, monkeypatch, form):
     assert hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest() == kc.GOLD["distinct"]["chosen_sha256"]
 
 
+@pytest.mark.parametrize("grid", ["given", "built"])
 @FORMS
-def test_cuda_fuse_and_sim3_reproduce_reference(gx, oracle, monkeypatch, form):
+def test_cuda_fuse_and_sim3_reproduce_reference(gx, oracle, monkeypatch, form, grid):
     """K16 against ORBmatcher::Fuse (search) and ORBmatcher::SearchBySim3 of the REFERENCE on real KeyFrames and MapPoints
     (tests/golden/ref_kf_*.npz): frames, stereo, the feature grid (K10) come from the CUDA path, MapPoint fields from the fixture."""
     _pick_form(monkeypatch, form)
+    # grid = built: cell_start / cell_items are NULL and the library assigns keypoints to cells itself (in the kernel for the
+    # 1024-thread form, on the host for the small form) - what the drop-in does
+    monkeypatch.setattr(gx.ORBmatcher, "PASS_GRID", grid == "given")
     import importlib.util, os
     spec = importlib.util.spec_from_file_location("kf_cases", os.path.join(os.path.dirname(__file__), "kf_cases.py"))
     kc = importlib.util.module_from_spec(spec); spec.loader.exec_module(kc)
